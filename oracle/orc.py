@@ -1,0 +1,206 @@
+"""ORACLE (test infrastructure, not product code): ctypes view of oracle/_build/liborc.so.
+
+CPU restatement of the reference's FE_Q multigrid path (see oracle/mg_oracle.cpp for the
+file:line map). Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+``--impl reference`` legs may import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "_build", "liborc.so")
+
+
+def build(force=False):
+    src = [os.path.join(_HERE, f) for f in ("mg_oracle.cpp", "basis1d.h", "Makefile")]
+    if (not force and os.path.exists(_LIB)
+            and all(os.path.getmtime(_LIB) >= os.path.getmtime(s) for s in src)):
+        return _LIB
+    subprocess.check_call(["make", "-C", _HERE], stdout=subprocess.DEVNULL)
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB):
+            build()
+        L = C.CDLL(_LIB)
+        dp = C.POINTER(C.c_double)
+        ip = C.POINTER(C.c_int)
+        L.orc_mg_create.restype = C.c_void_p
+        L.orc_mg_create.argtypes = [C.c_int, ip, C.c_int, dp, dp, C.c_uint, C.c_uint, C.c_uint, C.c_int]
+        L.orc_mg_destroy.argtypes = [C.c_void_p]
+        L.orc_mg_n_levels.argtypes = [C.c_void_p]
+        L.orc_mg_n_dofs.restype = C.c_longlong
+        L.orc_mg_n_dofs.argtypes = [C.c_void_p, C.c_int]
+        L.orc_mg_dof_grid.argtypes = [C.c_void_p, C.c_int, ip]
+        L.orc_mg_solve.restype = C.c_double
+        L.orc_mg_solve.argtypes = [C.c_void_p, C.c_int, dp]
+        L.orc_mg_solve_cg.restype = C.c_double
+        L.orc_mg_solve_cg.argtypes = [C.c_void_p, C.POINTER(C.c_uint), dp, C.c_int]
+        L.orc_mg_l2_error.restype = C.c_double
+        L.orc_mg_l2_error.argtypes = [C.c_void_p, C.c_int]
+        L.orc_mg_vmult.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp]
+        L.orc_mg_vmult_residual.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp, dp]
+        L.orc_mg_vmult_with_cg_update.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, dp, dp, dp, dp, dp]
+        L.orc_mg_get_vector.argtypes = [C.c_void_p, C.c_int, C.c_int, dp]
+        L.orc_mg_inverse_diagonal_dp.argtypes = [C.c_void_p, C.c_int, dp]
+        L.orc_mg_chebyshev_info.argtypes = [C.c_void_p, C.c_int, dp]
+        L.orc_mg_chebyshev_apply.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp]
+        L.orc_mg_transfer.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp]
+        L.orc_mg_vcycle.argtypes = [C.c_void_p, dp, dp]
+        L.orc_mg_time_matvec.restype = C.c_double
+        L.orc_mg_time_matvec.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.orc_mg_setup_times.argtypes = [C.c_void_p, dp]
+        L.orc_basis.argtypes = [C.c_int] + [dp] * 7
+        _lib = L
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def basis(p):
+    n = p + 1
+    S, G, D = (np.zeros((n, n)) for _ in range(3))
+    P1 = np.zeros((2 * p + 1, n))
+    gll, xq, wq = (np.zeros(n) for _ in range(3))
+    lib().orc_basis(p, _dp(S), _dp(G), _dp(D), _dp(P1), _dp(gll), _dp(xq), _dp(wq))
+    return dict(S=S, G=G, D=D, P1=P1, gll=gll, xq=xq, wq=wq)
+
+
+VEC_SOLUTION, VEC_RHS, VEC_INV_DIAG, VEC_UPDATE, VEC_RESIDUAL, VEC_DEFECT, VEC_CHEB_GUESS = range(7)
+
+
+class MultigridSolver:
+    """multigrid_solver.h:96-782 restated on the CPU; vectors in lexicographic numbering."""
+
+    def __init__(self, degree, n_subdivisions, n_refine, lower=(-0.9,) * 3, upper=(1.0,) * 3,
+                 degree_pre=2, degree_post=2, n_cycles=2, problem=0):
+        if isinstance(n_subdivisions, int):
+            n_subdivisions = (n_subdivisions,) * 3
+        self.degree = degree
+        nsub = (C.c_int * 3)(*n_subdivisions)
+        lo = (C.c_double * 3)(*lower)
+        hi = (C.c_double * 3)(*upper)
+        self.h = lib().orc_mg_create(degree, nsub, n_refine, lo, hi, degree_pre, degree_post, n_cycles, problem)
+        if not self.h:
+            raise ValueError("unsupported degree")
+        self.n_levels = lib().orc_mg_n_levels(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_mg_destroy(self.h)
+            self.h = None
+
+    def n_dofs(self, level=-1):
+        return lib().orc_mg_n_dofs(self.h, self._l(level))
+
+    def dof_grid(self, level=-1):
+        nd = (C.c_int * 3)()
+        lib().orc_mg_dof_grid(self.h, self._l(level), nd)
+        return tuple(nd)
+
+    def _l(self, level):
+        return level if level >= 0 else self.n_levels + level
+
+    def solve(self, do_analyze=False):
+        trace = np.zeros((self.n_levels, 4))
+        r = lib().orc_mg_solve(self.h, int(do_analyze), _dp(trace))
+        return (r, trace) if do_analyze else r
+
+    def solve_cg(self):
+        its = C.c_uint()
+        hist = np.zeros(64)
+        rate = lib().orc_mg_solve_cg(self.h, C.byref(its), _dp(hist), 64)
+        return its.value, rate, hist[:its.value + 1]
+
+    def compute_l2_error(self, level=-1):
+        return lib().orc_mg_l2_error(self.h, self._l(level))
+
+    def vmult(self, src, level=-1, double=True):
+        src = np.ascontiguousarray(src, dtype=np.float64)
+        dst = np.zeros_like(src)
+        lib().orc_mg_vmult(self.h, self._l(level), int(double), _dp(src), _dp(dst))
+        return dst
+
+    def vmult_residual(self, rhs, lhs, level=-1, double=True):
+        rhs = np.ascontiguousarray(rhs, dtype=np.float64)
+        lhs = np.ascontiguousarray(lhs, dtype=np.float64)
+        res = np.zeros_like(rhs)
+        lib().orc_mg_vmult_residual(self.h, self._l(level), int(double), _dp(rhs), _dp(lhs), _dp(res))
+        return res
+
+    def vmult_with_cg_update(self, alpha, beta, r, q, p, x, level=-1):
+        r, q, p, x = (np.array(v, dtype=np.float64) for v in (r, q, p, x))
+        sums = np.zeros(4)
+        lib().orc_mg_vmult_with_cg_update(self.h, self._l(level), alpha, beta, _dp(r), _dp(q), _dp(p), _dp(x), _dp(sums))
+        return sums, q, p, x
+
+    def get_vector(self, which, level=-1):
+        out = np.zeros(self.n_dofs(level))
+        lib().orc_mg_get_vector(self.h, which, self._l(level), _dp(out))
+        return out
+
+    def inverse_diagonal_dp(self, level=-1):
+        out = np.zeros(self.n_dofs(level))
+        lib().orc_mg_inverse_diagonal_dp(self.h, self._l(level), _dp(out))
+        return out
+
+    def chebyshev_info(self, level):
+        info = np.zeros(6)
+        lib().orc_mg_chebyshev_info(self.h, self._l(level), _dp(info))
+        return dict(min_eig=info[0], max_eig=info[1], theta=info[2], delta=info[3],
+                    degree=int(info[4]), cg_iterations=int(info[5]))
+
+    def chebyshev_vmult(self, b, level=-1):
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        x = np.zeros_like(b)
+        lib().orc_mg_chebyshev_apply(self.h, self._l(level), 0, _dp(x), _dp(b))
+        return x
+
+    def chebyshev_step(self, x, b, level=-1):
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        x = np.array(x, dtype=np.float64)
+        lib().orc_mg_chebyshev_apply(self.h, self._l(level), 1, _dp(x), _dp(b))
+        return x
+
+    def prolongate(self, coarse, fine_level, add_to=None):
+        coarse = np.ascontiguousarray(coarse, dtype=np.float64)
+        fine = np.zeros(self.n_dofs(fine_level)) if add_to is None else np.array(add_to, dtype=np.float64)
+        lib().orc_mg_transfer(self.h, self._l(fine_level), 0 if add_to is None else 1, _dp(fine), _dp(coarse))
+        return fine
+
+    def prolongate_no_boundary(self, coarse, fine_level):
+        coarse = np.ascontiguousarray(coarse, dtype=np.float64)
+        fine = np.zeros(self.n_dofs(fine_level))
+        lib().orc_mg_transfer(self.h, self._l(fine_level), 3, _dp(fine), _dp(coarse))
+        return fine
+
+    def restrict_and_add(self, fine, fine_level, coarse=None):
+        fine = np.ascontiguousarray(fine, dtype=np.float64)
+        c = np.zeros(self.n_dofs(self._l(fine_level) - 1)) if coarse is None else np.array(coarse, dtype=np.float64)
+        lib().orc_mg_transfer(self.h, self._l(fine_level), 2, _dp(c), _dp(fine))
+        return c
+
+    def vcycle(self, src):
+        src = np.ascontiguousarray(src, dtype=np.float64)
+        dst = np.zeros_like(src)
+        lib().orc_mg_vcycle(self.h, _dp(dst), _dp(src))
+        return dst
+
+    def time_matvec(self, double=True, n_mv=50):
+        return lib().orc_mg_time_matvec(self.h, int(double), n_mv)
+
+    def setup_times(self):
+        out = np.zeros(3)
+        lib().orc_mg_setup_times(self.h, _dp(out))
+        return out
