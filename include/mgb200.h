@@ -1,0 +1,153 @@
+/* mgb200 — C ABI of the B200-native matrix-free multigrid path.
+ *
+ * The reference (kronbichler/multigrid) has no FFI layer: its boundary is the set of C++
+ * duck-typed concepts that deal.II's solvers and its own MultigridSolver call on the
+ * operator.  Every entry point below names the reference interface it replaces
+ * (file:line under /root/reference).  All functions return 0 on success and a non-zero
+ * code on failure; mgb_last_error() gives the message (the header adapters re-throw it,
+ * mirroring AssertThrow, poisson_cube/program.cc:717-737).  No C++ types, no torch types.
+ *
+ * Conventions
+ *   - handles are opaque pointers; a solver owns its level operators, smoothers,
+ *     transfers and level vectors (multigrid_solver.h:709-751).
+ *   - "device pointer" = plain CUDA device address (e.g. torch.Tensor.data_ptr()).
+ *     "host pointer"   = ordinary host memory; the call copies inside.
+ *   - DoF vectors use the library's renumbered layout (patch interiors first, then
+ *     patch faces/edges/vertices); mgb_solver_lex_map() gives the permutation to the
+ *     lexicographic (x fastest) numbering of the (N_d p + 1)^3 grid.
+ *   - precision: MGB_F32 selects the V-cycle (float) level operator `matrix[level]`,
+ *     MGB_F64 the outer operator `matrix_dp[level]` (multigrid_solver.h:740-745).
+ *   - all work is ordered on one CUDA stream per solver; mgb_solver_sync() waits for it.
+ */
+#ifndef MGB200_H
+#define MGB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mgb_solver_t *mgb_solver;
+
+enum { MGB_F32 = 0, MGB_F64 = 1 };
+
+/* analytic problem definitions evaluated on the device at set-up time */
+enum {
+  MGB_PROBLEM_CUBE_SINE = 0, /* poisson_cube/program.cc:79-144, coefficient 1            */
+  MGB_PROBLEM_SHELL_COEF = 1 /* poisson_shell/program.cc:70-225 functions (variable coeff) */
+};
+
+/* kernel selection for the operator apply */
+enum {
+  MGB_KERNEL_AUTO = 0,     /* Cartesian sum-factorised patch kernel where admissible        */
+  MGB_KERNEL_GENERAL = 1   /* FEEvaluation-style evaluate / q-point op / integrate per cell */
+};
+
+typedef struct mgb_options {
+  int degree;              /* FE_Q degree p, 1..8                 (LaplaceRunTime, poisson_cube/program.cc:614-643) */
+  int n_subdivisions[3];   /* coarse cells per direction           (subdivided_hyper_cube/_rectangle, :528,:542)     */
+  int n_refinements;       /* global refinements = n_levels - 1    (:570)                                            */
+  double lower[3], upper[3];
+  int degree_pre;          /* Chebyshev degree pre-smoother        (multigrid_solver.h:104)                          */
+  int degree_post;         /* must equal degree_pre                (multigrid_solver.h:126-128)                      */
+  int n_cycles;            /* V-cycles per FMG level               (multigrid_solver.h:106)                          */
+  int problem;             /* MGB_PROBLEM_*                                                                          */
+  int kernel;              /* MGB_KERNEL_*                                                                           */
+  int device;              /* CUDA device ordinal                                                                    */
+  int max_patch_cells;     /* cells per patch direction (0 = automatic: 4, 2 or 1)                                   */
+} mgb_options;
+
+const char *mgb_last_error(void);
+int mgb_version(void);
+void mgb_default_options(mgb_options *opt);
+
+/* MultigridSolver<dim,p,float,double>::MultigridSolver   multigrid_solver.h:100-292 */
+int mgb_solver_create(const mgb_options *opt, mgb_solver *out);
+int mgb_solver_destroy(mgb_solver s);
+int mgb_solver_sync(mgb_solver s);
+
+int mgb_solver_n_levels(mgb_solver s);
+int64_t mgb_solver_n_dofs(mgb_solver s, int level);        /* LaplaceOperator::m()  (MatrixFreeOperators::Base) */
+int mgb_solver_dof_grid(mgb_solver s, int level, int nd[3]);
+int mgb_solver_patch_cells(mgb_solver s, int level);
+/* lex_to_dof[i] = library index of the DoF with lexicographic index i (host pointer, n_dofs entries) */
+int mgb_solver_lex_map(mgb_solver s, int level, uint32_t *lex_to_dof);
+
+/* double MultigridSolver::solve(bool do_analyze)          multigrid_solver.h:387-476
+ * trace (host, may be NULL): 4 doubles per level = error start, residual start, residual end, error end */
+int mgb_solver_solve(mgb_solver s, int do_analyze, double *reduction_rate, double *trace);
+/* pair<unsigned,double> MultigridSolver::solve_cg()       multigrid_solver.h:483-493 */
+int mgb_solver_solve_cg(mgb_solver s, unsigned int *iterations, double *reduction_rate);
+/* same, with the right-hand side taken from / the solution returned to HOST buffers in
+ * library numbering (rhs may be NULL = keep the assembled one; solution may be NULL)      */
+int mgb_solver_solve_cg_host(mgb_solver s, const double *rhs_host, double *solution_host,
+                             unsigned int *iterations, double *reduction_rate);
+/* residual history of the last solve_cg (host, up to n entries; returns count via *n)  */
+int mgb_solver_cg_history(mgb_solver s, double *history, int *n);
+/* double MultigridSolver::compute_l2_error(level)         multigrid_solver.h:298-343 */
+int mgb_solver_l2_error(mgb_solver s, int level, double *error);
+/* MultigridSolver::vmult(dst, src)  (one float V-cycle as preconditioner)  multigrid_solver.h:498-510 */
+int mgb_solver_vcycle(mgb_solver s, double *dst_dev, const double *src_dev);
+/* MultigridSolver::do_matvec / do_matvec_smoother         multigrid_solver.h:624-637 */
+int mgb_solver_do_matvec(mgb_solver s);
+int mgb_solver_do_matvec_smoother(mgb_solver s);
+/* MultigridSolver::print_wall_times                       multigrid_solver.h:348-371 : 6 doubles per level */
+int mgb_solver_timings(mgb_solver s, double *timings, int reset);
+/* device address of a solver-owned vector: which = 0 solution, 1 rhs, 2 residual (double);
+ * 3 defect, 4 t, 5 solution_update, 6 inverse diagonal (float)     multigrid_solver.h:709-735 */
+int mgb_solver_vector(mgb_solver s, int which, int level, void **dev_ptr);
+/* const Vector &MultigridSolver::get_solution()           multigrid_solver.h:376-382 (host copy) */
+int mgb_solver_get_solution(mgb_solver s, double *solution_host);
+
+/* LaplaceOperator<3,p,number> on level `level`            laplace_operator.h:56-164; vectors are device pointers
+ * of the operator's number type */
+int mgb_op_vmult(mgb_solver s, int level, int precision, void *dst, const void *src);           /* :575-601 */
+int mgb_op_vmult_add(mgb_solver s, int level, int precision, void *dst, const void *src);       /* Base::vmult_add */
+int mgb_op_Tvmult(mgb_solver s, int level, int precision, void *dst, const void *src);          /* Base::Tvmult (symmetric) */
+int mgb_op_vmult_residual(mgb_solver s, int level, int precision, const void *rhs, const void *lhs,
+                          void *residual);                                                       /* :607-634 */
+/* std::array<number,4> vmult_with_cg_update(alpha,beta,r,q,p,x)                                    :640-719 */
+int mgb_op_vmult_with_cg_update(mgb_solver s, int level, int precision, double alpha, double beta,
+                                const void *r, void *q, void *p, void *x, double sums[4]);
+/* compute_diagonal() + get_matrix_diagonal_inverse(): copies 1/diag to a device buffer            :747-800 */
+int mgb_op_inverse_diagonal(mgb_solver s, int level, int precision, void *inv_diag);
+int mgb_op_set_kernel(mgb_solver s, int kernel);
+
+/* PreconditionChebyshev<LaplaceOperator<float>>  (deal.II; call sites multigrid_solver.h:271-288,657-678) */
+/* info[6] = min_eig, max_eig (Lanczos estimates), theta, delta, degree, eigenvalue-CG iterations */
+int mgb_smoother_info(mgb_solver s, int level, double info[6]);
+int mgb_smoother_vmult(mgb_solver s, int level, float *x, const float *b);  /* zero initial guess   */
+int mgb_smoother_step(mgb_solver s, int level, float *x, const float *b);   /* nonzero guess        */
+
+/* MGTransferMatrixFree<3,number>  (deal.II; call sites multigrid_solver.h:213-221,415,668,674); level = fine level */
+int mgb_transfer_prolongate(mgb_solver s, int level, float *fine, const float *coarse);
+int mgb_transfer_prolongate_and_add(mgb_solver s, int level, float *fine, const float *coarse);
+int mgb_transfer_restrict_and_add(mgb_solver s, int level, float *coarse, const float *fine);
+int mgb_transfer_prolongate_no_boundary(mgb_solver s, int level, double *fine, const double *coarse);
+
+/* plain host<->device helpers so that a C/C++ caller needs no CUDA runtime of its own */
+int mgb_device_alloc(mgb_solver s, size_t bytes, void **dev_ptr);
+int mgb_device_free(mgb_solver s, void *dev_ptr);
+int mgb_copy_to_device(mgb_solver s, void *dst_dev, const void *src_host, size_t bytes);
+int mgb_copy_to_host(mgb_solver s, void *dst_host, const void *src_dev, size_t bytes);
+
+/* number of kernels of this library launched so far on the solver's stream */
+int64_t mgb_solver_launch_count(mgb_solver s);
+
+/* Host-only helpers (no GPU needed; used by the CPU test-suite for the host logic).
+ * 1-D ingredients of FE_Q(p)/QGauss(p+1) (deal.II ShapeInfo as consumed by FEEvaluation,
+ * laplace_operator.h:535): S,G,D,M1,K1 are (p+1)^2, P1 is (2p+1)(p+1), nodes/xq/wq are p+1 */
+int mgb_host_basis(int p, double *S, double *G, double *D, double *M1, double *K1, double *P1,
+                   double *nodes, double *xq, double *wq);
+/* patch-entity numbering of one box level (extract_compressed_indices, laplace_operator.h:226-353);
+ * lex_to_dof may be NULL */
+int mgb_host_numbering(int p, const int ncell[3], int max_patch_cells, int64_t *n_dofs,
+                       int64_t *n_interior, int *patch_cells, int64_t *n_constrained,
+                       uint32_t *lex_to_dof);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,412 @@
+"""multigrid_b200 -- host-side mirror of the reference's solver/operator interface over the C ABI.
+
+The numerical path lives entirely in ``libmgb200.so`` (hand-written sm_100a CUDA behind
+``include/mgb200.h``).  This module is plumbing: it binds the C ABI with ctypes and exposes
+classes that carry the reference's names and call signatures
+
+    MultigridSolver   <-> multigrid::MultigridSolver<3,p,float,double>   common/multigrid_solver.h:96-782
+    LaplaceOperator   <-> multigrid::LaplaceOperator<3,p,number>         common/laplace_operator.h:56-164
+    Smoother          <-> dealii::PreconditionChebyshev                  multigrid_solver.h:271-288
+    Transfer          <-> dealii::MGTransferMatrixFree                   multigrid_solver.h:213-221
+
+PyTorch is used only for device memory (vectors are ``torch.Tensor`` on ``cuda``).  There is no
+CPU fallback: loading fails loudly when the extension is missing, and creating a solver fails
+when no GPU is present.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmgb200.so")
+
+F32, F64 = 0, 1
+PROBLEM_CUBE_SINE, PROBLEM_SHELL_COEF = 0, 1
+KERNEL_AUTO, KERNEL_GENERAL = 0, 1
+
+
+class MgbError(RuntimeError):
+    """Raised where the reference would AssertThrow (poisson_cube/program.cc:717-737)."""
+
+
+class Options(C.Structure):
+    _fields_ = [
+        ("degree", C.c_int),
+        ("n_subdivisions", C.c_int * 3),
+        ("n_refinements", C.c_int),
+        ("lower", C.c_double * 3),
+        ("upper", C.c_double * 3),
+        ("degree_pre", C.c_int),
+        ("degree_post", C.c_int),
+        ("n_cycles", C.c_int),
+        ("problem", C.c_int),
+        ("kernel", C.c_int),
+        ("device", C.c_int),
+        ("max_patch_cells", C.c_int),
+    ]
+
+
+_lib = None
+
+# name -> (restype, argtypes); the full export list of include/mgb200.h
+_vp, _i, _d, _u = C.c_void_p, C.c_int, C.c_double, C.c_uint
+_dp, _ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
+SYMBOLS = {
+    "mgb_last_error": (C.c_char_p, []),
+    "mgb_version": (_i, []),
+    "mgb_default_options": (None, [C.POINTER(Options)]),
+    "mgb_solver_create": (_i, [C.POINTER(Options), C.POINTER(_vp)]),
+    "mgb_solver_destroy": (_i, [_vp]),
+    "mgb_solver_sync": (_i, [_vp]),
+    "mgb_solver_n_levels": (_i, [_vp]),
+    "mgb_solver_n_dofs": (C.c_int64, [_vp, _i]),
+    "mgb_solver_dof_grid": (_i, [_vp, _i, _ip]),
+    "mgb_solver_patch_cells": (_i, [_vp, _i]),
+    "mgb_solver_lex_map": (_i, [_vp, _i, C.POINTER(C.c_uint32)]),
+    "mgb_solver_solve": (_i, [_vp, _i, _dp, _dp]),
+    "mgb_solver_solve_cg": (_i, [_vp, C.POINTER(_u), _dp]),
+    "mgb_solver_solve_cg_host": (_i, [_vp, _vp, _vp, C.POINTER(_u), _dp]),
+    "mgb_solver_cg_history": (_i, [_vp, _dp, _ip]),
+    "mgb_solver_l2_error": (_i, [_vp, _i, _dp]),
+    "mgb_solver_vcycle": (_i, [_vp, _vp, _vp]),
+    "mgb_solver_do_matvec": (_i, [_vp]),
+    "mgb_solver_do_matvec_smoother": (_i, [_vp]),
+    "mgb_solver_timings": (_i, [_vp, _dp, _i]),
+    "mgb_solver_vector": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
+    "mgb_solver_get_solution": (_i, [_vp, _vp]),
+    "mgb_op_vmult": (_i, [_vp, _i, _i, _vp, _vp]),
+    "mgb_op_vmult_add": (_i, [_vp, _i, _i, _vp, _vp]),
+    "mgb_op_Tvmult": (_i, [_vp, _i, _i, _vp, _vp]),
+    "mgb_op_vmult_residual": (_i, [_vp, _i, _i, _vp, _vp, _vp]),
+    "mgb_op_vmult_with_cg_update": (_i, [_vp, _i, _i, _d, _d, _vp, _vp, _vp, _vp, _dp]),
+    "mgb_op_inverse_diagonal": (_i, [_vp, _i, _i, _vp]),
+    "mgb_op_set_kernel": (_i, [_vp, _i]),
+    "mgb_smoother_info": (_i, [_vp, _i, _dp]),
+    "mgb_smoother_vmult": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_smoother_step": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_transfer_prolongate": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_transfer_prolongate_and_add": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_transfer_restrict_and_add": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_transfer_prolongate_no_boundary": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_device_alloc": (_i, [_vp, C.c_size_t, C.POINTER(_vp)]),
+    "mgb_device_free": (_i, [_vp, _vp]),
+    "mgb_copy_to_device": (_i, [_vp, _vp, _vp, C.c_size_t]),
+    "mgb_copy_to_host": (_i, [_vp, _vp, _vp, C.c_size_t]),
+    "mgb_solver_launch_count": (C.c_int64, [_vp]),
+    # host-only helpers
+    "mgb_host_basis": (_i, [_i] + [_dp] * 9),
+    "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), C.POINTER(C.c_int64), _ip,
+                                C.POINTER(C.c_int64), C.POINTER(C.c_uint32)]),
+}
+
+
+def lib():
+    """Load libmgb200.so; there is deliberately no fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise MgbError(
+                "libmgb200.so is missing (%s): build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` or `make -C multigrid_b200/csrc -j8`; there is no CPU fallback" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _check(code):
+    if code != 0:
+        raise MgbError(lib().mgb_last_error().decode())
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def host_basis(p):
+    n = p + 1
+    out = {k: np.zeros((n, n)) for k in ("S", "G", "D", "M1", "K1")}
+    out["P1"] = np.zeros((2 * p + 1, n))
+    for k in ("nodes", "xq", "wq"):
+        out[k] = np.zeros(n)
+    f = lambda a: a.ctypes.data_as(_dp)
+    _check(lib().mgb_host_basis(p, f(out["S"]), f(out["G"]), f(out["D"]), f(out["M1"]), f(out["K1"]),
+                                f(out["P1"]), f(out["nodes"]), f(out["xq"]), f(out["wq"])))
+    return out
+
+
+def host_numbering(p, ncell, max_patch_cells=0, want_map=True):
+    nc = (C.c_int * 3)(*ncell)
+    nd, ni, ncon, M = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int()
+    _check(lib().mgb_host_numbering(p, nc, max_patch_cells, C.byref(nd), C.byref(ni), C.byref(M),
+                                    C.byref(ncon), None))
+    lex = None
+    if want_map:
+        lex = np.zeros(nd.value, dtype=np.uint32)
+        _check(lib().mgb_host_numbering(p, nc, max_patch_cells, C.byref(nd), C.byref(ni), C.byref(M),
+                                        C.byref(ncon), lex.ctypes.data_as(C.POINTER(C.c_uint32))))
+    return dict(n_dofs=nd.value, n_interior=ni.value, patch_cells=M.value, n_constrained=ncon.value,
+                lex_to_dof=lex)
+
+
+class LaplaceOperator:
+    """View of ``matrix[level]`` (float) or ``matrix_dp[level]`` (double) of a solver."""
+
+    def __init__(self, solver, level, precision):
+        self.solver, self.level, self.precision = solver, level, precision
+        import torch
+        self.dtype = torch.float64 if precision == F64 else torch.float32
+
+    def m(self):
+        return self.solver.n_dofs(self.level)
+
+    n = m
+
+    def initialize_dof_vector(self):
+        import torch
+        return torch.zeros(self.m(), dtype=self.dtype, device=self.solver.device)
+
+    def _chk(self, *ts):
+        for t in ts:
+            if t.dtype != self.dtype or t.numel() != self.m() or not t.is_cuda or not t.is_contiguous():
+                raise MgbError("vector does not match the operator (dtype/size/device)")
+
+    def vmult(self, dst, src):
+        self._chk(dst, src)
+        self.solver._torch_sync()
+        _check(lib().mgb_op_vmult(self.solver.h, self.level, self.precision, _ptr(dst), _ptr(src)))
+        self.solver.sync()
+
+    def Tvmult(self, dst, src):
+        self._chk(dst, src)
+        self.solver._torch_sync()
+        _check(lib().mgb_op_Tvmult(self.solver.h, self.level, self.precision, _ptr(dst), _ptr(src)))
+        self.solver.sync()
+
+    def vmult_add(self, dst, src):
+        self._chk(dst, src)
+        self.solver._torch_sync()
+        _check(lib().mgb_op_vmult_add(self.solver.h, self.level, self.precision, _ptr(dst), _ptr(src)))
+        self.solver.sync()
+
+    Tvmult_add = vmult_add
+
+    def vmult_residual(self, rhs, lhs, residual):
+        self._chk(rhs, lhs, residual)
+        self.solver._torch_sync()
+        _check(lib().mgb_op_vmult_residual(self.solver.h, self.level, self.precision, _ptr(rhs), _ptr(lhs),
+                                           _ptr(residual)))
+        self.solver.sync()
+
+    def vmult_with_cg_update(self, alpha, beta, r, q, p, x):
+        self._chk(r, q, p, x)
+        sums = (C.c_double * 4)()
+        self.solver._torch_sync()
+        _check(lib().mgb_op_vmult_with_cg_update(self.solver.h, self.level, self.precision, alpha, beta,
+                                                 _ptr(r), _ptr(q), _ptr(p), _ptr(x), sums))
+        return list(sums)
+
+    def get_matrix_diagonal_inverse(self):
+        d = self.initialize_dof_vector()
+        self.solver._torch_sync()
+        _check(lib().mgb_op_inverse_diagonal(self.solver.h, self.level, self.precision, _ptr(d)))
+        self.solver.sync()
+        return d
+
+    compute_diagonal = get_matrix_diagonal_inverse
+
+
+class MultigridSolver:
+    """Mixed-precision FMG / CG+V-cycle solver on a refined box mesh (one GPU)."""
+
+    def __init__(self, degree, n_subdivisions, n_refinements, lower=(-0.9,) * 3, upper=(1.0,) * 3,
+                 degree_pre=3, degree_post=3, n_cycles=2, problem=PROBLEM_CUBE_SINE,
+                 kernel=KERNEL_AUTO, device=0, max_patch_cells=0):
+        import torch
+        if isinstance(n_subdivisions, int):
+            n_subdivisions = (n_subdivisions,) * 3
+        o = Options()
+        lib().mgb_default_options(C.byref(o))
+        o.degree = degree
+        o.n_subdivisions[:] = list(n_subdivisions)
+        o.n_refinements = n_refinements
+        o.lower[:] = list(lower)
+        o.upper[:] = list(upper)
+        o.degree_pre, o.degree_post, o.n_cycles = degree_pre, degree_post, n_cycles
+        o.problem, o.kernel, o.device, o.max_patch_cells = problem, kernel, device, max_patch_cells
+        self.h = C.c_void_p()
+        self.device = torch.device("cuda", device)
+        self.degree = degree
+        _check(lib().mgb_solver_create(C.byref(o), C.byref(self.h)))
+        self.n_levels = lib().mgb_solver_n_levels(self.h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().mgb_solver_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _torch_sync(self):
+        import torch
+        torch.cuda.synchronize(self.device)
+
+    def sync(self):
+        _check(lib().mgb_solver_sync(self.h))
+
+    def _l(self, level):
+        return level if level >= 0 else self.n_levels + level
+
+    def n_dofs(self, level=-1):
+        return lib().mgb_solver_n_dofs(self.h, self._l(level))
+
+    def dof_grid(self, level=-1):
+        nd = (C.c_int * 3)()
+        _check(lib().mgb_solver_dof_grid(self.h, self._l(level), nd))
+        return tuple(nd)
+
+    def patch_cells(self, level=-1):
+        return lib().mgb_solver_patch_cells(self.h, self._l(level))
+
+    def lex_map(self, level=-1):
+        m = np.zeros(self.n_dofs(level), dtype=np.uint32)
+        _check(lib().mgb_solver_lex_map(self.h, self._l(level), m.ctypes.data_as(C.POINTER(C.c_uint32))))
+        return m.astype(np.int64)
+
+    def matrix(self, level=-1):
+        return LaplaceOperator(self, self._l(level), F32)
+
+    def matrix_dp(self, level=-1):
+        return LaplaceOperator(self, self._l(level), F64)
+
+    # --- reference driver interface (poisson_cube/program.cc:262-380) ---
+    def solve(self, do_analyze=False):
+        r = C.c_double()
+        trace = np.zeros((self.n_levels, 4))
+        _check(lib().mgb_solver_solve(self.h, int(do_analyze), C.byref(r), trace.ctypes.data_as(_dp)))
+        return (r.value, trace) if do_analyze else r.value
+
+    def solve_cg(self):
+        its, rate = C.c_uint(), C.c_double()
+        _check(lib().mgb_solver_solve_cg(self.h, C.byref(its), C.byref(rate)))
+        return its.value, rate.value
+
+    def solve_cg_host(self, rhs_host=None, solution_host=None):
+        """rhs_host / solution_host: pinned torch CPU tensors or numpy arrays (float64)."""
+        its, rate = C.c_uint(), C.c_double()
+        pr = C.c_void_p(rhs_host.data_ptr() if hasattr(rhs_host, "data_ptr") else rhs_host.ctypes.data) \
+            if rhs_host is not None else None
+        ps = C.c_void_p(solution_host.data_ptr() if hasattr(solution_host, "data_ptr")
+                        else solution_host.ctypes.data) if solution_host is not None else None
+        _check(lib().mgb_solver_solve_cg_host(self.h, pr, ps, C.byref(its), C.byref(rate)))
+        return its.value, rate.value
+
+    def cg_history(self):
+        n = C.c_int(1100)
+        hist = np.zeros(1100)
+        _check(lib().mgb_solver_cg_history(self.h, hist.ctypes.data_as(_dp), C.byref(n)))
+        return hist[:n.value]
+
+    def compute_l2_error(self, level=-1):
+        e = C.c_double()
+        _check(lib().mgb_solver_l2_error(self.h, self._l(level), C.byref(e)))
+        return e.value
+
+    def vmult(self, dst, src):
+        """Preconditioner: one float V-cycle (multigrid_solver.h:498-510)."""
+        self._torch_sync()
+        _check(lib().mgb_solver_vcycle(self.h, _ptr(dst), _ptr(src)))
+        self.sync()
+
+    def do_matvec(self):
+        _check(lib().mgb_solver_do_matvec(self.h))
+
+    def do_matvec_smoother(self):
+        _check(lib().mgb_solver_do_matvec_smoother(self.h))
+
+    def get_solution(self):
+        out = np.zeros(self.n_dofs())
+        _check(lib().mgb_solver_get_solution(self.h, C.c_void_p(out.ctypes.data)))
+        return out
+
+    def timings(self, reset=True):
+        t = np.zeros((self.n_levels, 6))
+        _check(lib().mgb_solver_timings(self.h, t.ctypes.data_as(_dp), int(reset)))
+        return t
+
+    def print_wall_times(self):
+        t = self.timings()
+        print("level  smoother    mg_mv     mg_vec    restrict  prolongate  inhomBC")
+        for l in range(1, self.n_levels):
+            print("L%-2d    %-12.4g%-10.4g%-10.4g%-10.4g%-12.4g%-10.4g"
+                  % (l, t[l][5], t[l][0], t[l][4], t[l][1], t[l][2], t[l][3]))
+
+    def launch_count(self):
+        return lib().mgb_solver_launch_count(self.h)
+
+    # --- access to solver-owned vectors as host arrays (library numbering) ---
+    _VEC = dict(solution=(0, np.float64), rhs=(1, np.float64), residual=(2, np.float64),
+                defect=(3, np.float32), t=(4, np.float32), solution_update=(5, np.float32),
+                inverse_diagonal=(6, np.float32))
+
+    def vector_ptr(self, name, level=-1):
+        which, dt = self._VEC[name]
+        p = C.c_void_p()
+        _check(lib().mgb_solver_vector(self.h, which, self._l(level), C.byref(p)))
+        return p, dt
+
+    def get_vector(self, name, level=-1):
+        p, dt = self.vector_ptr(name, level)
+        out = np.zeros(self.n_dofs(level), dtype=dt)
+        self.sync()
+        _check(lib().mgb_copy_to_host(self.h, C.c_void_p(out.ctypes.data), p, out.nbytes))
+        return out
+
+    def set_vector(self, name, values, level=-1):
+        p, dt = self.vector_ptr(name, level)
+        v = np.ascontiguousarray(values, dtype=dt)
+        _check(lib().mgb_copy_to_device(self.h, p, C.c_void_p(v.ctypes.data), v.nbytes))
+
+    # --- smoother / transfer hooks ---
+    def smoother_info(self, level):
+        info = (C.c_double * 6)()
+        _check(lib().mgb_smoother_info(self.h, self._l(level), info))
+        return dict(min_eig=info[0], max_eig=info[1], theta=info[2], delta=info[3], degree=int(info[4]),
+                    cg_iterations=int(info[5]))
+
+    def smoother_vmult(self, level, x, b):
+        self._torch_sync()
+        _check(lib().mgb_smoother_vmult(self.h, self._l(level), _ptr(x), _ptr(b)))
+        self.sync()
+
+    def smoother_step(self, level, x, b):
+        self._torch_sync()
+        _check(lib().mgb_smoother_step(self.h, self._l(level), _ptr(x), _ptr(b)))
+        self.sync()
+
+    def prolongate(self, level, fine, coarse):
+        self._torch_sync()
+        _check(lib().mgb_transfer_prolongate(self.h, self._l(level), _ptr(fine), _ptr(coarse)))
+        self.sync()
+
+    def prolongate_and_add(self, level, fine, coarse):
+        self._torch_sync()
+        _check(lib().mgb_transfer_prolongate_and_add(self.h, self._l(level), _ptr(fine), _ptr(coarse)))
+        self.sync()
+
+    def restrict_and_add(self, level, coarse, fine):
+        self._torch_sync()
+        _check(lib().mgb_transfer_restrict_and_add(self.h, self._l(level), _ptr(coarse), _ptr(fine)))
+        self.sync()
+
+    def prolongate_no_boundary(self, level, fine, coarse):
+        self._torch_sync()
+        _check(lib().mgb_transfer_prolongate_no_boundary(self.h, self._l(level), _ptr(fine), _ptr(coarse)))
+        self.sync()
+
+    def set_kernel(self, kernel):
+        _check(lib().mgb_op_set_kernel(self.h, kernel))

@@ -1,0 +1,633 @@
+// Degree-templated sm_100a kernels.  Included by degree_tu.cu with MGB_P defined.
+//
+// k_apply_general   : FEEvaluation-style cell kernel (evaluate -> quadrature-point operation ->
+//                     integrate) for arbitrary merged coefficients; restates
+//                     common/laplace_operator.h:529-558 + :438-523 with the gather/scatter of
+//                     common/vector_access_reduced.h on the patch entity table.
+// k_apply_cartesian : the same operator on axis-aligned cells with constant coefficient,
+//                     sum-factorised over a whole patch with 1-D mass/stiffness matrices and
+//                     fused vector epilogues.
+// k_transfer        : MGTransferMatrixFree prolongation / restriction per parent cell.
+// k_diagonal        : diagonal of the cell matrices (laplace_operator.h:770-800).
+// k_rhs_values      : int f phi   (value part of compute_residual, laplace_operator.h:828-841)
+// k_l2_error        : multigrid_solver.h:298-343
+#pragma once
+#include <cuda_runtime.h>
+
+#include "degree_kernels.h"
+#include "functions.cuh"
+
+namespace mgb
+{
+  template <int n>
+  struct ConstTables
+  {
+    double S[n * n], D[n * n], G[n * n], M1[n * n], K1[n * n], w[n], xq[n], nodes[n];
+    float  Sf[n * n], Df[n * n], M1f[n * n], K1f[n * n], wf[n];
+    double P1[(2 * n - 1) * n];
+  };
+
+  __constant__ ConstTables<MGB_P + 1> ctab;
+
+  template <typename T>
+  struct Tab;
+  template <>
+  struct Tab<double>
+  {
+    static __device__ __forceinline__ const double *S() { return ctab.S; }
+    static __device__ __forceinline__ const double *D() { return ctab.D; }
+    static __device__ __forceinline__ const double *M1() { return ctab.M1; }
+    static __device__ __forceinline__ const double *K1() { return ctab.K1; }
+    static __device__ __forceinline__ const double *w() { return ctab.w; }
+  };
+  template <>
+  struct Tab<float>
+  {
+    static __device__ __forceinline__ const float *S() { return ctab.Sf; }
+    static __device__ __forceinline__ const float *D() { return ctab.Df; }
+    static __device__ __forceinline__ const float *M1() { return ctab.M1f; }
+    static __device__ __forceinline__ const float *K1() { return ctab.K1f; }
+    static __device__ __forceinline__ const float *w() { return ctab.wf; }
+  };
+
+  // out (+)= Mat in  (or Mat^T in); Mat in constant memory, all indices compile-time
+  template <int n, typename T, bool TR, bool ADD>
+  __device__ __forceinline__ void
+  mat_vec(const T *__restrict__ Mc, const T (&in)[n], T (&out)[n])
+  {
+#pragma unroll
+    for (int o = 0; o < n; ++o)
+      {
+        T s = ADD ? out[o] : T(0);
+#pragma unroll
+        for (int i = 0; i < n; ++i)
+          s += (TR ? Mc[i * n + o] : Mc[o * n + i]) * in[i];
+        out[o] = s;
+      }
+  }
+
+  __host__ __device__ constexpr int
+  cells_per_block(const int p)
+  {
+    return p == 1 ? 32 : p == 2 ? 14 : p == 3 ? 8 : p == 4 ? 8 : p == 5 ? 4 : p == 6 ? 3 : 2;
+  }
+
+  // ------------------------------------------------------------------ general cell kernel
+  template <int p, typename T, bool VAR>
+  __global__ void
+  __launch_bounds__(cells_per_block(p) * (p + 1) * (p + 1))
+    k_apply_general(const ApplyArgs<T> A, T *__restrict__ acc)
+  {
+    constexpr int n    = p + 1;
+    constexpr int npad = n | 1; // odd x-stride: conflict-free line access in every direction
+    constexpr int NN   = n * n * npad;
+    constexpr int tpc  = n * n;
+    constexpr int CPB  = cells_per_block(p);
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T *smem = reinterpret_cast<T *>(smem_raw);
+
+    const int      cl     = threadIdx.x / tpc;
+    const int      t      = threadIdx.x - cl * tpc;
+    const int      a      = t / n;
+    const int      b      = t - a * n;
+    const uint32_t cell   = blockIdx.x * CPB + cl;
+    const bool     active = cell < A.L.n_cells;
+    T             *u      = smem + cl * 4 * NN;
+    T             *g0     = u + NN;
+    T             *g1     = g0 + NN;
+    T             *g2     = g1 + NN;
+    (void)g0;
+#define IDX(i, j, k) (((k)*n + (j)) * npad + (i))
+
+    // gather (vector_access_reduced.h:11-251): constrained entities read as zero
+    if (active)
+      for (int l = t; l < n * n * n; l += tpc)
+        {
+          const int i = l % n, j = (l / n) % n, k = l / (n * n);
+          bool      c;
+          const uint32_t d = cell_dof(A.L, cell, i, j, k, c);
+          u[IDX(i, j, k)]  = (c && !A.read_plain) ? T(0) : A.src[d];
+        }
+    __syncthreads();
+
+    const T *Sm = Tab<T>::S();
+    const T *Dm = Tab<T>::D();
+    T        r[n], s[n];
+
+    // evaluate: basis change to the Gauss points in x, y, z
+#pragma unroll
+    for (int i = 0; i < n; ++i)
+      r[i] = u[IDX(i, b, a)];
+    mat_vec<n, T, false, false>(Sm, r, s);
+#pragma unroll
+    for (int i = 0; i < n; ++i)
+      u[IDX(i, b, a)] = s[i];
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      r[j] = u[IDX(b, j, a)];
+    mat_vec<n, T, false, false>(Sm, r, s);
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      u[IDX(b, j, a)] = s[j];
+    __syncthreads();
+    // z: values at quadrature points, and collocation derivative in z
+#pragma unroll
+    for (int k = 0; k < n; ++k)
+      r[k] = u[IDX(b, a, k)];
+    mat_vec<n, T, false, false>(Sm, r, s);
+    mat_vec<n, T, false, false>(Dm, s, r);
+#pragma unroll
+    for (int k = 0; k < n; ++k)
+      {
+        u[IDX(b, a, k)]  = s[k];
+        g2[IDX(b, a, k)] = r[k];
+      }
+    __syncthreads();
+    // y derivative
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      r[j] = u[IDX(b, j, a)];
+    mat_vec<n, T, false, false>(Dm, r, s);
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      g1[IDX(b, j, a)] = s[j];
+    __syncthreads();
+    // x derivative, quadrature-point operation (laplace_operator.h:438-523), D_x^T
+#pragma unroll
+    for (int i = 0; i < n; ++i)
+      r[i] = u[IDX(i, b, a)];
+    mat_vec<n, T, false, false>(Dm, r, s);
+    {
+      const T *wq  = Tab<T>::w();
+      const T  wab = wq[a] * wq[b];
+      const T *cq  = VAR ? A.coef_q + (size_t)cell * 6 * (n * n * n) + (a * n + b) * n : nullptr;
+#pragma unroll
+      for (int i = 0; i < n; ++i)
+        {
+          T c0, c1, c2, c3, c4, c5;
+          if (VAR)
+            {
+              if (active)
+                {
+                  c0 = cq[0 * n * n * n + i];
+                  c1 = cq[1 * n * n * n + i];
+                  c2 = cq[2 * n * n * n + i];
+                  c3 = cq[3 * n * n * n + i];
+                  c4 = cq[4 * n * n * n + i];
+                  c5 = cq[5 * n * n * n + i];
+                }
+              else
+                c0 = c1 = c2 = c3 = c4 = c5 = T(0);
+            }
+          else
+            {
+              const T weight = wq[i] * wab;
+              c0             = A.coef[0] * weight;
+              c1             = A.coef[1] * weight;
+              c2             = A.coef[2] * weight;
+              c3             = A.coef[3] * weight;
+              c4             = A.coef[4] * weight;
+              c5             = A.coef[5] * weight;
+            }
+          const T t0 = s[i], t1 = g1[IDX(i, b, a)], t2 = g2[IDX(i, b, a)];
+          r[i]              = c0 * t0 + c3 * t1 + c4 * t2;
+          g1[IDX(i, b, a)]  = c3 * t0 + c1 * t1 + c5 * t2;
+          g2[IDX(i, b, a)]  = c4 * t0 + c5 * t1 + c2 * t2;
+        }
+    }
+    mat_vec<n, T, true, false>(Dm, r, s);
+#pragma unroll
+    for (int i = 0; i < n; ++i)
+      u[IDX(i, b, a)] = s[i];
+    __syncthreads();
+    // integrate: += D_y^T
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      {
+        r[j] = g1[IDX(b, j, a)];
+        s[j] = u[IDX(b, j, a)];
+      }
+    mat_vec<n, T, true, true>(Dm, r, s);
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      u[IDX(b, j, a)] = s[j];
+    __syncthreads();
+    // += D_z^T, then S_z^T
+#pragma unroll
+    for (int k = 0; k < n; ++k)
+      {
+        r[k] = g2[IDX(b, a, k)];
+        s[k] = u[IDX(b, a, k)];
+      }
+    mat_vec<n, T, true, true>(Dm, r, s);
+    mat_vec<n, T, true, false>(Sm, s, r);
+#pragma unroll
+    for (int k = 0; k < n; ++k)
+      u[IDX(b, a, k)] = r[k];
+    __syncthreads();
+    // S_y^T
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      r[j] = u[IDX(b, j, a)];
+    mat_vec<n, T, true, false>(Sm, r, s);
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      u[IDX(b, j, a)] = s[j];
+    __syncthreads();
+    // S_x^T
+#pragma unroll
+    for (int i = 0; i < n; ++i)
+      r[i] = u[IDX(i, b, a)];
+    mat_vec<n, T, true, false>(Sm, r, s);
+#pragma unroll
+    for (int i = 0; i < n; ++i)
+      u[IDX(i, b, a)] = s[i];
+    __syncthreads();
+
+    // scatter-add (vector_access_reduced.h:255-505): constrained entities skipped
+    if (active)
+      for (int l = t; l < n * n * n; l += tpc)
+        {
+          const int i = l % n, j = (l / n) % n, k = l / (n * n);
+          bool      c;
+          const uint32_t d = cell_dof(A.L, cell, i, j, k, c);
+          if (!c)
+            atomicAdd(&acc[d], u[IDX(i, j, k)]);
+        }
+#undef IDX
+  }
+
+  template <int p, typename T>
+  void
+  launch_apply_general(const ApplyArgs<T> &A, cudaStream_t stream)
+  {
+    constexpr int n    = p + 1;
+    constexpr int NN   = n * n * (n | 1);
+    constexpr int CPB  = cells_per_block(p);
+    const size_t  smem = (size_t)CPB * 4 * NN * sizeof(T);
+    const unsigned grid = (A.L.n_cells + CPB - 1) / CPB;
+    if (A.coef_q)
+      k_apply_general<p, T, true><<<grid, CPB * n * n, smem, stream>>>(A, A.dst);
+    else
+      k_apply_general<p, T, false><<<grid, CPB * n * n, smem, stream>>>(A, A.dst);
+  }
+
+  // ------------------------------------------------------------------ level transfer
+  // one block per parent (coarse) cell; P1 = 1-D embedding (2p+1) x (p+1)
+  template <int p, typename T>
+  __global__ void
+  k_transfer(const TransferArgs<T> A)
+  {
+    constexpr int n  = p + 1;
+    constexpr int nf = 2 * p + 1;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T            *P1   = reinterpret_cast<T *>(smem_raw);
+    T            *buf0 = P1 + nf * n;
+    T            *buf1 = buf0 + nf * nf * nf;
+    const int     tid = threadIdx.x, nt = blockDim.x;
+    for (int i = tid; i < nf * n; i += nt)
+      P1[i] = (T)ctab.P1[i];
+
+    const uint32_t ccell = blockIdx.x;
+    int            cx, cy, cz;
+    cell_coords(A.coarse, ccell, cx, cy, cz);
+
+    if (A.mode < 2)
+      {
+        // ---- prolongation: u (n^3) -> x -> y -> z -> fine (nf^3)
+        T *u = buf1; // n^3 <= nf*nf*n
+        for (int l = tid; l < n * n * n; l += nt)
+          {
+            const int i = l % n, j = (l / n) % n, k = l / (n * n);
+            bool      c;
+            const uint32_t d = cell_dof(A.coarse, ccell, i, j, k, c);
+            u[l]             = (c && A.constrained) ? T(0) : A.src[d];
+          }
+        __syncthreads();
+        // x: a[k][j][o] in buf0 (n*n*nf)
+        for (int l = tid; l < n * n * nf; l += nt)
+          {
+            const int o = l % nf, kj = l / nf;
+            T         s = 0;
+#pragma unroll
+            for (int i = 0; i < n; ++i)
+              s += P1[o * n + i] * u[kj * n + i];
+            buf0[l] = s;
+          }
+        __syncthreads();
+        // y: c[k][o][i] in buf1 (n*nf*nf)
+        for (int l = tid; l < n * nf * nf; l += nt)
+          {
+            const int i = l % nf, o = (l / nf) % nf, k = l / (nf * nf);
+            T         s = 0;
+#pragma unroll
+            for (int j = 0; j < n; ++j)
+              s += P1[o * n + j] * buf0[(k * n + j) * nf + i];
+            buf1[l] = s;
+          }
+        __syncthreads();
+        // z + write: every fine DoF is written by exactly one parent (lower-owner rule)
+        for (int l = tid; l < nf * nf * nf; l += nt)
+          {
+            const int I = l % nf, J = (l / nf) % nf, K = l / (nf * nf);
+            const bool owned = (I < 2 * p || cx == A.coarse.ncell[0] - 1) &&
+                               (J < 2 * p || cy == A.coarse.ncell[1] - 1) &&
+                               (K < 2 * p || cz == A.coarse.ncell[2] - 1);
+            if (!owned)
+              continue;
+            T s = 0;
+#pragma unroll
+            for (int k = 0; k < n; ++k)
+              s += P1[K * n + k] * buf1[(k * nf + J) * nf + I];
+            const int      fx = 2 * cx + (I > p), fy = 2 * cy + (J > p), fz = 2 * cz + (K > p);
+            const uint32_t fcell = cell_number(A.fine, fx, fy, fz);
+            bool           c;
+            const uint32_t d =
+              cell_dof(A.fine, fcell, I - (I > p) * p, J - (J > p) * p, K - (K > p) * p, c);
+            if (A.mode == 1)
+              A.dst[d] += s;
+            else
+              A.dst[d] = s;
+          }
+      }
+    else
+      {
+        // ---- restriction: fine (nf^3, weighted) -> z^T -> y^T -> x^T -> coarse (n^3), add
+        for (int l = tid; l < nf * nf * nf; l += nt)
+          {
+            const int I = l % nf, J = (l / nf) % nf, K = l / (nf * nf);
+            const int fx = 2 * cx + (I > p), fy = 2 * cy + (J > p), fz = 2 * cz + (K > p);
+            const uint32_t fcell = cell_number(A.fine, fx, fy, fz);
+            bool           c;
+            const uint32_t d =
+              cell_dof(A.fine, fcell, I - (I > p) * p, J - (J > p) * p, K - (K > p) * p, c);
+            T w = 1;
+            if ((I == 0 && cx > 0) || (I == 2 * p && cx < A.coarse.ncell[0] - 1))
+              w *= T(0.5);
+            if ((J == 0 && cy > 0) || (J == 2 * p && cy < A.coarse.ncell[1] - 1))
+              w *= T(0.5);
+            if ((K == 0 && cz > 0) || (K == 2 * p && cz < A.coarse.ncell[2] - 1))
+              w *= T(0.5);
+            buf0[l] = w * A.src[d];
+          }
+        __syncthreads();
+        // z^T: c[k][J][I] in buf1 (n*nf*nf)
+        for (int l = tid; l < n * nf * nf; l += nt)
+          {
+            const int IJ = l % (nf * nf), k = l / (nf * nf);
+            T         s  = 0;
+#pragma unroll
+            for (int K = 0; K < nf; ++K)
+              s += P1[K * n + k] * buf0[K * nf * nf + IJ];
+            buf1[l] = s;
+          }
+        __syncthreads();
+        // y^T: a[k][j][I] in buf0 (n*n*nf)
+        for (int l = tid; l < n * n * nf; l += nt)
+          {
+            const int I = l % nf, j = (l / nf) % n, k = l / (nf * n);
+            T         s = 0;
+#pragma unroll
+            for (int J = 0; J < nf; ++J)
+              s += P1[J * n + j] * buf1[(k * nf + J) * nf + I];
+            buf0[l] = s;
+          }
+        __syncthreads();
+        // x^T + scatter-add
+        for (int l = tid; l < n * n * n; l += nt)
+          {
+            const int i = l % n, kj = l / n;
+            T         s = 0;
+#pragma unroll
+            for (int I = 0; I < nf; ++I)
+              s += P1[I * n + i] * buf0[kj * nf + I];
+            bool           c;
+            const uint32_t d = cell_dof(A.coarse, ccell, i, (l / n) % n, l / (n * n), c);
+            if (!(c && A.constrained))
+              atomicAdd(&A.dst[d], s);
+          }
+      }
+  }
+
+  template <int p, typename T>
+  void
+  launch_transfer(const TransferArgs<T> &A, cudaStream_t stream)
+  {
+    constexpr int nf = 2 * p + 1;
+    constexpr int n  = p + 1;
+    const int     nt = nf * nf < 64 ? 64 : (nf * nf > 256 ? 256 : ((nf * nf + 31) / 32) * 32);
+    const size_t  smem = (size_t)(nf * n + nf * nf * nf + nf * nf * n) * sizeof(T);
+    static bool   attr_set = false;
+    if (!attr_set && smem > 48 * 1024)
+      {
+        cudaFuncSetAttribute(k_transfer<p, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = true;
+      }
+    k_transfer<p, T><<<A.coarse.n_cells, nt, smem, stream>>>(A);
+  }
+
+  // ------------------------------------------------------------------ diagonal
+  // diag_i = sum_q grad(phi_i)(q)^T C_q grad(phi_i)(q); one block per cell, thread per local DoF
+  template <int p, typename T>
+  __global__ void
+  k_diagonal(const DiagArgs<T> A)
+  {
+    constexpr int  n    = p + 1;
+    constexpr int  n3   = n * n * n;
+    const uint32_t cell = blockIdx.x;
+    for (int l = threadIdx.x; l < n3; l += blockDim.x)
+      {
+        const int i0 = l % n, i1 = (l / n) % n, i2 = l / (n * n);
+        double    sum = 0;
+        for (int q2 = 0; q2 < n; ++q2)
+          for (int q1 = 0; q1 < n; ++q1)
+            for (int q0 = 0; q0 < n; ++q0)
+              {
+                const double gx = ctab.G[q0 * n + i0] * ctab.S[q1 * n + i1] * ctab.S[q2 * n + i2];
+                const double gy = ctab.S[q0 * n + i0] * ctab.G[q1 * n + i1] * ctab.S[q2 * n + i2];
+                const double gz = ctab.S[q0 * n + i0] * ctab.S[q1 * n + i1] * ctab.G[q2 * n + i2];
+                double       c[6];
+                if (A.coef_q)
+                  {
+                    const T *cq = A.coef_q + (size_t)cell * 6 * n3 + (q2 * n + q1) * n + q0;
+                    for (int e = 0; e < 6; ++e)
+                      c[e] = cq[e * n3];
+                  }
+                else
+                  {
+                    const double weight = ctab.w[q0] * ctab.w[q1] * ctab.w[q2];
+                    for (int e = 0; e < 6; ++e)
+                      c[e] = (double)A.coef[e] * weight;
+                  }
+                sum += c[0] * gx * gx + c[1] * gy * gy + c[2] * gz * gz +
+                       2. * (c[3] * gx * gy + c[4] * gx * gz + c[5] * gy * gz);
+              }
+        bool           con;
+        const uint32_t d = cell_dof(A.L, cell, i0, i1, i2, con);
+        if (!con)
+          atomicAdd(&A.diag[d], (T)sum);
+      }
+  }
+
+  template <int p, typename T>
+  void
+  launch_diagonal(const DiagArgs<T> &A, cudaStream_t stream)
+  {
+    constexpr int n3 = (p + 1) * (p + 1) * (p + 1);
+    k_diagonal<p, T><<<A.L.n_cells, n3 < 256 ? ((n3 + 31) / 32) * 32 : 256, 0, stream>>>(A);
+  }
+
+  // ------------------------------------------------------------------ right-hand side values
+  template <int p>
+  __global__ void
+  k_rhs_values(const RhsArgs A)
+  {
+    constexpr int     n  = p + 1;
+    constexpr int     n3 = n * n * n;
+    __shared__ double v[n3];
+    const uint32_t    cell = blockIdx.x;
+    int               cx, cy, cz;
+    cell_coords(A.L, cell, cx, cy, cz);
+    const double detJ = A.L.h[0] * A.L.h[1] * A.L.h[2];
+    for (int q = threadIdx.x; q < n3; q += blockDim.x)
+      {
+        const int    q0 = q % n, q1 = (q / n) % n, q2 = q / (n * n);
+        const double x = A.L.lo[0] + (cx + ctab.xq[q0]) * A.L.h[0];
+        const double y = A.L.lo[1] + (cy + ctab.xq[q1]) * A.L.h[1];
+        const double z = A.L.lo[2] + (cz + ctab.xq[q2]) * A.L.h[2];
+        v[q]           = eval_fn(A.fn_id, x, y, z) * ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * detJ;
+      }
+    __syncthreads();
+    for (int l = threadIdx.x; l < n3; l += blockDim.x)
+      {
+        const int i0 = l % n, i1 = (l / n) % n, i2 = l / (n * n);
+        double    sum = 0;
+        for (int q2 = 0; q2 < n; ++q2)
+          for (int q1 = 0; q1 < n; ++q1)
+            {
+              const double s12 = ctab.S[q1 * n + i1] * ctab.S[q2 * n + i2];
+              for (int q0 = 0; q0 < n; ++q0)
+                sum += ctab.S[q0 * n + i0] * s12 * v[(q2 * n + q1) * n + q0];
+            }
+        bool           con;
+        const uint32_t d = cell_dof(A.L, cell, i0, i1, i2, con);
+        if (!con)
+          atomicAdd(&A.dst[d], sum);
+      }
+  }
+
+  template <int p>
+  void
+  launch_rhs_values(const RhsArgs &A, cudaStream_t stream)
+  {
+    constexpr int n3 = (p + 1) * (p + 1) * (p + 1);
+    k_rhs_values<p><<<A.L.n_cells, n3 < 256 ? ((n3 + 31) / 32) * 32 : 256, 0, stream>>>(A);
+  }
+
+  // ------------------------------------------------------------------ L2 error
+  template <int p>
+  __global__ void
+  k_l2_error(const ErrorArgs A)
+  {
+    constexpr int     n  = p + 1;
+    constexpr int     n3 = n * n * n;
+    __shared__ double u[n3];
+    __shared__ double red[2][32];
+    const uint32_t    cell = blockIdx.x;
+    int               cx, cy, cz;
+    cell_coords(A.L, cell, cx, cy, cz);
+    for (int l = threadIdx.x; l < n3; l += blockDim.x)
+      {
+        bool           con;
+        const uint32_t d = cell_dof(A.L, cell, l % n, (l / n) % n, l / (n * n), con);
+        u[l]             = A.u[d];
+      }
+    __syncthreads();
+    const double detJ = A.L.h[0] * A.L.h[1] * A.L.h[2];
+    double       err = 0, vol = 0;
+    for (int q = threadIdx.x; q < n3; q += blockDim.x)
+      {
+        const int q0 = q % n, q1 = (q / n) % n, q2 = q / (n * n);
+        double    val = 0;
+        for (int i2 = 0; i2 < n; ++i2)
+          for (int i1 = 0; i1 < n; ++i1)
+            {
+              const double s12 = ctab.S[q1 * n + i1] * ctab.S[q2 * n + i2];
+              for (int i0 = 0; i0 < n; ++i0)
+                val += ctab.S[q0 * n + i0] * s12 * u[(i2 * n + i1) * n + i0];
+            }
+        const double x    = A.L.lo[0] + (cx + ctab.xq[q0]) * A.L.h[0];
+        const double y    = A.L.lo[1] + (cy + ctab.xq[q1]) * A.L.h[1];
+        const double z    = A.L.lo[2] + (cz + ctab.xq[q2]) * A.L.h[2];
+        const double JxW  = ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * detJ;
+        const double diff = val - eval_fn(A.fn_id, x, y, z);
+        err += diff * diff * JxW;
+        vol += JxW;
+      }
+    for (int o = 16; o > 0; o >>= 1)
+      {
+        err += __shfl_down_sync(0xffffffffu, err, o);
+        vol += __shfl_down_sync(0xffffffffu, vol, o);
+      }
+    const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+    if (lane == 0)
+      {
+        red[0][warp] = err;
+        red[1][warp] = vol;
+      }
+    __syncthreads();
+    if (threadIdx.x == 0)
+      {
+        const int nw = (blockDim.x + 31) / 32;
+        double    e = 0, v = 0;
+        for (int i = 0; i < nw; ++i)
+          {
+            e += red[0][i];
+            v += red[1][i];
+          }
+        atomicAdd(&A.accum[0], e);
+        atomicAdd(&A.accum[1], v);
+      }
+  }
+
+  template <int p>
+  void
+  launch_l2_error(const ErrorArgs &A, cudaStream_t stream)
+  {
+    constexpr int n3 = (p + 1) * (p + 1) * (p + 1);
+    k_l2_error<p><<<A.L.n_cells, n3 < 256 ? ((n3 + 31) / 32) * 32 : 256, 0, stream>>>(A);
+  }
+
+  // ------------------------------------------------------------------ constant upload
+  template <int p>
+  void
+  init_constants(const Basis &b)
+  {
+    constexpr int       n = p + 1;
+    ConstTables<p + 1> *h = new ConstTables<p + 1>();
+    for (int i = 0; i < n * n; ++i)
+      {
+        h->S[i]   = b.S[i];
+        h->D[i]   = b.D[i];
+        h->G[i]   = b.G[i];
+        h->M1[i]  = b.M1[i];
+        h->K1[i]  = b.K1[i];
+        h->Sf[i]  = (float)b.S[i];
+        h->Df[i]  = (float)b.D[i];
+        h->M1f[i] = (float)b.M1[i];
+        h->K1f[i] = (float)b.K1[i];
+      }
+    for (int i = 0; i < n; ++i)
+      {
+        h->w[i]     = b.wq[i];
+        h->wf[i]    = (float)b.wq[i];
+        h->xq[i]    = b.xq[i];
+        h->nodes[i] = b.nodes[i];
+      }
+    for (int i = 0; i < (2 * p + 1) * n; ++i)
+      h->P1[i] = b.P1[i];
+    cudaMemcpyToSymbol(ctab, h, sizeof(*h));
+    delete h;
+  }
+} // namespace mgb

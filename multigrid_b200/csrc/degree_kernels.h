@@ -1,0 +1,98 @@
+// Interface between the degree-independent host code (solver.cu) and the per-degree
+// translation units (degree_tu.cu compiled once per p = 1..8).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "basis.h"
+#include "level.h"
+
+namespace mgb
+{
+  // operator apply:  what happens with the result y = K x of the cell loop
+  enum ApplyMode
+  {
+    APPLY_ADD = 0,      // dst += y                       (vmult_add / apply_add, laplace_operator.h:562-569)
+    APPLY_SET = 1,      // dst  = y, dst_B = src_B        (vmult, :575-601)
+    APPLY_RESIDUAL = 2, // dst  = rhs - y, dst_B -= src_B (vmult_residual, :607-634)
+    APPLY_CHEBYSHEV = 3 // dst  = (1+f1) src - f1 dst + f2 P^-1 (rhs - y)   (PreconditionChebyshev via
+                        //        vmult(dst,src,before,after), :725-741; dst holds x_{k-1} on entry)
+  };
+
+  template <typename T>
+  struct ApplyArgs
+  {
+    LevelDesc L;
+    const T  *src;
+    T        *dst;
+    const T  *rhs;      // APPLY_RESIDUAL / APPLY_CHEBYSHEV
+    const T  *inv_diag; // APPLY_CHEBYSHEV
+    T        *boundary_tmp; // scratch of size n_dofs - n_interior for the patch-boundary DoFs
+    const T  *coef_q;   // per-quadrature-point merged coefficient [cell][6][n^3] or nullptr
+    T         coef[6];  // affine constant-coefficient merged tensor (without quadrature weight)
+    T         f1, f2;
+    int       mode;
+    int       read_plain;    // 1: do not zero constrained entries on read (compute_residual)
+    int       first_chebyshev; // 1: x_{k-1} = 0 implied (iteration_index == 1)
+  };
+
+  template <typename T>
+  struct TransferArgs
+  {
+    LevelDesc fine, coarse;
+    const T  *src;
+    T        *dst;
+    int       mode;        // 0 prolongate (overwrite), 1 prolongate_and_add, 2 restrict_and_add
+    int       constrained; // MGTransferMatrixFree::initialize_constraints called
+  };
+
+  template <typename T>
+  struct DiagArgs
+  {
+    LevelDesc L;
+    T        *diag; // zero on entry; accumulates the unconstrained diagonal
+    const T  *coef_q;
+    T         coef[6];
+  };
+
+  struct RhsArgs
+  {
+    LevelDesc L;
+    double   *dst; // += int f phi
+    int       fn_id;
+  };
+
+  struct ErrorArgs
+  {
+    LevelDesc     L;
+    const double *u;
+    int           fn_id;
+    double       *accum; // [0] += error^2, [1] += volume
+  };
+
+  struct DegreeKernels
+  {
+    void (*init)(const Basis &);
+    void (*apply_general_f)(const ApplyArgs<float> &, cudaStream_t);
+    void (*apply_general_d)(const ApplyArgs<double> &, cudaStream_t);
+    void (*apply_cartesian_f)(const ApplyArgs<float> &, cudaStream_t);
+    void (*apply_cartesian_d)(const ApplyArgs<double> &, cudaStream_t);
+    void (*transfer_f)(const TransferArgs<float> &, cudaStream_t);
+    void (*transfer_d)(const TransferArgs<double> &, cudaStream_t);
+    void (*diagonal_f)(const DiagArgs<float> &, cudaStream_t);
+    void (*diagonal_d)(const DiagArgs<double> &, cudaStream_t);
+    void (*rhs_values)(const RhsArgs &, cudaStream_t);
+    void (*l2_error)(const ErrorArgs &, cudaStream_t);
+  };
+
+  const DegreeKernels &degree_kernels(int p);
+
+#define MGB_DECLARE_DEGREE(P) const DegreeKernels &degree_kernels_##P();
+  MGB_DECLARE_DEGREE(1)
+  MGB_DECLARE_DEGREE(2)
+  MGB_DECLARE_DEGREE(3)
+  MGB_DECLARE_DEGREE(4)
+  MGB_DECLARE_DEGREE(5)
+  MGB_DECLARE_DEGREE(6)
+  MGB_DECLARE_DEGREE(7)
+  MGB_DECLARE_DEGREE(8)
+} // namespace mgb

@@ -1,0 +1,1677 @@
+// Host orchestration of the matrix-free multigrid path on one B200 + degree-independent kernels.
+//
+//   LaplaceOperator<T>   <-> multigrid::LaplaceOperator<3,p,T>        common/laplace_operator.h:56-164
+//   Chebyshev<T>         <-> dealii::PreconditionChebyshev<...>       call sites common/multigrid_solver.h:271-288
+//   Transfer<T>          <-> dealii::MGTransferMatrixFree<3,T>        call sites common/multigrid_solver.h:213-221
+//   MultigridSolver      <-> multigrid::MultigridSolver<3,p,float,double>  common/multigrid_solver.h:96-782
+//
+// There is no CPU fallback: every numerical step below is a kernel launch on the solver's stream.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <array>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/mgb200.h"
+#include "basis.h"
+#include "degree_kernels.h"
+#include "functions.cuh"
+#include "level.h"
+#include "numbering.h"
+
+namespace mgb
+{
+#define MGB_CUDA_CHECK(call)                                                                   \
+  do                                                                                           \
+    {                                                                                          \
+      cudaError_t err__ = (call);                                                              \
+      if (err__ != cudaSuccess)                                                                \
+        throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(err__) +    \
+                                 " at " + __FILE__ + ":" + std::to_string(__LINE__));          \
+    }                                                                                          \
+  while (0)
+
+  const DegreeKernels &
+  degree_kernels(const int p)
+  {
+    switch (p)
+      {
+        case 1: return degree_kernels_1();
+        case 2: return degree_kernels_2();
+        case 3: return degree_kernels_3();
+        case 4: return degree_kernels_4();
+        case 5: return degree_kernels_5();
+        case 6: return degree_kernels_6();
+        case 7: return degree_kernels_7();
+        case 8: return degree_kernels_8();
+      }
+    throw std::runtime_error("polynomial degree must be between 1 and 8");
+  }
+
+  // ------------------------------------------------------------------ context
+  struct Ctx
+  {
+    int          device   = 0;
+    cudaStream_t stream   = nullptr;
+    int64_t      launches = 0;
+    double      *scal_dev = nullptr; // 16 device scalars for reductions
+    double      *scal_host = nullptr; // pinned mirror
+    bool         profile  = false;
+
+    void
+    init(const int dev)
+    {
+      device = dev;
+      MGB_CUDA_CHECK(cudaSetDevice(dev));
+      MGB_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+      MGB_CUDA_CHECK(cudaMalloc(&scal_dev, 16 * sizeof(double)));
+      MGB_CUDA_CHECK(cudaMallocHost(&scal_host, 16 * sizeof(double)));
+    }
+    void
+    destroy()
+    {
+      if (scal_dev)
+        cudaFree(scal_dev);
+      if (scal_host)
+        cudaFreeHost(scal_host);
+      if (stream)
+        cudaStreamDestroy(stream);
+      scal_dev = scal_host = nullptr;
+      stream               = nullptr;
+    }
+    void
+    sync()
+    {
+      MGB_CUDA_CHECK(cudaStreamSynchronize(stream));
+    }
+    void
+    check_launch()
+    {
+      ++launches;
+      MGB_CUDA_CHECK(cudaGetLastError());
+    }
+  };
+
+  template <typename T>
+  struct DVec
+  {
+    T     *p = nullptr;
+    size_t n = 0;
+    DVec()   = default;
+    DVec(const DVec &) = delete;
+    DVec &operator=(const DVec &) = delete;
+    ~DVec() { release(); }
+    void
+    alloc(const size_t count, cudaStream_t stream)
+    {
+      release();
+      n = count;
+      if (n)
+        {
+          MGB_CUDA_CHECK(cudaMalloc(&p, n * sizeof(T)));
+          MGB_CUDA_CHECK(cudaMemsetAsync(p, 0, n * sizeof(T), stream));
+        }
+    }
+    void
+    release()
+    {
+      if (p)
+        cudaFree(p);
+      p = nullptr;
+      n = 0;
+    }
+    void
+    swap(DVec &o)
+    {
+      std::swap(p, o.p);
+      std::swap(n, o.n);
+    }
+  };
+
+  // ------------------------------------------------------------------ generic vector kernels
+  template <typename F>
+  __global__ void
+  k_foreach(const size_t n, F f)
+  {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+      f(i);
+  }
+
+  static inline unsigned
+  grid_for(const size_t n, const int block = 256)
+  {
+    const size_t g = (n + block - 1) / block;
+    return (unsigned)std::min<size_t>(std::max<size_t>(g, 1), 148 * 16);
+  }
+
+  template <typename F>
+  void
+  foreach (Ctx &ctx, const size_t n, F f)
+  {
+    if (n == 0)
+      return;
+    k_foreach<<<grid_for(n), 256, 0, ctx.stream>>>(n, f);
+    ctx.check_launch();
+  }
+
+  // up to 4 simultaneous sums of products; warp-shuffle + shared reduction, one red.add.f64 per block
+  template <int NS, typename F>
+  __global__ void
+  k_reduce(const size_t n, F f, double *out)
+  {
+    double acc[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s)
+      acc[s] = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+      f(i, acc);
+    __shared__ double red[NS][8];
+#pragma unroll
+    for (int s = 0; s < NS; ++s)
+      {
+        double v = acc[s];
+        for (int o = 16; o > 0; o >>= 1)
+          v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0)
+          red[s][threadIdx.x >> 5] = v;
+      }
+    __syncthreads();
+    if (threadIdx.x < NS)
+      {
+        double v = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w)
+          v += red[threadIdx.x][w];
+        atomicAdd(&out[threadIdx.x], v);
+      }
+  }
+
+  // returns the sums on the host (synchronises the stream)
+  template <int NS, typename F>
+  void
+  reduce(Ctx &ctx, const size_t n, F f, double *result)
+  {
+    MGB_CUDA_CHECK(cudaMemsetAsync(ctx.scal_dev, 0, NS * sizeof(double), ctx.stream));
+    k_reduce<NS><<<grid_for(n), 256, 0, ctx.stream>>>(n, f, ctx.scal_dev);
+    ctx.check_launch();
+    MGB_CUDA_CHECK(cudaMemcpyAsync(
+      ctx.scal_host, ctx.scal_dev, NS * sizeof(double), cudaMemcpyDeviceToHost, ctx.stream));
+    ctx.sync();
+    for (int s = 0; s < NS; ++s)
+      result[s] = ctx.scal_host[s];
+  }
+
+  template <typename A, typename B>
+  double
+  dot(Ctx &ctx, const A *a, const B *b, const size_t n)
+  {
+    double r;
+    reduce<1>(
+      ctx, n, [=] __device__(size_t i, double *acc) { acc[0] += (double)a[i] * (double)b[i]; }, &r);
+    return r;
+  }
+
+  template <typename A, typename B>
+  void
+  convert(Ctx &ctx, A *dst, const B *src, const size_t n)
+  {
+    foreach (ctx, n, [=] __device__(size_t i) { dst[i] = (A)src[i]; });
+  }
+
+  // ------------------------------------------------------------------ level (device side)
+  struct Level
+  {
+    HostLevel      host;
+    LevelDesc      d; // with device pointers
+    DVec<uint32_t> ent_base, ent_mask, constrained;
+    DVec<uint8_t>  bflag;
+
+    void
+    upload(cudaStream_t stream)
+    {
+      ent_base.alloc(host.ent_base.size(), stream);
+      ent_mask.alloc(host.ent_mask.size(), stream);
+      constrained.alloc(host.constrained.size(), stream);
+      bflag.alloc(host.bflag.size(), stream);
+      MGB_CUDA_CHECK(cudaMemcpyAsync(ent_base.p, host.ent_base.data(), ent_base.n * 4, cudaMemcpyHostToDevice, stream));
+      MGB_CUDA_CHECK(cudaMemcpyAsync(ent_mask.p, host.ent_mask.data(), ent_mask.n * 4, cudaMemcpyHostToDevice, stream));
+      if (constrained.n)
+        MGB_CUDA_CHECK(cudaMemcpyAsync(constrained.p, host.constrained.data(), constrained.n * 4, cudaMemcpyHostToDevice, stream));
+      if (bflag.n)
+        MGB_CUDA_CHECK(cudaMemcpyAsync(bflag.p, host.bflag.data(), bflag.n, cudaMemcpyHostToDevice, stream));
+      MGB_CUDA_CHECK(cudaStreamSynchronize(stream));
+      d          = host.d;
+      d.ent_base = ent_base.p;
+      d.ent_mask = ent_mask.p;
+    }
+    size_t n_boundary() const { return d.n_dofs - d.n_interior; }
+  };
+
+  struct Nodes1D
+  {
+    double nodes[9], xq[9], w[9];
+  };
+
+  // visits every (patch, patch point): f(dof, constrained, gi, gj, gk); points shared between patches
+  // are visited more than once (callers are idempotent)
+  template <typename F>
+  __global__ void
+  k_patch_points(const LevelDesc L, F f)
+  {
+    const uint32_t patch = blockIdx.x;
+    const int      np3   = L.np * L.np * L.np;
+    const int      px = patch % L.npatch[0], py = (patch / L.npatch[0]) % L.npatch[1],
+              pz = patch / (L.npatch[0] * L.npatch[1]);
+    const int mp = L.M * L.p;
+    for (int l = threadIdx.x; l < np3; l += blockDim.x)
+      {
+        const int I = l % L.np, J = (l / L.np) % L.np, K = l / (L.np * L.np);
+        bool      c;
+        const uint32_t d = patch_dof(L, patch, I, J, K, c);
+        f(d, c, px * mp + I, py * mp + J, pz * mp + K);
+      }
+  }
+
+  template <typename F>
+  void
+  patch_points(Ctx &ctx, const LevelDesc &L, F f)
+  {
+    k_patch_points<<<L.n_patches, 256, 0, ctx.stream>>>(L, f);
+    ctx.check_launch();
+  }
+
+  __device__ __forceinline__ double
+  support_point(const LevelDesc &L, const Nodes1D &nd, const int dir, const int gi)
+  {
+    int cell = gi / L.p;
+    if (cell > L.ncell[dir] - 1)
+      cell = L.ncell[dir] - 1;
+    return L.lo[dir] + (cell + nd.nodes[gi - cell * L.p]) * L.h[dir];
+  }
+
+  // ------------------------------------------------------------------ operator
+  template <typename T>
+  struct LaplaceOperator
+  {
+    Ctx                 *ctx   = nullptr;
+    Level               *level = nullptr;
+    const DegreeKernels *dk    = nullptr;
+    T                    coef[6];
+    DVec<T>              coef_q;
+    bool                 cartesian = true; // axis-aligned cells and constant coefficient
+    int                  kernel    = MGB_KERNEL_AUTO;
+    DVec<T>              inverse_diagonal;
+    DVec<T>              tmp;          // full-length scratch (general kernel epilogues)
+    DVec<T>              boundary_tmp; // patch-boundary accumulator; invariant: zero between calls
+
+    size_t m() const { return level->d.n_dofs; }
+
+    void
+    initialize(Ctx &c, Level &l, const Basis &basis, const int coefficient_fn)
+    {
+      ctx   = &c;
+      level = &l;
+      dk    = &degree_kernels(l.d.p);
+      boundary_tmp.alloc(l.n_boundary(), c.stream);
+      evaluate_coefficient(basis, coefficient_fn);
+    }
+
+    // laplace_operator.h:359-432 (merged coefficient = c JxW J^-1 J^-T)
+    void
+    evaluate_coefficient(const Basis &basis, const int fn)
+    {
+      const LevelDesc &L    = level->d;
+      const double     detJ = L.h[0] * L.h[1] * L.h[2];
+      if (fn == FN_ONE)
+        {
+          cartesian = true;
+          for (int d = 0; d < 3; ++d)
+            coef[d] = (T)(detJ / (L.h[d] * L.h[d]));
+          coef[3] = coef[4] = coef[5] = 0;
+          return;
+        }
+      cartesian   = false;
+      const int n = L.n, n3 = n * n * n;
+      coef_q.alloc((size_t)L.n_cells * 6 * n3, ctx->stream);
+      Nodes1D nd;
+      for (int i = 0; i < n; ++i)
+        {
+          nd.xq[i] = basis.xq[i];
+          nd.w[i]  = basis.wq[i];
+        }
+      T              *cq = coef_q.p;
+      const LevelDesc Lc = L;
+      foreach (*ctx, (size_t)L.n_cells * n3, [=] __device__(size_t idx) {
+        const uint32_t cell = idx / n3;
+        const int      q    = idx - (size_t)cell * n3;
+        const int      q0 = q % n, q1 = (q / n) % n, q2 = q / (n * n);
+        int            cx, cy, cz;
+        cell_coords(Lc, cell, cx, cy, cz);
+        const double x = Lc.lo[0] + (cx + nd.xq[q0]) * Lc.h[0];
+        const double y = Lc.lo[1] + (cy + nd.xq[q1]) * Lc.h[1];
+        const double z = Lc.lo[2] + (cz + nd.xq[q2]) * Lc.h[2];
+        const double f = eval_fn(fn, x, y, z) * (nd.w[q0] * nd.w[q1] * nd.w[q2]) * detJ;
+        T           *c = cq + (size_t)cell * 6 * n3 + q;
+        c[0 * n3]      = (T)(f / (Lc.h[0] * Lc.h[0]));
+        c[1 * n3]      = (T)(f / (Lc.h[1] * Lc.h[1]));
+        c[2 * n3]      = (T)(f / (Lc.h[2] * Lc.h[2]));
+        c[3 * n3] = c[4 * n3] = c[5 * n3] = T(0);
+      });
+    }
+
+    bool use_cartesian() const
+    {
+      return cartesian && kernel == MGB_KERNEL_AUTO && (level->d.M * level->d.p + 1 <= 17);
+    }
+
+    void
+    fill_args(ApplyArgs<T> &A, const T *src, T *dst) const
+    {
+      A.L               = level->d;
+      A.src             = src;
+      A.dst             = dst;
+      A.rhs             = nullptr;
+      A.inv_diag        = nullptr;
+      A.boundary_tmp    = boundary_tmp.p;
+      A.coef_q          = coef_q.p;
+      for (int i = 0; i < 6; ++i)
+        A.coef[i] = coef[i];
+      A.f1 = A.f2       = 0;
+      A.mode            = APPLY_ADD;
+      A.read_plain      = 0;
+      A.first_chebyshev = 0;
+    }
+
+    void
+    launch_general(const ApplyArgs<T> &A) const
+    {
+      if (sizeof(T) == 8)
+        dk->apply_general_d(reinterpret_cast<const ApplyArgs<double> &>(A), ctx->stream);
+      else
+        dk->apply_general_f(reinterpret_cast<const ApplyArgs<float> &>(A), ctx->stream);
+      ctx->check_launch();
+    }
+
+    void
+    launch_cartesian(const ApplyArgs<T> &A) const
+    {
+      if (sizeof(T) == 8)
+        dk->apply_cartesian_d(reinterpret_cast<const ApplyArgs<double> &>(A), ctx->stream);
+      else
+        dk->apply_cartesian_f(reinterpret_cast<const ApplyArgs<float> &>(A), ctx->stream);
+      ctx->check_launch();
+    }
+
+    // the one entry point behind vmult / vmult_add / vmult_residual / Chebyshev step
+    void
+    apply(const int mode, T *dst, const T *src, const T *rhs = nullptr, const T *inv_diag = nullptr,
+          const T f1 = 0, const T f2 = 0, const bool first = false, const bool read_plain = false)
+    {
+      ApplyArgs<T> A;
+      fill_args(A, src, dst);
+      A.mode            = mode;
+      A.rhs             = rhs;
+      A.inv_diag        = inv_diag;
+      A.f1              = f1;
+      A.f2              = f2;
+      A.first_chebyshev = first;
+      A.read_plain      = read_plain;
+      const LevelDesc &L    = level->d;
+      const size_t     N    = L.n_dofs;
+      const uint8_t   *flag = level->bflag.p;
+
+      if (use_cartesian() && !read_plain)
+        {
+          launch_cartesian(A);
+          if (mode == APPLY_ADD)
+            return;
+          // patch-boundary DoFs: finish with the accumulated sums; Dirichlet rows are identity
+          T             *bt   = boundary_tmp.p;
+          const uint32_t nint = L.n_interior;
+          foreach (*ctx, N - nint, [=] __device__(size_t i) {
+            const size_t d = i + nint;
+            const T      y = flag[i] ? src[d] : bt[i];
+            bt[i]          = T(0);
+            if (mode == APPLY_SET)
+              dst[d] = y;
+            else if (mode == APPLY_RESIDUAL)
+              dst[d] = rhs[d] - y;
+            else
+              {
+                const T upd = f2 * inv_diag[d] * (rhs[d] - y);
+                dst[d] = first ? (T(1) + f1) * src[d] + upd : (T(1) + f1) * src[d] - f1 * dst[d] + upd;
+              }
+          });
+          return;
+        }
+
+      // general kernel: accumulate K src with red.global.add, then the vector operation
+      if (mode == APPLY_ADD)
+        {
+          launch_general(A);
+          return;
+        }
+      T *acc = dst;
+      if (mode != APPLY_SET)
+        {
+          if (tmp.n != N)
+            tmp.alloc(N, ctx->stream);
+          acc = tmp.p;
+        }
+      MGB_CUDA_CHECK(cudaMemsetAsync(acc, 0, N * sizeof(T), ctx->stream));
+      A.dst = acc;
+      launch_general(A);
+      const uint32_t *clist = level->constrained.p;
+      const size_t    nc    = level->constrained.n;
+      if (mode == APPLY_SET)
+        {
+          foreach (*ctx, nc, [=] __device__(size_t i) { dst[clist[i]] = src[clist[i]]; });
+          return;
+        }
+      foreach (*ctx, nc, [=] __device__(size_t i) { acc[clist[i]] = src[clist[i]]; });
+      if (mode == APPLY_RESIDUAL)
+        foreach (*ctx, N, [=] __device__(size_t d) { dst[d] = rhs[d] - acc[d]; });
+      else
+        foreach (*ctx, N, [=] __device__(size_t d) {
+          const T upd = f2 * inv_diag[d] * (rhs[d] - acc[d]);
+          dst[d] = first ? (T(1) + f1) * src[d] + upd : (T(1) + f1) * src[d] - f1 * dst[d] + upd;
+        });
+    }
+
+    void vmult(T *dst, const T *src) { apply(APPLY_SET, dst, src); }
+    void vmult_add(T *dst, const T *src) { apply(APPLY_ADD, dst, src); }
+    void vmult_residual(const T *rhs, const T *lhs, T *residual) { apply(APPLY_RESIDUAL, residual, lhs, rhs); }
+
+    // laplace_operator.h:640-719 (q = A p after the vector update, 4 dot products)
+    void
+    vmult_with_cg_update(const T alpha, const T beta, const T *r, T *q, T *pp, T *x, double sums[4])
+    {
+      const size_t N = m();
+      if (alpha == T(0))
+        foreach (*ctx, N, [=] __device__(size_t i) { pp[i] = q[i]; });
+      else
+        foreach (*ctx, N, [=] __device__(size_t i) {
+          x[i] += alpha * pp[i];
+          pp[i] = beta * pp[i] + q[i];
+        });
+      // the reference leaves constrained rows of q at zero here (no identity fix-up)
+      MGB_CUDA_CHECK(cudaMemsetAsync(q, 0, N * sizeof(T), ctx->stream));
+      apply(APPLY_ADD, q, pp);
+      reduce<4>(
+        *ctx,
+        N,
+        [=] __device__(size_t i, double *acc) {
+          const double qi = q[i], pi = pp[i], ri = r[i];
+          acc[0] += qi * pi;
+          acc[1] += ri * ri;
+          acc[2] += qi * ri;
+          acc[3] += qi * qi;
+        },
+        sums);
+    }
+
+    // laplace_operator.h:747-800
+    void
+    compute_diagonal()
+    {
+      const size_t N = m();
+      inverse_diagonal.alloc(N, ctx->stream);
+      DiagArgs<T> A;
+      A.L      = level->d;
+      A.diag   = inverse_diagonal.p;
+      A.coef_q = coef_q.p;
+      for (int i = 0; i < 6; ++i)
+        A.coef[i] = coef[i];
+      if (sizeof(T) == 8)
+        dk->diagonal_d(reinterpret_cast<const DiagArgs<double> &>(A), ctx->stream);
+      else
+        dk->diagonal_f(reinterpret_cast<const DiagArgs<float> &>(A), ctx->stream);
+      ctx->check_launch();
+      T              *dg    = inverse_diagonal.p;
+      const uint32_t *clist = level->constrained.p;
+      foreach (*ctx, level->constrained.n, [=] __device__(size_t i) { dg[clist[i]] = T(1); });
+      foreach (*ctx, N, [=] __device__(size_t i) { dg[i] = T(1) / dg[i]; });
+    }
+  };
+
+  // ------------------------------------------------------------------ Chebyshev smoother
+  static void
+  tridiagonal_extreme_eigenvalues(const std::vector<double> &diag,
+                                  const std::vector<double> &off,
+                                  double                    &emin,
+                                  double                    &emax)
+  {
+    const int k = (int)diag.size();
+    if (k == 0)
+      {
+        emin = emax = 1.;
+        return;
+      }
+    double glo = 1e300, ghi = -1e300;
+    for (int i = 0; i < k; ++i)
+      {
+        const double r = (i > 0 ? std::fabs(off[i - 1]) : 0.) + (i < k - 1 ? std::fabs(off[i]) : 0.);
+        glo            = std::min(glo, diag[i] - r);
+        ghi            = std::max(ghi, diag[i] + r);
+      }
+    auto n_below = [&](const double x) { // Sturm count
+      int    cnt = 0;
+      double d   = 1;
+      for (int i = 0; i < k; ++i)
+        {
+          d = diag[i] - x - (i > 0 ? off[i - 1] * off[i - 1] / d : 0.);
+          if (d == 0)
+            d = 1e-300;
+          cnt += d < 0;
+        }
+      return cnt;
+    };
+    auto bisect = [&](const int idx) {
+      double a = glo, c = ghi;
+      for (int it = 0; it < 200; ++it)
+        {
+          const double mid = 0.5 * (a + c);
+          (n_below(mid) > idx ? c : a) = mid;
+        }
+      return 0.5 * (a + c);
+    };
+    emin = bisect(0);
+    emax = bisect(k - 1);
+  }
+
+  template <typename T>
+  struct Chebyshev
+  {
+    static constexpr unsigned int invalid_degree = 0xffffffffu;
+    Ctx                *ctx = nullptr;
+    LaplaceOperator<T> *A   = nullptr;
+    double              smoothing_range     = 20.;
+    unsigned int        degree              = 1;
+    unsigned int        eig_cg_n_iterations = 15;
+    double              min_eig = 1, max_eig = 1, theta = 1, delta = 1;
+    unsigned int        cg_iterations = 0;
+    DVec<T>             solution_old;
+
+    // deal.II PreconditionChebyshev::estimate_eigenvalues: CG/Lanczos on D^-1 A started from
+    // "lexicographic index mod 11, mean removed, constrained entries zero"
+    void
+    initialize(Ctx &c, LaplaceOperator<T> &op, const Basis &)
+    {
+      ctx            = &c;
+      A              = &op;
+      const size_t N = op.m();
+      solution_old.alloc(N, c.stream);
+      DVec<T> g, h, d;
+      g.alloc(N, c.stream);
+      h.alloc(N, c.stream);
+      d.alloc(N, c.stream);
+      const LevelDesc L  = op.level->d;
+      T              *gp = g.p, *hp = h.p, *dp = d.p;
+      const T        *P = op.inverse_diagonal.p;
+      patch_points(c, L, [=] __device__(uint32_t dof, bool con, int gi, int gj, int gk) {
+        const size_t lex = ((size_t)gk * L.nd[1] + gj) * L.nd[0] + gi;
+        gp[dof]          = con ? T(0) : (T)(lex % 11);
+      });
+      // mean over all entries before constraining (cheap closed form avoided: do it on the device)
+      double sum;
+      {
+        // unconstrained pattern sum: recompute with constrained entries included
+        DVec<T> full;
+        full.alloc(N, c.stream);
+        T *fp = full.p;
+        patch_points(c, L, [=] __device__(uint32_t dof, bool, int gi, int gj, int gk) {
+          const size_t lex = ((size_t)gk * L.nd[1] + gj) * L.nd[0] + gi;
+          fp[dof]          = (T)(lex % 11);
+        });
+        reduce<1>(
+          c, N, [=] __device__(size_t i, double *acc) { acc[0] += (double)fp[i]; }, &sum);
+      }
+      const T         mean  = (T)(sum / N);
+      const uint8_t  *flag  = op.level->bflag.p;
+      const uint32_t  nint  = L.n_interior;
+      // g = -(pattern - mean) with constrained entries zero
+      foreach (c, N, [=] __device__(size_t i) {
+        const bool con = i >= nint && flag[i - nint];
+        gp[i]          = con ? T(0) : -(gp[i] - mean);
+      });
+      std::vector<double> diag, off;
+      double              res = std::sqrt(dot(c, gp, gp, N));
+      cg_iterations           = 0;
+      if (res > 1e-10 && eig_cg_n_iterations > 0)
+        {
+          foreach (c, N, [=] __device__(size_t i) {
+            hp[i] = P[i] * gp[i];
+            dp[i] = -hp[i];
+          });
+          double gh = dot(c, gp, hp, N);
+          double alpha_old = 0, beta_old = 0;
+          for (unsigned int it = 1;; ++it)
+            {
+              op.vmult(hp, dp);
+              const double alpha = gh / dot(c, dp, hp, N);
+              const T      al    = (T)alpha;
+              foreach (c, N, [=] __device__(size_t i) { gp[i] += al * hp[i]; });
+              res = std::sqrt(dot(c, gp, gp, N));
+              if (it == 1)
+                diag.push_back(1. / alpha);
+              else
+                {
+                  diag.push_back(1. / alpha + beta_old / alpha_old);
+                  off.push_back(std::sqrt(beta_old) / alpha_old);
+                }
+              cg_iterations = it;
+              if (it >= eig_cg_n_iterations || res <= 1e-10)
+                break;
+              foreach (c, N, [=] __device__(size_t i) { hp[i] = P[i] * gp[i]; });
+              const double gh_new = dot(c, gp, hp, N);
+              const double beta   = gh_new / gh;
+              gh                  = gh_new;
+              const T be          = (T)beta;
+              foreach (c, N, [=] __device__(size_t i) { dp[i] = be * dp[i] - hp[i]; });
+              alpha_old = alpha;
+              beta_old  = beta;
+            }
+          tridiagonal_extreme_eigenvalues(diag, off, min_eig, max_eig);
+        }
+      else
+        min_eig = max_eig = 1.;
+
+      const double max_est = 1.2 * max_eig;
+      const double alpha =
+        smoothing_range > 1. ? max_est / smoothing_range : std::min(0.9 * max_est, min_eig);
+      if (degree == invalid_degree)
+        {
+          const double actual_range = max_est / alpha;
+          const double sigma =
+            (1. - std::sqrt(1. / actual_range)) / (1. + std::sqrt(1. / actual_range));
+          const double eps = smoothing_range;
+          degree           = 1 + static_cast<unsigned int>(
+                         std::log(1. / eps + std::sqrt(1. / eps / eps - 1.)) / std::log(1. / sigma));
+        }
+      theta = (max_est + alpha) * 0.5;
+      delta = (max_est - alpha) * 0.5;
+      c.sync();
+    }
+
+    // x_{k+1} = (1+f1) x_k - f1 x_{k-1} + f2 P^-1 (b - A x_k), fused with the operator apply;
+    // the result lands in solution_old and the two vectors are swapped (as deal.II does)
+    void
+    fused_step(DVec<T> &x, const T *b, const double f1, const double f2, const bool first)
+    {
+      A->apply(APPLY_CHEBYSHEV, solution_old.p, x.p, b, A->inverse_diagonal.p, (T)f1, (T)f2, first);
+      x.swap(solution_old);
+    }
+
+    void
+    loop(DVec<T> &x, const T *b, const bool first_is_index_one)
+    {
+      if (degree < 2)
+        return;
+      double       rhok  = delta / theta;
+      const double sigma = theta / delta;
+      for (unsigned int k = 0; k < degree - 1; ++k)
+        {
+          const double rhokp = 1. / (2. * sigma - rhok);
+          const double f1 = rhokp * rhok, f2 = 2. * rhokp / delta;
+          rhok = rhokp;
+          fused_step(x, b, f1, f2, first_is_index_one && k == 0);
+        }
+    }
+
+    // zero initial guess (deal.II vmult): x = 1/theta P^-1 b, then degree-1 fused steps
+    void
+    vmult(DVec<T> &x, const T *b)
+    {
+      T       *xp = x.p;
+      const T *P  = A->inverse_diagonal.p;
+      const T  f2 = (T)(1. / theta);
+      foreach (*ctx, x.n, [=] __device__(size_t i) { xp[i] = f2 * P[i] * b[i]; });
+      loop(x, b, true);
+    }
+
+    // nonzero initial guess (deal.II step): degree fused steps
+    void
+    step(DVec<T> &x, const T *b)
+    {
+      fused_step(x, b, 0., 1. / theta, true);
+      loop(x, b, false);
+    }
+  };
+
+  // ------------------------------------------------------------------ transfer
+  template <typename T>
+  struct Transfer
+  {
+    Ctx                 *ctx = nullptr;
+    Level               *fine = nullptr, *coarse = nullptr;
+    const DegreeKernels *dk = nullptr;
+    bool                 constrained = false;
+
+    void
+    run(const int mode, T *dst, const T *src)
+    {
+      TransferArgs<T> A;
+      A.fine        = fine->d;
+      A.coarse      = coarse->d;
+      A.src         = src;
+      A.dst         = dst;
+      A.mode        = mode;
+      A.constrained = constrained;
+      if (sizeof(T) == 8)
+        dk->transfer_d(reinterpret_cast<const TransferArgs<double> &>(A), ctx->stream);
+      else
+        dk->transfer_f(reinterpret_cast<const TransferArgs<float> &>(A), ctx->stream);
+      ctx->check_launch();
+    }
+    void prolongate(T *f, const T *c) { run(0, f, c); }
+    void prolongate_and_add(T *f, const T *c) { run(1, f, c); }
+    void restrict_and_add(T *c, const T *f) { run(2, c, f); }
+  };
+
+  // ------------------------------------------------------------------ solver
+  struct MultigridSolver
+  {
+    mgb_options  opt;
+    Ctx          ctx;
+    Basis        basis;
+    int          n_levels = 0;
+    int          fn_solution, fn_rhs, fn_coef;
+    std::vector<std::unique_ptr<Level>>                   levels;
+    std::vector<std::unique_ptr<LaplaceOperator<float>>>  matrix;
+    std::vector<std::unique_ptr<LaplaceOperator<double>>> matrix_dp;
+    std::vector<std::unique_ptr<Chebyshev<float>>>        smooth;
+    std::vector<Transfer<float>>                          transfer;
+    std::vector<Transfer<double>>                         mg_transfer_no_boundary;
+    std::vector<std::unique_ptr<DVec<double>>>            solution, rhs, residual, bc_values;
+    std::vector<std::unique_ptr<DVec<float>>>             defect, t, solution_update;
+    DVec<double>                                          cg_g, cg_h, cg_d;
+    std::vector<double>                                   cg_history;
+    std::vector<std::array<double, 6>>                    timings;
+
+    explicit MultigridSolver(const mgb_options &o)
+      : opt(o)
+    {
+      setup(o);
+    }
+
+    // body of the constructor (extended device lambdas are not allowed inside constructors)
+    void
+    setup(const mgb_options &o)
+    {
+      if (o.degree < 1 || o.degree > 8)
+        throw std::runtime_error("polynomial degree must be between 1 and 8");
+      if (o.degree_pre != o.degree_post)
+        throw std::runtime_error("Change of pre- and post-smoother degree currently not possible");
+      if (o.n_refinements < 0 || o.n_subdivisions[0] < 1 || o.n_subdivisions[1] < 1 ||
+          o.n_subdivisions[2] < 1)
+        throw std::runtime_error("invalid mesh description");
+      ctx.init(o.device);
+      basis = make_basis(o.degree);
+      degree_kernels(o.degree).init(basis);
+      if (o.problem == MGB_PROBLEM_CUBE_SINE)
+        {
+          fn_solution = FN_CUBE_SOLUTION;
+          fn_rhs      = FN_CUBE_RHS;
+          fn_coef     = FN_ONE;
+        }
+      else if (o.problem == MGB_PROBLEM_SHELL_COEF)
+        {
+          fn_solution = FN_SHELL_SOLUTION;
+          fn_rhs      = FN_SHELL_RHS;
+          fn_coef     = FN_SHELL_COEFFICIENT;
+        }
+      else
+        throw std::runtime_error("unknown problem id");
+
+      n_levels = o.n_refinements + 1;
+      timings.assign(n_levels, {{0, 0, 0, 0, 0, 0}});
+      transfer.resize(n_levels);
+      mg_transfer_no_boundary.resize(n_levels);
+      const DegreeKernels *dk = &degree_kernels(o.degree);
+      for (int l = 0; l < n_levels; ++l)
+        {
+          int nc[3];
+          for (int d = 0; d < 3; ++d)
+            nc[d] = o.n_subdivisions[d] << l;
+          levels.emplace_back(new Level());
+          Level &lv = *levels.back();
+          build_box_level(o.degree, nc, choose_patch_cells(o.degree, nc, o.max_patch_cells), o.lower, o.upper, lv.host);
+          lv.upload(ctx.stream);
+          const size_t N = lv.d.n_dofs;
+          matrix.emplace_back(new LaplaceOperator<float>());
+          matrix_dp.emplace_back(new LaplaceOperator<double>());
+          matrix[l]->kernel    = o.kernel;
+          matrix_dp[l]->kernel = o.kernel;
+          matrix[l]->initialize(ctx, lv, basis, fn_coef);
+          matrix_dp[l]->initialize(ctx, lv, basis, fn_coef);
+          auto newd = [&]() { auto v = new DVec<double>(); v->alloc(N, ctx.stream); return std::unique_ptr<DVec<double>>(v); };
+          auto newf = [&]() { auto v = new DVec<float>(); v->alloc(N, ctx.stream); return std::unique_ptr<DVec<float>>(v); };
+          solution.push_back(newd());
+          rhs.push_back(newd());
+          residual.push_back(newd());
+          bc_values.push_back(newd());
+          defect.push_back(newf());
+          t.push_back(newf());
+          solution_update.push_back(newf());
+          if (l > 0)
+            {
+              transfer[l].ctx = mg_transfer_no_boundary[l].ctx = &ctx;
+              transfer[l].fine = mg_transfer_no_boundary[l].fine = levels[l].get();
+              transfer[l].coarse = mg_transfer_no_boundary[l].coarse = levels[l - 1].get();
+              transfer[l].dk = mg_transfer_no_boundary[l].dk = dk;
+              transfer[l].constrained                = true;
+              mg_transfer_no_boundary[l].constrained = false;
+            }
+        }
+      // inhomogeneous boundary values and right-hand side (multigrid_solver.h:224-262)
+      Nodes1D nd;
+      for (int i = 0; i <= o.degree; ++i)
+        nd.nodes[i] = basis.nodes[i];
+      for (int l = 0; l < n_levels; ++l)
+        {
+          const LevelDesc L   = levels[l]->d;
+          double         *bc  = bc_values[l]->p;
+          const int       fns = fn_solution;
+          patch_points(ctx, L, [=] __device__(uint32_t dof, bool con, int gi, int gj, int gk) {
+            if (con)
+              bc[dof] = eval_fn(fns,
+                                support_point(L, nd, 0, gi),
+                                support_point(L, nd, 1, gj),
+                                support_point(L, nd, 2, gk));
+          });
+          // rhs = int f phi - K u_bc  (laplace_operator.h:806-845): general kernel, plain read
+          const size_t N   = L.n_dofs;
+          double      *neg = residual[l]->p;
+          foreach (ctx, N, [=] __device__(size_t i) { neg[i] = -bc[i]; });
+          MGB_CUDA_CHECK(cudaMemsetAsync(rhs[l]->p, 0, N * sizeof(double), ctx.stream));
+          matrix_dp[l]->apply(APPLY_ADD, rhs[l]->p, neg, nullptr, nullptr, 0, 0, false, /*read_plain=*/true);
+          RhsArgs R;
+          R.L     = L;
+          R.dst   = rhs[l]->p;
+          R.fn_id = fn_rhs;
+          dk->rhs_values(R, ctx.stream);
+          ctx.check_launch();
+          MGB_CUDA_CHECK(cudaMemsetAsync(residual[l]->p, 0, N * sizeof(double), ctx.stream));
+        }
+      // smoothers (multigrid_solver.h:268-289)
+      for (int l = 0; l < n_levels; ++l)
+        {
+          smooth.emplace_back(new Chebyshev<float>());
+          Chebyshev<float> &s = *smooth[l];
+          if (l > 0)
+            {
+              s.smoothing_range     = 20.;
+              s.degree              = o.degree_pre;
+              s.eig_cg_n_iterations = 15;
+            }
+          else
+            {
+              s.smoothing_range     = 1e-3;
+              s.degree              = Chebyshev<float>::invalid_degree;
+              s.eig_cg_n_iterations = (unsigned int)matrix[0]->m();
+            }
+          matrix[l]->compute_diagonal();
+          s.initialize(ctx, *matrix[l], basis);
+        }
+      const size_t N = levels.back()->d.n_dofs;
+      cg_g.alloc(N, ctx.stream);
+      cg_h.alloc(N, ctx.stream);
+      cg_d.alloc(N, ctx.stream);
+      ctx.sync();
+    }
+
+    ~MultigridSolver() { ctx.destroy(); }
+
+    void
+    set_boundary_values(const int level, const bool zero)
+    {
+      double         *sol   = solution[level]->p;
+      const double   *bc    = bc_values[level]->p;
+      const uint32_t *clist = levels[level]->constrained.p;
+      foreach (ctx, levels[level]->constrained.n, [=] __device__(size_t i) {
+        const uint32_t d = clist[i];
+        sol[d]           = zero ? 0. : bc[d];
+      });
+    }
+
+    // multigrid_solver.h:298-343
+    double
+    compute_l2_error(const int level)
+    {
+      set_boundary_values(level, false);
+      MGB_CUDA_CHECK(cudaMemsetAsync(ctx.scal_dev, 0, 2 * sizeof(double), ctx.stream));
+      ErrorArgs E;
+      E.L     = levels[level]->d;
+      E.u     = solution[level]->p;
+      E.fn_id = fn_solution;
+      E.accum = ctx.scal_dev;
+      degree_kernels(opt.degree).l2_error(E, ctx.stream);
+      ctx.check_launch();
+      MGB_CUDA_CHECK(cudaMemcpyAsync(ctx.scal_host, ctx.scal_dev, 2 * sizeof(double), cudaMemcpyDeviceToHost, ctx.stream));
+      ctx.sync();
+      return std::sqrt(ctx.scal_host[0] / ctx.scal_host[1]);
+    }
+
+    // multigrid_solver.h:641-681 (all in float)
+    void
+    v_cycle(const int level, const unsigned int my_n_cycles)
+    {
+      if (level == 0)
+        {
+          smooth[0]->vmult(*solution_update[0], defect[0]->p);
+          return;
+        }
+      for (unsigned int c = 0; c < my_n_cycles; ++c)
+        {
+          if (c == 0)
+            smooth[level]->vmult(*solution_update[level], defect[level]->p);
+          else
+            smooth[level]->step(*solution_update[level], defect[level]->p);
+          matrix[level]->vmult_residual(defect[level]->p, solution_update[level]->p, t[level]->p);
+          MGB_CUDA_CHECK(cudaMemsetAsync(defect[level - 1]->p, 0, defect[level - 1]->n * sizeof(float), ctx.stream));
+          transfer[level].restrict_and_add(defect[level - 1]->p, t[level]->p);
+          v_cycle(level - 1, 1);
+          transfer[level].prolongate_and_add(solution_update[level]->p, solution_update[level - 1]->p);
+          smooth[level]->step(*solution_update[level], defect[level]->p);
+        }
+    }
+
+    // multigrid_solver.h:387-476
+    double
+    solve(const bool do_analyze, double *trace)
+    {
+      double reduction_rate = 1.;
+      convert(ctx, defect[0]->p, rhs[0]->p, rhs[0]->n);
+      smooth[0]->vmult(*t[0], defect[0]->p);
+      smooth[0]->step(*t[0], defect[0]->p);
+      convert(ctx, solution[0]->p, t[0]->p, t[0]->n);
+      for (int level = 1; level < n_levels; ++level)
+        {
+          const size_t N = levels[level]->d.n_dofs;
+          set_boundary_values(level - 1, false);
+          mg_transfer_no_boundary[level].prolongate(solution[level]->p, solution[level - 1]->p);
+          double init_residual = 1.;
+          if (do_analyze && trace)
+            trace[level * 4 + 0] = compute_l2_error(level);
+          set_boundary_values(level, true);
+          matrix_dp[level]->vmult_residual(rhs[level]->p, solution[level]->p, residual[level]->p);
+          convert(ctx, defect[level]->p, residual[level]->p, N);
+          if (do_analyze)
+            {
+              init_residual = std::sqrt(dot(ctx, residual[level]->p, residual[level]->p, N));
+              if (trace)
+                trace[level * 4 + 1] = init_residual;
+            }
+          v_cycle(level, opt.n_cycles);
+          {
+            double      *sol = solution[level]->p;
+            const float *upd = solution_update[level]->p;
+            foreach (ctx, N, [=] __device__(size_t i) { sol[i] += upd[i]; }); // internal::add_vector
+          }
+          if (do_analyze)
+            {
+              set_boundary_values(level, true);
+              matrix_dp[level]->vmult(residual[level]->p, solution[level]->p);
+              double       *res = residual[level]->p;
+              const double *b   = rhs[level]->p;
+              foreach (ctx, N, [=] __device__(size_t i) { res[i] = b[i] - res[i]; });
+              const double res_norm = std::sqrt(dot(ctx, res, res, N));
+              reduction_rate        = std::pow(res_norm / init_residual, 1. / opt.n_cycles);
+              if (trace)
+                {
+                  trace[level * 4 + 2] = res_norm;
+                  trace[level * 4 + 3] = compute_l2_error(level);
+                }
+            }
+        }
+      ctx.sync();
+      return reduction_rate;
+    }
+
+    // multigrid_solver.h:498-510
+    void
+    vmult(double *dst, const double *src)
+    {
+      const int    L = n_levels - 1;
+      const size_t N = levels[L]->d.n_dofs;
+      convert(ctx, defect[L]->p, src, N);
+      v_cycle(L, 1);
+      convert(ctx, dst, solution_update[L]->p, N);
+    }
+
+    // multigrid_solver.h:483-493 + deal.II SolverCG with ReductionControl(1000, 1e-16, 1e-9)
+    std::pair<unsigned int, double>
+    solve_cg()
+    {
+      const int    L = n_levels - 1;
+      const size_t N = levels[L]->d.n_dofs;
+      double      *x = solution[L]->p, *g = cg_g.p, *h = cg_h.p, *d = cg_d.p;
+      const double *b = rhs[L]->p;
+      cg_history.clear();
+      MGB_CUDA_CHECK(cudaMemsetAsync(x, 0, N * sizeof(double), ctx.stream));
+      foreach (ctx, N, [=] __device__(size_t i) { g[i] = -b[i]; });
+      double       res  = std::sqrt(dot(ctx, g, g, N));
+      const double res0 = res;
+      cg_history.push_back(res);
+      unsigned int it = 0;
+      if (res > 1e-16)
+        {
+          vmult(h, g);
+          foreach (ctx, N, [=] __device__(size_t i) { d[i] = -h[i]; });
+          double gh = dot(ctx, g, h, N);
+          while (true)
+            {
+              ++it;
+              matrix_dp[L]->vmult(h, d);
+              const double alpha = gh / dot(ctx, d, h, N);
+              double       r2;
+              // x += alpha d; g += alpha h; |g|^2 in the same pass
+              reduce<1>(
+                ctx,
+                N,
+                [=] __device__(size_t i, double *acc) {
+                  x[i] += alpha * d[i];
+                  const double gi = g[i] + alpha * h[i];
+                  g[i]            = gi;
+                  acc[0] += gi * gi;
+                },
+                &r2);
+              res = std::sqrt(r2);
+              cg_history.push_back(res);
+              if (res <= 1e-16 || res <= 1e-9 * res0 || it >= 1000)
+                break;
+              vmult(h, g);
+              const double gh_new = dot(ctx, g, h, N);
+              const double beta   = gh_new / gh;
+              gh                  = gh_new;
+              foreach (ctx, N, [=] __device__(size_t i) { d[i] = beta * d[i] - h[i]; });
+            }
+        }
+      ctx.sync();
+      return std::make_pair(it, it > 0 ? std::pow(res / res0, 1. / it) : 0.);
+    }
+  };
+} // namespace mgb
+
+// ====================================================================== C ABI
+using namespace mgb;
+
+static thread_local std::string g_last_error;
+
+struct mgb_solver_t
+{
+  MultigridSolver *impl;
+};
+
+#define MGB_TRY try {
+#define MGB_CATCH                                  \
+  }                                                \
+  catch (const std::exception &e)                  \
+  {                                                \
+    g_last_error = e.what();                       \
+    return 1;                                      \
+  }                                                \
+  catch (...)                                      \
+  {                                                \
+    g_last_error = "unknown error";                \
+    return 2;                                      \
+  }                                                \
+  return 0;
+
+static MultigridSolver &
+S(mgb_solver s)
+{
+  if (!s || !s->impl)
+    throw std::runtime_error("null solver handle");
+  return *s->impl;
+}
+
+static int
+check_level(MultigridSolver &s, int level)
+{
+  if (level < 0)
+    level += s.n_levels;
+  if (level < 0 || level >= s.n_levels)
+    throw std::runtime_error("level out of range");
+  return level;
+}
+
+extern "C"
+{
+  const char *mgb_last_error(void) { return g_last_error.c_str(); }
+  int mgb_version(void) { return 100; }
+
+  void
+  mgb_default_options(mgb_options *o)
+  {
+    std::memset(o, 0, sizeof(*o));
+    o->degree = 4;
+    for (int d = 0; d < 3; ++d)
+      {
+        o->n_subdivisions[d] = 1;
+        o->lower[d]          = -0.9;
+        o->upper[d]          = 1.0;
+      }
+    o->n_refinements = 3;
+    o->degree_pre = o->degree_post = 3;
+    o->n_cycles                    = 2;
+    o->problem                     = MGB_PROBLEM_CUBE_SINE;
+    o->kernel                      = MGB_KERNEL_AUTO;
+    o->device                      = 0;
+    o->max_patch_cells             = 0;
+  }
+
+  int
+  mgb_solver_create(const mgb_options *opt, mgb_solver *out)
+  {
+    MGB_TRY
+    if (!opt || !out)
+      throw std::runtime_error("null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+      throw std::runtime_error("no CUDA device available: mgb200 has no CPU fallback");
+    *out         = new mgb_solver_t{nullptr};
+    (*out)->impl = new MultigridSolver(*opt);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_destroy(mgb_solver s)
+  {
+    MGB_TRY
+    if (s)
+      {
+        delete s->impl;
+        delete s;
+      }
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_sync(mgb_solver s)
+  {
+    MGB_TRY
+    S(s).ctx.sync();
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_n_levels(mgb_solver s)
+  {
+    return s && s->impl ? s->impl->n_levels : -1;
+  }
+
+  int64_t
+  mgb_solver_n_dofs(mgb_solver s, int level)
+  {
+    try
+      {
+        MultigridSolver &m = S(s);
+        return m.levels[check_level(m, level)]->d.n_dofs;
+      }
+    catch (const std::exception &e)
+      {
+        g_last_error = e.what();
+        return -1;
+      }
+  }
+
+  int
+  mgb_solver_dof_grid(mgb_solver s, int level, int nd[3])
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    for (int d = 0; d < 3; ++d)
+      nd[d] = m.levels[level]->d.nd[d];
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_patch_cells(mgb_solver s, int level)
+  {
+    try
+      {
+        MultigridSolver &m = S(s);
+        return m.levels[check_level(m, level)]->d.M;
+      }
+    catch (const std::exception &e)
+      {
+        g_last_error = e.what();
+        return -1;
+      }
+  }
+
+  int
+  mgb_solver_lex_map(mgb_solver s, int level, uint32_t *lex_to_dof)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    build_lex_map(m.levels[check_level(m, level)]->host, lex_to_dof);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_solve(mgb_solver s, int do_analyze, double *reduction_rate, double *trace)
+  {
+    MGB_TRY
+    const double r = S(s).solve(do_analyze != 0, trace);
+    if (reduction_rate)
+      *reduction_rate = r;
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_solve_cg(mgb_solver s, unsigned int *iterations, double *reduction_rate)
+  {
+    MGB_TRY
+    auto r = S(s).solve_cg();
+    if (iterations)
+      *iterations = r.first;
+    if (reduction_rate)
+      *reduction_rate = r.second;
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_solve_cg_host(mgb_solver s, const double *rhs_host, double *solution_host,
+                           unsigned int *iterations, double *reduction_rate)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    const int        L = m.n_levels - 1;
+    const size_t     N = m.levels[L]->d.n_dofs;
+    if (rhs_host)
+      MGB_CUDA_CHECK(cudaMemcpyAsync(m.rhs[L]->p, rhs_host, N * sizeof(double), cudaMemcpyHostToDevice, m.ctx.stream));
+    auto r = m.solve_cg();
+    if (solution_host)
+      {
+        m.set_boundary_values(L, false);
+        MGB_CUDA_CHECK(cudaMemcpyAsync(solution_host, m.solution[L]->p, N * sizeof(double), cudaMemcpyDeviceToHost, m.ctx.stream));
+        m.ctx.sync();
+      }
+    if (iterations)
+      *iterations = r.first;
+    if (reduction_rate)
+      *reduction_rate = r.second;
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_cg_history(mgb_solver s, double *history, int *n)
+  {
+    MGB_TRY
+    MultigridSolver &m   = S(s);
+    const int        cnt = std::min<int>(*n, (int)m.cg_history.size());
+    for (int i = 0; i < cnt; ++i)
+      history[i] = m.cg_history[i];
+    *n = cnt;
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_l2_error(mgb_solver s, int level, double *error)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    *error             = m.compute_l2_error(check_level(m, level));
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_vcycle(mgb_solver s, double *dst_dev, const double *src_dev)
+  {
+    MGB_TRY
+    S(s).vmult(dst_dev, src_dev);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_do_matvec(mgb_solver s)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    const int        L = m.n_levels - 1;
+    m.matrix_dp[L]->vmult(m.residual[L]->p, m.solution[L]->p);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_do_matvec_smoother(mgb_solver s)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    const int        L = m.n_levels - 1;
+    m.matrix[L]->vmult(m.solution_update[L]->p, m.defect[L]->p);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_timings(mgb_solver s, double *timings, int reset)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    for (int l = 0; l < m.n_levels; ++l)
+      for (int j = 0; j < 6; ++j)
+        {
+          timings[l * 6 + j] = m.timings[l][j];
+          if (reset)
+            m.timings[l][j] = 0;
+        }
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_vector(mgb_solver s, int which, int level, void **dev_ptr)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    switch (which)
+      {
+        case 0: *dev_ptr = m.solution[level]->p; break;
+        case 1: *dev_ptr = m.rhs[level]->p; break;
+        case 2: *dev_ptr = m.residual[level]->p; break;
+        case 3: *dev_ptr = m.defect[level]->p; break;
+        case 4: *dev_ptr = m.t[level]->p; break;
+        case 5: *dev_ptr = m.solution_update[level]->p; break;
+        case 6: *dev_ptr = m.matrix[level]->inverse_diagonal.p; break;
+        default: throw std::runtime_error("unknown vector id");
+      }
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_get_solution(mgb_solver s, double *solution_host)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    const int        L = m.n_levels - 1;
+    m.set_boundary_values(L, false);
+    MGB_CUDA_CHECK(cudaMemcpyAsync(solution_host, m.solution[L]->p, m.solution[L]->n * sizeof(double), cudaMemcpyDeviceToHost, m.ctx.stream));
+    m.ctx.sync();
+    MGB_CATCH
+  }
+
+  int
+  mgb_op_vmult(mgb_solver s, int level, int precision, void *dst, const void *src)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (precision == MGB_F64)
+      m.matrix_dp[level]->vmult((double *)dst, (const double *)src);
+    else
+      m.matrix[level]->vmult((float *)dst, (const float *)src);
+    MGB_CATCH
+  }
+
+  int
+  mgb_op_vmult_add(mgb_solver s, int level, int precision, void *dst, const void *src)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    // Base::vmult_add = apply_add, then identity rows added for the constrained DoFs
+    if (precision == MGB_F64)
+      {
+        m.matrix_dp[level]->vmult_add((double *)dst, (const double *)src);
+        double         *d = (double *)dst;
+        const double   *x = (const double *)src;
+        const uint32_t *c = m.levels[level]->constrained.p;
+        foreach (m.ctx, m.levels[level]->constrained.n, [=] __device__(size_t i) { d[c[i]] += x[c[i]]; });
+      }
+    else
+      {
+        m.matrix[level]->vmult_add((float *)dst, (const float *)src);
+        float          *d = (float *)dst;
+        const float    *x = (const float *)src;
+        const uint32_t *c = m.levels[level]->constrained.p;
+        foreach (m.ctx, m.levels[level]->constrained.n, [=] __device__(size_t i) { d[c[i]] += x[c[i]]; });
+      }
+    MGB_CATCH
+  }
+
+  int
+  mgb_op_Tvmult(mgb_solver s, int level, int precision, void *dst, const void *src)
+  {
+    return mgb_op_vmult(s, level, precision, dst, src); // symmetric operator
+  }
+
+  int
+  mgb_op_vmult_residual(mgb_solver s, int level, int precision, const void *rhs, const void *lhs, void *residual)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (precision == MGB_F64)
+      m.matrix_dp[level]->vmult_residual((const double *)rhs, (const double *)lhs, (double *)residual);
+    else
+      m.matrix[level]->vmult_residual((const float *)rhs, (const float *)lhs, (float *)residual);
+    MGB_CATCH
+  }
+
+  int
+  mgb_op_vmult_with_cg_update(mgb_solver s, int level, int precision, double alpha, double beta,
+                              const void *r, void *q, void *p, void *x, double sums[4])
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (precision == MGB_F64)
+      m.matrix_dp[level]->vmult_with_cg_update(alpha, beta, (const double *)r, (double *)q, (double *)p, (double *)x, sums);
+    else
+      m.matrix[level]->vmult_with_cg_update((float)alpha, (float)beta, (const float *)r, (float *)q, (float *)p, (float *)x, sums);
+    MGB_CATCH
+  }
+
+  int
+  mgb_op_inverse_diagonal(mgb_solver s, int level, int precision, void *inv_diag)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (precision == MGB_F64)
+      {
+        m.matrix_dp[level]->compute_diagonal();
+        MGB_CUDA_CHECK(cudaMemcpyAsync(inv_diag, m.matrix_dp[level]->inverse_diagonal.p, m.matrix_dp[level]->m() * sizeof(double), cudaMemcpyDeviceToDevice, m.ctx.stream));
+      }
+    else
+      MGB_CUDA_CHECK(cudaMemcpyAsync(inv_diag, m.matrix[level]->inverse_diagonal.p, m.matrix[level]->m() * sizeof(float), cudaMemcpyDeviceToDevice, m.ctx.stream));
+    MGB_CATCH
+  }
+
+  int
+  mgb_op_set_kernel(mgb_solver s, int kernel)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    for (int l = 0; l < m.n_levels; ++l)
+      m.matrix[l]->kernel = m.matrix_dp[l]->kernel = kernel;
+    MGB_CATCH
+  }
+
+  int
+  mgb_smoother_info(mgb_solver s, int level, double info[6])
+  {
+    MGB_TRY
+    MultigridSolver &m        = S(s);
+    const Chebyshev<float> &c = *m.smooth[check_level(m, level)];
+    info[0]                   = c.min_eig;
+    info[1]                   = c.max_eig;
+    info[2]                   = c.theta;
+    info[3]                   = c.delta;
+    info[4]                   = c.degree;
+    info[5]                   = c.cg_iterations;
+    MGB_CATCH
+  }
+
+  static void
+  smoother_apply(MultigridSolver &m, int level, float *x, const float *b, bool step)
+  {
+    // run on a solver-owned vector (the smoother swaps buffers), then copy back
+    DVec<float> &work = *m.t[level];
+    const size_t N    = work.n;
+    MGB_CUDA_CHECK(cudaMemcpyAsync(work.p, x, N * sizeof(float), cudaMemcpyDeviceToDevice, m.ctx.stream));
+    if (step)
+      m.smooth[level]->step(work, b);
+    else
+      m.smooth[level]->vmult(work, b);
+    MGB_CUDA_CHECK(cudaMemcpyAsync(x, work.p, N * sizeof(float), cudaMemcpyDeviceToDevice, m.ctx.stream));
+  }
+
+  int
+  mgb_smoother_vmult(mgb_solver s, int level, float *x, const float *b)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    smoother_apply(m, check_level(m, level), x, b, false);
+    MGB_CATCH
+  }
+
+  int
+  mgb_smoother_step(mgb_solver s, int level, float *x, const float *b)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    smoother_apply(m, check_level(m, level), x, b, true);
+    MGB_CATCH
+  }
+
+  int
+  mgb_transfer_prolongate(mgb_solver s, int level, float *fine, const float *coarse)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (level == 0)
+      throw std::runtime_error("no transfer to level 0");
+    m.transfer[level].prolongate(fine, coarse);
+    MGB_CATCH
+  }
+
+  int
+  mgb_transfer_prolongate_and_add(mgb_solver s, int level, float *fine, const float *coarse)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (level == 0)
+      throw std::runtime_error("no transfer to level 0");
+    m.transfer[level].prolongate_and_add(fine, coarse);
+    MGB_CATCH
+  }
+
+  int
+  mgb_transfer_restrict_and_add(mgb_solver s, int level, float *coarse, const float *fine)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (level == 0)
+      throw std::runtime_error("no transfer from level 0");
+    m.transfer[level].restrict_and_add(coarse, fine);
+    MGB_CATCH
+  }
+
+  int
+  mgb_transfer_prolongate_no_boundary(mgb_solver s, int level, double *fine, const double *coarse)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (level == 0)
+      throw std::runtime_error("no transfer to level 0");
+    m.mg_transfer_no_boundary[level].prolongate(fine, coarse);
+    MGB_CATCH
+  }
+
+  int
+  mgb_device_alloc(mgb_solver s, size_t bytes, void **dev_ptr)
+  {
+    MGB_TRY
+    MGB_CUDA_CHECK(cudaSetDevice(S(s).ctx.device));
+    MGB_CUDA_CHECK(cudaMalloc(dev_ptr, bytes));
+    MGB_CUDA_CHECK(cudaMemsetAsync(*dev_ptr, 0, bytes, S(s).ctx.stream));
+    MGB_CATCH
+  }
+
+  int
+  mgb_device_free(mgb_solver s, void *dev_ptr)
+  {
+    MGB_TRY
+    S(s).ctx.sync();
+    MGB_CUDA_CHECK(cudaFree(dev_ptr));
+    MGB_CATCH
+  }
+
+  int
+  mgb_copy_to_device(mgb_solver s, void *dst_dev, const void *src_host, size_t bytes)
+  {
+    MGB_TRY
+    MGB_CUDA_CHECK(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, S(s).ctx.stream));
+    S(s).ctx.sync();
+    MGB_CATCH
+  }
+
+  int
+  mgb_copy_to_host(mgb_solver s, void *dst_host, const void *src_dev, size_t bytes)
+  {
+    MGB_TRY
+    MGB_CUDA_CHECK(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, S(s).ctx.stream));
+    S(s).ctx.sync();
+    MGB_CATCH
+  }
+
+  int64_t
+  mgb_solver_launch_count(mgb_solver s)
+  {
+    return s && s->impl ? s->impl->ctx.launches : -1;
+  }
+
+  // ---- host-only helpers (no GPU needed): used by the CPU test-suite for the host logic
+  int
+  mgb_host_basis(int p, double *S, double *G, double *D, double *M1, double *K1, double *P1,
+                 double *nodes, double *xq, double *wq)
+  {
+    MGB_TRY
+    if (p < 1 || p > 8)
+      throw std::runtime_error("polynomial degree must be between 1 and 8");
+    const Basis b = make_basis(p);
+    std::copy(b.S.begin(), b.S.end(), S);
+    std::copy(b.G.begin(), b.G.end(), G);
+    std::copy(b.D.begin(), b.D.end(), D);
+    std::copy(b.M1.begin(), b.M1.end(), M1);
+    std::copy(b.K1.begin(), b.K1.end(), K1);
+    std::copy(b.P1.begin(), b.P1.end(), P1);
+    std::copy(b.nodes.begin(), b.nodes.end(), nodes);
+    std::copy(b.xq.begin(), b.xq.end(), xq);
+    std::copy(b.wq.begin(), b.wq.end(), wq);
+    MGB_CATCH
+  }
+
+  // numbering of one box level: returns n_dofs / n_interior / M and fills lex_to_dof (n_dofs),
+  // ent_base (n_patches*27), ent_mask (n_patches) when non-NULL
+  int
+  mgb_host_numbering(int p, const int ncell[3], int max_patch_cells, int64_t *n_dofs, int64_t *n_interior,
+                     int *patch_cells, int64_t *n_constrained, uint32_t *lex_to_dof)
+  {
+    MGB_TRY
+    HostLevel    lvl;
+    const double lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
+    const int    M     = choose_patch_cells(p, ncell, max_patch_cells);
+    build_box_level(p, ncell, M, lo, hi, lvl);
+    *n_dofs        = lvl.d.n_dofs;
+    *n_interior    = lvl.d.n_interior;
+    *patch_cells   = M;
+    *n_constrained = (int64_t)lvl.constrained.size();
+    if (lex_to_dof)
+      build_lex_map(lvl, lex_to_dof);
+    MGB_CATCH
+  }
+}

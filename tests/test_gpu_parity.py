@@ -1,0 +1,269 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same seeded
+inputs.  Tolerances follow BASELINE.json's north_star: matvec relative error <= 1e-12 in double,
+<= 1e-5 in the float levels, identical CG iteration counts, L2 error to 3 significant digits."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "readme_table.json")))
+TOL = {True: 1e-12, False: 1e-5}
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch as t
+    if not t.cuda.is_available():
+        pytest.skip("no GPU")
+    return t
+
+
+def rel(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+class Pair:
+    """GPU solver + oracle on the same mesh, with the permutation between their numberings."""
+
+    def __init__(self, mgb, orc, torch, p, nsub, nref, **kw):
+        kw.setdefault("degree_pre", 3)
+        kw.setdefault("degree_post", 3)
+        kw.setdefault("n_cycles", 2)
+        okw = dict(kw)
+        self.g = mgb.MultigridSolver(p, nsub, nref, **kw)
+        okw.pop("kernel", None)
+        okw.pop("max_patch_cells", None)
+        self.o = orc.MultigridSolver(p, nsub, nref, **okw)
+        self.torch = torch
+        self.maps = {}
+
+    def lex(self, level):
+        level = self.g._l(level)
+        if level not in self.maps:
+            self.maps[level] = self.g.lex_map(level)
+        return self.maps[level]
+
+    def to_dev(self, x_lex, level, double=True):
+        v = np.zeros_like(x_lex)
+        v[self.lex(level)] = x_lex
+        return self.torch.tensor(v, dtype=self.torch.float64 if double else self.torch.float32, device="cuda")
+
+    def to_lex(self, t, level):
+        return t.double().cpu().numpy()[self.lex(level)]
+
+
+MESHES = [  # (p, nsub, nref, level, max_patch_cells)   -> covers M = 1, 2, 4 and ragged boxes
+    (1, (1, 1, 1), 3, -1, 0), (2, (1, 2, 1), 2, -1, 0), (3, (1, 1, 1), 2, -1, 0), (4, (1, 1, 1), 2, -1, 0),
+    (4, (3, 1, 2), 1, -1, 0), (4, (3, 1, 2), 0, -1, 0), (5, (1, 1, 1), 2, -1, 0), (6, (1, 1, 2), 1, -1, 0),
+    (7, (1, 1, 1), 1, -1, 0), (8, (1, 1, 1), 1, -1, 0), (4, (1, 1, 1), 3, -1, 2), (2, (1, 1, 1), 3, -1, 0),
+]
+
+
+@pytest.mark.parametrize("kernel", [0, 1])
+@pytest.mark.parametrize("double", [True, False])
+@pytest.mark.parametrize("mesh", MESHES)
+def test_vmult_family(mgb, orc, torch, mesh, double, kernel):
+    p, nsub, nref, level, maxm = mesh
+    P = Pair(mgb, orc, torch, p, nsub, nref, kernel=kernel, max_patch_cells=maxm)
+    op = P.g.matrix_dp(level) if double else P.g.matrix(level)
+    n = P.g.n_dofs(level)
+    assert n == P.o.n_dofs(level)
+    rng = np.random.default_rng(42)
+    x, b = rng.random(n), rng.random(n)
+    dx, db = P.to_dev(x, level, double), P.to_dev(b, level, double)
+    dst = op.initialize_dof_vector()
+    tol = TOL[double]
+    # vmult (laplace_operator.h:575-601)
+    op.vmult(dst, dx)
+    ref = P.o.vmult(x, level, double)
+    assert rel(P.to_lex(dst, level), ref) <= tol, ("vmult", rel(P.to_lex(dst, level), ref))
+    # Tvmult == vmult
+    dst.zero_()
+    op.Tvmult(dst, dx)
+    assert rel(P.to_lex(dst, level), ref) <= tol
+    # vmult_add
+    dst.copy_(db)
+    op.vmult_add(dst, dx)
+    assert rel(P.to_lex(dst, level), ref + b) <= tol, "vmult_add"
+    # vmult_residual (:607-634)
+    op.vmult_residual(db, dx, dst)
+    ref_r = P.o.vmult_residual(b, x, level, double)
+    assert np.abs(P.to_lex(dst, level) - ref_r).max() <= tol * np.abs(ref).max(), "vmult_residual"
+
+
+@pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 2), (3, (2, 1, 1), 1), (2, (1, 1, 1), 3)])
+def test_variable_coefficient(mgb, orc, torch, mesh):
+    """per-quadrature-point merged coefficient (laplace_operator.h:388-430, :493-522)"""
+    p, nsub, nref = mesh
+    P = Pair(mgb, orc, torch, p, nsub, nref, problem=1, lower=(0.1, 0.2, 0.3), upper=(0.9, 1.1, 1.0))
+    for double in (True, False):
+        op = P.g.matrix_dp() if double else P.g.matrix()
+        n = P.g.n_dofs()
+        x = np.random.default_rng(7).random(n)
+        dst = op.initialize_dof_vector()
+        op.vmult(dst, P.to_dev(x, -1, double))
+        ref = P.o.vmult(x, -1, double)
+        assert rel(P.to_lex(dst, -1), ref) <= TOL[double] * (1 if double else 3), rel(P.to_lex(dst, -1), ref)
+    d = P.g.matrix().get_matrix_diagonal_inverse()
+    assert rel(P.to_lex(d, -1), P.o.get_vector(orc.VEC_INV_DIAG)) <= 1e-5
+
+
+@pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 2), (3, (2, 1, 3), 1), (1, (1, 1, 1), 2), (8, (1, 1, 1), 1)])
+def test_diagonal_and_cg_update(mgb, orc, torch, mesh):
+    p, nsub, nref = mesh
+    P = Pair(mgb, orc, torch, p, nsub, nref)
+    d32 = P.g.matrix().get_matrix_diagonal_inverse()
+    assert rel(P.to_lex(d32, -1), P.o.get_vector(orc.VEC_INV_DIAG)) <= 1e-5
+    d64 = P.g.matrix_dp().get_matrix_diagonal_inverse()
+    assert rel(P.to_lex(d64, -1), P.o.inverse_diagonal_dp()) <= 1e-12
+    # vmult_with_cg_update (laplace_operator.h:640-719)
+    n = P.g.n_dofs()
+    rng = np.random.default_rng(5)
+    r, q, pp, x = (rng.random(n) for _ in range(4))
+    for alpha, beta in ((0.0, 0.0), (0.7, 0.3)):
+        sums_ref, q_ref, p_ref, x_ref = P.o.vmult_with_cg_update(alpha, beta, r, q, pp, x)
+        dr, dq, dp_, dx = (P.to_dev(v, -1) for v in (r, q, pp, x))
+        sums = P.g.matrix_dp().vmult_with_cg_update(alpha, beta, dr, dq, dp_, dx)
+        assert np.allclose(sums, sums_ref, rtol=1e-11), (sums, sums_ref)
+        assert rel(P.to_lex(dq, -1), q_ref) <= 1e-12
+        assert rel(P.to_lex(dp_, -1), p_ref) <= 1e-13
+        assert rel(P.to_lex(dx, -1), x_ref) <= 1e-13
+
+
+@pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 3), (3, (2, 1, 1), 2), (1, (1, 1, 1), 3), (2, (1, 1, 3), 2), (7, (1, 1, 1), 1)])
+def test_transfer(mgb, orc, torch, mesh):
+    p, nsub, nref = mesh
+    P = Pair(mgb, orc, torch, p, nsub, nref)
+    rng = np.random.default_rng(11)
+    for level in range(1, P.g.n_levels):
+        nf, nc = P.g.n_dofs(level), P.g.n_dofs(level - 1)
+        c, f = rng.random(nc), rng.random(nf)
+        dc, df = P.to_dev(c, level - 1, False), P.to_dev(f, level, False)
+        out = torch.zeros(nf, dtype=torch.float32, device="cuda")
+        P.g.prolongate(level, out, dc)
+        assert rel(P.to_lex(out, level), P.o.prolongate(c, level)) <= 1e-6, "prolongate"
+        out.copy_(df)
+        P.g.prolongate_and_add(level, out, dc)
+        assert rel(P.to_lex(out, level), P.o.prolongate(c, level, add_to=f)) <= 1e-6, "prolongate_and_add"
+        outc = dc.clone()
+        P.g.restrict_and_add(level, outc, df)
+        assert rel(P.to_lex(outc, level - 1), P.o.restrict_and_add(f, level, coarse=c)) <= 2e-6, "restrict"
+        out64 = torch.zeros(nf, dtype=torch.float64, device="cuda")
+        P.g.prolongate_no_boundary(level, out64, P.to_dev(c, level - 1, True))
+        assert rel(P.to_lex(out64, level), P.o.prolongate_no_boundary(c, level)) <= 1e-14
+        # restriction is the transpose of the (constrained) prolongation
+        lhs = float((P.to_lex(out, level) - f) @ f)
+        rhs = float((P.to_lex(outc, level - 1) - c) @ c)
+        assert abs(lhs - rhs) <= 2e-5 * abs(lhs)
+
+
+@pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 2, 3), (2, (1, 1, 1), 3, 2), (3, (1, 2, 1), 2, 4)])
+def test_smoother(mgb, orc, torch, mesh):
+    p, nsub, nref, deg = mesh
+    P = Pair(mgb, orc, torch, p, nsub, nref, degree_pre=deg, degree_post=deg)
+    rng = np.random.default_rng(3)
+    for level in range(P.g.n_levels):
+        gi, oi = P.g.smoother_info(level), P.o.chebyshev_info(level)
+        assert gi["degree"] == oi["degree"] and gi["cg_iterations"] == oi["cg_iterations"], (gi, oi)
+        assert abs(gi["max_eig"] - oi["max_eig"]) <= 2e-4 * oi["max_eig"], (gi, oi)
+        assert abs(gi["theta"] - oi["theta"]) <= 2e-4 * oi["theta"]
+        n = P.g.n_dofs(level)
+        b, x0 = rng.random(n), rng.random(n)
+        db = P.to_dev(b, level, False)
+        dx = torch.zeros(n, dtype=torch.float32, device="cuda")
+        P.g.smoother_vmult(level, dx, db)
+        ref = P.o.chebyshev_vmult(b, level)
+        assert rel(P.to_lex(dx, level), ref) <= 2e-3, ("vmult", level, rel(P.to_lex(dx, level), ref))
+        dx = P.to_dev(x0, level, False)
+        P.g.smoother_step(level, dx, db)
+        ref = P.o.chebyshev_step(x0, b, level)
+        assert rel(P.to_lex(dx, level), ref) <= 2e-3, ("step", level)
+
+
+@pytest.mark.parametrize("kernel", [0, 1])
+@pytest.mark.parametrize("mesh", [(4, 1, 3), (4, 3, 1), (2, 1, 3), (3, 1, 2), (6, 1, 1)])
+def test_solver_against_oracle(mgb, orc, torch, mesh, kernel):
+    p, nsub, nref = mesh
+    P = Pair(mgb, orc, torch, p, nsub, nref, kernel=kernel)
+    L = P.g.n_levels - 1
+    # right-hand side incl. inhomogeneous boundary lift (laplace_operator.h:806-845)
+    for level in range(P.g.n_levels):
+        rhs = P.g.get_vector("rhs", level)[P.lex(level)]
+        assert rel(rhs, P.o.get_vector(orc.VEC_RHS, level)) <= 1e-12, ("rhs", level)
+    # one V-cycle as preconditioner (multigrid_solver.h:498-510)
+    x = np.random.default_rng(9).random(P.g.n_dofs())
+    nd = P.g.dof_grid()
+    mask = np.ones((nd[2], nd[1], nd[0]))
+    mask[0], mask[-1], mask[:, 0], mask[:, -1], mask[:, :, 0], mask[:, :, -1] = (0,) * 6
+    x *= mask.ravel()
+    dst = torch.zeros(P.g.n_dofs(), dtype=torch.float64, device="cuda")
+    P.g.vmult(dst, P.to_dev(x, L))
+    ref = P.o.vcycle(x)
+    assert rel(P.to_lex(dst, L), ref) <= 5e-3, ("vcycle", rel(P.to_lex(dst, L), ref))
+    # FMG (multigrid_solver.h:387-476)
+    red, trace = P.g.solve(True)
+    red_o, trace_o = P.o.solve(True)
+    assert np.allclose(trace[1:], trace_o[1:], rtol=2e-2), (trace, trace_o)
+    assert abs(red - red_o) <= 2e-2 * red_o
+    e, e_o = P.g.compute_l2_error(), P.o.compute_l2_error()
+    assert abs(e - e_o) <= 5e-3 * e_o, (e, e_o)
+    # CG + V-cycle (multigrid_solver.h:483-493)
+    its, rate = P.g.solve_cg()
+    its_o, rate_o, hist_o = P.o.solve_cg()
+    assert its == its_o, (its, its_o)
+    hist = P.g.cg_history()
+    assert np.allclose(hist, hist_o, rtol=0.05), (hist, hist_o)
+    e, e_o = P.g.compute_l2_error(), P.o.compute_l2_error()
+    assert abs(e - e_o) <= 1e-3 * e_o, (e, e_o)
+    sol = P.g.get_solution()[P.lex(L)]
+    assert rel(sol, P.o.get_vector(orc.VEC_SOLUTION)) <= 1e-6
+
+
+def test_readme_golden_config1(mgb, torch):
+    """config 1 of BASELINE.json: 28^3 cells, 1 442 897 DoF; README.md:150"""
+    row = [r for r in GOLDEN["rows"] if r[0] == 21952][0]
+    s = mgb.MultigridSolver(4, 7, 2)
+    assert s.n_dofs() == row[1]
+    s.solve(False)
+    e_fmg = s.compute_l2_error()
+    its, rate = s.solve_cg()
+    e_cg = s.compute_l2_error()
+    assert its == row[5] == 8
+    assert abs(e_cg - row[4]) <= 1e-3 * row[4], e_cg          # 8.207e-07 to 3+ digits
+    assert abs(e_fmg - row[3]) <= 5e-3 * row[3], e_fmg        # 8.213e-07
+    assert abs(rate - row[6]) <= 0.05 * row[6], rate
+
+
+def test_properties_at_scale(mgb, torch):
+    """size-independent properties on a mesh the oracle would need minutes for: 64^3 cells, 17 M DoF"""
+    s = mgb.MultigridSolver(4, 1, 6)
+    n = s.n_dofs()
+    assert n == 16974593
+    op = s.matrix_dp()
+    g = torch.Generator(device="cuda").manual_seed(42)
+    x = torch.rand(n, dtype=torch.float64, device="cuda", generator=g)
+    y = torch.rand(n, dtype=torch.float64, device="cuda", generator=g)
+    ax, ay, axy = (op.initialize_dof_vector() for _ in range(3))
+    op.vmult(ax, x)
+    op.vmult(ay, y)
+    # symmetry and linearity
+    assert abs(float(ax @ y) - float(ay @ x)) <= 1e-12 * abs(float(ax @ y))
+    op.vmult(axy, 2.0 * x - 0.5 * y)
+    assert float((axy - (2.0 * ax - 0.5 * ay)).abs().max()) <= 1e-12 * float(ax.abs().max())
+    # Cartesian patch kernel == general cell kernel
+    s.set_kernel(mgb.KERNEL_GENERAL)
+    op.vmult(axy, x)
+    s.set_kernel(mgb.KERNEL_AUTO)
+    assert float((axy - ax).abs().max()) <= 1e-12 * float(ax.abs().max())
+    # positive definiteness on a zero-boundary vector + golden row of the README (README.md:154)
+    row = [r for r in GOLDEN["rows"] if r[1] == n][0]
+    its, rate = s.solve_cg()
+    e = s.compute_l2_error()
+    assert its == row[5]
+    assert abs(e - row[4]) <= 2e-3 * row[4], e
+    s.solve(False)
+    e = s.compute_l2_error()
+    assert abs(e - row[3]) <= 1e-2 * row[3], e
