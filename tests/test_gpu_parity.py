@@ -157,7 +157,8 @@ def test_transfer(mgb, orc, torch, mesh):
         # restriction is the transpose of the (constrained) prolongation
         lhs = float((P.to_lex(out, level) - f) @ f)
         rhs = float((P.to_lex(outc, level - 1) - c) @ c)
-        assert abs(lhs - rhs) <= 2e-5 * abs(lhs)
+        # (level 0 of a 1-subdivision mesh is all-Dirichlet for p = 1: both sides are float round-off)
+        assert abs(lhs - rhs) <= 2e-5 * abs(lhs) + 1e-6
 
 
 @pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 2, 3), (2, (1, 1, 1), 3, 2), (3, (1, 2, 1), 2, 4)])
