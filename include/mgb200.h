@@ -93,8 +93,19 @@ int mgb_solver_vcycle(mgb_solver s, double *dst_dev, const double *src_dev);
 /* MultigridSolver::do_matvec / do_matvec_smoother         multigrid_solver.h:624-637 */
 int mgb_solver_do_matvec(mgb_solver s);
 int mgb_solver_do_matvec_smoother(mgb_solver s);
-/* MultigridSolver::print_wall_times                       multigrid_solver.h:348-371 : 6 doubles per level */
+/* MultigridSolver::print_wall_times                       multigrid_solver.h:348-371 : 6 doubles per level
+ * (seconds; columns mg_mv, restrict, prolongate, inhomBC, mg_vec, smoother as timings[level][0..5], :776);
+ * measured with CUDA events on the solver stream while mgb_solver_profile(s, 1) is active       */
 int mgb_solver_timings(mgb_solver s, double *timings, int reset);
+/* switch the CUDA-event ranges on/off (the LIKWID regions of poisson_cube/program.cc:281-376)    */
+int mgb_solver_profile(mgb_solver s, int on);
+/* accumulated milliseconds / number of ranges per class on one level (16 entries each):
+ * 0..5 as above, 6 cell-loop kernel double, 7 cell-loop kernel float, 8 cell-loop kernel float with the
+ * fused Chebyshev update, 9 patch-boundary epilogue kernel, 10 outer CG vector work, 11 other    */
+int mgb_solver_class_times(mgb_solver s, int level, double *ms, int64_t *count, int reset);
+/* CUDA-event stopwatch on the solver's stream (Timer of poisson_cube/program.cc:283-322)         */
+int mgb_timer_start(mgb_solver s);
+int mgb_timer_stop(mgb_solver s, double *ms);
 /* device address of a solver-owned vector: which = 0 solution, 1 rhs, 2 residual (double);
  * 3 defect, 4 t, 5 solution_update, 6 inverse diagonal (float)     multigrid_solver.h:709-735 */
 int mgb_solver_vector(mgb_solver s, int which, int level, void **dev_ptr);
@@ -106,6 +117,8 @@ int mgb_solver_get_solution(mgb_solver s, double *solution_host);
 int mgb_op_vmult(mgb_solver s, int level, int precision, void *dst, const void *src);           /* :575-601 */
 int mgb_op_vmult_add(mgb_solver s, int level, int precision, void *dst, const void *src);       /* Base::vmult_add */
 int mgb_op_Tvmult(mgb_solver s, int level, int precision, void *dst, const void *src);          /* Base::Tvmult (symmetric) */
+/* vmult with HOST vectors in library numbering: copy in, apply, copy out (end-to-end call)      */
+int mgb_op_vmult_host(mgb_solver s, int level, int precision, void *dst_host, const void *src_host);
 int mgb_op_vmult_residual(mgb_solver s, int level, int precision, const void *rhs, const void *lhs,
                           void *residual);                                                       /* :607-634 */
 /* std::array<number,4> vmult_with_cg_update(alpha,beta,r,q,p,x)                                    :640-719 */

@@ -73,6 +73,11 @@ SYMBOLS = {
     "mgb_solver_do_matvec": (_i, [_vp]),
     "mgb_solver_do_matvec_smoother": (_i, [_vp]),
     "mgb_solver_timings": (_i, [_vp, _dp, _i]),
+    "mgb_solver_profile": (_i, [_vp, _i]),
+    "mgb_solver_class_times": (_i, [_vp, _i, _dp, C.POINTER(C.c_int64), _i]),
+    "mgb_timer_start": (_i, [_vp]),
+    "mgb_timer_stop": (_i, [_vp, _dp]),
+    "mgb_op_vmult_host": (_i, [_vp, _i, _i, _vp, _vp]),
     "mgb_solver_vector": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
     "mgb_solver_get_solution": (_i, [_vp, _vp]),
     "mgb_op_vmult": (_i, [_vp, _i, _i, _vp, _vp]),
@@ -337,6 +342,31 @@ class MultigridSolver:
         t = np.zeros((self.n_levels, 6))
         _check(lib().mgb_solver_timings(self.h, t.ctypes.data_as(_dp), int(reset)))
         return t
+
+    def profile(self, on=True):
+        _check(lib().mgb_solver_profile(self.h, int(on)))
+
+    CLASSES = ("mg_mv", "restrict", "prolongate", "inhomBC", "mg_vec", "smoother", "apply_f64", "apply_f32",
+               "apply_f32_chebyshev", "apply_epilogue", "cg_vec", "other")
+
+    def class_times(self, level=-1, reset=True):
+        """{class: (milliseconds, count)} of the CUDA-event ranges on one level."""
+        ms = (C.c_double * 16)()
+        cnt = (C.c_int64 * 16)()
+        _check(lib().mgb_solver_class_times(self.h, self._l(level), ms, cnt, int(reset)))
+        return {k: (ms[i], cnt[i]) for i, k in enumerate(self.CLASSES)}
+
+    def timer_start(self):
+        _check(lib().mgb_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_double()
+        _check(lib().mgb_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def vmult_host(self, dst_host, src_host, level=-1, precision=F64):
+        ptr = lambda a: C.c_void_p(a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data)
+        _check(lib().mgb_op_vmult_host(self.h, self._l(level), precision, ptr(dst_host), ptr(src_host)))
 
     def print_wall_times(self):
         t = self.timings()

@@ -64,6 +64,78 @@ namespace mgb
     double      *scal_host = nullptr; // pinned mirror
     bool         profile  = false;
 
+    // ---- optional CUDA-event ranges on the solver stream (README-style per-level table,
+    //      multigrid_solver.h:348-371, and per-kernel-class launch durations for bench.py)
+    static constexpr int n_classes_per_level = 16;
+    struct Range
+    {
+      cudaEvent_t a, b;
+      int         cls;
+    };
+    std::vector<Range>       open_ranges;
+    std::vector<cudaEvent_t> event_pool;
+    std::vector<double>      class_ms;
+    std::vector<int64_t>     class_count;
+    cudaEvent_t              timer_ev[2] = {nullptr, nullptr};
+
+    cudaEvent_t
+    get_event()
+    {
+      cudaEvent_t e;
+      if (!event_pool.empty())
+        {
+          e = event_pool.back();
+          event_pool.pop_back();
+        }
+      else
+        MGB_CUDA_CHECK(cudaEventCreate(&e));
+      return e;
+    }
+    // returns a handle (index) or -1 when profiling is off
+    int
+    range_begin(const int level, const int kind)
+    {
+      if (!profile)
+        return -1;
+      if (open_ranges.size() > 200000)
+        collect_ranges();
+      Range r;
+      r.a   = get_event();
+      r.b   = get_event();
+      r.cls = level * n_classes_per_level + kind;
+      MGB_CUDA_CHECK(cudaEventRecord(r.a, stream));
+      open_ranges.push_back(r);
+      return (int)open_ranges.size() - 1;
+    }
+    void
+    range_end(const int handle)
+    {
+      if (handle >= 0)
+        cudaEventRecord(open_ranges[handle].b, stream); // called from destructors: never throws
+    }
+    void
+    collect_ranges()
+    {
+      if (open_ranges.empty())
+        return;
+      MGB_CUDA_CHECK(cudaStreamSynchronize(stream));
+      for (const Range &r : open_ranges)
+        {
+          float ms = 0;
+          MGB_CUDA_CHECK(cudaEventElapsedTime(&ms, r.a, r.b));
+          if ((size_t)r.cls >= class_ms.size())
+            {
+              class_ms.resize(r.cls + 1, 0.);
+              class_count.resize(r.cls + 1, 0);
+            }
+          class_ms[r.cls] += ms;
+          class_count[r.cls] += 1;
+          event_pool.push_back(r.a);
+          event_pool.push_back(r.b);
+        }
+      open_ranges.clear();
+    }
+
     void
     init(const int dev)
     {
@@ -80,6 +152,19 @@ namespace mgb
         cudaFree(scal_dev);
       if (scal_host)
         cudaFreeHost(scal_host);
+      for (const Range &r : open_ranges)
+        {
+          cudaEventDestroy(r.a);
+          cudaEventDestroy(r.b);
+        }
+      open_ranges.clear();
+      for (cudaEvent_t e : event_pool)
+        cudaEventDestroy(e);
+      event_pool.clear();
+      for (int i = 0; i < 2; ++i)
+        if (timer_ev[i])
+          cudaEventDestroy(timer_ev[i]);
+      timer_ev[0] = timer_ev[1] = nullptr;
       if (stream)
         cudaStreamDestroy(stream);
       scal_dev = scal_host = nullptr;
@@ -96,6 +181,35 @@ namespace mgb
       ++launches;
       MGB_CUDA_CHECK(cudaGetLastError());
     }
+  };
+
+  // kinds of timed ranges (per level).  0..5 are the columns of print_wall_times
+  // (multigrid_solver.h:655-679,776); the rest are kernel classes
+  enum RangeKind
+  {
+    RK_MG_MV = 0,
+    RK_RESTRICT,
+    RK_PROLONGATE,
+    RK_INHOM_BC,
+    RK_MG_VEC,
+    RK_SMOOTHER,
+    RK_APPLY_F64,       // cell-loop kernel, double
+    RK_APPLY_F32,       // cell-loop kernel, float, set/add/residual
+    RK_APPLY_F32_CHEB,  // cell-loop kernel, float, fused Chebyshev update
+    RK_APPLY_EPILOGUE,  // patch-boundary epilogue kernel
+    RK_CG_VEC,          // outer CG vector updates and dot products
+    RK_OTHER
+  };
+
+  struct ScopedRange
+  {
+    Ctx &ctx;
+    int  h;
+    ScopedRange(Ctx &c, const int level, const int kind)
+      : ctx(c)
+      , h(c.range_begin(level, kind))
+    {}
+    ~ScopedRange() { ctx.range_end(h); }
   };
 
   template <typename T>
@@ -228,6 +342,7 @@ namespace mgb
   {
     HostLevel      host;
     LevelDesc      d; // with device pointers
+    int            index = 0; // multigrid level number
     DVec<uint32_t> ent_base, ent_mask, constrained;
     DVec<uint8_t>  bflag;
 
@@ -387,9 +502,16 @@ namespace mgb
       A.first_chebyshev = 0;
     }
 
+    int
+    range_kind(const int mode) const
+    {
+      return sizeof(T) == 8 ? RK_APPLY_F64 : (mode == APPLY_CHEBYSHEV ? RK_APPLY_F32_CHEB : RK_APPLY_F32);
+    }
+
     void
     launch_general(const ApplyArgs<T> &A) const
     {
+      ScopedRange range(*ctx, level->index, range_kind(A.mode));
       if (sizeof(T) == 8)
         dk->apply_general_d(reinterpret_cast<const ApplyArgs<double> &>(A), ctx->stream);
       else
@@ -400,6 +522,7 @@ namespace mgb
     void
     launch_cartesian(const ApplyArgs<T> &A) const
     {
+      ScopedRange range(*ctx, level->index, range_kind(A.mode));
       if (sizeof(T) == 8)
         dk->apply_cartesian_d(reinterpret_cast<const ApplyArgs<double> &>(A), ctx->stream);
       else
@@ -433,6 +556,7 @@ namespace mgb
           // patch-boundary DoFs: finish with the accumulated sums; Dirichlet rows are identity
           T             *bt   = boundary_tmp.p;
           const uint32_t nint = L.n_interior;
+          ScopedRange    range(*ctx, level->index, RK_APPLY_EPILOGUE);
           foreach (*ctx, N - nint, [=] __device__(size_t i) {
             const size_t d = i + nint;
             const T      y = flag[i] ? src[d] : bt[i];
@@ -791,7 +915,6 @@ namespace mgb
     std::vector<std::unique_ptr<DVec<float>>>             defect, t, solution_update;
     DVec<double>                                          cg_g, cg_h, cg_d;
     std::vector<double>                                   cg_history;
-    std::vector<std::array<double, 6>>                    timings;
 
     explicit MultigridSolver(const mgb_options &o)
       : opt(o)
@@ -829,7 +952,6 @@ namespace mgb
         throw std::runtime_error("unknown problem id");
 
       n_levels = o.n_refinements + 1;
-      timings.assign(n_levels, {{0, 0, 0, 0, 0, 0}});
       transfer.resize(n_levels);
       mg_transfer_no_boundary.resize(n_levels);
       const DegreeKernels *dk = &degree_kernels(o.degree);
@@ -840,6 +962,7 @@ namespace mgb
             nc[d] = o.n_subdivisions[d] << l;
           levels.emplace_back(new Level());
           Level &lv = *levels.back();
+          lv.index  = l;
           build_box_level(o.degree, nc, choose_patch_cells(o.degree, nc, o.max_patch_cells), o.lower, o.upper, lv.host);
           lv.upload(ctx.stream);
           const size_t N = lv.d.n_dofs;
@@ -963,21 +1086,37 @@ namespace mgb
     {
       if (level == 0)
         {
+          ScopedRange range(ctx, 0, RK_SMOOTHER);
           smooth[0]->vmult(*solution_update[0], defect[0]->p);
           return;
         }
       for (unsigned int c = 0; c < my_n_cycles; ++c)
         {
-          if (c == 0)
-            smooth[level]->vmult(*solution_update[level], defect[level]->p);
-          else
-            smooth[level]->step(*solution_update[level], defect[level]->p);
-          matrix[level]->vmult_residual(defect[level]->p, solution_update[level]->p, t[level]->p);
-          MGB_CUDA_CHECK(cudaMemsetAsync(defect[level - 1]->p, 0, defect[level - 1]->n * sizeof(float), ctx.stream));
-          transfer[level].restrict_and_add(defect[level - 1]->p, t[level]->p);
+          {
+            ScopedRange range(ctx, level, RK_SMOOTHER);
+            if (c == 0)
+              smooth[level]->vmult(*solution_update[level], defect[level]->p);
+            else
+              smooth[level]->step(*solution_update[level], defect[level]->p);
+          }
+          {
+            ScopedRange range(ctx, level, RK_MG_MV);
+            matrix[level]->vmult_residual(defect[level]->p, solution_update[level]->p, t[level]->p);
+          }
+          {
+            ScopedRange range(ctx, level, RK_RESTRICT);
+            MGB_CUDA_CHECK(cudaMemsetAsync(defect[level - 1]->p, 0, defect[level - 1]->n * sizeof(float), ctx.stream));
+            transfer[level].restrict_and_add(defect[level - 1]->p, t[level]->p);
+          }
           v_cycle(level - 1, 1);
-          transfer[level].prolongate_and_add(solution_update[level]->p, solution_update[level - 1]->p);
-          smooth[level]->step(*solution_update[level], defect[level]->p);
+          {
+            ScopedRange range(ctx, level, RK_PROLONGATE);
+            transfer[level].prolongate_and_add(solution_update[level]->p, solution_update[level - 1]->p);
+          }
+          {
+            ScopedRange range(ctx, level, RK_SMOOTHER);
+            smooth[level]->step(*solution_update[level], defect[level]->p);
+          }
         }
     }
 
@@ -1039,9 +1178,15 @@ namespace mgb
     {
       const int    L = n_levels - 1;
       const size_t N = levels[L]->d.n_dofs;
-      convert(ctx, defect[L]->p, src, N);
+      {
+        ScopedRange range(ctx, L, RK_MG_VEC);
+        convert(ctx, defect[L]->p, src, N);
+      }
       v_cycle(L, 1);
-      convert(ctx, dst, solution_update[L]->p, N);
+      {
+        ScopedRange range(ctx, L, RK_MG_VEC);
+        convert(ctx, dst, solution_update[L]->p, N);
+      }
     }
 
     // multigrid_solver.h:483-493 + deal.II SolverCG with ReductionControl(1000, 1e-16, 1e-9)
@@ -1068,6 +1213,7 @@ namespace mgb
             {
               ++it;
               matrix_dp[L]->vmult(h, d);
+              const int    rg    = ctx.range_begin(L, RK_CG_VEC);
               const double alpha = gh / dot(ctx, d, h, N);
               double       r2;
               // x += alpha d; g += alpha h; |g|^2 in the same pass
@@ -1081,11 +1227,13 @@ namespace mgb
                   acc[0] += gi * gi;
                 },
                 &r2);
+              ctx.range_end(rg);
               res = std::sqrt(r2);
               cg_history.push_back(res);
               if (res <= 1e-16 || res <= 1e-9 * res0 || it >= 1000)
                 break;
               vmult(h, g);
+              ScopedRange  range(ctx, L, RK_CG_VEC);
               const double gh_new = dot(ctx, g, h, N);
               const double beta   = gh_new / gh;
               gh                  = gh_new;
@@ -1356,13 +1504,78 @@ extern "C"
   {
     MGB_TRY
     MultigridSolver &m = S(s);
+    m.ctx.collect_ranges();
+    const int nk = Ctx::n_classes_per_level;
     for (int l = 0; l < m.n_levels; ++l)
       for (int j = 0; j < 6; ++j)
         {
-          timings[l * 6 + j] = m.timings[l][j];
-          if (reset)
-            m.timings[l][j] = 0;
+          const size_t c     = (size_t)l * nk + j;
+          timings[l * 6 + j] = c < m.ctx.class_ms.size() ? 1e-3 * m.ctx.class_ms[c] : 0.;
         }
+    if (reset)
+      {
+        std::fill(m.ctx.class_ms.begin(), m.ctx.class_ms.end(), 0.);
+        std::fill(m.ctx.class_count.begin(), m.ctx.class_count.end(), 0);
+      }
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_profile(mgb_solver s, int on)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    m.ctx.collect_ranges();
+    m.ctx.profile = on != 0;
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_class_times(mgb_solver s, int level, double *ms, int64_t *count, int reset)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    m.ctx.collect_ranges();
+    const int nk = Ctx::n_classes_per_level;
+    for (int j = 0; j < nk; ++j)
+      {
+        const size_t c = (size_t)level * nk + j;
+        ms[j]          = c < m.ctx.class_ms.size() ? m.ctx.class_ms[c] : 0.;
+        count[j]       = c < m.ctx.class_count.size() ? m.ctx.class_count[c] : 0;
+        if (reset && c < m.ctx.class_ms.size())
+          {
+            m.ctx.class_ms[c]    = 0;
+            m.ctx.class_count[c] = 0;
+          }
+      }
+    MGB_CATCH
+  }
+
+  int
+  mgb_timer_start(mgb_solver s)
+  {
+    MGB_TRY
+    Ctx &c = S(s).ctx;
+    for (int i = 0; i < 2; ++i)
+      if (!c.timer_ev[i])
+        MGB_CUDA_CHECK(cudaEventCreate(&c.timer_ev[i]));
+    MGB_CUDA_CHECK(cudaEventRecord(c.timer_ev[0], c.stream));
+    MGB_CATCH
+  }
+
+  int
+  mgb_timer_stop(mgb_solver s, double *ms)
+  {
+    MGB_TRY
+    Ctx &c = S(s).ctx;
+    if (!c.timer_ev[0])
+      throw std::runtime_error("mgb_timer_stop without mgb_timer_start");
+    MGB_CUDA_CHECK(cudaEventRecord(c.timer_ev[1], c.stream));
+    MGB_CUDA_CHECK(cudaEventSynchronize(c.timer_ev[1]));
+    float f = 0;
+    MGB_CUDA_CHECK(cudaEventElapsedTime(&f, c.timer_ev[0], c.timer_ev[1]));
+    *ms = f;
     MGB_CATCH
   }
 
@@ -1441,6 +1654,26 @@ extern "C"
   mgb_op_Tvmult(mgb_solver s, int level, int precision, void *dst, const void *src)
   {
     return mgb_op_vmult(s, level, precision, dst, src); // symmetric operator
+  }
+
+  int
+  mgb_op_vmult_host(mgb_solver s, int level, int precision, void *dst_host, const void *src_host)
+  {
+    MGB_TRY
+    MultigridSolver &m  = S(s);
+    level               = check_level(m, level);
+    const size_t N      = m.levels[level]->d.n_dofs;
+    const size_t bytes  = N * (precision == MGB_F64 ? sizeof(double) : sizeof(float));
+    void        *src    = precision == MGB_F64 ? (void *)m.solution[level]->p : (void *)m.defect[level]->p;
+    void        *dst    = precision == MGB_F64 ? (void *)m.residual[level]->p : (void *)m.t[level]->p;
+    MGB_CUDA_CHECK(cudaMemcpyAsync(src, src_host, bytes, cudaMemcpyHostToDevice, m.ctx.stream));
+    if (precision == MGB_F64)
+      m.matrix_dp[level]->vmult((double *)dst, (const double *)src);
+    else
+      m.matrix[level]->vmult((float *)dst, (const float *)src);
+    MGB_CUDA_CHECK(cudaMemcpyAsync(dst_host, dst, bytes, cudaMemcpyDeviceToHost, m.ctx.stream));
+    m.ctx.sync();
+    MGB_CATCH
   }
 
   int
