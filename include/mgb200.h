@@ -12,8 +12,8 @@
  *     transfers and level vectors (multigrid_solver.h:709-751).
  *   - "device pointer" = plain CUDA device address (e.g. torch.Tensor.data_ptr()).
  *     "host pointer"   = ordinary host memory; the call copies inside.
- *   - DoF vectors use the library's renumbered layout (patch interiors first, then
- *     patch faces/edges/vertices); mgb_solver_lex_map() gives the permutation to the
+ *   - DoF vectors use the library's renumbered layout (columns of 16 x 16-point tiles, z-plane
+ *     major inside a column); mgb_solver_lex_map() gives the permutation to the
  *     lexicographic (x fastest) numbering of the (N_d p + 1)^3 grid.
  *   - precision: MGB_F32 selects the V-cycle (float) level operator `matrix[level]`,
  *     MGB_F64 the outer operator `matrix_dp[level]` (multigrid_solver.h:740-745).
@@ -41,7 +41,7 @@ enum {
 
 /* kernel selection for the operator apply */
 enum {
-  MGB_KERNEL_AUTO = 0,     /* Cartesian sum-factorised patch kernel where admissible        */
+  MGB_KERNEL_AUTO = 0,     /* Cartesian streaming tile kernel where admissible              */
   MGB_KERNEL_GENERAL = 1   /* FEEvaluation-style evaluate / q-point op / integrate per cell */
 };
 
@@ -56,7 +56,7 @@ typedef struct mgb_options {
   int problem;             /* MGB_PROBLEM_*                                                                          */
   int kernel;              /* MGB_KERNEL_*                                                                           */
   int device;              /* CUDA device ordinal                                                                    */
-  int max_patch_cells;     /* cells per patch direction (0 = automatic: 4, 2 or 1)                                   */
+  int tile_cells;          /* cells per tile and direction (0 = automatic: about 16 points per tile direction)       */
 } mgb_options;
 
 const char *mgb_last_error(void);
@@ -71,7 +71,7 @@ int mgb_solver_sync(mgb_solver s);
 int mgb_solver_n_levels(mgb_solver s);
 int64_t mgb_solver_n_dofs(mgb_solver s, int level);        /* LaplaceOperator::m()  (MatrixFreeOperators::Base) */
 int mgb_solver_dof_grid(mgb_solver s, int level, int nd[3]);
-int mgb_solver_patch_cells(mgb_solver s, int level);
+int mgb_solver_tile_cells(mgb_solver s, int level);
 /* lex_to_dof[i] = library index of the DoF with lexicographic index i (host pointer, n_dofs entries) */
 int mgb_solver_lex_map(mgb_solver s, int level, uint32_t *lex_to_dof);
 
@@ -154,11 +154,10 @@ int64_t mgb_solver_launch_count(mgb_solver s);
  * laplace_operator.h:535): S,G,D,M1,K1 are (p+1)^2, P1 is (2p+1)(p+1), nodes/xq/wq are p+1 */
 int mgb_host_basis(int p, double *S, double *G, double *D, double *M1, double *K1, double *P1,
                    double *nodes, double *xq, double *wq);
-/* patch-entity numbering of one box level (extract_compressed_indices, laplace_operator.h:226-353);
- * lex_to_dof may be NULL */
-int mgb_host_numbering(int p, const int ncell[3], int max_patch_cells, int64_t *n_dofs,
-                       int64_t *n_interior, int *patch_cells, int64_t *n_constrained,
-                       uint32_t *lex_to_dof);
+/* tile-column numbering of one box level, all faces Dirichlet (the role of extract_compressed_indices,
+ * laplace_operator.h:226-353, which becomes a closed formula on box meshes); lex_to_dof may be NULL */
+int mgb_host_numbering(int p, const int ncell[3], int tile_cells, int64_t *n_dofs, int *tile_cells_used,
+                       int64_t *n_tiles, int64_t *n_constrained, uint32_t *lex_to_dof);
 
 #ifdef __cplusplus
 }

@@ -43,7 +43,7 @@ class Options(C.Structure):
         ("problem", C.c_int),
         ("kernel", C.c_int),
         ("device", C.c_int),
-        ("max_patch_cells", C.c_int),
+        ("tile_cells", C.c_int),
     ]
 
 
@@ -62,7 +62,7 @@ SYMBOLS = {
     "mgb_solver_n_levels": (_i, [_vp]),
     "mgb_solver_n_dofs": (C.c_int64, [_vp, _i]),
     "mgb_solver_dof_grid": (_i, [_vp, _i, _ip]),
-    "mgb_solver_patch_cells": (_i, [_vp, _i]),
+    "mgb_solver_tile_cells": (_i, [_vp, _i]),
     "mgb_solver_lex_map": (_i, [_vp, _i, C.POINTER(C.c_uint32)]),
     "mgb_solver_solve": (_i, [_vp, _i, _dp, _dp]),
     "mgb_solver_solve_cg": (_i, [_vp, C.POINTER(_u), _dp]),
@@ -101,7 +101,7 @@ SYMBOLS = {
     "mgb_solver_launch_count": (C.c_int64, [_vp]),
     # host-only helpers
     "mgb_host_basis": (_i, [_i] + [_dp] * 9),
-    "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), C.POINTER(C.c_int64), _ip,
+    "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), _ip, C.POINTER(C.c_int64),
                                 C.POINTER(C.c_int64), C.POINTER(C.c_uint32)]),
 }
 
@@ -144,18 +144,16 @@ def host_basis(p):
     return out
 
 
-def host_numbering(p, ncell, max_patch_cells=0, want_map=True):
+def host_numbering(p, ncell, tile_cells=0, want_map=True):
     nc = (C.c_int * 3)(*ncell)
-    nd, ni, ncon, M = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int()
-    _check(lib().mgb_host_numbering(p, nc, max_patch_cells, C.byref(nd), C.byref(ni), C.byref(M),
-                                    C.byref(ncon), None))
+    nd, nt, ncon, cw = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int()
     lex = None
+    _check(lib().mgb_host_numbering(p, nc, tile_cells, C.byref(nd), C.byref(cw), C.byref(nt), C.byref(ncon), None))
     if want_map:
         lex = np.zeros(nd.value, dtype=np.uint32)
-        _check(lib().mgb_host_numbering(p, nc, max_patch_cells, C.byref(nd), C.byref(ni), C.byref(M),
-                                        C.byref(ncon), lex.ctypes.data_as(C.POINTER(C.c_uint32))))
-    return dict(n_dofs=nd.value, n_interior=ni.value, patch_cells=M.value, n_constrained=ncon.value,
-                lex_to_dof=lex)
+        _check(lib().mgb_host_numbering(p, nc, tile_cells, C.byref(nd), C.byref(cw), C.byref(nt), C.byref(ncon),
+                                        lex.ctypes.data_as(C.POINTER(C.c_uint32))))
+    return dict(n_dofs=nd.value, tile_cells=cw.value, n_tiles=nt.value, n_constrained=ncon.value, lex_to_dof=lex)
 
 
 class LaplaceOperator:
@@ -230,7 +228,7 @@ class MultigridSolver:
 
     def __init__(self, degree, n_subdivisions, n_refinements, lower=(-0.9,) * 3, upper=(1.0,) * 3,
                  degree_pre=3, degree_post=3, n_cycles=2, problem=PROBLEM_CUBE_SINE,
-                 kernel=KERNEL_AUTO, device=0, max_patch_cells=0):
+                 kernel=KERNEL_AUTO, device=0, tile_cells=0):
         import torch
         if isinstance(n_subdivisions, int):
             n_subdivisions = (n_subdivisions,) * 3
@@ -242,7 +240,7 @@ class MultigridSolver:
         o.lower[:] = list(lower)
         o.upper[:] = list(upper)
         o.degree_pre, o.degree_post, o.n_cycles = degree_pre, degree_post, n_cycles
-        o.problem, o.kernel, o.device, o.max_patch_cells = problem, kernel, device, max_patch_cells
+        o.problem, o.kernel, o.device, o.tile_cells = problem, kernel, device, tile_cells
         self.h = C.c_void_p()
         self.device = torch.device("cuda", device)
         self.degree = degree
@@ -274,8 +272,8 @@ class MultigridSolver:
         _check(lib().mgb_solver_dof_grid(self.h, self._l(level), nd))
         return tuple(nd)
 
-    def patch_cells(self, level=-1):
-        return lib().mgb_solver_patch_cells(self.h, self._l(level))
+    def tile_cells(self, level=-1):
+        return lib().mgb_solver_tile_cells(self.h, self._l(level))
 
     def lex_map(self, level=-1):
         m = np.zeros(self.n_dofs(level), dtype=np.uint32)

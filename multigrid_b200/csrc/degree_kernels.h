@@ -26,7 +26,6 @@ namespace mgb
     T        *dst;
     const T  *rhs;      // APPLY_RESIDUAL / APPLY_CHEBYSHEV
     const T  *inv_diag; // APPLY_CHEBYSHEV
-    T        *boundary_tmp; // scratch of size n_dofs - n_interior for the patch-boundary DoFs
     const T  *coef_q;   // per-quadrature-point merged coefficient [cell][6][n^3] or nullptr
     T         coef[6];  // affine constant-coefficient merged tensor (without quadrature weight)
     T         f1, f2;

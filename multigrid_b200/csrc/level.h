@@ -1,16 +1,23 @@
 // Level description shared by host and device: the renumbered cell-to-DoF map.
 //
-// The reference stores, per cell, 3^dim "compressed" entity start indices (8 vertices,
-// 12 lines, 6 quads, 1 hex; DoFs inside an entity contiguous) -- common/laplace_operator.h:
-// 226-353, consumed by common/vector_access_reduced.h:11-251,255-505.  Here the same
-// 27-entry scheme is applied to a *patch* of M x M x M cells (M = 4, 2 or 1): a patch is
-// treated as one macro element with (M p - 1)^3 interior, 6 x (M p - 1)^2 face, 12 x (M p - 1)
-// edge and 8 vertex DoFs.  Numbering: all patch interiors first (contiguous per patch,
-// lexicographic), then patch faces, edges, vertices.  A thread block gathers a whole patch
-// with coalesced loads; DoFs interior to a patch are touched by exactly one block, so
-// fused vector updates on them need no second pass over HBM.  M = 1 is exactly the
-// reference layout.  Constrained (Dirichlet) entities are flagged per patch in a 27-bit
-// mask: read as 0, never written (vector_access_reduced.h:174-179,431-433).
+// The reference renumbers DoFs for matrix-free data locality
+// (DoFRenumbering::compute_matrix_free_data_locality, poisson_cube/program.cc:229-246) and stores,
+// per cell, 3^dim "compressed" entity start indices (common/laplace_operator.h:226-353, consumed by
+// common/vector_access_reduced.h:11-251,255-505).  On the uniformly refined box meshes of this path
+// the map is a closed formula, so no index table is stored or streamed at all:
+//
+//   the (nd0 x nd1 x nd2) grid of DoFs (nd = ncell * p + 1) is cut into columns of TW x TW points
+//   (TW = CW * p, CW cells per tile and direction); tile (tx,ty) owns the points
+//   [TW tx, TW tx + TW) x [TW ty, TW ty + TW) x [0, nd2) (the last tile in a direction is narrower,
+//   possibly one point wide).  Inside a tile column the numbering is z-plane major:
+//
+//       index = base(tx,ty) + gk * (wx wy) + ly * wx + lx ,   base = nd2 (ty TW nd0 + tx TW wy)
+//
+// so every z-plane of a full tile is one contiguous, 128-byte aligned chunk of TW^2 values.  A thread
+// block streams a tile column plane by plane with coalesced loads and owns the result at all of
+// its points (see cartesian_kernel.cuh): no scatter, no atomics.  Dirichlet DoFs are the points on the
+// flagged faces of the box: read as 0, never written by the cell loop
+// (vector_access_reduced.h:174-179,431-433).
 #pragma once
 #include <cstdint>
 
@@ -24,73 +31,90 @@ namespace mgb
 {
   struct LevelDesc
   {
-    int      p, n;       // degree, p+1
-    int      M;          // cells per patch and direction
-    int      np;         // points per patch and direction = M p + 1
-    int      q;          // interior points per patch and direction = M p - 1
-    int      npatch[3];  // patches per direction
-    int      ncell[3];   // cells per direction
-    int      nd[3];      // DoFs per direction
-    uint32_t n_patches, n_cells, n_dofs;
-    uint32_t n_interior; // DoFs interior to patches = n_patches q^3 (they come first)
+    int      p, n;      // degree, p+1
+    int      CW;        // cells per tile and direction (x and y)
+    int      TW;        // points per tile and direction = CW p
+    int      nt[2];     // tiles in x and y
+    int      ncell[3];  // cells per direction
+    int      nd[3];     // DoFs per direction
+    uint32_t n_cells, n_dofs;
+    uint32_t dirichlet; // bit 2d: low face of direction d is Dirichlet, bit 2d+1: high face
     double   lo[3], h[3];
-    const uint32_t *ent_base; // [n_patches][27] first DoF of every patch entity
-    const uint32_t *ent_mask; // [n_patches]     bit e set: entity e is Dirichlet-constrained
   };
 
-  // entity number (ex + 3 ey + 9 ez, e_d in {0 low, 1 interior, 2 high}) and offset inside
-  // the entity of patch point (I,J,K)
-  MGB_HD void
-  patch_point_entity(const int np, const int q, const int I, const int J, const int K, int &e, int &off)
+  MGB_HD int
+  imin(const int a, const int b)
   {
-    const int ex = I == 0 ? 0 : (I == np - 1 ? 2 : 1);
-    const int ey = J == 0 ? 0 : (J == np - 1 ? 2 : 1);
-    const int ez = K == 0 ? 0 : (K == np - 1 ? 2 : 1);
-    e            = ex + 3 * ey + 9 * ez;
-    const int sx = ex == 1 ? q : 1, sy = ey == 1 ? q : 1;
-    off          = (ex == 1 ? I - 1 : 0) + sx * ((ey == 1 ? J - 1 : 0) + sy * (ez == 1 ? K - 1 : 0));
+    return a < b ? a : b;
   }
 
+  // width of tile t in direction d (0 or 1)
+  MGB_HD int
+  tile_width(const LevelDesc &L, const int d, const int t)
+  {
+    return imin(L.TW, L.nd[d] - t * L.TW);
+  }
+
+  // first index of the column of tile (tx,ty)
   MGB_HD uint32_t
-  patch_dof(const LevelDesc &L, const uint32_t patch, const int I, const int J, const int K, bool &constrained)
+  tile_base(const LevelDesc &L, const int tx, const int ty)
   {
-    int e, off;
-    patch_point_entity(L.np, L.q, I, J, K, e, off);
-    constrained = (L.ent_mask[patch] >> e) & 1u;
-    return L.ent_base[patch * 27 + e] + (uint32_t)off;
+    const int wy = tile_width(L, 1, ty);
+    return (uint32_t)((uint64_t)L.nd[2] *
+                      ((uint64_t)ty * L.TW * L.nd[0] + (uint64_t)tx * L.TW * wy));
   }
 
-  // cells are numbered patch-major: cell = patch * M^3 + (lz M + ly) M + lx
+  // library index of the DoF at grid point (gi,gj,gk)
   MGB_HD uint32_t
-  cell_dof(const LevelDesc &L, const uint32_t cell, const int i, const int j, const int k, bool &constrained)
+  dof_index(const LevelDesc &L, const int gi, const int gj, const int gk)
   {
-    const int      M3    = L.M * L.M * L.M;
-    const uint32_t patch = cell / M3;
-    const int      lc    = cell - patch * M3;
-    const int      lx = lc % L.M, ly = (lc / L.M) % L.M, lz = lc / (L.M * L.M);
-    return patch_dof(L, patch, lx * L.p + i, ly * L.p + j, lz * L.p + k, constrained);
+    const int tx = gi / L.TW, ty = gj / L.TW;
+    const int lx = gi - tx * L.TW, ly = gj - ty * L.TW;
+    const int wx = tile_width(L, 0, tx), wy = tile_width(L, 1, ty);
+    return tile_base(L, tx, ty) + (uint32_t)gk * (uint32_t)(wx * wy) + (uint32_t)(ly * wx + lx);
   }
 
-  // global cell coordinates of a patch-major cell number
+  MGB_HD bool
+  is_constrained(const LevelDesc &L, const int gi, const int gj, const int gk)
+  {
+    const uint32_t m = L.dirichlet;
+    return (gi == 0 && (m & 1u)) || (gi == L.nd[0] - 1 && (m & 2u)) || (gj == 0 && (m & 4u)) ||
+           (gj == L.nd[1] - 1 && (m & 8u)) || (gk == 0 && (m & 16u)) || (gk == L.nd[2] - 1 && (m & 32u));
+  }
+
+  // constrained through a Dirichlet face in x or y (independent of the plane)
+  MGB_HD bool
+  is_constrained_xy(const LevelDesc &L, const int gi, const int gj)
+  {
+    const uint32_t m = L.dirichlet;
+    return (gi == 0 && (m & 1u)) || (gi == L.nd[0] - 1 && (m & 2u)) || (gj == 0 && (m & 4u)) ||
+           (gj == L.nd[1] - 1 && (m & 8u));
+  }
+
+  // cells are numbered lexicographically, x fastest
   MGB_HD void
   cell_coords(const LevelDesc &L, const uint32_t cell, int &cx, int &cy, int &cz)
   {
-    const int      M3    = L.M * L.M * L.M;
-    const uint32_t patch = cell / M3;
-    const int      lc    = cell - patch * M3;
-    const int      px = patch % L.npatch[0], py = (patch / L.npatch[0]) % L.npatch[1],
-              pz = patch / (L.npatch[0] * L.npatch[1]);
-    cx = px * L.M + lc % L.M;
-    cy = py * L.M + (lc / L.M) % L.M;
-    cz = pz * L.M + lc / (L.M * L.M);
+    cx               = cell % L.ncell[0];
+    const uint32_t r = cell / L.ncell[0];
+    cy               = r % L.ncell[1];
+    cz               = r / L.ncell[1];
   }
 
-  // patch-major cell number of global cell coordinates
   MGB_HD uint32_t
   cell_number(const LevelDesc &L, const int cx, const int cy, const int cz)
   {
-    const uint32_t patch =
-      ((uint32_t)(cz / L.M) * L.npatch[1] + (cy / L.M)) * L.npatch[0] + (cx / L.M);
-    return patch * (L.M * L.M * L.M) + ((cz % L.M) * L.M + (cy % L.M)) * L.M + (cx % L.M);
+    return ((uint32_t)cz * L.ncell[1] + cy) * L.ncell[0] + cx;
+  }
+
+  // DoF (i,j,k) of a cell, and whether it is Dirichlet-constrained
+  MGB_HD uint32_t
+  cell_dof(const LevelDesc &L, const uint32_t cell, const int i, const int j, const int k, bool &constrained)
+  {
+    int cx, cy, cz;
+    cell_coords(L, cell, cx, cy, cz);
+    const int gi = cx * L.p + i, gj = cy * L.p + j, gk = cz * L.p + k;
+    constrained  = is_constrained(L, gi, gj, gk);
+    return dof_index(L, gi, gj, gk);
   }
 } // namespace mgb

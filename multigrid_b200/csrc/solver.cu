@@ -341,30 +341,19 @@ namespace mgb
   struct Level
   {
     HostLevel      host;
-    LevelDesc      d; // with device pointers
+    LevelDesc      d;
     int            index = 0; // multigrid level number
-    DVec<uint32_t> ent_base, ent_mask, constrained;
-    DVec<uint8_t>  bflag;
+    DVec<uint32_t> constrained;
 
     void
     upload(cudaStream_t stream)
     {
-      ent_base.alloc(host.ent_base.size(), stream);
-      ent_mask.alloc(host.ent_mask.size(), stream);
       constrained.alloc(host.constrained.size(), stream);
-      bflag.alloc(host.bflag.size(), stream);
-      MGB_CUDA_CHECK(cudaMemcpyAsync(ent_base.p, host.ent_base.data(), ent_base.n * 4, cudaMemcpyHostToDevice, stream));
-      MGB_CUDA_CHECK(cudaMemcpyAsync(ent_mask.p, host.ent_mask.data(), ent_mask.n * 4, cudaMemcpyHostToDevice, stream));
       if (constrained.n)
         MGB_CUDA_CHECK(cudaMemcpyAsync(constrained.p, host.constrained.data(), constrained.n * 4, cudaMemcpyHostToDevice, stream));
-      if (bflag.n)
-        MGB_CUDA_CHECK(cudaMemcpyAsync(bflag.p, host.bflag.data(), bflag.n, cudaMemcpyHostToDevice, stream));
       MGB_CUDA_CHECK(cudaStreamSynchronize(stream));
-      d          = host.d;
-      d.ent_base = ent_base.p;
-      d.ent_mask = ent_mask.p;
+      d = host.d;
     }
-    size_t n_boundary() const { return d.n_dofs - d.n_interior; }
   };
 
   struct Nodes1D
@@ -372,23 +361,18 @@ namespace mgb
     double nodes[9], xq[9], w[9];
   };
 
-  // visits every (patch, patch point): f(dof, constrained, gi, gj, gk); points shared between patches
-  // are visited more than once (callers are idempotent)
+  // visits every grid point once: f(dof, constrained, gi, gj, gk)
   template <typename F>
   __global__ void
-  k_patch_points(const LevelDesc L, F f)
+  k_grid_points(const LevelDesc L, F f)
   {
-    const uint32_t patch = blockIdx.x;
-    const int      np3   = L.np * L.np * L.np;
-    const int      px = patch % L.npatch[0], py = (patch / L.npatch[0]) % L.npatch[1],
-              pz = patch / (L.npatch[0] * L.npatch[1]);
-    const int mp = L.M * L.p;
-    for (int l = threadIdx.x; l < np3; l += blockDim.x)
+    const size_t n = L.n_dofs;
+    for (size_t l = blockIdx.x * (size_t)blockDim.x + threadIdx.x; l < n; l += (size_t)gridDim.x * blockDim.x)
       {
-        const int I = l % L.np, J = (l / L.np) % L.np, K = l / (L.np * L.np);
-        bool      c;
-        const uint32_t d = patch_dof(L, patch, I, J, K, c);
-        f(d, c, px * mp + I, py * mp + J, pz * mp + K);
+        const int    gi = l % L.nd[0];
+        const size_t r  = l / L.nd[0];
+        const int    gj = r % L.nd[1], gk = r / L.nd[1];
+        f(dof_index(L, gi, gj, gk), is_constrained(L, gi, gj, gk), gi, gj, gk);
       }
   }
 
@@ -396,7 +380,7 @@ namespace mgb
   void
   patch_points(Ctx &ctx, const LevelDesc &L, F f)
   {
-    k_patch_points<<<L.n_patches, 256, 0, ctx.stream>>>(L, f);
+    k_grid_points<<<grid_for(L.n_dofs), 256, 0, ctx.stream>>>(L, f);
     ctx.check_launch();
   }
 
@@ -422,7 +406,6 @@ namespace mgb
     int                  kernel    = MGB_KERNEL_AUTO;
     DVec<T>              inverse_diagonal;
     DVec<T>              tmp;          // full-length scratch (general kernel epilogues)
-    DVec<T>              boundary_tmp; // patch-boundary accumulator; invariant: zero between calls
 
     size_t m() const { return level->d.n_dofs; }
 
@@ -432,7 +415,6 @@ namespace mgb
       ctx   = &c;
       level = &l;
       dk    = &degree_kernels(l.d.p);
-      boundary_tmp.alloc(l.n_boundary(), c.stream);
       evaluate_coefficient(basis, coefficient_fn);
     }
 
@@ -481,7 +463,8 @@ namespace mgb
 
     bool use_cartesian() const
     {
-      return cartesian && kernel == MGB_KERNEL_AUTO && (level->d.M * level->d.p + 1 <= 17);
+      // the streaming kernel is compiled for the default tile width of the degree
+      return cartesian && kernel == MGB_KERNEL_AUTO && level->d.CW == choose_tile_cells(level->d.p, 0);
     }
 
     void
@@ -492,7 +475,6 @@ namespace mgb
       A.dst             = dst;
       A.rhs             = nullptr;
       A.inv_diag        = nullptr;
-      A.boundary_tmp    = boundary_tmp.p;
       A.coef_q          = coef_q.p;
       for (int i = 0; i < 6; ++i)
         A.coef[i] = coef[i];
@@ -544,35 +526,14 @@ namespace mgb
       A.f2              = f2;
       A.first_chebyshev = first;
       A.read_plain      = read_plain;
-      const LevelDesc &L    = level->d;
-      const size_t     N    = L.n_dofs;
-      const uint8_t   *flag = level->bflag.p;
-
-      if (use_cartesian() && !read_plain)
+      if (use_cartesian())
         {
+          // streaming tile kernel: the vector operation is fused, every DoF is written once
           launch_cartesian(A);
-          if (mode == APPLY_ADD)
-            return;
-          // patch-boundary DoFs: finish with the accumulated sums; Dirichlet rows are identity
-          T             *bt   = boundary_tmp.p;
-          const uint32_t nint = L.n_interior;
-          ScopedRange    range(*ctx, level->index, RK_APPLY_EPILOGUE);
-          foreach (*ctx, N - nint, [=] __device__(size_t i) {
-            const size_t d = i + nint;
-            const T      y = flag[i] ? src[d] : bt[i];
-            bt[i]          = T(0);
-            if (mode == APPLY_SET)
-              dst[d] = y;
-            else if (mode == APPLY_RESIDUAL)
-              dst[d] = rhs[d] - y;
-            else
-              {
-                const T upd = f2 * inv_diag[d] * (rhs[d] - y);
-                dst[d] = first ? (T(1) + f1) * src[d] + upd : (T(1) + f1) * src[d] - f1 * dst[d] + upd;
-              }
-          });
           return;
         }
+      const LevelDesc &L = level->d;
+      const size_t     N = L.n_dofs;
 
       // general kernel: accumulate K src with red.global.add, then the vector operation
       if (mode == APPLY_ADD)
@@ -755,14 +716,13 @@ namespace mgb
         reduce<1>(
           c, N, [=] __device__(size_t i, double *acc) { acc[0] += (double)fp[i]; }, &sum);
       }
-      const T         mean  = (T)(sum / N);
-      const uint8_t  *flag  = op.level->bflag.p;
-      const uint32_t  nint  = L.n_interior;
+      const T mean = (T)(sum / N);
       // g = -(pattern - mean) with constrained entries zero
-      foreach (c, N, [=] __device__(size_t i) {
-        const bool con = i >= nint && flag[i - nint];
-        gp[i]          = con ? T(0) : -(gp[i] - mean);
-      });
+      foreach (c, N, [=] __device__(size_t i) { gp[i] = -(gp[i] - mean); });
+      {
+        const uint32_t *clist = op.level->constrained.p;
+        foreach (c, op.level->constrained.n, [=] __device__(size_t i) { gp[clist[i]] = T(0); });
+      }
       std::vector<double> diag, off;
       double              res = std::sqrt(dot(c, gp, gp, N));
       cg_iterations           = 0;
@@ -963,7 +923,7 @@ namespace mgb
           levels.emplace_back(new Level());
           Level &lv = *levels.back();
           lv.index  = l;
-          build_box_level(o.degree, nc, choose_patch_cells(o.degree, nc, o.max_patch_cells), o.lower, o.upper, lv.host);
+          build_box_level(o.degree, nc, choose_tile_cells(o.degree, o.tile_cells), o.lower, o.upper, 0x3fu, lv.host);
           lv.upload(ctx.stream);
           const size_t N = lv.d.n_dofs;
           matrix.emplace_back(new LaplaceOperator<float>());
@@ -1311,7 +1271,7 @@ extern "C"
     o->problem                     = MGB_PROBLEM_CUBE_SINE;
     o->kernel                      = MGB_KERNEL_AUTO;
     o->device                      = 0;
-    o->max_patch_cells             = 0;
+    o->tile_cells                  = 0;
   }
 
   int
@@ -1381,12 +1341,12 @@ extern "C"
   }
 
   int
-  mgb_solver_patch_cells(mgb_solver s, int level)
+  mgb_solver_tile_cells(mgb_solver s, int level)
   {
     try
       {
         MultigridSolver &m = S(s);
-        return m.levels[check_level(m, level)]->d.M;
+        return m.levels[check_level(m, level)]->d.CW;
       }
     catch (const std::exception &e)
       {
@@ -1888,21 +1848,21 @@ extern "C"
     MGB_CATCH
   }
 
-  // numbering of one box level: returns n_dofs / n_interior / M and fills lex_to_dof (n_dofs),
-  // ent_base (n_patches*27), ent_mask (n_patches) when non-NULL
+  // numbering of one box level with all faces Dirichlet: sizes, and lex_to_dof (n_dofs entries) when non-NULL
   int
-  mgb_host_numbering(int p, const int ncell[3], int max_patch_cells, int64_t *n_dofs, int64_t *n_interior,
-                     int *patch_cells, int64_t *n_constrained, uint32_t *lex_to_dof)
+  mgb_host_numbering(int p, const int ncell[3], int tile_cells, int64_t *n_dofs, int *tile_cells_used,
+                     int64_t *n_tiles, int64_t *n_constrained, uint32_t *lex_to_dof)
   {
     MGB_TRY
+    if (p < 1 || p > 8)
+      throw std::runtime_error("polynomial degree must be between 1 and 8");
     HostLevel    lvl;
     const double lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
-    const int    M     = choose_patch_cells(p, ncell, max_patch_cells);
-    build_box_level(p, ncell, M, lo, hi, lvl);
-    *n_dofs        = lvl.d.n_dofs;
-    *n_interior    = lvl.d.n_interior;
-    *patch_cells   = M;
-    *n_constrained = (int64_t)lvl.constrained.size();
+    build_box_level(p, ncell, choose_tile_cells(p, tile_cells), lo, hi, 0x3fu, lvl);
+    *n_dofs          = lvl.d.n_dofs;
+    *tile_cells_used = lvl.d.CW;
+    *n_tiles         = (int64_t)lvl.d.nt[0] * lvl.d.nt[1];
+    *n_constrained   = (int64_t)lvl.constrained.size();
     if (lex_to_dof)
       build_lex_map(lvl, lex_to_dof);
     MGB_CATCH

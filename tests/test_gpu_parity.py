@@ -35,7 +35,7 @@ class Pair:
         okw = dict(kw)
         self.g = mgb.MultigridSolver(p, nsub, nref, **kw)
         okw.pop("kernel", None)
-        okw.pop("max_patch_cells", None)
+        okw.pop("tile_cells", None)
         self.o = orc.MultigridSolver(p, nsub, nref, **okw)
         self.torch = torch
         self.maps = {}
@@ -55,7 +55,7 @@ class Pair:
         return t.double().cpu().numpy()[self.lex(level)]
 
 
-MESHES = [  # (p, nsub, nref, level, max_patch_cells)   -> covers M = 1, 2, 4 and ragged boxes
+MESHES = [  # (p, nsub, nref, level, tile_cells)   -> covers full, ragged and one-point-wide tiles
     (1, (1, 1, 1), 3, -1, 0), (2, (1, 2, 1), 2, -1, 0), (3, (1, 1, 1), 2, -1, 0), (4, (1, 1, 1), 2, -1, 0),
     (4, (3, 1, 2), 1, -1, 0), (4, (3, 1, 2), 0, -1, 0), (5, (1, 1, 1), 2, -1, 0), (6, (1, 1, 2), 1, -1, 0),
     (7, (1, 1, 1), 1, -1, 0), (8, (1, 1, 1), 1, -1, 0), (4, (1, 1, 1), 3, -1, 2), (2, (1, 1, 1), 3, -1, 0),
@@ -67,7 +67,7 @@ MESHES = [  # (p, nsub, nref, level, max_patch_cells)   -> covers M = 1, 2, 4 an
 @pytest.mark.parametrize("mesh", MESHES)
 def test_vmult_family(mgb, orc, torch, mesh, double, kernel):
     p, nsub, nref, level, maxm = mesh
-    P = Pair(mgb, orc, torch, p, nsub, nref, kernel=kernel, max_patch_cells=maxm)
+    P = Pair(mgb, orc, torch, p, nsub, nref, kernel=kernel, tile_cells=maxm)
     op = P.g.matrix_dp(level) if double else P.g.matrix(level)
     n = P.g.n_dofs(level)
     assert n == P.o.n_dofs(level)

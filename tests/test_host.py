@@ -50,31 +50,31 @@ def test_basis_matches_oracle(mgb, orc, p):
     assert np.allclose(a["K1"].sum(axis=0), 0, atol=1e-11)
 
 
-@pytest.mark.parametrize("p,ncell,maxm", [(1, (4, 4, 4), 0), (2, (4, 8, 4), 0), (4, (4, 4, 8), 0), (4, (2, 6, 2), 0),
-                                          (3, (3, 5, 7), 0), (4, (8, 8, 8), 2), (8, (2, 2, 4), 0), (5, (4, 4, 4), 0)])
-def test_numbering(mgb, p, ncell, maxm):
-    r = mgb.host_numbering(p, ncell, maxm)
+@pytest.mark.parametrize("p,ncell,cw", [(1, (4, 4, 4), 0), (2, (4, 8, 4), 0), (4, (4, 4, 8), 0), (4, (2, 6, 2), 0),
+                                        (3, (3, 5, 7), 0), (4, (8, 8, 8), 2), (8, (2, 2, 4), 0), (5, (4, 4, 4), 0),
+                                        (4, (9, 5, 1), 0), (1, (40, 17, 3), 0)])
+def test_numbering(mgb, p, ncell, cw):
+    """tile-column numbering of csrc/level.h: a permutation; every z-plane of a tile is one contiguous,
+    row-major chunk; tile columns follow each other; Dirichlet DoFs = the boundary points"""
+    r = mgb.host_numbering(p, ncell, cw)
     nd = [c * p + 1 for c in ncell]
     N = nd[0] * nd[1] * nd[2]
     assert r["n_dofs"] == N
     lex = r["lex_to_dof"].astype(np.int64)
     assert np.array_equal(np.sort(lex), np.arange(N))  # a permutation
-    M = r["patch_cells"]
-    assert all(c % M == 0 for c in ncell) and M * p + 1 <= 17
-    q = M * p - 1
-    n_patches = (ncell[0] // M) * (ncell[1] // M) * (ncell[2] // M)
-    assert r["n_interior"] == n_patches * q ** 3
-    # patch-interior DoFs come first and are contiguous per patch, lexicographic inside
+    CW = r["tile_cells"]
+    TW = CW * p
+    assert (cw == 0 and 12 <= TW <= 16) or CW == cw
+    ntx, nty = -(-nd[0] // TW), -(-nd[1] // TW)
+    assert r["n_tiles"] == ntx * nty
     grid = lex.reshape(nd[2], nd[1], nd[0])
-    if q > 0:
-        blk = grid[1:M * p, 1:M * p, 1:M * p].ravel()
-        assert np.array_equal(blk, np.arange(q ** 3))
-    interior = np.zeros((nd[2], nd[1], nd[0]), dtype=bool)
-    for k in range(nd[2]):
-        for j in range(nd[1]):
-            for i in range(nd[0]):
-                interior[k, j, i] = (i % (M * p) != 0) and (j % (M * p) != 0) and (k % (M * p) != 0)
-    assert (grid[interior] < r["n_interior"]).all() and (grid[~interior] >= r["n_interior"]).all()
+    base = 0
+    for ty in range(nty):
+        for tx in range(ntx):
+            wx, wy = min(TW, nd[0] - tx * TW), min(TW, nd[1] - ty * TW)
+            col = grid[:, ty * TW:ty * TW + wy, tx * TW:tx * TW + wx]
+            assert np.array_equal(col.ravel(), base + np.arange(nd[2] * wy * wx))
+            base += nd[2] * wy * wx
     n_boundary = N - (nd[0] - 2) * (nd[1] - 2) * (nd[2] - 2)
     assert r["n_constrained"] == n_boundary
 
