@@ -32,10 +32,13 @@ namespace mgb
     static constexpr int NI = TW + p + 1;                  // haloed points per direction: [-p, TW]
     static constexpr int NT = ((TW * TW + 31) / 32) * 32;  // threads per block
     static constexpr int NL = (NI * NI + NT - 1) / NT;     // source points per thread and plane
+    static constexpr int NXT = CW * NI * p;                // x-stage tasks per batch of p planes
+    static constexpr int NXR = (NXT + NT - 1) / NT;        // x-stage rounds
     // shared memory (elements): source planes | mx, kx | P, Q
     static constexpr int U_SIZE  = p * NI * NI;
     static constexpr int MX_SIZE = p * TW * NI;
-    static constexpr int PQ_SIZE = p * TW * TW;
+    static constexpr int PQP     = TW * TW + 16;           // plane pitch of P, Q (bank-conflict free)
+    static constexpr int PQ_SIZE = p * PQP;
     static constexpr int SMEM    = U_SIZE + 2 * MX_SIZE + 2 * PQ_SIZE;
   };
 
@@ -62,9 +65,76 @@ namespace mgb
     out[0] += wl * s;
   }
 
-  template <int p, typename T>
+
+  // stores `count` completed planes k0, k0+1, ... of one point column with the fused vector operation
+  // (the post-range operation of laplace_operator.h:607-741); all loads are issued before the stores
+  template <int p, typename T, int MODE>
+  __device__ __forceinline__ void
+  store_planes(const ApplyArgs<T> &A, const T (&y)[p + 1], const int k0, const int count,
+               const uint32_t own_off, const uint32_t own_stride, const bool xy_constrained)
+  {
+    const T *__restrict__ src = A.src;
+    const T *__restrict__ rhs = A.rhs;
+    const T *__restrict__ inv = A.inv_diag;
+    T *__restrict__ dst       = A.dst;
+    const int  nd2  = A.L.nd[2];
+    const bool z_lo = (A.L.dirichlet & 16u) != 0, z_hi = (A.L.dirichlet & 32u) != 0;
+    T          xs[p], rs[p], ds[p], os[p];
+    bool       con[p];
+#pragma unroll
+    for (int r = 0; r < p; ++r)
+      if (r < count)
+        {
+          const int      gk = k0 + r;
+          const uint32_t d  = own_off + (uint32_t)gk * own_stride;
+          con[r]            = xy_constrained || (gk == 0 && z_lo) || (gk == nd2 - 1 && z_hi);
+          if (MODE == APPLY_ADD)
+            os[r] = dst[d];
+          else
+            {
+              if (MODE == APPLY_CHEBYSHEV || con[r])
+                xs[r] = src[d];
+              if (MODE != APPLY_SET)
+                rs[r] = rhs[d];
+              if (MODE == APPLY_CHEBYSHEV)
+                {
+                  ds[r] = inv[d];
+                  if (!A.first_chebyshev)
+                    os[r] = dst[d];
+                }
+            }
+        }
+#pragma unroll
+    for (int r = 0; r < p; ++r)
+      if (r < count)
+        {
+          const uint32_t d = own_off + (uint32_t)(k0 + r) * own_stride;
+          T              v = y[r];
+          if (MODE == APPLY_ADD)
+            {
+              if (!con[r])
+                dst[d] = os[r] + v;
+              continue;
+            }
+          if (con[r])
+            v = xs[r]; // identity rows (laplace_operator.h:592-593, :632-633)
+          if (MODE == APPLY_SET)
+            dst[d] = v;
+          else if (MODE == APPLY_RESIDUAL)
+            dst[d] = rs[r] - v;
+          else
+            {
+              const T upd = A.f2 * ds[r] * (rs[r] - v);
+              dst[d]      = A.first_chebyshev ? (T(1) + A.f1) * xs[r] + upd :
+                                                (T(1) + A.f1) * xs[r] - A.f1 * os[r] + upd;
+            }
+        }
+  }
+
+  template <int p, typename T, int MODE>
   __global__ void
-  __launch_bounds__(TileCfg<p>::NT) k_apply_tile(const ApplyArgs<T> A, const int layers_per_segment)
+  __launch_bounds__(TileCfg<p>::NT, sizeof(T) == 8 ? 3 : 4)
+    k_apply_tile(const ApplyArgs<T> A, const int layers_per_segment)
   {
     using C           = TileCfg<p>;
     constexpr int n   = C::n;
@@ -73,24 +143,27 @@ namespace mgb
     constexpr int NI  = C::NI;
     constexpr int NT  = C::NT;
     constexpr int NL  = C::NL;
+    constexpr int NXR = C::NXR;
+    constexpr int PQP = C::PQP;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *u_s  = reinterpret_cast<T *>(smem_raw); // [plane][row J'+p][col I'+p]
     T *mx_s = u_s + C::U_SIZE;                 // [plane][I][row J'+p]
     T *kx_s = mx_s + C::MX_SIZE;
-    T *P_s  = kx_s + C::MX_SIZE;               // [plane][J][I]
+    T *P_s  = kx_s + C::MX_SIZE;               // [plane (pitch PQP)][J][I]
     T *Q_s  = P_s + C::PQ_SIZE;
 
-    const LevelDesc &L   = A.L;
-    const int        tid = threadIdx.x;
+    const LevelDesc &L      = A.L;
+    const int        tid    = threadIdx.x;
     const int        ntiles = L.nt[0] * L.nt[1];
     const int        tile = blockIdx.x % ntiles, seg = blockIdx.x / ntiles;
     const int        tx = tile % L.nt[0], ty = tile / L.nt[0];
     const int        gx0 = tx * TW, gy0 = ty * TW;
     const int        wx = tile_width(L, 0, tx), wy = tile_width(L, 1, ty);
-    const int        ncz = L.ncell[2];
+    const int        ncz = L.ncell[2], nd2 = L.nd[2];
     const int        c0 = seg * layers_per_segment;
     const int        c1 = imin(c0 + layers_per_segment, ncz);
     const bool       plain = A.read_plain != 0;
+    const T *__restrict__ src = A.src;
 
     // ---- per-thread source points (fixed over the planes)
     uint32_t src_off[NL];
@@ -109,20 +182,52 @@ namespace mgb
         src_stride[l] = 0;
         if (ok)
           {
-            const int txs = gi / TW, tys = gj / TW;
             src_off[l]    = dof_index(L, gi, gj, 0);
-            src_stride[l] = tile_width(L, 0, txs) * tile_width(L, 1, tys);
+            src_stride[l] = tile_width(L, 0, gi / TW) * tile_width(L, 1, gj / TW);
           }
       }
-    const bool z_lo_dirichlet = (L.dirichlet & 16u) != 0, z_hi_dirichlet = (L.dirichlet & 32u) != 0;
+    // planes that read as zero: outside the grid, or on a Dirichlet z-face
+    const int k_lo = (!plain && (L.dirichlet & 16u)) ? 1 : 0;
+    const int k_hi = (!plain && (L.dirichlet & 32u)) ? nd2 - 2 : nd2 - 1;
+
+    // ---- x-stage tasks of this thread: (cell column, row, plane) -> p output rows
+    int  x_in[NXR], x_out[NXR];
+    int  x_flags = 0; // bit 2r: previous cell exists, bit 2r+1: own cell exists, round r
+#pragma unroll
+    for (int r = 0; r < NXR; ++r)
+      {
+        const int t  = tid + r * NT;
+        const int rp = t % (NI * p), cxl = t / (NI * p);
+        const int b = rp / NI, row = rp - b * NI;
+        const int gc = tx * CW + cxl;
+        x_in[r]      = t < C::NXT ? rp * NI + cxl * p : -1;
+        x_out[r]     = (b * TW + cxl * p) * NI + row;
+        if (gc - 1 >= 0 && gc - 1 < L.ncell[0])
+          x_flags |= 1 << (2 * r);
+        if (gc < L.ncell[0])
+          x_flags |= 2 << (2 * r);
+      }
+    // ---- y-stage task of this thread: (I, plane, cell row) -> p output rows
+    int y_in, y_out, y_flags = 0;
+    {
+      const int Il = tid % TW, rest = tid / TW;
+      const int b = rest % p, cyl = rest / p;
+      const int gc = ty * CW + cyl;
+      y_in         = tid < TW * TW ? (b * TW + Il) * NI + cyl * p : -1;
+      y_out        = b * PQP + cyl * p * TW + Il;
+      if (gc - 1 >= 0 && gc - 1 < L.ncell[1])
+        y_flags |= 1;
+      if (gc < L.ncell[1])
+        y_flags |= 2;
+    }
 
     // ---- owned point of this thread
     const int  I = tid % TW, J = tid / TW;
     const bool owner = tid < TW * TW && I < wx && J < wy;
-    const int  gi = gx0 + I, gj = gy0 + J;
-    const bool xy_constrained = owner && is_constrained_xy(L, gi, gj);
+    const bool xy_constrained = owner && is_constrained_xy(L, gx0 + I, gy0 + J);
     const uint32_t own_off    = tile_base(L, tx, ty) + (uint32_t)(J * wx + I);
-    const int      own_stride = wx * wy;
+    const uint32_t own_stride = (uint32_t)(wx * wy);
+    const int      pq_off     = J * TW + I;
 
     const T *M1 = Tab<T>::M1();
     const T *K1 = Tab<T>::K1();
@@ -130,171 +235,158 @@ namespace mgb
 
     T Pz[n], Qz[n]; // P, Q of this thread's column on the planes of the current cell layer
     T carry = 0;
+    T pre[NL][p];   // source values of the next batch of planes (in flight during the stages)
 
-    // two-dimensional stages for `np` planes starting at plane k_first; results land in P_s / Q_s
-    auto planes_2d = [&](const int k_first, const int np) {
-      // (a) source planes -> shared memory (constrained and outside points read as zero)
-      for (int b = 0; b < np; ++b)
+    auto issue_loads = [&](const int c) {
+#pragma unroll
+      for (int b = 0; b < p; ++b)
         {
-          const int  gk     = k_first + b;
-          const bool z_zero = !plain && ((gk == 0 && z_lo_dirichlet) || (gk == L.nd[2] - 1 && z_hi_dirichlet));
+          const int  gk  = c * p + 1 + b;
+          const bool okz = gk >= k_lo && gk <= k_hi;
 #pragma unroll
           for (int l = 0; l < NL; ++l)
-            {
-              const int q = tid + l * NT;
-              if (q < NI * NI)
-                u_s[b * NI * NI + q] =
-                  (src_ok[l] && !z_zero) ? A.src[src_off[l] + (uint32_t)gk * (uint32_t)src_stride[l]] : T(0);
-            }
-        }
-      __syncthreads();
-      // (b) x-stage: task = (cell column cxl, row, plane)
-      for (int t = tid; t < CW * NI * np; t += NT)
-        {
-          const int rp = t % (NI * np), cxl = t / (NI * np);
-          const int b = rp / NI, row = rp - b * NI;
-          const int gc = tx * CW + cxl; // global cell of the output rows
-          const T   wl = gc - 1 >= 0 && gc - 1 < L.ncell[0] ? T(1) : T(0);
-          const T   wr = gc < L.ncell[0] ? T(1) : T(0);
-          T         x[2 * p + 1], om[p], ok[p];
-          const T  *up = u_s + b * NI * NI + row * NI + cxl * p;
-#pragma unroll
-          for (int i = 0; i < 2 * p + 1; ++i)
-            x[i] = up[i];
-          row_product<p, T>(M1, x, wl, wr, om);
-          row_product<p, T>(K1, x, wl, wr, ok);
-#pragma unroll
-          for (int r = 0; r < p; ++r)
-            {
-              mx_s[(b * TW + cxl * p + r) * NI + row] = om[r];
-              kx_s[(b * TW + cxl * p + r) * NI + row] = ok[r];
-            }
-        }
-      __syncthreads();
-      // (c) y-stage: task = (I, cell row cyl, plane)
-      for (int t = tid; t < TW * CW * np; t += NT)
-        {
-          const int Il = t % TW, rest = t / TW;
-          const int cyl = rest % CW, b = rest / CW;
-          const int gc  = ty * CW + cyl;
-          const T   wl = gc - 1 >= 0 && gc - 1 < L.ncell[1] ? T(1) : T(0);
-          const T   wr = gc < L.ncell[1] ? T(1) : T(0);
-          T         xm[2 * p + 1], xk[2 * p + 1], oP[p], oQ[p], oR[p];
-          const T  *mp = mx_s + (b * TW + Il) * NI + cyl * p;
-          const T  *kp = kx_s + (b * TW + Il) * NI + cyl * p;
-#pragma unroll
-          for (int i = 0; i < 2 * p + 1; ++i)
-            {
-              xm[i] = mp[i];
-              xk[i] = kp[i];
-            }
-          row_product<p, T>(M1, xm, wl, wr, oP);
-          row_product<p, T>(M1, xk, wl, wr, oQ);
-          row_product<p, T>(K1, xm, wl, wr, oR);
-#pragma unroll
-          for (int r = 0; r < p; ++r)
-            {
-              P_s[(b * TW + cyl * p + r) * TW + Il] = oP[r];
-              Q_s[(b * TW + cyl * p + r) * TW + Il] = cx * oQ[r] + cy * oR[r];
-            }
-        }
-      __syncthreads();
-    };
-
-    // ---- stores one completed plane with the fused vector operation
-    auto store_plane = [&](const int gk, T y) {
-      if (!owner)
-        return;
-      const uint32_t d = own_off + (uint32_t)gk * (uint32_t)own_stride;
-      const bool constrained =
-        xy_constrained || (gk == 0 && z_lo_dirichlet) || (gk == L.nd[2] - 1 && z_hi_dirichlet);
-      if (A.mode == APPLY_ADD)
-        {
-          if (!constrained)
-            A.dst[d] += y;
-          return;
-        }
-      if (constrained)
-        y = A.src[d]; // identity rows (laplace_operator.h:592-593, :632-633)
-      if (A.mode == APPLY_SET)
-        A.dst[d] = y;
-      else if (A.mode == APPLY_RESIDUAL)
-        A.dst[d] = A.rhs[d] - y;
-      else
-        {
-          const T xk  = A.src[d];
-          const T upd = A.f2 * A.inv_diag[d] * (A.rhs[d] - y);
-          if (A.first_chebyshev)
-            A.dst[d] = (T(1) + A.f1) * xk + upd;
-          else
-            A.dst[d] = (T(1) + A.f1) * xk - A.f1 * A.dst[d] + upd;
+            pre[l][b] = (src_ok[l] && okz) ? __ldg(src + src_off[l] + (uint32_t)gk * (uint32_t)src_stride[l]) : T(0);
         }
     };
 
-    // ---- march through the cell layers; layer c_begin < c0 only produces the carry
+    // ---- march through the cell layers.  Batch c = planes c p + 1 .. c p + p.  The first batch only
+    //      provides the lowest plane of the first layer; layer c_begin < c0 only produces the carry.
     const int c_begin = c0 > 0 ? c0 - 1 : 0;
-    planes_2d(c_begin * p, 1);
-    Pz[0] = owner ? P_s[J * TW + I] : T(0);
-    Qz[0] = owner ? Q_s[J * TW + I] : T(0);
-    for (int c = c_begin; c < c1; ++c)
+    issue_loads(c_begin - 1);
+    for (int c = c_begin - 1; c < c1; ++c)
       {
-        planes_2d(c * p + 1, p);
+        // (a) source planes -> shared memory
+#pragma unroll
+        for (int b = 0; b < p; ++b)
+#pragma unroll
+          for (int l = 0; l < NL; ++l)
+            if (tid + l * NT < NI * NI)
+              u_s[b * NI * NI + tid + l * NT] = pre[l][b];
+        __syncthreads();
+        if (c + 1 < c1)
+          issue_loads(c + 1);
+
+        // (b) x-stage: mx = Mx u, kx = Kx u
+#pragma unroll
+        for (int r = 0; r < NXR; ++r)
+          if (x_in[r] >= 0)
+            {
+              const T wl = (x_flags >> (2 * r)) & 1 ? T(1) : T(0);
+              const T wr = (x_flags >> (2 * r)) & 2 ? T(1) : T(0);
+              T       x[2 * p + 1], om[p], ok[p];
+#pragma unroll
+              for (int i = 0; i < 2 * p + 1; ++i)
+                x[i] = u_s[x_in[r] + i];
+              row_product<p, T>(M1, x, wl, wr, om);
+              row_product<p, T>(K1, x, wl, wr, ok);
+#pragma unroll
+              for (int i = 0; i < p; ++i)
+                {
+                  mx_s[x_out[r] + i * NI] = om[i];
+                  kx_s[x_out[r] + i * NI] = ok[i];
+                }
+            }
+        __syncthreads();
+
+        // (c) y-stage: P = My mx, Q = c0 My kx + c1 Ky mx
+        if (y_in >= 0)
+          {
+            const T wl = y_flags & 1 ? T(1) : T(0);
+            const T wr = y_flags & 2 ? T(1) : T(0);
+            T       xm[2 * p + 1], oP[p], oQ[p], oR[p];
+#pragma unroll
+            for (int i = 0; i < 2 * p + 1; ++i)
+              xm[i] = mx_s[y_in + i];
+            row_product<p, T>(M1, xm, wl, wr, oP);
+            row_product<p, T>(K1, xm, wl, wr, oR);
+#pragma unroll
+            for (int i = 0; i < p; ++i)
+              P_s[y_out + i * TW] = oP[i];
+#pragma unroll
+            for (int i = 0; i < 2 * p + 1; ++i)
+              xm[i] = kx_s[y_in + i];
+            row_product<p, T>(M1, xm, wl, wr, oQ);
+#pragma unroll
+            for (int i = 0; i < p; ++i)
+              Q_s[y_out + i * TW] = cx * oQ[i] + cy * oR[i];
+          }
+        __syncthreads();
+
+        // (d) z-stage: y = Mz Q + c2 Kz P on the cell layer c, fused vector operation
+        if (!owner)
+          continue;
 #pragma unroll
         for (int b = 0; b < p; ++b)
           {
-            Pz[b + 1] = owner ? P_s[(b * TW + J) * TW + I] : T(0);
-            Qz[b + 1] = owner ? Q_s[(b * TW + J) * TW + I] : T(0);
+            Pz[b + 1] = P_s[b * PQP + pq_off];
+            Qz[b + 1] = Q_s[b * PQP + pq_off];
           }
-        T y[n];
-#pragma unroll
-        for (int r = 0; r < n; ++r)
+        if (c >= c_begin)
           {
-            T s = 0, k = 0;
+            T y[n];
 #pragma unroll
-            for (int i = 0; i < n; ++i)
+            for (int r = 0; r < n; ++r)
               {
-                s += M1[r * n + i] * Qz[i];
-                k += K1[r * n + i] * Pz[i];
-              }
-            y[r] = s + cz * k;
-          }
-        y[0] += carry;
-        carry = y[p];
-        if (c >= c0)
-          {
+                T s = 0, k = 0;
 #pragma unroll
-            for (int r = 0; r < p; ++r)
-              store_plane(c * p + r, y[r]);
+                for (int i = 0; i < n; ++i)
+                  {
+                    s += M1[r * n + i] * Qz[i];
+                    k += K1[r * n + i] * Pz[i];
+                  }
+                y[r] = s + cz * k;
+              }
+            y[0] += carry;
+            carry = y[p];
+            if (c >= c0)
+              store_planes<p, T, MODE>(A, y, c * p, p, own_off, own_stride, xy_constrained);
           }
         Pz[0] = Pz[p];
         Qz[0] = Qz[p];
       }
-    if (c1 == ncz)
-      store_plane(ncz * p, carry);
+    if (c1 == ncz && owner)
+      {
+        T y[n];
+        y[0] = carry;
+        store_planes<p, T, MODE>(A, y, ncz * p, 1, own_off, own_stride, xy_constrained);
+      }
   }
 
-  template <int p, typename T>
+  template <int p, typename T, int MODE>
   void
-  launch_apply_cartesian(const ApplyArgs<T> &A, cudaStream_t stream)
+  launch_apply_tile(const ApplyArgs<T> &A, cudaStream_t stream)
   {
     using C           = TileCfg<p>;
     const size_t smem = (size_t)C::SMEM * sizeof(T);
     static bool  first = true;
     if (first)
       {
-        cudaFuncSetAttribute(k_apply_tile<p, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(k_apply_tile<p, T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         first = false;
       }
     const int ntiles = A.L.nt[0] * A.L.nt[1];
     const int ncz    = A.L.ncell[2];
     // enough blocks for several waves on 148 SMs, but at least 4 cell layers per segment
-    int nseg = (148 * 6 + ntiles - 1) / ntiles;
+    int nseg = (148 * 8 + ntiles - 1) / ntiles;
     if (nseg > ncz / 4)
       nseg = ncz / 4;
     if (nseg < 1)
       nseg = 1;
     const int lps = (ncz + nseg - 1) / nseg;
     nseg          = (ncz + lps - 1) / lps;
-    k_apply_tile<p, T><<<ntiles * nseg, C::NT, smem, stream>>>(A, lps);
+    k_apply_tile<p, T, MODE><<<ntiles * nseg, C::NT, smem, stream>>>(A, lps);
+  }
+
+  template <int p, typename T>
+  void
+  launch_apply_cartesian(const ApplyArgs<T> &A, cudaStream_t stream)
+  {
+    switch (A.mode)
+      {
+        case APPLY_ADD: launch_apply_tile<p, T, APPLY_ADD>(A, stream); break;
+        case APPLY_SET: launch_apply_tile<p, T, APPLY_SET>(A, stream); break;
+        case APPLY_RESIDUAL: launch_apply_tile<p, T, APPLY_RESIDUAL>(A, stream); break;
+        default: launch_apply_tile<p, T, APPLY_CHEBYSHEV>(A, stream); break;
+      }
   }
 } // namespace mgb
