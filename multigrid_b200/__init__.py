@@ -19,7 +19,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmgb200.so")
+LIB_PATH = os.environ.get("MGB200_LIB", os.path.join(_HERE, "libmgb200.so"))  # override: kernel experiments
 
 F32, F64 = 0, 1
 PROBLEM_CUBE_SINE, PROBLEM_SHELL_COEF = 0, 1

@@ -21,6 +21,13 @@
 #pragma once
 #include "degree_kernels.cuh"
 
+#ifndef MGB_MINB64
+#define MGB_MINB64 2
+#endif
+#ifndef MGB_MINB32
+#define MGB_MINB32 4
+#endif
+
 namespace mgb
 {
   template <int p>
@@ -39,32 +46,44 @@ namespace mgb
     static constexpr int MX_SIZE = p * TW * NI;
     static constexpr int PQP     = TW * TW + 16;           // plane pitch of P, Q (bank-conflict free)
     static constexpr int PQ_SIZE = p * PQP;
-    static constexpr int SMEM    = U_SIZE + 2 * MX_SIZE + 2 * PQ_SIZE;
+    static constexpr int SMEM    = 2 * U_SIZE + 2 * MX_SIZE + 2 * PQ_SIZE; // source planes double-buffered
   };
 
   // p output rows of cell-row products: out[r] = sum_i A[r][i] x[p+i] (own cell, if it exists)
   //                                     out[0] += sum_i A[p][i] x[i]   (previous cell, if it exists)
+  // Points outside the grid are read as zero, so a missing cell only has to be masked at the shared
+  // point x[p]: xl = x[p] if the previous cell exists else 0, xr likewise for the own cell.  (Rows
+  // r > 0 of a missing own cell belong to points outside the grid and are never stored.)
   template <int p, typename T>
   __device__ __forceinline__ void
-  row_product(const T *__restrict__ Ac, const T (&x)[2 * p + 1], const T wl, const T wr, T (&out)[p])
+  row_product(const T *__restrict__ Ac, const T (&x)[2 * p + 1], const T xl, const T xr, T (&out)[p])
   {
     constexpr int n = p + 1;
 #pragma unroll
     for (int r = 0; r < p; ++r)
       {
-        T s = 0;
+        T s = Ac[r * n] * xr;
 #pragma unroll
-        for (int i = 0; i < n; ++i)
+        for (int i = 1; i < n; ++i)
           s += Ac[r * n + i] * x[p + i];
-        out[r] = wr * s;
+        out[r] = s;
       }
-    T s = 0;
+    T s = Ac[p * n + p] * xl;
 #pragma unroll
-    for (int i = 0; i < n; ++i)
+    for (int i = 0; i < p; ++i)
       s += Ac[p * n + i] * x[i];
-    out[0] += wl * s;
+    out[0] += s;
   }
 
+  // asynchronous copy of one value global -> shared (LDGSTS); `valid == false` writes zero
+  template <typename T>
+  __device__ __forceinline__ void
+  cp_async_value(T *smem_dst, const T *gmem_src, const bool valid)
+  {
+    const uint32_t d  = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    const int      sz = valid ? (int)sizeof(T) : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;\n" ::"r"(d), "l"(gmem_src), "n"(sizeof(T)), "r"(sz));
+  }
 
   // stores `count` completed planes k0, k0+1, ... of one point column with the fused vector operation
   // (the post-range operation of laplace_operator.h:607-741); all loads are issued before the stores
@@ -133,7 +152,7 @@ namespace mgb
 
   template <int p, typename T, int MODE>
   __global__ void
-  __launch_bounds__(TileCfg<p>::NT, sizeof(T) == 8 ? 3 : 4)
+  __launch_bounds__(TileCfg<p>::NT, sizeof(T) == 8 ? MGB_MINB64 : MGB_MINB32)
     k_apply_tile(const ApplyArgs<T> A, const int layers_per_segment)
   {
     using C           = TileCfg<p>;
@@ -146,8 +165,8 @@ namespace mgb
     constexpr int NXR = C::NXR;
     constexpr int PQP = C::PQP;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    T *u_s  = reinterpret_cast<T *>(smem_raw); // [plane][row J'+p][col I'+p]
-    T *mx_s = u_s + C::U_SIZE;                 // [plane][I][row J'+p]
+    T *u_s  = reinterpret_cast<T *>(smem_raw); // [buffer][plane][row J'+p][col I'+p]
+    T *mx_s = u_s + 2 * C::U_SIZE;                 // [plane][I][row J'+p]
     T *kx_s = mx_s + C::MX_SIZE;
     T *P_s  = kx_s + C::MX_SIZE;               // [plane (pitch PQP)][J][I]
     T *Q_s  = P_s + C::PQ_SIZE;
@@ -235,9 +254,9 @@ namespace mgb
 
     T Pz[n], Qz[n]; // P, Q of this thread's column on the planes of the current cell layer
     T carry = 0;
-    T pre[NL][p];   // source values of the next batch of planes (in flight during the stages)
 
-    auto issue_loads = [&](const int c) {
+    // source planes of batch c -> shared-memory buffer `buf`, asynchronously
+    auto issue_loads = [&](const int c, const int buf) {
 #pragma unroll
       for (int b = 0; b < p; ++b)
         {
@@ -245,38 +264,41 @@ namespace mgb
           const bool okz = gk >= k_lo && gk <= k_hi;
 #pragma unroll
           for (int l = 0; l < NL; ++l)
-            pre[l][b] = (src_ok[l] && okz) ? __ldg(src + src_off[l] + (uint32_t)gk * (uint32_t)src_stride[l]) : T(0);
+            if (tid + l * NT < NI * NI)
+              {
+                const bool ok = src_ok[l] && okz;
+                cp_async_value(u_s + (buf * p + b) * NI * NI + tid + l * NT,
+                               ok ? src + src_off[l] + (uint32_t)gk * (uint32_t)src_stride[l] : src, ok);
+              }
         }
+      asm volatile("cp.async.commit_group;\n" ::);
     };
 
     // ---- march through the cell layers.  Batch c = planes c p + 1 .. c p + p.  The first batch only
     //      provides the lowest plane of the first layer; layer c_begin < c0 only produces the carry.
     const int c_begin = c0 > 0 ? c0 - 1 : 0;
-    issue_loads(c_begin - 1);
+    issue_loads(c_begin - 1, 0);
     for (int c = c_begin - 1; c < c1; ++c)
       {
-        // (a) source planes -> shared memory
-#pragma unroll
-        for (int b = 0; b < p; ++b)
-#pragma unroll
-          for (int l = 0; l < NL; ++l)
-            if (tid + l * NT < NI * NI)
-              u_s[b * NI * NI + tid + l * NT] = pre[l][b];
+        // (a) the planes of this batch have landed; prefetch the next batch into the other buffer
+        const int cur = (c - c_begin + 1) & 1;
+        asm volatile("cp.async.wait_group 0;\n" ::);
         __syncthreads();
         if (c + 1 < c1)
-          issue_loads(c + 1);
+          issue_loads(c + 1, cur ^ 1);
+        const T *u_c = u_s + cur * C::U_SIZE;
 
         // (b) x-stage: mx = Mx u, kx = Kx u
 #pragma unroll
         for (int r = 0; r < NXR; ++r)
           if (x_in[r] >= 0)
             {
-              const T wl = (x_flags >> (2 * r)) & 1 ? T(1) : T(0);
-              const T wr = (x_flags >> (2 * r)) & 2 ? T(1) : T(0);
-              T       x[2 * p + 1], om[p], ok[p];
+              T x[2 * p + 1], om[p], ok[p];
 #pragma unroll
               for (int i = 0; i < 2 * p + 1; ++i)
-                x[i] = u_s[x_in[r] + i];
+                x[i] = u_c[x_in[r] + i];
+              const T wl = (x_flags >> (2 * r)) & 1 ? x[p] : T(0);
+              const T wr = (x_flags >> (2 * r)) & 2 ? x[p] : T(0);
               row_product<p, T>(M1, x, wl, wr, om);
               row_product<p, T>(K1, x, wl, wr, ok);
 #pragma unroll
@@ -291,12 +313,12 @@ namespace mgb
         // (c) y-stage: P = My mx, Q = c0 My kx + c1 Ky mx
         if (y_in >= 0)
           {
-            const T wl = y_flags & 1 ? T(1) : T(0);
-            const T wr = y_flags & 2 ? T(1) : T(0);
-            T       xm[2 * p + 1], oP[p], oQ[p], oR[p];
+            T xm[2 * p + 1], oP[p], oQ[p], oR[p];
 #pragma unroll
             for (int i = 0; i < 2 * p + 1; ++i)
               xm[i] = mx_s[y_in + i];
+            T wl = y_flags & 1 ? xm[p] : T(0);
+            T wr = y_flags & 2 ? xm[p] : T(0);
             row_product<p, T>(M1, xm, wl, wr, oP);
             row_product<p, T>(K1, xm, wl, wr, oR);
 #pragma unroll
@@ -305,6 +327,8 @@ namespace mgb
 #pragma unroll
             for (int i = 0; i < 2 * p + 1; ++i)
               xm[i] = kx_s[y_in + i];
+            wl = y_flags & 1 ? xm[p] : T(0);
+            wr = y_flags & 2 ? xm[p] : T(0);
             row_product<p, T>(M1, xm, wl, wr, oQ);
 #pragma unroll
             for (int i = 0; i < p; ++i)

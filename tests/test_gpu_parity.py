@@ -168,7 +168,11 @@ def test_smoother(mgb, orc, torch, mesh):
     rng = np.random.default_rng(3)
     for level in range(P.g.n_levels):
         gi, oi = P.g.smoother_info(level), P.o.chebyshev_info(level)
-        assert gi["degree"] == oi["degree"] and gi["cg_iterations"] == oi["cg_iterations"], (gi, oi)
+        assert gi["degree"] == oi["degree"], (gi, oi)
+        # the eigenvalue CG runs its full 15 iterations on real levels; on the tiny ones it stops when the
+        # float residual underflows 1e-10, which may happen one iteration earlier or later
+        its_full = oi["cg_iterations"] == 15 or level == 0
+        assert abs(gi["cg_iterations"] - oi["cg_iterations"]) <= (0 if its_full else 1), (gi, oi)
         assert abs(gi["max_eig"] - oi["max_eig"]) <= 2e-4 * oi["max_eig"], (gi, oi)
         assert abs(gi["theta"] - oi["theta"]) <= 2e-4 * oi["theta"]
         n = P.g.n_dofs(level)
