@@ -54,24 +54,52 @@ namespace mgb
   // Points outside the grid are read as zero, so a missing cell only has to be masked at the shared
   // point x[p]: xl = x[p] if the previous cell exists else 0, xr likewise for the own cell.  (Rows
   // r > 0 of a missing own cell belong to points outside the grid and are never stored.)
+  // M1 and K1 are symmetric and persymmetric (A[r][i] = A[i][r] = A[p-r][p-i]); addressing every
+  // entry through one canonical representative leaves (p+1)(p+3)/4-ish distinct constants per matrix,
+  // few enough to live in uniform registers (the 2 (p+1)^2 separate entries are not)
+  template <int p>
+  __host__ __device__ constexpr int
+  canon(const int r, const int i)
+  {
+    int a = r, b = i;
+    if (b < a)
+      {
+        const int t = a;
+        a           = b;
+        b           = t;
+      }
+    int c = p - i, d = p - r; // (p-r, p-i) transposed so that c <= d is tested below
+    if (d < c)
+      {
+        const int t = c;
+        c           = d;
+        d           = t;
+      }
+    if (c < a || (c == a && d < b))
+      {
+        a = c;
+        b = d;
+      }
+    return a * (p + 1) + b;
+  }
+
   template <int p, typename T>
   __device__ __forceinline__ void
   row_product(const T *__restrict__ Ac, const T (&x)[2 * p + 1], const T xl, const T xr, T (&out)[p])
   {
-    constexpr int n = p + 1;
 #pragma unroll
     for (int r = 0; r < p; ++r)
       {
-        T s = Ac[r * n] * xr;
+        T s = Ac[canon<p>(r, 0)] * xr;
 #pragma unroll
-        for (int i = 1; i < n; ++i)
-          s += Ac[r * n + i] * x[p + i];
+        for (int i = 1; i <= p; ++i)
+          s += Ac[canon<p>(r, i)] * x[p + i];
         out[r] = s;
       }
-    T s = Ac[p * n + p] * xl;
+    T s = Ac[canon<p>(p, p)] * xl;
 #pragma unroll
     for (int i = 0; i < p; ++i)
-      s += Ac[p * n + i] * x[i];
+      s += Ac[canon<p>(p, i)] * x[i];
     out[0] += s;
   }
 
@@ -355,8 +383,8 @@ namespace mgb
 #pragma unroll
                 for (int i = 0; i < n; ++i)
                   {
-                    s += M1[r * n + i] * Qz[i];
-                    k += K1[r * n + i] * Pz[i];
+                    s += M1[canon<p>(r, i)] * Qz[i];
+                    k += K1[canon<p>(r, i)] * Pz[i];
                   }
                 y[r] = s + cz * k;
               }
