@@ -25,6 +25,7 @@ namespace mgb
     double S[n * n], D[n * n], G[n * n], M1[n * n], K1[n * n], w[n], xq[n], nodes[n];
     float  Sf[n * n], Df[n * n], M1f[n * n], K1f[n * n], wf[n];
     double P1[(2 * n - 1) * n];
+    float  P1f[(2 * n - 1) * n];
   };
 
   __constant__ ConstTables<MGB_P + 1> ctab;
@@ -626,7 +627,10 @@ namespace mgb
         h->nodes[i] = b.nodes[i];
       }
     for (int i = 0; i < (2 * p + 1) * n; ++i)
-      h->P1[i] = b.P1[i];
+      {
+        h->P1[i]  = b.P1[i];
+        h->P1f[i] = (float)b.P1[i];
+      }
     cudaMemcpyToSymbol(ctab, h, sizeof(*h));
     delete h;
   }

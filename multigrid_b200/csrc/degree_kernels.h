@@ -77,6 +77,8 @@ namespace mgb
     void (*apply_cartesian_d)(const ApplyArgs<double> &, cudaStream_t);
     void (*transfer_f)(const TransferArgs<float> &, cudaStream_t);
     void (*transfer_d)(const TransferArgs<double> &, cudaStream_t);
+    void (*transfer_tile_f)(const TransferArgs<float> &, cudaStream_t);
+    void (*transfer_tile_d)(const TransferArgs<double> &, cudaStream_t);
     void (*diagonal_f)(const DiagArgs<float> &, cudaStream_t);
     void (*diagonal_d)(const DiagArgs<double> &, cudaStream_t);
     void (*rhs_values)(const RhsArgs &, cudaStream_t);

@@ -5,6 +5,7 @@
 #endif
 #include "degree_kernels.cuh"
 #include "cartesian_kernel.cuh"
+#include "transfer_kernels.cuh"
 
 namespace mgb
 {
@@ -19,6 +20,8 @@ namespace mgb
                                     &launch_apply_cartesian<MGB_P, double>,
                                     &launch_transfer<MGB_P, float>,
                                     &launch_transfer<MGB_P, double>,
+                                    &launch_transfer_tile<MGB_P, float>,
+                                    &launch_transfer_tile<MGB_P, double>,
                                     &launch_diagonal<MGB_P, float>,
                                     &launch_diagonal<MGB_P, double>,
                                     &launch_rhs_values<MGB_P>,

@@ -835,6 +835,7 @@ namespace mgb
     Level               *fine = nullptr, *coarse = nullptr;
     const DegreeKernels *dk = nullptr;
     bool                 constrained = false;
+    int                  kernel      = MGB_KERNEL_AUTO;
 
     void
     run(const int mode, T *dst, const T *src)
@@ -846,10 +847,12 @@ namespace mgb
       A.dst         = dst;
       A.mode        = mode;
       A.constrained = constrained;
+      // streaming tile kernels are compiled for the default tile width of the degree
+      const bool tiles = fine->d.CW == choose_tile_cells(fine->d.p, 0) && kernel == MGB_KERNEL_AUTO;
       if (sizeof(T) == 8)
-        dk->transfer_d(reinterpret_cast<const TransferArgs<double> &>(A), ctx->stream);
+        (tiles ? dk->transfer_tile_d : dk->transfer_d)(reinterpret_cast<const TransferArgs<double> &>(A), ctx->stream);
       else
-        dk->transfer_f(reinterpret_cast<const TransferArgs<float> &>(A), ctx->stream);
+        (tiles ? dk->transfer_tile_f : dk->transfer_f)(reinterpret_cast<const TransferArgs<float> &>(A), ctx->stream);
       ctx->check_launch();
     }
     void prolongate(T *f, const T *c) { run(0, f, c); }
@@ -949,6 +952,7 @@ namespace mgb
               transfer[l].dk = mg_transfer_no_boundary[l].dk = dk;
               transfer[l].constrained                = true;
               mg_transfer_no_boundary[l].constrained = false;
+              transfer[l].kernel = mg_transfer_no_boundary[l].kernel = o.kernel;
             }
         }
       // inhomogeneous boundary values and right-hand side (multigrid_solver.h:224-262)
@@ -1685,7 +1689,10 @@ extern "C"
     MGB_TRY
     MultigridSolver &m = S(s);
     for (int l = 0; l < m.n_levels; ++l)
-      m.matrix[l]->kernel = m.matrix_dp[l]->kernel = kernel;
+      {
+        m.matrix[l]->kernel = m.matrix_dp[l]->kernel = kernel;
+        m.transfer[l].kernel = m.mg_transfer_no_boundary[l].kernel = kernel;
+      }
     MGB_CATCH
   }
 
