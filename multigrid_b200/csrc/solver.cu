@@ -569,6 +569,14 @@ namespace mgb
     }
 
     void vmult(T *dst, const T *src) { apply(APPLY_SET, dst, src); }
+    // dst = A src and the dot product src . dst (first sum of vmult_with_cg_update, laplace_operator.h:698)
+    void
+    vmult_dot(T *dst, const T *src, double *result)
+    {
+      apply(APPLY_SET, dst, src);
+      ScopedRange range(*ctx, level->index, RK_CG_VEC);
+      *result = dot(*ctx, src, dst, m());
+    }
     void vmult_add(T *dst, const T *src) { apply(APPLY_ADD, dst, src); }
     void vmult_residual(const T *rhs, const T *lhs, T *residual) { apply(APPLY_RESIDUAL, residual, lhs, rhs); }
 
@@ -1157,51 +1165,79 @@ namespace mgb
     std::pair<unsigned int, double>
     solve_cg()
     {
-      const int    L = n_levels - 1;
-      const size_t N = levels[L]->d.n_dofs;
-      double      *x = solution[L]->p, *g = cg_g.p, *h = cg_h.p, *d = cg_d.p;
+      // deal.II SolverCG (x0 = 0): g = -b; h = M^-1 g; d = -h; loop { h = A d; alpha = g.h_old / d.h;
+      // x += alpha d; g += alpha h; check |g|; h = M^-1 g; beta = g.h / g.h_old; d = beta d - h }.
+      // Vector work is fused as in the reference's merged loops (laplace_operator.h:640-719,
+      // multigrid_solver.h:516-619): the residual update also produces |g|^2 and the float defect of the
+      // V-cycle, and the preconditioned residual h = double(solution_update) is never materialised.
+      const int     L = n_levels - 1;
+      const size_t  N = levels[L]->d.n_dofs;
+      double       *x = solution[L]->p, *g = cg_g.p, *h = cg_h.p, *d = cg_d.p;
       const double *b = rhs[L]->p;
+      float        *def = defect[L]->p;
       cg_history.clear();
       MGB_CUDA_CHECK(cudaMemsetAsync(x, 0, N * sizeof(double), ctx.stream));
-      foreach (ctx, N, [=] __device__(size_t i) { g[i] = -b[i]; });
-      double       res  = std::sqrt(dot(ctx, g, g, N));
+      double r2;
+      {
+        ScopedRange range(ctx, L, RK_CG_VEC);
+        reduce<1>(
+          ctx,
+          N,
+          [=] __device__(size_t i, double *acc) {
+            const double gi = -b[i];
+            g[i]            = gi;
+            def[i]          = (float)gi;
+            acc[0] += gi * gi;
+          },
+          &r2);
+      }
+      double       res  = std::sqrt(r2);
       const double res0 = res;
       cg_history.push_back(res);
       unsigned int it = 0;
       if (res > 1e-16)
         {
-          vmult(h, g);
-          foreach (ctx, N, [=] __device__(size_t i) { d[i] = -h[i]; });
-          double gh = dot(ctx, g, h, N);
-          while (true)
+          double gh = 0;
+          for (;;)
             {
+              v_cycle(L, 1); // solution_update[L] = M^-1 defect[L]
+              const float *upd = solution_update[L]->p;
+              {
+                ScopedRange range(ctx, L, RK_CG_VEC);
+                double      gh_new;
+                reduce<1>(
+                  ctx, N, [=] __device__(size_t i, double *acc) { acc[0] += g[i] * (double)upd[i]; }, &gh_new);
+                if (it == 0)
+                  foreach (ctx, N, [=] __device__(size_t i) { d[i] = -(double)upd[i]; });
+                else
+                  {
+                    const double beta = gh_new / gh;
+                    foreach (ctx, N, [=] __device__(size_t i) { d[i] = beta * d[i] - (double)upd[i]; });
+                  }
+                gh = gh_new;
+              }
               ++it;
-              matrix_dp[L]->vmult(h, d);
-              const int    rg    = ctx.range_begin(L, RK_CG_VEC);
-              const double alpha = gh / dot(ctx, d, h, N);
-              double       r2;
-              // x += alpha d; g += alpha h; |g|^2 in the same pass
-              reduce<1>(
-                ctx,
-                N,
-                [=] __device__(size_t i, double *acc) {
-                  x[i] += alpha * d[i];
-                  const double gi = g[i] + alpha * h[i];
-                  g[i]            = gi;
-                  acc[0] += gi * gi;
-                },
-                &r2);
-              ctx.range_end(rg);
+              double dh;
+              matrix_dp[L]->vmult_dot(h, d, &dh);
+              {
+                ScopedRange  range(ctx, L, RK_CG_VEC);
+                const double alpha = gh / dh;
+                reduce<1>(
+                  ctx,
+                  N,
+                  [=] __device__(size_t i, double *acc) {
+                    x[i] += alpha * d[i];
+                    const double gi = g[i] + alpha * h[i];
+                    g[i]            = gi;
+                    def[i]          = (float)gi;
+                    acc[0] += gi * gi;
+                  },
+                  &r2);
+              }
               res = std::sqrt(r2);
               cg_history.push_back(res);
               if (res <= 1e-16 || res <= 1e-9 * res0 || it >= 1000)
                 break;
-              vmult(h, g);
-              ScopedRange  range(ctx, L, RK_CG_VEC);
-              const double gh_new = dot(ctx, g, h, N);
-              const double beta   = gh_new / gh;
-              gh                  = gh_new;
-              foreach (ctx, N, [=] __device__(size_t i) { d[i] = beta * d[i] - h[i]; });
             }
         }
       ctx.sync();
