@@ -248,8 +248,8 @@ class MultigridSolver:
         self.n_levels = lib().mgb_solver_n_levels(self.h)
 
     def close(self):
-        if getattr(self, "h", None):
-            lib().mgb_solver_destroy(self.h)
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.mgb_solver_destroy(self.h)
             self.h = None
 
     __del__ = close

@@ -19,6 +19,9 @@
 // cf. the pre/post range operations of laplace_operator.h:607-741) is fused into the same pass and
 // each vector is read / written exactly once from HBM; there are no atomics and no index table.
 #pragma once
+#include <type_traits>
+#include <utility>
+
 #include "degree_kernels.cuh"
 
 #ifndef MGB_MINB64
@@ -27,9 +30,26 @@
 #ifndef MGB_MINB32
 #define MGB_MINB32 4
 #endif
+#ifndef MGB_MINB32C
+#define MGB_MINB32C 3
+#endif
 
 namespace mgb
 {
+  // compile-time loop: f(std::integral_constant<int, 0>{}), ..., f(std::integral_constant<int, N-1>{})
+  template <typename F, int... Is>
+  __device__ __forceinline__ void
+  static_for_impl(F &&f, std::integer_sequence<int, Is...>)
+  {
+    (f(std::integral_constant<int, Is>{}), ...);
+  }
+  template <int N, typename F>
+  __device__ __forceinline__ void
+  static_for(F &&f)
+  {
+    static_for_impl(f, std::make_integer_sequence<int, N>{});
+  }
+
   template <int p>
   struct TileCfg
   {
@@ -113,74 +133,90 @@ namespace mgb
     asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;\n" ::"r"(d), "l"(gmem_src), "n"(sizeof(T)), "r"(sz));
   }
 
-  // stores `count` completed planes k0, k0+1, ... of one point column with the fused vector operation
-  // (the post-range operation of laplace_operator.h:607-741); all loads are issued before the stores
-  template <int p, typename T, int MODE>
+  // internal mode of the kernel: the first Chebyshev iteration (x_{k-1} = 0 implied) is its own instance
+  constexpr int APPLY_CHEBYSHEV_FIRST = 4;
+
+  // Stores COUNT completed planes of one point column with the fused vector operation (the post-range
+  // operation of laplace_operator.h:607-741).  `d0` = index of the first plane, consecutive planes are
+  // `stride` apart; bit r of `con` flags plane r as a Dirichlet row (only looked at when BND).  All loads
+  // are issued before the first store.
+  template <int p, typename T, int MODE, int COUNT, bool BND>
   __device__ __forceinline__ void
-  store_planes(const ApplyArgs<T> &A, const T (&y)[p + 1], const int k0, const int count,
-               const uint32_t own_off, const uint32_t own_stride, const bool xy_constrained)
+  store_planes(const ApplyArgs<T> &A, const T (&y)[p + 1], const uint32_t d0, const uint32_t stride,
+               const unsigned int con)
   {
     const T *__restrict__ src = A.src;
     const T *__restrict__ rhs = A.rhs;
     const T *__restrict__ inv = A.inv_diag;
     T *__restrict__ dst       = A.dst;
-    const int  nd2  = A.L.nd[2];
-    const bool z_lo = (A.L.dirichlet & 16u) != 0, z_hi = (A.L.dirichlet & 32u) != 0;
-    T          xs[p], rs[p], ds[p], os[p];
-    bool       con[p];
+    constexpr bool CHEB = MODE == APPLY_CHEBYSHEV || MODE == APPLY_CHEBYSHEV_FIRST;
+    T              xs[COUNT], rs[COUNT], ds[COUNT], os[COUNT];
 #pragma unroll
-    for (int r = 0; r < p; ++r)
-      if (r < count)
-        {
-          const int      gk = k0 + r;
-          const uint32_t d  = own_off + (uint32_t)gk * own_stride;
-          con[r]            = xy_constrained || (gk == 0 && z_lo) || (gk == nd2 - 1 && z_hi);
-          if (MODE == APPLY_ADD)
-            os[r] = dst[d];
-          else
-            {
-              if (MODE == APPLY_CHEBYSHEV || con[r])
-                xs[r] = src[d];
-              if (MODE != APPLY_SET)
-                rs[r] = rhs[d];
-              if (MODE == APPLY_CHEBYSHEV)
-                {
-                  ds[r] = inv[d];
-                  if (!A.first_chebyshev)
-                    os[r] = dst[d];
-                }
-            }
-        }
+    for (int r = 0; r < COUNT; ++r)
+      {
+        const uint32_t d = d0 + r * stride;
+        if (MODE == APPLY_ADD)
+          os[r] = dst[d];
+        else
+          {
+            if (CHEB || (BND && ((con >> r) & 1u)))
+              xs[r] = src[d];
+            if (MODE != APPLY_SET)
+              rs[r] = rhs[d];
+            if (CHEB)
+              ds[r] = inv[d];
+            if (MODE == APPLY_CHEBYSHEV)
+              os[r] = dst[d];
+          }
+      }
+    const T f1 = A.f1, f2 = A.f2, f1p = T(1) + A.f1;
 #pragma unroll
-    for (int r = 0; r < p; ++r)
-      if (r < count)
-        {
-          const uint32_t d = own_off + (uint32_t)(k0 + r) * own_stride;
-          T              v = y[r];
-          if (MODE == APPLY_ADD)
-            {
-              if (!con[r])
-                dst[d] = os[r] + v;
-              continue;
-            }
-          if (con[r])
-            v = xs[r]; // identity rows (laplace_operator.h:592-593, :632-633)
-          if (MODE == APPLY_SET)
-            dst[d] = v;
-          else if (MODE == APPLY_RESIDUAL)
-            dst[d] = rs[r] - v;
-          else
-            {
-              const T upd = A.f2 * ds[r] * (rs[r] - v);
-              dst[d]      = A.first_chebyshev ? (T(1) + A.f1) * xs[r] + upd :
-                                                (T(1) + A.f1) * xs[r] - A.f1 * os[r] + upd;
-            }
-        }
+    for (int r = 0; r < COUNT; ++r)
+      {
+        const uint32_t d = d0 + r * stride;
+        const bool     c = BND && ((con >> r) & 1u);
+        T              v = y[r];
+        if (MODE == APPLY_ADD)
+          {
+            if (!c)
+              dst[d] = os[r] + v;
+            continue;
+          }
+        if (c)
+          v = xs[r]; // identity rows (laplace_operator.h:592-593, :632-633)
+        if (MODE == APPLY_SET)
+          dst[d] = v;
+        else if (MODE == APPLY_RESIDUAL)
+          dst[d] = rs[r] - v;
+        else
+          {
+            T t = f2 * ds[r] * (rs[r] - v) + f1p * xs[r];
+            if (MODE == APPLY_CHEBYSHEV)
+              t -= f1 * os[r];
+            dst[d] = t;
+          }
+      }
   }
+
+  // asynchronous copy with an immediate shared-memory offset (bytes)
+  template <typename T, int OFFSET>
+  __device__ __forceinline__ void
+  cp_async_imm(const uint32_t smem_base, const T *gmem_src, const int src_bytes)
+  {
+    asm volatile("cp.async.ca.shared.global [%0 + %1], [%2], %3, %4;\n" ::"r"(smem_base), "n"(OFFSET), "l"(gmem_src),
+                 "n"(sizeof(T)), "r"(src_bytes));
+  }
+
+  template <int MODE, typename T>
+  struct TileMinBlocks
+  {
+    static constexpr int value =
+      sizeof(T) == 8 ? MGB_MINB64 : (MODE >= APPLY_CHEBYSHEV ? MGB_MINB32C : MGB_MINB32);
+  };
 
   template <int p, typename T, int MODE>
   __global__ void
-  __launch_bounds__(TileCfg<p>::NT, sizeof(T) == 8 ? MGB_MINB64 : MGB_MINB32)
+  __launch_bounds__(TileCfg<p>::NT, TileMinBlocks<MODE, T>::value)
     k_apply_tile(const ApplyArgs<T> A, const int layers_per_segment)
   {
     using C           = TileCfg<p>;
@@ -194,7 +230,7 @@ namespace mgb
     constexpr int PQP = C::PQP;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T *u_s  = reinterpret_cast<T *>(smem_raw); // [buffer][plane][row J'+p][col I'+p]
-    T *mx_s = u_s + 2 * C::U_SIZE;                 // [plane][I][row J'+p]
+    T *mx_s = u_s + 2 * C::U_SIZE;             // [plane][I][row J'+p]
     T *kx_s = mx_s + C::MX_SIZE;
     T *P_s  = kx_s + C::MX_SIZE;               // [plane (pitch PQP)][J][I]
     T *Q_s  = P_s + C::PQ_SIZE;
@@ -210,12 +246,10 @@ namespace mgb
     const int        c0 = seg * layers_per_segment;
     const int        c1 = imin(c0 + layers_per_segment, ncz);
     const bool       plain = A.read_plain != 0;
-    const T *__restrict__ src = A.src;
 
-    // ---- per-thread source points (fixed over the planes)
-    uint32_t src_off[NL];
-    int      src_stride[NL];
-    bool     src_ok[NL];
+    // ---- per-thread source points (fixed over the planes): running pointer, plane stride, copy size
+    const T *src_ptr[NL];
+    int      src_stride[NL], src_bytes[NL];
 #pragma unroll
     for (int l = 0; l < NL; ++l)
       {
@@ -224,22 +258,17 @@ namespace mgb
         bool      ok = q < NI * NI && gi >= 0 && gi < L.nd[0] && gj >= 0 && gj < L.nd[1];
         if (ok && !plain && is_constrained_xy(L, gi, gj))
           ok = false; // Dirichlet in x or y; the z-faces are handled per plane
-        src_ok[l]     = ok;
-        src_off[l]    = 0;
-        src_stride[l] = 0;
-        if (ok)
-          {
-            src_off[l]    = dof_index(L, gi, gj, 0);
-            src_stride[l] = tile_width(L, 0, gi / TW) * tile_width(L, 1, gj / TW);
-          }
+        src_bytes[l]  = ok ? (int)sizeof(T) : 0; // 0: the copy writes a zero
+        src_stride[l] = ok ? tile_width(L, 0, gi / TW) * tile_width(L, 1, gj / TW) : 0;
+        src_ptr[l]    = A.src + (ok ? dof_index(L, gi, gj, 0) : 0u);
       }
     // planes that read as zero: outside the grid, or on a Dirichlet z-face
     const int k_lo = (!plain && (L.dirichlet & 16u)) ? 1 : 0;
     const int k_hi = (!plain && (L.dirichlet & 32u)) ? nd2 - 2 : nd2 - 1;
 
     // ---- x-stage tasks of this thread: (cell column, row, plane) -> p output rows
-    int  x_in[NXR], x_out[NXR];
-    int  x_flags = 0; // bit 2r: previous cell exists, bit 2r+1: own cell exists, round r
+    int x_in[NXR], x_out[NXR];
+    int x_flags = 0; // bit 2r: previous cell exists, bit 2r+1: own cell exists, round r
 #pragma unroll
     for (int r = 0; r < NXR; ++r)
       {
@@ -272,8 +301,11 @@ namespace mgb
     const int  I = tid % TW, J = tid / TW;
     const bool owner = tid < TW * TW && I < wx && J < wy;
     const bool xy_constrained = owner && is_constrained_xy(L, gx0 + I, gy0 + J);
-    const uint32_t own_off    = tile_base(L, tx, ty) + (uint32_t)(J * wx + I);
+    // block-uniform: does this tile touch a Dirichlet face in x or y?
+    const bool tile_bnd = ((L.dirichlet & 1u) && tx == 0) || ((L.dirichlet & 2u) && gx0 + wx == L.nd[0]) ||
+                          ((L.dirichlet & 4u) && ty == 0) || ((L.dirichlet & 8u) && gy0 + wy == L.nd[1]);
     const uint32_t own_stride = (uint32_t)(wx * wy);
+    const uint32_t own_off    = tile_base(L, tx, ty) + (uint32_t)(J * wx + I);
     const int      pq_off     = J * TW + I;
 
     const T *M1 = Tab<T>::M1();
@@ -283,21 +315,39 @@ namespace mgb
     T Pz[n], Qz[n]; // P, Q of this thread's column on the planes of the current cell layer
     T carry = 0;
 
-    // source planes of batch c -> shared-memory buffer `buf`, asynchronously
+    const uint32_t u_base = (uint32_t)__cvta_generic_to_shared(u_s + tid);
+
+    // source planes of batch c (planes c p + 1 .. c p + p) -> shared-memory buffer `buf`, asynchronously
     auto issue_loads = [&](const int c, const int buf) {
-#pragma unroll
-      for (int b = 0; b < p; ++b)
+      const uint32_t sb = u_base + (uint32_t)(buf * C::U_SIZE * (int)sizeof(T));
+      const int      k0 = c * p + 1;
+      if (k0 >= k_lo && k0 + p - 1 <= k_hi)
         {
-          const int  gk  = c * p + 1 + b;
-          const bool okz = gk >= k_lo && gk <= k_hi;
-#pragma unroll
-          for (int l = 0; l < NL; ++l)
-            if (tid + l * NT < NI * NI)
+          static_for<NL>([&](auto lc) {
+            constexpr int l = decltype(lc)::value;
+            if (l + 1 < NL || tid + l * NT < NI * NI)
               {
-                const bool ok = src_ok[l] && okz;
-                cp_async_value(u_s + (buf * p + b) * NI * NI + tid + l * NT,
-                               ok ? src + src_off[l] + (uint32_t)gk * (uint32_t)src_stride[l] : src, ok);
+                const T *g = src_ptr[l] + (size_t)k0 * src_stride[l];
+                static_for<p>([&](auto bc) {
+                  constexpr int b = decltype(bc)::value;
+                  cp_async_imm<T, (b * NI * NI + l * NT) * (int)sizeof(T)>(sb, g + b * src_stride[l], src_bytes[l]);
+                });
               }
+          });
+        }
+      else
+        {
+#pragma unroll
+          for (int b = 0; b < p; ++b)
+            {
+              const int  gk  = k0 + b;
+              const bool okz = gk >= k_lo && gk <= k_hi;
+#pragma unroll
+              for (int l = 0; l < NL; ++l)
+                if (tid + l * NT < NI * NI)
+                  cp_async_value(u_s + (buf * p + b) * NI * NI + tid + l * NT,
+                                 okz ? src_ptr[l] + (size_t)gk * src_stride[l] : A.src, okz && src_bytes[l] != 0);
+            }
         }
       asm volatile("cp.async.commit_group;\n" ::);
     };
@@ -305,6 +355,7 @@ namespace mgb
     // ---- march through the cell layers.  Batch c = planes c p + 1 .. c p + p.  The first batch only
     //      provides the lowest plane of the first layer; layer c_begin < c0 only produces the carry.
     const int c_begin = c0 > 0 ? c0 - 1 : 0;
+    uint32_t  d_layer = own_off + (uint32_t)(c0 * p) * own_stride; // index of plane c p at this thread's point
     issue_loads(c_begin - 1, 0);
     for (int c = c_begin - 1; c < c1; ++c)
       {
@@ -391,7 +442,19 @@ namespace mgb
             y[0] += carry;
             carry = y[p];
             if (c >= c0)
-              store_planes<p, T, MODE>(A, y, c * p, p, own_off, own_stride, xy_constrained);
+              {
+                // block-uniform choice: only tiles on a Dirichlet face / the bottom layer look at constraints
+                if (tile_bnd || c == 0)
+                  {
+                    unsigned int con = xy_constrained ? 0xffu : 0u;
+                    if (c == 0 && (L.dirichlet & 16u))
+                      con |= 1u;
+                    store_planes<p, T, MODE, p, true>(A, y, d_layer, own_stride, con);
+                  }
+                else
+                  store_planes<p, T, MODE, p, false>(A, y, d_layer, own_stride, 0u);
+                d_layer += p * own_stride;
+              }
           }
         Pz[0] = Pz[p];
         Qz[0] = Qz[p];
@@ -400,7 +463,8 @@ namespace mgb
       {
         T y[n];
         y[0] = carry;
-        store_planes<p, T, MODE>(A, y, ncz * p, 1, own_off, own_stride, xy_constrained);
+        store_planes<p, T, MODE, 1, true>(A, y, d_layer, own_stride,
+                                          (xy_constrained || (L.dirichlet & 32u)) ? 1u : 0u);
       }
   }
 
@@ -438,7 +502,12 @@ namespace mgb
         case APPLY_ADD: launch_apply_tile<p, T, APPLY_ADD>(A, stream); break;
         case APPLY_SET: launch_apply_tile<p, T, APPLY_SET>(A, stream); break;
         case APPLY_RESIDUAL: launch_apply_tile<p, T, APPLY_RESIDUAL>(A, stream); break;
-        default: launch_apply_tile<p, T, APPLY_CHEBYSHEV>(A, stream); break;
+        default:
+          if (A.first_chebyshev)
+            launch_apply_tile<p, T, APPLY_CHEBYSHEV_FIRST>(A, stream);
+          else
+            launch_apply_tile<p, T, APPLY_CHEBYSHEV>(A, stream);
+          break;
       }
   }
 } // namespace mgb
