@@ -31,7 +31,7 @@
 #define MGB_MINB32 4
 #endif
 #ifndef MGB_MINB32C
-#define MGB_MINB32C 3
+#define MGB_MINB32C 4
 #endif
 
 namespace mgb
@@ -136,39 +136,53 @@ namespace mgb
   // internal mode of the kernel: the first Chebyshev iteration (x_{k-1} = 0 implied) is its own instance
   constexpr int APPLY_CHEBYSHEV_FIRST = 4;
 
-  // Stores COUNT completed planes of one point column with the fused vector operation (the post-range
-  // operation of laplace_operator.h:607-741).  `d0` = index of the first plane, consecutive planes are
-  // `stride` apart; bit r of `con` flags plane r as a Dirichlet row (only looked at when BND).  All loads
-  // are issued before the first store.
+  // Operands of the fused vector operation (the post-range operation of laplace_operator.h:607-741) on
+  // COUNT planes of one point column: loaded early (load_operands, before the y-stage) so that their
+  // latency is covered by the stages, consumed when the planes are complete (store_planes).
+  // `d0` = index of the first plane, consecutive planes are `stride` apart; bit r of `con` flags plane r
+  // as a Dirichlet row (only looked at when BND).
+  template <typename T, int COUNT>
+  struct Operands
+  {
+    T xs[COUNT], rs[COUNT], ds[COUNT], os[COUNT];
+  };
+
   template <int p, typename T, int MODE, int COUNT, bool BND>
   __device__ __forceinline__ void
-  store_planes(const ApplyArgs<T> &A, const T (&y)[p + 1], const uint32_t d0, const uint32_t stride,
-               const unsigned int con)
+  load_operands(const ApplyArgs<T> &A, Operands<T, COUNT> &o, const uint32_t d0, const uint32_t stride,
+                const unsigned int con)
   {
     const T *__restrict__ src = A.src;
     const T *__restrict__ rhs = A.rhs;
     const T *__restrict__ inv = A.inv_diag;
-    T *__restrict__ dst       = A.dst;
+    const T *__restrict__ dst = A.dst;
     constexpr bool CHEB = MODE == APPLY_CHEBYSHEV || MODE == APPLY_CHEBYSHEV_FIRST;
-    T              xs[COUNT], rs[COUNT], ds[COUNT], os[COUNT];
 #pragma unroll
     for (int r = 0; r < COUNT; ++r)
       {
         const uint32_t d = d0 + r * stride;
         if (MODE == APPLY_ADD)
-          os[r] = dst[d];
+          o.os[r] = dst[d];
         else
           {
             if (CHEB || (BND && ((con >> r) & 1u)))
-              xs[r] = src[d];
+              o.xs[r] = src[d];
             if (MODE != APPLY_SET)
-              rs[r] = rhs[d];
+              o.rs[r] = rhs[d];
             if (CHEB)
-              ds[r] = inv[d];
+              o.ds[r] = inv[d];
             if (MODE == APPLY_CHEBYSHEV)
-              os[r] = dst[d];
+              o.os[r] = dst[d];
           }
       }
+  }
+
+  template <int p, typename T, int MODE, int COUNT, bool BND>
+  __device__ __forceinline__ void
+  store_planes(const ApplyArgs<T> &A, const Operands<T, COUNT> &o, const T (&y)[p + 1], const uint32_t d0,
+               const uint32_t stride, const unsigned int con)
+  {
+    T *__restrict__ dst = A.dst;
     const T f1 = A.f1, f2 = A.f2, f1p = T(1) + A.f1;
 #pragma unroll
     for (int r = 0; r < COUNT; ++r)
@@ -179,20 +193,20 @@ namespace mgb
         if (MODE == APPLY_ADD)
           {
             if (!c)
-              dst[d] = os[r] + v;
+              dst[d] = o.os[r] + v;
             continue;
           }
         if (c)
-          v = xs[r]; // identity rows (laplace_operator.h:592-593, :632-633)
+          v = o.xs[r]; // identity rows (laplace_operator.h:592-593, :632-633)
         if (MODE == APPLY_SET)
           dst[d] = v;
         else if (MODE == APPLY_RESIDUAL)
-          dst[d] = rs[r] - v;
+          dst[d] = o.rs[r] - v;
         else
           {
-            T t = f2 * ds[r] * (rs[r] - v) + f1p * xs[r];
+            T t = f2 * o.ds[r] * (o.rs[r] - v) + f1p * o.xs[r];
             if (MODE == APPLY_CHEBYSHEV)
-              t -= f1 * os[r];
+              t -= f1 * o.os[r];
             dst[d] = t;
           }
       }
@@ -389,6 +403,23 @@ namespace mgb
             }
         __syncthreads();
 
+        // operands of the fused update for this layer: issued now, consumed after the z-stage
+        Operands<T, p> ops;
+        const bool     bnd = tile_bnd || c == 0; // block-uniform: only then constraints are looked at
+        unsigned int   con = 0;
+        if (owner && c >= c0)
+          {
+            if (bnd)
+              {
+                con = xy_constrained ? 0xffu : 0u;
+                if (c == 0 && (L.dirichlet & 16u))
+                  con |= 1u;
+                load_operands<p, T, MODE, p, true>(A, ops, d_layer, own_stride, con);
+              }
+            else
+              load_operands<p, T, MODE, p, false>(A, ops, d_layer, own_stride, 0u);
+          }
+
         // (c) y-stage: P = My mx, Q = c0 My kx + c1 Ky mx
         if (y_in >= 0)
           {
@@ -443,16 +474,10 @@ namespace mgb
             carry = y[p];
             if (c >= c0)
               {
-                // block-uniform choice: only tiles on a Dirichlet face / the bottom layer look at constraints
-                if (tile_bnd || c == 0)
-                  {
-                    unsigned int con = xy_constrained ? 0xffu : 0u;
-                    if (c == 0 && (L.dirichlet & 16u))
-                      con |= 1u;
-                    store_planes<p, T, MODE, p, true>(A, y, d_layer, own_stride, con);
-                  }
+                if (bnd)
+                  store_planes<p, T, MODE, p, true>(A, ops, y, d_layer, own_stride, con);
                 else
-                  store_planes<p, T, MODE, p, false>(A, y, d_layer, own_stride, 0u);
+                  store_planes<p, T, MODE, p, false>(A, ops, y, d_layer, own_stride, 0u);
                 d_layer += p * own_stride;
               }
           }
@@ -463,8 +488,10 @@ namespace mgb
       {
         T y[n];
         y[0] = carry;
-        store_planes<p, T, MODE, 1, true>(A, y, d_layer, own_stride,
-                                          (xy_constrained || (L.dirichlet & 32u)) ? 1u : 0u);
+        const unsigned int con = (xy_constrained || (L.dirichlet & 32u)) ? 1u : 0u;
+        Operands<T, 1>     ops;
+        load_operands<p, T, MODE, 1, true>(A, ops, d_layer, own_stride, con);
+        store_planes<p, T, MODE, 1, true>(A, ops, y, d_layer, own_stride, con);
       }
   }
 
