@@ -273,7 +273,7 @@ namespace mgb
         if (ok && !plain && is_constrained_xy(L, gi, gj))
           ok = false; // Dirichlet in x or y; the z-faces are handled per plane
         src_bytes[l]  = ok ? (int)sizeof(T) : 0; // 0: the copy writes a zero
-        src_stride[l] = ok ? tile_width(L, 0, gi / TW) * tile_width(L, 1, gj / TW) : 0;
+        src_stride[l] = ok ? (int)plane_pitch(L) : 0;
         src_ptr[l]    = A.src + (ok ? dof_index(L, gi, gj, 0) : 0u);
       }
     // planes that read as zero: outside the grid, or on a Dirichlet z-face
@@ -318,7 +318,7 @@ namespace mgb
     // block-uniform: does this tile touch a Dirichlet face in x or y?
     const bool tile_bnd = ((L.dirichlet & 1u) && tx == 0) || ((L.dirichlet & 2u) && gx0 + wx == L.nd[0]) ||
                           ((L.dirichlet & 4u) && ty == 0) || ((L.dirichlet & 8u) && gy0 + wy == L.nd[1]);
-    const uint32_t own_stride = (uint32_t)(wx * wy);
+    const uint32_t own_stride = plane_pitch(L);
     const uint32_t own_off    = tile_base(L, tx, ty) + (uint32_t)(J * wx + I);
     const int      pq_off     = J * TW + I;
 

@@ -9,11 +9,14 @@
 //   the (nd0 x nd1 x nd2) grid of DoFs (nd = ncell * p + 1) is cut into columns of TW x TW points
 //   (TW = CW * p, CW cells per tile and direction); tile (tx,ty) owns the points
 //   [TW tx, TW tx + TW) x [TW ty, TW ty + TW) x [0, nd2) (the last tile in a direction is narrower,
-//   possibly one point wide).  Inside a tile column the numbering is z-plane major:
+//   possibly one point wide).  The numbering is z-plane major over the whole level, tile by tile
+//   inside a plane:
 //
-//       index = base(tx,ty) + gk * (wx wy) + ly * wx + lx ,   base = nd2 (ty TW nd0 + tx TW wy)
+//       index = gk * (nd0 nd1) + offset(tx,ty) + ly * wx + lx ,   offset = ty TW nd0 + tx TW wy
 //
-// so every z-plane of a full tile is one contiguous, 128-byte aligned chunk of TW^2 values.  A thread
+// so every z-plane of a tile is one contiguous chunk of wx wy values, and a slab of z-planes is one
+// contiguous range of the vector: the ghost planes of a z-slab decomposition over several GPUs sit at
+// the two ends of the local vector and the owned DoFs in between (see `zg` below).  A thread
 // block streams a tile column plane by plane with coalesced loads and owns the result at all of
 // its points (see cartesian_kernel.cuh): no scatter, no atomics.  Dirichlet DoFs are the points on the
 // flagged faces of the box: read as 0, never written by the cell loop
@@ -55,13 +58,19 @@ namespace mgb
     return imin(L.TW, L.nd[d] - t * L.TW);
   }
 
-  // first index of the column of tile (tx,ty)
+  // distance between two z-planes of the level
+  MGB_HD uint32_t
+  plane_pitch(const LevelDesc &L)
+  {
+    return (uint32_t)L.nd[0] * (uint32_t)L.nd[1];
+  }
+
+  // index of the first point of tile (tx,ty) on plane 0
   MGB_HD uint32_t
   tile_base(const LevelDesc &L, const int tx, const int ty)
   {
     const int wy = tile_width(L, 1, ty);
-    return (uint32_t)((uint64_t)L.nd[2] *
-                      ((uint64_t)ty * L.TW * L.nd[0] + (uint64_t)tx * L.TW * wy));
+    return (uint32_t)ty * (uint32_t)(L.TW * L.nd[0]) + (uint32_t)tx * (uint32_t)(L.TW * wy);
   }
 
   // library index of the DoF at grid point (gi,gj,gk)
@@ -70,8 +79,8 @@ namespace mgb
   {
     const int tx = gi / L.TW, ty = gj / L.TW;
     const int lx = gi - tx * L.TW, ly = gj - ty * L.TW;
-    const int wx = tile_width(L, 0, tx), wy = tile_width(L, 1, ty);
-    return tile_base(L, tx, ty) + (uint32_t)gk * (uint32_t)(wx * wy) + (uint32_t)(ly * wx + lx);
+    const int wx = tile_width(L, 0, tx);
+    return (uint32_t)gk * plane_pitch(L) + tile_base(L, tx, ty) + (uint32_t)(ly * wx + lx);
   }
 
   MGB_HD bool

@@ -107,7 +107,7 @@ namespace mgb
           ok = false;
         c_ok[l]     = ok;
         c_off[l]    = ok ? dof_index(Lc, gi, gj, 0) : 0u;
-        c_stride[l] = ok ? tile_width(Lc, 0, gi / TW) * tile_width(Lc, 1, gj / TW) : 0;
+        c_stride[l] = ok ? (int)plane_pitch(Lc) : 0;
       }
     const int k_lo = (A.constrained && (Lc.dirichlet & 16u)) ? 1 : 0;
     const int k_hi = (A.constrained && (Lc.dirichlet & 32u)) ? Lc.nd[2] - 2 : Lc.nd[2] - 1;
@@ -119,7 +119,7 @@ namespace mgb
     parent_of<p>(gy0 + J, Lc.ncell[1], cyo, ryo);
     const int      cj0        = p * (cyo - cay);
     const uint32_t own_off    = tile_base(Lf, tx, ty) + (uint32_t)(J * wx + I);
-    const uint32_t own_stride = (uint32_t)(wx * wy);
+    const uint32_t own_stride = plane_pitch(Lf);
 
     T W[n]; // x/y-interpolated coarse planes of the current parent layer at this thread's point
 
@@ -257,7 +257,7 @@ namespace mgb
     const int  I = tid % TW, J = tid / TW;
     const bool owner = tid < TW * TW && I < wx && J < wy;
     const uint32_t own_off    = tile_base(Lf, tx, ty) + (uint32_t)(J * wx + I);
-    const uint32_t own_stride = (uint32_t)(wx * wy);
+    const uint32_t own_stride = plane_pitch(Lf);
 
     // x/y restriction of `np` planes held in z_s and addition into the coarse planes k_first, ...
     auto planes_2d = [&](const int k_first, const int np) {

@@ -54,8 +54,9 @@ def test_basis_matches_oracle(mgb, orc, p):
                                         (3, (3, 5, 7), 0), (4, (8, 8, 8), 2), (8, (2, 2, 4), 0), (5, (4, 4, 4), 0),
                                         (4, (9, 5, 1), 0), (1, (40, 17, 3), 0)])
 def test_numbering(mgb, p, ncell, cw):
-    """tile-column numbering of csrc/level.h: a permutation; every z-plane of a tile is one contiguous,
-    row-major chunk; tile columns follow each other; Dirichlet DoFs = the boundary points"""
+    """tile numbering of csrc/level.h: a permutation; z-plane major over the level (a slab of planes is one
+    contiguous range), inside a plane tile by tile, every tile one contiguous row-major chunk; Dirichlet
+    DoFs = the boundary points"""
     r = mgb.host_numbering(p, ncell, cw)
     nd = [c * p + 1 for c in ncell]
     N = nd[0] * nd[1] * nd[2]
@@ -69,12 +70,15 @@ def test_numbering(mgb, p, ncell, cw):
     assert r["n_tiles"] == ntx * nty
     grid = lex.reshape(nd[2], nd[1], nd[0])
     base = 0
-    for ty in range(nty):
-        for tx in range(ntx):
-            wx, wy = min(TW, nd[0] - tx * TW), min(TW, nd[1] - ty * TW)
-            col = grid[:, ty * TW:ty * TW + wy, tx * TW:tx * TW + wx]
-            assert np.array_equal(col.ravel(), base + np.arange(nd[2] * wy * wx))
-            base += nd[2] * wy * wx
+    for gk in (0, nd[2] // 2, nd[2] - 1):
+        base = gk * nd[0] * nd[1]
+        for ty in range(nty):
+            for tx in range(ntx):
+                wx, wy = min(TW, nd[0] - tx * TW), min(TW, nd[1] - ty * TW)
+                chunk = grid[gk, ty * TW:ty * TW + wy, tx * TW:tx * TW + wx]
+                assert np.array_equal(chunk.ravel(), base + np.arange(wy * wx))
+                base += wy * wx
+        assert base == (gk + 1) * nd[0] * nd[1]
     n_boundary = N - (nd[0] - 2) * (nd[1] - 2) * (nd[2] - 2)
     assert r["n_constrained"] == n_boundary
 
