@@ -161,13 +161,37 @@ def reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
+def weak_scaling_mesh(cells, n_gpus):
+    """The reference's weak-scaling series (poisson_cube/program.cc:508-527, `use_doubling_mesh`): the box is
+    doubled direction by direction, 128^3 -> 128x128x256 -> 128x256x256 -> 256^3 cells, here z first so that
+    every GPU's z-slab is 128^3 cells' worth of work.  Returns (n_subdivisions, n_refinements, lower, upper)."""
+    nref = cells.bit_length() - 1
+    assert 1 << nref == cells, "--cells must be a power of two"
+    if n_gpus == 1:
+        return (1, 1, 1), nref, (-0.9,) * 3, (1.0,) * 3
+    if n_gpus == 8:  # the cube again (sizes[] = 256: n_subdiv 1, one more refinement)
+        return (1, 1, 1), nref + 1, (-0.9,) * 3, (1.0,) * 3
+    assert n_gpus in (2, 4), "--gpus must be 1, 2, 4 or 8"
+    nsub = (1, 1, 2) if n_gpus == 2 else (1, 2, 2)
+    return nsub, nref, (-1.0,) * 3, tuple(0.9 + 1.9 * (k - 1) for k in nsub)
+
+
 def workload_config(args, n_gpus):
     cells = args.cells
-    return {"workload": "poisson_cube FE_Q<3>(%d), %d^3 cells per GPU, cube [-0.9,1]^3, 2 V-cycles/FMG level, "
-                        "Chebyshev 2+2 (deal.II >= 9.5 degree 3), CG to 1e-9" % (DEGREE, cells),
-            "degree": DEGREE, "cells_per_gpu": cells ** 3, "dofs_per_gpu": (DEGREE * cells + 1) ** 3,
-            "levels": cells.bit_length(), "parallelism": "1 GPU" if n_gpus == 1 else "%d independent sub-domains" % n_gpus,
-            "l2_flush": "inputs larger than L2 (every level-7 vector is >= 540 MB)"}
+    nsub, nref, lo, hi = weak_scaling_mesh(cells, n_gpus)
+    shape = [k << nref for k in nsub]
+    dofs = 1
+    for c in shape:
+        dofs *= DEGREE * c + 1
+    return {"workload": "poisson_cube FE_Q<3>(%d), %dx%dx%d cells = %d DoF on %d GPU(s) (%d^3 cells per GPU), box %s..%s, "
+                        "2 V-cycles/FMG level, Chebyshev 2+2 (deal.II >= 9.5 degree 3), CG to 1e-9"
+                        % (DEGREE, shape[0], shape[1], shape[2], dofs, n_gpus, cells, list(lo), list(hi)),
+            "degree": DEGREE, "cells": shape, "cells_per_gpu": cells ** 3, "total_dofs": dofs,
+            "levels": nref + 1,
+            "parallelism": "1 GPU" if n_gpus == 1 else
+            "%d z-slabs of whole cell layers, one per GPU; NCCL ghost-plane exchange per operator apply, "
+            "scalar all-reduces in CG; coarse levels replicated" % n_gpus,
+            "l2_flush": "inputs larger than L2 (every finest-level vector is >= 540 MB per GPU)"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -203,14 +227,16 @@ def native_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    nref = args.cells.bit_length() - 1
-    assert 1 << nref == args.cells, "--cells must be a power of two"
+    nsub, nref, lo, hi = weak_scaling_mesh(args.cells, world)
+    comm = mgb.comm_from_torch_distributed() if dist is not None else None
     t_setup = time.perf_counter()
-    s = mgb.MultigridSolver(DEGREE, 1, nref, degree_pre=3, degree_post=3, n_cycles=2, device=local_rank)
+    s = mgb.MultigridSolver(DEGREE, nsub, nref, lower=lo, upper=hi, degree_pre=3, degree_post=3, n_cycles=2,
+                            device=local_rank, comm=comm)
     s.sync()
     t_setup = time.perf_counter() - t_setup
-    n = s.n_dofs()
+    n = s.n_dofs()  # local vector length (owned + ghost planes)
     L = s.n_levels - 1
+    part = s.partition(L)
     hbm_gbs, peak_src = load_peaks()
 
     # ---- device-resident solve: W warm-up steps, K timed steps
@@ -230,6 +256,7 @@ def native_arm(args):
     ms = s.timer_stop()
     barrier()
     launches = s.launch_count() - launches0
+    exchanges = s.exchange_count()
     classes = s.class_times(L, reset=True)
     s.profile(False)
     ms_step = max_over_ranks(ms / args.steps)
@@ -263,12 +290,13 @@ def native_arm(args):
     clocks = sampler.stop() if rank == 0 else None
     return dict(s=s, n=n, L=L, its=its, rate=rate, ms_step=ms_step, ms_e2e=ms_e2e, mv=mv, classes=classes,
                 launches=launches, l2_error=l2_error, clocks=clocks, t_setup=t_setup, hbm_gbs=hbm_gbs,
-                peak_src=peak_src, rank=rank, world=world, dist=dist)
+                peak_src=peak_src, rank=rank, world=world, dist=dist, part=part, exchanges=exchanges)
 
 
 def report(args, r):
-    n, world = r["n"], r["world"]
-    total_dofs = n * world  # weak scaling: every GPU solves its own 128^3-cell sub-domain
+    world = r["world"]
+    n = r["part"]["n_owned"]             # DoFs this GPU owns (what its kernels produce per launch)
+    total_dofs = r["part"]["n_global"]   # one global problem, cut into z-slabs
     value = total_dofs / (1e-3 * r["ms_step"])
     e2e_value = total_dofs / (1e-3 * r["ms_e2e"])
     hbm = r["hbm_gbs"]
@@ -309,8 +337,9 @@ def report(args, r):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": value / BASELINE_CG_DOFS_PER_S,
         "dtype": "f64 outer CG / f32 V-cycle", "data": "synthetic", "config": workload_config(args, world),
-        "e2e": {"value": e2e_value, "unit": "DoF/s", "ms_per_step": r["ms_e2e"], "h2d_bytes_per_step": 8 * n * world,
-                "d2h_bytes_per_step": 8 * n * world, "api": "mgb_solver_solve_cg_host (pinned host rhs in, solution out)"},
+        "e2e": {"value": e2e_value, "unit": "DoF/s", "ms_per_step": r["ms_e2e"], "h2d_bytes_per_step": 8 * r["n"] * world,
+                "d2h_bytes_per_step": 8 * r["n"] * world, "api": "mgb_solver_solve_cg_host (pinned host rhs in, solution out)"},
+        "exchanges_total": r["exchanges"],
         "gpu_launches": r["launches"], "cg_iterations": r["its"], "cg_reduction_per_iteration": r["rate"],
         "l2_error": r["l2_error"], "total_dofs": total_dofs, "setup_s": r["t_setup"],
         "matvec": matvec, "roofline": roofline, "kernels_finest_level": kernels,

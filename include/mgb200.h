@@ -12,9 +12,16 @@
  *     transfers and level vectors (multigrid_solver.h:709-751).
  *   - "device pointer" = plain CUDA device address (e.g. torch.Tensor.data_ptr()).
  *     "host pointer"   = ordinary host memory; the call copies inside.
- *   - DoF vectors use the library's renumbered layout (columns of 16 x 16-point tiles, z-plane
- *     major inside a column); mgb_solver_lex_map() gives the permutation to the
+ *   - DoF vectors use the library's renumbered layout (z-plane major; inside a plane tile by tile,
+ *     16 x 16 points per tile); mgb_solver_lex_map() gives the permutation to the
  *     lexicographic (x fastest) numbering of the (N_d p + 1)^3 grid.
+ *   - several GPUs (one process per GPU, comm_size > 1): the mesh is cut into z-slabs of whole cell
+ *     layers, one per rank (the role of the p4est partition, poisson_cube/program.cc:193-195).  A
+ *     vector of a distributed level holds the local box = ghost planes below, owned planes, one ghost
+ *     plane on top (mgb_solver_partition()); every call refreshes the ghosts it reads
+ *     (update_ghost_values / compress of LinearAlgebra::distributed::Vector) through NCCL, and
+ *     sums and norms run over the owned planes of all ranks.  Levels too coarse to be cut are held
+ *     (and computed) completely by every rank.
  *   - precision: MGB_F32 selects the V-cycle (float) level operator `matrix[level]`,
  *     MGB_F64 the outer operator `matrix_dp[level]` (multigrid_solver.h:740-745).
  *   - all work is ordered on one CUDA stream per solver; mgb_solver_sync() waits for it.
@@ -57,11 +64,19 @@ typedef struct mgb_options {
   int kernel;              /* MGB_KERNEL_*                                                                           */
   int device;              /* CUDA device ordinal                                                                    */
   int tile_cells;          /* cells per tile and direction (0 = automatic: about 16 points per tile direction)       */
+  int comm_rank;           /* this process' rank, 0 .. comm_size-1  (MPI_Comm_rank of the reference's MPI_COMM_WORLD) */
+  int comm_size;           /* number of ranks = GPUs (0 or 1: one GPU, no communicator)                              */
+  unsigned char comm_id[128]; /* mgb_comm_unique_id() of rank 0, distributed to all ranks by the caller              */
 } mgb_options;
 
 const char *mgb_last_error(void);
 int mgb_version(void);
 void mgb_default_options(mgb_options *opt);
+
+/* Communicator bootstrap (replaces MPI_Init / MPI_COMM_WORLD of poisson_cube/program.cc:704-712): rank 0 calls
+ * this, the caller broadcasts the 128 bytes by its own means (torch.distributed, MPI, a file) and every rank
+ * passes them in mgb_options.comm_id; mgb_solver_create() is then collective over the ranks.             */
+int mgb_comm_unique_id(unsigned char id[128]);
 
 /* MultigridSolver<dim,p,float,double>::MultigridSolver   multigrid_solver.h:100-292 */
 int mgb_solver_create(const mgb_options *opt, mgb_solver *out);
@@ -69,7 +84,14 @@ int mgb_solver_destroy(mgb_solver s);
 int mgb_solver_sync(mgb_solver s);
 
 int mgb_solver_n_levels(mgb_solver s);
-int64_t mgb_solver_n_dofs(mgb_solver s, int level);        /* LaplaceOperator::m()  (MatrixFreeOperators::Base) */
+int64_t mgb_solver_n_dofs(mgb_solver s, int level);        /* length of a vector of this rank (one GPU: LaplaceOperator::m()) */
+/* The z-slab of this rank on one level (Utilities::MPI::Partitioner of the reference's vectors), 12 values:
+ * 0 distributed (0/1), 1 global DoFs = LaplaceOperator::m(), 2 local vector length, 3 first owned index,
+ * 4 number of owned entries, 5 global z-plane of local plane 0, 6 local planes, 7 planes of the level,
+ * 8 ghost cell layers below, 9 ghost plane on top (0/1), 10 first owned global cell layer, 11 one past the last */
+int mgb_solver_partition(mgb_solver s, int level, int64_t info[12]);
+/* ghost exchanges and all-reduces issued so far (0 on one GPU) */
+int64_t mgb_solver_exchange_count(mgb_solver s);
 int mgb_solver_dof_grid(mgb_solver s, int level, int nd[3]);
 int mgb_solver_tile_cells(mgb_solver s, int level);
 /* lex_to_dof[i] = library index of the DoF with lexicographic index i (host pointer, n_dofs entries) */
@@ -158,6 +180,13 @@ int mgb_host_basis(int p, double *S, double *G, double *D, double *M1, double *K
  * laplace_operator.h:226-353, which becomes a closed formula on box meshes); lex_to_dof may be NULL */
 int mgb_host_numbering(int p, const int ncell[3], int tile_cells, int64_t *n_dofs, int *tile_cells_used,
                        int64_t *n_tiles, int64_t *n_constrained, uint32_t *lex_to_dof);
+/* z-slab partition and ghost-exchange plan of `rank` of `n_ranks` on multigrid level `level` of a box with
+ * n_subdivisions coarse cells: info[12] as mgb_solver_partition(); plan[8] = {offset, count} (in values) of
+ * send_up, recv_dn, send_dn, recv_up: update_ghost_values sends send_up to rank+1 (its recv_dn) and send_dn to
+ * rank-1 (its recv_up); compress(add) sends recv_up to rank+1, which adds it to its send_dn range.
+ * lex_to_dof (may be NULL): local vector index of each point of the LOCAL box in lexicographic order     */
+int mgb_host_partition(int p, const int n_subdivisions[3], int level, int tile_cells, int n_ranks, int rank,
+                       int64_t info[12], int64_t plan[8], uint32_t *lex_to_dof);
 
 #ifdef __cplusplus
 }

@@ -44,6 +44,9 @@ class Options(C.Structure):
         ("kernel", C.c_int),
         ("device", C.c_int),
         ("tile_cells", C.c_int),
+        ("comm_rank", C.c_int),
+        ("comm_size", C.c_int),
+        ("comm_id", C.c_ubyte * 128),
     ]
 
 
@@ -61,6 +64,9 @@ SYMBOLS = {
     "mgb_solver_sync": (_i, [_vp]),
     "mgb_solver_n_levels": (_i, [_vp]),
     "mgb_solver_n_dofs": (C.c_int64, [_vp, _i]),
+    "mgb_solver_partition": (_i, [_vp, _i, C.POINTER(C.c_int64)]),
+    "mgb_solver_exchange_count": (C.c_int64, [_vp]),
+    "mgb_comm_unique_id": (_i, [C.POINTER(C.c_ubyte)]),
     "mgb_solver_dof_grid": (_i, [_vp, _i, _ip]),
     "mgb_solver_tile_cells": (_i, [_vp, _i]),
     "mgb_solver_lex_map": (_i, [_vp, _i, C.POINTER(C.c_uint32)]),
@@ -103,6 +109,8 @@ SYMBOLS = {
     "mgb_host_basis": (_i, [_i] + [_dp] * 9),
     "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), _ip, C.POINTER(C.c_int64),
                                 C.POINTER(C.c_int64), C.POINTER(C.c_uint32)]),
+    "mgb_host_partition": (_i, [_i, _ip, _i, _i, _i, _i, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                C.POINTER(C.c_uint32)]),
 }
 
 
@@ -156,6 +164,50 @@ def host_numbering(p, ncell, tile_cells=0, want_map=True):
     return dict(n_dofs=nd.value, tile_cells=cw.value, n_tiles=nt.value, n_constrained=ncon.value, lex_to_dof=lex)
 
 
+PARTITION_KEYS = ("distributed", "n_global", "n_local", "owned_begin", "n_owned", "plane0", "n_planes",
+                  "n_planes_global", "ghost_layers_below", "ghost_plane_top", "layer_begin", "layer_end")
+
+
+def host_partition(p, n_subdivisions, level, n_ranks, rank, tile_cells=0, want_map=False):
+    """z-slab of `rank` on one multigrid level and its ghost-exchange plan (host logic of csrc/numbering.h)."""
+    nsub = (C.c_int * 3)(*n_subdivisions)
+    info = (C.c_int64 * 12)()
+    plan = (C.c_int64 * 8)()
+    _check(lib().mgb_host_partition(p, nsub, level, tile_cells, n_ranks, rank, info, plan, None))
+    out = dict(zip(PARTITION_KEYS, info))
+    for i, k in enumerate(("send_up", "recv_dn", "send_dn", "recv_up")):
+        out[k] = (plan[2 * i], plan[2 * i + 1])
+    if want_map:
+        lex = np.zeros(out["n_local"], dtype=np.uint32)
+        _check(lib().mgb_host_partition(p, nsub, level, tile_cells, n_ranks, rank, info, plan,
+                                        lex.ctypes.data_as(C.POINTER(C.c_uint32))))
+        out["lex_to_dof"] = lex.astype(np.int64)
+    return out
+
+
+def comm_unique_id():
+    """128-byte NCCL id made by rank 0 (mgb_comm_unique_id); the caller distributes it to all ranks."""
+    buf = (C.c_ubyte * 128)()
+    _check(lib().mgb_comm_unique_id(buf))
+    return bytes(buf)
+
+
+def comm_from_torch_distributed():
+    """(rank, size, id) for MultigridSolver(comm=...) from an initialised torch.distributed process group:
+    rank 0 creates the id and broadcasts it (plumbing only; the data path talks NCCL itself)."""
+    import torch
+    import torch.distributed as dist
+    rank, size = dist.get_rank(), dist.get_world_size()
+    if size == 1:
+        return None
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    t = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        t.copy_(torch.frombuffer(bytearray(comm_unique_id()), dtype=torch.uint8))
+    dist.broadcast(t, 0)
+    return rank, size, bytes(t.cpu().numpy().tobytes())
+
+
 class LaplaceOperator:
     """View of ``matrix[level]`` (float) or ``matrix_dp[level]`` (double) of a solver."""
 
@@ -165,17 +217,22 @@ class LaplaceOperator:
         self.dtype = torch.float64 if precision == F64 else torch.float32
 
     def m(self):
-        return self.solver.n_dofs(self.level)
+        """global number of DoFs (MatrixFreeOperators::Base::m)"""
+        return self.solver.partition(self.level)["n_global"]
 
     n = m
 
+    def local_size(self):
+        """length of this rank's vectors: owned planes plus ghost planes (all DoFs on one GPU)"""
+        return self.solver.n_dofs(self.level)
+
     def initialize_dof_vector(self):
         import torch
-        return torch.zeros(self.m(), dtype=self.dtype, device=self.solver.device)
+        return torch.zeros(self.local_size(), dtype=self.dtype, device=self.solver.device)
 
     def _chk(self, *ts):
         for t in ts:
-            if t.dtype != self.dtype or t.numel() != self.m() or not t.is_cuda or not t.is_contiguous():
+            if t.dtype != self.dtype or t.numel() != self.local_size() or not t.is_cuda or not t.is_contiguous():
                 raise MgbError("vector does not match the operator (dtype/size/device)")
 
     def vmult(self, dst, src):
@@ -224,11 +281,13 @@ class LaplaceOperator:
 
 
 class MultigridSolver:
-    """Mixed-precision FMG / CG+V-cycle solver on a refined box mesh (one GPU)."""
+    """Mixed-precision FMG / CG+V-cycle solver on a refined box mesh.  One process per GPU: with
+    ``comm=(rank, size, id)`` (see comm_from_torch_distributed) the mesh is cut into z-slabs and the
+    constructor is collective over the ranks."""
 
     def __init__(self, degree, n_subdivisions, n_refinements, lower=(-0.9,) * 3, upper=(1.0,) * 3,
                  degree_pre=3, degree_post=3, n_cycles=2, problem=PROBLEM_CUBE_SINE,
-                 kernel=KERNEL_AUTO, device=0, tile_cells=0):
+                 kernel=KERNEL_AUTO, device=0, tile_cells=0, comm=None):
         import torch
         if isinstance(n_subdivisions, int):
             n_subdivisions = (n_subdivisions,) * 3
@@ -241,6 +300,11 @@ class MultigridSolver:
         o.upper[:] = list(upper)
         o.degree_pre, o.degree_post, o.n_cycles = degree_pre, degree_post, n_cycles
         o.problem, o.kernel, o.device, o.tile_cells = problem, kernel, device, tile_cells
+        self.rank, self.n_ranks = 0, 1
+        if comm is not None:
+            self.rank, self.n_ranks, cid = comm
+            o.comm_rank, o.comm_size = self.rank, self.n_ranks
+            o.comm_id[:] = list(cid)
         self.h = C.c_void_p()
         self.device = torch.device("cuda", device)
         self.degree = degree
@@ -266,6 +330,15 @@ class MultigridSolver:
 
     def n_dofs(self, level=-1):
         return lib().mgb_solver_n_dofs(self.h, self._l(level))
+
+    def partition(self, level=-1):
+        """z-slab of this rank on one level (see mgb_solver_partition)"""
+        info = (C.c_int64 * 12)()
+        _check(lib().mgb_solver_partition(self.h, self._l(level), info))
+        return dict(zip(PARTITION_KEYS, info))
+
+    def exchange_count(self):
+        return lib().mgb_solver_exchange_count(self.h)
 
     def dof_grid(self, level=-1):
         nd = (C.c_int * 3)()

@@ -231,7 +231,7 @@ namespace mgb
   template <int p, typename T, int MODE>
   __global__ void
   __launch_bounds__(TileCfg<p>::NT, TileMinBlocks<MODE, T>::value)
-    k_apply_tile(const ApplyArgs<T> A, const int layers_per_segment)
+    k_apply_tile(const ApplyArgs<T> A, const int layers_per_segment, const int layer_begin, const int layer_end)
   {
     using C           = TileCfg<p>;
     constexpr int n   = C::n;
@@ -257,8 +257,8 @@ namespace mgb
     const int        gx0 = tx * TW, gy0 = ty * TW;
     const int        wx = tile_width(L, 0, tx), wy = tile_width(L, 1, ty);
     const int        ncz = L.ncell[2], nd2 = L.nd[2];
-    const int        c0 = seg * layers_per_segment;
-    const int        c1 = imin(c0 + layers_per_segment, ncz);
+    const int        c0 = layer_begin + seg * layers_per_segment;
+    const int        c1 = imin(c0 + layers_per_segment, layer_end);
     const bool       plain = A.read_plain != 0;
 
     // ---- per-thread source points (fixed over the planes): running pointer, plane stride, copy size
@@ -484,7 +484,7 @@ namespace mgb
         Pz[0] = Pz[p];
         Qz[0] = Qz[p];
       }
-    if (c1 == ncz && owner)
+    if (c1 == ncz && owner && !L.ztop) // the top plane of the level (a ghost on all but the last z-slab)
       {
         T y[n];
         y[0] = carry;
@@ -508,7 +508,12 @@ namespace mgb
         first = false;
       }
     const int ntiles = A.L.nt[0] * A.L.nt[1];
-    const int ncz    = A.L.ncell[2];
+    // cell layers of this launch: by default all owned ones (the ghost layer below only feeds the carry)
+    const int l0  = A.layer_begin >= 0 ? A.layer_begin : A.L.zg;
+    const int l1  = A.layer_end >= 0 ? A.layer_end : A.L.ncell[2];
+    const int ncz = l1 - l0;
+    if (ncz <= 0)
+      return;
     // enough blocks for several waves on 148 SMs, but at least 4 cell layers per segment
     int nseg = (148 * 8 + ntiles - 1) / ntiles;
     if (nseg > ncz / 4)
@@ -517,7 +522,7 @@ namespace mgb
       nseg = 1;
     const int lps = (ncz + nseg - 1) / nseg;
     nseg          = (ncz + lps - 1) / lps;
-    k_apply_tile<p, T, MODE><<<ntiles * nseg, C::NT, smem, stream>>>(A, lps);
+    k_apply_tile<p, T, MODE><<<ntiles * nseg, C::NT, smem, stream>>>(A, lps, l0, l1);
   }
 
   template <int p, typename T>

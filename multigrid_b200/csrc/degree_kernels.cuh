@@ -538,6 +538,8 @@ namespace mgb
     const uint32_t    cell = blockIdx.x;
     int               cx, cy, cz;
     cell_coords(A.L, cell, cx, cy, cz);
+    if (cz < A.L.zg)
+      return; // ghost layer of a z-slab: integrated by the rank below
     for (int l = threadIdx.x; l < n3; l += blockDim.x)
       {
         bool           con;

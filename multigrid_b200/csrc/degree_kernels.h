@@ -32,6 +32,7 @@ namespace mgb
     int       mode;
     int       read_plain;    // 1: do not zero constrained entries on read (compute_residual)
     int       first_chebyshev; // 1: x_{k-1} = 0 implied (iteration_index == 1)
+    int       layer_begin, layer_end; // tile kernel: local cell layers of this launch (-1: all owned layers)
   };
 
   template <typename T>
@@ -42,6 +43,10 @@ namespace mgb
     T        *dst;
     int       mode;        // 0 prolongate (overwrite), 1 prolongate_and_add, 2 restrict_and_add
     int       constrained; // MGTransferMatrixFree::initialize_constraints called
+    // z-slabs (tile kernels): the parent layers [cz_begin, cz_end) in the local numbering of the coarse
+    // level are processed; the children of local coarse plane 0 start at local fine plane `f_shift`
+    // (may be negative), and `close_top` says that the last layer also owns the top fine plane
+    int cz_begin, cz_end, f_shift, close_top;
   };
 
   template <typename T>

@@ -43,7 +43,28 @@ namespace mgb
     uint32_t n_cells, n_dofs;
     uint32_t dirichlet; // bit 2d: low face of direction d is Dirichlet, bit 2d+1: high face
     double   lo[3], h[3];
+    // z-slab of a level distributed over several GPUs (all zero on one GPU and on replicated levels):
+    // ncell[2], nd[2], n_dofs, lo[2] and the z bits of `dirichlet` describe the LOCAL box, which is the
+    // owned cell layers plus `zg` ghost layers below; the planes [0, zg p) are copies of the last planes
+    // of the rank below, and with `ztop` the plane nd[2]-1 is a copy of the first owned plane of the rank
+    // above (the role of the ghost range of LinearAlgebra::distributed::Vector in the reference)
+    int      zg;      // ghost cell layers below (0 or 1)
+    int      ztop;    // 1: the top plane is a ghost
+    int      gk0;     // global index of the local plane 0
+    int      nd2_all; // planes of the whole level
   };
+
+  // first owned plane, one past the last owned plane
+  MGB_HD int
+  owned_plane_begin(const LevelDesc &L)
+  {
+    return L.zg * L.p;
+  }
+  MGB_HD int
+  owned_plane_end(const LevelDesc &L)
+  {
+    return L.nd[2] - L.ztop;
+  }
 
   MGB_HD int
   imin(const int a, const int b)

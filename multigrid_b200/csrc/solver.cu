@@ -7,6 +7,8 @@
 //
 // There is no CPU fallback: every numerical step below is a kernel launch on the solver's stream.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h> // types and enumerators only: the library is bound at run time (see Nccl below)
 
 #include <algorithm>
 #include <array>
@@ -54,10 +56,68 @@ namespace mgb
     throw std::runtime_error("polynomial degree must be between 1 and 8");
   }
 
+  // ------------------------------------------------------------------ NCCL (several GPUs only)
+  // The ghost exchange between z-slabs and the scalar all-reduces go through NCCL over NVLink.  The
+  // library is bound with dlopen on first use, so one GPU needs no NCCL at all and a host process
+  // that already carries a libnccl.so.2 (torch does) shares it.
+  struct Nccl
+  {
+    void *handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *)                                                       = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int)                                = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t)                                                           = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                              cudaStream_t)                                                           = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t)         = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t)               = nullptr;
+    ncclResult_t (*GroupStart)()                                                                      = nullptr;
+    ncclResult_t (*GroupEnd)()                                                                        = nullptr;
+    const char *(*GetErrorString)(ncclResult_t)                                                       = nullptr;
+
+    static Nccl &
+    get()
+    {
+      static Nccl n;
+      if (n.handle)
+        return n;
+      const char *names[] = {getenv("MGB200_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+      for (const char *name : names)
+        if (name && (n.handle = dlopen(name, RTLD_NOW | RTLD_GLOBAL)))
+          break;
+      if (!n.handle)
+        throw std::runtime_error("more than one GPU requested but libnccl.so.2 cannot be loaded");
+      auto sym = [&](const char *name) {
+        void *f = dlsym(n.handle, name);
+        if (!f)
+          throw std::runtime_error(std::string("NCCL symbol missing: ") + name);
+        return f;
+      };
+      n.GetUniqueId    = reinterpret_cast<decltype(n.GetUniqueId)>(sym("ncclGetUniqueId"));
+      n.CommInitRank   = reinterpret_cast<decltype(n.CommInitRank)>(sym("ncclCommInitRank"));
+      n.CommDestroy    = reinterpret_cast<decltype(n.CommDestroy)>(sym("ncclCommDestroy"));
+      n.AllReduce      = reinterpret_cast<decltype(n.AllReduce)>(sym("ncclAllReduce"));
+      n.Send           = reinterpret_cast<decltype(n.Send)>(sym("ncclSend"));
+      n.Recv           = reinterpret_cast<decltype(n.Recv)>(sym("ncclRecv"));
+      n.GroupStart     = reinterpret_cast<decltype(n.GroupStart)>(sym("ncclGroupStart"));
+      n.GroupEnd       = reinterpret_cast<decltype(n.GroupEnd)>(sym("ncclGroupEnd"));
+      n.GetErrorString = reinterpret_cast<decltype(n.GetErrorString)>(sym("ncclGetErrorString"));
+      return n;
+    }
+    void
+    check(const ncclResult_t r, const char *what)
+    {
+      if (r != ncclSuccess)
+        throw std::runtime_error(std::string("NCCL error in ") + what + ": " + GetErrorString(r));
+    }
+  };
+
   // ------------------------------------------------------------------ context
   struct Ctx
   {
     int          device   = 0;
+    int          rank = 0, n_ranks = 1; // z-slab decomposition over the GPUs of one node
+    ncclComm_t   comm     = nullptr;
+    int64_t      exchanges = 0;          // ghost exchanges + all-reduces issued so far
     cudaStream_t stream   = nullptr;
     int64_t      launches = 0;
     double      *scal_dev = nullptr; // 16 device scalars for reductions
@@ -146,8 +206,34 @@ namespace mgb
       MGB_CUDA_CHECK(cudaMallocHost(&scal_host, 16 * sizeof(double)));
     }
     void
+    init_comm(const int rank_, const int n_ranks_, const unsigned char *id)
+    {
+      rank    = rank_;
+      n_ranks = n_ranks_;
+      if (n_ranks <= 1)
+        return;
+      if (rank < 0 || rank >= n_ranks)
+        throw std::runtime_error("invalid rank");
+      Nccl        &n = Nccl::get();
+      ncclUniqueId uid;
+      static_assert(sizeof(uid) == 128, "ncclUniqueId is 128 bytes");
+      std::memcpy(&uid, id, sizeof(uid));
+      n.check(n.CommInitRank(&comm, n_ranks, uid, rank), "ncclCommInitRank");
+    }
+    // sum of `count` doubles over the ranks, in place, ordered on the solver stream
+    void
+    all_reduce_sum(double *dev, const int count)
+    {
+      Nccl &n = Nccl::get();
+      n.check(n.AllReduce(dev, dev, count, ncclDouble, ncclSum, comm, stream), "ncclAllReduce");
+      ++exchanges;
+    }
+    void
     destroy()
     {
+      if (comm)
+        Nccl::get().CommDestroy(comm);
+      comm = nullptr;
       if (scal_dev)
         cudaFree(scal_dev);
       if (scal_host)
@@ -220,6 +306,13 @@ namespace mgb
     DVec()   = default;
     DVec(const DVec &) = delete;
     DVec &operator=(const DVec &) = delete;
+    DVec(DVec &&o) noexcept
+      : p(o.p)
+      , n(o.n)
+    {
+      o.p = nullptr;
+      o.n = 0;
+    }
     ~DVec() { release(); }
     void
     alloc(const size_t count, cudaStream_t stream)
@@ -277,14 +370,14 @@ namespace mgb
   // up to 4 simultaneous sums of products; warp-shuffle + shared reduction, one red.add.f64 per block
   template <int NS, typename F>
   __global__ void
-  k_reduce(const size_t n, F f, double *out)
+  k_reduce(const size_t off, const size_t n, F f, double *out)
   {
     double acc[NS];
 #pragma unroll
     for (int s = 0; s < NS; ++s)
       acc[s] = 0;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-      f(i, acc);
+      f(i + off, acc);
     __shared__ double red[NS][8];
 #pragma unroll
     for (int s = 0; s < NS; ++s)
@@ -305,14 +398,37 @@ namespace mgb
       }
   }
 
+  // The entries of a vector that enter sums: on a distributed level the owned planes of the z-slab
+  // (one contiguous range), summed over the ranks; otherwise the whole vector.  Element-wise updates
+  // (foreach) run over all local entries instead: ghost entries are never trusted, every consumer
+  // (operator apply, prolongation) refreshes them first.
+  struct Span
+  {
+    size_t off = 0, n = 0;
+    bool   all_ranks = false;
+    Span() = default;
+    Span(const size_t count)
+      : off(0)
+      , n(count)
+      , all_ranks(false)
+    {}
+    Span(const size_t o, const size_t count, const bool ar)
+      : off(o)
+      , n(count)
+      , all_ranks(ar)
+    {}
+  };
+
   // returns the sums on the host (synchronises the stream)
   template <int NS, typename F>
   void
-  reduce(Ctx &ctx, const size_t n, F f, double *result)
+  reduce(Ctx &ctx, const Span sp, F f, double *result)
   {
     MGB_CUDA_CHECK(cudaMemsetAsync(ctx.scal_dev, 0, NS * sizeof(double), ctx.stream));
-    k_reduce<NS><<<grid_for(n), 256, 0, ctx.stream>>>(n, f, ctx.scal_dev);
+    k_reduce<NS><<<grid_for(sp.n), 256, 0, ctx.stream>>>(sp.off, sp.n, f, ctx.scal_dev);
     ctx.check_launch();
+    if (sp.all_ranks)
+      ctx.all_reduce_sum(ctx.scal_dev, NS);
     MGB_CUDA_CHECK(cudaMemcpyAsync(
       ctx.scal_host, ctx.scal_dev, NS * sizeof(double), cudaMemcpyDeviceToHost, ctx.stream));
     ctx.sync();
@@ -322,11 +438,11 @@ namespace mgb
 
   template <typename A, typename B>
   double
-  dot(Ctx &ctx, const A *a, const B *b, const size_t n)
+  dot(Ctx &ctx, const A *a, const B *b, const Span sp)
   {
     double r;
     reduce<1>(
-      ctx, n, [=] __device__(size_t i, double *acc) { acc[0] += (double)a[i] * (double)b[i]; }, &r);
+      ctx, sp, [=] __device__(size_t i, double *acc) { acc[0] += (double)a[i] * (double)b[i]; }, &r);
     return r;
   }
 
@@ -342,17 +458,80 @@ namespace mgb
   {
     HostLevel      host;
     LevelDesc      d;
+    Slab           slab;
+    ExchangePlan   plan;
+    Ctx           *ctx   = nullptr;
     int            index = 0; // multigrid level number
+    uint64_t       n_global = 0; // DoFs of the whole level (m() of the operator)
     DVec<uint32_t> constrained;
+    DVec<double>   plane_buf; // one z-plane: receive buffer of compress_add()
 
     void
-    upload(cudaStream_t stream)
+    upload(Ctx &c)
     {
-      constrained.alloc(host.constrained.size(), stream);
+      ctx = &c;
+      constrained.alloc(host.constrained.size(), c.stream);
       if (constrained.n)
-        MGB_CUDA_CHECK(cudaMemcpyAsync(constrained.p, host.constrained.data(), constrained.n * 4, cudaMemcpyHostToDevice, stream));
-      MGB_CUDA_CHECK(cudaStreamSynchronize(stream));
-      d = host.d;
+        MGB_CUDA_CHECK(cudaMemcpyAsync(constrained.p, host.constrained.data(), constrained.n * 4, cudaMemcpyHostToDevice, c.stream));
+      MGB_CUDA_CHECK(cudaStreamSynchronize(c.stream));
+      d        = host.d;
+      plan     = make_exchange_plan(d);
+      n_global = (uint64_t)d.nd[0] * d.nd[1] * d.nd2_all;
+      if (slab.distributed)
+        plane_buf.alloc(plane_pitch(d), c.stream);
+    }
+
+    // the entries that enter dot products and norms
+    Span owned() const { return Span(plan.owned[0], plan.owned[1], slab.distributed); }
+
+    // LinearAlgebra::distributed::Vector::update_ghost_values (laplace_operator.h:590,812): the p planes
+    // below the slab come from the rank below, the plane on top from the rank above; one NCCL group of
+    // at most two sends and two receives on the solver stream, contiguous ranges thanks to the
+    // plane-major numbering (level.h)
+    template <typename T>
+    void
+    update_ghosts(T *v) const
+    {
+      if (!slab.distributed)
+        return;
+      Nccl &n = Nccl::get();
+      n.check(n.GroupStart(), "ncclGroupStart");
+      if (d.ztop)
+        {
+          n.check(n.Send(v + plan.send_up[0], plan.send_up[1] * sizeof(T), ncclInt8, ctx->rank + 1, ctx->comm, ctx->stream), "ncclSend");
+          n.check(n.Recv(v + plan.recv_up[0], plan.recv_up[1] * sizeof(T), ncclInt8, ctx->rank + 1, ctx->comm, ctx->stream), "ncclRecv");
+        }
+      if (d.zg)
+        {
+          n.check(n.Send(v + plan.send_dn[0], plan.send_dn[1] * sizeof(T), ncclInt8, ctx->rank - 1, ctx->comm, ctx->stream), "ncclSend");
+          n.check(n.Recv(v + plan.recv_dn[0], plan.recv_dn[1] * sizeof(T), ncclInt8, ctx->rank - 1, ctx->comm, ctx->stream), "ncclRecv");
+        }
+      n.check(n.GroupEnd(), "ncclGroupEnd");
+      ++ctx->exchanges;
+    }
+
+    // Vector::compress(VectorOperation::add) for the one ghost plane that is ever written (the top plane,
+    // by the restriction): it is added to the first owned plane of the rank above
+    template <typename T>
+    void
+    compress_add(T *v)
+    {
+      if (!slab.distributed)
+        return;
+      Nccl &n   = Nccl::get();
+      T    *buf = reinterpret_cast<T *>(plane_buf.p);
+      n.check(n.GroupStart(), "ncclGroupStart");
+      if (d.ztop)
+        n.check(n.Send(v + plan.recv_up[0], plan.recv_up[1] * sizeof(T), ncclInt8, ctx->rank + 1, ctx->comm, ctx->stream), "ncclSend");
+      if (d.zg)
+        n.check(n.Recv(buf, plan.send_dn[1] * sizeof(T), ncclInt8, ctx->rank - 1, ctx->comm, ctx->stream), "ncclRecv");
+      n.check(n.GroupEnd(), "ncclGroupEnd");
+      ++ctx->exchanges;
+      if (d.zg)
+        {
+          T *own = v + plan.send_dn[0];
+          foreach (*ctx, plan.send_dn[1], [=] __device__(size_t i) { own[i] += buf[i]; });
+        }
     }
   };
 
@@ -407,7 +586,8 @@ namespace mgb
     DVec<T>              inverse_diagonal;
     DVec<T>              tmp;          // full-length scratch (general kernel epilogues)
 
-    size_t m() const { return level->d.n_dofs; }
+    size_t m() const { return level->d.n_dofs; }          // local vector length (owned + ghost planes)
+    size_t m_global() const { return level->n_global; } // MatrixFreeOperators::Base::m()
 
     void
     initialize(Ctx &c, Level &l, const Basis &basis, const int coefficient_fn)
@@ -482,6 +662,7 @@ namespace mgb
       A.mode            = APPLY_ADD;
       A.read_plain      = 0;
       A.first_chebyshev = 0;
+      A.layer_begin = A.layer_end = -1;
     }
 
     int
@@ -526,6 +707,9 @@ namespace mgb
       A.f2              = f2;
       A.first_chebyshev = first;
       A.read_plain      = read_plain;
+      // update_ghost_values of the source (laplace_operator.h:590): like the reference's vmult, this
+      // mutates the ghost range of the const source vector
+      level->update_ghosts(const_cast<T *>(src));
       if (use_cartesian())
         {
           // streaming tile kernel: the vector operation is fused, every DoF is written once
@@ -575,7 +759,7 @@ namespace mgb
     {
       apply(APPLY_SET, dst, src);
       ScopedRange range(*ctx, level->index, RK_CG_VEC);
-      *result = dot(*ctx, src, dst, m());
+      *result = dot(*ctx, src, dst, level->owned());
     }
     void vmult_add(T *dst, const T *src) { apply(APPLY_ADD, dst, src); }
     void vmult_residual(const T *rhs, const T *lhs, T *residual) { apply(APPLY_RESIDUAL, residual, lhs, rhs); }
@@ -597,7 +781,7 @@ namespace mgb
       apply(APPLY_ADD, q, pp);
       reduce<4>(
         *ctx,
-        N,
+        level->owned(),
         [=] __device__(size_t i, double *acc) {
           const double qi = q[i], pi = pp[i], ri = r[i];
           acc[0] += qi * pi;
@@ -629,6 +813,9 @@ namespace mgb
       const uint32_t *clist = level->constrained.p;
       foreach (*ctx, level->constrained.n, [=] __device__(size_t i) { dg[clist[i]] = T(1); });
       foreach (*ctx, N, [=] __device__(size_t i) { dg[i] = T(1) / dg[i]; });
+      // the cell loop above ran over the local box: the owned planes are complete (their cells are the
+      // owned layers and the ghost layer), the ghost planes are not
+      level->update_ghosts(dg);
     }
   };
 
@@ -703,11 +890,12 @@ namespace mgb
       g.alloc(N, c.stream);
       h.alloc(N, c.stream);
       d.alloc(N, c.stream);
-      const LevelDesc L  = op.level->d;
+      const LevelDesc L   = op.level->d;
+      const Span      own = op.level->owned();
       T              *gp = g.p, *hp = h.p, *dp = d.p;
       const T        *P = op.inverse_diagonal.p;
       patch_points(c, L, [=] __device__(uint32_t dof, bool con, int gi, int gj, int gk) {
-        const size_t lex = ((size_t)gk * L.nd[1] + gj) * L.nd[0] + gi;
+        const size_t lex = ((size_t)(gk + L.gk0) * L.nd[1] + gj) * L.nd[0] + gi;
         gp[dof]          = con ? T(0) : (T)(lex % 11);
       });
       // mean over all entries before constraining (cheap closed form avoided: do it on the device)
@@ -718,13 +906,13 @@ namespace mgb
         full.alloc(N, c.stream);
         T *fp = full.p;
         patch_points(c, L, [=] __device__(uint32_t dof, bool, int gi, int gj, int gk) {
-          const size_t lex = ((size_t)gk * L.nd[1] + gj) * L.nd[0] + gi;
+          const size_t lex = ((size_t)(gk + L.gk0) * L.nd[1] + gj) * L.nd[0] + gi;
           fp[dof]          = (T)(lex % 11);
         });
         reduce<1>(
-          c, N, [=] __device__(size_t i, double *acc) { acc[0] += (double)fp[i]; }, &sum);
+          c, own, [=] __device__(size_t i, double *acc) { acc[0] += (double)fp[i]; }, &sum);
       }
-      const T mean = (T)(sum / N);
+      const T mean = (T)(sum / op.m_global());
       // g = -(pattern - mean) with constrained entries zero
       foreach (c, N, [=] __device__(size_t i) { gp[i] = -(gp[i] - mean); });
       {
@@ -732,7 +920,7 @@ namespace mgb
         foreach (c, op.level->constrained.n, [=] __device__(size_t i) { gp[clist[i]] = T(0); });
       }
       std::vector<double> diag, off;
-      double              res = std::sqrt(dot(c, gp, gp, N));
+      double              res = std::sqrt(dot(c, gp, gp, own));
       cg_iterations           = 0;
       if (res > 1e-10 && eig_cg_n_iterations > 0)
         {
@@ -740,15 +928,15 @@ namespace mgb
             hp[i] = P[i] * gp[i];
             dp[i] = -hp[i];
           });
-          double gh = dot(c, gp, hp, N);
+          double gh = dot(c, gp, hp, own);
           double alpha_old = 0, beta_old = 0;
           for (unsigned int it = 1;; ++it)
             {
               op.vmult(hp, dp);
-              const double alpha = gh / dot(c, dp, hp, N);
+              const double alpha = gh / dot(c, dp, hp, own);
               const T      al    = (T)alpha;
               foreach (c, N, [=] __device__(size_t i) { gp[i] += al * hp[i]; });
-              res = std::sqrt(dot(c, gp, gp, N));
+              res = std::sqrt(dot(c, gp, gp, own));
               if (it == 1)
                 diag.push_back(1. / alpha);
               else
@@ -760,7 +948,7 @@ namespace mgb
               if (it >= eig_cg_n_iterations || res <= 1e-10)
                 break;
               foreach (c, N, [=] __device__(size_t i) { hp[i] = P[i] * gp[i]; });
-              const double gh_new = dot(c, gp, hp, N);
+              const double gh_new = dot(c, gp, hp, own);
               const double beta   = gh_new / gh;
               gh                  = gh_new;
               const T be          = (T)beta;
@@ -845,6 +1033,8 @@ namespace mgb
     bool                 constrained = false;
     int                  kernel      = MGB_KERNEL_AUTO;
 
+    DVec<T>              partial; // restriction onto a replicated coarse level: this rank's share
+
     void
     run(const int mode, T *dst, const T *src)
     {
@@ -855,17 +1045,67 @@ namespace mgb
       A.dst         = dst;
       A.mode        = mode;
       A.constrained = constrained;
+      // z-slabs: this rank handles the parents of its owned fine layers.  Local coarse plane 0 is the
+      // global coarse plane gk0_c, whose children start at the global fine plane 2 gk0_c.
+      const bool fd = fine->slab.distributed, cd = coarse->slab.distributed;
+      A.cz_begin    = cd ? coarse->d.zg : (fd ? fine->slab.c0 / 2 : 0);
+      A.cz_end      = cd || !fd ? coarse->d.ncell[2] : fine->slab.c1 / 2;
+      A.f_shift     = 2 * coarse->d.gk0 - fine->d.gk0;
+      A.close_top   = fine->d.ztop ? 0 : 1;
       // streaming tile kernels are compiled for the default tile width of the degree
       const bool tiles = fine->d.CW == choose_tile_cells(fine->d.p, 0) && kernel == MGB_KERNEL_AUTO;
+      if (!tiles && fd)
+        throw std::runtime_error("the cell-wise transfer kernel does not support z-slabs; use the default tile width");
       if (sizeof(T) == 8)
         (tiles ? dk->transfer_tile_d : dk->transfer_d)(reinterpret_cast<const TransferArgs<double> &>(A), ctx->stream);
       else
         (tiles ? dk->transfer_tile_f : dk->transfer_f)(reinterpret_cast<const TransferArgs<float> &>(A), ctx->stream);
       ctx->check_launch();
     }
-    void prolongate(T *f, const T *c) { run(0, f, c); }
-    void prolongate_and_add(T *f, const T *c) { run(1, f, c); }
-    void restrict_and_add(T *c, const T *f) { run(2, c, f); }
+    // the coarse plane on top of the slab is read: update_ghost_values of the coarse vector first
+    void
+    prolongate(T *f, const T *c)
+    {
+      coarse->update_ghosts(const_cast<T *>(c));
+      run(0, f, c);
+    }
+    void
+    prolongate_and_add(T *f, const T *c)
+    {
+      coarse->update_ghosts(const_cast<T *>(c));
+      run(1, f, c);
+    }
+    // every rank restricts its owned fine planes; what lands on the coarse plane on top of the slab
+    // belongs to the rank above (compress(add)), and a replicated coarse level gets the sum over all ranks
+    void
+    restrict_and_add(T *c, const T *f)
+    {
+      if (!fine->slab.distributed)
+        {
+          run(2, c, f);
+          return;
+        }
+      if (coarse->slab.distributed)
+        {
+          if (coarse->d.ztop)
+            MGB_CUDA_CHECK(cudaMemsetAsync(c + coarse->plan.recv_up[0], 0, coarse->plan.recv_up[1] * sizeof(T), ctx->stream));
+          run(2, c, f);
+          coarse->compress_add(c);
+          return;
+        }
+      const size_t nc = coarse->d.n_dofs;
+      if (partial.n != nc)
+        partial.alloc(nc, ctx->stream);
+      else
+        MGB_CUDA_CHECK(cudaMemsetAsync(partial.p, 0, nc * sizeof(T), ctx->stream));
+      run(2, partial.p, f);
+      Nccl &n = Nccl::get();
+      n.check(n.AllReduce(partial.p, partial.p, nc, sizeof(T) == 8 ? ncclDouble : ncclFloat, ncclSum, ctx->comm, ctx->stream),
+              "ncclAllReduce");
+      ++ctx->exchanges;
+      const T *part = partial.p;
+      foreach (*ctx, nc, [=] __device__(size_t i) { c[i] += part[i]; });
+    }
   };
 
   // ------------------------------------------------------------------ solver
@@ -905,6 +1145,7 @@ namespace mgb
           o.n_subdivisions[2] < 1)
         throw std::runtime_error("invalid mesh description");
       ctx.init(o.device);
+      ctx.init_comm(o.comm_rank, o.comm_size < 1 ? 1 : o.comm_size, o.comm_id);
       basis = make_basis(o.degree);
       degree_kernels(o.degree).init(basis);
       if (o.problem == MGB_PROBLEM_CUBE_SINE)
@@ -934,8 +1175,12 @@ namespace mgb
           levels.emplace_back(new Level());
           Level &lv = *levels.back();
           lv.index  = l;
-          build_box_level(o.degree, nc, choose_tile_cells(o.degree, o.tile_cells), o.lower, o.upper, 0x3fu, lv.host);
-          lv.upload(ctx.stream);
+          // thin slabs cost a ghost exchange per operator apply and save next to nothing: by default a
+          // level is cut only when every rank gets at least two cell layers
+          const char *ml = getenv("MGB200_MIN_SLAB_LAYERS");
+          lv.slab = make_slab(o.n_subdivisions[2], l, ctx.n_ranks, ctx.rank, ml ? std::max(1, atoi(ml)) : 2);
+          build_slab_level(o.degree, nc, choose_tile_cells(o.degree, o.tile_cells), o.lower, o.upper, 0x3fu, lv.slab, lv.host);
+          lv.upload(ctx);
           const size_t N = lv.d.n_dofs;
           matrix.emplace_back(new LaplaceOperator<float>());
           matrix_dp.emplace_back(new LaplaceOperator<double>());
@@ -991,6 +1236,7 @@ namespace mgb
           R.fn_id = fn_rhs;
           dk->rhs_values(R, ctx.stream);
           ctx.check_launch();
+          levels[l]->update_ghosts(rhs[l]->p); // the cell loop completed the owned planes only
           MGB_CUDA_CHECK(cudaMemsetAsync(residual[l]->p, 0, N * sizeof(double), ctx.stream));
         }
       // smoothers (multigrid_solver.h:268-289)
@@ -1008,7 +1254,7 @@ namespace mgb
             {
               s.smoothing_range     = 1e-3;
               s.degree              = Chebyshev<float>::invalid_degree;
-              s.eig_cg_n_iterations = (unsigned int)matrix[0]->m();
+              s.eig_cg_n_iterations = (unsigned int)matrix[0]->m_global();
             }
           matrix[l]->compute_diagonal();
           s.initialize(ctx, *matrix[l], basis);
@@ -1039,6 +1285,7 @@ namespace mgb
     compute_l2_error(const int level)
     {
       set_boundary_values(level, false);
+      levels[level]->update_ghosts(solution[level]->p);
       MGB_CUDA_CHECK(cudaMemsetAsync(ctx.scal_dev, 0, 2 * sizeof(double), ctx.stream));
       ErrorArgs E;
       E.L     = levels[level]->d;
@@ -1047,6 +1294,8 @@ namespace mgb
       E.accum = ctx.scal_dev;
       degree_kernels(opt.degree).l2_error(E, ctx.stream);
       ctx.check_launch();
+      if (levels[level]->slab.distributed)
+        ctx.all_reduce_sum(ctx.scal_dev, 2);
       MGB_CUDA_CHECK(cudaMemcpyAsync(ctx.scal_host, ctx.scal_dev, 2 * sizeof(double), cudaMemcpyDeviceToHost, ctx.stream));
       ctx.sync();
       return std::sqrt(ctx.scal_host[0] / ctx.scal_host[1]);
@@ -1114,7 +1363,7 @@ namespace mgb
           convert(ctx, defect[level]->p, residual[level]->p, N);
           if (do_analyze)
             {
-              init_residual = std::sqrt(dot(ctx, residual[level]->p, residual[level]->p, N));
+              init_residual = std::sqrt(dot(ctx, residual[level]->p, residual[level]->p, levels[level]->owned()));
               if (trace)
                 trace[level * 4 + 1] = init_residual;
             }
@@ -1131,7 +1380,7 @@ namespace mgb
               double       *res = residual[level]->p;
               const double *b   = rhs[level]->p;
               foreach (ctx, N, [=] __device__(size_t i) { res[i] = b[i] - res[i]; });
-              const double res_norm = std::sqrt(dot(ctx, res, res, N));
+              const double res_norm = std::sqrt(dot(ctx, res, res, levels[level]->owned()));
               reduction_rate        = std::pow(res_norm / init_residual, 1. / opt.n_cycles);
               if (trace)
                 {
@@ -1172,6 +1421,7 @@ namespace mgb
       // V-cycle, and the preconditioned residual h = double(solution_update) is never materialised.
       const int     L = n_levels - 1;
       const size_t  N = levels[L]->d.n_dofs;
+      const Span    own = levels[L]->owned();
       double       *x = solution[L]->p, *g = cg_g.p, *h = cg_h.p, *d = cg_d.p;
       const double *b = rhs[L]->p;
       float        *def = defect[L]->p;
@@ -1182,7 +1432,7 @@ namespace mgb
         ScopedRange range(ctx, L, RK_CG_VEC);
         reduce<1>(
           ctx,
-          N,
+          own,
           [=] __device__(size_t i, double *acc) {
             const double gi = -b[i];
             g[i]            = gi;
@@ -1206,7 +1456,7 @@ namespace mgb
                 ScopedRange range(ctx, L, RK_CG_VEC);
                 double      gh_new;
                 reduce<1>(
-                  ctx, N, [=] __device__(size_t i, double *acc) { acc[0] += g[i] * (double)upd[i]; }, &gh_new);
+                  ctx, own, [=] __device__(size_t i, double *acc) { acc[0] += g[i] * (double)upd[i]; }, &gh_new);
                 if (it == 0)
                   foreach (ctx, N, [=] __device__(size_t i) { d[i] = -(double)upd[i]; });
                 else
@@ -1224,7 +1474,7 @@ namespace mgb
                 const double alpha = gh / dh;
                 reduce<1>(
                   ctx,
-                  N,
+                  own,
                   [=] __device__(size_t i, double *acc) {
                     x[i] += alpha * d[i];
                     const double gi = g[i] + alpha * h[i];
@@ -1271,6 +1521,26 @@ struct mgb_solver_t
   }                                                \
   return 0;
 
+template <typename LevelLike>
+static void
+fill_partition_info(const LevelLike &lv, int64_t info[12])
+{
+  const LevelDesc &d = lv.d;
+  const ExchangePlan e = make_exchange_plan(d);
+  info[0]  = lv.slab.distributed;
+  info[1]  = (int64_t)d.nd[0] * d.nd[1] * d.nd2_all;
+  info[2]  = d.n_dofs;
+  info[3]  = e.owned[0];
+  info[4]  = e.owned[1];
+  info[5]  = d.gk0;
+  info[6]  = d.nd[2];
+  info[7]  = d.nd2_all;
+  info[8]  = d.zg;
+  info[9]  = d.ztop;
+  info[10] = lv.slab.c0;
+  info[11] = lv.slab.c1;
+}
+
 static MultigridSolver &
 S(mgb_solver s)
 {
@@ -1298,7 +1568,8 @@ extern "C"
   mgb_default_options(mgb_options *o)
   {
     std::memset(o, 0, sizeof(*o));
-    o->degree = 4;
+    o->degree    = 4;
+    o->comm_size = 1;
     for (int d = 0; d < 3; ++d)
       {
         o->n_subdivisions[d] = 1;
@@ -1367,6 +1638,32 @@ extern "C"
         g_last_error = e.what();
         return -1;
       }
+  }
+
+  int
+  mgb_solver_partition(mgb_solver s, int level, int64_t info[12])
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    fill_partition_info(*m.levels[check_level(m, level)], info);
+    MGB_CATCH
+  }
+
+  int64_t
+  mgb_solver_exchange_count(mgb_solver s)
+  {
+    return s && s->impl ? s->impl->ctx.exchanges : -1;
+  }
+
+  int
+  mgb_comm_unique_id(unsigned char id[128])
+  {
+    MGB_TRY
+    Nccl        &n = Nccl::get();
+    ncclUniqueId uid;
+    n.check(n.GetUniqueId(&uid), "ncclGetUniqueId");
+    std::memcpy(id, &uid, 128);
+    MGB_CATCH
   }
 
   int
@@ -1908,6 +2205,41 @@ extern "C"
     *n_constrained   = (int64_t)lvl.constrained.size();
     if (lex_to_dof)
       build_lex_map(lvl, lex_to_dof);
+    MGB_CATCH
+  }
+
+  int
+  mgb_host_partition(int p, const int n_subdivisions[3], int level, int tile_cells, int n_ranks, int rank,
+                     int64_t info[12], int64_t plan[8], uint32_t *lex_to_dof)
+  {
+    MGB_TRY
+    if (p < 1 || p > 8)
+      throw std::runtime_error("polynomial degree must be between 1 and 8");
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks || level < 0 || level > 20)
+      throw std::runtime_error("invalid rank or level");
+    struct
+    {
+      HostLevel host;
+      LevelDesc d;
+      Slab      slab;
+    } lv;
+    int nc[3];
+    for (int c = 0; c < 3; ++c)
+      nc[c] = n_subdivisions[c] << level;
+    const double lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
+    lv.slab            = make_slab(n_subdivisions[2], level, n_ranks, rank);
+    build_slab_level(p, nc, choose_tile_cells(p, tile_cells), lo, hi, 0x3fu, lv.slab, lv.host);
+    lv.d = lv.host.d;
+    fill_partition_info(lv, info);
+    const ExchangePlan e = make_exchange_plan(lv.d);
+    const uint64_t    *r[4] = {e.send_up, e.recv_dn, e.send_dn, e.recv_up};
+    for (int i = 0; i < 4; ++i)
+      {
+        plan[2 * i]     = r[i][0];
+        plan[2 * i + 1] = r[i][1];
+      }
+    if (lex_to_dof)
+      build_lex_map(lv.host, lex_to_dof);
     MGB_CATCH
   }
 }

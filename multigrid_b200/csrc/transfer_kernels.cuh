@@ -78,9 +78,9 @@ namespace mgb
     const int        tx = tile % Lf.nt[0], ty = tile / Lf.nt[0];
     const int        gx0 = tx * TW, gy0 = ty * TW;
     const int        wx = tile_width(Lf, 0, tx), wy = tile_width(Lf, 1, ty);
-    const int        ncz = Lc.ncell[2];
-    const int        cz0 = seg * layers_per_segment;
-    const int        cz1 = imin(cz0 + layers_per_segment, ncz);
+    const int        cz0 = A.cz_begin + seg * layers_per_segment;
+    const int        cz1 = imin(cz0 + layers_per_segment, A.cz_end);
+    const int        fsh = A.f_shift;
     const T *__restrict__ src = A.src;
     T *__restrict__ dst       = A.dst;
 
@@ -171,14 +171,14 @@ namespace mgb
         planes_2d(p * cz + 1, p, 1);
         if (owner)
           {
-            const int nr = cz == ncz - 1 ? 2 * p + 1 : 2 * p; // the top plane belongs to the last layer
+            const int nr = (cz == A.cz_end - 1 && A.close_top) ? 2 * p + 1 : 2 * p; // the top plane belongs to the last layer
             T         old[2 * p + 1];
             if (ADD)
               {
 #pragma unroll
                 for (int r = 0; r < 2 * p + 1; ++r)
                   if (r < nr)
-                    old[r] = dst[own_off + (uint32_t)(2 * p * cz + r) * own_stride];
+                    old[r] = dst[own_off + (uint32_t)(2 * p * cz + r + fsh) * own_stride];
               }
 #pragma unroll
             for (int r = 0; r < 2 * p + 1; ++r)
@@ -188,7 +188,7 @@ namespace mgb
 #pragma unroll
                   for (int k = 0; k < n; ++k)
                     s += p1_table<T>()[r * n + k] * W[k];
-                  const uint32_t d = own_off + (uint32_t)(2 * p * cz + r) * own_stride;
+                  const uint32_t d = own_off + (uint32_t)(2 * p * cz + r + fsh) * own_stride;
                   dst[d]           = ADD ? old[r] + s : s;
                 }
           }
@@ -217,9 +217,9 @@ namespace mgb
     const int        tx = tile % Lf.nt[0], ty = tile / Lf.nt[0];
     const int        gx0 = tx * TW, gy0 = ty * TW;
     const int        wx = tile_width(Lf, 0, tx), wy = tile_width(Lf, 1, ty);
-    const int        ncz = Lc.ncell[2];
-    const int        cz0 = seg * layers_per_segment;
-    const int        cz1 = imin(cz0 + layers_per_segment, ncz);
+    const int        cz0 = A.cz_begin + seg * layers_per_segment;
+    const int        cz1 = imin(cz0 + layers_per_segment, A.cz_end);
+    const int        fsh = A.f_shift;
     const T *__restrict__ src = A.src;
     T *__restrict__ dst       = A.dst;
 
@@ -293,11 +293,11 @@ namespace mgb
     T carry = 0;
     for (int cz = cz0; cz < cz1; ++cz)
       {
-        const int nr = cz == ncz - 1 ? 2 * p + 1 : 2 * p; // fine planes assigned to this parent layer
+        const int nr = (cz == A.cz_end - 1 && A.close_top) ? 2 * p + 1 : 2 * p; // fine planes assigned to this parent layer
         T         v[2 * p + 1], Z[n];
 #pragma unroll
         for (int r = 0; r < 2 * p + 1; ++r)
-          v[r] = (owner && r < nr) ? __ldg(src + own_off + (uint32_t)(2 * p * cz + r) * own_stride) : T(0);
+          v[r] = (owner && r < nr) ? __ldg(src + own_off + (uint32_t)(2 * p * cz + r + fsh) * own_stride) : T(0);
 #pragma unroll
         for (int k = 0; k < n; ++k)
           {
@@ -327,7 +327,9 @@ namespace mgb
   {
     using C          = XferCfg<p>;
     const int ntiles = A.fine.nt[0] * A.fine.nt[1];
-    const int ncz    = A.coarse.ncell[2];
+    const int ncz    = A.cz_end - A.cz_begin;
+    if (ncz <= 0)
+      return;
     int       nseg   = (148 * 8 + ntiles - 1) / ntiles;
     if (nseg > ncz / 2)
       nseg = ncz / 2;

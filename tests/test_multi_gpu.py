@@ -1,0 +1,37 @@
+"""Multi-GPU parity (z-slabs over the GPUs of one node, NCCL ghost exchange): one process per GPU under
+torchrun, every rank checks its owned entries against the global CPU oracle (tests/mgpu_worker.py).
+Skipped on boxes with fewer GPUs than ranks."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def run_ranks(n, args, timeout=600):
+    import torch
+    if not torch.cuda.is_available() or torch.cuda.device_count() < n:
+        pytest.skip("needs %d GPUs" % n)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % n, "--master-addr",
+           "127.0.0.1", "--master-port", str(29900 + os.getpid() % 90), os.path.join(ROOT, "tests", "mgpu_worker.py")] + args
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("mgpu worker ok") == n, r.stdout[-3000:]
+    return r.stdout
+
+
+@pytest.mark.parametrize("p,nsub,nref", [(4, "1,1,1", 3), (3, "1,2,3", 2), (2, "1,1,1", 4)])
+def test_two_gpus_against_oracle(mgb, orc, p, nsub, nref):
+    run_ranks(2, [str(p), nsub, str(nref)])
+
+
+def test_four_gpus_against_oracle(mgb, orc):
+    run_ranks(4, ["4", "1,1,1", "3"])
+
+
+def test_eight_gpus_against_oracle(mgb, orc):
+    run_ranks(8, ["4", "1,1,1", "4"])
