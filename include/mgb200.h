@@ -184,9 +184,11 @@ int mgb_host_numbering(int p, const int ncell[3], int tile_cells, int64_t *n_dof
  * n_subdivisions coarse cells: info[12] as mgb_solver_partition(); plan[8] = {offset, count} (in values) of
  * send_up, recv_dn, send_dn, recv_up: update_ghost_values sends send_up to rank+1 (its recv_dn) and send_dn to
  * rank-1 (its recv_up); compress(add) sends recv_up to rank+1, which adds it to its send_dn range.
+ * min_dofs: levels with fewer DoFs are held completely by every rank (the solver's default is 3 000 000,
+ * environment MGB200_MIN_SLAB_DOFS).
  * lex_to_dof (may be NULL): local vector index of each point of the LOCAL box in lexicographic order     */
 int mgb_host_partition(int p, const int n_subdivisions[3], int level, int tile_cells, int n_ranks, int rank,
-                       int64_t info[12], int64_t plan[8], uint32_t *lex_to_dof);
+                       int64_t min_dofs, int64_t info[12], int64_t plan[8], uint32_t *lex_to_dof);
 
 #ifdef __cplusplus
 }

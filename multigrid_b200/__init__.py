@@ -109,7 +109,7 @@ SYMBOLS = {
     "mgb_host_basis": (_i, [_i] + [_dp] * 9),
     "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), _ip, C.POINTER(C.c_int64),
                                 C.POINTER(C.c_int64), C.POINTER(C.c_uint32)]),
-    "mgb_host_partition": (_i, [_i, _ip, _i, _i, _i, _i, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+    "mgb_host_partition": (_i, [_i, _ip, _i, _i, _i, _i, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                 C.POINTER(C.c_uint32)]),
 }
 
@@ -168,18 +168,18 @@ PARTITION_KEYS = ("distributed", "n_global", "n_local", "owned_begin", "n_owned"
                   "n_planes_global", "ghost_layers_below", "ghost_plane_top", "layer_begin", "layer_end")
 
 
-def host_partition(p, n_subdivisions, level, n_ranks, rank, tile_cells=0, want_map=False):
+def host_partition(p, n_subdivisions, level, n_ranks, rank, tile_cells=0, want_map=False, min_dofs=0):
     """z-slab of `rank` on one multigrid level and its ghost-exchange plan (host logic of csrc/numbering.h)."""
     nsub = (C.c_int * 3)(*n_subdivisions)
     info = (C.c_int64 * 12)()
     plan = (C.c_int64 * 8)()
-    _check(lib().mgb_host_partition(p, nsub, level, tile_cells, n_ranks, rank, info, plan, None))
+    _check(lib().mgb_host_partition(p, nsub, level, tile_cells, n_ranks, rank, min_dofs, info, plan, None))
     out = dict(zip(PARTITION_KEYS, info))
     for i, k in enumerate(("send_up", "recv_dn", "send_dn", "recv_up")):
         out[k] = (plan[2 * i], plan[2 * i + 1])
     if want_map:
         lex = np.zeros(out["n_local"], dtype=np.uint32)
-        _check(lib().mgb_host_partition(p, nsub, level, tile_cells, n_ranks, rank, info, plan,
+        _check(lib().mgb_host_partition(p, nsub, level, tile_cells, n_ranks, rank, min_dofs, info, plan,
                                         lex.ctypes.data_as(C.POINTER(C.c_uint32))))
         out["lex_to_dof"] = lex.astype(np.int64)
     return out

@@ -37,21 +37,32 @@ namespace mgb
     int  zg = 0, ztop = 0; // ghost layer below / ghost plane on top
   };
 
-  // Level l has n0 2^l cell layers in z.  It is distributed when every rank gets the same number
-  // (>= min_layers) of whole layers AND the slabs nest with the level below (the children of a rank's layers are its
+  // Level l has n0 2^l cell layers in z.  It is distributed when it has at least `min_dofs` DoFs (below
+  // that a ghost exchange per operator apply costs more than computing the whole level on every rank),
+  // every rank gets the same number (>= min_layers) of whole layers AND the slabs nest with the level below (the children of a rank's layers are its
   // layers on the finer level): that needs the level below to be distributed too, or an even number of
   // layers per rank.  All other levels are held completely by every rank (the coarse levels: "the
   // coarse-grid solve stays on a single GPU", here computed redundantly so that the correction needs
   // no broadcast).
   inline Slab
-  make_slab(const int n0, const int level, const int n_ranks, const int rank, const int min_layers = 2)
+  make_slab(const int  p,
+            const int  nsub[3],
+            const int  level,
+            const int  n_ranks,
+            const int  rank,
+            const int  min_layers = 2,
+            const long min_dofs   = 3000000)
   {
-    bool dist = false;
+    const int n0   = nsub[2];
+    bool      dist = false;
     for (int l = 0; l <= level; ++l)
       {
         const long ncz = (long)n0 << l;
+        long       n   = 1;
+        for (int c = 0; c < 3; ++c)
+          n *= ((long)nsub[c] << l) * p + 1;
         dist = n_ranks > 1 && ncz % n_ranks == 0 && ncz / n_ranks >= min_layers &&
-               (l == 0 || dist || (ncz / n_ranks) % 2 == 0);
+               (dist || (n >= min_dofs && (l == 0 || (ncz / n_ranks) % 2 == 0)));
       }
     Slab s;
     s.rank    = rank;

@@ -118,6 +118,9 @@ namespace mgb
     int          rank = 0, n_ranks = 1; // z-slab decomposition over the GPUs of one node
     ncclComm_t   comm     = nullptr;
     int64_t      exchanges = 0;          // ghost exchanges + all-reduces issued so far
+    cudaStream_t comm_stream = nullptr;  // ghost exchange overlapped with the interior cell layers
+    cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
+    bool         overlap = true;
     cudaStream_t stream   = nullptr;
     int64_t      launches = 0;
     double      *scal_dev = nullptr; // 16 device scalars for reductions
@@ -219,6 +222,27 @@ namespace mgb
       static_assert(sizeof(uid) == 128, "ncclUniqueId is 128 bytes");
       std::memcpy(&uid, id, sizeof(uid));
       n.check(n.CommInitRank(&comm, n_ranks, uid, rank), "ncclCommInitRank");
+      int lo = 0, hi = 0;
+      MGB_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+      MGB_CUDA_CHECK(cudaStreamCreateWithPriority(&comm_stream, cudaStreamNonBlocking, hi));
+      MGB_CUDA_CHECK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+      MGB_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+      const char *ov = getenv("MGB200_OVERLAP");
+      overlap        = !(ov && ov[0] == '0');
+    }
+    // the comm stream continues after everything issued so far on the solver stream ...
+    void
+    fork_comm()
+    {
+      MGB_CUDA_CHECK(cudaEventRecord(ev_fork, stream));
+      MGB_CUDA_CHECK(cudaStreamWaitEvent(comm_stream, ev_fork, 0));
+    }
+    // ... and the solver stream after everything issued so far on the comm stream
+    void
+    join_comm()
+    {
+      MGB_CUDA_CHECK(cudaEventRecord(ev_join, comm_stream));
+      MGB_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_join, 0));
     }
     // sum of `count` doubles over the ranks, in place, ordered on the solver stream
     void
@@ -234,6 +258,14 @@ namespace mgb
       if (comm)
         Nccl::get().CommDestroy(comm);
       comm = nullptr;
+      if (comm_stream)
+        cudaStreamDestroy(comm_stream);
+      if (ev_fork)
+        cudaEventDestroy(ev_fork);
+      if (ev_join)
+        cudaEventDestroy(ev_join);
+      comm_stream = nullptr;
+      ev_fork = ev_join = nullptr;
       if (scal_dev)
         cudaFree(scal_dev);
       if (scal_host)
@@ -490,21 +522,22 @@ namespace mgb
     // plane-major numbering (level.h)
     template <typename T>
     void
-    update_ghosts(T *v) const
+    update_ghosts(T *v, cudaStream_t on = nullptr) const
     {
       if (!slab.distributed)
         return;
+      const cudaStream_t stream = on ? on : ctx->stream;
       Nccl &n = Nccl::get();
       n.check(n.GroupStart(), "ncclGroupStart");
       if (d.ztop)
         {
-          n.check(n.Send(v + plan.send_up[0], plan.send_up[1] * sizeof(T), ncclInt8, ctx->rank + 1, ctx->comm, ctx->stream), "ncclSend");
-          n.check(n.Recv(v + plan.recv_up[0], plan.recv_up[1] * sizeof(T), ncclInt8, ctx->rank + 1, ctx->comm, ctx->stream), "ncclRecv");
+          n.check(n.Send(v + plan.send_up[0], plan.send_up[1] * sizeof(T), ncclInt8, ctx->rank + 1, ctx->comm, stream), "ncclSend");
+          n.check(n.Recv(v + plan.recv_up[0], plan.recv_up[1] * sizeof(T), ncclInt8, ctx->rank + 1, ctx->comm, stream), "ncclRecv");
         }
       if (d.zg)
         {
-          n.check(n.Send(v + plan.send_dn[0], plan.send_dn[1] * sizeof(T), ncclInt8, ctx->rank - 1, ctx->comm, ctx->stream), "ncclSend");
-          n.check(n.Recv(v + plan.recv_dn[0], plan.recv_dn[1] * sizeof(T), ncclInt8, ctx->rank - 1, ctx->comm, ctx->stream), "ncclRecv");
+          n.check(n.Send(v + plan.send_dn[0], plan.send_dn[1] * sizeof(T), ncclInt8, ctx->rank - 1, ctx->comm, stream), "ncclSend");
+          n.check(n.Recv(v + plan.recv_dn[0], plan.recv_dn[1] * sizeof(T), ncclInt8, ctx->rank - 1, ctx->comm, stream), "ncclRecv");
         }
       n.check(n.GroupEnd(), "ncclGroupEnd");
       ++ctx->exchanges;
@@ -685,7 +718,6 @@ namespace mgb
     void
     launch_cartesian(const ApplyArgs<T> &A) const
     {
-      ScopedRange range(*ctx, level->index, range_kind(A.mode));
       if (sizeof(T) == 8)
         dk->apply_cartesian_d(reinterpret_cast<const ApplyArgs<double> &>(A), ctx->stream);
       else
@@ -709,13 +741,42 @@ namespace mgb
       A.read_plain      = read_plain;
       // update_ghost_values of the source (laplace_operator.h:590): like the reference's vmult, this
       // mutates the ghost range of the const source vector
-      level->update_ghosts(const_cast<T *>(src));
       if (use_cartesian())
         {
           // streaming tile kernel: the vector operation is fused, every DoF is written once
+          ScopedRange      range(*ctx, level->index, range_kind(A.mode));
+          const LevelDesc &L  = level->d;
+          const int        i0 = L.zg ? 2 : 0, i1 = L.ztop ? L.ncell[2] - 1 : L.ncell[2];
+          if (level->slab.distributed && ctx->overlap && i1 > i0)
+            {
+              // ghost exchange on the comm stream while the layers that read no ghost plane are
+              // computed; then the first owned layer (reads the p planes from below through the carry
+              // of the ghost layer) and the last one (reads the plane on top)
+              ctx->fork_comm();
+              level->update_ghosts(const_cast<T *>(src), ctx->comm_stream);
+              A.layer_begin = i0;
+              A.layer_end   = i1;
+              launch_cartesian(A);
+              ctx->join_comm();
+              if (L.zg)
+                {
+                  A.layer_begin = 1;
+                  A.layer_end   = 2;
+                  launch_cartesian(A);
+                }
+              if (L.ztop)
+                {
+                  A.layer_begin = L.ncell[2] - 1;
+                  A.layer_end   = L.ncell[2];
+                  launch_cartesian(A);
+                }
+              return;
+            }
+          level->update_ghosts(const_cast<T *>(src));
           launch_cartesian(A);
           return;
         }
+      level->update_ghosts(const_cast<T *>(src));
       const LevelDesc &L = level->d;
       const size_t     N = L.n_dofs;
 
@@ -1175,10 +1236,11 @@ namespace mgb
           levels.emplace_back(new Level());
           Level &lv = *levels.back();
           lv.index  = l;
-          // thin slabs cost a ghost exchange per operator apply and save next to nothing: by default a
-          // level is cut only when every rank gets at least two cell layers
-          const char *ml = getenv("MGB200_MIN_SLAB_LAYERS");
-          lv.slab = make_slab(o.n_subdivisions[2], l, ctx.n_ranks, ctx.rank, ml ? std::max(1, atoi(ml)) : 2);
+          // small levels cost a ghost exchange per operator apply and save next to nothing: by default a
+          // level is cut only from 3 M DoFs on (measured: profiles/r1_mgpu_levels.txt)
+          const char *ml = getenv("MGB200_MIN_SLAB_LAYERS"), *md = getenv("MGB200_MIN_SLAB_DOFS");
+          lv.slab = make_slab(o.degree, o.n_subdivisions, l, ctx.n_ranks, ctx.rank, ml ? std::max(1, atoi(ml)) : 2,
+                              md ? atol(md) : 3000000L);
           build_slab_level(o.degree, nc, choose_tile_cells(o.degree, o.tile_cells), o.lower, o.upper, 0x3fu, lv.slab, lv.host);
           lv.upload(ctx);
           const size_t N = lv.d.n_dofs;
@@ -2210,7 +2272,7 @@ extern "C"
 
   int
   mgb_host_partition(int p, const int n_subdivisions[3], int level, int tile_cells, int n_ranks, int rank,
-                     int64_t info[12], int64_t plan[8], uint32_t *lex_to_dof)
+                     int64_t min_dofs, int64_t info[12], int64_t plan[8], uint32_t *lex_to_dof)
   {
     MGB_TRY
     if (p < 1 || p > 8)
@@ -2227,7 +2289,7 @@ extern "C"
     for (int c = 0; c < 3; ++c)
       nc[c] = n_subdivisions[c] << level;
     const double lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
-    lv.slab            = make_slab(n_subdivisions[2], level, n_ranks, rank);
+    lv.slab            = make_slab(p, n_subdivisions, level, n_ranks, rank, 2, min_dofs);
     build_slab_level(p, nc, choose_tile_cells(p, tile_cells), lo, hi, 0x3fu, lv.slab, lv.host);
     lv.d = lv.host.d;
     fill_partition_info(lv, info);

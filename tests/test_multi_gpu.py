@@ -15,7 +15,8 @@ def run_ranks(n, args, timeout=600):
     import torch
     if not torch.cuda.is_available() or torch.cuda.device_count() < n:
         pytest.skip("needs %d GPUs" % n)
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    # the test meshes are far below the size from which the library cuts a level by default
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MGB200_MIN_SLAB_DOFS="0")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % n, "--master-addr",
            "127.0.0.1", "--master-port", str(29900 + os.getpid() % 90), os.path.join(ROOT, "tests", "mgpu_worker.py")] + args
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
