@@ -15,7 +15,7 @@ _LIB = os.path.join(_HERE, "_build", "liborc.so")
 
 
 def build(force=False):
-    src = [os.path.join(_HERE, f) for f in ("mg_oracle.cpp", "basis1d.h", "Makefile")]
+    src = [os.path.join(_HERE, f) for f in ("mg_oracle.cpp", "dg_oracle.cpp", "basis1d.h", "Makefile")]
     if (not force and os.path.exists(_LIB)
             and all(os.path.getmtime(_LIB) >= os.path.getmtime(s) for s in src)):
         return _LIB
@@ -60,6 +60,13 @@ def lib():
         L.orc_mg_time_matvec.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.orc_mg_setup_times.argtypes = [C.c_void_p, dp]
         L.orc_basis.argtypes = [C.c_int] + [dp] * 7
+        L.dgo_create.restype = C.c_void_p
+        L.dgo_create.argtypes = [C.c_int, ip, dp, dp, dp]
+        L.dgo_destroy.argtypes = [C.c_void_p]
+        L.dgo_n_dofs.restype = C.c_longlong
+        L.dgo_n_dofs.argtypes = [C.c_void_p]
+        L.dgo_penalty.argtypes = [C.c_void_p, dp]
+        L.dgo_vmult.argtypes = [C.c_void_p, dp, dp]
         _lib = L
     return _lib
 
@@ -204,3 +211,79 @@ class MultigridSolver:
         out = np.zeros(3)
         lib().orc_mg_setup_times(self.h, _dp(out))
         return out
+
+
+def dg_trafo(shear=0.12):
+    """vertex map of matvec_dg/program.cc:66-76: I + 0.12 (d+1)(e+1)"""
+    return np.eye(3) + shear * np.outer(np.arange(1, 4), np.arange(1, 4))
+
+
+DG_LOWER = tuple(-1. + 0.05 * (d + 1) for d in range(3))   # matvec_dg/program.cc:55-60
+DG_UPPER = tuple(0.95 - 0.06 * d for d in range(3))
+
+
+class DGOperator:
+    """SIP-DG Laplacian of laplace_operator_dg_face.h on the affine box mesh of matvec_dg/program.cc;
+    DoFs cell-wise contiguous, cells lexicographic (x fastest)."""
+
+    def __init__(self, degree, ncell, lower=DG_LOWER, upper=DG_UPPER, trafo=None):
+        self.degree, self.ncell = degree, tuple(ncell)
+        self.trafo = dg_trafo() if trafo is None else np.ascontiguousarray(trafo, dtype=np.float64)
+        nc = (C.c_int * 3)(*ncell)
+        lo = (C.c_double * 3)(*lower)
+        hi = (C.c_double * 3)(*upper)
+        self.lower, self.upper = tuple(lower), tuple(upper)
+        self.h = lib().dgo_create(degree, nc, lo, hi, _dp(self.trafo))
+        if not self.h:
+            raise ValueError("unsupported degree")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().dgo_destroy(self.h)
+            self.h = None
+
+    def n_dofs(self):
+        return lib().dgo_n_dofs(self.h)
+
+    def penalty(self):
+        s = np.zeros(3)
+        lib().dgo_penalty(self.h, _dp(s))
+        return s
+
+    def vmult(self, src):
+        src = np.ascontiguousarray(src, dtype=np.float64)
+        dst = np.zeros_like(src)
+        lib().dgo_vmult(self.h, _dp(src), _dp(dst))
+        return dst
+
+    def diagonal(self):
+        """exact diagonal by probing with unit vectors, 8 colours of cells (cells two apart do not couple)"""
+        n3 = (self.degree + 1) ** 3
+        nc = self.ncell
+        cells = np.arange(nc[0] * nc[1] * nc[2])
+        cx, cy, cz = cells % nc[0], (cells // nc[0]) % nc[1], cells // (nc[0] * nc[1])
+        colour = (cx % 2) + 2 * (cy % 2) + 4 * (cz % 2)
+        diag = np.zeros(self.n_dofs())
+        for col in range(8):
+            sel = cells[colour == col]
+            if sel.size == 0:
+                continue
+            for l in range(n3):
+                e = np.zeros(self.n_dofs())
+                e[sel * n3 + l] = 1.0
+                y = self.vmult(e)
+                diag[sel * n3 + l] = y[sel * n3 + l]
+        return diag
+
+    def support_points(self):
+        """physical coordinates of all DoFs, shape (n_dofs, 3)"""
+        b = basis(self.degree)
+        g = b["gll"]
+        n = self.degree + 1
+        nc = self.ncell
+        h = [(self.upper[d] - self.lower[d]) / nc[d] for d in range(3)]
+        cz, cy, cx, k, j, i = np.meshgrid(np.arange(nc[2]), np.arange(nc[1]), np.arange(nc[0]), np.arange(n),
+                                          np.arange(n), np.arange(n), indexing="ij")
+        X = np.stack([self.lower[0] + (cx + g[i]) * h[0], self.lower[1] + (cy + g[j]) * h[1],
+                      self.lower[2] + (cz + g[k]) * h[2]], axis=-1).reshape(-1, 3)
+        return X @ self.trafo.T
