@@ -162,6 +162,53 @@ int mgb_transfer_prolongate_and_add(mgb_solver s, int level, float *fine, const 
 int mgb_transfer_restrict_and_add(mgb_solver s, int level, float *coarse, const float *fine);
 int mgb_transfer_prolongate_no_boundary(mgb_solver s, int level, double *fine, const double *coarse);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Discontinuous Galerkin: symmetric interior-penalty Laplacian, FE_DGQ(p) on an affine box mesh
+ * (multigrid::LaplaceOperatorCompactCombine<dim,p,Number,type=1>, common/laplace_operator_dg.h:360-2026, verified by
+ * the reference against MFReference::LaplaceOperatorFaceBased, common/laplace_operator_dg_face.h:13-166; mesh and
+ * protocol of matvec_dg/program.cc:40-210 and matvec_dg_cheby/program.cc:40-200).
+ * DoFs are cell-wise contiguous (dof_indices_contiguous, laplace_operator_dg.h:1141-1142): cells lexicographic with
+ * x fastest, (k n + j) n + i inside a cell.  One kernel computes cell and face integrals of a cell and the fused
+ * vector operation ("actions" 0, 3, 4 of vmult_with_merged_ops, laplace_operator_dg.h:957-962).               */
+typedef struct mgb_dg_t *mgb_dg;
+
+typedef struct mgb_dg_options {
+  int degree;             /* 1..8                                                                   */
+  int n_subdivisions[3];  /* coarse cells per direction      (matvec_dg/program.cc:61-64)           */
+  int n_refinements;      /* global refinements              (:78)                                  */
+  double lower[3], upper[3]; /* box before the vertex map    (:55-60)                               */
+  double trafo[9];        /* row-major constant matrix applied to the vertices (:66-76)             */
+  int device;
+} mgb_dg_options;
+
+void mgb_dg_default_options(mgb_dg_options *opt);        /* the mesh of matvec_dg/program.cc, degree 4 */
+/* LaplaceOperatorCompactCombine::reinit                          laplace_operator_dg.h:360-769 */
+int mgb_dg_create(const mgb_dg_options *opt, mgb_dg *out);
+int mgb_dg_destroy(mgb_dg h);
+int mgb_dg_sync(mgb_dg h);
+int64_t mgb_dg_n_dofs(mgb_dg h);                                   /* m()                        :795-799 */
+int mgb_dg_n_cells(mgb_dg h, int ncell[3]);
+int mgb_dg_penalty(mgb_dg h, double sigma[3]);                     /* get_penalty, per face direction :789-793 */
+/* vectors are device pointers of the chosen precision (MGB_F32 / MGB_F64) */
+int mgb_dg_vmult(mgb_dg h, int precision, void *dst, const void *src);                       /* :827-841 */
+int mgb_dg_vmult_residual(mgb_dg h, int precision, const void *rhs, const void *lhs, void *residual); /* :843-849 */
+/* std::array<Number,4> vmult_with_cg_update(alpha,beta,r,q,p,x)                                  :862-905 */
+int mgb_dg_vmult_with_cg_update(mgb_dg h, int precision, double alpha, double beta, const void *r, void *q,
+                                void *p, void *x, double sums[4]);
+/* exact inverse diagonal of the SIP matrix (point Jacobi; the reference's JacobiTransformed block
+ * preconditioner, :2028-2256, is not built)                                                              */
+int mgb_dg_inverse_diagonal(mgb_dg h, int precision, void *inv_diag);
+/* vmult_with_chebyshev_update(preconditioner, rhs, iteration_index, factor1, factor2, solution, solution_old)
+ * :907-955 with the point-Jacobi preconditioner: iteration_index 0: solution = factor2 P^-1 rhs; otherwise
+ * solution_old = (1+factor1) solution - factor1 solution_old + factor2 P^-1 (rhs - A solution)  (the caller swaps) */
+int mgb_dg_vmult_with_chebyshev_update(mgb_dg h, int precision, const void *rhs, int iteration_index, double factor1,
+                                       double factor2, void *solution, void *solution_old);
+/* end-to-end: host vectors in, apply, host vector out */
+int mgb_dg_vmult_host(mgb_dg h, int precision, void *dst_host, const void *src_host);
+int mgb_dg_timer_start(mgb_dg h);
+int mgb_dg_timer_stop(mgb_dg h, double *ms);
+int64_t mgb_dg_launch_count(mgb_dg h);
+
 /* plain host<->device helpers so that a C/C++ caller needs no CUDA runtime of its own */
 int mgb_device_alloc(mgb_solver s, size_t bytes, void **dev_ptr);
 int mgb_device_free(mgb_solver s, void *dev_ptr);

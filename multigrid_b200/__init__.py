@@ -50,6 +50,18 @@ class Options(C.Structure):
     ]
 
 
+class DGOptions(C.Structure):
+    _fields_ = [
+        ("degree", C.c_int),
+        ("n_subdivisions", C.c_int * 3),
+        ("n_refinements", C.c_int),
+        ("lower", C.c_double * 3),
+        ("upper", C.c_double * 3),
+        ("trafo", C.c_double * 9),
+        ("device", C.c_int),
+    ]
+
+
 _lib = None
 
 # name -> (restype, argtypes); the full export list of include/mgb200.h
@@ -105,6 +117,23 @@ SYMBOLS = {
     "mgb_copy_to_device": (_i, [_vp, _vp, _vp, C.c_size_t]),
     "mgb_copy_to_host": (_i, [_vp, _vp, _vp, C.c_size_t]),
     "mgb_solver_launch_count": (C.c_int64, [_vp]),
+    # DG operator
+    "mgb_dg_default_options": (None, [C.POINTER(DGOptions)]),
+    "mgb_dg_create": (_i, [C.POINTER(DGOptions), C.POINTER(_vp)]),
+    "mgb_dg_destroy": (_i, [_vp]),
+    "mgb_dg_sync": (_i, [_vp]),
+    "mgb_dg_n_dofs": (C.c_int64, [_vp]),
+    "mgb_dg_n_cells": (_i, [_vp, _ip]),
+    "mgb_dg_penalty": (_i, [_vp, _dp]),
+    "mgb_dg_vmult": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_dg_vmult_residual": (_i, [_vp, _i, _vp, _vp, _vp]),
+    "mgb_dg_vmult_with_cg_update": (_i, [_vp, _i, _d, _d, _vp, _vp, _vp, _vp, _dp]),
+    "mgb_dg_inverse_diagonal": (_i, [_vp, _i, _vp]),
+    "mgb_dg_vmult_with_chebyshev_update": (_i, [_vp, _i, _vp, _i, _d, _d, _vp, _vp]),
+    "mgb_dg_vmult_host": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_dg_timer_start": (_i, [_vp]),
+    "mgb_dg_timer_stop": (_i, [_vp, _dp]),
+    "mgb_dg_launch_count": (C.c_int64, [_vp]),
     # host-only helpers
     "mgb_host_basis": (_i, [_i] + [_dp] * 9),
     "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), _ip, C.POINTER(C.c_int64),
@@ -511,3 +540,130 @@ class MultigridSolver:
 
     def set_kernel(self, kernel):
         _check(lib().mgb_op_set_kernel(self.h, kernel))
+
+
+class LaplaceOperatorDG:
+    """multigrid::LaplaceOperatorCompactCombine<3,p,Number,1> (common/laplace_operator_dg.h:360-2026): SIP-DG Laplacian
+    with FE_DGQ(p) on the affine box mesh of matvec_dg/program.cc:40-80.  Vectors are torch tensors on the
+    device, cell-wise contiguous; `precision` picks the float or the double kernels."""
+
+    def __init__(self, degree=4, n_subdivisions=(1, 1, 1), n_refinements=0, lower=None, upper=None, trafo=None,
+                 device=0, precision=F64):
+        import torch
+        o = DGOptions()
+        lib().mgb_dg_default_options(C.byref(o))
+        o.degree = degree
+        if isinstance(n_subdivisions, int):
+            n_subdivisions = (n_subdivisions,) * 3
+        o.n_subdivisions[:] = list(n_subdivisions)
+        o.n_refinements = n_refinements
+        if lower is not None:
+            o.lower[:] = list(lower)
+        if upper is not None:
+            o.upper[:] = list(upper)
+        if trafo is not None:
+            o.trafo[:] = [float(v) for v in np.asarray(trafo, dtype=np.float64).ravel()]
+        o.device = device
+        self.h = C.c_void_p()
+        self.device = torch.device("cuda", device)
+        self.precision = precision
+        self.dtype = torch.float64 if precision == F64 else torch.float32
+        self.degree = degree
+        _check(lib().mgb_dg_create(C.byref(o), C.byref(self.h)))
+
+    def close(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.mgb_dg_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _torch_sync(self):
+        import torch
+        torch.cuda.synchronize(self.device)
+
+    def sync(self):
+        _check(lib().mgb_dg_sync(self.h))
+
+    def m(self):
+        return lib().mgb_dg_n_dofs(self.h)
+
+    n = m
+
+    def n_cells(self):
+        nc = (C.c_int * 3)()
+        _check(lib().mgb_dg_n_cells(self.h, nc))
+        return tuple(nc)
+
+    def get_penalty(self):
+        s = (C.c_double * 3)()
+        _check(lib().mgb_dg_penalty(self.h, s))
+        return np.array(s)
+
+    def initialize_dof_vector(self):
+        import torch
+        return torch.zeros(self.m(), dtype=self.dtype, device=self.device)
+
+    def _chk(self, *ts):
+        for t in ts:
+            if t.dtype != self.dtype or t.numel() != self.m() or not t.is_cuda or not t.is_contiguous():
+                raise MgbError("vector does not match the operator (dtype/size/device)")
+
+    def vmult(self, dst, src):
+        self._chk(dst, src)
+        self._torch_sync()
+        _check(lib().mgb_dg_vmult(self.h, self.precision, _ptr(dst), _ptr(src)))
+        self.sync()
+
+    def vmult_residual(self, rhs, lhs, residual):
+        self._chk(rhs, lhs, residual)
+        self._torch_sync()
+        _check(lib().mgb_dg_vmult_residual(self.h, self.precision, _ptr(rhs), _ptr(lhs), _ptr(residual)))
+        self.sync()
+
+    def vmult_with_cg_update(self, alpha, beta, r, q, p, x):
+        self._chk(r, q, p, x)
+        sums = (C.c_double * 4)()
+        self._torch_sync()
+        _check(lib().mgb_dg_vmult_with_cg_update(self.h, self.precision, alpha, beta, _ptr(r), _ptr(q), _ptr(p),
+                                                 _ptr(x), sums))
+        return list(sums)
+
+    def get_matrix_diagonal_inverse(self):
+        d = self.initialize_dof_vector()
+        self._torch_sync()
+        _check(lib().mgb_dg_inverse_diagonal(self.h, self.precision, _ptr(d)))
+        self.sync()
+        return d
+
+    def vmult_with_chebyshev_update(self, rhs, iteration_index, factor1, factor2, solution, solution_old):
+        """as the reference (laplace_operator_dg.h:907-955): the new iterate lands in `solution_old`; the caller
+        swaps (iteration_index 0 writes `solution` directly)"""
+        self._chk(rhs, solution, solution_old)
+        self._torch_sync()
+        _check(lib().mgb_dg_vmult_with_chebyshev_update(self.h, self.precision, _ptr(rhs), iteration_index, factor1,
+                                                        factor2, _ptr(solution), _ptr(solution_old)))
+        self.sync()
+
+    def vmult_async(self, dst, src):
+        """no synchronisation (benchmark loops)"""
+        _check(lib().mgb_dg_vmult(self.h, self.precision, _ptr(dst), _ptr(src)))
+
+    def chebyshev_update_async(self, rhs, iteration_index, factor1, factor2, solution, solution_old):
+        _check(lib().mgb_dg_vmult_with_chebyshev_update(self.h, self.precision, _ptr(rhs), iteration_index, factor1,
+                                                        factor2, _ptr(solution), _ptr(solution_old)))
+
+    def vmult_host(self, dst_host, src_host):
+        ptr = lambda a: C.c_void_p(a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data)
+        _check(lib().mgb_dg_vmult_host(self.h, self.precision, ptr(dst_host), ptr(src_host)))
+
+    def timer_start(self):
+        _check(lib().mgb_dg_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_double()
+        _check(lib().mgb_dg_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def launch_count(self):
+        return lib().mgb_dg_launch_count(self.h)

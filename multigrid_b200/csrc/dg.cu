@@ -1,0 +1,596 @@
+// Host side and C ABI of the DG operator (include/mgb200.h, section "Discontinuous Galerkin").
+//   DGOperator  <->  multigrid::LaplaceOperatorCompactCombine<3,p,Number,1>   common/laplace_operator_dg.h:360-2026
+// There is no CPU fallback: every numerical step is a kernel launch on the operator's stream.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/mgb200.h"
+#include "basis.h"
+#include "dg_kernels.cuh"
+
+namespace mgb
+{
+#define MGB_DG_CHECK(call)                                                                      \
+  do                                                                                            \
+    {                                                                                           \
+      cudaError_t err__ = (call);                                                               \
+      if (err__ != cudaSuccess)                                                                 \
+        throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(err__) +     \
+                                 " at " + __FILE__ + ":" + std::to_string(__LINE__));           \
+    }                                                                                           \
+  while (0)
+
+  template <typename T, int n>
+  static DGTables<T, n>
+  make_tables(const Basis &b)
+  {
+    DGTables<T, n>           t;
+    std::vector<long double> nodes(b.nodes.begin(), b.nodes.end());
+    for (int i = 0; i < n * n; ++i)
+      {
+        t.S[i] = (T)b.S[i];
+        t.G[i] = (T)b.G[i];
+        t.D[i] = (T)b.D[i];
+      }
+    for (int i = 0; i < n; ++i)
+      {
+        t.e0[i] = (T)detail::dlag(nodes, i, 0.0L);
+        t.e1[i] = (T)detail::dlag(nodes, i, 1.0L);
+        t.w[i]  = (T)b.wq[i];
+      }
+    return t;
+  }
+
+  // diagonal entries of the 1-D matrices int phi phi, int phi' phi', int phi' phi and the end derivatives
+  struct DGDiagTables
+  {
+    double M[9], K[9], C[9], e0[9], e1[9];
+  };
+
+  struct DGGeom
+  {
+    double gt[6], gs[3][3], sigma[3], area[3];
+  };
+
+  // a(phi_i, phi_i): cell term + the faces on which phi_i does not vanish (see dg_kernels.cuh header)
+  template <typename T>
+  __global__ void
+  k_dg_inverse_diagonal(const int n, const int nc0, const int nc1, const int nc2, const DGGeom g, const DGDiagTables tb,
+                        T *__restrict__ out)
+  {
+    const size_t n3    = (size_t)n * n * n;
+    const size_t total = (size_t)nc0 * nc1 * nc2 * n3;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x)
+      {
+        const size_t c = idx / n3;
+        const int    l = (int)(idx - c * n3);
+        const int    i[3]  = {l % n, (l / n) % n, l / (n * n)};
+        const int    cc[3] = {(int)(c % nc0), (int)((c / nc0) % nc1), (int)(c / ((size_t)nc0 * nc1))};
+        const int    ncs[3] = {nc0, nc1, nc2};
+        const double M0 = tb.M[i[0]], M1 = tb.M[i[1]], M2 = tb.M[i[2]];
+        const double C0 = tb.C[i[0]], C1 = tb.C[i[1]], C2 = tb.C[i[2]];
+        double       v = g.gt[0] * tb.K[i[0]] * M1 * M2 + g.gt[1] * M0 * tb.K[i[1]] * M2 + g.gt[2] * M0 * M1 * tb.K[i[2]] +
+                   2. * (g.gt[3] * C0 * C1 * M2 + g.gt[4] * C0 * M1 * C2 + g.gt[5] * M0 * C1 * C2);
+        for (int d = 0; d < 3; ++d)
+          {
+            const int    da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2;
+            const double Ma = tb.M[i[da]], Mb = tb.M[i[db]], Ca = tb.C[i[da]], Cb = tb.C[i[db]];
+            for (int s = 0; s < 2; ++s)
+              {
+                if (i[d] != (s ? n - 1 : 0))
+                  continue;
+                const bool   interior = s ? cc[d] + 1 < ncs[d] : cc[d] > 0;
+                const double sgn = s ? 1. : -1., e = s ? tb.e1[i[d]] : tb.e0[i[d]];
+                const double term =
+                  g.sigma[d] * Ma * Mb - sgn * (g.gs[d][d] * e * Ma * Mb + g.gs[d][da] * Ca * Mb + g.gs[d][db] * Ma * Cb);
+                v += (interior ? 1. : 2.) * g.area[d] * term;
+              }
+          }
+        out[idx] = (T)(1. / v);
+      }
+  }
+
+  template <typename F>
+  __global__ void
+  k_dg_foreach(const size_t n, F f)
+  {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+      f(i);
+  }
+
+  // four sums of vmult_with_cg_update: q.p, r.r, q.r, q.q (warp shuffles, one atomic per block and sum)
+  template <typename T>
+  __global__ void
+  k_dg_cg_sums(const size_t n, const T *__restrict__ q, const T *__restrict__ p, const T *__restrict__ r, double *out)
+  {
+    double acc[4] = {0, 0, 0, 0};
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+      {
+        const double qi = q[i], pi = p[i], ri = r[i];
+        acc[0] += qi * pi;
+        acc[1] += ri * ri;
+        acc[2] += qi * ri;
+        acc[3] += qi * qi;
+      }
+    __shared__ double red[4][8];
+    for (int s = 0; s < 4; ++s)
+      {
+        double v = acc[s];
+        for (int o = 16; o > 0; o >>= 1)
+          v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0)
+          red[s][threadIdx.x >> 5] = v;
+      }
+    __syncthreads();
+    if (threadIdx.x < 4)
+      {
+        double v = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w)
+          v += red[threadIdx.x][w];
+        atomicAdd(&out[threadIdx.x], v);
+      }
+  }
+
+  struct DGOperator
+  {
+    mgb_dg_options opt;
+    int            p = 0, n = 0, nc[3] = {0, 0, 0};
+    size_t         n_cells = 0, n_dofs = 0;
+    cudaStream_t   stream   = nullptr;
+    cudaEvent_t    ev[2]    = {nullptr, nullptr};
+    int64_t        launches = 0;
+    Basis          basis;
+    DGGeom         geom;
+    DGDiagTables   dtab;
+    double        *scal_dev = nullptr, *scal_host = nullptr;
+    void          *inv_diag[2] = {nullptr, nullptr}; // float, double
+    void          *host_buf[2] = {nullptr, nullptr}; // device staging of the *_host entry points
+
+    explicit DGOperator(const mgb_dg_options &o)
+      : opt(o)
+    {
+      if (o.degree < 1 || o.degree > 8)
+        throw std::runtime_error("polynomial degree must be between 1 and 8");
+      if (o.n_refinements < 0 || o.n_refinements > 12)
+        throw std::runtime_error("invalid number of refinements");
+      p = o.degree;
+      n = p + 1;
+      double J[3][3], h[3];
+      n_cells = 1;
+      for (int d = 0; d < 3; ++d)
+        {
+          if (o.n_subdivisions[d] < 1 || !(o.upper[d] > o.lower[d]))
+            throw std::runtime_error("invalid mesh description");
+          nc[d] = o.n_subdivisions[d] << o.n_refinements;
+          h[d]  = (o.upper[d] - o.lower[d]) / nc[d];
+          n_cells *= (size_t)nc[d];
+        }
+      n_dofs = n_cells * n * n * n;
+      if (n_cells >= 0xffffffffull)
+        throw std::runtime_error("too many cells for one device");
+      for (int k = 0; k < 3; ++k)
+        for (int d = 0; d < 3; ++d)
+          J[k][d] = o.trafo[k * 3 + d] * h[d]; // d x_k / d xi_d
+      double det = J[0][0] * (J[1][1] * J[2][2] - J[1][2] * J[2][1]) - J[0][1] * (J[1][0] * J[2][2] - J[1][2] * J[2][0]) +
+                   J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]);
+      if (std::fabs(det) < 1e-300)
+        throw std::runtime_error("singular vertex map");
+      double Ji[3][3]; // Ji[d][k] = d xi_d / d x_k
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+          {
+            const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+            Ji[j][i]     = (J[i1][j1] * J[i2][j2] - J[i1][j2] * J[i2][j1]) / det;
+          }
+      det = std::fabs(det);
+      double Gm[3][3], gn[3];
+      for (int d = 0; d < 3; ++d)
+        for (int e = 0; e < 3; ++e)
+          Gm[d][e] = Ji[d][0] * Ji[e][0] + Ji[d][1] * Ji[e][1] + Ji[d][2] * Ji[e][2];
+      const int pair[6][2] = {{0, 0}, {1, 1}, {2, 2}, {0, 1}, {0, 2}, {1, 2}};
+      for (int e = 0; e < 6; ++e)
+        geom.gt[e] = det * Gm[pair[e][0]][pair[e][1]];
+      for (int d = 0; d < 3; ++d)
+        {
+          gn[d]         = std::sqrt(Gm[d][d]);
+          geom.sigma[d] = (p + 1.) * (p + 1.) * gn[d]; // penalty_factor = 1 (laplace_operator_dg.h:47,789-793)
+          geom.area[d]  = det * gn[d];
+          for (int e = 0; e < 3; ++e)
+            geom.gs[d][e] = Gm[d][e] / gn[d];
+        }
+      basis = make_basis(p);
+      std::vector<long double> nodes(basis.nodes.begin(), basis.nodes.end());
+      for (int i = 0; i < n; ++i)
+        {
+          double m = 0, k = 0, c = 0;
+          for (int q = 0; q < n; ++q)
+            {
+              const double s = basis.S[q * n + i], g = basis.G[q * n + i];
+              m += basis.wq[q] * s * s;
+              k += basis.wq[q] * g * g;
+              c += basis.wq[q] * g * s;
+            }
+          dtab.M[i]  = m;
+          dtab.K[i]  = k;
+          dtab.C[i]  = c;
+          dtab.e0[i] = (double)detail::dlag(nodes, i, 0.0L);
+          dtab.e1[i] = (double)detail::dlag(nodes, i, 1.0L);
+        }
+      int count = 0;
+      if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        throw std::runtime_error("no CUDA device: the DG operator has no CPU fallback");
+      MGB_DG_CHECK(cudaSetDevice(o.device));
+      MGB_DG_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+      MGB_DG_CHECK(cudaEventCreate(&ev[0]));
+      MGB_DG_CHECK(cudaEventCreate(&ev[1]));
+      MGB_DG_CHECK(cudaMalloc(&scal_dev, 4 * sizeof(double)));
+      MGB_DG_CHECK(cudaMallocHost(&scal_host, 4 * sizeof(double)));
+    }
+
+    ~DGOperator()
+    {
+      for (int i = 0; i < 2; ++i)
+        {
+          if (inv_diag[i])
+            cudaFree(inv_diag[i]);
+          if (host_buf[i])
+            cudaFree(host_buf[i]);
+          if (ev[i])
+            cudaEventDestroy(ev[i]);
+        }
+      if (scal_dev)
+        cudaFree(scal_dev);
+      if (scal_host)
+        cudaFreeHost(scal_host);
+      if (stream)
+        cudaStreamDestroy(stream);
+    }
+
+    unsigned grid(const size_t count) const { return (unsigned)std::min<size_t>((count + 255) / 256, 148 * 16); }
+
+    template <typename T>
+    T *
+    get_inverse_diagonal()
+    {
+      const int k = sizeof(T) == 8;
+      if (!inv_diag[k])
+        {
+          MGB_DG_CHECK(cudaMalloc(&inv_diag[k], n_dofs * sizeof(T)));
+          k_dg_inverse_diagonal<T><<<grid(n_dofs), 256, 0, stream>>>(n, nc[0], nc[1], nc[2], geom, dtab, (T *)inv_diag[k]);
+          ++launches;
+          MGB_DG_CHECK(cudaGetLastError());
+        }
+      return (T *)inv_diag[k];
+    }
+
+    template <int P, typename T>
+    void
+    launch(const DGArgs<T> &A)
+    {
+      static const DGTables<T, P + 1> tb = make_tables<T, P + 1>(make_basis(P));
+      launch_dg_apply<P, T>(A, tb, stream);
+    }
+
+    template <typename T>
+    void
+    apply(const int mode, T *dst, const T *src, const T *rhs = nullptr, const double f1 = 0, const double f2 = 0)
+    {
+      DGArgs<T> A;
+      for (int d = 0; d < 3; ++d)
+        {
+          A.nc[d]    = nc[d];
+          A.sigma[d] = (T)geom.sigma[d];
+          A.area[d]  = (T)geom.area[d];
+          for (int e = 0; e < 3; ++e)
+            A.gs[d][e] = (T)geom.gs[d][e];
+        }
+      for (int e = 0; e < 6; ++e)
+        A.gt[e] = (T)geom.gt[e];
+      A.n_cells  = (uint32_t)n_cells;
+      A.src      = src;
+      A.dst      = dst;
+      A.rhs      = rhs;
+      A.inv_diag = mode >= DG_CHEBYSHEV ? get_inverse_diagonal<T>() : nullptr;
+      A.f1       = (T)f1;
+      A.f2       = (T)f2;
+      A.mode     = mode;
+      switch (p)
+        {
+          case 1: launch<1, T>(A); break;
+          case 2: launch<2, T>(A); break;
+          case 3: launch<3, T>(A); break;
+          case 4: launch<4, T>(A); break;
+          case 5: launch<5, T>(A); break;
+          case 6: launch<6, T>(A); break;
+          case 7: launch<7, T>(A); break;
+          default: launch<8, T>(A); break;
+        }
+      ++launches;
+      MGB_DG_CHECK(cudaGetLastError());
+    }
+
+    // laplace_operator_dg.h:862-905
+    template <typename T>
+    void
+    vmult_with_cg_update(const T alpha, const T beta, const T *r, T *q, T *pp, T *x, double sums[4])
+    {
+      const size_t N = n_dofs;
+      if (alpha == T(0))
+        k_dg_foreach<<<grid(N), 256, 0, stream>>>(N, [=] __device__(size_t i) { pp[i] = q[i]; });
+      else
+        k_dg_foreach<<<grid(N), 256, 0, stream>>>(N, [=] __device__(size_t i) {
+          x[i] += alpha * pp[i];
+          pp[i] = beta * pp[i] + q[i];
+        });
+      ++launches;
+      apply<T>(DG_SET, q, pp);
+      MGB_DG_CHECK(cudaMemsetAsync(scal_dev, 0, 4 * sizeof(double), stream));
+      k_dg_cg_sums<T><<<grid(N), 256, 0, stream>>>(N, q, pp, r, scal_dev);
+      ++launches;
+      MGB_DG_CHECK(cudaMemcpyAsync(scal_host, scal_dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+      MGB_DG_CHECK(cudaStreamSynchronize(stream));
+      for (int s = 0; s < 4; ++s)
+        sums[s] = scal_host[s];
+    }
+
+    // laplace_operator_dg.h:907-955 with the point-Jacobi preconditioner
+    template <typename T>
+    void
+    chebyshev_update(const T *rhs, const int iteration_index, const double f1, const double f2, T *solution, T *solution_old)
+    {
+      if (iteration_index > 0)
+        {
+          apply<T>(iteration_index == 1 ? DG_CHEBYSHEV_FIRST : DG_CHEBYSHEV, solution_old, solution, rhs, f1, f2);
+          return;
+        }
+      const T     *P = get_inverse_diagonal<T>();
+      const T      f = (T)f2;
+      const size_t N = n_dofs;
+      k_dg_foreach<<<grid(N), 256, 0, stream>>>(N, [=] __device__(size_t i) { solution[i] = f * P[i] * rhs[i]; });
+      ++launches;
+      MGB_DG_CHECK(cudaGetLastError());
+    }
+  };
+} // namespace mgb
+
+// ====================================================================== C ABI
+using namespace mgb;
+
+struct mgb_dg_t
+{
+  DGOperator *impl;
+};
+
+// error string shared with solver.cu's mgb_last_error()
+void mgb_set_last_error(const char *msg);
+
+#define DG_TRY try {
+#define DG_CATCH                                   \
+  }                                                \
+  catch (const std::exception &e)                  \
+  {                                                \
+    mgb_set_last_error(e.what());                  \
+    return 1;                                      \
+  }                                                \
+  catch (...)                                      \
+  {                                                \
+    mgb_set_last_error("unknown error");           \
+    return 2;                                      \
+  }                                                \
+  return 0;
+
+static DGOperator &
+DGH(mgb_dg h)
+{
+  if (!h || !h->impl)
+    throw std::runtime_error("null DG operator handle");
+  return *h->impl;
+}
+
+static void
+check_precision(const int precision)
+{
+  if (precision != MGB_F32 && precision != MGB_F64)
+    throw std::runtime_error("precision must be MGB_F32 or MGB_F64");
+}
+
+extern "C"
+{
+  void
+  mgb_dg_default_options(mgb_dg_options *o)
+  {
+    std::memset(o, 0, sizeof(*o));
+    o->degree = 4;
+    for (int d = 0; d < 3; ++d)
+      {
+        o->n_subdivisions[d] = 1;
+        o->lower[d]          = -1. + 0.05 * (d + 1); // matvec_dg/program.cc:55-60
+        o->upper[d]          = 0.95 - 0.06 * d;
+        for (int e = 0; e < 3; ++e)
+          o->trafo[d * 3 + e] = (d == e ? 1. : 0.) + 0.12 * (d + 1) * (e + 1); // :66-71
+      }
+  }
+
+  int
+  mgb_dg_create(const mgb_dg_options *opt, mgb_dg *out)
+  {
+    DG_TRY
+    if (!opt || !out)
+      throw std::runtime_error("null argument");
+    *out         = new mgb_dg_t();
+    (*out)->impl = nullptr;
+    try
+      {
+        (*out)->impl = new DGOperator(*opt);
+      }
+    catch (...)
+      {
+        delete *out;
+        *out = nullptr;
+        throw;
+      }
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_destroy(mgb_dg h)
+  {
+    DG_TRY
+    if (h)
+      {
+        delete h->impl;
+        delete h;
+      }
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_sync(mgb_dg h)
+  {
+    DG_TRY
+    MGB_DG_CHECK(cudaStreamSynchronize(DGH(h).stream));
+    DG_CATCH
+  }
+
+  int64_t
+  mgb_dg_n_dofs(mgb_dg h)
+  {
+    return h && h->impl ? (int64_t)h->impl->n_dofs : -1;
+  }
+
+  int
+  mgb_dg_n_cells(mgb_dg h, int ncell[3])
+  {
+    DG_TRY
+    for (int d = 0; d < 3; ++d)
+      ncell[d] = DGH(h).nc[d];
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_penalty(mgb_dg h, double sigma[3])
+  {
+    DG_TRY
+    for (int d = 0; d < 3; ++d)
+      sigma[d] = DGH(h).geom.sigma[d];
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_vmult(mgb_dg h, int precision, void *dst, const void *src)
+  {
+    DG_TRY
+    check_precision(precision);
+    if (precision == MGB_F64)
+      DGH(h).apply<double>(DG_SET, (double *)dst, (const double *)src);
+    else
+      DGH(h).apply<float>(DG_SET, (float *)dst, (const float *)src);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_vmult_residual(mgb_dg h, int precision, const void *rhs, const void *lhs, void *residual)
+  {
+    DG_TRY
+    check_precision(precision);
+    if (precision == MGB_F64)
+      DGH(h).apply<double>(DG_RESIDUAL, (double *)residual, (const double *)lhs, (const double *)rhs);
+    else
+      DGH(h).apply<float>(DG_RESIDUAL, (float *)residual, (const float *)lhs, (const float *)rhs);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_vmult_with_cg_update(mgb_dg h, int precision, double alpha, double beta, const void *r, void *q, void *p,
+                              void *x, double sums[4])
+  {
+    DG_TRY
+    check_precision(precision);
+    if (precision == MGB_F64)
+      DGH(h).vmult_with_cg_update<double>(alpha, beta, (const double *)r, (double *)q, (double *)p, (double *)x, sums);
+    else
+      DGH(h).vmult_with_cg_update<float>((float)alpha, (float)beta, (const float *)r, (float *)q, (float *)p, (float *)x,
+                                         sums);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_inverse_diagonal(mgb_dg h, int precision, void *inv_diag)
+  {
+    DG_TRY
+    check_precision(precision);
+    DGOperator &o = DGH(h);
+    if (precision == MGB_F64)
+      MGB_DG_CHECK(cudaMemcpyAsync(inv_diag, o.get_inverse_diagonal<double>(), o.n_dofs * 8, cudaMemcpyDeviceToDevice, o.stream));
+    else
+      MGB_DG_CHECK(cudaMemcpyAsync(inv_diag, o.get_inverse_diagonal<float>(), o.n_dofs * 4, cudaMemcpyDeviceToDevice, o.stream));
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_vmult_with_chebyshev_update(mgb_dg h, int precision, const void *rhs, int iteration_index, double factor1,
+                                     double factor2, void *solution, void *solution_old)
+  {
+    DG_TRY
+    check_precision(precision);
+    if (precision == MGB_F64)
+      DGH(h).chebyshev_update<double>((const double *)rhs, iteration_index, factor1, factor2, (double *)solution,
+                                      (double *)solution_old);
+    else
+      DGH(h).chebyshev_update<float>((const float *)rhs, iteration_index, factor1, factor2, (float *)solution,
+                                     (float *)solution_old);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_vmult_host(mgb_dg h, int precision, void *dst_host, const void *src_host)
+  {
+    DG_TRY
+    check_precision(precision);
+    DGOperator  &o     = DGH(h);
+    const size_t bytes = o.n_dofs * (precision == MGB_F64 ? 8 : 4);
+    for (int i = 0; i < 2; ++i)
+      if (!o.host_buf[i])
+        MGB_DG_CHECK(cudaMalloc(&o.host_buf[i], o.n_dofs * 8));
+    MGB_DG_CHECK(cudaMemcpyAsync(o.host_buf[0], src_host, bytes, cudaMemcpyHostToDevice, o.stream));
+    if (precision == MGB_F64)
+      o.apply<double>(DG_SET, (double *)o.host_buf[1], (const double *)o.host_buf[0]);
+    else
+      o.apply<float>(DG_SET, (float *)o.host_buf[1], (const float *)o.host_buf[0]);
+    MGB_DG_CHECK(cudaMemcpyAsync(dst_host, o.host_buf[1], bytes, cudaMemcpyDeviceToHost, o.stream));
+    MGB_DG_CHECK(cudaStreamSynchronize(o.stream));
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_timer_start(mgb_dg h)
+  {
+    DG_TRY
+    MGB_DG_CHECK(cudaEventRecord(DGH(h).ev[0], DGH(h).stream));
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_timer_stop(mgb_dg h, double *ms)
+  {
+    DG_TRY
+    DGOperator &o = DGH(h);
+    MGB_DG_CHECK(cudaEventRecord(o.ev[1], o.stream));
+    MGB_DG_CHECK(cudaEventSynchronize(o.ev[1]));
+    float t = 0;
+    MGB_DG_CHECK(cudaEventElapsedTime(&t, o.ev[0], o.ev[1]));
+    *ms = t;
+    DG_CATCH
+  }
+
+  int64_t
+  mgb_dg_launch_count(mgb_dg h)
+  {
+    return h && h->impl ? h->impl->launches : -1;
+  }
+}

@@ -1563,6 +1563,13 @@ using namespace mgb;
 
 static thread_local std::string g_last_error;
 
+// used by the other translation units of the library (dg.cu)
+void
+mgb_set_last_error(const char *msg)
+{
+  g_last_error = msg;
+}
+
 struct mgb_solver_t
 {
   MultigridSolver *impl;

@@ -1,0 +1,115 @@
+"""GPU parity of the DG operator (csrc/dg_kernels.cuh through the C ABI) against the face-based CPU oracle
+(oracle/dg_oracle.cpp): matvec relative error <= 1e-12 in double and <= 1e-5 in float, as north_star asks."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+TOL = {1: 1e-12, 0: 1e-5}
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch as t
+    if not t.cuda.is_available():
+        pytest.skip("no GPU")
+    return t
+
+
+def rel(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+MESHES = [  # p, n_subdivisions, n_refinements, sheared
+    (1, (2, 2, 2), 1, True), (2, (1, 2, 1), 1, True), (3, (2, 1, 3), 1, True), (4, (1, 1, 1), 2, True),
+    (4, (3, 2, 1), 0, True), (4, (1, 1, 1), 0, True), (4, (2, 2, 2), 1, False), (5, (2, 1, 1), 1, True),
+    (6, (1, 2, 2), 0, True), (7, (2, 2, 1), 0, True), (8, (1, 1, 2), 1, True),
+]
+
+
+def make(mgb, orc, p, nsub, nref, sheared, precision):
+    trafo = orc.dg_trafo() if sheared else np.eye(3)
+    g = mgb.LaplaceOperatorDG(p, nsub, nref, trafo=trafo, precision=precision)
+    o = orc.DGOperator(p, [s << nref for s in nsub], trafo=trafo)
+    assert g.m() == o.n_dofs() and g.n_cells() == tuple(s << nref for s in nsub)
+    return g, o
+
+
+@pytest.mark.parametrize("precision", [1, 0])
+@pytest.mark.parametrize("mesh", MESHES)
+def test_vmult_family(mgb, orc, torch, mesh, precision):
+    p, nsub, nref, sheared = mesh
+    g, o = make(mgb, orc, p, nsub, nref, sheared, precision)
+    rng = np.random.default_rng(42)
+    x, b = rng.random(g.m()), rng.random(g.m())
+    dx = torch.tensor(x, dtype=g.dtype, device="cuda")
+    db = torch.tensor(b, dtype=g.dtype, device="cuda")
+    y = g.initialize_dof_vector()
+    g.vmult(y, dx)
+    ref = o.vmult(x)
+    assert rel(y.double().cpu().numpy(), ref) <= TOL[precision], ("vmult", rel(y.double().cpu().numpy(), ref))
+    g.vmult_residual(db, dx, y)
+    assert rel(y.double().cpu().numpy(), b - ref) <= TOL[precision]
+    assert np.allclose(g.get_penalty(), o.penalty(), rtol=1e-14)
+    # vmult_with_cg_update (laplace_operator_dg.h:862-905)
+    r_, q_, p_, x_ = (rng.random(g.m()) for _ in range(4))
+    dr, dq, dp, dxx = (torch.tensor(v, dtype=g.dtype, device="cuda") for v in (r_, q_, p_, x_))
+    sums = g.vmult_with_cg_update(0.3, 0.7, dr, dq, dp, dxx)
+    x_new, p_new = x_ + 0.3 * p_, 0.7 * p_ + q_
+    q_new = o.vmult(p_new)
+    sums_ref = [q_new @ p_new, r_ @ r_, q_new @ r_, q_new @ q_new]
+    assert np.allclose(sums, sums_ref, rtol=1e-11 if precision else 2e-5)
+    assert rel(dxx.double().cpu().numpy(), x_new) <= TOL[precision] and rel(dq.double().cpu().numpy(), q_new) <= TOL[precision]
+
+
+@pytest.mark.parametrize("precision", [1, 0])
+@pytest.mark.parametrize("mesh", [(2, (2, 2, 2), 0, True), (4, (2, 2, 2), 0, True), (3, (3, 2, 2), 0, False), (4, (1, 1, 1), 1, True)])
+def test_diagonal_and_chebyshev(mgb, orc, torch, mesh, precision):
+    p, nsub, nref, sheared = mesh
+    g, o = make(mgb, orc, p, nsub, nref, sheared, precision)
+    inv = g.get_matrix_diagonal_inverse().double().cpu().numpy()
+    diag = o.diagonal()  # unit-vector probing of the oracle
+    assert rel(inv, 1.0 / diag) <= (1e-12 if precision else 1e-6)
+    rng = np.random.default_rng(7)
+    n = g.m()
+    b, x0, x1 = rng.random(n), rng.random(n), rng.random(n)
+    f1, f2 = 0.6, 0.2  # matvec_dg_cheby/program.cc:119-121
+    db = torch.tensor(b, dtype=g.dtype, device="cuda")
+    sol = torch.tensor(x1, dtype=g.dtype, device="cuda")
+    old = torch.tensor(x0, dtype=g.dtype, device="cuda")
+    g.vmult_with_chebyshev_update(db, 2, f1, f2, sol, old)
+    ref = (1 + f1) * x1 - f1 * x0 + f2 / diag * (b - o.vmult(x1))
+    assert rel(old.double().cpu().numpy(), ref) <= 2 * TOL[precision]
+    old = torch.tensor(x0, dtype=g.dtype, device="cuda")
+    g.vmult_with_chebyshev_update(db, 1, f1, f2, sol, old)
+    ref = (1 + f1) * x1 + f2 / diag * (b - o.vmult(x1))
+    assert rel(old.double().cpu().numpy(), ref) <= 2 * TOL[precision]
+    g.vmult_with_chebyshev_update(db, 0, f1, f2, sol, old)
+    assert rel(sol.double().cpu().numpy(), f2 / diag * b) <= 2 * TOL[precision]
+
+
+def test_properties_at_scale(mgb, torch):
+    """131 M DoF (the matvec_dg benchmark size): symmetry and linearity of the kernel, float against double"""
+    g = mgb.LaplaceOperatorDG(4, (2, 2, 1), 6, precision=1)   # s = 20: 128 x 128 x 64 cells
+    n = g.m()
+    assert n == 131072000
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.rand(n, dtype=torch.float64, device="cuda", generator=gen)
+    y = torch.rand(n, dtype=torch.float64, device="cuda", generator=gen)
+    Ax, Ay = torch.empty_like(x), torch.empty_like(x)
+    g.vmult(Ax, x)
+    g.vmult(Ay, y)
+    xAy, yAx = torch.dot(x, Ay).item(), torch.dot(y, Ax).item()
+    assert abs(xAy - yAx) <= 1e-11 * abs(xAy)
+    assert torch.dot(x, Ax).item() > 0
+    gf = mgb.LaplaceOperatorDG(4, (2, 2, 1), 6, precision=0)
+    Axf = torch.empty(n, dtype=torch.float32, device="cuda")
+    gf.vmult(Axf, x.float())
+    assert (Axf.double() - Ax).abs().max().item() <= 1e-5 * Ax.abs().max().item()
+
+
+def test_vmult_host(mgb, orc, torch):
+    g, o = make(mgb, orc, 4, (2, 1, 1), 0, True, 1)
+    x = np.random.default_rng(3).random(g.m())
+    y = np.zeros_like(x)
+    g.vmult_host(y, x)
+    assert rel(y, o.vmult(x)) <= 1e-12
