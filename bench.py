@@ -349,6 +349,22 @@ def report(args, r):
     return line
 
 
+def dg_lines(r):
+    """BASELINE config 4 (secondary lines, one GPU): FE_DGQ<3>(4) SIP Laplacian on the 131 M DoF mesh of
+    matvec_dg/program.cc (s = 20), double vmult with the reference's 3 N bytes/DoF model (:204) and the float
+    fused Chebyshev update of matvec_dg_cheby/program.cc (5 N bytes/DoF, :178)."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import time_dg
+    r["s"].close()          # free the FE_Q solver's vectors first
+    torch.cuda.empty_cache()
+    out = time_dg.run(20, DEGREE, reps=10)
+    for v in out.values():
+        v["frac_hbm"] = v["gbs"] / r["hbm_gbs"]
+    out["workload"] = "matvec_dg s=20: 128x128x64 cells, FE_DGQ(4), affine sheared mesh, 131072000 DoF"
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -357,6 +373,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--cells", type=int, default=128, help="cells per direction and GPU (power of two)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-dg", action="store_true", help="skip the DG operator lines (BASELINE config 4)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     if args.impl == "reference":
@@ -372,6 +389,8 @@ def main():
                 "sample": "solve_cg on 32^3 cells = %d DoF, 2 timed solves, oracle/mg_oracle.cpp, %d OpenMP threads"
                           % (c["n_dofs"], c["cores"]),
                 "matvec_fp64_dofs_per_s": c["matvec_fp64_dofs_per_s"], "cg_iterations": c["iterations"]}
+        if r["world"] == 1 and not args.no_dg:
+            line["dg"] = dg_lines(r)
         print(json.dumps(line), flush=True)
     if r["dist"] is not None:
         r["dist"].barrier()

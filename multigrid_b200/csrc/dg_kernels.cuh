@@ -68,6 +68,7 @@ namespace mgb
     static constexpr int CPB = TPC >= 128 ? 1 : 128 / TPC;   // cells per block
     static constexpr int NT  = TPC * CPB;
     static constexpr int PER_CELL = 5 * n3 + 14 * n2;        // shared-memory elements per cell
+    static constexpr int TABLES   = 2 * n2 + n;              // S, G, w indexed by the lane (block-wide copy)
   };
 
   template <int TPC>
@@ -122,7 +123,17 @@ namespace mgb
     constexpr int TPC = C::TPC;
     extern __shared__ __align__(16) unsigned char dg_smem_raw[];
     const int slot = threadIdx.x / TPC, t = threadIdx.x % TPC;
-    T        *u_s  = reinterpret_cast<T *>(dg_smem_raw) + slot * C::PER_CELL;
+    // tables that the face sweeps index with the lane's (a,b): shared memory serves divergent indices,
+    // the constant bank (kernel parameters) only uniform ones
+    T *S_s = reinterpret_cast<T *>(dg_smem_raw), *G_s = S_s + n2, *w_s = G_s + n2;
+    for (int i = threadIdx.x; i < n2; i += C::NT)
+      {
+        S_s[i] = Tb.S[i];
+        G_s[i] = Tb.G[i];
+      }
+    if (threadIdx.x < n)
+      w_s[threadIdx.x] = Tb.w[threadIdx.x];
+    T        *u_s  = reinterpret_cast<T *>(dg_smem_raw) + C::TABLES + slot * C::PER_CELL;
     T        *y_s  = u_s + n3;
     T        *w0   = y_s + n3;
     T        *w1   = w0 + n3;
@@ -142,7 +153,7 @@ namespace mgb
     if (valid)
       for (int i = t; i < n3; i += TPC)
         u_s[i] = src[(size_t)c * n3 + i];
-    cell_sync<TPC>(slot);
+    __syncthreads(); // tables visible to all cells of the block
 
     // ================= cell integral: collocation at the Gauss points
     T yz[n]; // result pencil along z at (i,j) = (a,b)
@@ -212,7 +223,7 @@ namespace mgb
           for (int k = 0; k < n; ++k)
             {
               const int idx = k * n2 + b * n + a;
-              const T   W   = Tb.w[a] * Tb.w[b] * Tb.w[k];
+              const T   W   = w_s[a] * w_s[b] * Tb.w[k];
               const T   gx = w1[idx], gy = w2[idx], g2 = gz[k];
               w1[idx]       = W * (A.gt[0] * gx + A.gt[3] * gy + A.gt[4] * g2);
               w2[idx]       = W * (A.gt[3] * gx + A.gt[1] * gy + A.gt[5] * g2);
@@ -335,7 +346,7 @@ namespace mgb
 #pragma unroll
                 for (int i = 0; i < n; ++i)
                   {
-                    const T Sv = Tb.S[a * n + i], Gv = Tb.G[a * n + i];
+                    const T Sv = S_s[a * n + i], Gv = G_s[a * n + i];
                     sj += Sv * F[(3 * s + 0) * n2 + b * n + i];
                     sds += Sv * F[(3 * s + 1) * n2 + b * n + i];
                     const T tv = F[(3 * s + 2) * n2 + b * n + i];
@@ -351,7 +362,7 @@ namespace mgb
         cell_sync<TPC>(slot);
         if (active)
           { // sweep along b: thread (qa, qb); flux at the face Gauss point
-            const T wJ = A.area[d] * Tb.w[a] * Tb.w[b];
+            const T wJ = A.area[d] * w_s[a] * w_s[b];
 #pragma unroll
             for (int s = 0; s < 2; ++s)
               {
@@ -359,7 +370,7 @@ namespace mgb
 #pragma unroll
                 for (int i = 0; i < n; ++i)
                   {
-                    const T Sv = Tb.S[b * n + i], Gv = Tb.G[b * n + i];
+                    const T Sv = S_s[b * n + i], Gv = G_s[b * n + i];
                     J += Sv * H[(4 * s + 0) * n2 + i * n + a];
                     DS += Sv * H[(4 * s + 1) * n2 + i * n + a];
                     T2 += Gv * H[(4 * s + 2) * n2 + i * n + a];
@@ -381,7 +392,7 @@ namespace mgb
 #pragma unroll
                 for (int q = 0; q < n; ++q)
                   {
-                    const T Sv = Tb.S[q * n + b], Gv = Tb.G[q * n + b];
+                    const T Sv = S_s[q * n + b], Gv = G_s[q * n + b];
                     const T r1 = F[(3 * s + 0) * n2 + q * n + a], r2 = F[(3 * s + 1) * n2 + q * n + a];
                     a1 += Sv * r1;
                     a2 += Sv * r2;
@@ -405,7 +416,7 @@ namespace mgb
 #pragma unroll
                 for (int q = 0; q < n; ++q)
                   {
-                    const T Sv = Tb.S[q * n + a], Gv = Tb.G[q * n + a];
+                    const T Sv = S_s[q * n + a], Gv = G_s[q * n + a];
                     const T h0 = H[(4 * s + 0) * n2 + b * n + q], h1 = H[(4 * s + 1) * n2 + b * n + q];
                     V += Sv * h0 + g_da * Gv * h1;
                     N += Sv * h1;
@@ -457,7 +468,7 @@ namespace mgb
   launch_dg_apply(const DGArgs<T> &A, const DGTables<T, p + 1> &Tb, cudaStream_t stream)
   {
     using C           = DGCfg<p>;
-    const size_t smem = (size_t)C::PER_CELL * C::CPB * sizeof(T);
+    const size_t smem = (size_t)(C::TABLES + C::PER_CELL * C::CPB) * sizeof(T);
     static bool  first = true;
     if (first)
       {
