@@ -209,7 +209,17 @@ int mgb_dg_timer_start(mgb_dg h);
 int mgb_dg_timer_stop(mgb_dg h, double *ms);
 int64_t mgb_dg_launch_count(mgb_dg h);
 
-/* plain host<->device helpers so that a C/C++ caller needs no CUDA runtime of its own */
+/* The subset of LinearAlgebra::distributed::Vector<Number> the drivers use (poisson_cube/program.cc:262-380,
+ * multigrid_solver.h:54-67): device vectors of one level in the precision given; sums run over the owned
+ * entries of all ranks.  dot: a . b (l2_norm = sqrt(dot(v,v)));  sadd: y = sy y + ax x;  set: y = value;
+ * update_ghost_values: refresh the ghost planes of a z-slab (no-op on one GPU).                       */
+int mgb_vec_dot(mgb_solver s, int level, int precision, const void *a, const void *b, double *result);
+int mgb_vec_sadd(mgb_solver s, int level, int precision, void *y, double sy, double ax, const void *x);
+int mgb_vec_set(mgb_solver s, int level, int precision, void *y, double value);
+int mgb_vec_update_ghost_values(mgb_solver s, int level, int precision, void *v);
+
+/* plain host<->device helpers so that a C/C++ caller needs no CUDA runtime of its own; `s` may be NULL (vectors
+ * of the DG operator): current device, synchronous */
 int mgb_device_alloc(mgb_solver s, size_t bytes, void **dev_ptr);
 int mgb_device_free(mgb_solver s, void *dev_ptr);
 int mgb_copy_to_device(mgb_solver s, void *dst_dev, const void *src_host, size_t bytes);

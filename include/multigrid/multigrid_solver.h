@@ -1,0 +1,146 @@
+// multigrid::MultigridSolver<dim, fe_degree, Number, Number2> -- same name, template parameters and method names
+// as common/multigrid_solver.h:96-782 of the reference; bodies are calls into the C ABI (include/mgb200.h).
+// DoFHandler / Function objects of the reference's constructor (multigrid_solver.h:100-106) are replaced by a
+// MeshDescription (box generator + refinements, poisson_cube/program.cc:498-570) and a problem id whose analytic
+// solution, right-hand side and coefficient are evaluated on the device (poisson_cube/program.cc:79-144).
+#ifndef MULTIGRID_MULTIGRID_SOLVER_H
+#define MULTIGRID_MULTIGRID_SOLVER_H
+
+#include <cstdio>
+#include <utility>
+
+#include "laplace_operator.h"
+
+namespace multigrid
+{
+  struct MeshDescription
+  {
+    int    n_subdivisions[3] = {1, 1, 1}; // GridGenerator::subdivided_hyper_cube / _rectangle
+    int    n_refinements     = 0;         // Triangulation::refine_global
+    double lower[3] = {-0.9, -0.9, -0.9}, upper[3] = {1., 1., 1.};
+    int    problem = MGB_PROBLEM_CUBE_SINE;
+    // one process per GPU (MPI_COMM_WORLD of the reference): rank, size and the id of mgb_comm_unique_id()
+    int           comm_rank = 0, comm_size = 1;
+    unsigned char comm_id[128] = {};
+    int           device = 0;
+  };
+
+  template <int dim, int fe_degree, typename Number = float, typename Number2 = double>
+  class MultigridSolver
+  {
+    static_assert(dim == 3, "the B200 path implements dim = 3");
+    static_assert(std::is_same<Number, float>::value && std::is_same<Number2, double>::value,
+                  "mixed precision as the reference: float V-cycle, double outer solver (poisson_cube/program.cc:76-77)");
+
+  public:
+    typedef DeviceVector<Number2> VectorType;
+
+    // multigrid_solver.h:100-106
+    MultigridSolver(const MeshDescription &mesh, const unsigned int degree_pre, const unsigned int degree_post,
+                    const unsigned int n_cycles = 1)
+    {
+      mgb_options o;
+      mgb_default_options(&o);
+      o.degree = fe_degree;
+      for (int d = 0; d < 3; ++d)
+        {
+          o.n_subdivisions[d] = mesh.n_subdivisions[d];
+          o.lower[d]          = mesh.lower[d];
+          o.upper[d]          = mesh.upper[d];
+        }
+      o.n_refinements = mesh.n_refinements;
+      o.degree_pre    = (int)degree_pre;
+      o.degree_post   = (int)degree_post;
+      o.n_cycles      = (int)n_cycles;
+      o.problem       = mesh.problem;
+      o.device        = mesh.device;
+      o.comm_rank     = mesh.comm_rank;
+      o.comm_size     = mesh.comm_size;
+      for (int i = 0; i < 128; ++i)
+        o.comm_id[i] = mesh.comm_id[i];
+      check(mgb_solver_create(&o, &s_));
+    }
+    MultigridSolver(const MultigridSolver &) = delete;
+    MultigridSolver &operator=(const MultigridSolver &) = delete;
+    ~MultigridSolver()
+    {
+      if (s_)
+        mgb_solver_destroy(s_);
+    }
+
+    mgb_solver   handle() const { return s_; }
+    unsigned int n_levels() const { return (unsigned int)mgb_solver_n_levels(s_); }
+
+    // level operators: matrix[level] (float) and matrix_dp[level] (double), multigrid_solver.h:740-745
+    LaplaceOperator<dim, fe_degree, Number>
+    get_matrix(const int level = -1) const
+    {
+      LaplaceOperator<dim, fe_degree, Number> op;
+      op.initialize(s_, level);
+      return op;
+    }
+    LaplaceOperator<dim, fe_degree, Number2>
+    get_matrix_dp(const int level = -1) const
+    {
+      LaplaceOperator<dim, fe_degree, Number2> op;
+      op.initialize(s_, level);
+      return op;
+    }
+
+    // multigrid_solver.h:387-476: full multigrid cycle, returns the residual reduction rate on the finest level
+    double
+    solve(const bool do_analyze)
+    {
+      double rate = 0;
+      check(mgb_solver_solve(s_, do_analyze ? 1 : 0, &rate, nullptr));
+      return rate;
+    }
+    // multigrid_solver.h:483-493: CG preconditioned by one V-cycle; (iterations, reduction per iteration)
+    std::pair<unsigned int, double>
+    solve_cg()
+    {
+      unsigned int its  = 0;
+      double       rate = 0;
+      check(mgb_solver_solve_cg(s_, &its, &rate));
+      return std::make_pair(its, rate);
+    }
+    // multigrid_solver.h:498-510: one V-cycle as preconditioner
+    void vmult(VectorType &dst, const VectorType &src) const { check(mgb_solver_vcycle(s_, dst.begin(), src.begin())); }
+    // multigrid_solver.h:624-637
+    void do_matvec() { check(mgb_solver_do_matvec(s_)); }
+    void do_matvec_smoother() { check(mgb_solver_do_matvec_smoother(s_)); }
+    // multigrid_solver.h:298-343 (volume-normalised L2 error against the analytic solution)
+    double
+    compute_l2_error(const int level = -1) const
+    {
+      double e = 0;
+      check(mgb_solver_l2_error(s_, level, &e));
+      return e;
+    }
+    // multigrid_solver.h:348-371
+    void
+    print_wall_times()
+    {
+      const unsigned int  nl = n_levels();
+      std::vector<double> t(6 * nl);
+      check(mgb_solver_timings(s_, t.data(), 1));
+      std::printf("level  smoother    mg_mv       mg_vec      restrict    prolongate  inhomBC\n");
+      for (unsigned int l = 1; l < nl; ++l)
+        std::printf("L%-2u    %-12.4g%-12.4g%-12.4g%-12.4g%-12.4g%-12.4g\n", l, t[6 * l + 5], t[6 * l + 0], t[6 * l + 4],
+                    t[6 * l + 1], t[6 * l + 2], t[6 * l + 3]);
+    }
+    // multigrid_solver.h:376-382 (host copy in the library's numbering)
+    std::vector<double>
+    get_solution() const
+    {
+      std::vector<double> sol((std::size_t)mgb_solver_n_dofs(s_, -1));
+      check(mgb_solver_get_solution(s_, sol.data()));
+      return sol;
+    }
+    void synchronize() const { check(mgb_solver_sync(s_)); }
+
+  private:
+    mgb_solver s_ = nullptr;
+  };
+} // namespace multigrid
+#endif

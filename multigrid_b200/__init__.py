@@ -112,6 +112,10 @@ SYMBOLS = {
     "mgb_transfer_prolongate_and_add": (_i, [_vp, _i, _vp, _vp]),
     "mgb_transfer_restrict_and_add": (_i, [_vp, _i, _vp, _vp]),
     "mgb_transfer_prolongate_no_boundary": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_vec_dot": (_i, [_vp, _i, _i, _vp, _vp, _dp]),
+    "mgb_vec_sadd": (_i, [_vp, _i, _i, _vp, _d, _d, _vp]),
+    "mgb_vec_set": (_i, [_vp, _i, _i, _vp, _d]),
+    "mgb_vec_update_ghost_values": (_i, [_vp, _i, _i, _vp]),
     "mgb_device_alloc": (_i, [_vp, C.c_size_t, C.POINTER(_vp)]),
     "mgb_device_free": (_i, [_vp, _vp]),
     "mgb_copy_to_device": (_i, [_vp, _vp, _vp, C.c_size_t]),

@@ -1556,6 +1556,26 @@ namespace mgb
       return std::make_pair(it, it > 0 ? std::pow(res / res0, 1. / it) : 0.);
     }
   };
+  // ---- the subset of LinearAlgebra::distributed::Vector the drivers use (poisson_cube/program.cc, multigrid_solver.h)
+  template <typename T>
+  void
+  vec_ops(MultigridSolver &m, const int level, const int op, void *yv, const void *xv, const double a, const double b,
+          double *result)
+  {
+    Level       &lv = *m.levels[level];
+    const size_t N  = lv.d.n_dofs;
+    T           *y  = static_cast<T *>(yv);
+    const T     *x  = static_cast<const T *>(xv);
+    const T      ta = (T)a, tb = (T)b;
+    switch (op)
+      {
+        case 0: *result = dot(m.ctx, y, x, lv.owned()); break;                                        // y . x
+        case 1: foreach (m.ctx, N, [=] __device__(size_t i) { y[i] = ta * y[i] + tb * x[i]; }); break; // sadd
+        case 2: foreach (m.ctx, N, [=] __device__(size_t i) { y[i] = ta; }); break;                    // = a
+        default: throw std::runtime_error("unknown vector operation");
+      }
+  }
+
 } // namespace mgb
 
 // ====================================================================== C ABI
@@ -2194,9 +2214,69 @@ extern "C"
   }
 
   int
+  mgb_vec_dot(mgb_solver s, int level, int precision, const void *a, const void *b, double *result)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (precision == MGB_F64)
+      vec_ops<double>(m, level, 0, const_cast<void *>(a), b, 0, 0, result);
+    else
+      vec_ops<float>(m, level, 0, const_cast<void *>(a), b, 0, 0, result);
+    MGB_CATCH
+  }
+
+  int
+  mgb_vec_sadd(mgb_solver s, int level, int precision, void *y, double sy, double ax, const void *x)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    double dummy;
+    if (precision == MGB_F64)
+      vec_ops<double>(m, level, 1, y, x, sy, ax, &dummy);
+    else
+      vec_ops<float>(m, level, 1, y, x, sy, ax, &dummy);
+    MGB_CATCH
+  }
+
+  int
+  mgb_vec_set(mgb_solver s, int level, int precision, void *y, double value)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    double dummy;
+    if (precision == MGB_F64)
+      vec_ops<double>(m, level, 2, y, nullptr, value, 0, &dummy);
+    else
+      vec_ops<float>(m, level, 2, y, nullptr, value, 0, &dummy);
+    MGB_CATCH
+  }
+
+  int
+  mgb_vec_update_ghost_values(mgb_solver s, int level, int precision, void *v)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (precision == MGB_F64)
+      m.levels[level]->update_ghosts(static_cast<double *>(v));
+    else
+      m.levels[level]->update_ghosts(static_cast<float *>(v));
+    MGB_CATCH
+  }
+
+  int
   mgb_device_alloc(mgb_solver s, size_t bytes, void **dev_ptr)
   {
     MGB_TRY
+    if (!s) // no solver (DG operator vectors): current device, synchronous
+      {
+        MGB_CUDA_CHECK(cudaMalloc(dev_ptr, bytes));
+        MGB_CUDA_CHECK(cudaMemset(*dev_ptr, 0, bytes));
+        return 0;
+      }
     MGB_CUDA_CHECK(cudaSetDevice(S(s).ctx.device));
     MGB_CUDA_CHECK(cudaMalloc(dev_ptr, bytes));
     MGB_CUDA_CHECK(cudaMemsetAsync(*dev_ptr, 0, bytes, S(s).ctx.stream));
@@ -2207,7 +2287,10 @@ extern "C"
   mgb_device_free(mgb_solver s, void *dev_ptr)
   {
     MGB_TRY
-    S(s).ctx.sync();
+    if (s)
+      S(s).ctx.sync();
+    else
+      MGB_CUDA_CHECK(cudaDeviceSynchronize());
     MGB_CUDA_CHECK(cudaFree(dev_ptr));
     MGB_CATCH
   }
@@ -2216,6 +2299,12 @@ extern "C"
   mgb_copy_to_device(mgb_solver s, void *dst_dev, const void *src_host, size_t bytes)
   {
     MGB_TRY
+    if (!s)
+      {
+        MGB_CUDA_CHECK(cudaDeviceSynchronize());
+        MGB_CUDA_CHECK(cudaMemcpy(dst_dev, src_host, bytes, cudaMemcpyHostToDevice));
+        return 0;
+      }
     MGB_CUDA_CHECK(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, S(s).ctx.stream));
     S(s).ctx.sync();
     MGB_CATCH
@@ -2225,6 +2314,12 @@ extern "C"
   mgb_copy_to_host(mgb_solver s, void *dst_host, const void *src_dev, size_t bytes)
   {
     MGB_TRY
+    if (!s)
+      {
+        MGB_CUDA_CHECK(cudaDeviceSynchronize());
+        MGB_CUDA_CHECK(cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
+        return 0;
+      }
     MGB_CUDA_CHECK(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, S(s).ctx.stream));
     S(s).ctx.sync();
     MGB_CATCH

@@ -1,0 +1,63 @@
+// What a driver of the reference looks like after switching to the B200 library: the calls of
+// poisson_cube/program.cc:262-380 (solve, solve_cg, matvec timing, L2 error) on multigrid::MultigridSolver, a CG
+// iteration by hand on multigrid::LaplaceOperator / DeviceVector, and the DG operator of matvec_dg/program.cc.
+// Built by tests/test_cpp_adapter.py with g++ (no nvcc, no CUDA headers): only include/ and libmgb200.so.
+#include <cstdio>
+#include <cstdlib>
+
+#include "multigrid/laplace_operator_dg.h"
+#include "multigrid/multigrid_solver.h"
+
+int
+main(int argc, char **argv)
+{
+  try
+    {
+      constexpr int               degree = 4;
+      multigrid::MeshDescription mesh;
+      mesh.n_refinements = argc > 1 ? std::atoi(argv[1]) : 3;
+      multigrid::MultigridSolver<3, degree, float, double> solver(mesh, 3, 3, 2);
+      const double                                         rate = solver.solve(false);
+      const double                                         e_fmg = solver.compute_l2_error();
+      const std::pair<unsigned int, double>                cg = solver.solve_cg();
+      const double                                         e_cg = solver.compute_l2_error();
+      std::printf("fmg_reduction %.6e fmg_l2 %.6e cg_its %u cg_reduction %.6e cg_l2 %.6e\n", rate, e_fmg, cg.first, cg.second, e_cg);
+
+      // operator concept: q = A p, <p, q> and a residual through the level operator
+      auto                         A = solver.get_matrix_dp();
+      multigrid::DeviceVector<double> p, q, r;
+      A.initialize_dof_vector(p);
+      A.initialize_dof_vector(q);
+      A.initialize_dof_vector(r);
+      p = 1.0;
+      A.vmult(q, p);
+      const double pq = p * q;
+      A.vmult_residual(q, p, r); // r = q - A p = 0
+      std::printf("operator m %zu pAp %.12e residual_norm %.3e\n", A.m(), pq, (double)r.l2_norm());
+
+      // DG operator on the mesh of matvec_dg/program.cc, 2 refinements
+      mgb_dg_options o;
+      mgb_dg_default_options(&o);
+      o.n_refinements = 2;
+      multigrid::LaplaceOperatorCompactCombine<3, degree, double, 1> dg;
+      dg.reinit(o);
+      multigrid::DGVector<double> x, y;
+      dg.initialize_dof_vector(x);
+      dg.initialize_dof_vector(y);
+      std::vector<double> hx(dg.m(), 1.0);
+      x.import_from_host(hx);
+      dg.vmult(y, x);
+      dg.synchronize();
+      const std::vector<double> hy = y.export_to_host();
+      double                    xAx = 0;
+      for (std::size_t i = 0; i < hy.size(); ++i)
+        xAx += hx[i] * hy[i];
+      std::printf("dg m %zu penalty_x %.6e xAx %.12e\n", dg.m(), (double)dg.get_penalty(0, 0), xAx);
+    }
+  catch (const std::exception &e)
+    {
+      std::fprintf(stderr, "Exception: %s\n", e.what());
+      return 1;
+    }
+  return 0;
+}
