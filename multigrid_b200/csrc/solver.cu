@@ -70,6 +70,7 @@ namespace mgb
                               cudaStream_t)                                                           = nullptr;
     ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t)         = nullptr;
     ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t)               = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)()                                                                      = nullptr;
     ncclResult_t (*GroupEnd)()                                                                        = nullptr;
     const char *(*GetErrorString)(ncclResult_t)                                                       = nullptr;
@@ -96,6 +97,7 @@ namespace mgb
       n.CommInitRank   = reinterpret_cast<decltype(n.CommInitRank)>(sym("ncclCommInitRank"));
       n.CommDestroy    = reinterpret_cast<decltype(n.CommDestroy)>(sym("ncclCommDestroy"));
       n.AllReduce      = reinterpret_cast<decltype(n.AllReduce)>(sym("ncclAllReduce"));
+      n.AllGather      = reinterpret_cast<decltype(n.AllGather)>(sym("ncclAllGather"));
       n.Send           = reinterpret_cast<decltype(n.Send)>(sym("ncclSend"));
       n.Recv           = reinterpret_cast<decltype(n.Recv)>(sym("ncclRecv"));
       n.GroupStart     = reinterpret_cast<decltype(n.GroupStart)>(sym("ncclGroupStart"));
@@ -111,6 +113,153 @@ namespace mgb
     }
   };
 
+  // ------------------------------------------------------------------ peer-to-peer exchange over NVLink
+  // Every rank owns an "arena" (one cudaMalloc, IPC-mapped by all ranks of the node): counters, all-reduce
+  // slots and double-buffered receive buffers for the ghost planes.  A ghost exchange is two kernels per
+  // rank, no NCCL call and no host round trip:
+  //   k_p2p (push): waits for the neighbour's acknowledgement of the message before last, stores the
+  //                 boundary planes STRAIGHT INTO THE NEIGHBOUR'S receive buffer (remote stores over
+  //                 NVLink), fences, and the last block bumps the neighbour's data counter;
+  //   k_p2p (pull): waits on the own data counters, copies the planes into the ghost range of the vector
+  //                 and acknowledges.
+  // The all-reduce of the CG scalars is one single-warp kernel: every rank stores its partial sums into its
+  // slot on every peer, bumps a counter there, waits for all peers and adds the slots in rank order (so all
+  // ranks get bit-identical sums).  All waits are bounded (about 2 s) and raise an error flag instead of
+  // hanging the GPU.
+  namespace p2p
+  {
+    constexpr size_t FLAG_STRIDE = 128;  // one counter per 128-byte line
+    constexpr int    F_UP_DATA = 0, F_DN_DATA = 1, F_UP_ACK = 2, F_DN_ACK = 3, F_RED = 8; // F_RED + peer
+    constexpr size_t RED_OFFSET = 8192;  // [parity][rank][4] doubles
+    constexpr size_t BUF_OFFSET = 16384; // up[0], up[1], dn[0], dn[1]
+    constexpr int    MAX_RANKS  = 16;
+    constexpr long long TIMEOUT_CYCLES = 4000000000ll;
+
+    struct Msg
+    {
+      const uint32_t    *src = nullptr;
+      uint32_t          *dst = nullptr;
+      size_t             words = 0;
+      volatile uint32_t *wait_flag = nullptr;   // local counter that must reach wait_value first
+      uint32_t           wait_value = 0;
+      volatile uint32_t *signal_flag = nullptr; // counter (usually on the peer) set afterwards
+      uint32_t           signal_value = 0;
+    };
+
+    struct Peers
+    {
+      unsigned char *arena[MAX_RANKS];
+    };
+
+    __device__ int g_failed = 0; // sticky: after the first time-out no wait spins again
+
+    __device__ __forceinline__ void
+    spin_until(volatile uint32_t *flag, const uint32_t value, int *error)
+    {
+      const long long t0 = clock64();
+      while (*flag < value)
+        if (*reinterpret_cast<volatile int *>(&g_failed) || clock64() - t0 > TIMEOUT_CYCLES)
+          {
+            g_failed = 1;
+            *error   = 1;
+            break;
+          }
+    }
+
+    // 16-byte stores to the (256-byte aligned) buffers; the vector side is only element-aligned and is read
+    // or written with scalar accesses
+    __device__ __forceinline__ void
+    copy_words(const Msg &m)
+    {
+      const size_t start = blockIdx.x * (size_t)blockDim.x + threadIdx.x, step = (size_t)gridDim.x * blockDim.x;
+      const size_t quads = m.words / 4;
+      if ((reinterpret_cast<uintptr_t>(m.dst) & 15) == 0)
+        {
+          uint4 *d4 = reinterpret_cast<uint4 *>(m.dst);
+          for (size_t i = start; i < quads; i += step)
+            d4[i] = make_uint4(m.src[4 * i], m.src[4 * i + 1], m.src[4 * i + 2], m.src[4 * i + 3]);
+        }
+      else if ((reinterpret_cast<uintptr_t>(m.src) & 15) == 0)
+        {
+          const uint4 *s4 = reinterpret_cast<const uint4 *>(m.src);
+          for (size_t i = start; i < quads; i += step)
+            {
+              const uint4 v    = s4[i];
+              m.dst[4 * i]     = v.x;
+              m.dst[4 * i + 1] = v.y;
+              m.dst[4 * i + 2] = v.z;
+              m.dst[4 * i + 3] = v.w;
+            }
+        }
+      else
+        for (size_t i = start; i < 4 * quads; i += step)
+          m.dst[i] = m.src[i];
+      for (size_t i = 4 * quads + start; i < m.words; i += step)
+        m.dst[i] = m.src[i];
+    }
+
+    __global__ void
+    k_p2p(const Msg a, const Msg b, unsigned int *done, int *error)
+    {
+      if (threadIdx.x == 0)
+        {
+          if (a.wait_flag)
+            spin_until(a.wait_flag, a.wait_value, error);
+          if (b.wait_flag)
+            spin_until(b.wait_flag, b.wait_value, error);
+          __threadfence_system();
+        }
+      __syncthreads();
+      copy_words(a);
+      copy_words(b);
+      __syncthreads();
+      if (threadIdx.x == 0)
+        {
+          __threadfence_system(); // cumulative: orders the stores of the whole block (bar.sync above) before the ticket
+          const unsigned int ticket = atomicAdd(done, 1u);
+          if (ticket == gridDim.x - 1)
+            {
+              *done = 0;
+              __threadfence_system();
+              if (a.signal_flag)
+                *a.signal_flag = a.signal_value;
+              if (b.signal_flag)
+                *b.signal_flag = b.signal_value;
+            }
+        }
+    }
+
+    // one warp; `k` = 1-based number of this all-reduce
+    __global__ void
+    k_allreduce(const Peers peers, const int rank, const int n_ranks, const int count, const uint32_t k, double *inout,
+                int *error)
+    {
+      const int j      = threadIdx.x;
+      const int parity = k & 1u;
+      if (j < n_ranks)
+        {
+          volatile double *slot =
+            reinterpret_cast<volatile double *>(peers.arena[j] + RED_OFFSET) + (parity * MAX_RANKS + rank) * 4;
+          for (int c = 0; c < count; ++c)
+            slot[c] = inout[c];
+          __threadfence_system();
+          *reinterpret_cast<volatile uint32_t *>(peers.arena[j] + (F_RED + rank) * FLAG_STRIDE) = k;
+          spin_until(reinterpret_cast<volatile uint32_t *>(peers.arena[rank] + (F_RED + j) * FLAG_STRIDE), k, error);
+          __threadfence_system();
+        }
+      __syncthreads();
+      if (j < count)
+        {
+          const volatile double *slots =
+            reinterpret_cast<const volatile double *>(peers.arena[rank] + RED_OFFSET) + parity * MAX_RANKS * 4;
+          double sum = 0;
+          for (int r = 0; r < n_ranks; ++r)
+            sum += slots[r * 4 + j];
+          inout[j] = sum;
+        }
+    }
+  } // namespace p2p
+
   // ------------------------------------------------------------------ context
   struct Ctx
   {
@@ -118,6 +267,13 @@ namespace mgb
     int          rank = 0, n_ranks = 1; // z-slab decomposition over the GPUs of one node
     ncclComm_t   comm     = nullptr;
     int64_t      exchanges = 0;          // ghost exchanges + all-reduces issued so far
+    // peer-to-peer path (MGB200_P2P=1; the default is NCCL send/recv, which measured faster)
+    bool           p2p_on = false;
+    p2p::Peers     peers;
+    size_t         p2p_buf_bytes = 0;
+    uint32_t       n_up_sent = 0, n_dn_sent = 0, n_up_recv = 0, n_dn_recv = 0, n_reduce = 0;
+    unsigned int  *p2p_done  = nullptr; // ticket counter of k_p2p
+    int           *p2p_error = nullptr; // mapped pinned host memory: set by a wait that timed out
     cudaStream_t comm_stream = nullptr;  // ghost exchange overlapped with the interior cell layers
     cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
     bool         overlap = true;
@@ -244,10 +400,84 @@ namespace mgb
       MGB_CUDA_CHECK(cudaEventRecord(ev_join, comm_stream));
       MGB_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_join, 0));
     }
+    unsigned char *flag_at(const int r, const int f) const { return peers.arena[r] + f * p2p::FLAG_STRIDE; }
+    unsigned char *buffer_at(const int r, const int channel /*0 up, 1 down*/, const uint32_t k) const
+    {
+      return peers.arena[r] + p2p::BUF_OFFSET + (size_t)(2 * channel + (k & 1u)) * p2p_buf_bytes;
+    }
+
+    // allocate and zero the arena, exchange the IPC handles through NCCL, map the peers' arenas
+    void
+    init_p2p(const size_t max_message_bytes)
+    {
+      // opt-in: measured on 2 x B200 (profiles/r1_exchange_latency.txt) one exchange costs 21-29 us this way
+      // and 11-24 us through NCCL's grouped send/recv, so NCCL stays the default
+      const char *env = getenv("MGB200_P2P");
+      if (n_ranks <= 1 || !(env && env[0] == '1') || n_ranks > p2p::MAX_RANKS)
+        return;
+      Nccl &n         = Nccl::get();
+      p2p_buf_bytes   = (max_message_bytes + 255) / 256 * 256;
+      const size_t sz = p2p::BUF_OFFSET + 4 * p2p_buf_bytes;
+      unsigned char *mine = nullptr;
+      MGB_CUDA_CHECK(cudaMalloc(&mine, sz));
+      MGB_CUDA_CHECK(cudaMemset(mine, 0, sz));
+      MGB_CUDA_CHECK(cudaMalloc(&p2p_done, sizeof(unsigned int)));
+      MGB_CUDA_CHECK(cudaMemset(p2p_done, 0, sizeof(unsigned int)));
+      MGB_CUDA_CHECK(cudaHostAlloc(&p2p_error, sizeof(int), cudaHostAllocMapped));
+      *p2p_error = 0;
+      MGB_CUDA_CHECK(cudaDeviceSynchronize());
+      cudaIpcMemHandle_t handle;
+      MGB_CUDA_CHECK(cudaIpcGetMemHandle(&handle, mine));
+      static_assert(sizeof(handle) == 64, "cudaIpcMemHandle_t is 64 bytes");
+      unsigned char *all_dev = nullptr;
+      MGB_CUDA_CHECK(cudaMalloc(&all_dev, 64 * n_ranks));
+      MGB_CUDA_CHECK(cudaMemcpy(all_dev + 64 * rank, &handle, 64, cudaMemcpyHostToDevice));
+      n.check(n.AllGather(all_dev + 64 * rank, all_dev, 64, ncclInt8, comm, stream), "ncclAllGather");
+      MGB_CUDA_CHECK(cudaStreamSynchronize(stream));
+      std::vector<cudaIpcMemHandle_t> all(n_ranks);
+      MGB_CUDA_CHECK(cudaMemcpy(all.data(), all_dev, 64 * n_ranks, cudaMemcpyDeviceToHost));
+      MGB_CUDA_CHECK(cudaFree(all_dev));
+      bool ok = true;
+      for (int r = 0; r < n_ranks; ++r)
+        {
+          peers.arena[r] = nullptr;
+          if (r == rank)
+            peers.arena[r] = mine;
+          else if (cudaIpcOpenMemHandle(reinterpret_cast<void **>(&peers.arena[r]), all[r], cudaIpcMemLazyEnablePeerAccess) !=
+                   cudaSuccess)
+            {
+              cudaGetLastError();
+              ok = false;
+            }
+        }
+      // all ranks must agree (one failed mapping anywhere -> everybody uses NCCL)
+      double flag = ok ? 0. : 1.;
+      MGB_CUDA_CHECK(cudaMemcpy(scal_dev, &flag, sizeof(double), cudaMemcpyHostToDevice));
+      n.check(n.AllReduce(scal_dev, scal_dev, 1, ncclDouble, ncclSum, comm, stream), "ncclAllReduce");
+      MGB_CUDA_CHECK(cudaStreamSynchronize(stream));
+      MGB_CUDA_CHECK(cudaMemcpy(&flag, scal_dev, sizeof(double), cudaMemcpyDeviceToHost));
+      p2p_on = flag == 0.;
+    }
+
+    void
+    check_p2p_error() const
+    {
+      if (p2p_error && *p2p_error)
+        throw std::runtime_error("a peer-to-peer wait timed out: the ranks are out of step (or a peer died)");
+    }
+
     // sum of `count` doubles over the ranks, in place, ordered on the solver stream
     void
     all_reduce_sum(double *dev, const int count)
     {
+      if (p2p_on && count <= 4)
+        {
+          ++n_reduce;
+          p2p::k_allreduce<<<1, 32, 0, stream>>>(peers, rank, n_ranks, count, n_reduce, dev, p2p_error);
+          check_launch();
+          ++exchanges;
+          return;
+        }
       Nccl &n = Nccl::get();
       n.check(n.AllReduce(dev, dev, count, ncclDouble, ncclSum, comm, stream), "ncclAllReduce");
       ++exchanges;
@@ -255,6 +485,24 @@ namespace mgb
     void
     destroy()
     {
+      if (p2p_buf_bytes)
+        {
+          cudaDeviceSynchronize();
+          for (int r = 0; r < n_ranks; ++r)
+            if (peers.arena[r])
+              {
+                if (r == rank)
+                  cudaFree(peers.arena[r]);
+                else
+                  cudaIpcCloseMemHandle(peers.arena[r]);
+              }
+          if (p2p_done)
+            cudaFree(p2p_done);
+          if (p2p_error)
+            cudaFreeHost(p2p_error);
+          p2p_buf_bytes = 0;
+          p2p_on        = false;
+        }
       if (comm)
         Nccl::get().CommDestroy(comm);
       comm = nullptr;
@@ -464,6 +712,7 @@ namespace mgb
     MGB_CUDA_CHECK(cudaMemcpyAsync(
       ctx.scal_host, ctx.scal_dev, NS * sizeof(double), cudaMemcpyDeviceToHost, ctx.stream));
     ctx.sync();
+    ctx.check_p2p_error();
     for (int s = 0; s < NS; ++s)
       result[s] = ctx.scal_host[s];
   }
@@ -526,6 +775,12 @@ namespace mgb
     {
       if (!slab.distributed)
         return;
+      if (ctx->p2p_on)
+        {
+          p2p_exchange(v + plan.send_up[0], d.ztop ? plan.send_up[1] : 0, v + plan.send_dn[0], d.zg ? plan.send_dn[1] : 0,
+                       v + plan.recv_dn[0], d.zg ? plan.recv_dn[1] : 0, v + plan.recv_up[0], d.ztop ? plan.recv_up[1] : 0);
+          return;
+        }
       const cudaStream_t stream = on ? on : ctx->stream;
       Nccl &n = Nccl::get();
       n.check(n.GroupStart(), "ncclGroupStart");
@@ -543,6 +798,82 @@ namespace mgb
       ++ctx->exchanges;
     }
 
+    // One exchange over peer memory (see namespace p2p): `n_up` values at `send_up` are stored into the
+    // receive buffer of the rank above, `n_dn` values at `send_dn` into that of the rank below; then the
+    // message from below (`n_below` values) is copied to `from_below` and the one from above to `from_above`.
+    // A count of zero means "no message on this channel".  The message counters advance identically on both
+    // ends of a channel because all ranks issue the same sequence of exchanges.
+    template <typename T>
+    void
+    p2p_exchange(const T *send_up, const uint64_t n_up, const T *send_dn, const uint64_t n_dn, T *from_below,
+                 const uint64_t n_below, T *from_above, const uint64_t n_above) const
+    {
+      const bool do_send_up = n_up > 0, do_send_dn = n_dn > 0, do_recv_below = n_below > 0, do_recv_above = n_above > 0;
+      Ctx      &c = *ctx;
+      const int r = c.rank;
+      auto flag   = [&](const int rank, const int f) { return reinterpret_cast<volatile uint32_t *>(c.flag_at(rank, f)); };
+      auto launch = [&](const p2p::Msg &a, const p2p::Msg &b) {
+        const size_t words = a.words + b.words;
+        if (words == 0)
+          return;
+        const unsigned blocks = (unsigned)std::min<size_t>(std::max<size_t>(words / 8192, 1), 148);
+        p2p::k_p2p<<<blocks, 256, 0, c.stream>>>(a, b, c.p2p_done, c.p2p_error);
+        c.check_launch();
+      };
+      p2p::Msg up, dn, fb, fa;
+      if (do_send_up)
+        {
+          up.src   = reinterpret_cast<const uint32_t *>(send_up);
+          up.words = n_up * sizeof(T) / 4;
+          up.dst   = reinterpret_cast<uint32_t *>(c.buffer_at(r + 1, 0, c.n_up_sent));
+          if (c.n_up_sent >= 2)
+            {
+              up.wait_flag  = flag(r, p2p::F_UP_ACK);
+              up.wait_value = c.n_up_sent - 1;
+            }
+          up.signal_flag  = flag(r + 1, p2p::F_UP_DATA);
+          up.signal_value = ++c.n_up_sent;
+        }
+      if (do_send_dn)
+        {
+          dn.src   = reinterpret_cast<const uint32_t *>(send_dn);
+          dn.words = n_dn * sizeof(T) / 4;
+          dn.dst   = reinterpret_cast<uint32_t *>(c.buffer_at(r - 1, 1, c.n_dn_sent));
+          if (c.n_dn_sent >= 2)
+            {
+              dn.wait_flag  = flag(r, p2p::F_DN_ACK);
+              dn.wait_value = c.n_dn_sent - 1;
+            }
+          dn.signal_flag  = flag(r - 1, p2p::F_DN_DATA);
+          dn.signal_value = ++c.n_dn_sent;
+        }
+      if (up.words * 4 > c.p2p_buf_bytes || dn.words * 4 > c.p2p_buf_bytes)
+        throw std::runtime_error("ghost message larger than the peer-to-peer buffer");
+      launch(up, dn);
+      if (do_recv_below)
+        {
+          fb.src          = reinterpret_cast<const uint32_t *>(c.buffer_at(r, 0, c.n_up_recv));
+          fb.dst          = reinterpret_cast<uint32_t *>(from_below);
+          fb.words        = n_below * sizeof(T) / 4;
+          fb.wait_flag    = flag(r, p2p::F_UP_DATA);
+          fb.wait_value   = c.n_up_recv + 1;
+          fb.signal_flag  = flag(r - 1, p2p::F_UP_ACK);
+          fb.signal_value = ++c.n_up_recv;
+        }
+      if (do_recv_above)
+        {
+          fa.src          = reinterpret_cast<const uint32_t *>(c.buffer_at(r, 1, c.n_dn_recv));
+          fa.dst          = reinterpret_cast<uint32_t *>(from_above);
+          fa.words        = n_above * sizeof(T) / 4;
+          fa.wait_flag    = flag(r, p2p::F_DN_DATA);
+          fa.wait_value   = c.n_dn_recv + 1;
+          fa.signal_flag  = flag(r + 1, p2p::F_DN_ACK);
+          fa.signal_value = ++c.n_dn_recv;
+        }
+      launch(fb, fa);
+      ++c.exchanges;
+    }
+
     // Vector::compress(VectorOperation::add) for the one ghost plane that is ever written (the top plane,
     // by the restriction): it is added to the first owned plane of the rank above
     template <typename T>
@@ -551,8 +882,20 @@ namespace mgb
     {
       if (!slab.distributed)
         return;
+      T *buf = reinterpret_cast<T *>(plane_buf.p);
+      if (ctx->p2p_on)
+        {
+          // upward channel only: the plane on top travels to the rank above
+          p2p_exchange<T>(v + plan.recv_up[0], d.ztop ? plan.recv_up[1] : 0, nullptr, 0, buf, d.zg ? plan.send_dn[1] : 0,
+                          nullptr, 0);
+          if (d.zg)
+            {
+              T *own = v + plan.send_dn[0];
+              foreach (*ctx, plan.send_dn[1], [=] __device__(size_t i) { own[i] += buf[i]; });
+            }
+          return;
+        }
       Nccl &n   = Nccl::get();
-      T    *buf = reinterpret_cast<T *>(plane_buf.p);
       n.check(n.GroupStart(), "ncclGroupStart");
       if (d.ztop)
         n.check(n.Send(v + plan.recv_up[0], plan.recv_up[1] * sizeof(T), ncclInt8, ctx->rank + 1, ctx->comm, ctx->stream), "ncclSend");
@@ -747,7 +1090,7 @@ namespace mgb
           ScopedRange      range(*ctx, level->index, range_kind(A.mode));
           const LevelDesc &L  = level->d;
           const int        i0 = L.zg ? 2 : 0, i1 = L.ztop ? L.ncell[2] - 1 : L.ncell[2];
-          if (level->slab.distributed && ctx->overlap && i1 > i0)
+          if (level->slab.distributed && ctx->overlap && !ctx->p2p_on && i1 > i0)
             {
               // ghost exchange on the comm stream while the layers that read no ghost plane are
               // computed; then the first owned layer (reads the p planes from below through the carry
@@ -1270,6 +1613,15 @@ namespace mgb
               transfer[l].kernel = mg_transfer_no_boundary[l].kernel = o.kernel;
             }
         }
+      {
+        // peer-to-peer ghost exchange: the receive buffers hold the largest message, p planes of doubles
+        size_t max_msg = 0;
+        for (int l = 0; l < n_levels; ++l)
+          if (levels[l]->slab.distributed)
+            max_msg = std::max<size_t>(max_msg, (size_t)o.degree * plane_pitch(levels[l]->d) * sizeof(double));
+        if (max_msg)
+          ctx.init_p2p(max_msg);
+      }
       // inhomogeneous boundary values and right-hand side (multigrid_solver.h:224-262)
       Nodes1D nd;
       for (int i = 0; i <= o.degree; ++i)

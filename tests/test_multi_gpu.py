@@ -11,12 +11,12 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def run_ranks(n, args, timeout=600):
+def run_ranks(n, args, timeout=600, p2p=False):
     import torch
     if not torch.cuda.is_available() or torch.cuda.device_count() < n:
         pytest.skip("needs %d GPUs" % n)
     # the test meshes are far below the size from which the library cuts a level by default
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MGB200_MIN_SLAB_DOFS="0")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MGB200_MIN_SLAB_DOFS="0", MGB200_P2P="1" if p2p else "0")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % n, "--master-addr",
            "127.0.0.1", "--master-port", str(29900 + os.getpid() % 90), os.path.join(ROOT, "tests", "mgpu_worker.py")] + args
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
@@ -28,6 +28,12 @@ def run_ranks(n, args, timeout=600):
 @pytest.mark.parametrize("p,nsub,nref", [(4, "1,1,1", 3), (3, "1,2,3", 2), (2, "1,1,1", 4)])
 def test_two_gpus_against_oracle(mgb, orc, p, nsub, nref):
     run_ranks(2, [str(p), nsub, str(nref)])
+
+
+def test_two_gpus_peer_to_peer_exchange(mgb, orc):
+    """the optional exchange over IPC-mapped peer memory (kernels store straight into the neighbour's buffers)"""
+    out = run_ranks(2, ["4", "1,1,1", "3"], p2p=True)
+    assert "exchanges" in out
 
 
 def test_four_gpus_against_oracle(mgb, orc):
