@@ -1673,6 +1673,7 @@ namespace mgb
           matrix[l]->compute_diagonal();
           s.initialize(ctx, *matrix[l], basis);
         }
+      choose_graph_level();
       const size_t N = levels.back()->d.n_dofs;
       cg_g.alloc(N, ctx.stream);
       cg_h.alloc(N, ctx.stream);
@@ -1680,7 +1681,13 @@ namespace mgb
       ctx.sync();
     }
 
-    ~MultigridSolver() { ctx.destroy(); }
+    ~MultigridSolver()
+    {
+      for (CycleGraph &g : cycle_graphs)
+        if (g.exec)
+          cudaGraphExecDestroy(g.exec);
+      ctx.destroy();
+    }
 
     void
     set_boundary_values(const int level, const bool zero)
@@ -1715,9 +1722,121 @@ namespace mgb
       return std::sqrt(ctx.scal_host[0] / ctx.scal_host[1]);
     }
 
-    // multigrid_solver.h:641-681 (all in float)
+    // ---- CUDA graphs for the launch-bound coarse part of the V-cycle.  Below `graph_level` every kernel runs
+    //      for a few microseconds, so the cycle costs what the host needs to launch it; one captured graph
+    //      replaces ~25 launches per level.  The Chebyshev steps swap vectors, so the device addresses a cycle
+    //      works on alternate: graphs are cached by the address state they were captured for, and launching
+    //      one puts the host-side pointers into the state the captured code left them in.
+    struct CycleGraph
+    {
+      std::vector<void *> pre, post;
+      cudaGraphExec_t     exec = nullptr;
+    };
+    std::vector<CycleGraph> cycle_graphs;
+    int                     graph_level = -1; // v_cycle(graph_level, 1) is one graph launch; -1: off
+    int64_t                 graph_launches = 0;
+    unsigned int            v_cycle_calls = 0;
+
+    std::vector<void *>
+    pointer_state(const int level) const
+    {
+      std::vector<void *> st;
+      for (int l = 0; l <= level; ++l)
+        {
+          st.push_back(solution_update[l]->p);
+          st.push_back(smooth[l]->solution_old.p);
+        }
+      return st;
+    }
+
+    void
+    choose_graph_level()
+    {
+      const char *env   = getenv("MGB200_GRAPH_DOFS");
+      const long  limit = env ? atol(env) : 3000000L;
+      graph_level       = -1;
+      for (int l = 0; l < n_levels - 1; ++l)
+        if (!levels[l]->slab.distributed && matrix[l]->use_cartesian() && (long)levels[l]->d.n_dofs <= limit &&
+            transfer_uses_tiles(l))
+          graph_level = l;
+        else
+          break;
+      if (graph_level < 1)
+        graph_level = -1;
+    }
+    bool
+    transfer_uses_tiles(const int l) const
+    {
+      return l == 0 || (levels[l]->d.CW == choose_tile_cells(levels[l]->d.p, 0) && transfer[l].kernel == MGB_KERNEL_AUTO);
+    }
+
+    void
+    v_cycle_graph(const int level)
+    {
+      const std::vector<void *> pre = pointer_state(level);
+      for (CycleGraph &g : cycle_graphs)
+        if (g.pre == pre)
+          {
+            MGB_CUDA_CHECK(cudaGraphLaunch(g.exec, ctx.stream));
+            ++graph_launches;
+            ctx.launches += graph_kernels; // the kernels inside the graph
+            for (int l = 0; l <= level; ++l)
+              {
+                solution_update[l]->p       = static_cast<float *>(g.post[2 * l]);
+                smooth[l]->solution_old.p = static_cast<float *>(g.post[2 * l + 1]);
+              }
+            return;
+          }
+      if (cycle_graphs.size() >= 8)
+        { // unexpected number of address states: fall back to plain launches
+          v_cycle_plain(level, 1);
+          return;
+        }
+      CycleGraph   g;
+      cudaGraph_t  graph   = nullptr;
+      const int64_t before = ctx.launches;
+      g.pre                = pre;
+      MGB_CUDA_CHECK(cudaStreamBeginCapture(ctx.stream, cudaStreamCaptureModeRelaxed));
+      try
+        {
+          v_cycle_plain(level, 1);
+        }
+      catch (...)
+        {
+          cudaStreamEndCapture(ctx.stream, &graph);
+          if (graph)
+            cudaGraphDestroy(graph);
+          throw;
+        }
+      MGB_CUDA_CHECK(cudaStreamEndCapture(ctx.stream, &graph));
+      MGB_CUDA_CHECK(cudaGraphInstantiate(&g.exec, graph, 0));
+      MGB_CUDA_CHECK(cudaGraphDestroy(graph));
+      g.post          = pointer_state(level);
+      graph_kernels   = ctx.launches - before; // kernels inside one graph launch (for the launch count)
+      MGB_CUDA_CHECK(cudaGraphLaunch(g.exec, ctx.stream));
+      ++graph_launches;
+      cycle_graphs.push_back(g);
+    }
+    int64_t graph_kernels = 0;
+
     void
     v_cycle(const int level, const unsigned int my_n_cycles)
+    {
+      // the first cycles run plainly (kernel attributes are set on first launch); profiling needs the
+      // per-range events, which a graph does not record
+      if (level == graph_level && my_n_cycles == 1 && !ctx.profile && v_cycle_calls >= 2)
+        {
+          v_cycle_graph(level);
+          return;
+        }
+      if (level == graph_level)
+        ++v_cycle_calls;
+      v_cycle_plain(level, my_n_cycles);
+    }
+
+    // multigrid_solver.h:641-681 (all in float)
+    void
+    v_cycle_plain(const int level, const unsigned int my_n_cycles)
     {
       if (level == 0)
         {
@@ -1743,7 +1862,10 @@ namespace mgb
             MGB_CUDA_CHECK(cudaMemsetAsync(defect[level - 1]->p, 0, defect[level - 1]->n * sizeof(float), ctx.stream));
             transfer[level].restrict_and_add(defect[level - 1]->p, t[level]->p);
           }
-          v_cycle(level - 1, 1);
+          if (level - 1 == graph_level)
+            v_cycle(level - 1, 1);
+          else
+            v_cycle_plain(level - 1, 1);
           {
             ScopedRange range(ctx, level, RK_PROLONGATE);
             transfer[level].prolongate_and_add(solution_update[level]->p, solution_update[level - 1]->p);
@@ -2467,6 +2589,12 @@ extern "C"
         m.matrix[l]->kernel = m.matrix_dp[l]->kernel = kernel;
         m.transfer[l].kernel = m.mg_transfer_no_boundary[l].kernel = kernel;
       }
+    m.ctx.sync();
+    for (auto &g : m.cycle_graphs) // captured with the previous kernel selection
+      if (g.exec)
+        cudaGraphExecDestroy(g.exec);
+    m.cycle_graphs.clear();
+    m.choose_graph_level();
     MGB_CATCH
   }
 
