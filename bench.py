@@ -365,6 +365,19 @@ def dg_lines(r):
     return out
 
 
+def varcoef_lines(r):
+    """BASELINE config 3's streaming pattern (secondary lines, one GPU): FE_Q<3>(4) operator with a merged coefficient
+    per quadrature point (laplace_operator.h:388-430,493-522) and the coefficient of poisson_shell/program.cc:97-118,
+    on the 64^3-cell box (17 M DoF, 1.6 GB coefficient stream); 111.4 / 56.6 bytes per DoF."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import time_varcoef
+    out = time_varcoef.run(64, DEGREE, reps=10)
+    for k in ("fp64", "fp32"):
+        out[k]["frac_hbm"] = out[k]["gbs"] / r["hbm_gbs"]
+    out["workload"] = "FE_Q(4) variable-coefficient matvec, 64^3 cells, per-q-point merged coefficient streamed once"
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -391,6 +404,7 @@ def main():
                 "matvec_fp64_dofs_per_s": c["matvec_fp64_dofs_per_s"], "cg_iterations": c["iterations"]}
         if r["world"] == 1 and not args.no_dg:
             line["dg"] = dg_lines(r)
+            line["variable_coefficient"] = varcoef_lines(r)
         print(json.dumps(line), flush=True)
     if r["dist"] is not None:
         r["dist"].barrier()
