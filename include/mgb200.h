@@ -195,11 +195,16 @@ int mgb_dg_vmult_residual(mgb_dg h, int precision, const void *rhs, const void *
 /* std::array<Number,4> vmult_with_cg_update(alpha,beta,r,q,p,x)                                  :862-905 */
 int mgb_dg_vmult_with_cg_update(mgb_dg h, int precision, double alpha, double beta, const void *r, void *q,
                                 void *p, void *x, double sums[4]);
-/* exact inverse diagonal of the SIP matrix (point Jacobi; the reference's JacobiTransformed block
- * preconditioner, :2028-2256, is not built)                                                              */
+/* exact inverse diagonal of the SIP matrix (point Jacobi) */
 int mgb_dg_inverse_diagonal(mgb_dg h, int precision, void *inv_diag);
+/* preconditioner of the Chebyshev update: 0 = point Jacobi (default), 1 = multigrid::JacobiTransformed
+ * (laplace_operator_dg.h:2028-2256 with LocalBasisTransformer type 0, :176-222: cell-wise V D^-1 V^T in the tensor basis of
+ * the generalised eigenvectors of the 1-D SIP Laplacian w.r.t. the 1-D mass matrix, D = diag(V^T A_KK V))     */
+int mgb_dg_set_preconditioner(mgb_dg h, int kind);
+/* JacobiTransformed::vmult (:2046-2083) or the point-Jacobi scaling: dst = P^-1 src */
+int mgb_dg_preconditioner_vmult(mgb_dg h, int precision, void *dst, const void *src);
 /* vmult_with_chebyshev_update(preconditioner, rhs, iteration_index, factor1, factor2, solution, solution_old)
- * :907-955 with the point-Jacobi preconditioner: iteration_index 0: solution = factor2 P^-1 rhs; otherwise
+ * :907-955 with the selected preconditioner P: iteration_index 0: solution = factor2 P^-1 rhs; otherwise
  * solution_old = (1+factor1) solution - factor1 solution_old + factor2 P^-1 (rhs - A solution)  (the caller swaps) */
 int mgb_dg_vmult_with_chebyshev_update(mgb_dg h, int precision, const void *rhs, int iteration_index, double factor1,
                                        double factor2, void *solution, void *solution_old);

@@ -134,6 +134,8 @@ SYMBOLS = {
     "mgb_dg_vmult_with_cg_update": (_i, [_vp, _i, _d, _d, _vp, _vp, _vp, _vp, _dp]),
     "mgb_dg_inverse_diagonal": (_i, [_vp, _i, _vp]),
     "mgb_dg_vmult_with_chebyshev_update": (_i, [_vp, _i, _vp, _i, _d, _d, _vp, _vp]),
+    "mgb_dg_set_preconditioner": (_i, [_vp, _i]),
+    "mgb_dg_preconditioner_vmult": (_i, [_vp, _i, _vp, _vp]),
     "mgb_dg_vmult_host": (_i, [_vp, _i, _vp, _vp]),
     "mgb_dg_timer_start": (_i, [_vp]),
     "mgb_dg_timer_stop": (_i, [_vp, _dp]),
@@ -647,6 +649,21 @@ class LaplaceOperatorDG:
         self._torch_sync()
         _check(lib().mgb_dg_vmult_with_chebyshev_update(self.h, self.precision, _ptr(rhs), iteration_index, factor1,
                                                         factor2, _ptr(solution), _ptr(solution_old)))
+        self.sync()
+
+    POINT_JACOBI, JACOBI_TRANSFORMED = 0, 1
+
+    def set_preconditioner(self, kind):
+        """preconditioner of vmult_with_chebyshev_update: POINT_JACOBI or JACOBI_TRANSFORMED
+        (multigrid::JacobiTransformed, laplace_operator_dg.h:2028-2256)"""
+        self._torch_sync()
+        _check(lib().mgb_dg_set_preconditioner(self.h, kind))
+
+    def preconditioner_vmult(self, dst, src):
+        """JacobiTransformed::vmult / point-Jacobi scaling: dst = P^-1 src"""
+        self._chk(dst, src)
+        self._torch_sync()
+        _check(lib().mgb_dg_preconditioner_vmult(self.h, self.precision, _ptr(dst), _ptr(src)))
         self.sync()
 
     def vmult_async(self, dst, src):

@@ -3,6 +3,7 @@
 // There is no CPU fallback: every numerical step is a kernel launch on the operator's stream.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <stdexcept>
@@ -25,6 +26,126 @@ namespace mgb
     }                                                                                           \
   while (0)
 
+  // LocalBasisTransformer<dim, 0, degree, Number> (laplace_operator_dg.h:176-222): generalised eigenvectors of the
+  // 1-D SIP Laplacian (cell term + both end faces, penalty N^2) with respect to the 1-D mass matrix, in the nodal
+  // basis.  The reference calls LAPACK (compute_generalized_eigenvalues_symmetric); here: Cholesky of the mass
+  // matrix + cyclic Jacobi rotations.  V[k n + j] = component j of eigenvector k, eigenvalues ascending.  Sign
+  // and scaling of the vectors do not matter for V D^-1 V^T with D = diag(V^T A V).
+  inline std::vector<double>
+  jacobi_transformed_eigenvectors(const Basis &b)
+  {
+    const int                n = b.n;
+    std::vector<long double> nodes(b.nodes.begin(), b.nodes.end());
+    std::vector<double>      M(n * n), A(n * n);
+    const double             penalty = (double)n * n; // penalty_factor = 1 (laplace_operator_dg.h:47,198)
+    for (int i = 0; i < n; ++i)
+      for (int j = 0; j < n; ++j)
+        {
+          double m = 0, l = 0;
+          for (int q = 0; q < n; ++q)
+            {
+              m += b.S[q * n + i] * b.S[q * n + j] * b.wq[q];
+              l += b.G[q * n + i] * b.G[q * n + j] * b.wq[q];
+            }
+          const double vi0 = i == 0, vj0 = j == 0, vi1 = i == n - 1, vj1 = j == n - 1;
+          const double gi0 = (double)detail::dlag(nodes, i, 0.0L), gj0 = (double)detail::dlag(nodes, j, 0.0L);
+          const double gi1 = (double)detail::dlag(nodes, i, 1.0L), gj1 = (double)detail::dlag(nodes, j, 1.0L);
+          l += vi0 * vj0 * penalty + 0.5 * gi0 * vj0 + 0.5 * gj0 * vi0;
+          l += vi1 * vj1 * penalty - 0.5 * gi1 * vj1 - 0.5 * gj1 * vi1;
+          M[i * n + j] = m;
+          A[i * n + j] = l;
+        }
+    // M = L L^T
+    std::vector<double> L(n * n, 0.);
+    for (int i = 0; i < n; ++i)
+      for (int j = 0; j <= i; ++j)
+        {
+          double s = M[i * n + j];
+          for (int k = 0; k < j; ++k)
+            s -= L[i * n + k] * L[j * n + k];
+          L[i * n + j] = i == j ? std::sqrt(s) : s / L[j * n + j];
+        }
+    // C = L^-1 A L^-T
+    std::vector<double> X(n * n), C(n * n);
+    for (int c = 0; c < n; ++c) // X = L^-1 A (column by column, forward substitution)
+      for (int i = 0; i < n; ++i)
+        {
+          double s = A[i * n + c];
+          for (int k = 0; k < i; ++k)
+            s -= L[i * n + k] * X[k * n + c];
+          X[i * n + c] = s / L[i * n + i];
+        }
+    for (int r = 0; r < n; ++r) // C = X L^-T: row r of C solves L C_r^T = X_r^T
+      for (int i = 0; i < n; ++i)
+        {
+          double s = X[r * n + i];
+          for (int k = 0; k < i; ++k)
+            s -= L[i * n + k] * C[r * n + k];
+          C[r * n + i] = s / L[i * n + i];
+        }
+    for (int i = 0; i < n; ++i)
+      for (int j = 0; j < i; ++j)
+        C[i * n + j] = C[j * n + i] = 0.5 * (C[i * n + j] + C[j * n + i]);
+    // cyclic Jacobi: C W = W diag
+    std::vector<double> W(n * n, 0.);
+    for (int i = 0; i < n; ++i)
+      W[i * n + i] = 1;
+    for (int sweep = 0; sweep < 100; ++sweep)
+      {
+        double off = 0;
+        for (int i = 0; i < n; ++i)
+          for (int j = 0; j < i; ++j)
+            off += C[i * n + j] * C[i * n + j];
+        if (off < 1e-60)
+          break;
+        for (int pp = 0; pp < n; ++pp)
+          for (int q = pp + 1; q < n; ++q)
+            {
+              if (C[pp * n + q] == 0.)
+                continue;
+              const double theta = (C[q * n + q] - C[pp * n + pp]) / (2. * C[pp * n + q]);
+              const double t  = (theta >= 0 ? 1. : -1.) / (std::fabs(theta) + std::sqrt(theta * theta + 1.));
+              const double cs = 1. / std::sqrt(t * t + 1.), sn = t * cs;
+              for (int k = 0; k < n; ++k)
+                {
+                  const double ckp = C[k * n + pp], ckq = C[k * n + q];
+                  C[k * n + pp]    = cs * ckp - sn * ckq;
+                  C[k * n + q]     = sn * ckp + cs * ckq;
+                }
+              for (int k = 0; k < n; ++k)
+                {
+                  const double cpk = C[pp * n + k], cqk = C[q * n + k];
+                  C[pp * n + k]    = cs * cpk - sn * cqk;
+                  C[q * n + k]     = sn * cpk + cs * cqk;
+                }
+              for (int k = 0; k < n; ++k)
+                {
+                  const double wkp = W[k * n + pp], wkq = W[k * n + q];
+                  W[k * n + pp]    = cs * wkp - sn * wkq;
+                  W[k * n + q]     = sn * wkp + cs * wkq;
+                }
+            }
+      }
+    // eigenvectors of the pencil: v = L^-T w, sorted by eigenvalue
+    std::vector<int> order(n);
+    for (int i = 0; i < n; ++i)
+      order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int x, int y) { return C[x * n + x] < C[y * n + y]; });
+    std::vector<double> V(n * n);
+    for (int k = 0; k < n; ++k)
+      {
+        const int col = order[k];
+        for (int i = n - 1; i >= 0; --i) // back substitution with L^T
+          {
+            double s = W[i * n + col];
+            for (int j = i + 1; j < n; ++j)
+              s -= L[j * n + i] * V[k * n + j];
+            V[k * n + i] = s / L[i * n + i];
+          }
+      }
+    return V;
+  }
+
   template <typename T, int n>
   static DGTables<T, n>
   make_tables(const Basis &b)
@@ -43,6 +164,9 @@ namespace mgb
         t.e1[i] = (T)detail::dlag(nodes, i, 1.0L);
         t.w[i]  = (T)b.wq[i];
       }
+    const std::vector<double> V = jacobi_transformed_eigenvectors(b);
+    for (int i = 0; i < n * n; ++i)
+      t.V[i] = (T)V[i];
     return t;
   }
 
@@ -150,6 +274,9 @@ namespace mgb
     double        *scal_dev = nullptr, *scal_host = nullptr;
     void          *inv_diag[2] = {nullptr, nullptr}; // float, double
     void          *host_buf[2] = {nullptr, nullptr}; // device staging of the *_host entry points
+    int            preconditioner = 0;                // 0 point Jacobi, 1 JacobiTransformed
+    void          *jt_dinv[2] = {nullptr, nullptr};   // [64 cell types][n^3], float / double
+    std::vector<double> jt_dinv_host;
 
     explicit DGOperator(const mgb_dg_options &o)
       : opt(o)
@@ -240,6 +367,8 @@ namespace mgb
             cudaFree(inv_diag[i]);
           if (host_buf[i])
             cudaFree(host_buf[i]);
+          if (jt_dinv[i])
+            cudaFree(jt_dinv[i]);
           if (ev[i])
             cudaEventDestroy(ev[i]);
         }
@@ -266,6 +395,141 @@ namespace mgb
           MGB_DG_CHECK(cudaGetLastError());
         }
       return (T *)inv_diag[k];
+    }
+
+    // JacobiTransformed::local_compute_diagonals (laplace_operator_dg.h:2098-2233): D = diag(V^T A_KK V) with the
+    // cell-local matrix A_KK (cell term + the cell's own share of its six faces), which on this mesh depends on the
+    // cell only through which of its faces lie on the boundary.  A_KK is probed with the operator kernel itself
+    // on a mesh of at most 3 x 3 x 3 cells of the same size that contains every type: cells of equal parity are
+    // no neighbours, so 8 colours x n^3 transformed unit vectors give all diagonals.
+    void
+    build_jacobi_transformed()
+    {
+      if (!jt_dinv_host.empty())
+        return;
+      const int      n3 = n * n * n;
+      mgb_dg_options po = opt;
+      int            ncp[3];
+      for (int d = 0; d < 3; ++d)
+        {
+          ncp[d]               = std::min(nc[d], 3);
+          po.n_subdivisions[d] = ncp[d];
+          po.upper[d]          = opt.lower[d] + (opt.upper[d] - opt.lower[d]) / nc[d] * ncp[d];
+        }
+      po.n_refinements = 0;
+      DGOperator                probe(po);
+      const std::vector<double> V = jacobi_transformed_eigenvectors(basis);
+      const size_t              np = probe.n_dofs;
+      double                   *du = nullptr, *dy = nullptr;
+      MGB_DG_CHECK(cudaMalloc(&du, np * sizeof(double)));
+      MGB_DG_CHECK(cudaMalloc(&dy, np * sizeof(double)));
+      std::vector<double> u(np), y(np), vk(n3);
+      jt_dinv_host.assign((size_t)64 * n3, 0.);
+      for (int k = 0; k < n3; ++k)
+        {
+          const int k0 = k % n, k1 = (k / n) % n, k2 = k / (n * n);
+          for (int l2 = 0; l2 < n; ++l2)
+            for (int l1 = 0; l1 < n; ++l1)
+              for (int l0 = 0; l0 < n; ++l0)
+                vk[(l2 * n + l1) * n + l0] = V[k0 * n + l0] * V[k1 * n + l1] * V[k2 * n + l2];
+          for (int colour = 0; colour < 8; ++colour)
+            {
+              std::fill(u.begin(), u.end(), 0.);
+              bool any = false;
+              for (size_t c = 0; c < probe.n_cells; ++c)
+                {
+                  const int cx = c % ncp[0], cy = (c / ncp[0]) % ncp[1], cz = c / (ncp[0] * ncp[1]);
+                  if (((cx & 1) | ((cy & 1) << 1) | ((cz & 1) << 2)) != colour)
+                    continue;
+                  any = true;
+                  std::copy(vk.begin(), vk.end(), u.begin() + c * n3);
+                }
+              if (!any)
+                continue;
+              MGB_DG_CHECK(cudaMemcpyAsync(du, u.data(), np * sizeof(double), cudaMemcpyHostToDevice, probe.stream));
+              probe.apply<double>(DG_SET, dy, du);
+              MGB_DG_CHECK(cudaMemcpyAsync(y.data(), dy, np * sizeof(double), cudaMemcpyDeviceToHost, probe.stream));
+              MGB_DG_CHECK(cudaStreamSynchronize(probe.stream));
+              for (size_t c = 0; c < probe.n_cells; ++c)
+                {
+                  const int cx = c % ncp[0], cy = (c / ncp[0]) % ncp[1], cz = c / (ncp[0] * ncp[1]);
+                  if (((cx & 1) | ((cy & 1) << 1) | ((cz & 1) << 2)) != colour)
+                    continue;
+                  double dsum = 0;
+                  for (int l = 0; l < n3; ++l)
+                    dsum += vk[l] * y[c * n3 + l];
+                  const int tx = (cx == 0 ? 1 : 0) + (cx == ncp[0] - 1 ? 2 : 0);
+                  const int ty = (cy == 0 ? 1 : 0) + (cy == ncp[1] - 1 ? 2 : 0);
+                  const int tz = (cz == 0 ? 1 : 0) + (cz == ncp[2] - 1 ? 2 : 0);
+                  jt_dinv_host[(size_t)((tz * 4 + ty) * 4 + tx) * n3 + k] = 1. / dsum;
+                }
+            }
+        }
+      cudaFree(du);
+      cudaFree(dy);
+      launches += probe.launches;
+      MGB_DG_CHECK(cudaSetDevice(opt.device));
+    }
+
+    template <typename T>
+    const T *
+    get_jt_dinv()
+    {
+      const int k = sizeof(T) == 8;
+      if (!jt_dinv[k])
+        {
+          build_jacobi_transformed();
+          std::vector<T> h(jt_dinv_host.begin(), jt_dinv_host.end());
+          MGB_DG_CHECK(cudaMalloc(&jt_dinv[k], h.size() * sizeof(T)));
+          MGB_DG_CHECK(cudaMemcpyAsync(jt_dinv[k], h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, stream));
+          MGB_DG_CHECK(cudaStreamSynchronize(stream));
+        }
+      return (const T *)jt_dinv[k];
+    }
+
+    template <int P, typename T>
+    void
+    launch_jt(const DGArgs<T> &A, const T scale)
+    {
+      static const DGTables<T, P + 1> tb = make_tables<T, P + 1>(make_basis(P));
+      launch_dg_jacobi_transformed<P, T>(A, tb, scale, stream);
+    }
+
+    // dst = scale * P^-1 src with the selected preconditioner (JacobiTransformed::vmult, :2046-2083, or point Jacobi)
+    template <typename T>
+    void
+    preconditioner_vmult(T *dst, const T *src, const double scale)
+    {
+      if (preconditioner == 0)
+        {
+          const T     *P = get_inverse_diagonal<T>();
+          const T      f = (T)scale;
+          const size_t N = n_dofs;
+          k_dg_foreach<<<grid(N), 256, 0, stream>>>(N, [=] __device__(size_t i) { dst[i] = f * P[i] * src[i]; });
+        }
+      else
+        {
+          DGArgs<T> A;
+          for (int d = 0; d < 3; ++d)
+            A.nc[d] = nc[d];
+          A.n_cells = (uint32_t)n_cells;
+          A.src     = src;
+          A.dst     = dst;
+          A.jt_dinv = get_jt_dinv<T>();
+          switch (p)
+            {
+              case 1: launch_jt<1, T>(A, (T)scale); break;
+              case 2: launch_jt<2, T>(A, (T)scale); break;
+              case 3: launch_jt<3, T>(A, (T)scale); break;
+              case 4: launch_jt<4, T>(A, (T)scale); break;
+              case 5: launch_jt<5, T>(A, (T)scale); break;
+              case 6: launch_jt<6, T>(A, (T)scale); break;
+              case 7: launch_jt<7, T>(A, (T)scale); break;
+              default: launch_jt<8, T>(A, (T)scale); break;
+            }
+        }
+      ++launches;
+      MGB_DG_CHECK(cudaGetLastError());
     }
 
     template <int P, typename T>
@@ -295,7 +559,8 @@ namespace mgb
       A.src      = src;
       A.dst      = dst;
       A.rhs      = rhs;
-      A.inv_diag = mode >= DG_CHEBYSHEV ? get_inverse_diagonal<T>() : nullptr;
+      A.inv_diag = (mode >= DG_CHEBYSHEV && preconditioner == 0) ? get_inverse_diagonal<T>() : nullptr;
+      A.jt_dinv  = (mode >= DG_CHEBYSHEV && preconditioner == 1) ? get_jt_dinv<T>() : nullptr;
       A.f1       = (T)f1;
       A.f2       = (T)f2;
       A.mode     = mode;
@@ -348,12 +613,7 @@ namespace mgb
           apply<T>(iteration_index == 1 ? DG_CHEBYSHEV_FIRST : DG_CHEBYSHEV, solution_old, solution, rhs, f1, f2);
           return;
         }
-      const T     *P = get_inverse_diagonal<T>();
-      const T      f = (T)f2;
-      const size_t N = n_dofs;
-      k_dg_foreach<<<grid(N), 256, 0, stream>>>(N, [=] __device__(size_t i) { solution[i] = f * P[i] * rhs[i]; });
-      ++launches;
-      MGB_DG_CHECK(cudaGetLastError());
+      preconditioner_vmult<T>(solution, rhs, f2);
     }
   };
 } // namespace mgb
@@ -544,6 +804,30 @@ extern "C"
     else
       DGH(h).chebyshev_update<float>((const float *)rhs, iteration_index, factor1, factor2, (float *)solution,
                                      (float *)solution_old);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_set_preconditioner(mgb_dg h, int kind)
+  {
+    DG_TRY
+    if (kind != 0 && kind != 1)
+      throw std::runtime_error("preconditioner must be 0 (point Jacobi) or 1 (JacobiTransformed)");
+    DGH(h).preconditioner = kind;
+    if (kind == 1)
+      DGH(h).build_jacobi_transformed();
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_preconditioner_vmult(mgb_dg h, int precision, void *dst, const void *src)
+  {
+    DG_TRY
+    check_precision(precision);
+    if (precision == MGB_F64)
+      DGH(h).preconditioner_vmult<double>((double *)dst, (const double *)src, 1.);
+    else
+      DGH(h).preconditioner_vmult<float>((float *)dst, (const float *)src, 1.);
     DG_CATCH
   }
 

@@ -39,6 +39,7 @@ namespace mgb
     T D[n * n]; // D[q n + r] = l_r'(x_q)
     T e0[n], e1[n]; // phi_i'(0), phi_i'(1)
     T w[n];
+    T V[n * n]; // V[k n + j] = component j of the k-th generalised eigenvector of (1-D SIP Laplace, 1-D mass)
   };
 
   template <typename T>
@@ -50,6 +51,7 @@ namespace mgb
     T       *dst;
     const T *rhs;
     const T *inv_diag;
+    const T *jt_dinv;  // JacobiTransformed: 1 / diag(V^T A_KK V) per cell type [64][n^3]; nullptr: point Jacobi
     T        f1, f2;
     int      mode;
     T        gt[6];    // detJ J^-1 J^-T: 00 11 22 01 02 12
@@ -110,6 +112,117 @@ namespace mgb
           s += M[q * n + r] * in[r];
         out[q] = s;
       }
+  }
+
+  // type of a cell for the cell-local matrix A_KK: per direction 0 interior, 1 low boundary, 2 high, 3 both
+  __device__ __forceinline__ int
+  dg_cell_type(const int cx, const int cy, const int cz, const int *nc)
+  {
+    const int tx = (cx == 0 ? 1 : 0) + (cx == nc[0] - 1 ? 2 : 0);
+    const int ty = (cy == 0 ? 1 : 0) + (cy == nc[1] - 1 ? 2 : 0);
+    const int tz = (cz == 0 ? 1 : 0) + (cz == nc[2] - 1 ? 2 : 0);
+    return (tz * 4 + ty) * 4 + tx;
+  }
+
+  // multigrid::JacobiTransformed::do_local_operation (laplace_operator_dg.h:2085-2095): r <- V (D^-1 (V^T r)) with
+  // the tensor-product transform V x V x V and D = diag(V^T A_KK V) of the cell's type.  `r` holds the input and
+  // the result (n^3 values in shared memory), `a0`, `a1` are work arrays; thread (a,b) sweeps pencils.
+  template <int n, int TPC, typename T>
+  __device__ __forceinline__ void
+  jacobi_transformed_local(T *r, T *a0, T *a1, const T *__restrict__ V, const T *__restrict__ dinv, const bool active,
+                           const int a, const int b, const int slot)
+  {
+    constexpr int n2 = n * n;
+    T             in[n], out[n];
+    if (active)
+      { // V^T along z: out[k] = sum_j V[k][j] in[j]
+#pragma unroll
+        for (int k = 0; k < n; ++k)
+          in[k] = r[k * n2 + b * n + a];
+        prod<n>(V, in, out);
+#pragma unroll
+        for (int k = 0; k < n; ++k)
+          a0[k * n2 + b * n + a] = out[k];
+      }
+    cell_sync<TPC>(slot);
+    if (active)
+      { // along y
+#pragma unroll
+        for (int j = 0; j < n; ++j)
+          in[j] = a0[(b * n + j) * n + a];
+        prod<n>(V, in, out);
+#pragma unroll
+        for (int j = 0; j < n; ++j)
+          a1[(b * n + j) * n + a] = out[j];
+      }
+    cell_sync<TPC>(slot);
+    if (active)
+      { // along x: to the eigenbasis, scale, and back along x
+#pragma unroll
+        for (int i = 0; i < n; ++i)
+          in[i] = a1[(b * n + a) * n + i];
+        prod<n>(V, in, out);
+#pragma unroll
+        for (int i = 0; i < n; ++i)
+          out[i] *= dinv[(b * n + a) * n + i];
+        tprod<n>(V, out, in);
+#pragma unroll
+        for (int i = 0; i < n; ++i)
+          a0[(b * n + a) * n + i] = in[i];
+      }
+    cell_sync<TPC>(slot);
+    if (active)
+      { // V along y
+#pragma unroll
+        for (int j = 0; j < n; ++j)
+          in[j] = a0[(b * n + j) * n + a];
+        tprod<n>(V, in, out);
+#pragma unroll
+        for (int j = 0; j < n; ++j)
+          a1[(b * n + j) * n + a] = out[j];
+      }
+    cell_sync<TPC>(slot);
+    if (active)
+      { // V along z
+#pragma unroll
+        for (int k = 0; k < n; ++k)
+          in[k] = a1[k * n2 + b * n + a];
+        tprod<n>(V, in, out);
+#pragma unroll
+        for (int k = 0; k < n; ++k)
+          r[k * n2 + b * n + a] = out[k];
+      }
+    cell_sync<TPC>(slot);
+  }
+
+  // JacobiTransformed::vmult (laplace_operator_dg.h:2046-2083): dst = scale * P^-1 src, one cell per thread group
+  template <int p, typename T>
+  __global__ void
+  __launch_bounds__(DGCfg<p>::NT)
+    k_dg_jacobi_transformed(const DGArgs<T> A, const DGTables<T, p + 1> Tb, const T scale)
+  {
+    using C           = DGCfg<p>;
+    constexpr int n   = C::n;
+    constexpr int n2  = C::n2;
+    constexpr int n3  = C::n3;
+    constexpr int TPC = C::TPC;
+    __shared__ T buf[C::CPB * 3 * n3];
+    const int    slot = threadIdx.x / TPC, t = threadIdx.x % TPC;
+    T           *r = buf + slot * 3 * n3, *a0 = r + n3, *a1 = a0 + n3;
+    const uint32_t cell   = blockIdx.x * C::CPB + slot;
+    const bool     valid  = cell < A.n_cells;
+    const bool     active = valid && t < n2;
+    const uint32_t c  = valid ? cell : 0;
+    const int      cx = c % A.nc[0], cy = (c / A.nc[0]) % A.nc[1], cz = c / (A.nc[0] * A.nc[1]);
+    if (valid)
+      for (int i = t; i < n3; i += TPC)
+        r[i] = A.src[(size_t)c * n3 + i];
+    cell_sync<TPC>(slot);
+    jacobi_transformed_local<n, TPC, T>(r, a0, a1, Tb.V, A.jt_dinv + dg_cell_type(cx, cy, cz, A.nc) * n3, active, t % n,
+                                        t / n, slot);
+    if (valid)
+      for (int i = t; i < n3; i += TPC)
+        A.dst[(size_t)c * n3 + i] = scale * r[i];
   }
 
   template <int p, typename T>
@@ -441,6 +554,27 @@ namespace mgb
       }
 
     // ================= fused vector operation, coalesced over the cell
+    if (A.mode >= DG_CHEBYSHEV && A.jt_dinv != nullptr)
+      {
+        // Chebyshev update with the JacobiTransformed preconditioner (laplace_operator_dg.h:1839-1860): the residual
+        // rhs - A x of the cell goes through V D^-1 V^T before the update (block-uniform branch)
+        const size_t off = (size_t)c * n3;
+        if (valid)
+          for (int i = t; i < n3; i += TPC)
+            y_s[i] = A.rhs[off + i] - y_s[i];
+        cell_sync<TPC>(slot);
+        jacobi_transformed_local<n, TPC, T>(y_s, w0, w1, Tb.V, A.jt_dinv + dg_cell_type(cx, cy, cz, A.nc) * n3, active, a, b,
+                                            slot);
+        if (valid)
+          for (int i = t; i < n3; i += TPC)
+            {
+              T r = A.f2 * y_s[i] + (T(1) + A.f1) * u_s[i];
+              if (A.mode == DG_CHEBYSHEV)
+                r -= A.f1 * A.dst[off + i];
+              A.dst[off + i] = r;
+            }
+        return;
+      }
     if (valid)
       {
         const size_t off = (size_t)c * n3;
@@ -477,5 +611,14 @@ namespace mgb
       }
     const unsigned blocks = (A.n_cells + C::CPB - 1) / C::CPB;
     k_dg_apply<p, T><<<blocks, C::NT, smem, stream>>>(A, Tb);
+  }
+
+  template <int p, typename T>
+  void
+  launch_dg_jacobi_transformed(const DGArgs<T> &A, const DGTables<T, p + 1> &Tb, const T scale, cudaStream_t stream)
+  {
+    using C               = DGCfg<p>;
+    const unsigned blocks = (A.n_cells + C::CPB - 1) / C::CPB;
+    k_dg_jacobi_transformed<p, T><<<blocks, C::NT, 0, stream>>>(A, Tb, scale);
   }
 } // namespace mgb

@@ -287,3 +287,66 @@ class DGOperator:
         X = np.stack([self.lower[0] + (cx + g[i]) * h[0], self.lower[1] + (cy + g[j]) * h[1],
                       self.lower[2] + (cz + g[k]) * h[2]], axis=-1).reshape(-1, 3)
         return X @ self.trafo.T
+
+
+class JacobiTransformed:
+    """multigrid::JacobiTransformed (laplace_operator_dg.h:2028-2256) with LocalBasisTransformer type 0 (:176-222)
+    restated with numpy/scipy: V = generalised eigenvectors of the 1-D SIP Laplacian w.r.t. the 1-D mass matrix
+    (LAPACK through scipy.linalg.eigh, as the reference's compute_generalized_eigenvalues_symmetric), and per cell
+    D = diag(V^T A_KK V) obtained by probing the oracle's face-based operator (8 colours of cells)."""
+
+    def __init__(self, op):
+        import scipy.linalg
+        self.op = op
+        p = op.degree
+        n = p + 1
+        b = basis(p)
+        S, G, w, nodes = b["S"], b["G"], b["wq"], b["gll"]
+
+        def dl(i, x):
+            s = 0.0
+            for m in range(n):
+                if m != i:
+                    v = 1.0 / (nodes[i] - nodes[m])
+                    for l in range(n):
+                        if l != i and l != m:
+                            v *= (x - nodes[l]) / (nodes[i] - nodes[l])
+                    s += v
+            return s
+        mass = S.T @ np.diag(w) @ S
+        lapl = G.T @ np.diag(w) @ G
+        pen = float(n * n)  # penalty_factor = 1
+        v0, v1 = np.eye(n)[0], np.eye(n)[p]
+        g0 = np.array([dl(i, 0.0) for i in range(n)])
+        g1 = np.array([dl(i, 1.0) for i in range(n)])
+        lapl = lapl + pen * np.outer(v0, v0) + 0.5 * (np.outer(g0, v0) + np.outer(v0, g0))
+        lapl = lapl + pen * np.outer(v1, v1) - 0.5 * (np.outer(g1, v1) + np.outer(v1, g1))
+        self.eigenvalues, vecs = scipy.linalg.eigh(lapl, mass)
+        self.V = vecs.T.copy()  # V[k, j] = component j of eigenvector k
+        # diagonal of V^T A_KK V per cell by probing
+        nc = op.ncell
+        n3 = n ** 3
+        cells = np.arange(nc[0] * nc[1] * nc[2])
+        cx, cy, cz = cells % nc[0], (cells // nc[0]) % nc[1], cells // (nc[0] * nc[1])
+        colour = (cx % 2) + 2 * (cy % 2) + 4 * (cz % 2)
+        self.diag = np.zeros((cells.size, n3))
+        V = self.V
+        for k in range(n3):
+            k0, k1, k2 = k % n, (k // n) % n, k // (n * n)
+            vk = np.einsum("c,b,a->cba", V[k2], V[k1], V[k0]).ravel()
+            for col in range(8):
+                sel = cells[colour == col]
+                if sel.size == 0:
+                    continue
+                u = np.zeros(op.n_dofs())
+                u.reshape(-1, n3)[sel] = vk
+                y = op.vmult(u).reshape(-1, n3)
+                self.diag[sel, k] = y[sel] @ vk
+
+    def vmult(self, src):
+        n = self.op.degree + 1
+        V = self.V
+        r = np.asarray(src, dtype=np.float64).reshape(-1, n, n, n)      # [cell, z, y, x]
+        c = np.einsum("kz,jy,ix,czyx->ckji", V, V, V, r)                 # V^T in every direction
+        c = c / self.diag.reshape(-1, n, n, n)
+        return np.einsum("kz,jy,ix,ckji->czyx", V, V, V, c).ravel()     # back to the nodal basis

@@ -113,3 +113,41 @@ def test_vmult_host(mgb, orc, torch):
     y = np.zeros_like(x)
     g.vmult_host(y, x)
     assert rel(y, o.vmult(x)) <= 1e-12
+
+
+@pytest.mark.parametrize("precision", [1, 0])
+@pytest.mark.parametrize("mesh", [(2, (1, 2, 3), 0, True), (4, (3, 2, 2), 0, True), (3, (1, 1, 1), 2, False), (4, (2, 1, 2), 1, True),
+                                  (6, (2, 2, 1), 0, True)])
+def test_jacobi_transformed(mgb, orc, torch, mesh, precision):
+    """multigrid::JacobiTransformed (laplace_operator_dg.h:2028-2256): V D^-1 V^T per cell, alone and inside the fused
+    Chebyshev update, against the numpy/scipy restatement (LAPACK eigenvectors, diagonals probed from the oracle)"""
+    p, nsub, nref, sheared = mesh
+    g, o = make(mgb, orc, p, nsub, nref, sheared, precision)
+    J = orc.JacobiTransformed(o)
+    g.set_preconditioner(g.JACOBI_TRANSFORMED)
+    rng = np.random.default_rng(11)
+    n = g.m()
+    r = rng.random(n) - 0.5
+    dr = torch.tensor(r, dtype=g.dtype, device="cuda")
+    z = g.initialize_dof_vector()
+    g.preconditioner_vmult(z, dr)
+    tol = 1e-11 if precision else 2e-5
+    assert rel(z.double().cpu().numpy(), J.vmult(r)) <= tol
+    b, x0, x1 = rng.random(n), rng.random(n), rng.random(n)
+    f1, f2 = 0.6, 0.2
+    db = torch.tensor(b, dtype=g.dtype, device="cuda")
+    sol = torch.tensor(x1, dtype=g.dtype, device="cuda")
+    old = torch.tensor(x0, dtype=g.dtype, device="cuda")
+    g.vmult_with_chebyshev_update(db, 2, f1, f2, sol, old)
+    ref = (1 + f1) * x1 - f1 * x0 + f2 * J.vmult(b - o.vmult(x1))
+    assert rel(old.double().cpu().numpy(), ref) <= 2 * tol
+    old = torch.tensor(x0, dtype=g.dtype, device="cuda")
+    g.vmult_with_chebyshev_update(db, 1, f1, f2, sol, old)
+    ref = (1 + f1) * x1 + f2 * J.vmult(b - o.vmult(x1))
+    assert rel(old.double().cpu().numpy(), ref) <= 2 * tol
+    g.vmult_with_chebyshev_update(db, 0, f1, f2, sol, old)
+    assert rel(sol.double().cpu().numpy(), f2 * J.vmult(b)) <= 2 * tol
+    # back to point Jacobi
+    g.set_preconditioner(g.POINT_JACOBI)
+    g.preconditioner_vmult(z, dr)
+    assert rel(z.double().cpu().numpy(), r / o.diagonal()) <= (1e-12 if precision else 1e-6)

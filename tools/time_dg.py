@@ -22,7 +22,7 @@ def run(steps=20, degree=4, reps=20):
             fn = lambda: g.vmult_async(b, a)
             nvec = 3
         else:
-            g.get_matrix_diagonal_inverse()
+            g.set_preconditioner(g.JACOBI_TRANSFORMED)   # as matvec_dg_cheby/program.cc:108
             fn = lambda: g.chebyshev_update_async(c, 2, 0.6, 0.2, a, b)
             nvec = 5
         fn()
