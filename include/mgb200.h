@@ -208,6 +208,14 @@ int mgb_dg_preconditioner_vmult(mgb_dg h, int precision, void *dst, const void *
  * solution_old = (1+factor1) solution - factor1 solution_old + factor2 P^-1 (rhs - A solution)  (the caller swaps) */
 int mgb_dg_vmult_with_chebyshev_update(mgb_dg h, int precision, const void *rhs, int iteration_index, double factor1,
                                        double factor2, void *solution, void *solution_old);
+/* Same-degree transfer between the DG space and the FE_Q space of level `level` of solver `s` on the same mesh
+ * (one GPU; both vectors of the given precision, the FE_Q vector in the solver's numbering):
+ * prolongate_add_cg_to_dg(dst_dg, src_cg)                                   laplace_operator_dg.h:1863-1894: dg += P cg
+ * vmult_residual_and_restrict_to_cg(rhs, lhs, restricted_residual)           :851-860 (action 1, :1798-1819):
+ *                                                                           restricted = P^T (rhs - A lhs)          */
+int mgb_dg_prolongate_add_cg_to_dg(mgb_dg h, mgb_solver s, int level, int precision, void *dg, const void *cg);
+int mgb_dg_vmult_residual_and_restrict_to_cg(mgb_dg h, mgb_solver s, int level, int precision, const void *rhs,
+                                             const void *lhs, void *restricted_residual);
 /* end-to-end: host vectors in, apply, host vector out */
 int mgb_dg_vmult_host(mgb_dg h, int precision, void *dst_host, const void *src_host);
 int mgb_dg_timer_start(mgb_dg h);

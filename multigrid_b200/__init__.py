@@ -134,6 +134,8 @@ SYMBOLS = {
     "mgb_dg_vmult_with_cg_update": (_i, [_vp, _i, _d, _d, _vp, _vp, _vp, _vp, _dp]),
     "mgb_dg_inverse_diagonal": (_i, [_vp, _i, _vp]),
     "mgb_dg_vmult_with_chebyshev_update": (_i, [_vp, _i, _vp, _i, _d, _d, _vp, _vp]),
+    "mgb_dg_prolongate_add_cg_to_dg": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
+    "mgb_dg_vmult_residual_and_restrict_to_cg": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "mgb_dg_set_preconditioner": (_i, [_vp, _i]),
     "mgb_dg_preconditioner_vmult": (_i, [_vp, _i, _vp, _vp]),
     "mgb_dg_vmult_host": (_i, [_vp, _i, _vp, _vp]),
@@ -652,6 +654,22 @@ class LaplaceOperatorDG:
         self.sync()
 
     POINT_JACOBI, JACOBI_TRANSFORMED = 0, 1
+
+    def prolongate_add_cg_to_dg(self, solver, level, dst_dg, src_cg):
+        """laplace_operator_dg.h:1863-1894: dst_dg += (FE_Q vector of `level` of `solver` seen from the DG space)"""
+        self._torch_sync()
+        solver.sync()
+        _check(lib().mgb_dg_prolongate_add_cg_to_dg(self.h, solver.h, solver._l(level), self.precision, _ptr(dst_dg),
+                                                    _ptr(src_cg)))
+        self.sync()
+
+    def vmult_residual_and_restrict_to_cg(self, solver, level, rhs, lhs, restricted_residual):
+        """laplace_operator_dg.h:851-860: restricted_residual = P^T (rhs - A lhs), an FE_Q vector"""
+        self._torch_sync()
+        solver.sync()
+        _check(lib().mgb_dg_vmult_residual_and_restrict_to_cg(self.h, solver.h, solver._l(level), self.precision, _ptr(rhs),
+                                                              _ptr(lhs), _ptr(restricted_residual)))
+        self.sync()
 
     def set_preconditioner(self, kind):
         """preconditioner of vmult_with_chebyshev_update: POINT_JACOBI or JACOBI_TRANSFORMED

@@ -13,6 +13,10 @@
 #include "../../include/mgb200.h"
 #include "basis.h"
 #include "dg_kernels.cuh"
+#include "level.h"
+
+struct mgb_solver_t;
+const mgb::LevelDesc *mgb_internal_level_desc(mgb_solver_t *s, int level);
 
 namespace mgb
 {
@@ -260,6 +264,66 @@ namespace mgb
       }
   }
 
+  // ---- same-degree transfer between the DG space and FE_Q on the same mesh (laplace_operator_dg.h:1798-1819,
+  //      1863-1894).  Both bases are Lagrange bases in the same Gauss-Lobatto points, so the 1-D change of basis of
+  //      LocalBasisTransformer<dim,1,...> (:106-141) is the identity and the transfer is the cell-to-DoF map of FE_Q:
+  //      prolongation gathers (constrained FE_Q entries read as zero, vector_access_reduced.h:174-179), restriction
+  //      scatter-adds (constrained entries skipped, :431-433) -- written as a gather per FE_Q point over its up to
+  //      8 cells, so it needs no atomics.
+  template <typename T>
+  __global__ void
+  k_cg_to_dg_add(const LevelDesc L, const T *__restrict__ cg, T *__restrict__ dg)
+  {
+    const int    n = L.n, n3 = n * n * n;
+    const size_t total = (size_t)L.n_cells * n3;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x)
+      {
+        const uint32_t c = idx / n3;
+        const int      l = (int)(idx - (size_t)c * n3);
+        bool           con;
+        const uint32_t d = cell_dof(L, c, l % n, (l / n) % n, l / (n * n), con);
+        if (!con)
+          dg[idx] += cg[d];
+      }
+  }
+
+  template <typename T>
+  __global__ void
+  k_dg_to_cg_add(const LevelDesc L, const T *__restrict__ dg, T *__restrict__ cg)
+  {
+    const int    p = L.p, n = L.n, n3 = n * n * n;
+    const size_t total = L.n_dofs;
+    for (size_t lex = blockIdx.x * (size_t)blockDim.x + threadIdx.x; lex < total; lex += (size_t)gridDim.x * blockDim.x)
+      {
+        const int    g0 = lex % L.nd[0];
+        const size_t r  = lex / L.nd[0];
+        const int    g1 = r % L.nd[1], g2 = r / L.nd[1];
+        if (is_constrained(L, g0, g1, g2))
+          continue;
+        T sum = 0;
+        for (int dz = 0; dz < 2; ++dz)
+          {
+            const int cz = g2 / p - dz, k = g2 - cz * p;
+            if (cz < 0 || cz >= L.ncell[2] || k > p)
+              continue;
+            for (int dy = 0; dy < 2; ++dy)
+              {
+                const int cy = g1 / p - dy, j = g1 - cy * p;
+                if (cy < 0 || cy >= L.ncell[1] || j > p)
+                  continue;
+                for (int dx = 0; dx < 2; ++dx)
+                  {
+                    const int cx = g0 / p - dx, i = g0 - cx * p;
+                    if (cx < 0 || cx >= L.ncell[0] || i > p)
+                      continue;
+                    sum += dg[(size_t)cell_number(L, cx, cy, cz) * n3 + (k * n + j) * n + i];
+                  }
+              }
+          }
+        cg[dof_index(L, g0, g1, g2)] += sum;
+      }
+  }
+
   struct DGOperator
   {
     mgb_dg_options opt;
@@ -485,6 +549,39 @@ namespace mgb
           MGB_DG_CHECK(cudaStreamSynchronize(stream));
         }
       return (const T *)jt_dinv[k];
+    }
+
+    void
+    check_same_mesh(const LevelDesc &L) const
+    {
+      if (L.p != p || L.ncell[0] != nc[0] || L.ncell[1] != nc[1] || L.ncell[2] != nc[2])
+        throw std::runtime_error("the FE_Q level and the DG operator must share degree and mesh");
+    }
+    // prolongate_add_cg_to_dg (laplace_operator_dg.h:1863-1894): dg += cg
+    template <typename T>
+    void
+    prolongate_add_cg_to_dg(const LevelDesc &L, T *dg, const T *cg)
+    {
+      check_same_mesh(L);
+      k_cg_to_dg_add<T><<<grid(n_dofs), 256, 0, stream>>>(L, cg, dg);
+      ++launches;
+      MGB_DG_CHECK(cudaGetLastError());
+    }
+    // vmult_residual_and_restrict_to_cg (laplace_operator_dg.h:851-860, action 1 :1798-1819): restricted = R (rhs - A lhs)
+    template <typename T>
+    void
+    vmult_residual_and_restrict_to_cg(const LevelDesc &L, const T *rhs, const T *lhs, T *restricted)
+    {
+      check_same_mesh(L);
+      for (int i = 0; i < 2; ++i)
+        if (!host_buf[i])
+          MGB_DG_CHECK(cudaMalloc(&host_buf[i], n_dofs * 8));
+      T *res = (T *)host_buf[0];
+      apply<T>(DG_RESIDUAL, res, lhs, rhs);
+      MGB_DG_CHECK(cudaMemsetAsync(restricted, 0, (size_t)L.n_dofs * sizeof(T), stream));
+      k_dg_to_cg_add<T><<<grid(L.n_dofs), 256, 0, stream>>>(L, res, restricted);
+      ++launches;
+      MGB_DG_CHECK(cudaGetLastError());
     }
 
     template <int P, typename T>
@@ -804,6 +901,33 @@ extern "C"
     else
       DGH(h).chebyshev_update<float>((const float *)rhs, iteration_index, factor1, factor2, (float *)solution,
                                      (float *)solution_old);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_prolongate_add_cg_to_dg(mgb_dg h, mgb_solver s, int level, int precision, void *dg, const void *cg)
+  {
+    DG_TRY
+    check_precision(precision);
+    const LevelDesc L = *mgb_internal_level_desc(s, level);
+    if (precision == MGB_F64)
+      DGH(h).prolongate_add_cg_to_dg<double>(L, (double *)dg, (const double *)cg);
+    else
+      DGH(h).prolongate_add_cg_to_dg<float>(L, (float *)dg, (const float *)cg);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_vmult_residual_and_restrict_to_cg(mgb_dg h, mgb_solver s, int level, int precision, const void *rhs,
+                                           const void *lhs, void *restricted_residual)
+  {
+    DG_TRY
+    check_precision(precision);
+    const LevelDesc L = *mgb_internal_level_desc(s, level);
+    if (precision == MGB_F64)
+      DGH(h).vmult_residual_and_restrict_to_cg<double>(L, (const double *)rhs, (const double *)lhs, (double *)restricted_residual);
+    else
+      DGH(h).vmult_residual_and_restrict_to_cg<float>(L, (const float *)rhs, (const float *)lhs, (float *)restricted_residual);
     DG_CATCH
   }
 

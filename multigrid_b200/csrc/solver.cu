@@ -2064,6 +2064,11 @@ mgb_set_last_error(const char *msg)
   g_last_error = msg;
 }
 
+// level description, stream and V-cycle vectors of a solver for dg.cu (same-degree DG <-> FE_Q transfer and the DG
+// solver built on top of the FE_Q hierarchy); not part of the public C ABI
+struct mgb_solver_t;
+const mgb::LevelDesc *mgb_internal_level_desc(mgb_solver_t *s, int level);
+
 struct mgb_solver_t
 {
   MultigridSolver *impl;
@@ -2120,6 +2125,17 @@ check_level(MultigridSolver &s, int level)
   if (level < 0 || level >= s.n_levels)
     throw std::runtime_error("level out of range");
   return level;
+}
+
+const mgb::LevelDesc *
+mgb_internal_level_desc(mgb_solver_t *s, int level)
+{
+  MultigridSolver &m = S(s);
+  Level           &l = *m.levels[check_level(m, level)];
+  if (l.slab.distributed)
+    throw std::runtime_error("the DG <-> FE_Q transfer runs on one GPU");
+  m.ctx.sync();
+  return &l.d;
 }
 
 extern "C"

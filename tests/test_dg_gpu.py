@@ -151,3 +151,50 @@ def test_jacobi_transformed(mgb, orc, torch, mesh, precision):
     g.set_preconditioner(g.POINT_JACOBI)
     g.preconditioner_vmult(z, dr)
     assert rel(z.double().cpu().numpy(), r / o.diagonal()) <= (1e-12 if precision else 1e-6)
+
+
+@pytest.mark.parametrize("precision", [1, 0])
+@pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 2), (3, (2, 1, 3), 1), (2, (1, 2, 1), 2), (5, (1, 1, 2), 1)])
+def test_dg_fe_q_transfer(mgb, orc, torch, mesh, precision):
+    """prolongate_add_cg_to_dg / vmult_residual_and_restrict_to_cg (laplace_operator_dg.h:851-860,1798-1819,1863-1894):
+    the same-degree transfer is the FE_Q cell-to-DoF map; restriction is the transpose, Dirichlet DoFs excluded"""
+    p, nsub, nref = mesh
+    lower, upper = (-0.9,) * 3, (1.0,) * 3
+    s = mgb.MultigridSolver(p, nsub, nref, lower=lower, upper=upper)
+    g = mgb.LaplaceOperatorDG(p, nsub, nref, lower=lower, upper=upper, trafo=np.eye(3), precision=precision)
+    o = orc.DGOperator(p, [k << nref for k in nsub], lower=lower, upper=upper, trafo=np.eye(3))
+    L = s.n_levels - 1
+    nd = s.dof_grid(L)
+    nc = g.n_cells()
+    n = p + 1
+    lexmap = s.lex_map(L)
+    # lexicographic FE_Q index of every DG DoF
+    cz, cy, cx, k, j, i = np.meshgrid(np.arange(nc[2]), np.arange(nc[1]), np.arange(nc[0]), np.arange(n), np.arange(n),
+                                      np.arange(n), indexing="ij")
+    lex = (((cz * p + k) * nd[1] + cy * p + j) * nd[0] + cx * p + i).ravel()
+    mask = np.ones((nd[2], nd[1], nd[0]))
+    mask[0], mask[-1], mask[:, 0], mask[:, -1], mask[:, :, 0], mask[:, :, -1] = (0,) * 6
+    mask = mask.ravel()
+    rng = np.random.default_rng(21)
+    cg_lex = rng.random(s.n_dofs(L))
+    dg0 = rng.random(g.m())
+    cg = np.zeros_like(cg_lex)
+    cg[lexmap] = cg_lex
+    tol = 1e-13 if precision else 1e-6
+    d_dg = torch.tensor(dg0, dtype=g.dtype, device="cuda")
+    g.prolongate_add_cg_to_dg(s, L, d_dg, torch.tensor(cg, dtype=g.dtype, device="cuda"))
+    assert rel(d_dg.double().cpu().numpy(), dg0 + (cg_lex * mask)[lex]) <= tol
+    # restriction of the residual
+    rhs, lhs = rng.random(g.m()), rng.random(g.m())
+    out = torch.full((s.n_dofs(L),), 7.0, dtype=g.dtype, device="cuda")  # must be overwritten (restricted_residual = 0 first)
+    g.vmult_residual_and_restrict_to_cg(s, L, torch.tensor(rhs, dtype=g.dtype, device="cuda"),
+                                        torch.tensor(lhs, dtype=g.dtype, device="cuda"), out)
+    res = rhs - o.vmult(lhs)
+    ref_lex = np.zeros(s.n_dofs(L))
+    np.add.at(ref_lex, lex, res)
+    ref_lex *= mask
+    got = out.double().cpu().numpy()[lexmap]
+    assert rel(got, ref_lex) <= (1e-12 if precision else 2e-5)
+    # transpose property: <P c, d> = <c, P^T d> on unconstrained entries
+    c2 = rng.random(s.n_dofs(L)) * mask
+    assert abs(((c2)[lex]) @ res - c2 @ ref_lex) <= 1e-10 * abs(c2 @ ref_lex)
