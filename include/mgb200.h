@@ -153,6 +153,12 @@ int mgb_op_set_kernel(mgb_solver s, int kernel);
 /* PreconditionChebyshev<LaplaceOperator<float>>  (deal.II; call sites multigrid_solver.h:271-288,657-678) */
 /* info[6] = min_eig, max_eig (Lanczos estimates), theta, delta, degree, eigenvalue-CG iterations */
 int mgb_smoother_info(mgb_solver s, int level, double info[6]);
+/* PreconditionChebyshev::initialize with other AdditionalData than the FE_Q solver's (multigrid_solver_dg.h:271-291):
+ * degree < 0 = automatic (numbers::invalid_unsigned_int), eig_cg_n_iterations < 0 = m() */
+int mgb_smoother_reinit(mgb_solver s, int level, double smoothing_range, int degree, int eig_cg_n_iterations);
+/* v_cycle(maxlevel, 1) on the solver's own vectors: solution_update[maxlevel] = V-cycle(defect[maxlevel])
+ * (multigrid_solver_dg.h:575-603; get the vectors with mgb_solver_vector, after the call)                      */
+int mgb_solver_vcycle_inplace(mgb_solver s);
 int mgb_smoother_vmult(mgb_solver s, int level, float *x, const float *b);  /* zero initial guess   */
 int mgb_smoother_step(mgb_solver s, int level, float *x, const float *b);   /* nonzero guess        */
 

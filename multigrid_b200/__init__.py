@@ -105,6 +105,8 @@ SYMBOLS = {
     "mgb_op_vmult_with_cg_update": (_i, [_vp, _i, _i, _d, _d, _vp, _vp, _vp, _vp, _dp]),
     "mgb_op_inverse_diagonal": (_i, [_vp, _i, _i, _vp]),
     "mgb_op_set_kernel": (_i, [_vp, _i]),
+    "mgb_smoother_reinit": (_i, [_vp, _i, _d, _i, _i]),
+    "mgb_solver_vcycle_inplace": (_i, [_vp]),
     "mgb_smoother_info": (_i, [_vp, _i, _dp]),
     "mgb_smoother_vmult": (_i, [_vp, _i, _vp, _vp]),
     "mgb_smoother_step": (_i, [_vp, _i, _vp, _vp]),
@@ -515,6 +517,12 @@ class MultigridSolver:
         _check(lib().mgb_smoother_info(self.h, self._l(level), info))
         return dict(min_eig=info[0], max_eig=info[1], theta=info[2], delta=info[3], degree=int(info[4]),
                     cg_iterations=int(info[5]))
+
+    def smoother_reinit(self, level, smoothing_range, degree, eig_cg_n_iterations):
+        _check(lib().mgb_smoother_reinit(self.h, self._l(level), smoothing_range, degree, eig_cg_n_iterations))
+
+    def vcycle_inplace(self):
+        _check(lib().mgb_solver_vcycle_inplace(self.h))
 
     def smoother_vmult(self, level, x, b):
         self._torch_sync()

@@ -2068,6 +2068,7 @@ mgb_set_last_error(const char *msg)
 // solver built on top of the FE_Q hierarchy); not part of the public C ABI
 struct mgb_solver_t;
 const mgb::LevelDesc *mgb_internal_level_desc(mgb_solver_t *s, int level);
+cudaStream_t          mgb_internal_stream(mgb_solver_t *s);
 
 struct mgb_solver_t
 {
@@ -2125,6 +2126,12 @@ check_level(MultigridSolver &s, int level)
   if (level < 0 || level >= s.n_levels)
     throw std::runtime_error("level out of range");
   return level;
+}
+
+cudaStream_t
+mgb_internal_stream(mgb_solver_t *s)
+{
+  return S(s).ctx.stream;
 }
 
 const mgb::LevelDesc *
@@ -2611,6 +2618,34 @@ extern "C"
         cudaGraphExecDestroy(g.exec);
     m.cycle_graphs.clear();
     m.choose_graph_level();
+    MGB_CATCH
+  }
+
+  int
+  mgb_smoother_reinit(mgb_solver s, int level, double smoothing_range, int degree, int eig_cg_n_iterations)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    m.ctx.sync();
+    for (auto &g : m.cycle_graphs) // captured with the previous smoother
+      if (g.exec)
+        cudaGraphExecDestroy(g.exec);
+    m.cycle_graphs.clear();
+    Chebyshev<float> &c   = *m.smooth[level];
+    c.smoothing_range     = smoothing_range;
+    c.degree              = degree < 0 ? Chebyshev<float>::invalid_degree : (unsigned int)degree;
+    c.eig_cg_n_iterations = eig_cg_n_iterations < 0 ? (unsigned int)m.matrix[level]->m_global() : (unsigned int)eig_cg_n_iterations;
+    c.initialize(m.ctx, *m.matrix[level], m.basis);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_vcycle_inplace(mgb_solver s)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    m.v_cycle(m.n_levels - 1, 1);
     MGB_CATCH
   }
 

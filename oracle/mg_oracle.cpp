@@ -1480,6 +1480,19 @@ extern "C"
     info[5]                   = c.cg_iterations;
   }
 
+  // re-initialise the smoother of one level (multigrid_solver_dg.h:271-291 uses other degrees / ranges than
+  // multigrid_solver.h:268-289): degree < 0 selects the automatic degree of the coarse solver
+  void
+  orc_mg_smoother_reinit(void *h, int level, double smoothing_range, int degree, int eig_cg_n_iterations)
+  {
+    MultigridSolver  *s = static_cast<MultigridSolver *>(h);
+    Chebyshev<float> &c = s->smooth[level];
+    c.smoothing_range     = smoothing_range;
+    c.degree              = degree < 0 ? Chebyshev<float>::invalid_degree : (unsigned int)degree;
+    c.eig_cg_n_iterations = eig_cg_n_iterations < 0 ? (unsigned int)s->matrix[level].m() : (unsigned int)eig_cg_n_iterations;
+    c.initialize(s->matrix[level]);
+  }
+
   // mode 0: x = vmult(b) (zero initial guess), mode 1: step(x, b)
   void
   orc_mg_chebyshev_apply(void *h, int level, int mode, double *x, const double *b)

@@ -54,6 +54,7 @@ def lib():
         L.orc_mg_inverse_diagonal_dp.argtypes = [C.c_void_p, C.c_int, dp]
         L.orc_mg_chebyshev_info.argtypes = [C.c_void_p, C.c_int, dp]
         L.orc_mg_chebyshev_apply.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp]
+        L.orc_mg_smoother_reinit.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_int]
         L.orc_mg_transfer.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp]
         L.orc_mg_vcycle.argtypes = [C.c_void_p, dp, dp]
         L.orc_mg_time_matvec.restype = C.c_double
@@ -167,6 +168,10 @@ class MultigridSolver:
         lib().orc_mg_chebyshev_info(self.h, self._l(level), _dp(info))
         return dict(min_eig=info[0], max_eig=info[1], theta=info[2], delta=info[3],
                     degree=int(info[4]), cg_iterations=int(info[5]))
+
+    def smoother_reinit(self, level, smoothing_range, degree, eig_cg_n_iterations):
+        """degree < 0: automatic degree (coarse solver); eig_cg_n_iterations < 0: as many as the level has DoFs"""
+        lib().orc_mg_smoother_reinit(self.h, self._l(level), smoothing_range, degree, eig_cg_n_iterations)
 
     def chebyshev_vmult(self, b, level=-1):
         b = np.ascontiguousarray(b, dtype=np.float64)
