@@ -228,6 +228,53 @@ int mgb_dg_timer_start(mgb_dg h);
 int mgb_dg_timer_stop(mgb_dg h, double *ms);
 int64_t mgb_dg_launch_count(mgb_dg h);
 
+/* ---- DG multigrid solver: multigrid::MultigridSolverDG<3,p,float,double>     common/multigrid_solver_dg.h:44-735
+ * Outer CG in double on the SIP-DG operator, preconditioned by one float cycle: Chebyshev(JacobiTransformed) on the
+ * DG space, same-degree transfer to FE_Q on the same mesh, the FE_Q V-cycle of mgb_solver below it (finest FE_Q
+ * smoother one degree lower, coarse range 2e-3, :272-293), transfer back, Chebyshev step (:605-633).
+ * Mesh: box [lower, upper], n_subdivisions coarse cells, n_refinements (poisson_dg/program.cc:356-409); problem
+ * data of poisson_dg/program.cc:70-135 (the same sine solution as poisson_cube).  One GPU.                    */
+typedef struct mgb_dg_solver_t *mgb_dg_solver;
+
+typedef struct mgb_dg_solver_options {
+  int degree;               /* 1..8                                                                      */
+  int n_subdivisions[3];
+  int n_refinements;
+  double lower[3], upper[3];
+  int degree_pre, degree_post; /* Chebyshev degree (equal, multigrid_solver_dg.h:83-85); default 3       */
+  int preconditioner;       /* of the DG smoother: 1 = JacobiTransformed (reference, :294-304), 0 = point Jacobi */
+  int device;
+} mgb_dg_solver_options;
+
+void mgb_dg_solver_default_options(mgb_dg_solver_options *opt);
+int mgb_dg_solver_create(const mgb_dg_solver_options *opt, mgb_dg_solver *out);    /* constructor :59-322 */
+int mgb_dg_solver_destroy(mgb_dg_solver h);
+int64_t mgb_dg_solver_n_dofs(mgb_dg_solver h);
+/* the two parts, for inspection and for the operator-level entry points; owned by the solver */
+int mgb_dg_solver_parts(mgb_dg_solver h, mgb_solver *fe_q_hierarchy, mgb_dg *dg_operator);
+/* std::pair<double,double> solve_cg(tolerance) :410-424: (log(tol)/log(rate), rate); also the iteration count.
+ * SolverCG with ReductionControl(100, 1e-16, tolerance), zero initial guess                                  */
+int mgb_dg_solver_solve_cg(mgb_dg_solver h, double tolerance, double *iterations_estimate, double *reduction_rate,
+                           unsigned int *n_iterations);
+/* residual norms of the last solve_cg: initial value and one per iteration; returns how many in *count       */
+int mgb_dg_solver_residual_history(mgb_dg_solver h, double *history, int capacity, int *count);
+/* vmult(dst, src) :429-441: one cycle as preconditioner, double device vectors of mgb_dg_solver_n_dofs()     */
+int mgb_dg_solver_vmult(mgb_dg_solver h, double *dst, const double *src);
+int mgb_dg_solver_l2_error(mgb_dg_solver h, double *error);                        /* compute_l2_error :328-366 */
+/* device pointers of the solver's vectors: 0 solution, 1 rhs, 2 residual (double); 3 defect_dg,
+ * 4 solution_update_dg (float; the smoother swaps vectors, ask again after a cycle)              :663-693 */
+int mgb_dg_solver_vector(mgb_dg_solver h, int which, void **dev_ptr);
+int mgb_dg_solver_get_solution(mgb_dg_solver h, double *solution_host);            /* get_solution :399-403 */
+/* info = {min_eig, max_eig, theta, delta, degree, cg_iterations} of smooth_dg                     :294-304 */
+int mgb_dg_solver_smoother_info(mgb_dg_solver h, double info[6]);
+int mgb_dg_solver_do_matvec(mgb_dg_solver h);                                      /* :539-543 (double)  */
+int mgb_dg_solver_do_matvec_smoother(mgb_dg_solver h);                             /* :548-552 (float)   */
+int mgb_dg_solver_sync(mgb_dg_solver h);
+/* end-to-end call: solve_cg, then the solution copied to a host buffer (may be NULL)                       */
+int mgb_dg_solver_solve_cg_host(mgb_dg_solver h, double tolerance, double *solution_host, double *iterations_estimate,
+                                double *reduction_rate, unsigned int *n_iterations);
+int64_t mgb_dg_solver_launch_count(mgb_dg_solver h);      /* kernels of the DG part + the FE_Q hierarchy */
+
 /* The subset of LinearAlgebra::distributed::Vector<Number> the drivers use (poisson_cube/program.cc:262-380,
  * multigrid_solver.h:54-67): device vectors of one level in the precision given; sums run over the owned
  * entries of all ranks.  dot: a . b (l2_norm = sqrt(dot(v,v)));  sadd: y = sy y + ax x;  set: y = value;

@@ -62,6 +62,20 @@ class DGOptions(C.Structure):
     ]
 
 
+class DGSolverOptions(C.Structure):
+    _fields_ = [
+        ("degree", C.c_int),
+        ("n_subdivisions", C.c_int * 3),
+        ("n_refinements", C.c_int),
+        ("lower", C.c_double * 3),
+        ("upper", C.c_double * 3),
+        ("degree_pre", C.c_int),
+        ("degree_post", C.c_int),
+        ("preconditioner", C.c_int),
+        ("device", C.c_int),
+    ]
+
+
 _lib = None
 
 # name -> (restype, argtypes); the full export list of include/mgb200.h
@@ -144,6 +158,24 @@ SYMBOLS = {
     "mgb_dg_timer_start": (_i, [_vp]),
     "mgb_dg_timer_stop": (_i, [_vp, _dp]),
     "mgb_dg_launch_count": (C.c_int64, [_vp]),
+    # DG multigrid solver
+    "mgb_dg_solver_default_options": (None, [C.POINTER(DGSolverOptions)]),
+    "mgb_dg_solver_create": (_i, [C.POINTER(DGSolverOptions), C.POINTER(_vp)]),
+    "mgb_dg_solver_destroy": (_i, [_vp]),
+    "mgb_dg_solver_n_dofs": (C.c_int64, [_vp]),
+    "mgb_dg_solver_parts": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp)]),
+    "mgb_dg_solver_solve_cg": (_i, [_vp, _d, _dp, _dp, C.POINTER(_u)]),
+    "mgb_dg_solver_residual_history": (_i, [_vp, _dp, _i, _ip]),
+    "mgb_dg_solver_vmult": (_i, [_vp, _vp, _vp]),
+    "mgb_dg_solver_l2_error": (_i, [_vp, _dp]),
+    "mgb_dg_solver_vector": (_i, [_vp, _i, C.POINTER(_vp)]),
+    "mgb_dg_solver_get_solution": (_i, [_vp, _vp]),
+    "mgb_dg_solver_smoother_info": (_i, [_vp, _dp]),
+    "mgb_dg_solver_do_matvec": (_i, [_vp]),
+    "mgb_dg_solver_do_matvec_smoother": (_i, [_vp]),
+    "mgb_dg_solver_sync": (_i, [_vp]),
+    "mgb_dg_solver_solve_cg_host": (_i, [_vp, _d, _vp, _dp, _dp, C.POINTER(_u)]),
+    "mgb_dg_solver_launch_count": (C.c_int64, [_vp]),
     # host-only helpers
     "mgb_host_basis": (_i, [_i] + [_dp] * 9),
     "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), _ip, C.POINTER(C.c_int64),
@@ -714,3 +746,119 @@ class LaplaceOperatorDG:
 
     def launch_count(self):
         return lib().mgb_dg_launch_count(self.h)
+
+
+class MultigridSolverDG:
+    """multigrid::MultigridSolverDG<3,p,float,double> (common/multigrid_solver_dg.h:44-735): CG in double on the
+    SIP-DG operator preconditioned by one float cycle (Chebyshev/JacobiTransformed on the DG space, same-degree
+    transfer to FE_Q, the FE_Q V-cycle below).  Problem data of poisson_dg/program.cc:70-135."""
+
+    JACOBI, JACOBI_TRANSFORMED = 0, 1
+
+    def __init__(self, degree=4, n_subdivisions=(1, 1, 1), n_refinements=3, lower=(-1.,) * 3, upper=(1.,) * 3,
+                 degree_pre=3, degree_post=3, preconditioner=1, device=0):
+        import torch
+        o = DGSolverOptions()
+        lib().mgb_dg_solver_default_options(C.byref(o))
+        o.degree = degree
+        if isinstance(n_subdivisions, int):
+            n_subdivisions = (n_subdivisions,) * 3
+        o.n_subdivisions[:] = list(n_subdivisions)
+        o.n_refinements = n_refinements
+        o.lower[:] = list(lower)
+        o.upper[:] = list(upper)
+        o.degree_pre, o.degree_post, o.preconditioner, o.device = degree_pre, degree_post, preconditioner, device
+        self.h = C.c_void_p()
+        self.device = torch.device("cuda", device)
+        self.degree = degree
+        _check(lib().mgb_dg_solver_create(C.byref(o), C.byref(self.h)))
+
+    def close(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.mgb_dg_solver_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def n_dofs(self):
+        return lib().mgb_dg_solver_n_dofs(self.h)
+
+    def sync(self):
+        _check(lib().mgb_dg_solver_sync(self.h))
+
+    def solve_cg(self, tolerance=1e-3):
+        """-> (log(tol)/log(rate), rate) as the reference; `last_step` holds the iteration count"""
+        est, rate, its = C.c_double(), C.c_double(), C.c_uint()
+        _check(lib().mgb_dg_solver_solve_cg(self.h, tolerance, C.byref(est), C.byref(rate), C.byref(its)))
+        self.last_step = its.value
+        return est.value, rate.value
+
+    def solve_cg_host(self, tolerance, solution_host=None):
+        est, rate, its = C.c_double(), C.c_double(), C.c_uint()
+        ptr = None if solution_host is None else C.c_void_p(
+            solution_host.data_ptr() if hasattr(solution_host, "data_ptr") else solution_host.ctypes.data)
+        _check(lib().mgb_dg_solver_solve_cg_host(self.h, tolerance, ptr, C.byref(est), C.byref(rate), C.byref(its)))
+        self.last_step = its.value
+        return est.value, rate.value
+
+    def residual_history(self):
+        hist = np.zeros(128)
+        cnt = C.c_int()
+        _check(lib().mgb_dg_solver_residual_history(self.h, hist.ctypes.data_as(_dp), 128, C.byref(cnt)))
+        return hist[:cnt.value]
+
+    def vmult(self, dst, src):
+        """one cycle as preconditioner: double device tensors"""
+        import torch
+        assert dst.dtype == torch.float64 and src.dtype == torch.float64 and dst.numel() == src.numel() == self.n_dofs()
+        torch.cuda.synchronize(self.device)
+        _check(lib().mgb_dg_solver_vmult(self.h, C.c_void_p(dst.data_ptr()), C.c_void_p(src.data_ptr())))
+        self.sync()
+
+    def compute_l2_error(self):
+        e = C.c_double()
+        _check(lib().mgb_dg_solver_l2_error(self.h, C.byref(e)))
+        return e.value
+
+    def get_solution(self):
+        out = np.zeros(self.n_dofs())
+        _check(lib().mgb_dg_solver_get_solution(self.h, C.c_void_p(out.ctypes.data)))
+        return out
+
+    def get_vector(self, which):
+        """host copy of 0 solution, 1 rhs, 2 residual (double), 3 defect_dg, 4 solution_update_dg (float)"""
+        p = C.c_void_p()
+        self.sync()
+        _check(lib().mgb_dg_solver_vector(self.h, which, C.byref(p)))
+        out = np.zeros(self.n_dofs(), dtype=np.float64 if which < 3 else np.float32)
+        fe, _ = self.parts()
+        _check(lib().mgb_copy_to_host(fe, C.c_void_p(out.ctypes.data), p, out.nbytes))
+        return out
+
+    def smoother_info(self):
+        info = np.zeros(6)
+        _check(lib().mgb_dg_solver_smoother_info(self.h, info.ctypes.data_as(_dp)))
+        return dict(min_eig=info[0], max_eig=info[1], theta=info[2], delta=info[3], degree=int(info[4]),
+                    cg_iterations=int(info[5]))
+
+    def parts(self):
+        """(handle of the FE_Q hierarchy, handle of the DG operator), owned by this solver"""
+        fe, dg = C.c_void_p(), C.c_void_p()
+        _check(lib().mgb_dg_solver_parts(self.h, C.byref(fe), C.byref(dg)))
+        return fe, dg
+
+    def fe_smoother_info(self, level):
+        fe, _ = self.parts()
+        info = np.zeros(6)
+        _check(lib().mgb_smoother_info(fe, level, info.ctypes.data_as(_dp)))
+        return dict(min_eig=info[0], max_eig=info[1], theta=info[2], delta=info[3], degree=int(info[4]),
+                    cg_iterations=int(info[5]))
+
+    def do_matvec(self):
+        _check(lib().mgb_dg_solver_do_matvec(self.h))
+
+    def do_matvec_smoother(self):
+        _check(lib().mgb_dg_solver_do_matvec_smoother(self.h))
+
+    def launch_count(self):
+        return lib().mgb_dg_solver_launch_count(self.h)

@@ -15,8 +15,11 @@
 #include "dg_kernels.cuh"
 #include "level.h"
 
+#include "functions.cuh"
+
 struct mgb_solver_t;
 const mgb::LevelDesc *mgb_internal_level_desc(mgb_solver_t *s, int level);
+cudaStream_t          mgb_internal_stream(mgb_solver_t *s);
 
 namespace mgb
 {
@@ -231,6 +234,35 @@ namespace mgb
       f(i);
   }
 
+  // sum_i f(i, acc) for NS sums (warp shuffles, one atomic per block and sum)
+  template <int NS, typename F>
+  __global__ void
+  k_dg_reduce(const size_t n, F f, double *out)
+  {
+    double acc[NS];
+    for (int s = 0; s < NS; ++s)
+      acc[s] = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+      f(i, acc);
+    __shared__ double red[NS][8];
+    for (int s = 0; s < NS; ++s)
+      {
+        double v = acc[s];
+        for (int o = 16; o > 0; o >>= 1)
+          v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0)
+          red[s][threadIdx.x >> 5] = v;
+      }
+    __syncthreads();
+    if (threadIdx.x < NS)
+      {
+        double v = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w)
+          v += red[threadIdx.x][w];
+        atomicAdd(&out[threadIdx.x], v);
+      }
+  }
+
   // four sums of vmult_with_cg_update: q.p, r.r, q.r, q.q (warp shuffles, one atomic per block and sum)
   template <typename T>
   __global__ void
@@ -330,6 +362,7 @@ namespace mgb
     int            p = 0, n = 0, nc[3] = {0, 0, 0};
     size_t         n_cells = 0, n_dofs = 0;
     cudaStream_t   stream   = nullptr;
+    bool           owns_stream = true;
     cudaEvent_t    ev[2]    = {nullptr, nullptr};
     int64_t        launches = 0;
     Basis          basis;
@@ -440,11 +473,42 @@ namespace mgb
         cudaFree(scal_dev);
       if (scal_host)
         cudaFreeHost(scal_host);
-      if (stream)
+      if (stream && owns_stream)
         cudaStreamDestroy(stream);
     }
 
     unsigned grid(const size_t count) const { return (unsigned)std::min<size_t>((count + 255) / 256, 148 * 16); }
+
+    // run on another stream (the FE_Q solver's, for the DG multigrid solver)
+    void
+    use_stream(cudaStream_t s)
+    {
+      if (owns_stream && stream)
+        cudaStreamDestroy(stream);
+      stream      = s;
+      owns_stream = false;
+    }
+    template <typename F>
+    void foreach (const size_t count, F f)
+    {
+      k_dg_foreach<<<grid(count), 256, 0, stream>>>(count, f);
+      ++launches;
+      MGB_DG_CHECK(cudaGetLastError());
+    }
+    // r[0..NS) = sums over i of what f adds to acc[]; one host synchronisation (the reference's MPI sum)
+    template <int NS, typename F>
+    void
+    sums(double *r, F f)
+    {
+      static_assert(NS <= 4, "scal_dev holds four sums");
+      MGB_DG_CHECK(cudaMemsetAsync(scal_dev, 0, 4 * sizeof(double), stream));
+      k_dg_reduce<NS><<<grid(n_dofs), 256, 0, stream>>>(n_dofs, f, scal_dev);
+      ++launches;
+      MGB_DG_CHECK(cudaMemcpyAsync(scal_host, scal_dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+      MGB_DG_CHECK(cudaStreamSynchronize(stream));
+      for (int s = 0; s < NS; ++s)
+        r[s] = scal_host[s];
+    }
 
     template <typename T>
     T *
@@ -713,7 +777,50 @@ namespace mgb
       preconditioner_vmult<T>(solution, rhs, f2);
     }
   };
+
+  // extreme eigenvalues of the Lanczos tridiagonal matrix of the eigenvalue-estimating CG (Sturm bisection)
+  static void
+  dg_tridiagonal_extreme_eigenvalues(const std::vector<double> &diag, const std::vector<double> &off, double &emin,
+                                     double &emax)
+  {
+    const int k = (int)diag.size();
+    emin = emax = 1.;
+    if (k == 0)
+      return;
+    double lo = 1e300, hi = -1e300;
+    for (int i = 0; i < k; ++i)
+      {
+        const double r = (i > 0 ? std::fabs(off[i - 1]) : 0.) + (i < k - 1 ? std::fabs(off[i]) : 0.);
+        lo             = std::min(lo, diag[i] - r);
+        hi             = std::max(hi, diag[i] + r);
+      }
+    const auto count_below = [&](const double x) {
+      int    cnt = 0;
+      double q   = 1;
+      for (int i = 0; i < k; ++i)
+        {
+          q = diag[i] - x - (i > 0 ? off[i - 1] * off[i - 1] / q : 0.);
+          if (q == 0)
+            q = 1e-300;
+          cnt += q < 0;
+        }
+      return cnt;
+    };
+    const auto kth = [&](const int idx) {
+      double a = lo, c = hi;
+      for (int it = 0; it < 200; ++it)
+        {
+          const double mid = 0.5 * (a + c);
+          (count_below(mid) > idx ? c : a) = mid;
+        }
+      return 0.5 * (a + c);
+    };
+    emin = kth(0);
+    emax = kth(k - 1);
+  }
 } // namespace mgb
+
+#include "dg_solver.cuh"
 
 // ====================================================================== C ABI
 using namespace mgb;
@@ -746,6 +853,20 @@ DGH(mgb_dg h)
 {
   if (!h || !h->impl)
     throw std::runtime_error("null DG operator handle");
+  return *h->impl;
+}
+
+struct mgb_dg_solver_t
+{
+  DGMultigridSolver *impl;
+  mgb_dg_t           op; // view of impl->op for the operator-level entry points
+};
+
+static DGMultigridSolver &
+DGS(mgb_dg_solver h)
+{
+  if (!h || !h->impl)
+    throw std::runtime_error("null DG solver handle");
   return *h->impl;
 }
 
@@ -1000,5 +1121,207 @@ extern "C"
   mgb_dg_launch_count(mgb_dg h)
   {
     return h && h->impl ? h->impl->launches : -1;
+  }
+  // ------------------------------------------------------------------ DG multigrid solver
+  void
+  mgb_dg_solver_default_options(mgb_dg_solver_options *o)
+  {
+    if (!o)
+      return;
+    std::memset(o, 0, sizeof(*o));
+    o->degree = 4;
+    for (int d = 0; d < 3; ++d)
+      {
+        o->n_subdivisions[d] = 1;
+        o->lower[d]          = -1.; // poisson_dg/program.cc:357-376 (doubling mesh, remainder 0)
+        o->upper[d]          = 1.;
+      }
+    o->n_refinements  = 3;
+    o->degree_pre     = 3; // poisson_dg/program.cc:518-519
+    o->degree_post    = 3;
+    o->preconditioner = 1;
+  }
+
+  int
+  mgb_dg_solver_create(const mgb_dg_solver_options *opt, mgb_dg_solver *out)
+  {
+    DG_TRY
+    if (!opt || !out)
+      throw std::runtime_error("null argument");
+    *out      = nullptr;
+    auto *h   = new mgb_dg_solver_t;
+    h->impl   = nullptr;
+    h->op.impl = nullptr;
+    try
+      {
+        h->impl    = new DGMultigridSolver(*opt);
+        h->op.impl = h->impl->op;
+      }
+    catch (...)
+      {
+        delete h;
+        throw;
+      }
+    *out = h;
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_destroy(mgb_dg_solver h)
+  {
+    DG_TRY
+    if (h)
+      {
+        delete h->impl;
+        delete h;
+      }
+    DG_CATCH
+  }
+
+  int64_t
+  mgb_dg_solver_n_dofs(mgb_dg_solver h)
+  {
+    return h && h->impl ? (int64_t)h->impl->N : -1;
+  }
+
+  int
+  mgb_dg_solver_parts(mgb_dg_solver h, mgb_solver *fe, mgb_dg *dg)
+  {
+    DG_TRY
+    DGMultigridSolver &m = DGS(h);
+    if (fe)
+      *fe = m.fe;
+    if (dg)
+      *dg = &h->op;
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_solve_cg(mgb_dg_solver h, double tolerance, double *its_estimate, double *rate, unsigned int *its)
+  {
+    DG_TRY
+    if (!(tolerance > 0 && tolerance < 1))
+      throw std::runtime_error("tolerance must be in (0, 1)");
+    DGS(h).solve_cg(tolerance, its_estimate, rate, its);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_residual_history(mgb_dg_solver h, double *history, int capacity, int *count)
+  {
+    DG_TRY
+    DGMultigridSolver &m = DGS(h);
+    const int          k = (int)m.residual_history.size();
+    for (int i = 0; i < std::min(k, capacity); ++i)
+      history[i] = m.residual_history[i];
+    if (count)
+      *count = k;
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_vmult(mgb_dg_solver h, double *dst, const double *src)
+  {
+    DG_TRY
+    DGS(h).vmult(dst, src);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_l2_error(mgb_dg_solver h, double *error)
+  {
+    DG_TRY
+    *error = DGS(h).compute_l2_error();
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_vector(mgb_dg_solver h, int which, void **dev_ptr)
+  {
+    DG_TRY
+    DGMultigridSolver &m = DGS(h);
+    switch (which)
+      {
+        case 0: *dev_ptr = m.solution; break;
+        case 1: *dev_ptr = m.rhs; break;
+        case 2: *dev_ptr = m.g; break;
+        case 3: *dev_ptr = m.defect_dg; break;
+        case 4: *dev_ptr = m.solution_update_dg; break;
+        default: throw std::runtime_error("unknown vector id");
+      }
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_get_solution(mgb_dg_solver h, double *host)
+  {
+    DG_TRY
+    DGMultigridSolver &m = DGS(h);
+    MGB_DG_CHECK(cudaMemcpyAsync(host, m.solution, m.N * sizeof(double), cudaMemcpyDeviceToHost, m.op->stream));
+    MGB_DG_CHECK(cudaStreamSynchronize(m.op->stream));
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_smoother_info(mgb_dg_solver h, double info[6])
+  {
+    DG_TRY
+    const DGChebyshev &c = DGS(h).smooth_dg;
+    info[0]              = c.min_eig;
+    info[1]              = c.max_eig;
+    info[2]              = c.theta;
+    info[3]              = c.delta;
+    info[4]              = c.degree;
+    info[5]              = c.cg_iterations;
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_do_matvec(mgb_dg_solver h)
+  {
+    DG_TRY
+    DGMultigridSolver &m = DGS(h);
+    m.op->apply<double>(DG_SET, m.g, m.solution);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_do_matvec_smoother(mgb_dg_solver h)
+  {
+    DG_TRY
+    DGMultigridSolver &m = DGS(h);
+    m.op->apply<float>(DG_SET, m.solution_update_dg, m.defect_dg);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_sync(mgb_dg_solver h)
+  {
+    DG_TRY
+    MGB_DG_CHECK(cudaStreamSynchronize(DGS(h).op->stream));
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solver_solve_cg_host(mgb_dg_solver h, double tolerance, double *solution_host, double *its_estimate, double *rate,
+                              unsigned int *its)
+  {
+    DG_TRY
+    if (!(tolerance > 0 && tolerance < 1))
+      throw std::runtime_error("tolerance must be in (0, 1)");
+    DGMultigridSolver &m = DGS(h);
+    m.solve_cg(tolerance, its_estimate, rate, its);
+    if (solution_host)
+      MGB_DG_CHECK(cudaMemcpyAsync(solution_host, m.solution, m.N * sizeof(double), cudaMemcpyDeviceToHost, m.op->stream));
+    MGB_DG_CHECK(cudaStreamSynchronize(m.op->stream));
+    DG_CATCH
+  }
+
+  int64_t
+  mgb_dg_solver_launch_count(mgb_dg_solver h)
+  {
+    if (!h || !h->impl)
+      return -1;
+    return h->impl->op->launches + mgb_solver_launch_count(h->impl->fe);
   }
 }

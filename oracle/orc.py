@@ -355,3 +355,154 @@ class JacobiTransformed:
         c = np.einsum("kz,jy,ix,czyx->ckji", V, V, V, r)                 # V^T in every direction
         c = c / self.diag.reshape(-1, n, n, n)
         return np.einsum("kz,jy,ix,ckji->czyx", V, V, V, c).ravel()     # back to the nodal basis
+
+
+class ChebyshevDG:
+    """deal.II PreconditionChebyshev as multigrid_solver_dg.h:294-304 sets it up over the DG operator: eigenvalue
+    estimate by eig_cg_n_iterations of CG on P^-1 A from the vector "index mod 11, mean removed", max estimate x 1.2,
+    then the three-term recurrence (vmult: zero start, step: given start)."""
+
+    def __init__(self, op, prec, smoothing_range=20., degree=3, eig_cg_n_iterations=15):
+        self.op, self.prec, self.degree = op, prec, degree
+        N = op.n_dofs()
+        g = (np.arange(N) % 11).astype(np.float64)
+        g = -(g - g.mean())
+        diag, off = [], []
+        h = prec(g)
+        d = -h
+        gh = g @ h
+        alpha_old = beta_old = 0.0
+        for it in range(1, eig_cg_n_iterations + 1):
+            h = op.vmult(d)
+            alpha = gh / (d @ h)
+            g = g + alpha * h
+            if it == 1:
+                diag.append(1. / alpha)
+            else:
+                diag.append(1. / alpha + beta_old / alpha_old)
+                off.append(np.sqrt(beta_old) / alpha_old)
+            self.cg_iterations = it
+            if np.linalg.norm(g) <= 1e-10:
+                break
+            h = prec(g)
+            gh_new = g @ h
+            beta = gh_new / gh
+            gh = gh_new
+            d = beta * d - h
+            alpha_old, beta_old = alpha, beta
+        T = np.diag(diag) + np.diag(off, 1) + np.diag(off, -1)
+        ev = np.linalg.eigvalsh(T)
+        self.min_eig, self.max_eig = ev[0], ev[-1]
+        max_est = 1.2 * self.max_eig
+        a = max_est / smoothing_range
+        self.theta, self.delta = 0.5 * (max_est + a), 0.5 * (max_est - a)
+
+    def _loop(self, x, x_old, b):
+        rhok, sigma = self.delta / self.theta, self.theta / self.delta
+        for _ in range(self.degree - 1):
+            rhokp = 1. / (2. * sigma - rhok)
+            f1, f2 = rhokp * rhok, 2. * rhokp / self.delta
+            rhok = rhokp
+            x, x_old = x + f1 * (x - x_old) + f2 * self.prec(b - self.op.vmult(x)), x
+        return x
+
+    def vmult(self, b):
+        return self._loop(self.prec(b) / self.theta, np.zeros_like(b), b)
+
+    def step(self, x, b):
+        return self._loop(x + self.prec(b - self.op.vmult(x)) / self.theta, x, b)
+
+
+class MultigridSolverDG:
+    """multigrid::MultigridSolverDG (common/multigrid_solver_dg.h:44-735) composed from the oracle's parts: the
+    face-based DG operator (dg_oracle.cpp), JacobiTransformed / ChebyshevDG above, and the FE_Q hierarchy of
+    mg_oracle.cpp with the smoother settings of :272-293.  Double precision in the DG part (the reference runs
+    the cycle in float); small meshes only."""
+
+    def __init__(self, degree, n_subdivisions, n_refine, lower=(-1.,) * 3, upper=(1.,) * 3, degree_pre=3,
+                 degree_post=3, preconditioner=1):
+        if isinstance(n_subdivisions, int):
+            n_subdivisions = (n_subdivisions,) * 3
+        assert degree_pre == degree_post
+        self.fe = MultigridSolver(degree, n_subdivisions, n_refine, lower, upper, degree_pre, degree_post, 1)
+        L = self.fe.n_levels - 1
+        self.fe.smoother_reinit(0, 2e-3, -1, -1)
+        if L > 0:
+            self.fe.smoother_reinit(L, 20., max(1, degree_pre - 1), 15)
+        nc = [k << n_refine for k in n_subdivisions]
+        self.op = DGOperator(degree, nc, lower=lower, upper=upper, trafo=np.eye(3))
+        if preconditioner == 1:
+            self.jt = JacobiTransformed(self.op)
+            self.prec = self.jt.vmult
+        else:
+            inv = 1. / self.op.diagonal()
+            self.prec = lambda v: inv * v
+        self.smooth = ChebyshevDG(self.op, self.prec, 20., degree_pre, 15)
+        p, n = degree, degree + 1
+        nd = self.fe.dof_grid(L)
+        cz, cy, cx, k, j, i = np.meshgrid(np.arange(nc[2]), np.arange(nc[1]), np.arange(nc[0]), np.arange(n),
+                                          np.arange(n), np.arange(n), indexing="ij")
+        self.lex = (((cz * p + k) * nd[1] + cy * p + j) * nd[0] + cx * p + i).ravel()
+        mask = np.ones((nd[2], nd[1], nd[0]))
+        mask[0], mask[-1], mask[:, 0], mask[:, -1], mask[:, :, 0], mask[:, :, -1] = (0,) * 6
+        self.mask = mask.ravel()
+        # rhs_i = (f, phi_i) with QGauss(p+1)   (multigrid_solver_dg.h:243-265)
+        b = basis(p)
+        S, xq, wq = b["S"], b["xq"], b["wq"]
+        h = [(upper[d] - lower[d]) / nc[d] for d in range(3)]
+        self.h, self.nc, self.lower = h, nc, lower
+        X = lower[0] + h[0] * (cx + xq[i])
+        Y = lower[1] + h[1] * (cy + xq[j])
+        Z = lower[2] + h[2] * (cz + xq[k])
+        self.Xq = (X, Y, Z)
+        f = 3 * (3 * np.pi) ** 2 * np.sin(3 * np.pi * X) * np.sin(3 * np.pi * Y) * np.sin(3 * np.pi * Z)
+        self.W = wq[k] * wq[j] * wq[i] * h[0] * h[1] * h[2]
+        self.S = S
+        self.rhs = np.einsum("rc,qb,pa,zyxrqp->zyxcba", S, S, S, f * self.W).ravel()
+        self.solution = np.zeros_like(self.rhs)
+
+    def n_dofs(self):
+        return self.op.n_dofs()
+
+    def vmult(self, src):
+        """dg_v_cycle(1) (multigrid_solver_dg.h:605-633)"""
+        x = self.smooth.vmult(src)
+        res = src - self.op.vmult(x)
+        d = np.zeros(self.mask.size)
+        np.add.at(d, self.lex, res)
+        u = self.fe.vcycle(d * self.mask)
+        x = x + (u * self.mask)[self.lex]
+        return self.smooth.step(x, src)
+
+    def solve_cg(self, tolerance=1e-3):
+        """SolverCG with ReductionControl(100, 1e-16, tolerance) (:410-424) -> (estimate, rate, residual history)"""
+        x = np.zeros_like(self.rhs)
+        g = -self.rhs
+        res0 = np.linalg.norm(g)
+        hist = [res0]
+        it, gh, d = 0, 0., None
+        while not (hist[-1] <= 1e-16 or hist[-1] <= tolerance * res0):
+            it += 1
+            h = self.vmult(g)
+            gh_new = g @ h
+            d = -h if it == 1 else (gh_new / gh) * d - h
+            gh = gh_new
+            h = self.op.vmult(d)
+            alpha = gh / (d @ h)
+            x += alpha * d
+            g = g + alpha * h
+            hist.append(np.linalg.norm(g))
+            assert it < 100
+        self.solution = x
+        self.last_step = it
+        rate = (hist[-1] / res0) ** (1. / it)
+        return np.log(tolerance) / np.log(rate), rate, np.array(hist)
+
+    def compute_l2_error(self):
+        """:328-366"""
+        n = self.op.degree + 1
+        u = self.solution.reshape(self.nc[2], self.nc[1], self.nc[0], n, n, n)
+        uq = np.einsum("rc,qb,pa,zyxcba->zyxrqp", self.S, self.S, self.S, u)
+        X, Y, Z = self.Xq
+        ex = np.sin(3 * np.pi * X) * np.sin(3 * np.pi * Y) * np.sin(3 * np.pi * Z)
+        return np.sqrt(np.sum((uq - ex) ** 2 * self.W) / np.sum(self.W))
