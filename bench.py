@@ -362,6 +362,12 @@ def dg_lines(r):
     for v in out.values():
         v["frac_hbm"] = v["gbs"] / r["hbm_gbs"]
     out["workload"] = "matvec_dg s=20: 128x128x64 cells, FE_DGQ(4), affine sheared mesh, 131072000 DoF"
+    # poisson_dg/program.cc:227-263 on its doubling-mesh cycle 21 (128^3 cells, 262 M DG DoF), default tolerance 1e-3:
+    # MultigridSolverDG = CG(double) + Chebyshev/JacobiTransformed + FE_Q V-cycle (float), minimum of 4 solves
+    import time_dg_solver
+    torch.cuda.empty_cache()
+    out["poisson_dg_solve"] = time_dg_solver.run(21, DEGREE, 1e-3)
+    out["poisson_dg_solve"]["workload"] = "poisson_dg cycle 21: [-1,1]^3, 128^3 cells, FE_DGQ(4), solve_cg(1e-3)"
     return out
 
 

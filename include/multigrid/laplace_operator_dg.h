@@ -1,6 +1,6 @@
 // multigrid::LaplaceOperatorCompactCombine<dim, fe_degree, Number, type> -- names and argument order of
 // common/laplace_operator_dg.h:360-363,771-955 over the C ABI (include/mgb200.h, mgb_dg_*).  type = 1 (FE_DGQ on
-// Gauss-Lobatto points) is built; the Chebyshev preconditioner is the point-Jacobi diagonal.
+// Gauss-Lobatto points) is built; the Chebyshev preconditioner is the point-Jacobi diagonal or JacobiTransformed.
 #ifndef MULTIGRID_LAPLACE_OPERATOR_DG_H
 #define MULTIGRID_LAPLACE_OPERATOR_DG_H
 
@@ -109,6 +109,32 @@ namespace multigrid
                                                solution.begin(), solution_old.begin()));
       if (iteration_index > 0)
         solution.swap(solution_old);
+    }
+    // preconditioner of the Chebyshev update: point Jacobi, or the JacobiTransformed object that the reference
+    // passes as `prec` (laplace_operator_dg.h:2028-2256, matvec_dg_cheby/program.cc:108)
+    enum Preconditioner
+    {
+      point_jacobi       = 0,
+      jacobi_transformed = 1
+    };
+    void set_preconditioner(const Preconditioner kind) { check(mgb_dg_set_preconditioner(h_, (int)kind)); }
+    // JacobiTransformed::vmult  :2046-2083 (or the point-Jacobi scaling)
+    void
+    preconditioner_vmult(VectorType &dst, const VectorType &src) const
+    {
+      check(mgb_dg_preconditioner_vmult(h_, prec, dst.begin(), src.begin()));
+    }
+    // :1863-1894 and :851-860: the FE_Q space is level `level` of a multigrid::MultigridSolver on the same mesh
+    void
+    prolongate_add_cg_to_dg(VectorType &dst, const DeviceVector<Number> &src_cg) const
+    {
+      check(mgb_dg_prolongate_add_cg_to_dg(h_, src_cg.solver(), src_cg.level(), prec, dst.begin(), src_cg.begin()));
+    }
+    void
+    vmult_residual_and_restrict_to_cg(const VectorType &rhs, const VectorType &lhs, DeviceVector<Number> &residual_cg) const
+    {
+      check(mgb_dg_vmult_residual_and_restrict_to_cg(h_, residual_cg.solver(), residual_cg.level(), prec, rhs.begin(),
+                                                     lhs.begin(), residual_cg.begin()));
     }
     void synchronize() const { check(mgb_dg_sync(h_)); }
 

@@ -6,6 +6,7 @@
 #include <cstdlib>
 
 #include "multigrid/laplace_operator_dg.h"
+#include "multigrid/multigrid_solver_dg.h"
 #include "multigrid/multigrid_solver.h"
 
 int
@@ -53,6 +54,31 @@ main(int argc, char **argv)
       for (std::size_t i = 0; i < hy.size(); ++i)
         xAx += hx[i] * hy[i];
       std::printf("dg m %zu penalty_x %.6e xAx %.12e\n", dg.m(), (double)dg.get_penalty(0, 0), xAx);
+      dg.set_preconditioner(dg.jacobi_transformed);
+      dg.preconditioner_vmult(y, x); // y = P^-1 x with JacobiTransformed
+      dg.synchronize();
+      double xPx = 0;
+      {
+        const std::vector<double> hp = y.export_to_host();
+        for (std::size_t i = 0; i < hp.size(); ++i)
+          xPx += hx[i] * hp[i];
+      }
+      std::printf("xPx %.12e\n", xPx);
+      if (argc > 99) // compiled, not run: the transfer needs an FE_Q level on the same (unsheared) mesh
+        {
+          dg.prolongate_add_cg_to_dg(y, p);
+          dg.vmult_residual_and_restrict_to_cg(x, y, q);
+        }
+
+      // DG multigrid solver as poisson_dg/program.cc:227-263: [-1,1]^3, 2 refinements, tolerance 1e-3
+      multigrid::MeshDescription dmesh;
+      dmesh.n_refinements = 2;
+      for (int d = 0; d < 3; ++d)
+        dmesh.lower[d] = -1.;
+      multigrid::MultigridSolverDG<3, degree, float, double> dg_solver(dmesh, 3, 3, 1);
+      const std::pair<double, double>                         dg_cg = dg_solver.solve_cg(1e-3);
+      std::printf("dg_cg_its %u dg_cg_rate %.6e dg_l2 %.6e\n", dg_solver.last_step(), dg_cg.second,
+                  dg_solver.compute_l2_error());
     }
   catch (const std::exception &e)
     {

@@ -64,3 +64,10 @@ def test_example_driver_matches_oracle(mgb, orc):
     x = np.ones(d.n_dofs())
     assert abs(float(out["xAx"]) - x @ d.vmult(x)) <= 1e-10 * abs(x @ d.vmult(x))
     assert abs(float(out["penalty_x"]) - d.penalty()[0]) <= 1e-6 * d.penalty()[0]  # printed with 7 digits
+    jt = orc.JacobiTransformed(d)
+    assert float(out["xPx"]) > 0 and abs(float(out["xPx"]) - x @ jt.vmult(x)) <= 1e-9 * abs(x @ jt.vmult(x))
+    ds = orc.MultigridSolverDG(4, (1, 1, 1), 2)
+    _, rate_dg, _ = ds.solve_cg(1e-3)
+    assert int(out["dg_cg_its"]) == ds.last_step
+    assert abs(float(out["dg_cg_rate"]) - rate_dg) <= 3e-2 * rate_dg
+    assert abs(float(out["dg_l2"]) - ds.compute_l2_error()) <= 1e-3 * ds.compute_l2_error()
