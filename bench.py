@@ -318,9 +318,14 @@ def report(args, r):
                "apply_f64": kernel("apply_f64", 2, 8)}
     epi_ms, epi_cnt = cls["apply_epilogue"]
     dom = kernels["apply_f32_chebyshev"]
-    roofline = {"bound": "hbm", "kernel": "k_apply_cartesian<4,4,float> with fused Chebyshev update (finest level)",
+    # dram__bytes_read.sum + dram__bytes_write.sum of one finest-level launch on 128^3 cells per GPU, from the
+    # `ncu --set full` capture summarised in profiles/r1_tile_f32x2_ncu_full_summary.txt (2.215 GB + 0.523 GB)
+    traffic = 2.215254e9 + 0.522742e9 if n == 135005697 else None
+    roofline = {"bound": "hbm", "kernel": "k_apply_tile_f32x2<4, APPLY_CHEBYSHEV> (float operator apply with fused "
+                                          "Chebyshev update, finest level)",
                 "achieved": dom["achieved_gbs"], "peak": hbm, "unit": "GB/s", "frac": dom["frac_hbm"],
-                "traffic": None, "peak_source": r["peak_src"], "ms_per_launch": dom["ms_per_launch"],
+                "traffic": traffic, "traffic_source": "profiles/r1_tile_f32x2_ncu_full_summary.txt",
+                "peak_source": r["peak_src"], "ms_per_launch": dom["ms_per_launch"],
                 "share_of_step": dom["share_of_step"],
                 "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_dof"] * n}
     fl = flops_per_dof(DEGREE)

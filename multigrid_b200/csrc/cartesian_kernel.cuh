@@ -19,6 +19,7 @@
 // cf. the pre/post range operations of laplace_operator.h:607-741) is fused into the same pass and
 // each vector is read / written exactly once from HBM; there are no atomics and no index table.
 #pragma once
+#include <cstdlib>
 #include <type_traits>
 #include <utility>
 
@@ -67,6 +68,10 @@ namespace mgb
     static constexpr int PQP     = TW * TW + 16;           // plane pitch of P, Q (bank-conflict free)
     static constexpr int PQ_SIZE = p * PQP;
     static constexpr int SMEM    = 2 * U_SIZE + 2 * MX_SIZE + 2 * PQ_SIZE; // source planes double-buffered
+    // packed float kernel: plane pitch of the (mx, kx) pairs such that the x-stage tasks of a warp, which run
+    // through (row, plane, cell column), store to consecutive 8-byte slots modulo 16 across a change of plane
+    static constexpr int MXP2  = TW * NI + (((NI - TW * NI) % 16) + 16) % 16;
+    static constexpr int SMEM2 = 2 * U_SIZE + 2 * p * MXP2 + 2 * PQ_SIZE;  // in floats
   };
 
   // p output rows of cell-row products: out[r] = sum_i A[r][i] x[p+i] (own cell, if it exists)
@@ -495,16 +500,34 @@ namespace mgb
       }
   }
 
+  // cartesian_kernel_f32x2.cuh: the float instance on packed fp32 arithmetic
+  template <int p, int MODE>
+  __global__ void k_apply_tile_f32x2(const ApplyArgs<float> A, const int layers_per_segment, const int layer_begin,
+                                     const int layer_end);
+
+  // MGB200_F32X2=0 selects the scalar float kernel (A/B measurements)
+  inline bool
+  use_f32x2()
+  {
+    static const bool on = [] {
+      const char *e = getenv("MGB200_F32X2");
+      return !(e && e[0] == '0');
+    }();
+    return on;
+  }
+
   template <int p, typename T, int MODE>
   void
   launch_apply_tile(const ApplyArgs<T> &A, cudaStream_t stream)
   {
     using C           = TileCfg<p>;
-    const size_t smem = (size_t)C::SMEM * sizeof(T);
+    const size_t smem = (size_t)C::SMEM * sizeof(T), smem2 = (size_t)C::SMEM2 * sizeof(float);
     static bool  first = true;
     if (first)
       {
         cudaFuncSetAttribute(k_apply_tile<p, T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if constexpr (std::is_same<T, float>::value)
+          cudaFuncSetAttribute(k_apply_tile_f32x2<p, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
         first = false;
       }
     const int ntiles = A.L.nt[0] * A.L.nt[1];
@@ -522,6 +545,12 @@ namespace mgb
       nseg = 1;
     const int lps = (ncz + nseg - 1) / nseg;
     nseg          = (ncz + lps - 1) / lps;
+    if constexpr (std::is_same<T, float>::value)
+      if (use_f32x2())
+        {
+          k_apply_tile_f32x2<p, MODE><<<ntiles * nseg, C::NT, smem2, stream>>>(A, lps, l0, l1);
+          return;
+        }
     k_apply_tile<p, T, MODE><<<ntiles * nseg, C::NT, smem, stream>>>(A, lps, l0, l1);
   }
 
@@ -543,3 +572,5 @@ namespace mgb
       }
   }
 } // namespace mgb
+
+#include "cartesian_kernel_f32x2.cuh"

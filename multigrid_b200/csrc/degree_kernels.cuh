@@ -23,6 +23,7 @@ namespace mgb
   struct ConstTables
   {
     double S[n * n], D[n * n], G[n * n], M1[n * n], K1[n * n], w[n], xq[n], nodes[n];
+    float2 MKf[n * n]; // (M1f, K1f) entry by entry, for the packed fp32 kernel
     float  Sf[n * n], Df[n * n], M1f[n * n], K1f[n * n], wf[n];
     double P1[(2 * n - 1) * n];
     float  P1f[(2 * n - 1) * n];
@@ -620,6 +621,7 @@ namespace mgb
         h->Df[i]  = (float)b.D[i];
         h->M1f[i] = (float)b.M1[i];
         h->K1f[i] = (float)b.K1[i];
+        h->MKf[i] = make_float2((float)b.M1[i], (float)b.K1[i]);
       }
     for (int i = 0; i < n; ++i)
       {
