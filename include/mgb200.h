@@ -275,6 +275,41 @@ int mgb_dg_solver_solve_cg_host(mgb_dg_solver h, double tolerance, double *solut
                                 double *reduction_rate, unsigned int *n_iterations);
 int64_t mgb_dg_solver_launch_count(mgb_dg_solver h);      /* kernels of the DG part + the FE_Q hierarchy */
 
+/* ---- Adaptive meshes with hanging nodes (poisson_l/program.cc:232-260,465-541)
+ * FE_Q(p) Laplacian on a forest of n_roots[0] x n_roots[1] x n_roots[2] root cells filling [lower, upper]
+ * (root_mask[z][y][x] != 0 keeps a root cell; NULL keeps all: GridGenerator::hyper_L is a 2x2x2 grid with one
+ * root removed), refined globally and then cell by cell; the mesh is kept 2:1 balanced over faces, edges and
+ * corners (p4est).  Hanging-node constraints (AffineConstraints of DoFTools::make_hanging_node_constraints, with
+ * chains resolved) and the homogeneous Dirichlet condition on the whole boundary are applied inside the kernel
+ * while it gathers and scatters; constrained rows are identity rows (laplace_operator.h:592-593).
+ * The vector holds the unconstrained and the Dirichlet DoFs; hanging-node values are not stored.
+ * Mesh and numbering are host data (no GPU needed for create / refine / n_dofs / info / tables); vmult and
+ * inverse_diagonal are kernels and fail without a device.                                                   */
+typedef struct mgb_adaptive_t *mgb_adaptive;
+int mgb_adaptive_create(int degree, const int n_roots[3], const unsigned char *root_mask, const double lower[3],
+                        const double upper[3], int n_global_refinements, int device, mgb_adaptive *out);
+int mgb_adaptive_destroy(mgb_adaptive h);
+int64_t mgb_adaptive_n_cells(mgb_adaptive h);
+/* active cells in the library's order: level[n_cells], position[n_cells][3] in units of cells of that level */
+int mgb_adaptive_cells(mgb_adaptive h, int *level, int *position);
+/* Triangulation::execute_coarsening_and_refinement with refine flags (poisson_l/program.cc:508-541): flags[n_cells] */
+int mgb_adaptive_refine(mgb_adaptive h, const unsigned char *flags);
+int64_t mgb_adaptive_n_dofs(mgb_adaptive h);
+/* info = {n_dofs, n_dirichlet, hanging local nodes, constraint rows, constraint entries, finest level} */
+int mgb_adaptive_info(mgb_adaptive h, int64_t info[6]);
+int mgb_adaptive_dof_points(mgb_adaptive h, double *xyz /* [n_dofs][3] */);
+int mgb_adaptive_dirichlet(mgb_adaptive h, unsigned char *mask /* [n_dofs] */);
+/* host copies of the tables the kernel reads: cell_index[n_cells][(p+1)^3] (>= 0 DoF, -1 zero, <= -2 row -2-e),
+ * row_start[rows+1], row_dof / row_w[entries]; any pointer may be NULL                                          */
+int mgb_adaptive_tables(mgb_adaptive h, int32_t *cell_index, int32_t *row_start, int32_t *row_dof, double *row_w);
+/* LaplaceOperator::vmult on the active mesh                                          laplace_operator.h:575-601 */
+int mgb_adaptive_vmult(mgb_adaptive h, int precision, void *dst, const void *src);
+/* compute_diagonal + inverse, exact (cell operator applied to every constraint column)   :747-800 */
+int mgb_adaptive_inverse_diagonal(mgb_adaptive h, int precision, void *inv_diag);
+int mgb_adaptive_vmult_host(mgb_adaptive h, int precision, void *dst_host, const void *src_host);
+int mgb_adaptive_sync(mgb_adaptive h);
+int64_t mgb_adaptive_launch_count(mgb_adaptive h);
+
 /* The subset of LinearAlgebra::distributed::Vector<Number> the drivers use (poisson_cube/program.cc:262-380,
  * multigrid_solver.h:54-67): device vectors of one level in the precision given; sums run over the owned
  * entries of all ranks.  dot: a . b (l2_norm = sqrt(dot(v,v)));  sadd: y = sy y + ax x;  set: y = value;

@@ -176,6 +176,22 @@ SYMBOLS = {
     "mgb_dg_solver_sync": (_i, [_vp]),
     "mgb_dg_solver_solve_cg_host": (_i, [_vp, _d, _vp, _dp, _dp, C.POINTER(_u)]),
     "mgb_dg_solver_launch_count": (C.c_int64, [_vp]),
+    # adaptive meshes with hanging nodes
+    "mgb_adaptive_create": (_i, [_i, _ip, C.POINTER(C.c_ubyte), _dp, _dp, _i, _i, C.POINTER(_vp)]),
+    "mgb_adaptive_destroy": (_i, [_vp]),
+    "mgb_adaptive_n_cells": (C.c_int64, [_vp]),
+    "mgb_adaptive_cells": (_i, [_vp, _ip, _ip]),
+    "mgb_adaptive_refine": (_i, [_vp, C.POINTER(C.c_ubyte)]),
+    "mgb_adaptive_n_dofs": (C.c_int64, [_vp]),
+    "mgb_adaptive_info": (_i, [_vp, C.POINTER(C.c_int64)]),
+    "mgb_adaptive_dof_points": (_i, [_vp, _dp]),
+    "mgb_adaptive_dirichlet": (_i, [_vp, C.POINTER(C.c_ubyte)]),
+    "mgb_adaptive_tables": (_i, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), _dp]),
+    "mgb_adaptive_vmult": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_adaptive_inverse_diagonal": (_i, [_vp, _i, _vp]),
+    "mgb_adaptive_vmult_host": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_adaptive_sync": (_i, [_vp]),
+    "mgb_adaptive_launch_count": (C.c_int64, [_vp]),
     # host-only helpers
     "mgb_host_basis": (_i, [_i] + [_dp] * 9),
     "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), _ip, C.POINTER(C.c_int64),
@@ -862,3 +878,112 @@ class MultigridSolverDG:
 
     def launch_count(self):
         return lib().mgb_dg_solver_launch_count(self.h)
+
+
+class LaplaceOperatorAdaptive:
+    """FE_Q(p) Laplacian on an adaptively refined box forest with hanging nodes (the operator of
+    poisson_l/program.cc:232-260 on the meshes of :465-541).  Mesh and numbering live on the host; vmult and the
+    diagonal are kernels.  `root_mask[z][y][x]` selects root cells (hyper_L: 2x2x2 with one root removed)."""
+
+    def __init__(self, degree, n_roots=(1, 1, 1), root_mask=None, lower=(-1.,) * 3, upper=(1.,) * 3, n_global_refinements=0,
+                 device=0):
+        nr = (C.c_int * 3)(*n_roots)
+        lo = (C.c_double * 3)(*lower)
+        hi = (C.c_double * 3)(*upper)
+        mask = None
+        if root_mask is not None:
+            m = np.ascontiguousarray(root_mask, dtype=np.uint8).ravel()
+            assert m.size == n_roots[0] * n_roots[1] * n_roots[2]
+            mask = m.ctypes.data_as(C.POINTER(C.c_ubyte))
+        self.h = C.c_void_p()
+        self.degree, self.device_index = degree, device
+        self.lower, self.upper, self.n_roots = tuple(lower), tuple(upper), tuple(n_roots)
+        _check(lib().mgb_adaptive_create(degree, nr, mask, lo, hi, n_global_refinements, device, C.byref(self.h)))
+
+    def close(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.mgb_adaptive_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def n_cells(self):
+        return lib().mgb_adaptive_n_cells(self.h)
+
+    def cells(self):
+        """(level[n_cells], position[n_cells, 3]) of the active cells, in the library's order"""
+        n = self.n_cells()
+        level = np.zeros(n, dtype=np.int32)
+        pos = np.zeros((n, 3), dtype=np.int32)
+        _check(lib().mgb_adaptive_cells(self.h, level.ctypes.data_as(_ip), pos.ctypes.data_as(_ip)))
+        return level, pos
+
+    def cell_boxes(self):
+        """lower corner and size of every active cell, shape (n_cells, 3) each"""
+        level, pos = self.cells()
+        H = (np.array(self.upper) - np.array(self.lower)) / np.array(self.n_roots)
+        size = H[None, :] / (2.0 ** level)[:, None]
+        return np.array(self.lower)[None, :] + pos * size, size
+
+    def refine(self, flags):
+        f = np.ascontiguousarray(flags, dtype=np.uint8)
+        assert f.size == self.n_cells()
+        _check(lib().mgb_adaptive_refine(self.h, f.ctypes.data_as(C.POINTER(C.c_ubyte))))
+
+    def m(self):
+        n = lib().mgb_adaptive_n_dofs(self.h)
+        if n < 0:
+            raise MgbError(lib().mgb_last_error().decode())
+        return n
+
+    n_dofs = m
+
+    def info(self):
+        v = (C.c_int64 * 6)()
+        _check(lib().mgb_adaptive_info(self.h, v))
+        return dict(n_dofs=v[0], n_dirichlet=v[1], hanging_local_nodes=v[2], constraint_rows=v[3],
+                    constraint_entries=v[4], max_level=v[5])
+
+    def dof_points(self):
+        out = np.zeros((self.m(), 3))
+        _check(lib().mgb_adaptive_dof_points(self.h, out.ctypes.data_as(_dp)))
+        return out
+
+    def dirichlet_mask(self):
+        out = np.zeros(self.m(), dtype=np.uint8)
+        _check(lib().mgb_adaptive_dirichlet(self.h, out.ctypes.data_as(C.POINTER(C.c_ubyte))))
+        return out.astype(bool)
+
+    def tables(self):
+        inf = self.info()
+        n3 = (self.degree + 1) ** 3
+        ci = np.zeros((self.n_cells(), n3), dtype=np.int32)
+        rs = np.zeros(inf["constraint_rows"] + 1, dtype=np.int32)
+        rd = np.zeros(max(inf["constraint_entries"], 1), dtype=np.int32)
+        rw = np.zeros(max(inf["constraint_entries"], 1))
+        i32 = C.POINTER(C.c_int32)
+        _check(lib().mgb_adaptive_tables(self.h, ci.ctypes.data_as(i32), rs.ctypes.data_as(i32), rd.ctypes.data_as(i32),
+                                         rw.ctypes.data_as(_dp)))
+        return ci, rs, rd[:inf["constraint_entries"]], rw[:inf["constraint_entries"]]
+
+    def sync(self):
+        _check(lib().mgb_adaptive_sync(self.h))
+
+    def vmult(self, dst, src, precision=F64):
+        import torch
+        torch.cuda.synchronize()
+        _check(lib().mgb_adaptive_vmult(self.h, precision, _ptr(dst), _ptr(src)))
+        self.sync()
+
+    def get_matrix_diagonal_inverse(self, out, precision=F64):
+        import torch
+        torch.cuda.synchronize()
+        _check(lib().mgb_adaptive_inverse_diagonal(self.h, precision, _ptr(out)))
+        self.sync()
+
+    def vmult_host(self, dst_host, src_host, precision=F64):
+        _check(lib().mgb_adaptive_vmult_host(self.h, precision, C.c_void_p(dst_host.ctypes.data),
+                                             C.c_void_p(src_host.ctypes.data)))
+
+    def launch_count(self):
+        return lib().mgb_adaptive_launch_count(self.h)
