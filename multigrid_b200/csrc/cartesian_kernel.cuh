@@ -140,6 +140,8 @@ namespace mgb
 
   // internal mode of the kernel: the first Chebyshev iteration (x_{k-1} = 0 implied) is its own instance
   constexpr int APPLY_CHEBYSHEV_FIRST = 4;
+  // dst = A src together with the sum of src[i] dst[i] (first sum of vmult_with_cg_update, laplace_operator.h:698)
+  constexpr int APPLY_SET_DOT = 5;
 
   // Operands of the fused vector operation (the post-range operation of laplace_operator.h:607-741) on
   // COUNT planes of one point column: loaded early (load_operands, before the y-stage) so that their
@@ -170,9 +172,9 @@ namespace mgb
           o.os[r] = dst[d];
         else
           {
-            if (CHEB || (BND && ((con >> r) & 1u)))
+            if (CHEB || MODE == APPLY_SET_DOT || (BND && ((con >> r) & 1u)))
               o.xs[r] = src[d];
-            if (MODE != APPLY_SET)
+            if (MODE != APPLY_SET && MODE != APPLY_SET_DOT)
               o.rs[r] = rhs[d];
             if (CHEB)
               o.ds[r] = inv[d];
@@ -183,10 +185,11 @@ namespace mgb
   }
 
   template <int p, typename T, int MODE, int COUNT, bool BND>
-  __device__ __forceinline__ void
+  __device__ __forceinline__ double
   store_planes(const ApplyArgs<T> &A, const Operands<T, COUNT> &o, const T (&y)[p + 1], const uint32_t d0,
                const uint32_t stride, const unsigned int con)
   {
+    double dot = 0;
     T *__restrict__ dst = A.dst;
     const T f1 = A.f1, f2 = A.f2, f1p = T(1) + A.f1;
 #pragma unroll
@@ -205,6 +208,11 @@ namespace mgb
           v = o.xs[r]; // identity rows (laplace_operator.h:592-593, :632-633)
         if (MODE == APPLY_SET)
           dst[d] = v;
+        else if (MODE == APPLY_SET_DOT)
+          {
+            dst[d] = v;
+            dot += (double)o.xs[r] * (double)v;
+          }
         else if (MODE == APPLY_RESIDUAL)
           dst[d] = o.rs[r] - v;
         else
@@ -215,6 +223,7 @@ namespace mgb
             dst[d] = t;
           }
       }
+    return dot;
   }
 
   // asynchronous copy with an immediate shared-memory offset (bytes)
@@ -333,6 +342,7 @@ namespace mgb
 
     T Pz[n], Qz[n]; // P, Q of this thread's column on the planes of the current cell layer
     T carry = 0;
+    double dot_acc = 0; // APPLY_SET_DOT
 
     const uint32_t u_base = (uint32_t)__cvta_generic_to_shared(u_s + tid);
 
@@ -480,9 +490,9 @@ namespace mgb
             if (c >= c0)
               {
                 if (bnd)
-                  store_planes<p, T, MODE, p, true>(A, ops, y, d_layer, own_stride, con);
+                  dot_acc += store_planes<p, T, MODE, p, true>(A, ops, y, d_layer, own_stride, con);
                 else
-                  store_planes<p, T, MODE, p, false>(A, ops, y, d_layer, own_stride, 0u);
+                  dot_acc += store_planes<p, T, MODE, p, false>(A, ops, y, d_layer, own_stride, 0u);
                 d_layer += p * own_stride;
               }
           }
@@ -496,7 +506,25 @@ namespace mgb
         const unsigned int con = (xy_constrained || (L.dirichlet & 32u)) ? 1u : 0u;
         Operands<T, 1>     ops;
         load_operands<p, T, MODE, 1, true>(A, ops, d_layer, own_stride, con);
-        store_planes<p, T, MODE, 1, true>(A, ops, y, d_layer, own_stride, con);
+        dot_acc += store_planes<p, T, MODE, 1, true>(A, ops, y, d_layer, own_stride, con);
+      }
+    if (MODE == APPLY_SET_DOT)
+      {
+        // block sum of the per-thread partial sums: warp shuffles, one atomic per block
+        __syncthreads(); // every warp is done with the stages: the staging memory is free
+        double *red = reinterpret_cast<double *>(smem_raw);
+        for (int o = 16; o > 0; o >>= 1)
+          dot_acc += __shfl_down_sync(0xffffffffu, dot_acc, o);
+        if ((tid & 31) == 0)
+          red[tid >> 5] = dot_acc;
+        __syncthreads();
+        if (tid == 0)
+          {
+            double t = 0;
+            for (int w = 0; w < NT / 32; ++w)
+              t += red[w];
+            atomicAdd(A.dot_out, t);
+          }
       }
   }
 
@@ -561,7 +589,15 @@ namespace mgb
     switch (A.mode)
       {
         case APPLY_ADD: launch_apply_tile<p, T, APPLY_ADD>(A, stream); break;
-        case APPLY_SET: launch_apply_tile<p, T, APPLY_SET>(A, stream); break;
+        case APPLY_SET:
+          if constexpr (sizeof(T) == 8)
+            if (A.dot_out != nullptr)
+              {
+                launch_apply_tile<p, T, APPLY_SET_DOT>(A, stream);
+                break;
+              }
+          launch_apply_tile<p, T, APPLY_SET>(A, stream);
+          break;
         case APPLY_RESIDUAL: launch_apply_tile<p, T, APPLY_RESIDUAL>(A, stream); break;
         default:
           if (A.first_chebyshev)

@@ -1039,6 +1039,7 @@ namespace mgb
       A.read_plain      = 0;
       A.first_chebyshev = 0;
       A.layer_begin = A.layer_end = -1;
+      A.dot_out     = nullptr;
     }
 
     int
@@ -1071,10 +1072,12 @@ namespace mgb
     // the one entry point behind vmult / vmult_add / vmult_residual / Chebyshev step
     void
     apply(const int mode, T *dst, const T *src, const T *rhs = nullptr, const T *inv_diag = nullptr,
-          const T f1 = 0, const T f2 = 0, const bool first = false, const bool read_plain = false)
+          const T f1 = 0, const T f2 = 0, const bool first = false, const bool read_plain = false,
+          double *dot_out = nullptr)
     {
       ApplyArgs<T> A;
       fill_args(A, src, dst);
+      A.dot_out         = dot_out;
       A.mode            = mode;
       A.rhs             = rhs;
       A.inv_diag        = inv_diag;
@@ -1161,10 +1164,24 @@ namespace mgb
     void
     vmult_dot(T *dst, const T *src, double *result)
     {
+      if (sizeof(T) == 8 && use_cartesian() && fuse_dot)
+        {
+          // the tile kernel adds src[i] dst[i] of the points it stores (exactly the owned ones) to a device scalar
+          MGB_CUDA_CHECK(cudaMemsetAsync(ctx->scal_dev, 0, sizeof(double), ctx->stream));
+          apply(APPLY_SET, dst, src, nullptr, nullptr, 0, 0, false, false, ctx->scal_dev);
+          if (level->owned().all_ranks)
+            ctx->all_reduce_sum(ctx->scal_dev, 1);
+          MGB_CUDA_CHECK(cudaMemcpyAsync(ctx->scal_host, ctx->scal_dev, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+          ctx->sync();
+          ctx->check_p2p_error();
+          *result = ctx->scal_host[0];
+          return;
+        }
       apply(APPLY_SET, dst, src);
       ScopedRange range(*ctx, level->index, RK_CG_VEC);
       *result = dot(*ctx, src, dst, level->owned());
     }
+    bool fuse_dot = getenv("MGB200_FUSE_DOT") == nullptr || getenv("MGB200_FUSE_DOT")[0] != '0'; // A/B switch
     void vmult_add(T *dst, const T *src) { apply(APPLY_ADD, dst, src); }
     void vmult_residual(const T *rhs, const T *lhs, T *residual) { apply(APPLY_RESIDUAL, residual, lhs, rhs); }
 
