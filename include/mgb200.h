@@ -185,6 +185,10 @@ typedef struct mgb_dg_options {
   double lower[3], upper[3]; /* box before the vertex map    (:55-60)                               */
   double trafo[9];        /* row-major constant matrix applied to the vertices (:66-76)             */
   int device;
+  /* one process per GPU (the reference's MPI ranks): z-slabs of whole cell layers, the number of layers must be
+   * a multiple of comm_size; comm_id from mgb_comm_unique_id() of rank 0.  comm_size <= 1: one GPU             */
+  int comm_rank, comm_size;
+  unsigned char comm_id[128];
 } mgb_dg_options;
 
 void mgb_dg_default_options(mgb_dg_options *opt);        /* the mesh of matvec_dg/program.cc, degree 4 */
@@ -194,6 +198,11 @@ int mgb_dg_destroy(mgb_dg h);
 int mgb_dg_sync(mgb_dg h);
 int64_t mgb_dg_n_dofs(mgb_dg h);                                   /* m()                        :795-799 */
 int mgb_dg_n_cells(mgb_dg h, int ncell[3]);
+/* z-slab of this rank: info = {DoFs of the whole mesh, local vector length (owned + ghost cell layers), offset of
+ * the owned range, owned DoFs, first owned cell layer, owned cell layers}.  Vectors passed to mgb_dg_* have the
+ * local length; their ghost layers are refreshed by the library (the MPI face exchange of :981-1058)           */
+int mgb_dg_partition(mgb_dg h, int64_t info[6]);
+int64_t mgb_dg_exchange_count(mgb_dg h);
 int mgb_dg_penalty(mgb_dg h, double sigma[3]);                     /* get_penalty, per face direction :789-793 */
 /* vectors are device pointers of the chosen precision (MGB_F32 / MGB_F64) */
 int mgb_dg_vmult(mgb_dg h, int precision, void *dst, const void *src);                       /* :827-841 */

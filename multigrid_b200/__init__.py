@@ -59,6 +59,9 @@ class DGOptions(C.Structure):
         ("upper", C.c_double * 3),
         ("trafo", C.c_double * 9),
         ("device", C.c_int),
+        ("comm_rank", C.c_int),
+        ("comm_size", C.c_int),
+        ("comm_id", C.c_ubyte * 128),
     ]
 
 
@@ -145,6 +148,8 @@ SYMBOLS = {
     "mgb_dg_n_dofs": (C.c_int64, [_vp]),
     "mgb_dg_n_cells": (_i, [_vp, _ip]),
     "mgb_dg_penalty": (_i, [_vp, _dp]),
+    "mgb_dg_partition": (_i, [_vp, C.POINTER(C.c_int64)]),
+    "mgb_dg_exchange_count": (C.c_int64, [_vp]),
     "mgb_dg_vmult": (_i, [_vp, _i, _vp, _vp]),
     "mgb_dg_vmult_residual": (_i, [_vp, _i, _vp, _vp, _vp]),
     "mgb_dg_vmult_with_cg_update": (_i, [_vp, _i, _d, _d, _vp, _vp, _vp, _vp, _dp]),
@@ -612,10 +617,14 @@ class LaplaceOperatorDG:
     device, cell-wise contiguous; `precision` picks the float or the double kernels."""
 
     def __init__(self, degree=4, n_subdivisions=(1, 1, 1), n_refinements=0, lower=None, upper=None, trafo=None,
-                 device=0, precision=F64):
+                 device=0, precision=F64, comm=None):
+        """comm = (rank, size, unique_id bytes) for one process per GPU (comm_from_torch_distributed())"""
         import torch
         o = DGOptions()
         lib().mgb_dg_default_options(C.byref(o))
+        if comm is not None and comm[1] > 1:
+            o.comm_rank, o.comm_size = comm[0], comm[1]
+            o.comm_id[:] = list(comm[2])
         o.degree = degree
         if isinstance(n_subdivisions, int):
             n_subdivisions = (n_subdivisions,) * 3
@@ -658,6 +667,15 @@ class LaplaceOperatorDG:
         nc = (C.c_int * 3)()
         _check(lib().mgb_dg_n_cells(self.h, nc))
         return tuple(nc)
+
+    def partition(self):
+        """z-slab of this rank: vectors have `n_local` entries, of which [owned_offset, owned_offset + n_owned) are owned"""
+        v = (C.c_int64 * 6)()
+        _check(lib().mgb_dg_partition(self.h, v))
+        return dict(n_global=v[0], n_local=v[1], owned_offset=v[2], n_owned=v[3], first_layer=v[4], n_layers=v[5])
+
+    def exchange_count(self):
+        return lib().mgb_dg_exchange_count(self.h)
 
     def get_penalty(self):
         s = (C.c_double * 3)()

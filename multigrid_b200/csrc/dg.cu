@@ -20,6 +20,12 @@
 struct mgb_solver_t;
 const mgb::LevelDesc *mgb_internal_level_desc(mgb_solver_t *s, int level);
 cudaStream_t          mgb_internal_stream(mgb_solver_t *s);
+struct mgb_comm_t;
+mgb_comm_t *mgb_internal_comm_create(int rank, int size, const unsigned char id[128], int device);
+void        mgb_internal_comm_destroy(mgb_comm_t *c);
+void        mgb_internal_comm_exchange(mgb_comm_t *c, cudaStream_t stream, const void *send_up, void *recv_dn, const void *send_dn,
+                                       void *recv_up, size_t count, int is_double);
+void        mgb_internal_comm_allreduce(mgb_comm_t *c, cudaStream_t stream, double *dev, int count);
 
 namespace mgb
 {
@@ -191,17 +197,17 @@ namespace mgb
   // a(phi_i, phi_i): cell term + the faces on which phi_i does not vanish (see dg_kernels.cuh header)
   template <typename T>
   __global__ void
-  k_dg_inverse_diagonal(const int n, const int nc0, const int nc1, const int nc2, const DGGeom g, const DGDiagTables tb,
-                        T *__restrict__ out)
+  k_dg_inverse_diagonal(const int n, const int nc0, const int nc1, const int nc2, const int local_layers, const int cz_shift,
+                        const DGGeom g, const DGDiagTables tb, T *__restrict__ out)
   {
     const size_t n3    = (size_t)n * n * n;
-    const size_t total = (size_t)nc0 * nc1 * nc2 * n3;
+    const size_t total = (size_t)nc0 * nc1 * local_layers * n3;
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x)
       {
         const size_t c = idx / n3;
         const int    l = (int)(idx - c * n3);
         const int    i[3]  = {l % n, (l / n) % n, l / (n * n)};
-        const int    cc[3] = {(int)(c % nc0), (int)((c / nc0) % nc1), (int)(c / ((size_t)nc0 * nc1))};
+        const int    cc[3] = {(int)(c % nc0), (int)((c / nc0) % nc1), (int)(c / ((size_t)nc0 * nc1)) + cz_shift};
         const int    ncs[3] = {nc0, nc1, nc2};
         const double M0 = tb.M[i[0]], M1 = tb.M[i[1]], M2 = tb.M[i[2]];
         const double C0 = tb.C[i[0]], C1 = tb.C[i[1]], C2 = tb.C[i[2]];
@@ -237,13 +243,13 @@ namespace mgb
   // sum_i f(i, acc) for NS sums (warp shuffles, one atomic per block and sum)
   template <int NS, typename F>
   __global__ void
-  k_dg_reduce(const size_t n, F f, double *out)
+  k_dg_reduce(const size_t off, const size_t n, F f, double *out)
   {
     double acc[NS];
     for (int s = 0; s < NS; ++s)
       acc[s] = 0;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-      f(i, acc);
+      f(off + i, acc);
     __shared__ double red[NS][8];
     for (int s = 0; s < NS; ++s)
       {
@@ -266,11 +272,13 @@ namespace mgb
   // four sums of vmult_with_cg_update: q.p, r.r, q.r, q.q (warp shuffles, one atomic per block and sum)
   template <typename T>
   __global__ void
-  k_dg_cg_sums(const size_t n, const T *__restrict__ q, const T *__restrict__ p, const T *__restrict__ r, double *out)
+  k_dg_cg_sums(const size_t off, const size_t n, const T *__restrict__ q, const T *__restrict__ p, const T *__restrict__ r,
+               double *out)
   {
     double acc[4] = {0, 0, 0, 0};
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    for (size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x; j < n; j += (size_t)gridDim.x * blockDim.x)
       {
+        const size_t i  = off + j;
         const double qi = q[i], pi = p[i], ri = r[i];
         acc[0] += qi * pi;
         acc[1] += ri * ri;
@@ -360,7 +368,12 @@ namespace mgb
   {
     mgb_dg_options opt;
     int            p = 0, n = 0, nc[3] = {0, 0, 0};
-    size_t         n_cells = 0, n_dofs = 0;
+    size_t         n_cells = 0, n_dofs = 0; // LOCAL cells / vector length: owned layers + the ghost layers of the z-slab
+    // z-slabs over the GPUs (one process per GPU): this rank owns `lz` of the nc[2] cell layers, starting at layer cz0;
+    // a ghost layer of the rank below (zg) precedes and one of the rank above (ztop) follows them in every vector
+    int         rank = 0, n_ranks = 1, lz = 0, cz0 = 0, zg = 0, ztop = 0;
+    size_t      layer_dofs = 0, owned_off = 0, owned_n = 0, n_dofs_global = 0;
+    mgb_comm_t *comm = nullptr;
     cudaStream_t   stream   = nullptr;
     bool           owns_stream = true;
     cudaEvent_t    ev[2]    = {nullptr, nullptr};
@@ -394,7 +407,22 @@ namespace mgb
           h[d]  = (o.upper[d] - o.lower[d]) / nc[d];
           n_cells *= (size_t)nc[d];
         }
-      n_dofs = n_cells * n * n * n;
+      n_dofs_global = n_cells * n * n * n;
+      n_ranks       = o.comm_size > 1 ? o.comm_size : 1;
+      rank          = n_ranks > 1 ? o.comm_rank : 0;
+      if (rank < 0 || rank >= n_ranks)
+        throw std::runtime_error("invalid communicator rank");
+      if (nc[2] % n_ranks != 0)
+        throw std::runtime_error("the number of cell layers in z must be a multiple of the number of GPUs");
+      lz         = nc[2] / n_ranks;
+      cz0        = rank * lz;
+      zg         = rank > 0 ? 1 : 0;
+      ztop       = rank + 1 < n_ranks ? 1 : 0;
+      layer_dofs = (size_t)nc[0] * nc[1] * n * n * n;
+      n_cells    = (size_t)nc[0] * nc[1] * (lz + zg + ztop);
+      n_dofs     = n_cells * n * n * n;
+      owned_off  = zg * layer_dofs;
+      owned_n    = lz * layer_dofs;
       if (n_cells >= 0xffffffffull)
         throw std::runtime_error("too many cells for one device");
       for (int k = 0; k < 3; ++k)
@@ -454,6 +482,8 @@ namespace mgb
       MGB_DG_CHECK(cudaEventCreate(&ev[1]));
       MGB_DG_CHECK(cudaMalloc(&scal_dev, 4 * sizeof(double)));
       MGB_DG_CHECK(cudaMallocHost(&scal_host, 4 * sizeof(double)));
+      if (n_ranks > 1)
+        comm = mgb_internal_comm_create(rank, n_ranks, o.comm_id, o.device);
     }
 
     ~DGOperator()
@@ -475,7 +505,23 @@ namespace mgb
         cudaFreeHost(scal_host);
       if (stream && owns_stream)
         cudaStreamDestroy(stream);
+      if (comm)
+        mgb_internal_comm_destroy(comm);
     }
+
+    // update_ghost_values (the MPI face exchange of laplace_operator_dg.h:981-1058): the top owned cell layer goes to
+    // the rank above, the bottom one to the rank below, one NCCL group on the operator's stream
+    template <typename T>
+    void
+    update_ghosts(T *v)
+    {
+      if (n_ranks == 1)
+        return;
+      mgb_internal_comm_exchange(comm, stream, v + owned_off + owned_n - layer_dofs, v, v + owned_off, v + owned_off + owned_n,
+                                 layer_dofs, sizeof(T) == 8);
+      ++exchanges;
+    }
+    int64_t exchanges = 0;
 
     unsigned grid(const size_t count) const { return (unsigned)std::min<size_t>((count + 255) / 256, 148 * 16); }
 
@@ -502,8 +548,10 @@ namespace mgb
     {
       static_assert(NS <= 4, "scal_dev holds four sums");
       MGB_DG_CHECK(cudaMemsetAsync(scal_dev, 0, 4 * sizeof(double), stream));
-      k_dg_reduce<NS><<<grid(n_dofs), 256, 0, stream>>>(n_dofs, f, scal_dev);
+      k_dg_reduce<NS><<<grid(owned_n), 256, 0, stream>>>(owned_off, owned_n, f, scal_dev);
       ++launches;
+      if (n_ranks > 1)
+        mgb_internal_comm_allreduce(comm, stream, scal_dev, NS);
       MGB_DG_CHECK(cudaMemcpyAsync(scal_host, scal_dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, stream));
       MGB_DG_CHECK(cudaStreamSynchronize(stream));
       for (int s = 0; s < NS; ++s)
@@ -518,7 +566,8 @@ namespace mgb
       if (!inv_diag[k])
         {
           MGB_DG_CHECK(cudaMalloc(&inv_diag[k], n_dofs * sizeof(T)));
-          k_dg_inverse_diagonal<T><<<grid(n_dofs), 256, 0, stream>>>(n, nc[0], nc[1], nc[2], geom, dtab, (T *)inv_diag[k]);
+          k_dg_inverse_diagonal<T><<<grid(n_dofs), 256, 0, stream>>>(n, nc[0], nc[1], nc[2], lz + zg + ztop, cz0 - zg, geom, dtab,
+                                                                     (T *)inv_diag[k]);
           ++launches;
           MGB_DG_CHECK(cudaGetLastError());
         }
@@ -545,6 +594,8 @@ namespace mgb
           po.upper[d]          = opt.lower[d] + (opt.upper[d] - opt.lower[d]) / nc[d] * ncp[d];
         }
       po.n_refinements = 0;
+      po.comm_rank     = 0;
+      po.comm_size     = 1;
       DGOperator                probe(po);
       const std::vector<double> V = jacobi_transformed_eigenvectors(basis);
       const size_t              np = probe.n_dofs;
@@ -618,6 +669,8 @@ namespace mgb
     void
     check_same_mesh(const LevelDesc &L) const
     {
+      if (n_ranks > 1)
+        throw std::runtime_error("the DG <-> FE_Q transfer runs on one GPU");
       if (L.p != p || L.ncell[0] != nc[0] || L.ncell[1] != nc[1] || L.ncell[2] != nc[2])
         throw std::runtime_error("the FE_Q level and the DG operator must share degree and mesh");
     }
@@ -673,7 +726,9 @@ namespace mgb
           DGArgs<T> A;
           for (int d = 0; d < 3; ++d)
             A.nc[d] = nc[d];
-          A.n_cells = (uint32_t)n_cells;
+          A.n_cells    = (uint32_t)((size_t)nc[0] * nc[1] * lz);
+          A.cell_begin = (uint32_t)((size_t)nc[0] * nc[1] * zg);
+          A.cz_shift   = cz0 - zg;
           A.src     = src;
           A.dst     = dst;
           A.jt_dinv = get_jt_dinv<T>();
@@ -716,7 +771,10 @@ namespace mgb
         }
       for (int e = 0; e < 6; ++e)
         A.gt[e] = (T)geom.gt[e];
-      A.n_cells  = (uint32_t)n_cells;
+      A.n_cells    = (uint32_t)((size_t)nc[0] * nc[1] * lz);
+      A.cell_begin = (uint32_t)((size_t)nc[0] * nc[1] * zg);
+      A.cz_shift   = cz0 - zg;
+      update_ghosts(const_cast<T *>(src));
       A.src      = src;
       A.dst      = dst;
       A.rhs      = rhs;
@@ -756,8 +814,10 @@ namespace mgb
       ++launches;
       apply<T>(DG_SET, q, pp);
       MGB_DG_CHECK(cudaMemsetAsync(scal_dev, 0, 4 * sizeof(double), stream));
-      k_dg_cg_sums<T><<<grid(N), 256, 0, stream>>>(N, q, pp, r, scal_dev);
+      k_dg_cg_sums<T><<<grid(owned_n), 256, 0, stream>>>(owned_off, owned_n, q, pp, r, scal_dev);
       ++launches;
+      if (n_ranks > 1)
+        mgb_internal_comm_allreduce(comm, stream, scal_dev, 4);
       MGB_DG_CHECK(cudaMemcpyAsync(scal_host, scal_dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, stream));
       MGB_DG_CHECK(cudaStreamSynchronize(stream));
       for (int s = 0; s < 4; ++s)
@@ -948,6 +1008,26 @@ extern "C"
     for (int d = 0; d < 3; ++d)
       ncell[d] = DGH(h).nc[d];
     DG_CATCH
+  }
+
+  int
+  mgb_dg_partition(mgb_dg h, int64_t info[6])
+  {
+    DG_TRY
+    const DGOperator &o = DGH(h);
+    info[0]             = (int64_t)o.n_dofs_global;
+    info[1]             = (int64_t)o.n_dofs;
+    info[2]             = (int64_t)o.owned_off;
+    info[3]             = (int64_t)o.owned_n;
+    info[4]             = o.cz0;
+    info[5]             = o.lz;
+    DG_CATCH
+  }
+
+  int64_t
+  mgb_dg_exchange_count(mgb_dg h)
+  {
+    return h && h->impl ? h->impl->exchanges : -1;
   }
 
   int

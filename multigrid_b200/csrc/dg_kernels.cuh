@@ -45,8 +45,10 @@ namespace mgb
   template <typename T>
   struct DGArgs
   {
-    int      nc[3];
-    uint32_t n_cells;
+    int      nc[3];      // cells of the whole mesh (all ranks)
+    uint32_t n_cells;    // cells this launch works on: the local cells cell_begin .. cell_begin + n_cells - 1
+    uint32_t cell_begin; // z-slabs: the owned layers follow a ghost layer of the rank below (0 on one GPU)
+    int      cz_shift;   // z-position of the first LOCAL cell layer in the whole mesh
     const T *src;
     T       *dst;
     const T *rhs;
@@ -209,11 +211,11 @@ namespace mgb
     __shared__ T buf[C::CPB * 3 * n3];
     const int    slot = threadIdx.x / TPC, t = threadIdx.x % TPC;
     T           *r = buf + slot * 3 * n3, *a0 = r + n3, *a1 = a0 + n3;
-    const uint32_t cell   = blockIdx.x * C::CPB + slot;
-    const bool     valid  = cell < A.n_cells;
+    const uint32_t cell   = A.cell_begin + blockIdx.x * C::CPB + slot;
+    const bool     valid  = cell < A.cell_begin + A.n_cells;
     const bool     active = valid && t < n2;
     const uint32_t c  = valid ? cell : 0;
-    const int      cx = c % A.nc[0], cy = (c / A.nc[0]) % A.nc[1], cz = c / (A.nc[0] * A.nc[1]);
+    const int      cx = c % A.nc[0], cy = (c / A.nc[0]) % A.nc[1], cz = c / (A.nc[0] * A.nc[1]) + A.cz_shift;
     if (valid)
       for (int i = t; i < n3; i += TPC)
         r[i] = A.src[(size_t)c * n3 + i];
@@ -254,12 +256,12 @@ namespace mgb
     T        *F    = w2 + n3; // 6 face arrays: [side][j, ds, ts]  (later R1, R2)
     T        *H    = F + 6 * n2; // 8 face arrays: [side][Sj, Sds, Sts, Gts]  (later A1, A2, A3)
 
-    const uint32_t cell   = blockIdx.x * C::CPB + slot;
-    const bool     valid  = cell < A.n_cells;
+    const uint32_t cell   = A.cell_begin + blockIdx.x * C::CPB + slot;
+    const bool     valid  = cell < A.cell_begin + A.n_cells;
     const bool     active = valid && t < n2;
     const int      a = t % n, b = t / n;
     const uint32_t c  = valid ? cell : 0;
-    const int      cx = c % A.nc[0], cy = (c / A.nc[0]) % A.nc[1], cz = c / (A.nc[0] * A.nc[1]);
+    const int      cx = c % A.nc[0], cy = (c / A.nc[0]) % A.nc[1], cz = c / (A.nc[0] * A.nc[1]) + A.cz_shift;
     const T *__restrict__ src = A.src;
 
     // ---- own values

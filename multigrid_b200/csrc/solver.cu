@@ -2092,6 +2092,75 @@ struct mgb_solver_t
   MultigridSolver *impl;
 };
 
+// one-process-per-GPU communicator for the other translation units (the DG operator's cell-layer exchange): the
+// same dlopen'ed NCCL as the solver; not part of the public C ABI
+struct mgb_comm_t
+{
+  ncclComm_t comm = nullptr;
+  int        rank = 0, size = 1;
+};
+
+mgb_comm_t *
+mgb_internal_comm_create(const int rank, const int size, const unsigned char id[128], const int device)
+{
+  if (size < 1 || rank < 0 || rank >= size)
+    throw std::runtime_error("invalid communicator rank / size");
+  mgb_comm_t *c = new mgb_comm_t;
+  c->rank       = rank;
+  c->size       = size;
+  if (size > 1)
+    {
+      Nccl &n = Nccl::get();
+      static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+      ncclUniqueId uid;
+      std::memcpy(&uid, id, sizeof(uid));
+      MGB_CUDA_CHECK(cudaSetDevice(device));
+      n.check(n.CommInitRank(&c->comm, size, uid, rank), "ncclCommInitRank");
+    }
+  return c;
+}
+
+void
+mgb_internal_comm_destroy(mgb_comm_t *c)
+{
+  if (c && c->comm)
+    Nccl::get().CommDestroy(c->comm);
+  delete c;
+}
+
+// update_ghost_values of a z-slab vector: `count` values go up to rank + 1 (its recv_dn) and down to rank - 1
+// (its recv_up) in one NCCL group
+void
+mgb_internal_comm_exchange(mgb_comm_t *c, cudaStream_t stream, const void *send_up, void *recv_dn, const void *send_dn,
+                           void *recv_up, const size_t count, const int is_double)
+{
+  if (c->size == 1)
+    return;
+  Nccl                &n  = Nccl::get();
+  const ncclDataType_t dt = is_double ? ncclDouble : ncclFloat;
+  n.check(n.GroupStart(), "ncclGroupStart");
+  if (c->rank + 1 < c->size)
+    {
+      n.check(n.Send(send_up, count, dt, c->rank + 1, c->comm, stream), "ncclSend");
+      n.check(n.Recv(recv_up, count, dt, c->rank + 1, c->comm, stream), "ncclRecv");
+    }
+  if (c->rank > 0)
+    {
+      n.check(n.Send(send_dn, count, dt, c->rank - 1, c->comm, stream), "ncclSend");
+      n.check(n.Recv(recv_dn, count, dt, c->rank - 1, c->comm, stream), "ncclRecv");
+    }
+  n.check(n.GroupEnd(), "ncclGroupEnd");
+}
+
+void
+mgb_internal_comm_allreduce(mgb_comm_t *c, cudaStream_t stream, double *dev, const int count)
+{
+  if (c->size == 1)
+    return;
+  Nccl &n = Nccl::get();
+  n.check(n.AllReduce(dev, dev, count, ncclDouble, ncclSum, c->comm, stream), "ncclAllReduce");
+}
+
 #define MGB_TRY try {
 #define MGB_CATCH                                  \
   }                                                \
