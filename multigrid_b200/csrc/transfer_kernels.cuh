@@ -123,19 +123,57 @@ namespace mgb
 
     T W[n]; // x/y-interpolated coarse planes of the current parent layer at this thread's point
 
-    // interpolates the coarse planes k_first .. k_first + np - 1 in x and y; thread (I,J) gets W[w0 + b]
-    auto planes_2d = [&](const int k_first, const int np, const int w0) {
-      for (int b = 0; b < np; ++b)
+    // coarse planes k_first .. k_first + np - 1 under the tile -> registers (requested one parent layer ahead)
+    T    creg[p][NLC];
+    auto load_coarse = [&](const int k_first, const int np) {
+#pragma unroll
+      for (int b = 0; b < p; ++b)
         {
           const int  gk  = k_first + b;
-          const bool okz = gk >= k_lo && gk <= k_hi;
+          const bool okz = b < np && gk >= k_lo && gk <= k_hi;
+#pragma unroll
+          for (int l = 0; l < NLC; ++l)
+            creg[b][l] = (c_ok[l] && okz) ? __ldg(src + c_off[l] + (uint32_t)gk * (uint32_t)c_stride[l]) : T(0);
+        }
+    };
+    // full tiles of a whole number of parent cells (see k_restrict_tile): a line is interpolated parent cell by
+    // parent cell from registers
+    constexpr bool ALIGNED = TW % (2 * p) == 0;
+    constexpr int  NPC     = ALIGNED ? TW / (2 * p) : 1;
+    constexpr int  NCF     = p * NPC + 1;
+    const bool     fast    = ALIGNED && wx == TW && wy == TW;
+
+    // interpolates the np coarse planes held in creg in x and y; thread (I,J) gets W[w0 + b]
+    auto planes_2d = [&](const int np, const int w0) {
+#pragma unroll
+      for (int b = 0; b < p; ++b)
+        if (b < np)
 #pragma unroll
           for (int l = 0; l < NLC; ++l)
             if (tid + l * NT < NC * NC)
-              c_s[b * NC * NC + tid + l * NT] =
-                (c_ok[l] && okz) ? __ldg(src + c_off[l] + (uint32_t)gk * (uint32_t)c_stride[l]) : T(0);
-        }
+              c_s[b * NC * NC + tid + l * NT] = creg[b][l];
       __syncthreads();
+      if (fast)
+        for (int t = tid; t < np * NCF; t += NT)
+          {
+            const int cj = t % NCF, b = t / NCF;
+            T         cv[NCF];
+#pragma unroll
+            for (int ci = 0; ci < NCF; ++ci)
+              cv[ci] = c_s[(b * NC + cj) * NC + ci];
+#pragma unroll
+            for (int c = 0; c < NPC; ++c)
+#pragma unroll
+              for (int r = 0; r < 2 * p; ++r)
+                {
+                  T v = 0;
+#pragma unroll
+                  for (int i = 0; i < n; ++i)
+                    v += p1_table<T>()[r * n + i] * cv[p * c + i];
+                  t_s[(b * NC + cj) * TW + 2 * p * c + r] = v;
+                }
+          }
+      else
       for (int t = tid; t < TW * NC * np; t += NT)
         {
           const int fi = t % TW, rest = t / TW;
@@ -165,10 +203,14 @@ namespace mgb
           }
     };
 
-    planes_2d(p * cz0, 1, 0);
+    load_coarse(p * cz0, 1);
+    planes_2d(1, 0);
+    load_coarse(p * cz0 + 1, p);
     for (int cz = cz0; cz < cz1; ++cz)
       {
-        planes_2d(p * cz + 1, p, 1);
+        planes_2d(p, 1);
+        if (cz + 1 < cz1)
+          load_coarse(p * (cz + 1) + 1, p);
         if (owner)
           {
             const int nr = (cz == A.cz_end - 1 && A.close_top) ? 2 * p + 1 : 2 * p; // the top plane belongs to the last layer
@@ -207,7 +249,7 @@ namespace mgb
     constexpr int NT = C::NT;
     constexpr int NC = C::NC;
     __shared__ T Wx[NC * TW], Wy[NC * TW]; // Wx[ci][fi] = weight of fine column fi in coarse node ci
-    __shared__ T z_s[p * TW * TW];         // [plane][fj][fi]
+    __shared__ __align__(16) T z_s[p * TW * TW]; // [plane][fj][fi]
     __shared__ T x_s[p * TW * NC];         // [plane][fj][ci]
 
     const LevelDesc &Lf = A.fine, &Lc = A.coarse;
@@ -259,9 +301,61 @@ namespace mgb
     const uint32_t own_off    = tile_base(Lf, tx, ty) + (uint32_t)(J * wx + I);
     const uint32_t own_stride = plane_pitch(Lf);
 
+    // Full tiles whose width is a whole number of parent cells (all but the ragged last tile row / column, and only
+    // degrees with TW % 2p == 0): every line of the tile restricts parent cell by parent cell with the 2p x (p+1)
+    // block of P1 as compile-time constants -- 2p (p+1) FMAs per parent instead of a dense TW-term sum per coarse
+    // node, the line in registers instead of two shared-memory reads per term.
+    constexpr bool ALIGNED = TW % (2 * p) == 0;
+    constexpr int  NPC     = ALIGNED ? TW / (2 * p) : 1; // parent cells across a tile
+    constexpr int  NCF     = p * NPC + 1;                // coarse nodes across a tile
+    const bool     fast    = ALIGNED && wx == TW && wy == TW;
+    auto           line_restrict = [&](const T(&f)[TW], T(&out)[NCF]) {
+#pragma unroll
+      for (int i = 0; i < NCF; ++i)
+        out[i] = 0;
+#pragma unroll
+      for (int c = 0; c < NPC; ++c)
+#pragma unroll
+        for (int r = 0; r < 2 * p; ++r)
+#pragma unroll
+          for (int i = 0; i < n; ++i)
+            out[p * c + i] += p1_table<T>()[r * n + i] * f[2 * p * c + r];
+    };
+
     // x/y restriction of `np` planes held in z_s and addition into the coarse planes k_first, ...
     auto planes_2d = [&](const int k_first, const int np) {
       __syncthreads();
+      if (fast)
+        {
+          for (int t = tid; t < np * TW; t += NT)
+            {
+              const int fj = t % TW, b = t / TW;
+              T         f[TW], out[NCF];
+#pragma unroll
+              for (int fi = 0; fi < TW; ++fi)
+                f[fi] = z_s[(b * TW + fj) * TW + fi];
+              line_restrict(f, out);
+#pragma unroll
+              for (int ci = 0; ci < NCF; ++ci)
+                x_s[(b * TW + fj) * NC + ci] = out[ci];
+            }
+          __syncthreads();
+          for (int t = tid; t < np * NCF; t += NT)
+            {
+              const int ci = t % NCF, b = t / NCF;
+              T         f[TW], out[NCF];
+#pragma unroll
+              for (int fj = 0; fj < TW; ++fj)
+                f[fj] = x_s[(b * TW + fj) * NC + ci];
+              line_restrict(f, out);
+              const int gi = bx + ci, gk = k_first + b;
+#pragma unroll
+              for (int cj = 0; cj < NCF; ++cj)
+                if (!(A.constrained && is_constrained(Lc, gi, by + cj, gk)))
+                  atomicAdd(dst + dof_index(Lc, gi, by + cj, gk), out[cj]);
+            }
+          return;
+        }
       for (int t = tid; t < np * TW * ncx; t += NT)
         {
           const int ci = t % ncx, rest = t / ncx;
