@@ -1,0 +1,69 @@
+// multigrid::LaplaceOperator on adaptively refined meshes with hanging nodes -- the operator that
+// poisson_l/program.cc:232-260 builds from a MatrixFree object with AffineConstraints (hanging nodes + zero boundary
+// values), over the C ABI (include/mgb200.h, mgb_adaptive_*).  The mesh (Triangulation + refine flags of
+// poisson_l/program.cc:465-541) is owned by the operator: a forest of root cells, refined cell by cell and kept 2:1
+// balanced.  The vector holds the unconstrained and the Dirichlet DoFs; hanging-node values are not stored.
+#ifndef MULTIGRID_LAPLACE_OPERATOR_ADAPTIVE_H
+#define MULTIGRID_LAPLACE_OPERATOR_ADAPTIVE_H
+
+#include "laplace_operator_dg.h" // DGVector: plain device array
+
+namespace multigrid
+{
+  template <int dim, int fe_degree, typename number>
+  class AdaptiveLaplaceOperator
+  {
+    static_assert(dim == 3, "the B200 path implements dim = 3");
+
+  public:
+    typedef DGVector<number> VectorType;
+    AdaptiveLaplaceOperator() = default;
+    AdaptiveLaplaceOperator(const AdaptiveLaplaceOperator &) = delete;
+    ~AdaptiveLaplaceOperator()
+    {
+      if (h_)
+        mgb_adaptive_destroy(h_);
+    }
+    // GridGenerator::subdivided_hyper_rectangle / hyper_L (root_mask[z][y][x] == 0 removes a root cell) + refine_global
+    void
+    reinit(const int n_roots[3], const unsigned char *root_mask, const double lower[3], const double upper[3],
+           const int n_global_refinements, const int device = 0)
+    {
+      if (h_)
+        mgb_adaptive_destroy(h_);
+      h_ = nullptr;
+      check(mgb_adaptive_create(fe_degree, n_roots, root_mask, lower, upper, n_global_refinements, device, &h_));
+    }
+    std::size_t n_active_cells() const { return (std::size_t)mgb_adaptive_n_cells(h_); }
+    // level and position (in cells of that level) of the active cells, in the order the refine flags refer to
+    void
+    get_cells(std::vector<int> &level, std::vector<int> &position) const
+    {
+      level.resize(n_active_cells());
+      position.resize(3 * n_active_cells());
+      check(mgb_adaptive_cells(h_, level.data(), position.data()));
+    }
+    // cell->set_refine_flag() + execute_coarsening_and_refinement()   poisson_l/program.cc:508-541
+    void execute_refinement(const std::vector<unsigned char> &flags) { check(mgb_adaptive_refine(h_, flags.data())); }
+    std::size_t
+    m() const
+    {
+      const int64_t n = mgb_adaptive_n_dofs(h_);
+      if (n < 0)
+        throw std::runtime_error(std::string("mgb200: ") + mgb_last_error());
+      return (std::size_t)n;
+    }
+    std::size_t n() const { return m(); }
+    void        initialize_dof_vector(VectorType &v) const { v.reinit(m()); }
+    // laplace_operator.h:575-601 with the constraints applied in the kernel
+    void vmult(VectorType &dst, const VectorType &src) const { check(mgb_adaptive_vmult(h_, prec, dst.begin(), src.begin())); }
+    // compute_diagonal + get_matrix_diagonal_inverse   laplace_operator.h:747-800
+    void compute_diagonal(VectorType &inverse_diagonal) const { check(mgb_adaptive_inverse_diagonal(h_, prec, inverse_diagonal.begin())); }
+    void synchronize() const { check(mgb_adaptive_sync(h_)); }
+
+  private:
+    static constexpr int prec = precision_of<number>::value;
+    mgb_adaptive         h_   = nullptr;
+  };
+} // namespace multigrid
+#endif

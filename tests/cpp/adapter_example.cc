@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 
+#include "multigrid/laplace_operator_adaptive.h"
 #include "multigrid/laplace_operator_dg.h"
 #include "multigrid/multigrid_solver_dg.h"
 #include "multigrid/multigrid_solver.h"
@@ -69,6 +70,37 @@ main(int argc, char **argv)
           dg.prolongate_add_cg_to_dg(y, p);
           dg.vmult_residual_and_restrict_to_cg(x, y, q);
         }
+
+      // operator on an adaptively refined hyper_L (poisson_l/program.cc:465-541): one global refinement, then the cells
+      // next to the re-entrant edge x = y = 0 once more; x^T A x of the all-ones vector counts the boundary layer
+      {
+        const int           roots[3] = {2, 2, 2};
+        const unsigned char mask[8]  = {1, 1, 1, 1, 1, 1, 1, 0};
+        const double        lo[3] = {-1, -1, -1}, hi[3] = {1, 1, 1};
+        multigrid::AdaptiveLaplaceOperator<3, 2, double> ad;
+        ad.reinit(roots, mask, lo, hi, 1);
+        std::vector<int> lev, pos;
+        ad.get_cells(lev, pos);
+        std::vector<unsigned char> flags(lev.size(), 0);
+        for (std::size_t c = 0; c < lev.size(); ++c)
+          {
+            const double hc = 1. / (1 << lev[c]), cx = -1 + (pos[3 * c] + 0.5) * hc, cy = -1 + (pos[3 * c + 1] + 0.5) * hc;
+            flags[c]        = cx * cx + cy * cy < 0.55 * 0.55;
+          }
+        ad.execute_refinement(flags);
+        multigrid::DGVector<double> ax, ay;
+        ad.initialize_dof_vector(ax);
+        ad.initialize_dof_vector(ay);
+        std::vector<double> ones(ad.m(), 1.0);
+        ax.import_from_host(ones);
+        ad.vmult(ay, ax);
+        ad.synchronize();
+        const std::vector<double> r = ay.export_to_host();
+        double                    e = 0;
+        for (double v : r)
+          e += v;
+        std::printf("adaptive_cells %zu adaptive_m %zu adaptive_xAx %.12e\n", ad.n_active_cells(), ad.m(), e);
+      }
 
       // DG multigrid solver as poisson_dg/program.cc:227-263: [-1,1]^3, 2 refinements, tolerance 1e-3
       multigrid::MeshDescription dmesh;

@@ -66,6 +66,18 @@ def test_example_driver_matches_oracle(mgb, orc):
     assert abs(float(out["penalty_x"]) - d.penalty()[0]) <= 1e-6 * d.penalty()[0]  # printed with 7 digits
     jt = orc.JacobiTransformed(d)
     assert float(out["xPx"]) > 0 and abs(float(out["xPx"]) - x @ jt.vmult(x)) <= 1e-9 * abs(x @ jt.vmult(x))
+    # the adaptive operator of the example: same mesh through the Python mirror, energy against the geometric oracle
+    from oracle import adaptive_oracle
+    mask = np.ones((2, 2, 2), dtype=np.uint8)
+    mask[1, 1, 1] = 0
+    a = mgb.LaplaceOperatorAdaptive(2, (2, 2, 2), mask, n_global_refinements=1)
+    lo, sz = a.cell_boxes()
+    a.refine(np.hypot(*(lo + 0.5 * sz)[:, :2].T) < 0.55)
+    lo, sz = a.cell_boxes()
+    oa = adaptive_oracle.AdaptiveOracle(2, lo, sz)
+    assert int(out["adaptive_cells"]) == a.n_cells() and int(out["adaptive_m"]) == oa.n_dofs()
+    e_ref = float(np.ones(oa.n_dofs()) @ oa.vmult(np.ones(oa.n_dofs())))
+    assert abs(float(out["adaptive_xAx"]) - e_ref) <= 1e-10 * abs(e_ref)
     ds = orc.MultigridSolverDG(4, (1, 1, 1), 2)
     _, rate_dg, _ = ds.solve_cg(1e-3)
     assert int(out["dg_cg_its"]) == ds.last_step
