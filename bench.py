@@ -389,6 +389,18 @@ def varcoef_lines(r):
     return out
 
 
+def adaptive_lines(r):
+    """BASELINE config 5's access pattern (secondary lines, one GPU): FE_Q(3) on hyper_L refined towards the re-entrant
+    edge, hanging-node and Dirichlet constraints applied in the kernel (poisson_l/program.cc:232-260)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import time_adaptive
+    out = time_adaptive.run(3, 4, 3, reps=20)
+    for k in ("vmult_f64", "vmult_f32"):
+        out[k]["frac_hbm"] = out[k]["gbs"] / r["hbm_gbs"]
+    out["workload"] = "FE_Q(3) on hyper_L, 4 global refinements + 3 rounds towards the re-entrant edge, hanging nodes in-kernel"
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -416,6 +428,7 @@ def main():
         if r["world"] == 1 and not args.no_dg:
             line["dg"] = dg_lines(r)
             line["variable_coefficient"] = varcoef_lines(r)
+            line["adaptive"] = adaptive_lines(r)
         print(json.dumps(line), flush=True)
     if r["dist"] is not None:
         r["dist"].barrier()

@@ -87,8 +87,9 @@ namespace mgb
     const int        gx0 = tx * TW, gy0 = ty * TW;
     const int        wx = tile_width(L, 0, tx), wy = tile_width(L, 1, ty);
     const int        ncz = L.ncell[2], nd2 = L.nd[2];
-    const int        c0 = layer_begin + seg * layers_per_segment;
-    const int        c1 = imin(c0 + layers_per_segment, layer_end);
+    const bool       second = A.layer_begin2 >= 0 && seg == 1; // two single layers in one launch
+    const int        c0 = second ? A.layer_begin2 : layer_begin + seg * layers_per_segment;
+    const int        c1 = second ? c0 + 1 : imin(c0 + layers_per_segment, layer_end);
     const bool       plain = A.read_plain != 0;
 
     // ---- per-thread source points (fixed over the planes): running pointer, plane stride, copy size

@@ -33,6 +33,7 @@ namespace mgb
     int       read_plain;    // 1: do not zero constrained entries on read (compute_residual)
     int       first_chebyshev; // 1: x_{k-1} = 0 implied (iteration_index == 1)
     int       layer_begin, layer_end; // tile kernel: local cell layers of this launch (-1: all owned layers)
+    int       layer_begin2;           // tile kernel: if >= 0 the launch works on the two single layers layer_begin and layer_begin2
     double   *dot_out;   // APPLY_SET on the tile kernel: if set, sum of src[i] * dst[i] over the stored points is added here
   };
 

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -507,18 +508,24 @@ namespace mgb
         cudaStreamDestroy(stream);
       if (comm)
         mgb_internal_comm_destroy(comm);
+      if (comm_stream)
+        {
+          cudaStreamDestroy(comm_stream);
+          cudaEventDestroy(comm_ev[0]);
+          cudaEventDestroy(comm_ev[1]);
+        }
     }
 
     // update_ghost_values (the MPI face exchange of laplace_operator_dg.h:981-1058): the top owned cell layer goes to
     // the rank above, the bottom one to the rank below, one NCCL group on the operator's stream
     template <typename T>
     void
-    update_ghosts(T *v)
+    update_ghosts(T *v, cudaStream_t on = nullptr)
     {
       if (n_ranks == 1)
         return;
-      mgb_internal_comm_exchange(comm, stream, v + owned_off + owned_n - layer_dofs, v, v + owned_off, v + owned_off + owned_n,
-                                 layer_dofs, sizeof(T) == 8);
+      mgb_internal_comm_exchange(comm, on ? on : stream, v + owned_off + owned_n - layer_dofs, v, v + owned_off,
+                                 v + owned_off + owned_n, layer_dofs, sizeof(T) == 8);
       ++exchanges;
     }
     int64_t exchanges = 0;
@@ -771,10 +778,10 @@ namespace mgb
         }
       for (int e = 0; e < 6; ++e)
         A.gt[e] = (T)geom.gt[e];
-      A.n_cells    = (uint32_t)((size_t)nc[0] * nc[1] * lz);
-      A.cell_begin = (uint32_t)((size_t)nc[0] * nc[1] * zg);
+      const size_t layer_cells = (size_t)nc[0] * nc[1];
+      A.n_cells    = (uint32_t)(layer_cells * lz);
+      A.cell_begin = (uint32_t)(layer_cells * zg);
       A.cz_shift   = cz0 - zg;
-      update_ghosts(const_cast<T *>(src));
       A.src      = src;
       A.dst      = dst;
       A.rhs      = rhs;
@@ -783,20 +790,62 @@ namespace mgb
       A.f1       = (T)f1;
       A.f2       = (T)f2;
       A.mode     = mode;
-      switch (p)
+      const auto run = [&](const DGArgs<T> &B) {
+        switch (p)
+          {
+            case 1: launch<1, T>(B); break;
+            case 2: launch<2, T>(B); break;
+            case 3: launch<3, T>(B); break;
+            case 4: launch<4, T>(B); break;
+            case 5: launch<5, T>(B); break;
+            case 6: launch<6, T>(B); break;
+            case 7: launch<7, T>(B); break;
+            default: launch<8, T>(B); break;
+          }
+        ++launches;
+        MGB_DG_CHECK(cudaGetLastError());
+      };
+      if (n_ranks > 1 && overlap && lz >= 3)
         {
-          case 1: launch<1, T>(A); break;
-          case 2: launch<2, T>(A); break;
-          case 3: launch<3, T>(A); break;
-          case 4: launch<4, T>(A); break;
-          case 5: launch<5, T>(A); break;
-          case 6: launch<6, T>(A); break;
-          case 7: launch<7, T>(A); break;
-          default: launch<8, T>(A); break;
+          // the exchange of the ghost cell layers runs on the communication stream while the cell layers that touch no
+          // ghost layer are computed (laplace_operator_dg.h:981-1058 overlaps its MPI messages the same way); then the
+          // first and the last owned layer
+          if (!comm_stream)
+            {
+              MGB_DG_CHECK(cudaStreamCreateWithFlags(&comm_stream, cudaStreamNonBlocking));
+              MGB_DG_CHECK(cudaEventCreateWithFlags(&comm_ev[0], cudaEventDisableTiming));
+              MGB_DG_CHECK(cudaEventCreateWithFlags(&comm_ev[1], cudaEventDisableTiming));
+            }
+          MGB_DG_CHECK(cudaEventRecord(comm_ev[0], stream));
+          MGB_DG_CHECK(cudaStreamWaitEvent(comm_stream, comm_ev[0], 0));
+          update_ghosts(const_cast<T *>(src), comm_stream);
+          MGB_DG_CHECK(cudaEventRecord(comm_ev[1], comm_stream));
+          const int first = zg ? 1 : 0, last = ztop ? 1 : 0; // owned layers that read a ghost layer
+          DGArgs<T> B   = A;
+          B.cell_begin  = (uint32_t)(layer_cells * (zg + first));
+          B.n_cells     = (uint32_t)(layer_cells * (lz - first - last));
+          run(B);
+          MGB_DG_CHECK(cudaStreamWaitEvent(stream, comm_ev[1], 0));
+          if (first)
+            {
+              B.cell_begin = (uint32_t)(layer_cells * zg);
+              B.n_cells    = (uint32_t)layer_cells;
+              run(B);
+            }
+          if (last)
+            {
+              B.cell_begin = (uint32_t)(layer_cells * (zg + lz - 1));
+              B.n_cells    = (uint32_t)layer_cells;
+              run(B);
+            }
+          return;
         }
-      ++launches;
-      MGB_DG_CHECK(cudaGetLastError());
+      update_ghosts(const_cast<T *>(src));
+      run(A);
     }
+    bool         overlap     = getenv("MGB200_DG_OVERLAP") == nullptr || getenv("MGB200_DG_OVERLAP")[0] != '0';
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t  comm_ev[2]  = {nullptr, nullptr};
 
     // laplace_operator_dg.h:862-905
     template <typename T>

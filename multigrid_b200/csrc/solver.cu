@@ -1039,6 +1039,7 @@ namespace mgb
       A.read_plain      = 0;
       A.first_chebyshev = 0;
       A.layer_begin = A.layer_end = -1;
+      A.layer_begin2 = -1;
       A.dot_out     = nullptr;
     }
 
@@ -1104,13 +1105,21 @@ namespace mgb
               A.layer_end   = i1;
               launch_cartesian(A);
               ctx->join_comm();
-              if (L.zg)
+              if (L.zg && L.ztop)
+                {
+                  // both boundary layers in one launch
+                  A.layer_begin  = 1;
+                  A.layer_end    = 2;
+                  A.layer_begin2 = L.ncell[2] - 1;
+                  launch_cartesian(A);
+                }
+              else if (L.zg)
                 {
                   A.layer_begin = 1;
                   A.layer_end   = 2;
                   launch_cartesian(A);
                 }
-              if (L.ztop)
+              else if (L.ztop)
                 {
                   A.layer_begin = L.ncell[2] - 1;
                   A.layer_end   = L.ncell[2];
