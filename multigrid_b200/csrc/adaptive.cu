@@ -86,6 +86,9 @@ namespace mgb
       for (const ACell &k : cells)
         max_level = std::max(max_level, k.level);
       const int L = max_level;
+      for (int d = 0; d < 3; ++d) // node indices are packed into 19 bits per direction (pack_key)
+        if (((int64_t)nroot[d] << L) * p + 1 >= (int64_t)1 << 19)
+          throw std::runtime_error("mesh too fine for the node index range: reduce the root grid, the degree or the number of levels");
       std::sort(cells.begin(), cells.end(), [L](const ACell &a, const ACell &b) {
         for (int d = 2; d >= 0; --d)
           {
@@ -431,8 +434,15 @@ namespace mgb
                 }
         }
       row_cache.clear();
+      check_size();
     }
     size_t n_dofs() const { return dirichlet.size(); }
+    void
+    check_size() const
+    {
+      if (dirichlet.size() >= 0x7fffffffull || row_dof.size() >= 0x7fffffffull)
+        throw std::runtime_error("too many DoFs for 32-bit indices");
+    }
   };
 } // namespace mgb
 

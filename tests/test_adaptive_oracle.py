@@ -91,3 +91,9 @@ def test_refinement_api_errors(mgb):
         mgb.LaplaceOperatorAdaptive(2, (1, 1, 1), np.zeros((1, 1, 1), dtype=np.uint8))
     op = mgb.LaplaceOperatorAdaptive(2, (1, 1, 1), None, n_global_refinements=1)
     assert op.n_cells() == 8 and op.m() == 125 and op.info()["hanging_local_nodes"] == 0
+    # node indices must fit the key: 64 roots x 2^8 cells x degree 8 does not
+    with pytest.raises(mgb.MgbError):
+        deep = mgb.LaplaceOperatorAdaptive(8, (64, 1, 1), None, (-1.,) * 3, (1.,) * 3, 0)
+        for _ in range(13):
+            lo, sz = deep.cell_boxes()
+            deep.refine(np.linalg.norm(lo, axis=1) < 1e-9 + np.linalg.norm(lo, axis=1).min())
