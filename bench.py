@@ -229,6 +229,9 @@ def native_arm(args):
 
     nsub, nref, lo, hi = weak_scaling_mesh(args.cells, world)
     comm = mgb.comm_from_torch_distributed() if dist is not None else None
+    # CUDA context creation and the first touch of the device (seconds on a fresh box) are not part of the solver set-up
+    torch.zeros(1, device="cuda")
+    torch.cuda.synchronize()
     t_setup = time.perf_counter()
     s = mgb.MultigridSolver(DEGREE, nsub, nref, lower=lo, upper=hi, degree_pre=3, degree_post=3, n_cycles=2,
                             device=local_rank, comm=comm)
