@@ -253,6 +253,11 @@ typedef struct mgb_dg_solver_options {
   int degree_pre, degree_post; /* Chebyshev degree (equal, multigrid_solver_dg.h:83-85); default 3       */
   int preconditioner;       /* of the DG smoother: 1 = JacobiTransformed (reference, :294-304), 0 = point Jacobi */
   int device;
+  /* one process per GPU (the reference's MPI_COMM_WORLD): as in mgb_options; the DG operator and the finest FE_Q
+   * level share the z-slabs (cell layers in z a multiple of comm_size, at least two per GPU) and one communicator;
+   * vectors are then the local DG vectors of mgb_dg_partition() on the operator of mgb_dg_solver_parts()        */
+  int comm_rank, comm_size;
+  unsigned char comm_id[128];
 } mgb_dg_solver_options;
 
 void mgb_dg_solver_default_options(mgb_dg_solver_options *opt);

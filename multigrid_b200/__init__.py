@@ -76,6 +76,9 @@ class DGSolverOptions(C.Structure):
         ("degree_post", C.c_int),
         ("preconditioner", C.c_int),
         ("device", C.c_int),
+        ("comm_rank", C.c_int),
+        ("comm_size", C.c_int),
+        ("comm_id", C.c_ubyte * 128),
     ]
 
 
@@ -790,10 +793,15 @@ class MultigridSolverDG:
     JACOBI, JACOBI_TRANSFORMED = 0, 1
 
     def __init__(self, degree=4, n_subdivisions=(1, 1, 1), n_refinements=3, lower=(-1.,) * 3, upper=(1.,) * 3,
-                 degree_pre=3, degree_post=3, preconditioner=1, device=0):
+                 degree_pre=3, degree_post=3, preconditioner=1, device=0, comm=None):
+        """comm = (rank, size, unique_id bytes) for one process per GPU (comm_from_torch_distributed()): the DG
+        operator and the finest FE_Q level share the z-slabs; vectors are the local DG vectors (partition())"""
         import torch
         o = DGSolverOptions()
         lib().mgb_dg_solver_default_options(C.byref(o))
+        if comm is not None and comm[1] > 1:
+            o.comm_rank, o.comm_size = comm[0], comm[1]
+            o.comm_id[:] = list(comm[2])
         o.degree = degree
         if isinstance(n_subdivisions, int):
             n_subdivisions = (n_subdivisions,) * 3
@@ -880,6 +888,12 @@ class MultigridSolverDG:
         fe, dg = C.c_void_p(), C.c_void_p()
         _check(lib().mgb_dg_solver_parts(self.h, C.byref(fe), C.byref(dg)))
         return fe, dg
+
+    def partition(self):
+        """z-slab of this rank (as LaplaceOperatorDG.partition())"""
+        v = (C.c_int64 * 6)()
+        _check(lib().mgb_dg_partition(self.parts()[1], v))
+        return dict(n_global=v[0], n_local=v[1], owned_offset=v[2], n_owned=v[3], first_layer=v[4], n_layers=v[5])
 
     def fe_smoother_info(self, level):
         fe, _ = self.parts()

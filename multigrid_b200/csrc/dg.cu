@@ -27,6 +27,7 @@ void        mgb_internal_comm_destroy(mgb_comm_t *c);
 void        mgb_internal_comm_exchange(mgb_comm_t *c, cudaStream_t stream, const void *send_up, void *recv_dn, const void *send_dn,
                                        void *recv_up, size_t count, int is_double);
 void        mgb_internal_comm_allreduce(mgb_comm_t *c, cudaStream_t stream, double *dev, int count);
+mgb_comm_t *mgb_internal_comm_borrow(mgb_solver_t *s);
 
 namespace mgb
 {
@@ -389,7 +390,9 @@ namespace mgb
     void          *jt_dinv[2] = {nullptr, nullptr};   // [64 cell types][n^3], float / double
     std::vector<double> jt_dinv_host;
 
-    explicit DGOperator(const mgb_dg_options &o)
+    // `borrowed`: the communicator of the FE_Q solver the operator works with (DG multigrid solver); without it
+    // and with comm_size > 1 the operator makes its own from o.comm_id
+    explicit DGOperator(const mgb_dg_options &o, mgb_comm_t *borrowed = nullptr)
       : opt(o)
     {
       if (o.degree < 1 || o.degree > 8)
@@ -483,7 +486,9 @@ namespace mgb
       MGB_DG_CHECK(cudaEventCreate(&ev[1]));
       MGB_DG_CHECK(cudaMalloc(&scal_dev, 4 * sizeof(double)));
       MGB_DG_CHECK(cudaMallocHost(&scal_host, 4 * sizeof(double)));
-      if (n_ranks > 1)
+      if (borrowed)
+        comm = borrowed;
+      else if (n_ranks > 1)
         comm = mgb_internal_comm_create(rank, n_ranks, o.comm_id, o.device);
     }
 
@@ -676,12 +681,13 @@ namespace mgb
     void
     check_same_mesh(const LevelDesc &L) const
     {
-      if (n_ranks > 1)
-        throw std::runtime_error("the DG <-> FE_Q transfer runs on one GPU");
-      if (L.p != p || L.ncell[0] != nc[0] || L.ncell[1] != nc[1] || L.ncell[2] != nc[2])
-        throw std::runtime_error("the FE_Q level and the DG operator must share degree and mesh");
+      // on several GPUs both sides hold the same z-slab: the FE_Q box is the owned cell layers plus the ghost layer
+      // below, so FE_Q cell c and DG cell c are the same cell (the DG vector has one more ghost layer on top)
+      if (L.p != p || L.ncell[0] != nc[0] || L.ncell[1] != nc[1] || L.ncell[2] != lz + zg || L.zg != zg || L.ztop != ztop)
+        throw std::runtime_error("the FE_Q level and the DG operator must share degree, mesh and partition");
     }
-    // prolongate_add_cg_to_dg (laplace_operator_dg.h:1863-1894): dg += cg
+    // prolongate_add_cg_to_dg (laplace_operator_dg.h:1863-1894): dg += cg.  On several GPUs the caller has updated
+    // the ghost planes of cg (the top plane of the last owned cell layer is a ghost)
     template <typename T>
     void
     prolongate_add_cg_to_dg(const LevelDesc &L, T *dg, const T *cg)
@@ -702,6 +708,7 @@ namespace mgb
           MGB_DG_CHECK(cudaMalloc(&host_buf[i], n_dofs * 8));
       T *res = (T *)host_buf[0];
       apply<T>(DG_RESIDUAL, res, lhs, rhs);
+      update_ghosts(res); // the first owned FE_Q plane sums over the cell layer below (compress(add) of the reference)
       MGB_DG_CHECK(cudaMemsetAsync(restricted, 0, (size_t)L.n_dofs * sizeof(T), stream));
       k_dg_to_cg_add<T><<<grid(L.n_dofs), 256, 0, stream>>>(L, res, restricted);
       ++launches;

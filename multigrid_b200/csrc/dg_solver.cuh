@@ -11,6 +11,8 @@ namespace mgb
   struct DGCellGeom
   {
     int    n, nc[3];
+    size_t cell_begin, n_cells; // owned cells of this rank in its local numbering
+    int    cz_shift;            // global cell layer of local layer 0
     double lower[3], h[3], T[9], jxw; // x = T (lower + h (c + xi)), jxw = |det(T diag(h))|
   };
 
@@ -28,11 +30,11 @@ namespace mgb
     double                  *Ss = sm + n3; // [n^2]
     for (int i = threadIdx.x; i < n * n; i += blockDim.x)
       Ss[i] = S[i];
-    const size_t n_cells = (size_t)g.nc[0] * g.nc[1] * g.nc[2];
     double       err = 0, vol = 0;
-    for (size_t c = blockIdx.x; c < n_cells; c += gridDim.x)
+    for (size_t c = g.cell_begin + blockIdx.x; c < g.cell_begin + g.n_cells; c += gridDim.x)
       {
-        const int cx = (int)(c % g.nc[0]), cy = (int)((c / g.nc[0]) % g.nc[1]), cz = (int)(c / ((size_t)g.nc[0] * g.nc[1]));
+        const int cx = (int)(c % g.nc[0]), cy = (int)((c / g.nc[0]) % g.nc[1]),
+                  cz = (int)(c / ((size_t)g.nc[0] * g.nc[1])) + g.cz_shift;
         __syncthreads();
         for (int q = threadIdx.x; q < n3; q += blockDim.x)
           {
@@ -138,10 +140,11 @@ namespace mgb
       MGB_DG_CHECK(cudaMalloc(&g, N * sizeof(float)));
       MGB_DG_CHECK(cudaMalloc(&h, N * sizeof(float)));
       MGB_DG_CHECK(cudaMalloc(&d, N * sizeof(float)));
-      double sum[2];
-      op.sums<2>(sum, [=] __device__(size_t i, double *acc) { acc[0] += (double)(i % 11); });
-      const float mean = (float)(sum[0] / (double)N);
-      op.foreach (N, [=] __device__(size_t i) { g[i] = -((float)(i % 11) - mean); });
+      double       sum[2];
+      const size_t shift = (size_t)(op.cz0 - op.zg) * op.layer_dofs; // global index of local entry 0
+      op.sums<2>(sum, [=] __device__(size_t i, double *acc) { acc[0] += (double)((i + shift) % 11); });
+      const float mean = (float)(sum[0] / (double)op.n_dofs_global);
+      op.foreach (N, [=] __device__(size_t i) { g[i] = -((float)((i + shift) % 11) - mean); });
       std::vector<double> diag, off;
       double              res = std::sqrt(dot(g, g));
       cg_iterations           = 0;
@@ -261,6 +264,9 @@ namespace mgb
       fo.n_cycles    = 1;
       fo.problem     = MGB_PROBLEM_CUBE_SINE;
       fo.device      = o.device;
+      fo.comm_rank   = o.comm_rank;
+      fo.comm_size   = o.comm_size > 1 ? o.comm_size : 1;
+      std::memcpy(fo.comm_id, o.comm_id, sizeof(fo.comm_id));
       if (mgb_solver_create(&fo, &fe) != 0)
         throw std::runtime_error(mgb_last_error());
       try
@@ -304,8 +310,11 @@ namespace mgb
           dopt.upper[k]          = opt.upper[k];
           dopt.trafo[4 * k]      = 1.;
         }
-      dopt.device = opt.device;
-      op          = new DGOperator(dopt);
+      dopt.device    = opt.device;
+      dopt.comm_rank = opt.comm_rank;
+      dopt.comm_size = opt.comm_size > 1 ? opt.comm_size : 1;
+      // one process per GPU: the DG operator shares the z-slabs and the NCCL communicator of the FE_Q hierarchy
+      op = new DGOperator(dopt, dopt.comm_size > 1 ? mgb_internal_comm_borrow(fe) : nullptr);
       op->use_stream(mgb_internal_stream(fe));
       op->preconditioner = opt.preconditioner;
       op->check_same_mesh(Lfine);
@@ -369,9 +378,12 @@ namespace mgb
       for (int k = 0; k < 9; ++k)
         G.T[k] = (k % 4 == 0) ? 1. : 0.;
       G.jxw             = det;
+      G.cell_begin      = (size_t)op->nc[0] * op->nc[1] * op->zg;
+      G.n_cells         = (size_t)op->nc[0] * op->nc[1] * op->lz;
+      G.cz_shift        = op->cz0 - op->zg;
       const int    n    = op->n;
       const size_t smem = (size_t)(n * n * n + n * n) * sizeof(double);
-      const unsigned blocks = (unsigned)std::min<size_t>(op->n_cells, 148 * 32);
+      const unsigned blocks = (unsigned)std::min<size_t>(G.n_cells, 148 * 32);
       k_dg_cell_integrals<<<blocks, 128, smem, op->stream>>>(G, mode, fn, basis_dev, basis_dev + n * n, basis_dev + n * n + n,
                                                               u, out);
       ++op->launches;
@@ -384,6 +396,8 @@ namespace mgb
     {
       MGB_DG_CHECK(cudaMemsetAsync(op->scal_dev, 0, 4 * sizeof(double), op->stream));
       cell_integrals(1, FN_CUBE_SOLUTION, solution, op->scal_dev);
+      if (op->n_ranks > 1)
+        mgb_internal_comm_allreduce(op->comm, op->stream, op->scal_dev, 2);
       MGB_DG_CHECK(cudaMemcpyAsync(op->scal_host, op->scal_dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, op->stream));
       MGB_DG_CHECK(cudaStreamSynchronize(op->stream));
       return std::sqrt(op->scal_host[0] / op->scal_host[1]);
@@ -399,6 +413,8 @@ namespace mgb
       op->vmult_residual_and_restrict_to_cg<float>(Lfine, defect_dg, solution_update_dg, (float *)fe_defect);
       fe_check(mgb_solver_vcycle_inplace(fe));
       fe_check(mgb_solver_vector(fe, 5, maxlevel, &fe_update)); // the smoother swaps vectors: ask after the cycle
+      if (op->n_ranks > 1)
+        fe_check(mgb_vec_update_ghost_values(fe, maxlevel, MGB_F32, fe_update));
       op->prolongate_add_cg_to_dg<float>(Lfine, solution_update_dg, (const float *)fe_update);
       smooth_dg.step(solution_update_dg, defect_dg);
     }

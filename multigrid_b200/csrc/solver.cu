@@ -2107,6 +2107,7 @@ struct mgb_comm_t
 {
   ncclComm_t comm = nullptr;
   int        rank = 0, size = 1;
+  bool       owned = true;
 };
 
 mgb_comm_t *
@@ -2132,7 +2133,7 @@ mgb_internal_comm_create(const int rank, const int size, const unsigned char id[
 void
 mgb_internal_comm_destroy(mgb_comm_t *c)
 {
-  if (c && c->comm)
+  if (c && c->comm && c->owned)
     Nccl::get().CommDestroy(c->comm);
   delete c;
 }
@@ -2229,15 +2230,31 @@ mgb_internal_stream(mgb_solver_t *s)
   return S(s).ctx.stream;
 }
 
+// the local box of a level; on several GPUs the z-slab of this rank (the DG operator checks that its own slab is
+// the same one)
 const mgb::LevelDesc *
 mgb_internal_level_desc(mgb_solver_t *s, int level)
 {
   MultigridSolver &m = S(s);
   Level           &l = *m.levels[check_level(m, level)];
-  if (l.slab.distributed)
-    throw std::runtime_error("the DG <-> FE_Q transfer runs on one GPU");
+  if (m.ctx.n_ranks > 1 && !l.slab.distributed)
+    throw std::runtime_error("the DG <-> FE_Q transfer needs a distributed finest FE_Q level (too few cell layers per GPU)");
   m.ctx.sync();
   return &l.d;
+}
+
+// the solver's communicator for the DG operator of the DG multigrid solver (one NCCL communicator per solver);
+// the returned object does not own it
+mgb_comm_t *
+mgb_internal_comm_borrow(mgb_solver_t *s)
+{
+  MultigridSolver &m = S(s);
+  mgb_comm_t      *c = new mgb_comm_t;
+  c->comm            = m.ctx.comm;
+  c->rank            = m.ctx.rank;
+  c->size            = m.ctx.n_ranks;
+  c->owned           = false;
+  return c;
 }
 
 extern "C"

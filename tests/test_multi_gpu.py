@@ -53,3 +53,14 @@ def test_two_gpus_dg_operator_against_oracle(mgb, orc, p, nsub, nref):
 
 def test_four_gpus_dg_operator_against_oracle(mgb, orc):
     run_ranks(4, ["4", "1,1,1", "2"], worker="mgpu_dg_worker.py", ok="mgpu dg worker ok")
+
+
+@pytest.mark.parametrize("p,nsub,nref", [(2, "1,1,1", 2), (3, "1,1,2", 2)])
+def test_two_gpus_dg_multigrid_solver_against_oracle(mgb, orc, p, nsub, nref):
+    """MultigridSolverDG (common/multigrid_solver_dg.h) with one process per GPU: same CG iteration count, residual
+    history, L2 error and solution as the global oracle composition"""
+    run_ranks(2, [str(p), nsub, str(nref)], worker="mgpu_dg_solver_worker.py", ok="mgpu dg solver worker ok")
+
+
+def test_four_gpus_dg_multigrid_solver_against_oracle(mgb, orc):
+    run_ranks(4, ["2", "1,1,1", "3"], worker="mgpu_dg_solver_worker.py", ok="mgpu dg solver worker ok")
