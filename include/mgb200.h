@@ -224,7 +224,9 @@ int mgb_dg_preconditioner_vmult(mgb_dg h, int precision, void *dst, const void *
 int mgb_dg_vmult_with_chebyshev_update(mgb_dg h, int precision, const void *rhs, int iteration_index, double factor1,
                                        double factor2, void *solution, void *solution_old);
 /* Same-degree transfer between the DG space and the FE_Q space of level `level` of solver `s` on the same mesh
- * (one GPU; both vectors of the given precision, the FE_Q vector in the solver's numbering):
+ * (both vectors of the given precision, the FE_Q vector in the solver's numbering; on several GPUs operator and
+ * level must hold the same z-slab and the caller refreshes the ghost planes of src_cg before prolongating, as
+ * mgb_dg_solver does):
  * prolongate_add_cg_to_dg(dst_dg, src_cg)                                   laplace_operator_dg.h:1863-1894: dg += P cg
  * vmult_residual_and_restrict_to_cg(rhs, lhs, restricted_residual)           :851-860 (action 1, :1798-1819):
  *                                                                           restricted = P^T (rhs - A lhs)          */
