@@ -37,6 +37,10 @@ namespace multigrid
       o.degree_pre    = (int)degree_pre;
       o.degree_post   = (int)degree_post;
       o.device        = mesh.device;
+      o.comm_rank     = mesh.comm_rank; // one process per GPU: z-slabs shared by the DG operator and the FE_Q hierarchy
+      o.comm_size     = mesh.comm_size;
+      for (int i = 0; i < 128; ++i)
+        o.comm_id[i] = mesh.comm_id[i];
       check(mgb_dg_solver_create(&o, &s_));
     }
     MultigridSolverDG(const MultigridSolverDG &) = delete;
