@@ -5,6 +5,8 @@ oracle still reproduces the file, the GPU tests compare the library with it dire
   fe_q_p{p}   : y = A x, FE_Q(p) on the cube [-0.9,1]^3, 2 x 2 x 2 cells (p <= 4: 4 x 4 x 4), lexicographic, Dirichlet rows identity
   dg_p{p}     : y = A x, SIP-DG FE_DGQ(p) on the sheared mesh of matvec_dg, 2 x 2 x 2 cells, cell-wise
   adaptive_*  : y = A x on the hanging-node meshes of tests/adaptive_cases.py, in the order of the sorted DoF coordinates
+  dg_solver_* : MultigridSolverDG (FE_DGQ(2), 4 x 4 x 4 cells on [-1,1]^3): residual history of solve_cg(1e-8), [L2 error],
+                and one preconditioner cycle applied to a seeded vector
 """
 import os
 import sys
@@ -52,7 +54,16 @@ def generate():
         x = np.zeros(o.n_dofs())
         x[order] = seeded(o.n_dofs(), 200 + i)
         out["adaptive_" + name] = o.vmult(x)[order]
+    s = orc.MultigridSolverDG(*DG_SOLVER_CASE)
+    out["dg_solver_cycle"] = s.vmult(seeded(s.n_dofs(), 300))
+    _, _, hist = s.solve_cg(1e-8)
+    out["dg_solver_history"] = np.asarray(hist)
+    out["dg_solver_l2_error"] = np.array([s.compute_l2_error()])
+    out["dg_solver_solution"] = s.solution.copy()
     return out
+
+
+DG_SOLVER_CASE = (2, (1, 1, 1), 2)      # degree, n_subdivisions, n_refinements
 
 
 if __name__ == "__main__":

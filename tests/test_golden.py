@@ -21,7 +21,8 @@ def test_oracle_reproduces_golden_vectors(orc, mgb):
     now = make_golden.generate()
     assert sorted(now) == sorted(GOLD.files)
     for k in GOLD.files:
-        assert rel(now[k], GOLD[k]) <= 1e-13, k
+        # (the solver runs sum in OpenMP reductions: rounding differs with the number of threads)
+        assert rel(now[k], GOLD[k]) <= (1e-9 if k.startswith("dg_solver") else 1e-13), k
 
 
 @pytest.mark.gpu
@@ -61,3 +62,23 @@ def test_library_against_golden_adaptive(mgb):
         dst = torch.zeros(op.m(), dtype=torch.float64, device="cuda")
         op.vmult(dst, torch.tensor(x, device="cuda"))
         assert rel(dst.cpu().numpy()[order], GOLD["adaptive_" + name]) <= 1e-12, name
+
+
+@pytest.mark.gpu
+def test_library_against_golden_dg_solver(mgb):
+    """MultigridSolverDG against the stored oracle run: the float cycle against the double one (2e-4), the same
+    number of CG iterations, the residual history, the L2 error to 3 digits"""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    g = mgb.MultigridSolverDG(*make_golden.DG_SOLVER_CASE)
+    src = make_golden.seeded(g.n_dofs(), 300)
+    dst = torch.zeros(g.n_dofs(), dtype=torch.float64, device="cuda")
+    g.vmult(dst, torch.tensor(src, device="cuda"))
+    assert rel(dst.cpu().numpy(), GOLD["dg_solver_cycle"]) <= 2e-4
+    g.solve_cg(1e-8)
+    hist, want = g.residual_history(), GOLD["dg_solver_history"]
+    assert hist.size == want.size
+    assert np.all(np.abs(hist - want) <= 0.1 * want + 1e-6 * want[0])
+    assert abs(g.compute_l2_error() - GOLD["dg_solver_l2_error"][0]) <= 1e-3 * GOLD["dg_solver_l2_error"][0]
+    assert rel(g.get_solution(), GOLD["dg_solver_solution"]) <= 1e-6
