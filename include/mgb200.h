@@ -178,6 +178,12 @@ int mgb_transfer_prolongate_no_boundary(mgb_solver s, int level, double *fine, c
  * vector operation ("actions" 0, 3, 4 of vmult_with_merged_ops, laplace_operator_dg.h:957-962).               */
 typedef struct mgb_dg_t *mgb_dg;
 
+#define MGB_DG_BASIS_GAUSS_LOBATTO 0 /* FE_DGQ(p): Lagrange in the Gauss-Lobatto points         (reference type 1) */
+#define MGB_DG_BASIS_HERMITE 1       /* FE_DGQHermite(p): Hermite-like interpolation            (reference type 0) */
+#define MGB_DG_BASIS_GAUSS 2         /* FE_DGQArbitraryNodes(QGauss(p+1)): collocated with the quadrature (type 2) */
+/* MGB_DG_BASIS_* of the reference's template parameter `type` (0, 1, 2) */
+#define MGB_DG_BASIS_OF_TYPE(type) ((type) == 0 ? MGB_DG_BASIS_HERMITE : ((type) == 1 ? MGB_DG_BASIS_GAUSS_LOBATTO : MGB_DG_BASIS_GAUSS))
+
 typedef struct mgb_dg_options {
   int degree;             /* 1..8                                                                   */
   int n_subdivisions[3];  /* coarse cells per direction      (matvec_dg/program.cc:61-64)           */
@@ -189,6 +195,10 @@ typedef struct mgb_dg_options {
    * a multiple of comm_size; comm_id from mgb_comm_unique_id() of rank 0.  comm_size <= 1: one GPU             */
   int comm_rank, comm_size;
   unsigned char comm_id[128];
+  /* 1-D basis of the DG space (template parameter `type` of LaplaceOperatorCompactCombine,
+   * laplace_operator_dg.h:346-350; matvec_dg/program.cc:44-49): one of MGB_DG_BASIS_*.  Zero, the default, is
+   * FE_DGQ; poisson_dg uses FE_DGQHermite (poisson_dg/program.cc:174).  Vectors hold the coefficients of this basis */
+  int basis;
 } mgb_dg_options;
 
 void mgb_dg_default_options(mgb_dg_options *opt);        /* the mesh of matvec_dg/program.cc, degree 4 */
@@ -260,6 +270,7 @@ typedef struct mgb_dg_solver_options {
    * vectors are then the local DG vectors of mgb_dg_partition() on the operator of mgb_dg_solver_parts()        */
   int comm_rank, comm_size;
   unsigned char comm_id[128];
+  int basis;                /* MGB_DG_BASIS_* of the DG space (default FE_DGQ; poisson_dg: MGB_DG_BASIS_HERMITE)  */
 } mgb_dg_solver_options;
 
 void mgb_dg_solver_default_options(mgb_dg_solver_options *opt);

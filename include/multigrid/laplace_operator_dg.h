@@ -1,6 +1,7 @@
 // multigrid::LaplaceOperatorCompactCombine<dim, fe_degree, Number, type> -- names and argument order of
-// common/laplace_operator_dg.h:360-363,771-955 over the C ABI (include/mgb200.h, mgb_dg_*).  type = 1 (FE_DGQ on
-// Gauss-Lobatto points) is built; the Chebyshev preconditioner is the point-Jacobi diagonal or JacobiTransformed.
+// common/laplace_operator_dg.h:360-363,771-955 over the C ABI (include/mgb200.h, mgb_dg_*).  type = 0 (FE_DGQHermite),
+// 1 (FE_DGQ on Gauss-Lobatto points) and 2 (FE_DGQArbitraryNodes(QGauss)) as in the reference (:346-348); vectors hold
+// the coefficients of that basis.  The Chebyshev preconditioner is the point-Jacobi diagonal or JacobiTransformed.
 #ifndef MULTIGRID_LAPLACE_OPERATOR_DG_H
 #define MULTIGRID_LAPLACE_OPERATOR_DG_H
 
@@ -58,7 +59,7 @@ namespace multigrid
   template <int dim, int fe_degree, typename Number, int type = 1>
   class LaplaceOperatorCompactCombine
   {
-    static_assert(dim == 3 && type == 1, "FE_DGQ (type 1) in 3-D is built");
+    static_assert(dim == 3 && type >= 0 && type <= 2, "3-D, type 0 (Hermite), 1 (Gauss-Lobatto) or 2 (Gauss)");
 
   public:
     typedef DGVector<Number> VectorType;
@@ -74,6 +75,7 @@ namespace multigrid
     reinit(mgb_dg_options o)
     {
       o.degree = fe_degree;
+      o.basis  = MGB_DG_BASIS_OF_TYPE(type);
       check(mgb_dg_create(&o, &h_));
     }
     std::size_t m() const { return (std::size_t)mgb_dg_n_dofs(h_); }

@@ -21,8 +21,10 @@ namespace multigrid
 
   public:
     // multigrid_solver_dg.h:59-65; n_cycles is accepted and, as in the reference (dg_v_cycle(1), :436), not used
+    // basis: MGB_DG_BASIS_* of the DG space; the reference's solver is written for FE_DGQHermite
+    // (LaplaceOperatorCompactCombine<dim, fe_degree, Number> with its default type 0, multigrid_solver_dg.h:700-701)
     MultigridSolverDG(const MeshDescription &mesh, const unsigned int degree_pre, const unsigned int degree_post,
-                      const unsigned int /*n_cycles*/ = 1)
+                      const unsigned int /*n_cycles*/ = 1, const int basis = MGB_DG_BASIS_GAUSS_LOBATTO)
     {
       mgb_dg_solver_options o;
       mgb_dg_solver_default_options(&o);
@@ -37,6 +39,7 @@ namespace multigrid
       o.degree_pre    = (int)degree_pre;
       o.degree_post   = (int)degree_post;
       o.device        = mesh.device;
+      o.basis         = basis;
       o.comm_rank     = mesh.comm_rank; // one process per GPU: z-slabs shared by the DG operator and the FE_Q hierarchy
       o.comm_size     = mesh.comm_size;
       for (int i = 0; i < 128; ++i)

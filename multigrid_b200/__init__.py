@@ -62,6 +62,7 @@ class DGOptions(C.Structure):
         ("comm_rank", C.c_int),
         ("comm_size", C.c_int),
         ("comm_id", C.c_ubyte * 128),
+        ("basis", C.c_int),
     ]
 
 
@@ -79,6 +80,7 @@ class DGSolverOptions(C.Structure):
         ("comm_rank", C.c_int),
         ("comm_size", C.c_int),
         ("comm_id", C.c_ubyte * 128),
+        ("basis", C.c_int),
     ]
 
 
@@ -614,13 +616,23 @@ class MultigridSolver:
         _check(lib().mgb_op_set_kernel(self.h, kernel))
 
 
+# 1-D basis of the DG space: MGB_DG_BASIS_* of include/mgb200.h; dg_basis_of_type() maps the reference's template
+# parameter `type` (laplace_operator_dg.h:346-350: 0 Hermite, 1 FE_DGQ, 2 Gauss)
+DG_BASIS_GAUSS_LOBATTO, DG_BASIS_HERMITE, DG_BASIS_GAUSS = 0, 1, 2
+
+
+def dg_basis_of_type(type_):
+    return {0: DG_BASIS_HERMITE, 1: DG_BASIS_GAUSS_LOBATTO, 2: DG_BASIS_GAUSS}[type_]
+
+
 class LaplaceOperatorDG:
-    """multigrid::LaplaceOperatorCompactCombine<3,p,Number,1> (common/laplace_operator_dg.h:360-2026): SIP-DG Laplacian
-    with FE_DGQ(p) on the affine box mesh of matvec_dg/program.cc:40-80.  Vectors are torch tensors on the
-    device, cell-wise contiguous; `precision` picks the float or the double kernels."""
+    """multigrid::LaplaceOperatorCompactCombine<3,p,Number,type> (common/laplace_operator_dg.h:360-2026): SIP-DG
+    Laplacian on the affine box mesh of matvec_dg/program.cc:40-80 with FE_DGQ(p) (default), FE_DGQHermite(p) or
+    FE_DGQArbitraryNodes(QGauss(p+1)) (`basis`).  Vectors are torch tensors on the device, cell-wise contiguous
+    coefficients of that basis; `precision` picks the float or the double kernels."""
 
     def __init__(self, degree=4, n_subdivisions=(1, 1, 1), n_refinements=0, lower=None, upper=None, trafo=None,
-                 device=0, precision=F64, comm=None):
+                 device=0, precision=F64, comm=None, basis=DG_BASIS_GAUSS_LOBATTO):
         """comm = (rank, size, unique_id bytes) for one process per GPU (comm_from_torch_distributed())"""
         import torch
         o = DGOptions()
@@ -640,6 +652,7 @@ class LaplaceOperatorDG:
         if trafo is not None:
             o.trafo[:] = [float(v) for v in np.asarray(trafo, dtype=np.float64).ravel()]
         o.device = device
+        o.basis = basis
         self.h = C.c_void_p()
         self.device = torch.device("cuda", device)
         self.precision = precision
@@ -793,8 +806,9 @@ class MultigridSolverDG:
     JACOBI, JACOBI_TRANSFORMED = 0, 1
 
     def __init__(self, degree=4, n_subdivisions=(1, 1, 1), n_refinements=3, lower=(-1.,) * 3, upper=(1.,) * 3,
-                 degree_pre=3, degree_post=3, preconditioner=1, device=0, comm=None):
-        """comm = (rank, size, unique_id bytes) for one process per GPU (comm_from_torch_distributed()): the DG
+                 degree_pre=3, degree_post=3, preconditioner=1, device=0, comm=None, basis=DG_BASIS_GAUSS_LOBATTO):
+        """basis: DG_BASIS_* (poisson_dg/program.cc:174 uses FE_DGQHermite = DG_BASIS_HERMITE).
+        comm = (rank, size, unique_id bytes) for one process per GPU (comm_from_torch_distributed()): the DG
         operator and the finest FE_Q level share the z-slabs; vectors are the local DG vectors (partition())"""
         import torch
         o = DGSolverOptions()
@@ -810,6 +824,7 @@ class MultigridSolverDG:
         o.lower[:] = list(lower)
         o.upper[:] = list(upper)
         o.degree_pre, o.degree_post, o.preconditioner, o.device = degree_pre, degree_post, preconditioner, device
+        o.basis = basis
         self.h = C.c_void_p()
         self.device = torch.device("cuda", device)
         self.degree = degree

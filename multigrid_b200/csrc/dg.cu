@@ -47,10 +47,9 @@ namespace mgb
   // matrix + cyclic Jacobi rotations.  V[k n + j] = component j of eigenvector k, eigenvalues ascending.  Sign
   // and scaling of the vectors do not matter for V D^-1 V^T with D = diag(V^T A V).
   inline std::vector<double>
-  jacobi_transformed_eigenvectors(const Basis &b)
+  jacobi_transformed_eigenvectors(const DGBasis &b)
   {
     const int                n = b.n;
-    std::vector<long double> nodes(b.nodes.begin(), b.nodes.end());
     std::vector<double>      M(n * n), A(n * n);
     const double             penalty = (double)n * n; // penalty_factor = 1 (laplace_operator_dg.h:47,198)
     for (int i = 0; i < n; ++i)
@@ -62,9 +61,8 @@ namespace mgb
               m += b.S[q * n + i] * b.S[q * n + j] * b.wq[q];
               l += b.G[q * n + i] * b.G[q * n + j] * b.wq[q];
             }
-          const double vi0 = i == 0, vj0 = j == 0, vi1 = i == n - 1, vj1 = j == n - 1;
-          const double gi0 = (double)detail::dlag(nodes, i, 0.0L), gj0 = (double)detail::dlag(nodes, j, 0.0L);
-          const double gi1 = (double)detail::dlag(nodes, i, 1.0L), gj1 = (double)detail::dlag(nodes, j, 1.0L);
+          const double vi0 = b.f0[i], vj0 = b.f0[j], vi1 = b.f1[i], vj1 = b.f1[j];
+          const double gi0 = b.e0[i], gj0 = b.e0[j], gi1 = b.e1[i], gj1 = b.e1[j];
           l += vi0 * vj0 * penalty + 0.5 * gi0 * vj0 + 0.5 * gj0 * vi0;
           l += vi1 * vj1 * penalty - 0.5 * gi1 * vj1 - 0.5 * gj1 * vi1;
           M[i * n + j] = m;
@@ -163,10 +161,9 @@ namespace mgb
 
   template <typename T, int n>
   static DGTables<T, n>
-  make_tables(const Basis &b)
+  make_tables(const DGBasis &b)
   {
     DGTables<T, n>           t;
-    std::vector<long double> nodes(b.nodes.begin(), b.nodes.end());
     for (int i = 0; i < n * n; ++i)
       {
         t.S[i] = (T)b.S[i];
@@ -175,8 +172,10 @@ namespace mgb
       }
     for (int i = 0; i < n; ++i)
       {
-        t.e0[i] = (T)detail::dlag(nodes, i, 0.0L);
-        t.e1[i] = (T)detail::dlag(nodes, i, 1.0L);
+        t.e0[i] = (T)b.e0[i];
+        t.e1[i] = (T)b.e1[i];
+        t.f0[i] = (T)b.f0[i];
+        t.f1[i] = (T)b.f1[i];
         t.w[i]  = (T)b.wq[i];
       }
     const std::vector<double> V = jacobi_transformed_eigenvectors(b);
@@ -188,7 +187,7 @@ namespace mgb
   // diagonal entries of the 1-D matrices int phi phi, int phi' phi', int phi' phi and the end derivatives
   struct DGDiagTables
   {
-    double M[9], K[9], C[9], e0[9], e1[9];
+    double M[9], K[9], C[9], e0[9], e1[9], f0[9], f1[9];
   };
 
   struct DGGeom
@@ -221,12 +220,13 @@ namespace mgb
             const double Ma = tb.M[i[da]], Mb = tb.M[i[db]], Ca = tb.C[i[da]], Cb = tb.C[i[db]];
             for (int s = 0; s < 2; ++s)
               {
-                if (i[d] != (s ? n - 1 : 0))
+                const double f = s ? tb.f1[i[d]] : tb.f0[i[d]]; // trace of the 1-D function: one node of the Gauss-Lobatto basis
+                if (f == 0.)
                   continue;
                 const bool   interior = s ? cc[d] + 1 < ncs[d] : cc[d] > 0;
                 const double sgn = s ? 1. : -1., e = s ? tb.e1[i[d]] : tb.e0[i[d]];
-                const double term =
-                  g.sigma[d] * Ma * Mb - sgn * (g.gs[d][d] * e * Ma * Mb + g.gs[d][da] * Ca * Mb + g.gs[d][db] * Ma * Cb);
+                const double term = g.sigma[d] * f * f * Ma * Mb -
+                                    sgn * f * (g.gs[d][d] * e * Ma * Mb + f * (g.gs[d][da] * Ca * Mb + g.gs[d][db] * Ma * Cb));
                 v += (interior ? 1. : 2.) * g.area[d] * term;
               }
           }
@@ -366,6 +366,52 @@ namespace mgb
       }
   }
 
+  // Change of basis of a DG vector, cell by cell: out (+)= (M x M x M) in with the 1-D matrix M (TRANSPOSE: M^T);
+  // LocalBasisTransformer<dim,1,...>::apply (laplace_operator_dg.h:106-141, 290-322) for the bases whose coefficients
+  // are not the values in the Gauss-Lobatto points.  One cell per 128 threads, three sweeps in shared memory.
+  struct DGMatrix1D
+  {
+    double m[81];
+  };
+  template <typename T, bool TRANSPOSE, bool ADD>
+  __global__ void
+  k_dg_basis_change(const int n, const size_t n_cells, const DGMatrix1D M, const T *in, T *out)
+  {
+    extern __shared__ __align__(16) unsigned char bc_smem[];
+    T        *a = reinterpret_cast<T *>(bc_smem), *b = a + n * n * n;
+    const int n2 = n * n, n3 = n2 * n;
+    for (size_t c = blockIdx.x; c < n_cells; c += gridDim.x)
+      {
+        for (int i = threadIdx.x; i < n3; i += blockDim.x)
+          a[i] = in[c * n3 + i];
+        __syncthreads();
+        for (int dir = 0; dir < 3; ++dir)
+          {
+            const int st = dir == 0 ? 1 : (dir == 1 ? n : n2);
+            for (int i = threadIdx.x; i < n3; i += blockDim.x)
+              {
+                const int r = (i / st) % n, base = i - r * st;
+                double    v = 0;
+                for (int k = 0; k < n; ++k)
+                  v += (TRANSPOSE ? M.m[k * n + r] : M.m[r * n + k]) * (double)a[base + k * st];
+                b[i] = (T)v;
+              }
+            __syncthreads();
+            T *t = a;
+            a    = b;
+            b    = t;
+          }
+        for (int i = threadIdx.x; i < n3; i += blockDim.x)
+          {
+            if (ADD)
+              out[c * n3 + i] += a[i];
+            else
+              out[c * n3 + i] = a[i];
+          }
+        __syncthreads();
+      }
+  }
+
   struct DGOperator
   {
     mgb_dg_options opt;
@@ -380,7 +426,7 @@ namespace mgb
     bool           owns_stream = true;
     cudaEvent_t    ev[2]    = {nullptr, nullptr};
     int64_t        launches = 0;
-    Basis          basis;
+    DGBasis        basis;
     DGGeom         geom;
     DGDiagTables   dtab;
     double        *scal_dev = nullptr, *scal_host = nullptr;
@@ -459,8 +505,9 @@ namespace mgb
           for (int e = 0; e < 3; ++e)
             geom.gs[d][e] = Gm[d][e] / gn[d];
         }
-      basis = make_basis(p);
-      std::vector<long double> nodes(basis.nodes.begin(), basis.nodes.end());
+      if (o.basis < DG_BASIS_GAUSS_LOBATTO || o.basis > DG_BASIS_GAUSS)
+        throw std::runtime_error("unknown DG basis");
+      basis = make_dg_basis(p, o.basis);
       for (int i = 0; i < n; ++i)
         {
           double m = 0, k = 0, c = 0;
@@ -474,8 +521,10 @@ namespace mgb
           dtab.M[i]  = m;
           dtab.K[i]  = k;
           dtab.C[i]  = c;
-          dtab.e0[i] = (double)detail::dlag(nodes, i, 0.0L);
-          dtab.e1[i] = (double)detail::dlag(nodes, i, 1.0L);
+          dtab.e0[i] = basis.e0[i];
+          dtab.e1[i] = basis.e1[i];
+          dtab.f0[i] = basis.f0[i];
+          dtab.f1[i] = basis.f1[i];
         }
       int count = 0;
       if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
@@ -678,6 +727,21 @@ namespace mgb
       return (const T *)jt_dinv[k];
     }
 
+    template <typename T, bool TRANSPOSE, bool ADD>
+    void
+    basis_change(const std::vector<double> &M, const T *in, T *out)
+    {
+      DGMatrix1D m;
+      for (int i = 0; i < n * n; ++i)
+        m.m[i] = M[i];
+      const size_t   cells  = n_dofs / ((size_t)n * n * n);
+      const unsigned blocks = (unsigned)std::min<size_t>(cells, 148 * 16);
+      k_dg_basis_change<T, TRANSPOSE, ADD>
+        <<<blocks, 128, 2 * n * n * n * sizeof(T), stream>>>(n, cells, m, in, out);
+      ++launches;
+      MGB_DG_CHECK(cudaGetLastError());
+    }
+
     void
     check_same_mesh(const LevelDesc &L) const
     {
@@ -693,7 +757,17 @@ namespace mgb
     prolongate_add_cg_to_dg(const LevelDesc &L, T *dg, const T *cg)
     {
       check_same_mesh(L);
-      k_cg_to_dg_add<T><<<grid(n_dofs), 256, 0, stream>>>(L, cg, dg);
+      if (basis.kind == DG_BASIS_GAUSS_LOBATTO)
+        k_cg_to_dg_add<T><<<grid(n_dofs), 256, 0, stream>>>(L, cg, dg);
+      else
+        { // values in the Gauss-Lobatto points of every cell, then the coefficients of the DG basis
+          if (!host_buf[1])
+            MGB_DG_CHECK(cudaMalloc(&host_buf[1], n_dofs * 8));
+          T *tmp = (T *)host_buf[1];
+          MGB_DG_CHECK(cudaMemsetAsync(tmp, 0, n_dofs * sizeof(T), stream));
+          k_cg_to_dg_add<T><<<grid(n_dofs), 256, 0, stream>>>(L, cg, tmp);
+          basis_change<T, false, true>(basis.Binv, tmp, dg);
+        }
       ++launches;
       MGB_DG_CHECK(cudaGetLastError());
     }
@@ -709,18 +783,34 @@ namespace mgb
       T *res = (T *)host_buf[0];
       apply<T>(DG_RESIDUAL, res, lhs, rhs);
       update_ghosts(res); // the first owned FE_Q plane sums over the cell layer below (compress(add) of the reference)
+      if (basis.kind != DG_BASIS_GAUSS_LOBATTO)
+        basis_change<T, true, false>(basis.Binv, res, res); // transpose of the prolongation's change of basis
       MGB_DG_CHECK(cudaMemsetAsync(restricted, 0, (size_t)L.n_dofs * sizeof(T), stream));
       k_dg_to_cg_add<T><<<grid(L.n_dofs), 256, 0, stream>>>(L, res, restricted);
       ++launches;
       MGB_DG_CHECK(cudaGetLastError());
     }
 
+    // 1-D tables of the operator's basis (kernel parameters), built once per degree, precision and basis
+    template <int P, typename T>
+    const DGTables<T, P + 1> &
+    tables() const
+    {
+      static DGTables<T, P + 1> tb[3];
+      static bool               made[3] = {false, false, false};
+      if (!made[basis.kind])
+        {
+          tb[basis.kind]   = make_tables<T, P + 1>(make_dg_basis(P, basis.kind));
+          made[basis.kind] = true;
+        }
+      return tb[basis.kind];
+    }
+
     template <int P, typename T>
     void
     launch_jt(const DGArgs<T> &A, const T scale)
     {
-      static const DGTables<T, P + 1> tb = make_tables<T, P + 1>(make_basis(P));
-      launch_dg_jacobi_transformed<P, T>(A, tb, scale, stream);
+      launch_dg_jacobi_transformed<P, T>(A, tables<P, T>(), scale, stream);
     }
 
     // dst = scale * P^-1 src with the selected preconditioner (JacobiTransformed::vmult, :2046-2083, or point Jacobi)
@@ -766,8 +856,10 @@ namespace mgb
     void
     launch(const DGArgs<T> &A)
     {
-      static const DGTables<T, P + 1> tb = make_tables<T, P + 1>(make_basis(P));
-      launch_dg_apply<P, T>(A, tb, stream);
+      if (basis.kind == DG_BASIS_GAUSS_LOBATTO)
+        launch_dg_apply<P, T, false>(A, tables<P, T>(), stream);
+      else
+        launch_dg_apply<P, T, true>(A, tables<P, T>(), stream);
     }
 
     template <typename T>

@@ -38,6 +38,7 @@ namespace mgb
     T G[n * n]; // phi_i'(x_q)
     T D[n * n]; // D[q n + r] = l_r'(x_q)
     T e0[n], e1[n]; // phi_i'(0), phi_i'(1)
+    T f0[n], f1[n]; // phi_i(0), phi_i(1): unit vectors for the Gauss-Lobatto basis (kernel variant GEN = false)
     T w[n];
     T V[n * n]; // V[k n + j] = component j of the k-th generalised eigenvector of (1-D SIP Laplace, 1-D mass)
   };
@@ -227,7 +228,11 @@ namespace mgb
         A.dst[(size_t)c * n3 + i] = scale * r[i];
   }
 
-  template <int p, typename T>
+  // GEN = false: nodal basis with a node on each end point (FE_DGQ on the Gauss-Lobatto points): the trace of a pencil
+  // is its end value.  GEN = true: any tensor-product basis (FE_DGQHermite, FE_DGQArbitraryNodes(QGauss)); traces and
+  // their transposes go through the tables f0 / f1 (laplace_operator_dg.h:1179-1199, 1359-1389 use the structure of
+  // each basis instead; the result is the same operator in that basis).
+  template <int p, typename T, bool GEN>
   __global__ void
   __launch_bounds__(DGCfg<p>::NT) k_dg_apply(const DGArgs<T> A, const DGTables<T, p + 1> Tb)
   {
@@ -417,11 +422,16 @@ namespace mgb
             for (int s = 0; s < 2; ++s)
               {
                 const T *eK = s ? Tb.e1 : Tb.e0, *eN = s ? Tb.e0 : Tb.e1;
-                const T  tK = s ? own[n - 1] : own[0];
+                const T *fK = s ? Tb.f1 : Tb.f0, *fN = s ? Tb.f0 : Tb.f1;
+                T        tK = GEN ? T(0) : (s ? own[n - 1] : own[0]);
                 T        dK = 0;
 #pragma unroll
                 for (int l = 0; l < n; ++l)
-                  dK += eK[l] * own[l];
+                  {
+                    dK += eK[l] * own[l];
+                    if (GEN)
+                      tK += fK[l] * own[l];
+                  }
                 const bool interior = s ? (cd + 1 < A.nc[d]) : (cd > 0);
                 T          jump, dsum, tsum;
                 if (interior)
@@ -433,7 +443,9 @@ namespace mgb
                       {
                         const T v = __ldg(nb + l * sd);
                         dN += eN[l] * v;
-                        if (l == (s ? 0 : n - 1))
+                        if (GEN)
+                          tN += fN[l] * v;
+                        else if (l == (s ? 0 : n - 1))
                           tN = v;
                       }
                     jump = tK - tN;
@@ -537,11 +549,12 @@ namespace mgb
                     N += Sv * h1;
                   }
                 N *= g_dd;
-                const T *eK = s ? Tb.e1 : Tb.e0;
+                const T *eK = s ? Tb.e1 : Tb.e0, *fK = s ? Tb.f1 : Tb.f0;
 #pragma unroll
                 for (int l = 0; l < n; ++l)
-                  yd[l] += N * eK[l];
-                yd[s ? n - 1 : 0] += V;
+                  yd[l] += GEN ? N * eK[l] + V * fK[l] : N * eK[l];
+                if (!GEN)
+                  yd[s ? n - 1 : 0] += V;
               }
 #pragma unroll
             for (int l = 0; l < n; ++l)
@@ -599,7 +612,7 @@ namespace mgb
       }
   }
 
-  template <int p, typename T>
+  template <int p, typename T, bool GEN>
   void
   launch_dg_apply(const DGArgs<T> &A, const DGTables<T, p + 1> &Tb, cudaStream_t stream)
   {
@@ -608,11 +621,11 @@ namespace mgb
     static bool  first = true;
     if (first)
       {
-        cudaFuncSetAttribute(k_dg_apply<p, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(k_dg_apply<p, T, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         first = false;
       }
     const unsigned blocks = (A.n_cells + C::CPB - 1) / C::CPB;
-    k_dg_apply<p, T><<<blocks, C::NT, smem, stream>>>(A, Tb);
+    k_dg_apply<p, T, GEN><<<blocks, C::NT, smem, stream>>>(A, Tb);
   }
 
   template <int p, typename T>

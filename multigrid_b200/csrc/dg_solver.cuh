@@ -311,6 +311,7 @@ namespace mgb
           dopt.trafo[4 * k]      = 1.;
         }
       dopt.device    = opt.device;
+      dopt.basis     = opt.basis;
       dopt.comm_rank = opt.comm_rank;
       dopt.comm_size = opt.comm_size > 1 ? opt.comm_size : 1;
       // one process per GPU: the DG operator shares the z-slabs and the NCCL communicator of the FE_Q hierarchy

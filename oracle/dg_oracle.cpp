@@ -31,6 +31,7 @@ namespace
     orc::Basis1D b;
     std::vector<double> S, G;   // [q][i] values / derivatives at the Gauss points
     std::vector<double> e0, e1; // phi_i'(0), phi_i'(1)
+    std::vector<double> f0, f1; // phi_i(0), phi_i(1)
     long   ncells, ndofs;
   };
 
@@ -112,6 +113,10 @@ extern "C"
     std::vector<long double> nodes(g->b.gll.begin(), g->b.gll.end());
     g->e0.resize(g->n);
     g->e1.resize(g->n);
+    g->f0.assign(g->n, 0.);
+    g->f1.assign(g->n, 0.);
+    g->f0[0]        = 1;
+    g->f1[g->n - 1] = 1;
     for (int i = 0; i < g->n; ++i)
       {
         g->e0[i] = (double)orc::lagrange_deriv(nodes, i, 0.0L);
@@ -120,6 +125,23 @@ extern "C"
     g->ncells = (long)ncell[0] * ncell[1] * ncell[2];
     g->ndofs  = g->ncells * g->n * g->n * g->n;
     return g;
+  }
+
+  // Another 1-D basis of the same polynomial space (FE_DGQHermite, FE_DGQArbitraryNodes(QGauss): template parameter
+  // `type` of LaplaceOperatorCompactCombine, laplace_operator_dg.h:346-350; matvec_dg/program.cc:44-49): the tables
+  // S[q n + i] = phi_i(x_q), G = phi_i'(x_q), f0/f1 = phi_i(0/1), e0/e1 = phi_i'(0/1) come from oracle/orc.py
+  void
+  dgo_set_basis(void *h, const double *S, const double *G, const double *f0, const double *f1, const double *e0,
+                const double *e1)
+  {
+    DG       *g = static_cast<DG *>(h);
+    const int n = g->n;
+    g->S.assign(S, S + n * n);
+    g->G.assign(G, G + n * n);
+    g->f0.assign(f0, f0 + n);
+    g->f1.assign(f1, f1 + n);
+    g->e0.assign(e0, e0 + n);
+    g->e1.assign(e1, e1 + n);
   }
 
   void dgo_destroy(void *h) { delete static_cast<DG *>(h); }
@@ -140,9 +162,7 @@ extern "C"
     const DG &g  = *static_cast<DG *>(h);
     const int n  = g.n, n3 = n * n * n;
     std::memset(dst, 0, sizeof(double) * g.ndofs);
-    std::vector<double> v0(n, 0.), v1(n, 0.);
-    v0[0]     = 1;
-    v1[n - 1] = 1;
+    const std::vector<double> &v0 = g.f0, &v1 = g.f1;
     // ---- cells (laplace_operator_dg_face.h:58-77)
 #pragma omp parallel for
     for (long c = 0; c < g.ncells; ++c)

@@ -64,6 +64,7 @@ def lib():
         L.dgo_create.restype = C.c_void_p
         L.dgo_create.argtypes = [C.c_int, ip, dp, dp, dp]
         L.dgo_destroy.argtypes = [C.c_void_p]
+        L.dgo_set_basis.argtypes = [C.c_void_p] + [dp] * 6
         L.dgo_n_dofs.restype = C.c_longlong
         L.dgo_n_dofs.argtypes = [C.c_void_p]
         L.dgo_penalty.argtypes = [C.c_void_p, dp]
@@ -83,6 +84,76 @@ def basis(p):
     gll, xq, wq = (np.zeros(n) for _ in range(3))
     lib().orc_basis(p, _dp(S), _dp(G), _dp(D), _dp(P1), _dp(gll), _dp(xq), _dp(wq))
     return dict(S=S, G=G, D=D, P1=P1, gll=gll, xq=xq, wq=wq)
+
+
+DG_BASIS_GAUSS_LOBATTO, DG_BASIS_HERMITE, DG_BASIS_GAUSS = 0, 1, 2   # reference `type` 1, 0, 2
+
+
+def _hermite_like_roots(p):
+    """Polynomials::HermiteLikeInterpolation of deal.II (1-D basis of FE_DGQHermite; call sites
+    poisson_dg/program.cc:174, matvec_dg/program.cc:44-45), restated from its definition: every function in
+    product form w prod (x - r_k).  phi_0 / phi_1 carry value / derivative at 0 (phi_0(0) = 1, phi_0'(0) + phi_1'(0) = 0,
+    int phi_0 phi_1 = 0 fixes the extra root x* of phi_0), phi_p / phi_{p-1} mirror them, the interior functions have
+    double roots at both ends and are 1 at one root of the Jacobi polynomial P^(4,4)_{p-3} (scipy.special.roots_jacobi)
+    and 0 at the others.  deal.II itself is not available here: PARITY UNPINNED for the Hermite coefficients, the
+    space and the operator are pinned by the change-of-basis tests (tests/test_dg_basis.py)."""
+    if p == 1:
+        return [([1.], -1.), ([0.], 1.)]
+    if p == 2:
+        return [([1., 1.], 1.), ([0., 1.], -2.), ([0., 0.], 1.)]
+    jr = []
+    if p > 3:
+        import scipy.special
+        jr = list(0.5 * (scipy.special.roots_jacobi(p - 3, 4, 4)[0] + 1.))
+    # int_0^1 x (x - x*) common^2 = 0 with the shared factor common = prod (x - r_j) (x - 1)^2 of phi_0 and phi_1,
+    # integrated with numpy's Gauss-Legendre rule on p + 2 points (exact)
+    xg, wg = np.polynomial.legendre.leggauss(p + 2)
+    xg, wg = 0.5 * (xg + 1.), 0.5 * wg
+    c2 = xg * np.prod([(xg - rk) ** 2 for rk in jr + [1., 1.]], axis=0)
+    xs = np.sum(wg * xg * c2) / np.sum(wg * c2)
+    val = lambda r, w, x: w * np.prod([x - rk for rk in r])
+    der = lambda r, w, x: w * sum(np.prod([x - r[k] for k in range(len(r)) if k != m]) for m in range(len(r)))
+    r0, r1 = [xs] + jr + [1., 1.], [0.] + jr + [1., 1.]
+    w0 = 1. / val(r0, 1., 0.)
+    w1 = -der(r0, w0, 0.) / der(r1, 1., 0.)
+    out = [(r0, w0), (r1, w1)]
+    for i in range(2, p - 1):
+        r = [0., 0.] + [jr[j] for j in range(p - 3) if j != i - 2] + [1., 1.]
+        out.append((r, 1. / val(r, 1., jr[i - 2])))
+    sign = -1. if p % 2 else 1.
+    out.append(([1. - rk for rk in r1], w1 * sign))
+    out.append(([1. - rk for rk in r0], w0 * sign))
+    return out
+
+
+def dg_basis(p, kind=DG_BASIS_GAUSS_LOBATTO):
+    """1-D tables of a DG basis: S[q, i] = phi_i(x_q), G = phi_i'(x_q) at the Gauss points, f0/f1 = phi_i(0/1),
+    e0/e1 = phi_i'(0/1), B[j, i] = phi_i(Gauss-Lobatto point j)"""
+    b = basis(p)
+    n = p + 1
+    if kind == DG_BASIS_HERMITE:
+        polys = _hermite_like_roots(p)
+    else:
+        x = b["gll"] if kind == DG_BASIS_GAUSS_LOBATTO else b["xq"]
+        polys = [([x[l] for l in range(n) if l != i], 1. / np.prod([x[i] - x[l] for l in range(n) if l != i]))
+                 for i in range(n)]
+
+    def val(i, x):
+        r, w = polys[i]
+        return w * np.prod([x - rk for rk in r])
+
+    def der(i, x):
+        r, w = polys[i]
+        return w * sum(np.prod([x - r[k] for k in range(len(r)) if k != m]) for m in range(len(r)))
+    t = dict(xq=b["xq"], wq=b["wq"], gll=b["gll"], kind=kind)
+    t["S"] = np.array([[val(i, x) for i in range(n)] for x in b["xq"]])
+    t["G"] = np.array([[der(i, x) for i in range(n)] for x in b["xq"]])
+    t["B"] = np.array([[val(i, x) for i in range(n)] for x in b["gll"]])
+    t["f0"], t["f1"] = np.array([val(i, 0.) for i in range(n)]), np.array([val(i, 1.) for i in range(n)])
+    t["e0"], t["e1"] = np.array([der(i, 0.) for i in range(n)]), np.array([der(i, 1.) for i in range(n)])
+    for k in ("S", "G", "B", "f0", "f1", "e0", "e1"):
+        t[k] = np.ascontiguousarray(np.where(np.abs(t[k]) < 1e-15, 0., t[k]))
+    return t
 
 
 VEC_SOLUTION, VEC_RHS, VEC_INV_DIAG, VEC_UPDATE, VEC_RESIDUAL, VEC_DEFECT, VEC_CHEB_GUESS = range(7)
@@ -231,8 +302,9 @@ class DGOperator:
     """SIP-DG Laplacian of laplace_operator_dg_face.h on the affine box mesh of matvec_dg/program.cc;
     DoFs cell-wise contiguous, cells lexicographic (x fastest)."""
 
-    def __init__(self, degree, ncell, lower=DG_LOWER, upper=DG_UPPER, trafo=None):
+    def __init__(self, degree, ncell, lower=DG_LOWER, upper=DG_UPPER, trafo=None, basis=DG_BASIS_GAUSS_LOBATTO):
         self.degree, self.ncell = degree, tuple(ncell)
+        self.tables = dg_basis(degree, basis)
         self.trafo = dg_trafo() if trafo is None else np.ascontiguousarray(trafo, dtype=np.float64)
         nc = (C.c_int * 3)(*ncell)
         lo = (C.c_double * 3)(*lower)
@@ -241,6 +313,9 @@ class DGOperator:
         self.h = lib().dgo_create(degree, nc, lo, hi, _dp(self.trafo))
         if not self.h:
             raise ValueError("unsupported degree")
+        if basis != DG_BASIS_GAUSS_LOBATTO:
+            t = self.tables
+            lib().dgo_set_basis(self.h, _dp(t["S"]), _dp(t["G"]), _dp(t["f0"]), _dp(t["f1"]), _dp(t["e0"]), _dp(t["e1"]))
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -305,25 +380,12 @@ class JacobiTransformed:
         self.op = op
         p = op.degree
         n = p + 1
-        b = basis(p)
-        S, G, w, nodes = b["S"], b["G"], b["wq"], b["gll"]
-
-        def dl(i, x):
-            s = 0.0
-            for m in range(n):
-                if m != i:
-                    v = 1.0 / (nodes[i] - nodes[m])
-                    for l in range(n):
-                        if l != i and l != m:
-                            v *= (x - nodes[l]) / (nodes[i] - nodes[l])
-                    s += v
-            return s
+        b = op.tables
+        S, G, w = b["S"], b["G"], b["wq"]
         mass = S.T @ np.diag(w) @ S
         lapl = G.T @ np.diag(w) @ G
         pen = float(n * n)  # penalty_factor = 1
-        v0, v1 = np.eye(n)[0], np.eye(n)[p]
-        g0 = np.array([dl(i, 0.0) for i in range(n)])
-        g1 = np.array([dl(i, 1.0) for i in range(n)])
+        v0, v1, g0, g1 = b["f0"], b["f1"], b["e0"], b["e1"]
         lapl = lapl + pen * np.outer(v0, v0) + 0.5 * (np.outer(g0, v0) + np.outer(v0, g0))
         lapl = lapl + pen * np.outer(v1, v1) - 0.5 * (np.outer(g1, v1) + np.outer(v1, g1))
         self.eigenvalues, vecs = scipy.linalg.eigh(lapl, mass)
@@ -420,7 +482,7 @@ class MultigridSolverDG:
     the cycle in float); small meshes only."""
 
     def __init__(self, degree, n_subdivisions, n_refine, lower=(-1.,) * 3, upper=(1.,) * 3, degree_pre=3,
-                 degree_post=3, preconditioner=1):
+                 degree_post=3, preconditioner=1, basis=DG_BASIS_GAUSS_LOBATTO):
         if isinstance(n_subdivisions, int):
             n_subdivisions = (n_subdivisions,) * 3
         assert degree_pre == degree_post
@@ -430,7 +492,10 @@ class MultigridSolverDG:
         if L > 0:
             self.fe.smoother_reinit(L, 20., max(1, degree_pre - 1), 15)
         nc = [k << n_refine for k in n_subdivisions]
-        self.op = DGOperator(degree, nc, lower=lower, upper=upper, trafo=np.eye(3))
+        self.op = DGOperator(degree, nc, lower=lower, upper=upper, trafo=np.eye(3), basis=basis)
+        # LocalBasisTransformer<dim,1,...> (laplace_operator_dg.h:106-141): DG coefficients from the values in the
+        # Gauss-Lobatto points of FE_Q (the identity for FE_DGQ)
+        self.Binv = np.linalg.inv(self.op.tables["B"])
         if preconditioner == 1:
             self.jt = JacobiTransformed(self.op)
             self.prec = self.jt.vmult
@@ -447,7 +512,7 @@ class MultigridSolverDG:
         mask[0], mask[-1], mask[:, 0], mask[:, -1], mask[:, :, 0], mask[:, :, -1] = (0,) * 6
         self.mask = mask.ravel()
         # rhs_i = (f, phi_i) with QGauss(p+1)   (multigrid_solver_dg.h:243-265)
-        b = basis(p)
+        b = self.op.tables
         S, xq, wq = b["S"], b["xq"], b["wq"]
         h = [(upper[d] - lower[d]) / nc[d] for d in range(3)]
         self.h, self.nc, self.lower = h, nc, lower
@@ -469,10 +534,15 @@ class MultigridSolverDG:
         x = self.smooth.vmult(src)
         res = src - self.op.vmult(x)
         d = np.zeros(self.mask.size)
-        np.add.at(d, self.lex, res)
+        np.add.at(d, self.lex, self._basis_change(res, self.Binv.T))       # action 1 epilogue, :1798-1819
         u = self.fe.vcycle(d * self.mask)
-        x = x + (u * self.mask)[self.lex]
+        x = x + self._basis_change((u * self.mask)[self.lex], self.Binv)    # prolongate_add_cg_to_dg, :1863-1894
         return self.smooth.step(x, src)
+
+    def _basis_change(self, v, M):
+        n = self.op.degree + 1
+        r = np.asarray(v).reshape(-1, n, n, n)
+        return np.einsum("kz,jy,ix,czyx->ckji", M, M, M, r).ravel()
 
     def solve_cg(self, tolerance=1e-3):
         """SolverCG with ReductionControl(100, 1e-16, tolerance) (:410-424) -> (estimate, rate, residual history)"""
