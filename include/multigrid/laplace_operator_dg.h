@@ -56,7 +56,7 @@ namespace multigrid
     std::size_t n_    = 0;
   };
 
-  template <int dim, int fe_degree, typename Number, int type = 1>
+  template <int dim, int fe_degree, typename Number, int type = 0>
   class LaplaceOperatorCompactCombine
   {
     static_assert(dim == 3 && type >= 0 && type <= 2, "3-D, type 0 (Hermite), 1 (Gauss-Lobatto) or 2 (Gauss)");

@@ -21,10 +21,11 @@ namespace multigrid
 
   public:
     // multigrid_solver_dg.h:59-65; n_cycles is accepted and, as in the reference (dg_v_cycle(1), :436), not used
-    // basis: MGB_DG_BASIS_* of the DG space; the reference's solver is written for FE_DGQHermite
-    // (LaplaceOperatorCompactCombine<dim, fe_degree, Number> with its default type 0, multigrid_solver_dg.h:700-701)
+    // basis: MGB_DG_BASIS_* of the DG space; the default is the reference's: its solver runs on FE_DGQHermite
+    // (LaplaceOperatorCompactCombine<dim, fe_degree, Number> with the default type 0, multigrid_solver_dg.h:700-701;
+    // poisson_dg/program.cc:174), so right-hand side and solution are coefficients of that basis
     MultigridSolverDG(const MeshDescription &mesh, const unsigned int degree_pre, const unsigned int degree_post,
-                      const unsigned int /*n_cycles*/ = 1, const int basis = MGB_DG_BASIS_GAUSS_LOBATTO)
+                      const unsigned int /*n_cycles*/ = 1, const int basis = MGB_DG_BASIS_HERMITE)
     {
       mgb_dg_solver_options o;
       mgb_dg_solver_default_options(&o);

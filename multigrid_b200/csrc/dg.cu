@@ -373,42 +373,52 @@ namespace mgb
   {
     double m[81];
   };
-  template <typename T, bool TRANSPOSE, bool ADD>
+  template <int n, typename T, bool TRANSPOSE, bool ADD>
   __global__ void
-  k_dg_basis_change(const int n, const size_t n_cells, const DGMatrix1D M, const T *in, T *out)
+  __launch_bounds__(128) k_dg_basis_change(const size_t n_cells, const DGMatrix1D M, const T *in, T *out)
   {
-    extern __shared__ __align__(16) unsigned char bc_smem[];
-    T        *a = reinterpret_cast<T *>(bc_smem), *b = a + n * n * n;
-    const int n2 = n * n, n3 = n2 * n;
-    for (size_t c = blockIdx.x; c < n_cells; c += gridDim.x)
+    constexpr int n2 = n * n, n3 = n2 * n;
+    __shared__ T  buf[2][n3];
+    const size_t  c = blockIdx.x;
+    if (c >= n_cells)
+      return;
+    for (int i = threadIdx.x; i < n3; i += 128)
+      buf[0][i] = in[c * n3 + i];
+    __syncthreads();
+    // pencil-wise sweeps: a thread owns the n values of a line along the sweep direction
+#pragma unroll
+    for (int dir = 0; dir < 3; ++dir)
       {
-        for (int i = threadIdx.x; i < n3; i += blockDim.x)
-          a[i] = in[c * n3 + i];
-        __syncthreads();
-        for (int dir = 0; dir < 3; ++dir)
+        const T *a  = buf[dir & 1];
+        T       *b  = buf[(dir + 1) & 1];
+        const int st = dir == 0 ? 1 : (dir == 1 ? n : n2);
+        for (int l = threadIdx.x; l < n2; l += 128)
           {
-            const int st = dir == 0 ? 1 : (dir == 1 ? n : n2);
-            for (int i = threadIdx.x; i < n3; i += blockDim.x)
+            // the two indices across the sweep direction
+            const int u = l % n, v = l / n;
+            const int base = dir == 0 ? (v * n + u) * n : (dir == 1 ? v * n2 + u : v * n + u);
+            T         x[n];
+#pragma unroll
+            for (int k = 0; k < n; ++k)
+              x[k] = a[base + k * st];
+#pragma unroll
+            for (int r = 0; r < n; ++r)
               {
-                const int r = (i / st) % n, base = i - r * st;
-                double    v = 0;
+                double s = 0;
+#pragma unroll
                 for (int k = 0; k < n; ++k)
-                  v += (TRANSPOSE ? M.m[k * n + r] : M.m[r * n + k]) * (double)a[base + k * st];
-                b[i] = (T)v;
+                  s += (TRANSPOSE ? M.m[k * n + r] : M.m[r * n + k]) * (double)x[k];
+                b[base + r * st] = (T)s;
               }
-            __syncthreads();
-            T *t = a;
-            a    = b;
-            b    = t;
-          }
-        for (int i = threadIdx.x; i < n3; i += blockDim.x)
-          {
-            if (ADD)
-              out[c * n3 + i] += a[i];
-            else
-              out[c * n3 + i] = a[i];
           }
         __syncthreads();
+      }
+    for (int i = threadIdx.x; i < n3; i += 128)
+      {
+        if (ADD)
+          out[c * n3 + i] += buf[1][i];
+        else
+          out[c * n3 + i] = buf[1][i];
       }
   }
 
@@ -734,10 +744,15 @@ namespace mgb
       DGMatrix1D m;
       for (int i = 0; i < n * n; ++i)
         m.m[i] = M[i];
-      const size_t   cells  = n_dofs / ((size_t)n * n * n);
-      const unsigned blocks = (unsigned)std::min<size_t>(cells, 148 * 16);
-      k_dg_basis_change<T, TRANSPOSE, ADD>
-        <<<blocks, 128, 2 * n * n * n * sizeof(T), stream>>>(n, cells, m, in, out);
+      const size_t cells = n_dofs / ((size_t)n * n * n);
+      switch (n)
+        {
+#define MGB_BC(N) \
+  case N: k_dg_basis_change<N, T, TRANSPOSE, ADD><<<(unsigned)cells, 128, 0, stream>>>(cells, m, in, out); break;
+          MGB_BC(2) MGB_BC(3) MGB_BC(4) MGB_BC(5) MGB_BC(6) MGB_BC(7) MGB_BC(8) MGB_BC(9)
+#undef MGB_BC
+          default: throw std::runtime_error("unsupported degree");
+        }
       ++launches;
       MGB_DG_CHECK(cudaGetLastError());
     }
@@ -856,10 +871,13 @@ namespace mgb
     void
     launch(const DGArgs<T> &A)
     {
+      static const bool generic_only = std::getenv("MGB200_DG_GENERIC") != nullptr; // A/B switch of the timing tools
       if (basis.kind == DG_BASIS_GAUSS_LOBATTO)
-        launch_dg_apply<P, T, false>(A, tables<P, T>(), stream);
+        launch_dg_apply<P, T, 0>(A, tables<P, T>(), stream);
+      else if (basis.kind == DG_BASIS_GAUSS && !generic_only)
+        launch_dg_apply<P, T, 2>(A, tables<P, T>(), stream);
       else
-        launch_dg_apply<P, T, true>(A, tables<P, T>(), stream);
+        launch_dg_apply<P, T, 1>(A, tables<P, T>(), stream);
     }
 
     template <typename T>

@@ -232,10 +232,14 @@ namespace mgb
   // is its end value.  GEN = true: any tensor-product basis (FE_DGQHermite, FE_DGQArbitraryNodes(QGauss)); traces and
   // their transposes go through the tables f0 / f1 (laplace_operator_dg.h:1179-1199, 1359-1389 use the structure of
   // each basis instead; the result is the same operator in that basis).
-  template <int p, typename T, bool GEN>
+  // KIND = 2: generic traces and S = I (basis collocated with the Gauss points, FE_DGQArbitraryNodes(QGauss)): the six
+  // interpolation sweeps of the cell term and the S-sums of the face stages drop out (laplace_operator_dg.h:1179).
+  template <int p, typename T, int KIND>
   __global__ void
   __launch_bounds__(DGCfg<p>::NT) k_dg_apply(const DGArgs<T> A, const DGTables<T, p + 1> Tb)
   {
+    constexpr bool GEN    = KIND != 0;
+    constexpr bool COLLOC = KIND == 2;
     using C           = DGCfg<p>;
     constexpr int n   = C::n;
     constexpr int n2  = C::n2;
@@ -279,6 +283,9 @@ namespace mgb
     T yz[n]; // result pencil along z at (i,j) = (a,b)
     {
       T in[n], out[n];
+      const T *uq = COLLOC ? u_s : w0; // values at the Gauss points
+      if (!COLLOC)
+      {
       if (active)
         { // interpolate along z, thread (i,j)
 #pragma unroll
@@ -312,27 +319,28 @@ namespace mgb
             w0[(b * n + a) * n + i] = out[i];
         }
       cell_sync<TPC>(slot);
+      }
       // reference gradient at the Gauss points: gx -> w1, gy -> w2, gz in registers of thread (i,j)
       T gz[n];
       if (active)
         {
 #pragma unroll
           for (int i = 0; i < n; ++i)
-            in[i] = w0[(b * n + a) * n + i];
+            in[i] = uq[(b * n + a) * n + i];
           prod<n>(Tb.D, in, out);
 #pragma unroll
           for (int i = 0; i < n; ++i)
             w1[(b * n + a) * n + i] = out[i];
 #pragma unroll
           for (int j = 0; j < n; ++j)
-            in[j] = w0[(b * n + j) * n + a];
+            in[j] = uq[(b * n + j) * n + a];
           prod<n>(Tb.D, in, out);
 #pragma unroll
           for (int j = 0; j < n; ++j)
             w2[(b * n + j) * n + a] = out[j];
 #pragma unroll
           for (int k = 0; k < n; ++k)
-            in[k] = w0[k * n2 + b * n + a];
+            in[k] = uq[k * n2 + b * n + a];
           prod<n>(Tb.D, in, gz);
         }
       cell_sync<TPC>(slot);
@@ -375,29 +383,48 @@ namespace mgb
 #pragma unroll
           for (int i = 0; i < n; ++i)
             in[i] = w0[(b * n + a) * n + i] + out[i];
-          tprod<n>(Tb.S, in, out);
+          if (COLLOC)
+            {
+#pragma unroll
+              for (int i = 0; i < n; ++i)
+                out[i] = in[i];
+            }
+          else
+            tprod<n>(Tb.S, in, out);
 #pragma unroll
           for (int i = 0; i < n; ++i)
             w1[(b * n + a) * n + i] = out[i];
         }
       cell_sync<TPC>(slot);
-      if (active)
-        { // S^T along y, thread (i,k)
+      if (COLLOC)
+        {
+          if (active)
+            { // the result pencil along z, thread (i,j)
 #pragma unroll
-          for (int j = 0; j < n; ++j)
-            in[j] = w1[(b * n + j) * n + a];
-          tprod<n>(Tb.S, in, out);
-#pragma unroll
-          for (int j = 0; j < n; ++j)
-            w2[(b * n + j) * n + a] = out[j];
+              for (int k = 0; k < n; ++k)
+                yz[k] = w1[k * n2 + b * n + a];
+            }
         }
-      cell_sync<TPC>(slot);
-      if (active)
-        { // S^T along z, thread (i,j)
+      else
+        {
+          if (active)
+            { // S^T along y, thread (i,k)
 #pragma unroll
-          for (int k = 0; k < n; ++k)
-            in[k] = w2[k * n2 + b * n + a];
-          tprod<n>(Tb.S, in, yz);
+              for (int j = 0; j < n; ++j)
+                in[j] = w1[(b * n + j) * n + a];
+              tprod<n>(Tb.S, in, out);
+#pragma unroll
+              for (int j = 0; j < n; ++j)
+                w2[(b * n + j) * n + a] = out[j];
+            }
+          cell_sync<TPC>(slot);
+          if (active)
+            { // S^T along z, thread (i,j)
+#pragma unroll
+              for (int k = 0; k < n; ++k)
+                in[k] = w2[k * n2 + b * n + a];
+              tprod<n>(Tb.S, in, yz);
+            }
         }
     }
 
@@ -441,6 +468,8 @@ namespace mgb
 #pragma unroll
                     for (int l = 0; l < n; ++l)
                       {
+                        if (GEN && fN[l] == T(0) && eN[l] == T(0))
+                          continue; // FE_DGQHermite: two layers of the neighbour (laplace_operator_dg.h:565,1015)
                         const T v = __ldg(nb + l * sd);
                         dN += eN[l] * v;
                         if (GEN)
@@ -470,15 +499,27 @@ namespace mgb
             for (int s = 0; s < 2; ++s)
               {
                 T sj = 0, sds = 0, sts = 0, gts = 0;
-#pragma unroll
-                for (int i = 0; i < n; ++i)
+                if (COLLOC)
                   {
-                    const T Sv = S_s[a * n + i], Gv = G_s[a * n + i];
-                    sj += Sv * F[(3 * s + 0) * n2 + b * n + i];
-                    sds += Sv * F[(3 * s + 1) * n2 + b * n + i];
-                    const T tv = F[(3 * s + 2) * n2 + b * n + i];
-                    sts += Sv * tv;
-                    gts += Gv * tv;
+                    sj  = F[(3 * s + 0) * n2 + t];
+                    sds = F[(3 * s + 1) * n2 + t];
+                    sts = F[(3 * s + 2) * n2 + t];
+#pragma unroll
+                    for (int i = 0; i < n; ++i)
+                      gts += G_s[a * n + i] * F[(3 * s + 2) * n2 + b * n + i];
+                  }
+                else
+                  {
+#pragma unroll
+                    for (int i = 0; i < n; ++i)
+                      {
+                        const T Sv = S_s[a * n + i], Gv = G_s[a * n + i];
+                        sj += Sv * F[(3 * s + 0) * n2 + b * n + i];
+                        sds += Sv * F[(3 * s + 1) * n2 + b * n + i];
+                        const T tv = F[(3 * s + 2) * n2 + b * n + i];
+                        sts += Sv * tv;
+                        gts += Gv * tv;
+                      }
                   }
                 H[(4 * s + 0) * n2 + t] = sj;
                 H[(4 * s + 1) * n2 + t] = sds;
@@ -494,14 +535,26 @@ namespace mgb
             for (int s = 0; s < 2; ++s)
               {
                 T J = 0, DS = 0, T1 = 0, T2 = 0;
-#pragma unroll
-                for (int i = 0; i < n; ++i)
+                if (COLLOC)
                   {
-                    const T Sv = S_s[b * n + i], Gv = G_s[b * n + i];
-                    J += Sv * H[(4 * s + 0) * n2 + i * n + a];
-                    DS += Sv * H[(4 * s + 1) * n2 + i * n + a];
-                    T2 += Gv * H[(4 * s + 2) * n2 + i * n + a];
-                    T1 += Sv * H[(4 * s + 3) * n2 + i * n + a];
+                    J  = H[(4 * s + 0) * n2 + t];
+                    DS = H[(4 * s + 1) * n2 + t];
+                    T1 = H[(4 * s + 3) * n2 + t];
+#pragma unroll
+                    for (int i = 0; i < n; ++i)
+                      T2 += G_s[b * n + i] * H[(4 * s + 2) * n2 + i * n + a];
+                  }
+                else
+                  {
+#pragma unroll
+                    for (int i = 0; i < n; ++i)
+                      {
+                        const T Sv = S_s[b * n + i], Gv = G_s[b * n + i];
+                        J += Sv * H[(4 * s + 0) * n2 + i * n + a];
+                        DS += Sv * H[(4 * s + 1) * n2 + i * n + a];
+                        T2 += Gv * H[(4 * s + 2) * n2 + i * n + a];
+                        T1 += Sv * H[(4 * s + 3) * n2 + i * n + a];
+                      }
                   }
                 const T sgn = s ? T(1) : T(-1);
                 const T m   = sgn * (g_dd * DS + g_da * T1 + g_db * T2);
@@ -516,14 +569,25 @@ namespace mgb
             for (int s = 0; s < 2; ++s)
               {
                 T a1 = 0, a2 = 0, a3 = 0;
-#pragma unroll
-                for (int q = 0; q < n; ++q)
+                if (COLLOC)
                   {
-                    const T Sv = S_s[q * n + b], Gv = G_s[q * n + b];
-                    const T r1 = F[(3 * s + 0) * n2 + q * n + a], r2 = F[(3 * s + 1) * n2 + q * n + a];
-                    a1 += Sv * r1;
-                    a2 += Sv * r2;
-                    a3 += Gv * r2;
+                    a1 = F[(3 * s + 0) * n2 + t];
+                    a2 = F[(3 * s + 1) * n2 + t];
+#pragma unroll
+                    for (int q = 0; q < n; ++q)
+                      a3 += G_s[q * n + b] * F[(3 * s + 1) * n2 + q * n + a];
+                  }
+                else
+                  {
+#pragma unroll
+                    for (int q = 0; q < n; ++q)
+                      {
+                        const T Sv = S_s[q * n + b], Gv = G_s[q * n + b];
+                        const T r1 = F[(3 * s + 0) * n2 + q * n + a], r2 = F[(3 * s + 1) * n2 + q * n + a];
+                        a1 += Sv * r1;
+                        a2 += Sv * r2;
+                        a3 += Gv * r2;
+                      }
                   }
                 H[(4 * s + 0) * n2 + t] = a1 + g_db * a3;
                 H[(4 * s + 1) * n2 + t] = a2;
@@ -540,13 +604,24 @@ namespace mgb
             for (int s = 0; s < 2; ++s)
               {
                 T V = 0, N = 0;
-#pragma unroll
-                for (int q = 0; q < n; ++q)
+                if (COLLOC)
                   {
-                    const T Sv = S_s[q * n + a], Gv = G_s[q * n + a];
-                    const T h0 = H[(4 * s + 0) * n2 + b * n + q], h1 = H[(4 * s + 1) * n2 + b * n + q];
-                    V += Sv * h0 + g_da * Gv * h1;
-                    N += Sv * h1;
+#pragma unroll
+                    for (int q = 0; q < n; ++q)
+                      V += G_s[q * n + a] * H[(4 * s + 1) * n2 + b * n + q];
+                    V = H[(4 * s + 0) * n2 + t] + g_da * V;
+                    N = H[(4 * s + 1) * n2 + t];
+                  }
+                else
+                  {
+#pragma unroll
+                    for (int q = 0; q < n; ++q)
+                      {
+                        const T Sv = S_s[q * n + a], Gv = G_s[q * n + a];
+                        const T h0 = H[(4 * s + 0) * n2 + b * n + q], h1 = H[(4 * s + 1) * n2 + b * n + q];
+                        V += Sv * h0 + g_da * Gv * h1;
+                        N += Sv * h1;
+                      }
                   }
                 N *= g_dd;
                 const T *eK = s ? Tb.e1 : Tb.e0, *fK = s ? Tb.f1 : Tb.f0;
@@ -612,7 +687,7 @@ namespace mgb
       }
   }
 
-  template <int p, typename T, bool GEN>
+  template <int p, typename T, int KIND>
   void
   launch_dg_apply(const DGArgs<T> &A, const DGTables<T, p + 1> &Tb, cudaStream_t stream)
   {
@@ -621,11 +696,11 @@ namespace mgb
     static bool  first = true;
     if (first)
       {
-        cudaFuncSetAttribute(k_dg_apply<p, T, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(k_dg_apply<p, T, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         first = false;
       }
     const unsigned blocks = (A.n_cells + C::CPB - 1) / C::CPB;
-    k_dg_apply<p, T, GEN><<<blocks, C::NT, smem, stream>>>(A, Tb);
+    k_dg_apply<p, T, KIND><<<blocks, C::NT, smem, stream>>>(A, Tb);
   }
 
   template <int p, typename T>

@@ -78,7 +78,7 @@ def test_example_driver_matches_oracle(mgb, orc):
     assert int(out["adaptive_cells"]) == a.n_cells() and int(out["adaptive_m"]) == oa.n_dofs()
     e_ref = float(np.ones(oa.n_dofs()) @ oa.vmult(np.ones(oa.n_dofs())))
     assert abs(float(out["adaptive_xAx"]) - e_ref) <= 1e-10 * abs(e_ref)
-    ds = orc.MultigridSolverDG(4, (1, 1, 1), 2)
+    ds = orc.MultigridSolverDG(4, (1, 1, 1), 2, basis=orc.DG_BASIS_HERMITE)   # the adapter's default, as the reference
     _, rate_dg, _ = ds.solve_cg(1e-3)
     assert int(out["dg_cg_its"]) == ds.last_step
     assert abs(float(out["dg_cg_rate"]) - rate_dg) <= 3e-2 * rate_dg

@@ -1,6 +1,6 @@
 """DG benchmark protocols: matvec_dg/program.cc:139-204 (double vmult, GB/s at 3 N bytes per DoF) and
 matvec_dg_cheby/program.cc:110-190 (float Chebyshev update, iteration index 2, factors 0.6 / 0.2, 5 N bytes per DoF).
-usage: python tools/time_dg.py [n_cell_steps=20] [degree=4]"""
+usage: python tools/time_dg.py [n_cell_steps=20] [degree=4] [basis=0: FE_DGQ, 1: FE_DGQHermite, 2: Gauss]"""
 import os
 import sys
 
@@ -9,11 +9,11 @@ import torch
 import multigrid_b200 as mgb
 
 
-def run(steps=20, degree=4, reps=20):
+def run(steps=20, degree=4, reps=20, basis=0):
     nsub = tuple(2 if c < steps % 3 else 1 for c in range(3))   # matvec_dg/program.cc:61-64
     out = {}
     for name, prec in (("vmult_f64", mgb.F64), ("vmult_f32", mgb.F32), ("cheby_f32", mgb.F32), ("cheby_f64", mgb.F64)):
-        g = mgb.LaplaceOperatorDG(degree, nsub, steps // 3, precision=prec)
+        g = mgb.LaplaceOperatorDG(degree, nsub, steps // 3, precision=prec, basis=basis)
         n = g.m()
         a = torch.rand(n, dtype=g.dtype, device="cuda")
         b = torch.rand(n, dtype=g.dtype, device="cuda")
@@ -44,5 +44,6 @@ def run(steps=20, degree=4, reps=20):
 if __name__ == "__main__":
     steps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
     deg = int(sys.argv[2]) if len(sys.argv) > 2 else 4
-    for k, v in run(steps, deg).items():
-        print("DG p=%d %-10s n=%d  %.3f ms  %.3e DoF/s  %.0f GB/s (%d B/DoF)" % (deg, k, v["n_dofs"], v["ms"], v["dofs_per_s"], v["gbs"], v["bytes_per_dof"]))
+    basis = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+    for k, v in run(steps, deg, basis=basis).items():
+        print("DG basis=%d p=%d %-10s n=%d  %.3f ms  %.3e DoF/s  %.0f GB/s (%d B/DoF)" % (basis, deg, k, v["n_dofs"], v["ms"], v["dofs_per_s"], v["gbs"], v["bytes_per_dof"]))

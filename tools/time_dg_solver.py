@@ -1,6 +1,6 @@
 """poisson_dg protocol (poisson_dg/program.cc:227-263): MultigridSolverDG on the doubling mesh, minimum of 4 CG solves
 to the given tolerance; DoF/s = DG DoFs / solve time.
-usage: python tools/time_dg_solver.py [cycle=18] [degree=4] [tolerance=1e-3]"""
+usage: python tools/time_dg_solver.py [cycle=18] [degree=4] [tolerance=1e-3] [basis=0: FE_DGQ, 1: FE_DGQHermite, 2: Gauss]"""
 import os
 import sys
 import time
@@ -18,10 +18,10 @@ def doubling_mesh(cycle):
     return nsub, cycle // 3, (-1.,) * 3, upper
 
 
-def run(cycle=18, degree=4, tolerance=1e-3, n_solves=4, preconditioner=1):
+def run(cycle=18, degree=4, tolerance=1e-3, n_solves=4, preconditioner=1, basis=0):
     nsub, nref, lower, upper = doubling_mesh(cycle)
     t0 = time.perf_counter()
-    s = mgb.MultigridSolverDG(degree, nsub, nref, lower, upper, 3, 3, preconditioner)
+    s = mgb.MultigridSolverDG(degree, nsub, nref, lower, upper, 3, 3, preconditioner, basis=basis)
     s.sync()
     setup = time.perf_counter() - t0
     n = s.n_dofs()
@@ -52,5 +52,7 @@ if __name__ == "__main__":
     cyc = int(sys.argv[1]) if len(sys.argv) > 1 else 18
     deg = int(sys.argv[2]) if len(sys.argv) > 2 else 4
     tol = float(sys.argv[3]) if len(sys.argv) > 3 else 1e-3
-    for k, v in run(cyc, deg, tol).items():
+    basis = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+    print('basis', basis)
+    for k, v in run(cyc, deg, tol, basis=basis).items():
         print(k, v)
