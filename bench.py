@@ -376,6 +376,11 @@ def dg_lines(r):
     torch.cuda.empty_cache()
     out["poisson_dg_solve"] = time_dg_solver.run(21, DEGREE, 1e-3)
     out["poisson_dg_solve"]["workload"] = "poisson_dg cycle 21: [-1,1]^3, 128^3 cells, FE_DGQ(4), solve_cg(1e-3)"
+    # the same solve on the reference's own basis, FE_DGQHermite (poisson_dg/program.cc:174): vectors are Hermite
+    # coefficients, the DG <-> FE_Q transfer carries the change of basis
+    torch.cuda.empty_cache()
+    out["poisson_dg_solve_hermite"] = time_dg_solver.run(21, DEGREE, 1e-3, basis=1)
+    out["poisson_dg_solve_hermite"]["workload"] = "poisson_dg cycle 21: [-1,1]^3, 128^3 cells, FE_DGQHermite(4), solve_cg(1e-3)"
     return out
 
 

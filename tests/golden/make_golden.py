@@ -7,6 +7,9 @@ oracle still reproduces the file, the GPU tests compare the library with it dire
   adaptive_*  : y = A x on the hanging-node meshes of tests/adaptive_cases.py, in the order of the sorted DoF coordinates
   dg_solver_* : MultigridSolverDG (FE_DGQ(2), 4 x 4 x 4 cells on [-1,1]^3): residual history of solve_cg(1e-8), [L2 error],
                 and one preconditioner cycle applied to a seeded vector
+  dg_hermite_p{p}, dg_gauss_p{p} : as dg_p{p} on FE_DGQHermite(p) / FE_DGQArbitraryNodes(QGauss(p+1)) (coefficient vectors of
+                that basis in and out)
+  dg_hermite_solver_* : as dg_solver_* on FE_DGQHermite(2), the basis of poisson_dg (poisson_dg/program.cc:174)
 """
 import os
 import sys
@@ -44,6 +47,9 @@ def generate():
         out["fe_q_p%d" % p] = o.vmult(seeded(o.n_dofs(), p))
         d = orc.DGOperator(p, (2, 2, 2))
         out["dg_p%d" % p] = d.vmult(seeded(d.n_dofs(), 100 + p))
+        for name, kind in (("hermite", orc.DG_BASIS_HERMITE), ("gauss", orc.DG_BASIS_GAUSS)):
+            d = orc.DGOperator(p, (2, 2, 2), basis=kind)
+            out["dg_%s_p%d" % (name, p)] = d.vmult(seeded(d.n_dofs(), 100 + p))
     import multigrid_b200 as mgb          # host side only: mesh and cell list (no GPU needed)
     from adaptive_cases import make
     for i, name in enumerate(sorted(CASES)):
@@ -60,6 +66,12 @@ def generate():
     out["dg_solver_history"] = np.asarray(hist)
     out["dg_solver_l2_error"] = np.array([s.compute_l2_error()])
     out["dg_solver_solution"] = s.solution.copy()
+    s = orc.MultigridSolverDG(*DG_SOLVER_CASE, basis=orc.DG_BASIS_HERMITE)
+    out["dg_hermite_solver_cycle"] = s.vmult(seeded(s.n_dofs(), 300))
+    _, _, hist = s.solve_cg(1e-8)
+    out["dg_hermite_solver_history"] = np.asarray(hist)
+    out["dg_hermite_solver_l2_error"] = np.array([s.compute_l2_error()])
+    out["dg_hermite_solver_solution"] = s.solution.copy()
     return out
 
 

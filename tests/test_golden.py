@@ -22,7 +22,7 @@ def test_oracle_reproduces_golden_vectors(orc, mgb):
     assert sorted(now) == sorted(GOLD.files)
     for k in GOLD.files:
         # (the solver runs sum in OpenMP reductions: rounding differs with the number of threads)
-        assert rel(now[k], GOLD[k]) <= (1e-9 if k.startswith("dg_solver") else 1e-13), k
+        assert rel(now[k], GOLD[k]) <= (1e-9 if "solver" in k else 1e-13), k
 
 
 @pytest.mark.gpu
@@ -65,20 +65,37 @@ def test_library_against_golden_adaptive(mgb):
 
 
 @pytest.mark.gpu
-def test_library_against_golden_dg_solver(mgb):
+@pytest.mark.parametrize("p", range(1, 9))
+@pytest.mark.parametrize("name", ["hermite", "gauss"])
+def test_library_against_golden_dg_bases(mgb, orc, p, name):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    kind = {"hermite": mgb.DG_BASIS_HERMITE, "gauss": mgb.DG_BASIS_GAUSS}[name]
+    g = mgb.LaplaceOperatorDG(p, (2, 2, 2), 0, trafo=orc.dg_trafo(), basis=kind)
+    x = make_golden.seeded(g.m(), 100 + p)
+    y = g.initialize_dof_vector()
+    g.vmult(y, torch.tensor(x, device="cuda"))
+    assert rel(y.cpu().numpy(), GOLD["dg_%s_p%d" % (name, p)]) <= 1e-12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prefix", ["dg_solver", "dg_hermite_solver"])
+def test_library_against_golden_dg_solver(mgb, prefix):
     """MultigridSolverDG against the stored oracle run: the float cycle against the double one (2e-4), the same
     number of CG iterations, the residual history, the L2 error to 3 digits"""
     import torch
     if not torch.cuda.is_available():
         pytest.skip("no GPU")
-    g = mgb.MultigridSolverDG(*make_golden.DG_SOLVER_CASE)
+    basis = mgb.DG_BASIS_HERMITE if "hermite" in prefix else mgb.DG_BASIS_GAUSS_LOBATTO
+    g = mgb.MultigridSolverDG(*make_golden.DG_SOLVER_CASE, basis=basis)
     src = make_golden.seeded(g.n_dofs(), 300)
     dst = torch.zeros(g.n_dofs(), dtype=torch.float64, device="cuda")
     g.vmult(dst, torch.tensor(src, device="cuda"))
-    assert rel(dst.cpu().numpy(), GOLD["dg_solver_cycle"]) <= 2e-4
+    assert rel(dst.cpu().numpy(), GOLD[prefix + "_cycle"]) <= 2e-4
     g.solve_cg(1e-8)
-    hist, want = g.residual_history(), GOLD["dg_solver_history"]
+    hist, want = g.residual_history(), GOLD[prefix + "_history"]
     assert hist.size == want.size
     assert np.all(np.abs(hist - want) <= 0.1 * want + 1e-6 * want[0])
-    assert abs(g.compute_l2_error() - GOLD["dg_solver_l2_error"][0]) <= 1e-3 * GOLD["dg_solver_l2_error"][0]
-    assert rel(g.get_solution(), GOLD["dg_solver_solution"]) <= 1e-6
+    assert abs(g.compute_l2_error() - GOLD[prefix + "_l2_error"][0]) <= 1e-3 * GOLD[prefix + "_l2_error"][0]
+    assert rel(g.get_solution(), GOLD[prefix + "_solution"]) <= 1e-6
