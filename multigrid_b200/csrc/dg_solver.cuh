@@ -249,6 +249,8 @@ namespace mgb
         throw std::runtime_error("smoother degree must be at least 1");
       if (o.preconditioner != 0 && o.preconditioner != 1)
         throw std::runtime_error("preconditioner: 0 = point Jacobi, 1 = JacobiTransformed");
+      if (o.basis < DG_BASIS_GAUSS_LOBATTO || o.basis > DG_BASIS_GAUSS)
+        throw std::runtime_error("unknown DG basis");
       mgb_options fo;
       mgb_default_options(&fo);
       fo.degree        = o.degree;

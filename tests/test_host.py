@@ -36,6 +36,21 @@ def test_error_reporting(mgb):
         mgb.host_basis(11)
 
 
+def test_dg_options_are_checked_before_the_device(mgb):
+    """an unknown DG basis is an error of the options (return code + message), with or without a GPU; a valid basis
+    without a GPU fails loudly - there is no CPU fallback"""
+    with pytest.raises(mgb.MgbError, match="basis"):
+        mgb.LaplaceOperatorDG(2, (1, 1, 1), 0, basis=7)
+    with pytest.raises(mgb.MgbError, match="basis"):
+        mgb.MultigridSolverDG(2, (1, 1, 1), 1, basis=-1)
+    import torch
+    if not torch.cuda.is_available():
+        for kind in (mgb.DG_BASIS_GAUSS_LOBATTO, mgb.DG_BASIS_HERMITE, mgb.DG_BASIS_GAUSS):
+            with pytest.raises(mgb.MgbError, match="no CUDA device|CUDA"):
+                mgb.LaplaceOperatorDG(2, (1, 1, 1), 0, basis=kind)
+    assert [mgb.dg_basis_of_type(t) for t in (0, 1, 2)] == [mgb.DG_BASIS_HERMITE, mgb.DG_BASIS_GAUSS_LOBATTO, mgb.DG_BASIS_GAUSS]
+
+
 @pytest.mark.parametrize("p", range(1, 9))
 def test_basis_matches_oracle(mgb, orc, p):
     a, b = mgb.host_basis(p), orc.basis(p)

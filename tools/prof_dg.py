@@ -1,4 +1,5 @@
-"""ncu driver: a few DG operator applies (double vmult, float Chebyshev update) on 16 M DoF."""
+"""ncu driver: a few DG operator applies (double vmult, float Chebyshev update) on 16 M DoF.
+usage: python tools/prof_dg.py [basis=0: FE_DGQ, 1: FE_DGQHermite, 2: Gauss]"""
 import os
 import sys
 
@@ -6,8 +7,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import multigrid_b200 as mgb
 
+BASIS = int(sys.argv[1]) if len(sys.argv) > 1 else 0
 for prec in (mgb.F64, mgb.F32):
-    g = mgb.LaplaceOperatorDG(4, (2, 2, 1), 5, precision=prec)
+    g = mgb.LaplaceOperatorDG(4, (2, 2, 1), 5, precision=prec, basis=BASIS)
     n = g.m()
     a, b, c = (torch.rand(n, dtype=g.dtype, device="cuda") for _ in range(3))
     g.get_matrix_diagonal_inverse()
