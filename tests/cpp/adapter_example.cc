@@ -65,6 +65,36 @@ main(int argc, char **argv)
           xPx += hx[i] * hp[i];
       }
       std::printf("xPx %.12e\n", xPx);
+      {
+        // the same operator with the reference's default template argument (type 0, FE_DGQHermite) and on the Gauss
+        // basis (type 2): z^T A z of one coefficient vector (not a constant function) in each basis
+        multigrid::LaplaceOperatorCompactCombine<3, degree, double> dg_hermite;
+        multigrid::LaplaceOperatorCompactCombine<3, degree, double, 2> dg_gauss;
+        dg_hermite.reinit(o);
+        dg_gauss.reinit(o);
+        std::vector<double> hz(dg.m());
+        for (std::size_t i = 0; i < hz.size(); ++i)
+          hz[i] = 0.1 + (i % 7) / 7.;
+        multigrid::DGVector<double> z;
+        dg.initialize_dof_vector(z);
+        z.import_from_host(hz);
+        double e[2] = {0, 0};
+        dg_hermite.vmult(y, z);
+        dg_hermite.synchronize();
+        {
+          const std::vector<double> h = y.export_to_host();
+          for (std::size_t i = 0; i < h.size(); ++i)
+            e[0] += hz[i] * h[i];
+        }
+        dg_gauss.vmult(y, z);
+        dg_gauss.synchronize();
+        {
+          const std::vector<double> h = y.export_to_host();
+          for (std::size_t i = 0; i < h.size(); ++i)
+            e[1] += hz[i] * h[i];
+        }
+        std::printf("xAx_hermite %.12e xAx_gauss %.12e\n", e[0], e[1]);
+      }
       if (argc > 99) // compiled, not run: the transfer needs an FE_Q level on the same (unsheared) mesh
         {
           dg.prolongate_add_cg_to_dg(y, p);

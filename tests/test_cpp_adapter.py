@@ -64,6 +64,11 @@ def test_example_driver_matches_oracle(mgb, orc):
     x = np.ones(d.n_dofs())
     assert abs(float(out["xAx"]) - x @ d.vmult(x)) <= 1e-10 * abs(x @ d.vmult(x))
     assert abs(float(out["penalty_x"]) - d.penalty()[0]) <= 1e-6 * d.penalty()[0]  # printed with 7 digits
+    for name, kind in (("xAx_hermite", orc.DG_BASIS_HERMITE), ("xAx_gauss", orc.DG_BASIS_GAUSS)):
+        dk = orc.DGOperator(4, (4, 4, 4), basis=kind)
+        z = 0.1 + (np.arange(dk.n_dofs()) % 7) / 7.
+        want = z @ dk.vmult(z)
+        assert abs(float(out[name]) - want) <= 1e-10 * abs(want), name
     jt = orc.JacobiTransformed(d)
     assert float(out["xPx"]) > 0 and abs(float(out["xPx"]) - x @ jt.vmult(x)) <= 1e-9 * abs(x @ jt.vmult(x))
     # the adaptive operator of the example: same mesh through the Python mirror, energy against the geometric oracle

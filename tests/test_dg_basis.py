@@ -27,6 +27,8 @@ def test_hermite_like_basis_known_values(orc):
             M = t["S"].T @ np.diag(t["wq"]) @ t["S"]
             assert abs(M[0, 1]) < 1e-15 and abs(M[p, p - 1]) < 1e-15
         assert np.linalg.cond(t["B"]) < 10
+        # partition of unity (value 1 and slope 0 at both ends, 1 in the interior nodes: p + 1 conditions on degree p)
+        assert np.allclose(t["S"].sum(axis=1), 1, atol=1e-14) and np.allclose(t["G"].sum(axis=1), 0, atol=1e-12)
 
 
 def test_gauss_basis_is_collocated(orc):
