@@ -38,7 +38,7 @@ namespace mgb
     T G[n * n]; // phi_i'(x_q)
     T D[n * n]; // D[q n + r] = l_r'(x_q)
     T e0[n], e1[n]; // phi_i'(0), phi_i'(1)
-    T f0[n], f1[n]; // phi_i(0), phi_i(1): unit vectors for the Gauss-Lobatto basis (kernel variant GEN = false)
+    T f0[n], f1[n]; // phi_i(0), phi_i(1): unit vectors for the Gauss-Lobatto basis (kernel variant KIND = 0)
     T w[n];
     T V[n * n]; // V[k n + j] = component j of the k-th generalised eigenvector of (1-D SIP Laplace, 1-D mass)
   };
@@ -228,8 +228,8 @@ namespace mgb
         A.dst[(size_t)c * n3 + i] = scale * r[i];
   }
 
-  // GEN = false: nodal basis with a node on each end point (FE_DGQ on the Gauss-Lobatto points): the trace of a pencil
-  // is its end value.  GEN = true: any tensor-product basis (FE_DGQHermite, FE_DGQArbitraryNodes(QGauss)); traces and
+  // KIND = 0: nodal basis with a node on each end point (FE_DGQ on the Gauss-Lobatto points): the trace of a pencil
+  // is its end value.  KIND = 1: any tensor-product basis (FE_DGQHermite, FE_DGQArbitraryNodes(QGauss)); traces and
   // their transposes go through the tables f0 / f1 (laplace_operator_dg.h:1179-1199, 1359-1389 use the structure of
   // each basis instead; the result is the same operator in that basis).
   // KIND = 2: generic traces and S = I (basis collocated with the Gauss points, FE_DGQArbitraryNodes(QGauss)): the six
