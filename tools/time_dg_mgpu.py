@@ -1,6 +1,6 @@
 """Weak scaling of the DG operator (matvec_dg protocol per GPU: 128 x 128 x 64 cells, FE_DGQ(4), 131 M DoF per GPU):
 z-slabs of cell layers, ghost layers over NCCL.  Run under torchrun, one process per GPU.
-usage: python -m torch.distributed.run --nproc-per-node N tools/time_dg_mgpu.py [reps=10]"""
+usage: python -m torch.distributed.run --nproc-per-node N tools/time_dg_mgpu.py [reps=10] [basis=0: FE_DGQ, 1: FE_DGQHermite, 2: Gauss]"""
 import os
 import sys
 
@@ -12,6 +12,7 @@ import multigrid_b200 as mgb
 
 def main():
     reps = int(sys.argv[1]) if len(sys.argv) > 1 else 10
+    basis = int(sys.argv[2]) if len(sys.argv) > 2 else 0
     lr = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(lr)
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -20,7 +21,7 @@ def main():
     out = {}
     for name, prec in (("vmult_f64", mgb.F64), ("cheby_f32", mgb.F32)):
         comm = mgb.comm_from_torch_distributed() if world > 1 else None
-        g = mgb.LaplaceOperatorDG(4, (2, 2, world), 6, precision=prec, device=lr, comm=comm)
+        g = mgb.LaplaceOperatorDG(4, (2, 2, world), 6, precision=prec, device=lr, comm=comm, basis=basis)
         q = g.partition()
         a = torch.rand(q["n_local"], dtype=g.dtype, device="cuda")
         b = torch.rand(q["n_local"], dtype=g.dtype, device="cuda")

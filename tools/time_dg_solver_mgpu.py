@@ -19,6 +19,7 @@ def main():
     base = int(sys.argv[1]) if len(sys.argv) > 1 else 21
     degree = int(sys.argv[2]) if len(sys.argv) > 2 else 4
     tol = float(sys.argv[3]) if len(sys.argv) > 3 else 1e-3
+    basis = int(sys.argv[4]) if len(sys.argv) > 4 else 0   # 0: FE_DGQ, 1: FE_DGQHermite, 2: Gauss
     rank, local, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     torch.cuda.set_device(local)
     comm = None
@@ -27,7 +28,7 @@ def main():
         comm = mgb.comm_from_torch_distributed()
     cycle = base + (world.bit_length() - 1)
     nsub, nref, lower, upper = doubling_mesh(cycle)
-    s = mgb.MultigridSolverDG(degree, nsub, nref, lower, upper, 3, 3, 1, device=local, comm=comm)
+    s = mgb.MultigridSolverDG(degree, nsub, nref, lower, upper, 3, 3, 1, device=local, comm=comm, basis=basis)
     q = s.partition()
     best = 1e30
     for _ in range(4):
