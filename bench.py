@@ -370,6 +370,11 @@ def dg_lines(r):
     for v in out.values():
         v["frac_hbm"] = v["gbs"] / r["hbm_gbs"]
     out["workload"] = "matvec_dg s=20: 128x128x64 cells, FE_DGQ(4), affine sheared mesh, 131072000 DoF"
+    # the same protocol on FE_DGQArbitraryNodes(QGauss) (matvec_dg/program.cc:48-49, type 2): collocation kernel variant
+    gauss = time_dg.run(20, DEGREE, reps=10, basis=2)
+    for v in gauss.values():
+        v["frac_hbm"] = v["gbs"] / r["hbm_gbs"]
+    out["gauss_basis"] = gauss
     # poisson_dg/program.cc:227-263 on its doubling-mesh cycle 21 (128^3 cells, 262 M DG DoF), default tolerance 1e-3:
     # MultigridSolverDG = CG(double) + Chebyshev/JacobiTransformed + FE_Q V-cycle (float), minimum of 4 solves
     import time_dg_solver
