@@ -17,12 +17,14 @@ from oracle import orc  # noqa: E402  (the checker)
 
 def main():
     p, nsub, nref = int(sys.argv[1]), tuple(int(v) for v in sys.argv[2].split(",")), int(sys.argv[3])
+    basis = int(sys.argv[4]) if len(sys.argv) > 4 else 0      # DG_BASIS_*: 0 FE_DGQ, 1 FE_DGQHermite, 2 Gauss
     rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lower, upper = (-1.,) * 3, tuple(-1. + 2. * s for s in nsub)
-    o = orc.MultigridSolverDG(p, nsub, nref, lower, upper)      # the whole mesh
-    g = mgb.MultigridSolverDG(p, nsub, nref, lower, upper, device=local, comm=mgb.comm_from_torch_distributed())
+    o = orc.MultigridSolverDG(p, nsub, nref, lower, upper, basis=basis)      # the whole mesh
+    g = mgb.MultigridSolverDG(p, nsub, nref, lower, upper, device=local, comm=mgb.comm_from_torch_distributed(),
+                              basis=basis)
     q = g.partition()
     assert q["n_global"] == o.n_dofs() and q["n_owned"] * dist.get_world_size() == o.n_dofs()
     assert g.n_dofs() == q["n_local"]

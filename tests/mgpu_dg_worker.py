@@ -20,17 +20,18 @@ def rel(a, b):
 
 def main():
     p, nsub, nref = int(sys.argv[1]), tuple(int(v) for v in sys.argv[2].split(",")), int(sys.argv[3])
+    basis = int(sys.argv[4]) if len(sys.argv) > 4 else 0      # DG_BASIS_*: 0 FE_DGQ, 1 FE_DGQHermite, 2 Gauss
     rank = int(os.environ["RANK"])
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
-    o = orc.DGOperator(p, [s << nref for s in nsub])          # the whole mesh, sheared as matvec_dg
+    o = orc.DGOperator(p, [s << nref for s in nsub], basis=basis)          # the whole mesh, sheared as matvec_dg
     rng = np.random.default_rng(5)
     x, b, x_old = rng.standard_normal(o.n_dofs()), rng.standard_normal(o.n_dofs()), rng.standard_normal(o.n_dofs())
     Ax = o.vmult(x)
     for precision, dtype, tol in ((mgb.F64, torch.float64, 1e-12), (mgb.F32, torch.float32, 1e-5)):
         comm = mgb.comm_from_torch_distributed()   # a unique id makes one communicator: a fresh one per operator
         g = mgb.LaplaceOperatorDG(p, nsub, nref, trafo=orc.dg_trafo(), device=int(os.environ["LOCAL_RANK"]),
-                                  precision=precision, comm=comm)
+                                  precision=precision, comm=comm, basis=basis)
         q = g.partition()
         assert q["n_global"] == o.n_dofs() and q["n_owned"] * dist.get_world_size() == o.n_dofs()
         layer = q["n_owned"] // q["n_layers"]

@@ -51,6 +51,12 @@ def test_two_gpus_dg_operator_against_oracle(mgb, orc, p, nsub, nref):
     run_ranks(2, [str(p), nsub, str(nref)], worker="mgpu_dg_worker.py", ok="mgpu dg worker ok")
 
 
+@pytest.mark.parametrize("basis", [1, 2])
+def test_two_gpus_dg_operator_other_bases(mgb, orc, basis):
+    """the same on FE_DGQHermite (1) and the Gauss basis (2): ghost cell layers carry coefficients of that basis"""
+    run_ranks(2, ["4", "1,1,1", "2", str(basis)], worker="mgpu_dg_worker.py", ok="mgpu dg worker ok")
+
+
 def test_four_gpus_dg_operator_against_oracle(mgb, orc):
     run_ranks(4, ["4", "1,1,1", "2"], worker="mgpu_dg_worker.py", ok="mgpu dg worker ok")
 
@@ -60,6 +66,13 @@ def test_two_gpus_dg_multigrid_solver_against_oracle(mgb, orc, p, nsub, nref):
     """MultigridSolverDG (common/multigrid_solver_dg.h) with one process per GPU: same CG iteration count, residual
     history, L2 error and solution as the global oracle composition"""
     run_ranks(2, [str(p), nsub, str(nref)], worker="mgpu_dg_solver_worker.py", ok="mgpu dg solver worker ok")
+
+
+@pytest.mark.parametrize("basis", [1, 2])
+def test_two_gpus_dg_multigrid_solver_other_bases(mgb, orc, basis):
+    """poisson_dg's own basis FE_DGQHermite (1) and the Gauss basis (2): the change of basis of the DG <-> FE_Q transfer
+    runs on every local cell layer, ghost layers included"""
+    run_ranks(2, ["2", "1,1,1", "2", str(basis)], worker="mgpu_dg_solver_worker.py", ok="mgpu dg solver worker ok")
 
 
 def test_four_gpus_dg_multigrid_solver_against_oracle(mgb, orc):
