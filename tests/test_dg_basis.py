@@ -121,3 +121,21 @@ def test_product_tables_match_the_oracle(orc, basis_dump, p, kind):
         assert np.abs(d[k] - t[k]).max() <= 2e-12 * max(1., np.abs(t[k]).max()), k
     assert np.abs(d["Binv"].reshape(n, n) @ t["B"] - np.eye(n)).max() <= 1e-12
     assert np.abs(d["D"].reshape(n, n) - orc.basis(p)["D"]).max() <= 1e-12 * np.abs(d["D"]).max()
+
+
+def test_a_gauss_basis_solve_serves_a_hermite_caller(orc):
+    """The plan of DESIGN.md section 8 for the next round, pinned on the oracle: with C = B_H^-1 B_G (Gauss coefficients ->
+    Hermite coefficients, per direction) the right-hand side is a dual vector, b_G = C^T b_H, the solution a primal one,
+    x_H = C x_G; the L2 errors agree and the residual norm of the Hermite stopping test is |C^-T r_G|."""
+    args = (2, 1, 2)
+    h = orc.MultigridSolverDG(*args, basis=orc.DG_BASIS_HERMITE)
+    g = orc.MultigridSolverDG(*args, basis=orc.DG_BASIS_GAUSS)
+    C = np.linalg.inv(h.op.tables["B"]) @ g.op.tables["B"]
+    assert np.abs(change(h.rhs, C.T, 3) - g.rhs).max() <= 1e-12 * np.abs(g.rhs).max()
+    h.solve_cg(1e-10)
+    g.solve_cg(1e-10)
+    assert np.abs(change(g.solution, C, 3) - h.solution).max() <= 1e-7 * np.abs(h.solution).max()
+    assert np.isclose(g.compute_l2_error(), h.compute_l2_error(), rtol=1e-6)
+    r_g = g.rhs - g.op.vmult(g.solution)
+    r_h = h.rhs - h.op.vmult(change(g.solution, C, 3))
+    assert np.isclose(np.linalg.norm(change(r_g, np.linalg.inv(C).T, 3)), np.linalg.norm(r_h), rtol=1e-6, atol=1e-12)
