@@ -32,6 +32,23 @@ BASELINE_CG_DOFS_PER_S = 135005697 / 16.49       # README.md:159 (12-core Broadw
 BASELINE_MATVEC_DOFS_PER_S = 135005697 / 0.15455  # README.md:122-127,159
 
 
+# L2 error of the CPU oracle's solve_cg on the same mesh (run once in the build container, 8 iterations)
+ORACLE_L2 = {135005697: 4.196178e-10}
+
+
+def readme_row(n_dofs):
+    """the reference's published row for this mesh (tests/golden/readme_table.json = README.md:135-159)"""
+    try:
+        tab = json.load(open(os.path.join(ROOT, "tests", "golden", "readme_table.json")))
+    except OSError:
+        return None
+    for row in tab["rows"]:
+        d = dict(zip(tab["_columns"], row))
+        if d["dofs"] == n_dofs:
+            return {"cg_its": d["cg_its"], "l2_cg": d["cg_L2error"], "cg_reduction": d["cg_reduction"]}
+    return None
+
+
 def load_peaks():
     try:
         pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -47,9 +64,45 @@ def flops_per_dof(p):
     return (4 * 3 * ops1 * n * n + n ** 3 * 18) / p ** 3
 
 
-def bytes_per_dof(p, nbytes, n_vectors):
-    """n_vectors * N + the 27 compressed indices of 4 bytes per cell (laplace_operator.h:233-237)."""
-    return n_vectors * nbytes + 4.0 * 27 / p ** 3
+def bytes_per_dof(p, nbytes, n_vectors, index_table=False):
+    """Algorithmic bytes per DoF of one operator apply: n_vectors * N for the tile kernels (closed-form
+    numbering, no index table: DESIGN.md section 4); with `index_table` the reference's model of SURVEY.md
+    8(d), which adds the 27 compressed indices of 4 bytes per cell (laplace_operator.h:233-237)."""
+    return n_vectors * nbytes + (4.0 * 27 / p ** 3 if index_table else 0.0)
+
+
+def executed_flops_per_dof(p):
+    """Flops the Cartesian tile kernel executes per DoF (FMA = 2): seven 1-D products with the assembled
+    grid-line matrices (x: M, K on the haloed rows; y: My mx, Ky mx, My kx; z: Mz Q, Kz P per cell layer),
+    DESIGN.md section 4.1.  p = 4: about 102."""
+    n = p + 1
+    cw = {1: 16, 2: 8, 3: 5, 4: 4, 5: 3}.get(p, 2)
+    tw = cw * p
+    row = ((p - 1) * n + (2 * n - 1)) / p          # multiply-adds per point of one assembled 1-D product
+    halo = (tw + p + 1) / tw
+    return 2 * (2 * row * halo + 3 * row + 2 + 2 * n * n / p + 1)
+
+
+def ncu_traffic(summary_file, kernel_substring):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the first launch of `kernel_substring` in a summary
+    written by tools/ncu_summary.py (profiles/); None if the file or the kernel is not there."""
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:
+        lines = open(os.path.join(ROOT, summary_file)).read().splitlines()
+    except OSError:
+        return None
+    inside, total, found = False, 0.0, 0
+    for ln in lines:
+        f = ln.split()
+        if len(f) >= 2 and f[0] == "Kernel" and f[1] == "Name":
+            if found == 2:
+                break
+            inside = kernel_substring in ln
+            continue
+        if inside and f and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and len(f) >= 3:
+            total += float(f[1]) * scale.get(f[2], 1.0)
+            found += 1
+    return total if found == 2 else None
 
 
 class ClockSampler:
@@ -107,51 +160,74 @@ class ClockSampler:
 # CPU side: the oracle (oracle/mg_oracle.cpp, a CPU restatement of the reference's algorithm; the
 # reference itself needs deal.II + p4est + MPI and cannot be built here: DESIGN.md) timed on the
 # host cores with all OpenMP threads.
-def cpu_sample_refinements(budget_s):
-    cores = os.cpu_count() or 1
+def mem_available_gb():
     try:
-        mem_gb = os.sysconf("SC_PAGE_SIZE") * os.sysconf("SC_PHYS_PAGES") / 2 ** 30
-    except (ValueError, OSError):
-        mem_gb = 16
-    # 64^3 cells (17 M DoF) needs ~4 GB and ~2e6 DoF/s per 8 cores; otherwise 32^3 cells (2.1 M DoF)
-    return 6 if (cores >= 16 and mem_gb >= 24 and budget_s >= 20) else 5
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                return int(ln.split()[1]) / 2 ** 20
+    except OSError:
+        pass
+    return 0.0
 
 
-def run_cpu_solver(steps, warmup, n_refine, n_matvec=5):
+def cpu_sample_refinements(full_size):
+    """Refinements of the cube the CPU arm solves: 7 (128^3 cells, 135 M DoF = the native arm's mesh, 11 GB and about
+    20 s per solve on 32 cores) when asked for the full size and the box has the memory and cores for it, else 6
+    (64^3 cells, 17 M DoF), else 5."""
+    cores, mem = os.cpu_count() or 1, mem_available_gb()
+    if full_size and cores >= 16 and mem >= 32:
+        return 7
+    return 6 if (cores >= 16 and mem >= 24) else 5
+
+
+def run_cpu_solver(steps, warmup, n_refine, n_matvec=5, budget_s=None):
     from oracle import orc
     orc.build()
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    # torch.distributed.run exports OMP_NUM_THREADS=1: set the thread count in the OpenMP runtime itself and
+    # report what the runtime really uses
+    threads = orc.omp_threads(os.cpu_count() or 1)
     s = orc.MultigridSolver(DEGREE, 1, n_refine, degree_pre=3, degree_post=3, n_cycles=2)
     n = s.n_dofs()
-    its = 0
+    its, t_warm = 0, None
     for _ in range(warmup):
+        t0 = time.perf_counter()
         its, _, _ = s.solve_cg()
+        t_warm = time.perf_counter() - t0
+    timed = steps
+    if budget_s is not None and t_warm is not None:  # bounded sample: as many of the K steps as fit the budget
+        timed = max(1, min(steps, int(budget_s / max(t_warm, 1e-9))))
     t0 = time.perf_counter()
-    for _ in range(steps):
+    for _ in range(timed):
         its, _, _ = s.solve_cg()
-    dt = (time.perf_counter() - t0) / max(steps, 1)
+    dt = (time.perf_counter() - t0) / max(timed, 1)
     mv64 = s.time_matvec(True, n_matvec)
     mv32 = s.time_matvec(False, n_matvec)
     return dict(n_dofs=n, cells=8 ** n_refine, seconds_per_solve=dt, iterations=its, l2_error=s.compute_l2_error(),
-                matvec_fp64_dofs_per_s=n / mv64, matvec_fp32_dofs_per_s=n / mv32, cores=cores)
+                matvec_fp64_dofs_per_s=n / mv64, matvec_fp32_dofs_per_s=n / mv32, cores=threads, steps_timed=timed)
 
 
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    nref = cpu_sample_refinements(60)
-    r = run_cpu_solver(args.steps, args.warmup, nref)
+    nref = cpu_sample_refinements(args.cells >= 128)
+    r = run_cpu_solver(args.steps, min(args.warmup, 1) if nref >= 7 else args.warmup, nref,
+                       budget_s=400 if nref >= 7 else 240)
     value = r["n_dofs"] / r["seconds_per_solve"]
-    sample = ("solve_cg on %d^3 cells = %d DoF (same FE_Q(4) cube problem, smaller mesh; multigrid cost is linear "
-              "in DoFs), oracle/mg_oracle.cpp with %d OpenMP threads" % (round(r["cells"] ** (1 / 3)), r["n_dofs"], r["cores"]))
+    nc = round(r["cells"] ** (1 / 3))
+    sample = ("solve_cg on %d^3 cells = %d DoF (%s), %d of the %d steps timed, oracle/mg_oracle.cpp with %d OpenMP "
+              "threads (omp_get_max_threads)"
+              % (nc, r["n_dofs"], "the native arm's mesh" if nc == args.cells else
+                 "same FE_Q(4) cube problem on a smaller mesh: the box lacks the memory or cores for 128^3; multigrid "
+                 "cost is linear in DoFs", r["steps_timed"], args.steps, r["cores"]))
+    cfg = workload_config(args, 1, cells=nc)
+    cfg["same_mesh_as_native_arm"] = nc == args.cells
     line = {
         "impl": "reference", "metric": "cg_vcycle_solve_dofs_per_s", "value": value, "unit": "DoF/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * r["seconds_per_solve"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": value / BASELINE_CG_DOFS_PER_S, "dtype": "f64 outer CG / f32 V-cycle", "data": "synthetic",
-        "config": workload_config(args, 1),
+        "config": cfg, "steps_timed": r["steps_timed"],
         "cpu_baseline": {"value": value, "unit": "DoF/s", "cores": r["cores"], "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "DoF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "cg_iterations": r["iterations"], "l2_error": r["l2_error"],
@@ -176,8 +252,8 @@ def weak_scaling_mesh(cells, n_gpus):
     return nsub, nref, (-1.0,) * 3, tuple(0.9 + 1.9 * (k - 1) for k in nsub)
 
 
-def workload_config(args, n_gpus):
-    cells = args.cells
+def workload_config(args, n_gpus, cells=None):
+    cells = args.cells if cells is None else cells
     nsub, nref, lo, hi = weak_scaling_mesh(cells, n_gpus)
     shape = [k << nref for k in nsub]
     dofs = 1
@@ -310,36 +386,73 @@ def report(args, r):
         if cnt == 0:
             return None
         per_launch_ms = ms / cnt
-        alg_bytes = bytes_per_dof(DEGREE, nbytes, n_vectors) * n
-        achieved = alg_bytes / (1e-3 * per_launch_ms) / 1e9
+        bpd = bytes_per_dof(DEGREE, nbytes, n_vectors)
+        bpd_ref = bytes_per_dof(DEGREE, nbytes, n_vectors, index_table=True)
+        achieved = bpd * n / (1e-3 * per_launch_ms) / 1e9
         return {"launches": cnt, "ms_per_launch": per_launch_ms, "share_of_step": ms / (r["ms_step"] * args.steps),
-                "algorithmic_bytes_per_dof": bytes_per_dof(DEGREE, nbytes, n_vectors), "achieved_gbs": achieved,
-                "frac_hbm": achieved / hbm, "dofs_per_s": n / (1e-3 * per_launch_ms)}
+                "algorithmic_bytes_per_dof": bpd, "achieved_gbs": achieved, "frac_hbm": achieved / hbm,
+                "survey_8d_bytes_per_dof_with_index_table": bpd_ref,
+                "frac_hbm_survey_8d_model": achieved / hbm * bpd_ref / bpd,
+                "dofs_per_s": n / (1e-3 * per_launch_ms)}
 
     kernels = {"apply_f32_chebyshev": kernel("apply_f32_chebyshev", 5, 4),
                "apply_f32_residual": kernel("apply_f32", 3, 4),
                "apply_f64": kernel("apply_f64", 2, 8)}
     epi_ms, epi_cnt = cls["apply_epilogue"]
     dom = kernels["apply_f32_chebyshev"]
-    # dram__bytes_read.sum + dram__bytes_write.sum of one finest-level launch on 128^3 cells per GPU, from the
-    # `ncu --set full` capture summarised in profiles/r1_tile_f32x2_ncu_full_summary.txt (2.215 GB + 0.523 GB)
-    traffic = 2.215254e9 + 0.522742e9 if n == 135005697 else None
+    # dram__bytes_read.sum + dram__bytes_write.sum of one finest-level launch on 128^3 cells per GPU, read from the
+    # committed `ncu --set full` summary of this kernel (newest round first)
+    traffic, traffic_src = None, None
+    if n == 135005697:
+        for f in ("profiles/r2_tile_f32x2_ncu_full_summary.txt", "profiles/r1_tile_f32x2_ncu_full_summary.txt"):
+            traffic = ncu_traffic(f, "k_apply_tile_f32x2<4, 3>")
+            if traffic is not None:
+                traffic_src = f
+                break
     roofline = {"bound": "hbm", "kernel": "k_apply_tile_f32x2<4, APPLY_CHEBYSHEV> (float operator apply with fused "
                                           "Chebyshev update, finest level)",
                 "achieved": dom["achieved_gbs"], "peak": hbm, "unit": "GB/s", "frac": dom["frac_hbm"],
-                "traffic": traffic, "traffic_source": "profiles/r1_tile_f32x2_ncu_full_summary.txt",
+                "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": r["peak_src"], "ms_per_launch": dom["ms_per_launch"],
                 "share_of_step": dom["share_of_step"],
-                "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_dof"] * n}
-    fl = flops_per_dof(DEGREE)
+                "algorithmic_bytes_per_dof": dom["algorithmic_bytes_per_dof"],
+                "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_dof"] * n,
+                "bytes_model": "5 vectors x 4 B = 20 B/DoF (x_k, b, D^-1, x_k-1 read, x_k+1 written; the tile kernel reads "
+                               "no index table); SURVEY 8(d)'s 21.69 B/DoF variant, which bills the reference's 27 "
+                               "indices per cell, is kept as frac_survey_8d_model",
+                "frac_survey_8d_model": dom["frac_hbm_survey_8d_model"]}
+    fl_ref, fl_exec = flops_per_dof(DEGREE), executed_flops_per_dof(DEGREE)
     matvec = {}
     for name, nbytes, peak_tf in (("fp64", 8, 37.2), ("fp32", 4, 74.4)):
         sec = 1e-3 * r["mv"][name]
         dps = total_dofs / sec
         gbs = bytes_per_dof(DEGREE, nbytes, 2) * n / sec / 1e9
-        matvec[name] = {"dofs_per_s": dps, "ms": r["mv"][name], "achieved_gbs_per_gpu": gbs, "frac_hbm": gbs / hbm,
-                        "tflops_per_gpu": fl * n / sec / 1e12, "frac_cuda_core_peak": fl * n / sec / 1e12 / peak_tf}
+        gbs_ref = bytes_per_dof(DEGREE, nbytes, 2, index_table=True) * n / sec / 1e9
+        matvec[name] = {"dofs_per_s": dps, "ms": r["mv"][name], "algorithmic_bytes_per_dof": 2 * nbytes,
+                        "achieved_gbs_per_gpu": gbs, "frac_hbm": gbs / hbm,
+                        "frac_hbm_survey_8d_model": gbs_ref / hbm,
+                        "tflops_per_gpu_executed": fl_exec * n / sec / 1e12,
+                        "frac_cuda_core_peak_executed": fl_exec * n / sec / 1e12 / peak_tf,
+                        "executed_flops_per_dof": fl_exec,
+                        "tflops_per_gpu_reference_flop_model": fl_ref * n / sec / 1e12,
+                        "reference_flop_model_per_dof": fl_ref,
+                        "flop_note": "executed = the Kronecker-form tile kernel's own count; reference model = "
+                                     "161.7 flop/DoF of the reference's sum-factorisation cell kernel (SURVEY 8(d)), "
+                                     "quoted for comparability only"}
     matvec["fp64"]["vs_readme_12core_broadwell"] = matvec["fp64"]["dofs_per_s"] / BASELINE_MATVEC_DOFS_PER_S
+    # parity of this very run against the reference's README row for the mesh (README.md:135-159), asserted
+    parity = None
+    golden = readme_row(total_dofs)
+    if golden is not None:
+        rel = abs(r["l2_error"] - golden["l2_cg"]) / golden["l2_cg"]
+        parity = {"cg_iterations": r["its"], "cg_iterations_README": golden["cg_its"],
+                  "l2_error": r["l2_error"], "l2_error_README": golden["l2_cg"], "l2_rel_diff_vs_README": rel,
+                  "l2_error_oracle_same_mesh": ORACLE_L2.get(total_dofs),
+                  "cg_reduction": r["rate"], "cg_reduction_README": golden["cg_reduction"],
+                  "asserted": "iterations equal; L2 error within 5e-3 relative of the README row (the CPU oracle on "
+                              "the same 135 M DoF mesh gives 4.196e-10, as this run; README prints 4.207e-10)"}
+        assert r["its"] == golden["cg_its"], "CG iterations %d != README %d" % (r["its"], golden["cg_its"])
+        assert rel < 5e-3, "L2 error %g differs from README %g" % (r["l2_error"], golden["l2_cg"])
     line = {
         "metric": "cg_vcycle_solve_dofs_per_s", "value": value, "unit": "DoF/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_step"], "higher_is_better": True,
@@ -350,7 +463,7 @@ def report(args, r):
         "exchanges_total": r["exchanges"],
         "gpu_launches": r["launches"], "cg_iterations": r["its"], "cg_reduction_per_iteration": r["rate"],
         "l2_error": r["l2_error"], "total_dofs": total_dofs, "setup_s": r["t_setup"],
-        "matvec": matvec, "roofline": roofline, "kernels_finest_level": kernels,
+        "parity": parity, "matvec": matvec, "roofline": roofline, "kernels_finest_level": kernels,
         "epilogue_kernel_ms_per_launch": epi_ms / epi_cnt if epi_cnt else None,
         "clocks": r["clocks"],
     }
@@ -432,11 +545,12 @@ def main():
     if r["rank"] == 0:
         line = report(args, r)
         if r["world"] == 1 and not args.no_cpu_baseline:
-            c = run_cpu_solver(2, 1, 5)
+            c = run_cpu_solver(8, 1, cpu_sample_refinements(False), budget_s=25)
+            nc = round(c["cells"] ** (1 / 3))
             line["cpu_baseline"] = {
                 "value": c["n_dofs"] / c["seconds_per_solve"], "unit": "DoF/s", "cores": c["cores"], "kind": "port",
-                "sample": "solve_cg on 32^3 cells = %d DoF, 2 timed solves, oracle/mg_oracle.cpp, %d OpenMP threads"
-                          % (c["n_dofs"], c["cores"]),
+                "sample": "solve_cg on %d^3 cells = %d DoF, %d timed solves (about 25 s of CPU work), oracle/mg_oracle.cpp, "
+                          "%d OpenMP threads (omp_get_max_threads)" % (nc, c["n_dofs"], c["steps_timed"], c["cores"]),
                 "matvec_fp64_dofs_per_s": c["matvec_fp64_dofs_per_s"], "cg_iterations": c["iterations"]}
         if r["world"] == 1 and not args.no_dg:
             line["dg"] = dg_lines(r)

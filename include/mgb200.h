@@ -112,6 +112,12 @@ int mgb_solver_cg_history(mgb_solver s, double *history, int *n);
 int mgb_solver_l2_error(mgb_solver s, int level, double *error);
 /* MultigridSolver::vmult(dst, src)  (one float V-cycle as preconditioner)  multigrid_solver.h:498-510 */
 int mgb_solver_vcycle(mgb_solver s, double *dst_dev, const double *src_dev);
+/* std::array<Number2,2> MultigridSolver::vmult_with_residual_update(residual, update, factor)   multigrid_solver.h:516-619
+ * The preconditioner entry of a merged CG: defect = float(residual + factor update), one V-cycle, then in one pass
+ * residual += factor update, update = V-cycle result, sums[0] = <update_new, residual_new>, sums[1] = <update_new,
+ * factor update_old> over all ranks (factor == 0: residual untouched, sums[1] = sums[0]); Dirichlet rows are identity rows. */
+int mgb_solver_vmult_with_residual_update(mgb_solver s, double *residual_dev, double *update_dev, double factor,
+                                          double sums[2]);
 /* MultigridSolver::do_matvec / do_matvec_smoother         multigrid_solver.h:624-637 */
 int mgb_solver_do_matvec(mgb_solver s);
 int mgb_solver_do_matvec_smoother(mgb_solver s);
@@ -345,6 +351,11 @@ int mgb_vec_dot(mgb_solver s, int level, int precision, const void *a, const voi
 int mgb_vec_sadd(mgb_solver s, int level, int precision, void *y, double sy, double ax, const void *x);
 int mgb_vec_set(mgb_solver s, int level, int precision, void *y, double value);
 int mgb_vec_update_ghost_values(mgb_solver s, int level, int precision, void *v);
+/* compress(VectorOperation::add) and zero_out_ghost_values of LinearAlgebra::distributed::Vector (the calls around
+ * every cell loop that writes ghosts, laplace_operator.h:590,843): ghost planes are added to their owners on the
+ * neighbouring z-slabs and then zeroed / ghost planes are zeroed.  No-ops on one GPU and on replicated levels. */
+int mgb_vec_compress_add(mgb_solver s, int level, int precision, void *v);
+int mgb_vec_zero_out_ghost_values(mgb_solver s, int level, int precision, void *v);
 
 /* plain host<->device helpers so that a C/C++ caller needs no CUDA runtime of its own; `s` may be NULL (vectors
  * of the DG operator): current device, synchronous */

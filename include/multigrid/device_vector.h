@@ -125,8 +125,13 @@ namespace multigrid
     {
       check(mgb_vec_update_ghost_values(s_, level_, precision_of<Number>::value, data_));
     }
-    void zero_out_ghost_values() const {}
-    void compress() {}
+    void zero_out_ghost_values() const
+    {
+      check(mgb_vec_zero_out_ghost_values(s_, level_, precision_of<Number>::value, data_));
+    }
+    // compress(VectorOperation::add): ghost entries are added to their owners on the neighbouring z-slabs and
+    // zeroed (no-op on one GPU and on replicated levels)
+    void compress() { check(mgb_vec_compress_add(s_, level_, precision_of<Number>::value, data_)); }
 
     // host <-> device in the library's numbering (mgb_solver_lex_map gives the permutation)
     void

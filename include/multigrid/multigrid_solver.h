@@ -7,6 +7,7 @@
 #define MULTIGRID_MULTIGRID_SOLVER_H
 
 #include <cstdio>
+#include <array>
 #include <utility>
 
 #include "laplace_operator.h"
@@ -106,6 +107,14 @@ namespace multigrid
     }
     // multigrid_solver.h:498-510: one V-cycle as preconditioner
     void vmult(VectorType &dst, const VectorType &src) const { check(mgb_solver_vcycle(s_, dst.begin(), src.begin())); }
+    // multigrid_solver.h:516-619: preconditioner entry of the merged CG
+    std::array<Number2, 2>
+    vmult_with_residual_update(VectorType &residual, VectorType &update, const Number2 factor) const
+    {
+      double sums[2] = {0., 0.};
+      check(mgb_solver_vmult_with_residual_update(s_, residual.begin(), update.begin(), (double)factor, sums));
+      return {{(Number2)sums[0], (Number2)sums[1]}};
+    }
     // multigrid_solver.h:624-637
     void do_matvec() { check(mgb_solver_do_matvec(s_)); }
     void do_matvec_smoother() { check(mgb_solver_do_matvec_smoother(s_)); }

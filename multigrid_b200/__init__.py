@@ -110,6 +110,7 @@ SYMBOLS = {
     "mgb_solver_cg_history": (_i, [_vp, _dp, _ip]),
     "mgb_solver_l2_error": (_i, [_vp, _i, _dp]),
     "mgb_solver_vcycle": (_i, [_vp, _vp, _vp]),
+    "mgb_solver_vmult_with_residual_update": (_i, [_vp, _vp, _vp, _d, C.POINTER(C.c_double)]),
     "mgb_solver_do_matvec": (_i, [_vp]),
     "mgb_solver_do_matvec_smoother": (_i, [_vp]),
     "mgb_solver_timings": (_i, [_vp, _dp, _i]),
@@ -140,6 +141,8 @@ SYMBOLS = {
     "mgb_vec_sadd": (_i, [_vp, _i, _i, _vp, _d, _d, _vp]),
     "mgb_vec_set": (_i, [_vp, _i, _i, _vp, _d]),
     "mgb_vec_update_ghost_values": (_i, [_vp, _i, _i, _vp]),
+    "mgb_vec_compress_add": (_i, [_vp, _i, _i, _vp]),
+    "mgb_vec_zero_out_ghost_values": (_i, [_vp, _i, _i, _vp]),
     "mgb_device_alloc": (_i, [_vp, C.c_size_t, C.POINTER(_vp)]),
     "mgb_device_free": (_i, [_vp, _vp]),
     "mgb_copy_to_device": (_i, [_vp, _vp, _vp, C.c_size_t]),
@@ -494,6 +497,14 @@ class MultigridSolver:
         self._torch_sync()
         _check(lib().mgb_solver_vcycle(self.h, _ptr(dst), _ptr(src)))
         self.sync()
+
+    def vmult_with_residual_update(self, residual, update, factor):
+        """multigrid_solver.h:516-619: residual += factor update; update = V-cycle(residual); returns
+        (<update, residual>, <update, factor update_old>)."""
+        self._torch_sync()
+        sums = (C.c_double * 2)()
+        _check(lib().mgb_solver_vmult_with_residual_update(self.h, _ptr(residual), _ptr(update), float(factor), sums))
+        return sums[0], sums[1]
 
     def do_matvec(self):
         _check(lib().mgb_solver_do_matvec(self.h))

@@ -19,6 +19,7 @@
 // cf. the pre/post range operations of laplace_operator.h:607-741) is fused into the same pass and
 // each vector is read / written exactly once from HBM; there are no atomics and no index table.
 #pragma once
+#include <algorithm>
 #include <cstdlib>
 #include <type_traits>
 #include <utility>
@@ -142,6 +143,12 @@ namespace mgb
   constexpr int APPLY_CHEBYSHEV_FIRST = 4;
   // dst = A src together with the sum of src[i] dst[i] (first sum of vmult_with_cg_update, laplace_operator.h:698)
   constexpr int APPLY_SET_DOT = 5;
+  // Chebyshev with a zero initial guess (deal.II PreconditionChebyshev::vmult): the iterate x_1 = f0 P^-1 b is never
+  // stored.  ZERO is iteration index 1 with the source x_1 formed on the fly from the staged planes of b and P^-1
+  // (x_0 = 0 implied); DERIVED is iteration index 2, whose x_{k-1} = x_1 is recomputed from the operands b and P^-1
+  // it loads anyway.  Same float operations as the stored variant, (f0 * P^-1) * b, so the results are bit-identical.
+  constexpr int APPLY_CHEBYSHEV_ZERO    = 6;
+  constexpr int APPLY_CHEBYSHEV_DERIVED = 7;
 
   // Operands of the fused vector operation (the post-range operation of laplace_operator.h:607-741) on
   // COUNT planes of one point column: loaded early (load_operands, before the y-stage) so that their
@@ -163,7 +170,8 @@ namespace mgb
     const T *__restrict__ rhs = A.rhs;
     const T *__restrict__ inv = A.inv_diag;
     const T *__restrict__ dst = A.dst;
-    constexpr bool CHEB = MODE == APPLY_CHEBYSHEV || MODE == APPLY_CHEBYSHEV_FIRST;
+    constexpr bool CHEB = MODE == APPLY_CHEBYSHEV || MODE == APPLY_CHEBYSHEV_FIRST || MODE == APPLY_CHEBYSHEV_ZERO ||
+                          MODE == APPLY_CHEBYSHEV_DERIVED;
 #pragma unroll
     for (int r = 0; r < COUNT; ++r)
       {
@@ -172,7 +180,7 @@ namespace mgb
           o.os[r] = dst[d];
         else
           {
-            if (CHEB || MODE == APPLY_SET_DOT || (BND && ((con >> r) & 1u)))
+            if (MODE != APPLY_CHEBYSHEV_ZERO && (CHEB || MODE == APPLY_SET_DOT || (BND && ((con >> r) & 1u))))
               o.xs[r] = src[d];
             if (MODE != APPLY_SET && MODE != APPLY_SET_DOT)
               o.rs[r] = rhs[d];
@@ -191,13 +199,18 @@ namespace mgb
   {
     double dot = 0;
     T *__restrict__ dst = A.dst;
-    const T f1 = A.f1, f2 = A.f2, f1p = T(1) + A.f1;
+    const T f1 = A.f1, f2 = A.f2, f1p = T(1) + A.f1, f0 = A.f0;
 #pragma unroll
     for (int r = 0; r < COUNT; ++r)
       {
         const uint32_t d = d0 + r * stride;
         const bool     c = BND && ((con >> r) & 1u);
         T              v = y[r];
+        T              xs = o.xs[r], os = o.os[r];
+        if (MODE == APPLY_CHEBYSHEV_ZERO)
+          xs = (f0 * o.ds[r]) * o.rs[r]; // x_1 at this point, as staged for the stages
+        if (MODE == APPLY_CHEBYSHEV_DERIVED)
+          os = (f0 * o.ds[r]) * o.rs[r]; // x_{k-1} = x_1
         if (MODE == APPLY_ADD)
           {
             if (!c)
@@ -205,21 +218,21 @@ namespace mgb
             continue;
           }
         if (c)
-          v = o.xs[r]; // identity rows (laplace_operator.h:592-593, :632-633)
+          v = xs; // identity rows (laplace_operator.h:592-593, :632-633)
         if (MODE == APPLY_SET)
           dst[d] = v;
         else if (MODE == APPLY_SET_DOT)
           {
             dst[d] = v;
-            dot += (double)o.xs[r] * (double)v;
+            dot += (double)xs * (double)v;
           }
         else if (MODE == APPLY_RESIDUAL)
           dst[d] = o.rs[r] - v;
         else
           {
-            T t = f2 * o.ds[r] * (o.rs[r] - v) + f1p * o.xs[r];
-            if (MODE == APPLY_CHEBYSHEV)
-              t -= f1 * o.os[r];
+            T t = f2 * o.ds[r] * (o.rs[r] - v) + f1p * xs;
+            if (MODE == APPLY_CHEBYSHEV || MODE == APPLY_CHEBYSHEV_DERIVED)
+              t -= f1 * os;
             dst[d] = t;
           }
       }
@@ -545,16 +558,30 @@ namespace mgb
     return on;
   }
 
+  // MGB200_SHORT_SEGMENTS=0 keeps segments of >= 4 cell layers on every level (A/B measurements)
+  inline bool
+  use_short_segments()
+  {
+    static const bool on = [] {
+      const char *e = getenv("MGB200_SHORT_SEGMENTS");
+      return !(e && e[0] == '0');
+    }();
+    return on;
+  }
+
   template <int p, typename T, int MODE>
   void
   launch_apply_tile(const ApplyArgs<T> &A, cudaStream_t stream)
   {
     using C           = TileCfg<p>;
-    const size_t smem = (size_t)C::SMEM * sizeof(T), smem2 = (size_t)C::SMEM2 * sizeof(float);
+    // the zero-guess Chebyshev instance stages the planes of b and P^-1: one more double-buffered plane array
+    const size_t smem  = (size_t)C::SMEM * sizeof(T),
+                 smem2 = (size_t)(C::SMEM2 + (MODE == APPLY_CHEBYSHEV_ZERO ? 2 * C::U_SIZE : 0)) * sizeof(float);
     static bool  first = true;
     if (first)
       {
-        cudaFuncSetAttribute(k_apply_tile<p, T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if constexpr (MODE != APPLY_CHEBYSHEV_ZERO && MODE != APPLY_CHEBYSHEV_DERIVED)
+          cudaFuncSetAttribute(k_apply_tile<p, T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if constexpr (std::is_same<T, float>::value)
           cudaFuncSetAttribute(k_apply_tile_f32x2<p, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
         first = false;
@@ -572,6 +599,12 @@ namespace mgb
       nseg = ncz / 4;
     if (nseg < 1)
       nseg = 1;
+    // small levels cannot fill the device with segments of >= 4 layers: a block is a serial chain of
+    // (layers + 2) batches, so shorter segments (down to one layer, at the price of re-computing the carry
+    // layer) cut the latency of the launch-bound coarse levels roughly in half
+    const int slots = 148 * TileMinBlocks<MODE, T>::value;
+    if (ntiles * nseg < slots && use_short_segments())
+      nseg = std::max(nseg, std::min(ncz, slots / ntiles));
     int lps = (ncz + nseg - 1) / nseg;
     nseg    = (ncz + lps - 1) / lps;
     if (A.layer_begin2 >= 0) // the first and the last owned layer of a z-slab: one segment each
@@ -580,12 +613,13 @@ namespace mgb
         nseg = 2;
       }
     if constexpr (std::is_same<T, float>::value)
-      if (use_f32x2())
+      if (use_f32x2() || MODE == APPLY_CHEBYSHEV_ZERO || MODE == APPLY_CHEBYSHEV_DERIVED)
         {
           k_apply_tile_f32x2<p, MODE><<<ntiles * nseg, C::NT, smem2, stream>>>(A, lps, l0, l1);
           return;
         }
-    k_apply_tile<p, T, MODE><<<ntiles * nseg, C::NT, smem, stream>>>(A, lps, l0, l1);
+    if constexpr (MODE != APPLY_CHEBYSHEV_ZERO && MODE != APPLY_CHEBYSHEV_DERIVED)
+      k_apply_tile<p, T, MODE><<<ntiles * nseg, C::NT, smem, stream>>>(A, lps, l0, l1);
   }
 
   template <int p, typename T>
@@ -606,6 +640,16 @@ namespace mgb
           break;
         case APPLY_RESIDUAL: launch_apply_tile<p, T, APPLY_RESIDUAL>(A, stream); break;
         default:
+          if constexpr (std::is_same<T, float>::value)
+            if (A.first_chebyshev >= 2)
+              {
+                // zero-guess variants (packed float kernel only; solver.cu never asks for them otherwise)
+                if (A.first_chebyshev == 2)
+                  launch_apply_tile<p, T, APPLY_CHEBYSHEV_ZERO>(A, stream);
+                else
+                  launch_apply_tile<p, T, APPLY_CHEBYSHEV_DERIVED>(A, stream);
+                break;
+              }
           if (A.first_chebyshev)
             launch_apply_tile<p, T, APPLY_CHEBYSHEV_FIRST>(A, stream);
           else

@@ -78,6 +78,11 @@ namespace mgb
     T      *u_s   = reinterpret_cast<T *>(smem_raw);                    // [buffer][plane][row J'+p][col I'+p]
     float2 *mk_s  = reinterpret_cast<float2 *>(u_s + 2 * C::U_SIZE);    // (mx, kx) [plane][I][row J'+p]
     float2 *qp_s  = mk_s + p * C::MXP2;                                // (Q, P)  [plane (pitch PQP)][J][I]
+    // zero-guess Chebyshev: u_s stages the planes of b, v_s (same shape, behind everything else) those of P^-1;
+    // u_s is turned into x_1 = (f0 P^-1) b in place once the copies have landed
+    constexpr bool ZERO  = MODE == APPLY_CHEBYSHEV_ZERO;
+    constexpr int  V_OFF = C::SMEM2; // v_s - u_s in floats
+    T             *v_s   = u_s + V_OFF;
 
     const LevelDesc &L      = A.L;
     const int        tid    = threadIdx.x;
@@ -105,8 +110,9 @@ namespace mgb
           ok = false; // Dirichlet in x or y; the z-faces are handled per plane
         src_bytes[l]  = ok ? (int)sizeof(T) : 0; // 0: the copy writes a zero
         src_stride[l] = ok ? (int)plane_pitch(L) : 0;
-        src_ptr[l]    = A.src + (ok ? dof_index(L, gi, gj, 0) : 0u);
+        src_ptr[l]    = (ZERO ? A.rhs : A.src) + (ok ? dof_index(L, gi, gj, 0) : 0u);
       }
+    const ptrdiff_t inv_delta = ZERO ? A.inv_diag - A.rhs : 0; // P^-1 sits at the same index as b
     // planes that read as zero: outside the grid, or on a Dirichlet z-face
     const int k_lo = (!plain && (L.dirichlet & 16u)) ? 1 : 0;
     const int k_hi = (!plain && (L.dirichlet & 32u)) ? nd2 - 2 : nd2 - 1;
@@ -177,6 +183,9 @@ namespace mgb
                 static_for<p>([&](auto bc) {
                   constexpr int b = decltype(bc)::value;
                   cp_async_imm<T, (b * NI * NI + l * NT) * (int)sizeof(T)>(sb, g + b * src_stride[l], src_bytes[l]);
+                  if (ZERO)
+                    cp_async_imm<T, (V_OFF + b * NI * NI + l * NT) * (int)sizeof(T)>(sb, g + b * src_stride[l] + inv_delta,
+                                                                                    src_bytes[l]);
                 });
               }
           });
@@ -191,8 +200,12 @@ namespace mgb
 #pragma unroll
               for (int l = 0; l < NL; ++l)
                 if (tid + l * NT < NI * NI)
-                  cp_async_value(u_s + (buf * p + b) * NI * NI + tid + l * NT,
-                                 okz ? src_ptr[l] + (size_t)gk * src_stride[l] : A.src, okz && src_bytes[l] != 0);
+                  {
+                    const T *g = okz ? src_ptr[l] + (size_t)gk * src_stride[l] : src_ptr[l];
+                    cp_async_value(u_s + (buf * p + b) * NI * NI + tid + l * NT, g, okz && src_bytes[l] != 0);
+                    if (ZERO)
+                      cp_async_value(v_s + (buf * p + b) * NI * NI + tid + l * NT, g + inv_delta, okz && src_bytes[l] != 0);
+                  }
             }
         }
       asm volatile("cp.async.commit_group;\n" ::);
@@ -207,7 +220,21 @@ namespace mgb
       {
         // (a) the planes of this batch have landed; prefetch the next batch into the other buffer
         const int cur = (c - c_begin + 1) & 1;
-        asm volatile("cp.async.wait_group 0;\n" ::);
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        if (ZERO)
+          {
+            // x_1 = (f0 P^-1) b on the elements this thread copied itself (they have landed for it)
+            const T f0 = A.f0;
+#pragma unroll
+            for (int b = 0; b < p; ++b)
+#pragma unroll
+              for (int l = 0; l < NL; ++l)
+                if (l + 1 < NL || tid + l * NT < NI * NI)
+                  {
+                    const int e = (cur * p + b) * NI * NI + tid + l * NT;
+                    u_s[e]      = (f0 * v_s[e]) * u_s[e];
+                  }
+          }
         __syncthreads();
         if (c + 1 < c1)
           issue_loads(c + 1, cur ^ 1);

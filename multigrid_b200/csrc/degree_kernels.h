@@ -29,9 +29,12 @@ namespace mgb
     const T  *coef_q;   // per-quadrature-point merged coefficient [cell][6][n^3] or nullptr
     T         coef[6];  // affine constant-coefficient merged tensor (without quadrature weight)
     T         f1, f2;
+    T         f0;            // zero-guess Chebyshev (first_chebyshev >= 2): x_1 = f0 P^-1 rhs
     int       mode;
     int       read_plain;    // 1: do not zero constrained entries on read (compute_residual)
-    int       first_chebyshev; // 1: x_{k-1} = 0 implied (iteration_index == 1)
+    int       first_chebyshev; // 1: x_{k-1} = 0 implied (iteration_index == 1); tile kernel, float: 2 = index 1 of a zero
+                               // initial guess (src = f0 P^-1 rhs formed on the fly, `src` unused), 3 = index 2 of it
+                               // (x_{k-1} = f0 P^-1 rhs recomputed instead of read from dst)
     int       layer_begin, layer_end; // tile kernel: local cell layers of this launch (-1: all owned layers)
     int       layer_begin2;           // tile kernel: if >= 0 the launch works on the two single layers layer_begin and layer_begin2
     double   *dot_out;   // APPLY_SET on the tile kernel: if set, sum of src[i] * dst[i] over the stored points is added here

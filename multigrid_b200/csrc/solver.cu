@@ -292,6 +292,7 @@ namespace mgb
       int         cls;
     };
     std::vector<Range>       open_ranges;
+    int                      range_depth = 0; // ranges begun but not yet ended (they nest)
     std::vector<cudaEvent_t> event_pool;
     std::vector<double>      class_ms;
     std::vector<int64_t>     class_count;
@@ -316,7 +317,9 @@ namespace mgb
     {
       if (!profile)
         return -1;
-      if (open_ranges.size() > 200000)
+      // flush only between top-level ranges: an enclosing range has no end event yet and its
+      // handle (an index into open_ranges) must stay valid until its range_end
+      if (open_ranges.size() > 200000 && range_depth == 0)
         collect_ranges();
       Range r;
       r.a   = get_event();
@@ -324,18 +327,22 @@ namespace mgb
       r.cls = level * n_classes_per_level + kind;
       MGB_CUDA_CHECK(cudaEventRecord(r.a, stream));
       open_ranges.push_back(r);
+      ++range_depth;
       return (int)open_ranges.size() - 1;
     }
     void
     range_end(const int handle)
     {
-      if (handle >= 0)
-        cudaEventRecord(open_ranges[handle].b, stream); // called from destructors: never throws
+      if (handle >= 0 && (size_t)handle < open_ranges.size())
+        {
+          cudaEventRecord(open_ranges[handle].b, stream); // called from destructors: never throws
+          --range_depth;
+        }
     }
     void
     collect_ranges()
     {
-      if (open_ranges.empty())
+      if (open_ranges.empty() || range_depth != 0)
         return;
       MGB_CUDA_CHECK(cudaStreamSynchronize(stream));
       for (const Range &r : open_ranges)
@@ -911,6 +918,72 @@ namespace mgb
     }
   };
 
+  // LinearAlgebra::distributed::Vector::compress(VectorOperation::add) in full (the C-ABI entry behind
+  // multigrid::DeviceVector::compress): BOTH ghost ranges travel to their owners and are added there -- the
+  // plane on top into the first owned plane of the rank above, the p planes below into the top p owned planes
+  // of the rank below -- and the ghost entries are zeroed afterwards, as deal.II leaves them.
+  template <typename T>
+  void
+  compress_add_all(Level &l, T *v)
+  {
+    if (!l.slab.distributed)
+      return;
+    Ctx               &c    = *l.ctx;
+    const ExchangePlan &pl  = l.plan;
+    const bool         up = l.d.ztop != 0, dn = l.d.zg != 0;
+    DVec<T>            buf_up, buf_dn; // what arrives from below (for send_dn range) / from above (for send_up range)
+    if (dn)
+      buf_up.alloc(pl.send_dn[1], c.stream);
+    if (up)
+      buf_dn.alloc(pl.send_up[1], c.stream);
+    Nccl &n = Nccl::get();
+    n.check(n.GroupStart(), "ncclGroupStart");
+    if (up)
+      {
+        n.check(n.Send(v + pl.recv_up[0], pl.recv_up[1] * sizeof(T), ncclInt8, c.rank + 1, c.comm, c.stream), "ncclSend");
+        n.check(n.Recv(buf_dn.p, pl.send_up[1] * sizeof(T), ncclInt8, c.rank + 1, c.comm, c.stream), "ncclRecv");
+      }
+    if (dn)
+      {
+        n.check(n.Send(v + pl.recv_dn[0], pl.recv_dn[1] * sizeof(T), ncclInt8, c.rank - 1, c.comm, c.stream), "ncclSend");
+        n.check(n.Recv(buf_up.p, pl.send_dn[1] * sizeof(T), ncclInt8, c.rank - 1, c.comm, c.stream), "ncclRecv");
+      }
+    n.check(n.GroupEnd(), "ncclGroupEnd");
+    ++c.exchanges;
+    if (dn)
+      {
+        T *own = v + pl.send_dn[0], *b = buf_up.p, *ghost = v + pl.recv_dn[0];
+        foreach (c, pl.send_dn[1], [=] __device__(size_t i) { own[i] += b[i]; });
+        foreach (c, pl.recv_dn[1], [=] __device__(size_t i) { ghost[i] = T(0); });
+      }
+    if (up)
+      {
+        T *own = v + pl.send_up[0], *b = buf_dn.p, *ghost = v + pl.recv_up[0];
+        foreach (c, pl.send_up[1], [=] __device__(size_t i) { own[i] += b[i]; });
+        foreach (c, pl.recv_up[1], [=] __device__(size_t i) { ghost[i] = T(0); });
+      }
+    c.sync(); // the temporaries are released on return
+  }
+
+  template <typename T>
+  void
+  zero_ghosts(Level &l, T *v)
+  {
+    if (!l.slab.distributed)
+      return;
+    Ctx &c = *l.ctx;
+    if (l.d.zg)
+      {
+        T *ghost = v + l.plan.recv_dn[0];
+        foreach (c, l.plan.recv_dn[1], [=] __device__(size_t i) { ghost[i] = T(0); });
+      }
+    if (l.d.ztop)
+      {
+        T *ghost = v + l.plan.recv_up[0];
+        foreach (c, l.plan.recv_up[1], [=] __device__(size_t i) { ghost[i] = T(0); });
+      }
+  }
+
   struct Nodes1D
   {
     double nodes[9], xq[9], w[9];
@@ -1035,6 +1108,7 @@ namespace mgb
       for (int i = 0; i < 6; ++i)
         A.coef[i] = coef[i];
       A.f1 = A.f2       = 0;
+      A.f0              = 0;
       A.mode            = APPLY_ADD;
       A.read_plain      = 0;
       A.first_chebyshev = 0;
@@ -1073,8 +1147,8 @@ namespace mgb
     // the one entry point behind vmult / vmult_add / vmult_residual / Chebyshev step
     void
     apply(const int mode, T *dst, const T *src, const T *rhs = nullptr, const T *inv_diag = nullptr,
-          const T f1 = 0, const T f2 = 0, const bool first = false, const bool read_plain = false,
-          double *dot_out = nullptr)
+          const T f1 = 0, const T f2 = 0, const int first = 0, const bool read_plain = false,
+          double *dot_out = nullptr, const T f0 = 0)
     {
       ApplyArgs<T> A;
       fill_args(A, src, dst);
@@ -1084,8 +1158,13 @@ namespace mgb
       A.inv_diag        = inv_diag;
       A.f1              = f1;
       A.f2              = f2;
+      A.f0              = f0;
       A.first_chebyshev = first;
       A.read_plain      = read_plain;
+      // zero-guess Chebyshev (first == 2): the source x_1 = f0 P^-1 rhs is formed inside the tile kernel, so it is
+      // the ghost planes of rhs that have to be current (those of P^-1 are, compute_diagonal)
+      if (first == 2)
+        src = rhs;
       // update_ghost_values of the source (laplace_operator.h:590): like the reference's vmult, this
       // mutates the ghost range of the const source vector
       if (use_cartesian())
@@ -1164,7 +1243,7 @@ namespace mgb
       else
         foreach (*ctx, N, [=] __device__(size_t d) {
           const T upd = f2 * inv_diag[d] * (rhs[d] - acc[d]);
-          dst[d] = first ? (T(1) + f1) * src[d] + upd : (T(1) + f1) * src[d] - f1 * dst[d] + upd;
+          dst[d] = first != 0 ? (T(1) + f1) * src[d] + upd : (T(1) + f1) * src[d] - f1 * dst[d] + upd;
         });
     }
 
@@ -1411,27 +1490,38 @@ namespace mgb
     // x_{k+1} = (1+f1) x_k - f1 x_{k-1} + f2 P^-1 (b - A x_k), fused with the operator apply;
     // the result lands in solution_old and the two vectors are swapped (as deal.II does)
     void
-    fused_step(DVec<T> &x, const T *b, const double f1, const double f2, const bool first)
+    fused_step(DVec<T> &x, const T *b, const double f1, const double f2, const int first, const T f0 = 0)
     {
-      A->apply(APPLY_CHEBYSHEV, solution_old.p, x.p, b, A->inverse_diagonal.p, (T)f1, (T)f2, first);
+      A->apply(APPLY_CHEBYSHEV, solution_old.p, x.p, b, A->inverse_diagonal.p, (T)f1, (T)f2, first, false, nullptr, f0);
       x.swap(solution_old);
     }
 
+    // `zero_guess`: the iterate x_1 = f0 P^-1 b was not stored (vmult on the packed float tile kernel): step k = 0
+    // forms it on the fly, step k = 1 recomputes it as x_{k-1}
     void
-    loop(DVec<T> &x, const T *b, const bool first_is_index_one)
+    loop(DVec<T> &x, const T *b, const bool first_is_index_one, const bool zero_guess = false)
     {
       if (degree < 2)
         return;
       double       rhok  = delta / theta;
       const double sigma = theta / delta;
+      const T      f0    = (T)(1. / theta);
       for (unsigned int k = 0; k < degree - 1; ++k)
         {
           const double rhokp = 1. / (2. * sigma - rhok);
           const double f1 = rhokp * rhok, f2 = 2. * rhokp / delta;
           rhok = rhokp;
-          fused_step(x, b, f1, f2, first_is_index_one && k == 0);
+          if (zero_guess && k < 2)
+            fused_step(x, b, f1, f2, k == 0 ? 2 : 3, f0);
+          else
+            fused_step(x, b, f1, f2, first_is_index_one && k == 0 ? 1 : 0);
         }
     }
+
+    // MGB200_FUSE_ZERO_GUESS=0: store x_1 with a separate pass as before (A/B measurements)
+    // (only the packed float tile kernel has the zero-guess instances: MGB200_F32X2=0 switches them off as well)
+    bool fuse_zero_guess = (getenv("MGB200_FUSE_ZERO_GUESS") == nullptr || getenv("MGB200_FUSE_ZERO_GUESS")[0] != '0') &&
+                           (getenv("MGB200_F32X2") == nullptr || getenv("MGB200_F32X2")[0] != '0');
 
     // zero initial guess (deal.II vmult): x = 1/theta P^-1 b, then degree-1 fused steps
     void
@@ -1440,7 +1530,13 @@ namespace mgb
       T       *xp = x.p;
       const T *P  = A->inverse_diagonal.p;
       const T  f2 = (T)(1. / theta);
-      foreach (*ctx, x.n, [=] __device__(size_t i) { xp[i] = f2 * P[i] * b[i]; });
+      if (std::is_same<T, float>::value && degree >= 2 && fuse_zero_guess && A->use_cartesian())
+        {
+          // x_1 never touches HBM: 28 instead of 48 bytes per DoF for the three-step pre-smoother
+          loop(x, b, true, true);
+          return;
+        }
+      foreach (*ctx, x.n, [=] __device__(size_t i) { xp[i] = (f2 * P[i]) * b[i]; });
       loop(x, b, true);
     }
 
@@ -1555,6 +1651,7 @@ namespace mgb
     std::vector<std::unique_ptr<DVec<double>>>            solution, rhs, residual, bc_values;
     std::vector<std::unique_ptr<DVec<float>>>             defect, t, solution_update;
     DVec<double>                                          cg_g, cg_h, cg_d;
+    DVec<double>                                          con_scratch; // vmult_with_residual_update: parked identity rows
     std::vector<double>                                   cg_history;
 
     explicit MultigridSolver(const mgb_options &o)
@@ -1972,6 +2069,92 @@ namespace mgb
       }
     }
 
+    // multigrid_solver.h:516-619: the preconditioner entry of a merged CG.  defect = float(residual + factor update);
+    // V-cycle; then in ONE pass over the vectors  residual += factor update,  update = double(V-cycle result) and the
+    // sums  <z, residual_new>, <z, factor update_old>  (z = the new update) over the owned entries of all ranks.
+    // Dirichlet rows are identity rows of the preconditioner (:570-577, :598-603): z = residual_new there.
+    // factor == 0 skips the residual update; both sums are then <z, residual>.
+    std::array<double, 2>
+    vmult_with_residual_update(double *residual, double *update, const double factor)
+    {
+      const int    L   = n_levels - 1;
+      Level       &lvl = *levels[L];
+      const size_t N   = lvl.d.n_dofs;
+      const Span   own = lvl.owned();
+      float       *def = defect[L]->p;
+      {
+        ScopedRange range(ctx, L, RK_MG_VEC);
+        if (factor != 0.)
+          foreach (ctx, N, [=] __device__(size_t i) { def[i] = (float)(residual[i] + factor * update[i]); });
+        else
+          convert(ctx, def, residual, N);
+      }
+      v_cycle(L, 1);
+      float         *z     = solution_update[L]->p;
+      const uint32_t *clist = lvl.constrained.p;
+      const size_t   nc    = lvl.constrained.n;
+      const size_t   o0 = own.off, o1 = own.off + own.n;
+      double         sums[2];
+      ScopedRange    range(ctx, L, RK_MG_VEC);
+      // identity rows: park (residual_new, factor update_old) of the constrained DoFs and zero the V-cycle result
+      // there, so that the main pass contributes nothing for them
+      if (con_scratch.n < 2 * nc)
+        con_scratch.alloc(2 * nc, ctx.stream);
+      double *park = con_scratch.p;
+      foreach (ctx, nc, [=] __device__(size_t k) {
+        const uint32_t i = clist[k];
+        const double   fu = factor != 0. ? factor * update[i] : 0.;
+        park[2 * k]       = residual[i] + fu;
+        park[2 * k + 1]   = fu;
+        z[i]              = 0.f;
+      });
+      reduce<2>(
+        ctx,
+        own,
+        [=] __device__(size_t i, double *acc) {
+          const double mg = (double)z[i], fu = factor != 0. ? factor * update[i] : 0.;
+          const double res = residual[i] + fu;
+          residual[i]      = res;
+          update[i]        = mg;
+          acc[0] += mg * res;
+          acc[1] += mg * fu;
+        },
+        sums);
+      if (nc)
+        {
+          double fix[2];
+          reduce<2>(
+            ctx,
+            Span(0, nc, own.all_ranks),
+            [=] __device__(size_t k, double *acc) {
+              const uint32_t i = clist[k];
+              const double   res = park[2 * k];
+              update[i]          = res;
+              residual[i]        = res;
+              if (i >= o0 && i < o1)
+                {
+                  acc[0] += res * res;
+                  acc[1] += res * park[2 * k + 1];
+                }
+            },
+            fix);
+          sums[0] += fix[0];
+          sums[1] += fix[1];
+        }
+      else if (own.all_ranks)
+        {
+          // every rank must take part in the all-reduce of the fix-up even without constrained DoFs of its own
+          double fix[2];
+          reduce<2>(ctx, Span(0, 0, true), [=] __device__(size_t, double *) {}, fix);
+          sums[0] += fix[0];
+          sums[1] += fix[1];
+        }
+      if (factor == 0.)
+        sums[1] = sums[0];
+      // (ghost planes of a z-slab are left alone: every consumer refreshes them, section 7 of DESIGN.md)
+      return {{sums[0], sums[1]}};
+    }
+
     // multigrid_solver.h:483-493 + deal.II SolverCG with ReductionControl(1000, 1e-16, 1e-9)
     std::pair<unsigned int, double>
     solve_cg()
@@ -2010,6 +2193,9 @@ namespace mgb
       if (res > 1e-16)
         {
           double gh = 0;
+          // x += alpha d is postponed into the next direction update (which reads d anyway) or the final pass:
+          // 8 bytes per DoF and iteration less than updating x together with the residual
+          double alpha_pending = 0;
           for (;;)
             {
               v_cycle(L, 1); // solution_update[L] = M^-1 defect[L]
@@ -2023,8 +2209,12 @@ namespace mgb
                   foreach (ctx, N, [=] __device__(size_t i) { d[i] = -(double)upd[i]; });
                 else
                   {
-                    const double beta = gh_new / gh;
-                    foreach (ctx, N, [=] __device__(size_t i) { d[i] = beta * d[i] - (double)upd[i]; });
+                    const double beta = gh_new / gh, ap = alpha_pending;
+                    foreach (ctx, N, [=] __device__(size_t i) {
+                      const double di = d[i];
+                      x[i] += ap * di;
+                      d[i] = beta * di - (double)upd[i];
+                    });
                   }
                 gh = gh_new;
               }
@@ -2034,11 +2224,11 @@ namespace mgb
               {
                 ScopedRange  range(ctx, L, RK_CG_VEC);
                 const double alpha = gh / dh;
+                alpha_pending      = alpha;
                 reduce<1>(
                   ctx,
                   own,
                   [=] __device__(size_t i, double *acc) {
-                    x[i] += alpha * d[i];
                     const double gi = g[i] + alpha * h[i];
                     g[i]            = gi;
                     def[i]          = (float)gi;
@@ -2051,6 +2241,11 @@ namespace mgb
               if (res <= 1e-16 || res <= 1e-9 * res0 || it >= 1000)
                 break;
             }
+          {
+            ScopedRange  range(ctx, L, RK_CG_VEC);
+            const double ap = alpha_pending;
+            foreach (ctx, N, [=] __device__(size_t i) { x[i] += ap * d[i]; });
+          }
         }
       ctx.sync();
       return std::make_pair(it, it > 0 ? std::pow(res / res0, 1. / it) : 0.);
@@ -2471,6 +2666,16 @@ extern "C"
   {
     MGB_TRY
     S(s).vmult(dst_dev, src_dev);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_vmult_with_residual_update(mgb_solver s, double *residual_dev, double *update_dev, double factor, double sums[2])
+  {
+    MGB_TRY
+    const std::array<double, 2> r = S(s).vmult_with_residual_update(residual_dev, update_dev, factor);
+    sums[0]                       = r[0];
+    sums[1]                       = r[1];
     MGB_CATCH
   }
 
@@ -2907,6 +3112,32 @@ extern "C"
       m.levels[level]->update_ghosts(static_cast<double *>(v));
     else
       m.levels[level]->update_ghosts(static_cast<float *>(v));
+    MGB_CATCH
+  }
+
+  int
+  mgb_vec_compress_add(mgb_solver s, int level, int precision, void *v)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (precision == MGB_F64)
+      compress_add_all(*m.levels[level], static_cast<double *>(v));
+    else
+      compress_add_all(*m.levels[level], static_cast<float *>(v));
+    MGB_CATCH
+  }
+
+  int
+  mgb_vec_zero_out_ghost_values(mgb_solver s, int level, int precision, void *v)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (precision == MGB_F64)
+      zero_ghosts(*m.levels[level], static_cast<double *>(v));
+    else
+      zero_ghosts(*m.levels[level], static_cast<float *>(v));
     MGB_CATCH
   }
 

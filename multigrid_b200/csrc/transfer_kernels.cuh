@@ -429,6 +429,9 @@ namespace mgb
       nseg = ncz / 2;
     if (nseg < 1)
       nseg = 1;
+    // small levels: one parent layer per block rather than an idle device (as launch_apply_tile)
+    if (ntiles * nseg < 148 * 4 && use_short_segments())
+      nseg = std::max(nseg, std::min(ncz, 148 * 4 / ntiles));
     const int lps = (ncz + nseg - 1) / nseg;
     nseg          = (ncz + lps - 1) / lps;
     if (A.mode == 0)

@@ -30,6 +30,9 @@
 #include <cstring>
 #include <memory>
 #include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #include "basis1d.h"
 
@@ -1562,6 +1565,28 @@ extern "C"
       else
         s->matrix[L].vmult(s->solution_update[L].data(), s->defect[L].data());
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() / n_mv;
+  }
+
+  // threads the OpenMP runtime really uses (bench.py reports this, not the value it asked for)
+  int
+  orc_omp_max_threads()
+  {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+  }
+
+  void
+  orc_omp_set_threads(int n)
+  {
+#ifdef _OPENMP
+    if (n > 0)
+      omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
   }
 
   void

@@ -26,6 +26,13 @@ def build(force=False):
 _lib = None
 
 
+def omp_threads(n=None):
+    """set (n given) and return the thread count the OpenMP runtime of the oracle uses"""
+    if n is not None:
+        lib().orc_omp_set_threads(int(n))
+    return int(lib().orc_omp_max_threads())
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -59,6 +66,8 @@ def lib():
         L.orc_mg_vcycle.argtypes = [C.c_void_p, dp, dp]
         L.orc_mg_time_matvec.restype = C.c_double
         L.orc_mg_time_matvec.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.orc_omp_max_threads.restype = C.c_int
+        L.orc_omp_set_threads.argtypes = [C.c_int]
         L.orc_mg_setup_times.argtypes = [C.c_void_p, dp]
         L.orc_basis.argtypes = [C.c_int] + [dp] * 7
         L.dgo_create.restype = C.c_void_p

@@ -105,8 +105,30 @@ def main():
             got, ref = sc.owned_pair(coarse, o.restrict_and_add(x, level))
             assert rel(got, ref) < 1e-5, ("restrict", level, rel(got, ref))
             n_checked += 3
-    # V-cycle as preconditioner, FMG, CG
+    # compress(add) / zero_out_ghost_values of the vector interface (mgb_vec_compress_add): ghost planes are added
+    # to their owners on the neighbouring slabs, then zeroed
     sl = Slab(s, L)
+    for dt, prec in ((torch.float64, mgb.F64), (torch.float32, mgb.F32)):
+        v = torch.full((sl.nloc,), 2.0, dtype=dt, device="cuda")
+        v[torch.tensor(sl.own, device="cuda")] = 1.0
+        mgb._check(mgb.lib().mgb_vec_compress_add(s.h, L, prec, mgb._ptr(v)))
+        s.sync()
+        got = v.double().cpu().numpy()
+        ob, no = sl.q["owned_begin"], sl.q["n_owned"]
+        want = np.zeros(sl.nloc)
+        want[ob:ob + no] = 1.0
+        if rank > 0:                       # the plane shared with the top ghost plane of the rank below
+            want[ob:ob + sl.pitch] += 2.0
+        if rank + 1 < R:                   # the p planes the rank above holds as ghosts
+            want[ob + no - p * sl.pitch:ob + no] += 2.0
+        assert np.array_equal(got, want), ("compress_add", dt, np.abs(got - want).max())
+        v.fill_(5.0)
+        mgb._check(mgb.lib().mgb_vec_zero_out_ghost_values(s.h, L, prec, mgb._ptr(v)))
+        s.sync()
+        got = v.double().cpu().numpy()
+        assert np.all(got[sl.own] == 5.0) and np.all(got[~sl.own] == 0.0), "zero_out_ghost_values"
+    n_checked += 4
+    # V-cycle as preconditioner, FMG, CG
     N = o.n_dofs(L)
     nd = s.dof_grid(L)
     mask = np.ones((nd[2] if not sl.q["distributed"] else sl.q["n_planes_global"], nd[1], nd[0]))

@@ -111,6 +111,32 @@ def test_variable_coefficient(mgb, orc, torch, mesh):
     assert rel(P.to_lex(d, -1), P.o.get_vector(orc.VEC_INV_DIAG)) <= 1e-5
 
 
+@pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 3), (3, (2, 1, 1), 2), (2, (1, 1, 1), 3)])
+def test_variable_coefficient_solve(mgb, orc, torch, mesh):
+    """solve_cg / FMG with the per-quadrature-point coefficient of poisson_shell/program.cc:97-225 on a box: right-hand
+    side on every level, identical CG iteration count, residual history, L2 error, solution"""
+    p, nsub, nref = mesh
+    P = Pair(mgb, orc, torch, p, nsub, nref, problem=1, lower=(0.1, 0.2, 0.3), upper=(0.9, 1.1, 1.0))
+    L = P.g.n_levels - 1
+    for level in range(P.g.n_levels):
+        rhs = P.g.get_vector("rhs", level)[P.lex(level)]
+        assert rel(rhs, P.o.get_vector(orc.VEC_RHS, level)) <= 1e-12, ("rhs", level)
+    its, rate = P.g.solve_cg()
+    its_o, rate_o, hist_o = P.o.solve_cg()
+    assert its == its_o, (its, its_o)
+    hist = P.g.cg_history()
+    assert np.allclose(hist, hist_o, rtol=0.05), (hist, hist_o)
+    e, e_o = P.g.compute_l2_error(), P.o.compute_l2_error()
+    assert abs(e - e_o) <= 1e-3 * e_o, (e, e_o)
+    sol = P.g.get_solution()[P.lex(L)]
+    assert rel(sol, P.o.get_vector(orc.VEC_SOLUTION)) <= 1e-6
+    red, trace = P.g.solve(True)
+    red_o, trace_o = P.o.solve(True)
+    assert np.allclose(trace[1:], trace_o[1:], rtol=3e-2), (trace, trace_o)
+    e, e_o = P.g.compute_l2_error(), P.o.compute_l2_error()
+    assert abs(e - e_o) <= 5e-3 * e_o, (e, e_o)
+
+
 @pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 2), (3, (2, 1, 3), 1), (1, (1, 1, 1), 2), (8, (1, 1, 1), 1)])
 def test_diagonal_and_cg_update(mgb, orc, torch, mesh):
     p, nsub, nref = mesh
@@ -225,6 +251,38 @@ def test_solver_against_oracle(mgb, orc, torch, mesh, kernel):
     assert abs(e - e_o) <= 1e-3 * e_o, (e, e_o)
     sol = P.g.get_solution()[P.lex(L)]
     assert rel(sol, P.o.get_vector(orc.VEC_SOLUTION)) <= 1e-6
+
+
+@pytest.mark.parametrize("mesh", [(4, 1, 2), (2, (1, 2, 1), 2)])
+def test_vmult_with_residual_update(mgb, orc, torch, mesh):
+    """MultigridSolver::vmult_with_residual_update (multigrid_solver.h:516-619) against its definition composed from the
+    oracle's V-cycle: residual += factor update, update = M^-1 residual (identity on Dirichlet rows), the two sums"""
+    p, nsub, nref = mesh
+    P = Pair(mgb, orc, torch, p, nsub, nref)
+    L = P.g.n_levels - 1
+    n = P.g.n_dofs()
+    nd = P.g.dof_grid()
+    interior = np.ones((nd[2], nd[1], nd[0]), dtype=bool)
+    interior[0], interior[-1], interior[:, 0], interior[:, -1], interior[:, :, 0], interior[:, :, -1] = (False,) * 6
+    interior = interior.ravel()
+    rng = np.random.default_rng(11)
+    for factor in (0.0, 0.37):
+        r, u = rng.random(n), rng.random(n)
+        dr, du = P.to_dev(r, L), P.to_dev(u, L)
+        s0, s1 = P.g.vmult_with_residual_update(dr, du, factor)
+        r_new = r + factor * u
+        z = P.o.vcycle(np.where(interior, r_new, 0.0))
+        z = np.where(interior, z, r_new)            # identity rows (:570-577, :598-603)
+        ref0 = float(z @ r_new)
+        ref1 = float(z @ (factor * u)) if factor != 0.0 else ref0
+        assert rel(P.to_lex(dr, L), r_new) <= 1e-14, factor
+        assert rel(P.to_lex(du, L), z) <= 5e-3, (factor, rel(P.to_lex(du, L), z))
+        assert abs(s0 - ref0) <= 5e-3 * abs(ref0) and abs(s1 - ref1) <= 5e-3 * abs(ref1), (factor, s0, ref0, s1, ref1)
+        # the sums are those of the vectors the call returned (exact, double)
+        zz, rr = P.to_lex(du, L), P.to_lex(dr, L)
+        assert abs(s0 - float(zz @ rr)) <= 1e-12 * abs(s0)
+        if factor != 0.0:
+            assert abs(s1 - float(zz @ (factor * u))) <= 1e-12 * abs(s1)
 
 
 def test_readme_golden_config1(mgb, torch):

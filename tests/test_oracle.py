@@ -184,3 +184,60 @@ def test_chebyshev_matches_textbook_recurrence(orc):
         x_old, x, rho = x, x_new, rho_new
     got = s.chebyshev_step(x0, b, 1)
     assert np.abs(got - x).max() <= 2e-5 * np.abs(x).max()
+
+
+def _even_odd(A):
+    """deal.II's even-odd compression of a 1-D table A[i][q] (basis function i at point q), the layout
+    `apply_1d_matvec_kernel` reads (matrix_vector_kernel.h:47-101): rows i < n/2 hold the even parts
+    (A[i][q] + A[i][n-1-q]) / 2, rows n-1-i the odd parts, the middle row the plain values; columns q < (n+1)/2."""
+    n = A.shape[0]
+    off, mid = (n + 1) // 2, n // 2
+    eo = np.zeros((n, off))
+    for i in range(mid):
+        for q in range(off):
+            eo[i, q] = 0.5 * (A[i, q] + A[i, n - 1 - q])
+            eo[n - 1 - i, q] = 0.5 * (A[i, q] - A[i, n - 1 - q])
+    if n % 2 == 1:
+        eo[mid, :] = A[mid, :off]
+    return np.ascontiguousarray(eo)
+
+
+@pytest.mark.parametrize("p", range(1, 9))
+def test_reference_even_odd_kernel(orc, p):
+    """The one piece of the reference that can be executed here: common/matrix_vector_kernel.h (compiled from where it
+    lies into oracle/_ref/libref1d.so by `make -C oracle ref`).  Its even-odd 1-D product, fed with the oracle's own
+    tables S (values of the Gauss-Lobatto basis in the Gauss points) and D (collocation derivative), must reproduce the
+    dense products the oracle and the CUDA kernels' host tables are built from -- evaluation (contract over rows) and
+    integration (the transpose), types 0 (symmetric) and 1 (anti-symmetric)."""
+    import ctypes as C
+    import subprocess
+    here = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle")
+    so = os.path.join(here, "_ref", "libref1d.so")
+    if os.path.exists("/root/reference/common/matrix_vector_kernel.h"):
+        subprocess.check_call(["make", "-C", here, "ref"], stdout=subprocess.DEVNULL)
+    if not os.path.exists(so):
+        pytest.skip("oracle/_ref/libref1d.so not built and /root/reference absent")
+    lib = C.CDLL(so)
+    dp = C.POINTER(C.c_double)
+    lib.ref_apply_1d.argtypes = [C.c_int, C.c_int, C.c_int, dp, dp, dp]
+    b = orc.basis(p)
+    n = p + 1
+    x = np.random.default_rng(p).random(n)
+    out = np.zeros(n)
+
+    def ref(table_iq, typ, rows):
+        eo = _even_odd(table_iq)
+        assert lib.ref_apply_1d(n, typ, int(rows), eo.ctypes.data_as(dp), x.ctypes.data_as(dp), out.ctypes.data_as(dp)) == 0
+        return out.copy()
+
+    S, D = b["S"], b["D"]            # S[q][i], D[q][r]
+    # the symmetries the compressed layout relies on (SURVEY appendix A.1)
+    assert np.allclose(S, S[::-1, ::-1], atol=1e-14) and np.allclose(D, -D[::-1, ::-1], atol=1e-13)
+    assert np.allclose(ref(S.T, 0, True), S @ x, atol=1e-14)       # evaluate: out[q] = sum_i S[q][i] x[i]
+    assert np.allclose(ref(S.T, 0, False), S.T @ x, atol=1e-14)    # integrate: out[i] = sum_q S[q][i] x[q]
+    assert np.allclose(ref(D.T, 1, True), D @ x, atol=1e-12)       # collocation derivative
+    assert np.allclose(ref(D.T, 1, False), D.T @ x, atol=1e-12)    # and its transpose
+    # G = D S is the gradient table the oracle's cell kernel applies (oracle/basis1d.h)
+    x_q = ref(S.T, 0, True)
+    x, keep = x_q, x
+    assert np.allclose(ref(D.T, 1, True), b["G"] @ keep, atol=1e-11)  # evaluate then differentiate, as the reference does
