@@ -46,6 +46,15 @@ enum {
   MGB_PROBLEM_SHELL_COEF = 1 /* poisson_shell/program.cc:70-225 functions (variable coeff) */
 };
 
+/* geometry of the structured mesh: the map from the unit box of mesh coordinates to physical space; inside a cell
+ * the geometry is the degree-p polynomial through the mapped support points (MappingQGeneric, multigrid_solver.h:138-139) */
+enum {
+  MGB_GEOMETRY_BOX = 0,          /* [lower, upper], axis-aligned cells (subdivided_hyper_rectangle)                        */
+  MGB_GEOMETRY_SHELL_SECTOR = 1, /* one of the six coarse cells of hyper_shell(0, r0, r1, 6), poisson_shell/program.cc:426,
+                                    and its refinements; geometry_params = {r0, r1, opening half-angle (pi/4: whole face)} */
+  MGB_GEOMETRY_AFFINE = 2        /* x = lower + A ((upper - lower) o xi), geometry_params[0..8] = A row-major (sheared cells) */
+};
+
 /* kernel selection for the operator apply */
 enum {
   MGB_KERNEL_AUTO = 0,     /* Cartesian streaming tile kernel where admissible              */
@@ -67,6 +76,8 @@ typedef struct mgb_options {
   int comm_rank;           /* this process' rank, 0 .. comm_size-1  (MPI_Comm_rank of the reference's MPI_COMM_WORLD) */
   int comm_size;           /* number of ranks = GPUs (0 or 1: one GPU, no communicator)                              */
   unsigned char comm_id[128]; /* mgb_comm_unique_id() of rank 0, distributed to all ranks by the caller              */
+  int geometry;            /* MGB_GEOMETRY_*  (MGB_GEOMETRY_BOX unless set)                                          */
+  double geometry_params[12];
 } mgb_options;
 
 const char *mgb_last_error(void);

@@ -24,6 +24,7 @@ LIB_PATH = os.environ.get("MGB200_LIB", os.path.join(_HERE, "libmgb200.so"))  # 
 F32, F64 = 0, 1
 PROBLEM_CUBE_SINE, PROBLEM_SHELL_COEF = 0, 1
 KERNEL_AUTO, KERNEL_GENERAL = 0, 1
+GEOMETRY_BOX, GEOMETRY_SHELL_SECTOR, GEOMETRY_AFFINE = 0, 1, 2
 
 
 class MgbError(RuntimeError):
@@ -47,6 +48,8 @@ class Options(C.Structure):
         ("comm_rank", C.c_int),
         ("comm_size", C.c_int),
         ("comm_id", C.c_ubyte * 128),
+        ("geometry", C.c_int),
+        ("geometry_params", C.c_double * 12),
     ]
 
 
@@ -387,7 +390,10 @@ class MultigridSolver:
 
     def __init__(self, degree, n_subdivisions, n_refinements, lower=(-0.9,) * 3, upper=(1.0,) * 3,
                  degree_pre=3, degree_post=3, n_cycles=2, problem=PROBLEM_CUBE_SINE,
-                 kernel=KERNEL_AUTO, device=0, tile_cells=0, comm=None):
+                 kernel=KERNEL_AUTO, device=0, tile_cells=0, comm=None, geometry=GEOMETRY_BOX, geometry_params=None):
+        """geometry: GEOMETRY_BOX (axis-aligned cells on [lower, upper]), GEOMETRY_SHELL_SECTOR (one coarse cell of
+        hyper_shell(0, r0, r1, 6) and its refinements, geometry_params = (r0, r1, opening half-angle), default
+        (0.5, 1.0, pi/4)), GEOMETRY_AFFINE (x = lower + A ((upper - lower) o xi), geometry_params = A row-major)."""
         import torch
         if isinstance(n_subdivisions, int):
             n_subdivisions = (n_subdivisions,) * 3
@@ -400,6 +406,10 @@ class MultigridSolver:
         o.upper[:] = list(upper)
         o.degree_pre, o.degree_post, o.n_cycles = degree_pre, degree_post, n_cycles
         o.problem, o.kernel, o.device, o.tile_cells = problem, kernel, device, tile_cells
+        o.geometry = geometry
+        if geometry_params is not None:
+            gp = list(geometry_params)
+            o.geometry_params[:len(gp)] = gp
         self.rank, self.n_ranks = 0, 1
         if comm is not None:
             self.rank, self.n_ranks, cid = comm

@@ -480,6 +480,118 @@ namespace mgb
     k_diagonal<p, T><<<A.L.n_cells, n3 < 256 ? ((n3 + 31) / 32) * 32 : 256, 0, stream>>>(A);
   }
 
+  // ------------------------------------------------------------------ mapped cells (MappingQGeneric(p))
+  // Images of the (p+1)^3 Gauss-Lobatto support points of cell (cx,cy,cz) under the geometry map, X[d * n^3 + l]
+  // with l lexicographic (x fastest): the control points of the cell's polynomial geometry.  All threads of the
+  // block take part; the caller synchronises before reading X.
+  template <int p>
+  __device__ __forceinline__ void
+  cell_support_points(const Geometry &g, const LevelDesc &L, const int cx, const int cy, const int cz, double *X)
+  {
+    constexpr int n = p + 1, n3 = n * n * n;
+    const double  ia = 1. / L.ncell[0], ib = 1. / L.ncell[1], ic = (double)L.p / (L.nd2_all - 1);
+    const int     cz_global = cz + L.gk0 / L.p;
+    for (int l = threadIdx.x; l < n3; l += blockDim.x)
+      {
+        const int i = l % n, j = (l / n) % n, k = l / (n * n);
+        double    x[3];
+        geometry_point(g, (cx + ctab.nodes[i]) * ia, (cy + ctab.nodes[j]) * ib, (cz_global + ctab.nodes[k]) * ic, x);
+        X[l]          = x[0];
+        X[n3 + l]     = x[1];
+        X[2 * n3 + l] = x[2];
+      }
+  }
+
+  // position x and Jacobian J[d][e] = d x_d / d xi_e of the cell's polynomial geometry at quadrature point (q0,q1,q2)
+  template <int p>
+  __device__ __forceinline__ void
+  mapped_point(const double *X, const int q0, const int q1, const int q2, double x[3], double J[3][3])
+  {
+    constexpr int n = p + 1, n3 = n * n * n;
+    for (int d = 0; d < 3; ++d)
+      {
+        x[d] = 0;
+        for (int e = 0; e < 3; ++e)
+          J[d][e] = 0;
+      }
+    for (int k = 0; k < n; ++k)
+      for (int j = 0; j < n; ++j)
+        {
+          const double s2 = ctab.S[q2 * n + k], g2 = ctab.G[q2 * n + k];
+          const double s1 = ctab.S[q1 * n + j], g1 = ctab.G[q1 * n + j];
+          for (int i = 0; i < n; ++i)
+            {
+              const double s0 = ctab.S[q0 * n + i], g0 = ctab.G[q0 * n + i];
+              const int    l  = (k * n + j) * n + i;
+              const double v = s0 * s1 * s2, d0 = g0 * s1 * s2, d1 = s0 * g1 * s2, d2 = s0 * s1 * g2;
+              for (int d = 0; d < 3; ++d)
+                {
+                  const double Xd = X[d * n3 + l];
+                  x[d] += Xd * v;
+                  J[d][0] += Xd * d0;
+                  J[d][1] += Xd * d1;
+                  J[d][2] += Xd * d2;
+                }
+            }
+        }
+  }
+
+  __device__ __forceinline__ double
+  det3(const double J[3][3])
+  {
+    return J[0][0] * (J[1][1] * J[2][2] - J[1][2] * J[2][1]) - J[0][1] * (J[1][0] * J[2][2] - J[1][2] * J[2][0]) +
+           J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]);
+  }
+
+  // laplace_operator.h:388-430 on general cells: c(x_q) JxW J^-1 J^-T, six entries per quadrature point
+  template <int p, typename T>
+  __global__ void
+  k_mapped_coefficient(const CoefArgs<T> A)
+  {
+    constexpr int     n = p + 1, n3 = n * n * n;
+    __shared__ double X[3 * n3];
+    const uint32_t    cell = blockIdx.x;
+    int               cx, cy, cz;
+    cell_coords(A.L, cell, cx, cy, cz);
+    cell_support_points<p>(A.geom, A.L, cx, cy, cz, X);
+    __syncthreads();
+    for (int q = threadIdx.x; q < n3; q += blockDim.x)
+      {
+        const int q0 = q % n, q1 = (q / n) % n, q2 = q / (n * n);
+        double    x[3], J[3][3];
+        mapped_point<p>(X, q0, q1, q2, x, J);
+        const double det = det3(J);
+        // inverse Jacobian: I[e][d] = d xi_e / d x_d (cofactors)
+        double I[3][3];
+        I[0][0] = (J[1][1] * J[2][2] - J[1][2] * J[2][1]) / det;
+        I[0][1] = (J[0][2] * J[2][1] - J[0][1] * J[2][2]) / det;
+        I[0][2] = (J[0][1] * J[1][2] - J[0][2] * J[1][1]) / det;
+        I[1][0] = (J[1][2] * J[2][0] - J[1][0] * J[2][2]) / det;
+        I[1][1] = (J[0][0] * J[2][2] - J[0][2] * J[2][0]) / det;
+        I[1][2] = (J[0][2] * J[1][0] - J[0][0] * J[1][2]) / det;
+        I[2][0] = (J[1][0] * J[2][1] - J[1][1] * J[2][0]) / det;
+        I[2][1] = (J[0][1] * J[2][0] - J[0][0] * J[2][1]) / det;
+        I[2][2] = (J[0][0] * J[1][1] - J[0][1] * J[1][0]) / det;
+        const double f = eval_fn(A.fn_id, x[0], x[1], x[2]) * ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * fabs(det);
+        auto         m = [&](const int e, const int g) { return f * (I[e][0] * I[g][0] + I[e][1] * I[g][1] + I[e][2] * I[g][2]); };
+        T           *c = A.coef_q + (size_t)cell * 6 * n3 + q;
+        c[0 * n3]      = (T)m(0, 0);
+        c[1 * n3]      = (T)m(1, 1);
+        c[2 * n3]      = (T)m(2, 2);
+        c[3 * n3]      = (T)m(0, 1);
+        c[4 * n3]      = (T)m(0, 2);
+        c[5 * n3]      = (T)m(1, 2);
+      }
+  }
+
+  template <int p, typename T>
+  void
+  launch_coefficient(const CoefArgs<T> &A, cudaStream_t stream)
+  {
+    constexpr int n3 = (p + 1) * (p + 1) * (p + 1);
+    k_mapped_coefficient<p, T><<<A.L.n_cells, n3 < 128 ? ((n3 + 31) / 32) * 32 : 128, 0, stream>>>(A);
+  }
+
   // ------------------------------------------------------------------ right-hand side values
   template <int p>
   __global__ void
@@ -488,13 +600,27 @@ namespace mgb
     constexpr int     n  = p + 1;
     constexpr int     n3 = n * n * n;
     __shared__ double v[n3];
+    __shared__ double X[3 * n3]; // mapped cells: support points of the cell geometry
     const uint32_t    cell = blockIdx.x;
     int               cx, cy, cz;
     cell_coords(A.L, cell, cx, cy, cz);
     const double detJ = A.L.h[0] * A.L.h[1] * A.L.h[2];
+    const bool   mapped = A.geom.kind != 0;
+    if (mapped)
+      {
+        cell_support_points<p>(A.geom, A.L, cx, cy, cz, X);
+        __syncthreads();
+      }
     for (int q = threadIdx.x; q < n3; q += blockDim.x)
       {
         const int    q0 = q % n, q1 = (q / n) % n, q2 = q / (n * n);
+        if (mapped)
+          {
+            double x[3], J[3][3];
+            mapped_point<p>(X, q0, q1, q2, x, J);
+            v[q] = eval_fn(A.fn_id, x[0], x[1], x[2]) * ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * fabs(det3(J));
+            continue;
+          }
         const double x = A.L.lo[0] + (cx + ctab.xq[q0]) * A.L.h[0];
         const double y = A.L.lo[1] + (cy + ctab.xq[q1]) * A.L.h[1];
         const double z = A.L.lo[2] + (cz + ctab.xq[q2]) * A.L.h[2];
@@ -535,12 +661,16 @@ namespace mgb
     constexpr int     n  = p + 1;
     constexpr int     n3 = n * n * n;
     __shared__ double u[n3];
+    __shared__ double X[3 * n3]; // mapped cells: support points of the cell geometry
     __shared__ double red[2][32];
     const uint32_t    cell = blockIdx.x;
     int               cx, cy, cz;
     cell_coords(A.L, cell, cx, cy, cz);
     if (cz < A.L.zg)
       return; // ghost layer of a z-slab: integrated by the rank below
+    const bool mapped = A.geom.kind != 0;
+    if (mapped)
+      cell_support_points<p>(A.geom, A.L, cx, cy, cz, X);
     for (int l = threadIdx.x; l < n3; l += blockDim.x)
       {
         bool           con;
@@ -561,10 +691,19 @@ namespace mgb
               for (int i0 = 0; i0 < n; ++i0)
                 val += ctab.S[q0 * n + i0] * s12 * u[(i2 * n + i1) * n + i0];
             }
-        const double x    = A.L.lo[0] + (cx + ctab.xq[q0]) * A.L.h[0];
-        const double y    = A.L.lo[1] + (cy + ctab.xq[q1]) * A.L.h[1];
-        const double z    = A.L.lo[2] + (cz + ctab.xq[q2]) * A.L.h[2];
-        const double JxW  = ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * detJ;
+        double x    = A.L.lo[0] + (cx + ctab.xq[q0]) * A.L.h[0];
+        double y    = A.L.lo[1] + (cy + ctab.xq[q1]) * A.L.h[1];
+        double z    = A.L.lo[2] + (cz + ctab.xq[q2]) * A.L.h[2];
+        double JxW  = ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * detJ;
+        if (mapped)
+          {
+            double xm[3], J[3][3];
+            mapped_point<p>(X, q0, q1, q2, xm, J);
+            x   = xm[0];
+            y   = xm[1];
+            z   = xm[2];
+            JxW = ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * fabs(det3(J));
+          }
         const double diff = val - eval_fn(A.fn_id, x, y, z);
         err += diff * diff * JxW;
         vol += JxW;

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include "basis.h"
+#include "geometry.h"
 #include "level.h"
 
 namespace mgb
@@ -66,6 +67,7 @@ namespace mgb
   struct RhsArgs
   {
     LevelDesc L;
+    Geometry  geom;
     double   *dst; // += int f phi
     int       fn_id;
   };
@@ -73,9 +75,20 @@ namespace mgb
   struct ErrorArgs
   {
     LevelDesc     L;
+    Geometry      geom;
     const double *u;
     int           fn_id;
     double       *accum; // [0] += error^2, [1] += volume
+  };
+
+  // merged coefficient c(x_q) JxW J^-1 J^-T per quadrature point on a mapped mesh (laplace_operator.h:388-430)
+  template <typename T>
+  struct CoefArgs
+  {
+    LevelDesc L;
+    Geometry  geom;
+    T        *coef_q; // [cell][6][n^3], entries 00, 11, 22, 01, 02, 12
+    int       fn_id;
   };
 
   struct DegreeKernels
@@ -91,6 +104,8 @@ namespace mgb
     void (*transfer_tile_d)(const TransferArgs<double> &, cudaStream_t);
     void (*diagonal_f)(const DiagArgs<float> &, cudaStream_t);
     void (*diagonal_d)(const DiagArgs<double> &, cudaStream_t);
+    void (*coefficient_f)(const CoefArgs<float> &, cudaStream_t);
+    void (*coefficient_d)(const CoefArgs<double> &, cudaStream_t);
     void (*rhs_values)(const RhsArgs &, cudaStream_t);
     void (*l2_error)(const ErrorArgs &, cudaStream_t);
   };

@@ -24,6 +24,8 @@ namespace mgb
                                     &launch_transfer_tile<MGB_P, double>,
                                     &launch_diagonal<MGB_P, float>,
                                     &launch_diagonal<MGB_P, double>,
+                                    &launch_coefficient<MGB_P, float>,
+                                    &launch_coefficient<MGB_P, double>,
                                     &launch_rhs_values<MGB_P>,
                                     &launch_l2_error<MGB_P>};
     return k;

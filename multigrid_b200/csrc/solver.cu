@@ -1021,6 +1021,19 @@ namespace mgb
     return L.lo[dir] + (cell + nd.nodes[gi - cell * L.p]) * L.h[dir];
   }
 
+  // mesh coordinate in [0,1] of grid point gi in direction dir (z: of the whole level, not of the z-slab)
+  __device__ __forceinline__ double
+  unit_coordinate(const LevelDesc &L, const Nodes1D &nd, const int dir, const int gi)
+  {
+    int cell = gi / L.p;
+    if (cell > L.ncell[dir] - 1)
+      cell = L.ncell[dir] - 1;
+    const double node = nd.nodes[gi - cell * L.p];
+    if (dir == 2)
+      return (cell + L.gk0 / L.p + node) * L.p / (L.nd2_all - 1);
+    return (cell + node) / L.ncell[dir];
+  }
+
   // ------------------------------------------------------------------ operator
   template <typename T>
   struct LaplaceOperator
@@ -1039,20 +1052,69 @@ namespace mgb
     size_t m_global() const { return level->n_global; } // MatrixFreeOperators::Base::m()
 
     void
-    initialize(Ctx &c, Level &l, const Basis &basis, const int coefficient_fn)
+    initialize(Ctx &c, Level &l, const Basis &basis, const int coefficient_fn, const Geometry &geom)
     {
       ctx   = &c;
       level = &l;
       dk    = &degree_kernels(l.d.p);
-      evaluate_coefficient(basis, coefficient_fn);
+      evaluate_coefficient(basis, coefficient_fn, geom);
     }
 
     // laplace_operator.h:359-432 (merged coefficient = c JxW J^-1 J^-T)
     void
-    evaluate_coefficient(const Basis &basis, const int fn)
+    evaluate_coefficient(const Basis &basis, const int fn, const Geometry &geom)
     {
       const LevelDesc &L    = level->d;
       const double     detJ = L.h[0] * L.h[1] * L.h[2];
+      if (geom.kind == MGB_GEOMETRY_AFFINE && fn == FN_ONE)
+        {
+          // affine cells, constant coefficient: one tensor for all cells (:374-387), here with all six entries.
+          // J = A diag(h): coef = |det J| J^-1 J^-T without the quadrature weight
+          cartesian = false;
+          double J[3][3], I[3][3];
+          for (int d = 0; d < 3; ++d)
+            for (int e = 0; e < 3; ++e)
+              J[d][e] = geom.par[3 * d + e] * L.h[e];
+          const double det = J[0][0] * (J[1][1] * J[2][2] - J[1][2] * J[2][1]) - J[0][1] * (J[1][0] * J[2][2] - J[1][2] * J[2][0]) +
+                             J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]);
+          I[0][0] = (J[1][1] * J[2][2] - J[1][2] * J[2][1]) / det;
+          I[0][1] = (J[0][2] * J[2][1] - J[0][1] * J[2][2]) / det;
+          I[0][2] = (J[0][1] * J[1][2] - J[0][2] * J[1][1]) / det;
+          I[1][0] = (J[1][2] * J[2][0] - J[1][0] * J[2][2]) / det;
+          I[1][1] = (J[0][0] * J[2][2] - J[0][2] * J[2][0]) / det;
+          I[1][2] = (J[0][2] * J[1][0] - J[0][0] * J[1][2]) / det;
+          I[2][0] = (J[1][0] * J[2][1] - J[1][1] * J[2][0]) / det;
+          I[2][1] = (J[0][1] * J[2][0] - J[0][0] * J[2][1]) / det;
+          I[2][2] = (J[0][0] * J[1][1] - J[0][1] * J[1][0]) / det;
+          auto m = [&](const int e, const int g) {
+            return std::fabs(det) * (I[e][0] * I[g][0] + I[e][1] * I[g][1] + I[e][2] * I[g][2]);
+          };
+          coef[0] = (T)m(0, 0);
+          coef[1] = (T)m(1, 1);
+          coef[2] = (T)m(2, 2);
+          coef[3] = (T)m(0, 1);
+          coef[4] = (T)m(0, 2);
+          coef[5] = (T)m(1, 2);
+          return;
+        }
+      if (geom.kind != MGB_GEOMETRY_BOX)
+        {
+          // general cells: one tensor per quadrature point from the Jacobian of the polynomial cell geometry (:388-430)
+          cartesian   = false;
+          const int n = L.n, n3 = n * n * n;
+          coef_q.alloc((size_t)L.n_cells * 6 * n3, ctx->stream);
+          CoefArgs<T> A;
+          A.L      = L;
+          A.geom   = geom;
+          A.coef_q = coef_q.p;
+          A.fn_id  = fn;
+          if (sizeof(T) == 8)
+            dk->coefficient_d(reinterpret_cast<const CoefArgs<double> &>(A), ctx->stream);
+          else
+            dk->coefficient_f(reinterpret_cast<const CoefArgs<float> &>(A), ctx->stream);
+          ctx->check_launch();
+          return;
+        }
       if (fn == FN_ONE)
         {
           cartesian = true;
@@ -1642,6 +1704,7 @@ namespace mgb
     Basis        basis;
     int          n_levels = 0;
     int          fn_solution, fn_rhs, fn_coef;
+    Geometry     geom;
     std::vector<std::unique_ptr<Level>>                   levels;
     std::vector<std::unique_ptr<LaplaceOperator<float>>>  matrix;
     std::vector<std::unique_ptr<LaplaceOperator<double>>> matrix_dp;
@@ -1689,6 +1752,19 @@ namespace mgb
         }
       else
         throw std::runtime_error("unknown problem id");
+      if (o.geometry < MGB_GEOMETRY_BOX || o.geometry > MGB_GEOMETRY_AFFINE)
+        throw std::runtime_error("unknown geometry id");
+      geom.kind = o.geometry;
+      for (int d = 0; d < 3; ++d)
+        {
+          geom.lo[d] = o.lower[d];
+          geom.hi[d] = o.upper[d];
+        }
+      for (int i = 0; i < 12; ++i)
+        geom.par[i] = o.geometry_params[i];
+      if (geom.kind == MGB_GEOMETRY_SHELL_SECTOR &&
+          !(geom.par[0] > 0 && geom.par[1] > geom.par[0] && geom.par[2] > 0 && geom.par[2] < 1.5))
+        throw std::runtime_error("shell sector: need 0 < r0 < r1 and an opening half-angle in (0, 1.5)");
 
       n_levels = o.n_refinements + 1;
       transfer.resize(n_levels);
@@ -1714,8 +1790,8 @@ namespace mgb
           matrix_dp.emplace_back(new LaplaceOperator<double>());
           matrix[l]->kernel    = o.kernel;
           matrix_dp[l]->kernel = o.kernel;
-          matrix[l]->initialize(ctx, lv, basis, fn_coef);
-          matrix_dp[l]->initialize(ctx, lv, basis, fn_coef);
+          matrix[l]->initialize(ctx, lv, basis, fn_coef, geom);
+          matrix_dp[l]->initialize(ctx, lv, basis, fn_coef, geom);
           auto newd = [&]() { auto v = new DVec<double>(); v->alloc(N, ctx.stream); return std::unique_ptr<DVec<double>>(v); };
           auto newf = [&]() { auto v = new DVec<float>(); v->alloc(N, ctx.stream); return std::unique_ptr<DVec<float>>(v); };
           solution.push_back(newd());
@@ -1754,12 +1830,24 @@ namespace mgb
           const LevelDesc L   = levels[l]->d;
           double         *bc  = bc_values[l]->p;
           const int       fns = fn_solution;
+          const Geometry  gm  = geom;
           patch_points(ctx, L, [=] __device__(uint32_t dof, bool con, int gi, int gj, int gk) {
-            if (con)
+            if (!con)
+              return;
+            if (gm.kind == MGB_GEOMETRY_BOX)
               bc[dof] = eval_fn(fns,
                                 support_point(L, nd, 0, gi),
                                 support_point(L, nd, 1, gj),
                                 support_point(L, nd, 2, gk));
+            else
+              {
+                // mapped support point: the geometry map at the node's mesh coordinates (what the polynomial cell
+                // geometry interpolates)
+                double x[3];
+                geometry_point(gm, unit_coordinate(L, nd, 0, gi), unit_coordinate(L, nd, 1, gj),
+                               unit_coordinate(L, nd, 2, gk), x);
+                bc[dof] = eval_fn(fns, x[0], x[1], x[2]);
+              }
           });
           // rhs = int f phi - K u_bc  (laplace_operator.h:806-845): general kernel, plain read
           const size_t N   = L.n_dofs;
@@ -1769,6 +1857,7 @@ namespace mgb
           matrix_dp[l]->apply(APPLY_ADD, rhs[l]->p, neg, nullptr, nullptr, 0, 0, false, /*read_plain=*/true);
           RhsArgs R;
           R.L     = L;
+          R.geom  = geom;
           R.dst   = rhs[l]->p;
           R.fn_id = fn_rhs;
           dk->rhs_values(R, ctx.stream);
@@ -1833,6 +1922,7 @@ namespace mgb
       MGB_CUDA_CHECK(cudaMemsetAsync(ctx.scal_dev, 0, 2 * sizeof(double), ctx.stream));
       ErrorArgs E;
       E.L     = levels[level]->d;
+      E.geom  = geom;
       E.u     = solution[level]->p;
       E.fn_id = fn_solution;
       E.accum = ctx.scal_dev;
@@ -2473,6 +2563,12 @@ extern "C"
     o->degree_pre = o->degree_post = 3;
     o->n_cycles                    = 2;
     o->problem                     = MGB_PROBLEM_CUBE_SINE;
+    o->geometry                    = MGB_GEOMETRY_BOX;
+    for (int i = 0; i < 12; ++i)
+      o->geometry_params[i] = 0.;
+    o->geometry_params[0] = 0.5;                    // hyper_shell(center, 0.5, 1.0, 6): poisson_shell/program.cc:426
+    o->geometry_params[1] = 1.0;
+    o->geometry_params[2] = 0.78539816339744830962; // a whole cube face
     o->kernel                      = MGB_KERNEL_AUTO;
     o->device                      = 0;
     o->tile_cells                  = 0;

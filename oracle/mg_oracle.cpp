@@ -104,6 +104,85 @@ namespace orc
 
   typedef double (*Fn)(const double *);
 
+  // ---------------------------------------------------------------- geometry
+  // Map from the unit box of mesh coordinates to physical space.  kind 0: the box [lo, hi] (axis-aligned cells,
+  // subdivided_hyper_rectangle); kind 1: one of the six coarse cells of GridGenerator::hyper_shell(0, r0, r1, 6)
+  // (poisson_shell/program.cc:426) -- a cube face of half-width tan(alpha) projected radially, radius r0..r1 --
+  // and its uniform refinements; kind 2: affine, x = lo + A ((hi - lo) o xi).  Inside a cell the geometry is the
+  // degree-p polynomial through the images of the Gauss-Lobatto support points, as MappingQGeneric(p)
+  // (multigrid_solver.h:138-139) represents a manifold; deal.II's SphericalManifold places points by weighted
+  // averages on the sphere, not by this analytic map, so against the reference's shell meshes this is PARITY UNPINNED.
+  struct Geometry
+  {
+    int    kind = 0;
+    double lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
+    double par[12] = {0};
+
+    void
+    point(const double xi[3], double x[3]) const
+    {
+      if (kind == 1)
+        {
+          const double half = std::tan(par[2]);
+          const double v[3] = {half * (2 * xi[0] - 1), half * (2 * xi[1] - 1), 1.};
+          const double len  = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+          const double r    = par[0] * (1 - xi[2]) + par[1] * xi[2];
+          for (int d = 0; d < 3; ++d)
+            x[d] = r * v[d] / len;
+        }
+      else
+        {
+          double u[3];
+          for (int d = 0; d < 3; ++d)
+            u[d] = (hi[d] - lo[d]) * xi[d];
+          for (int d = 0; d < 3; ++d)
+            x[d] = lo[d] + (kind == 2 ? par[3 * d] * u[0] + par[3 * d + 1] * u[1] + par[3 * d + 2] * u[2] : u[d]);
+        }
+    }
+  };
+
+  // inverse and determinant of a 3 x 3 matrix by Gauss-Jordan elimination with partial pivoting
+  static double
+  invert3(const double A[3][3], double inv[3][3])
+  {
+    double M[3][6];
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j)
+        {
+          M[i][j]     = A[i][j];
+          M[i][3 + j] = i == j;
+        }
+    double det = 1;
+    for (int c = 0; c < 3; ++c)
+      {
+        int piv = c;
+        for (int r = c + 1; r < 3; ++r)
+          if (std::fabs(M[r][c]) > std::fabs(M[piv][c]))
+            piv = r;
+        if (piv != c)
+          {
+            for (int j = 0; j < 6; ++j)
+              std::swap(M[c][j], M[piv][j]);
+            det = -det;
+          }
+        det *= M[c][c];
+        const double d = 1. / M[c][c];
+        for (int j = 0; j < 6; ++j)
+          M[c][j] *= d;
+        for (int r = 0; r < 3; ++r)
+          if (r != c)
+            {
+              const double f = M[r][c];
+              for (int j = 0; j < 6; ++j)
+                M[r][j] -= f * M[c][j];
+            }
+      }
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j)
+        inv[i][j] = M[i][3 + j];
+    return det;
+  }
+
   // ---------------------------------------------------------------- 1-D sweeps
   // out[.., o, ..] (+)= sum_i M[o][i] in[.., i, ..]   (transpose: M[i][o])
   template <typename T, int n, int dir, bool transpose, bool add>
@@ -142,6 +221,7 @@ namespace orc
     double         lo[3], h[3];
     vector<T>      S, D, wq;
     bool           variable = false;
+    Geometry       geom;
     T              coef_affine[6];
     vector<T>      coef_q; // [cell][q][6]
     vector<T>      inv_diag;
@@ -187,6 +267,59 @@ namespace orc
       return i == 0 || j == 0 || k == 0 || i == nd[0] - 1 || j == nd[1] - 1 || k == nd[2] - 1;
     }
 
+    // control points of the polynomial geometry of cell (cx,cy,cz): X[l][d], l lexicographic over the support points
+    void
+    cell_nodes(const int cx, const int cy, const int cz, vector<double> &X) const
+    {
+      X.resize(3 * n * n * n);
+      for (int k = 0, l = 0; k < n; ++k)
+        for (int j = 0; j < n; ++j)
+          for (int i = 0; i < n; ++i, ++l)
+            {
+              const double xi[3] = {(cx + b->gll[i]) / nc[0], (cy + b->gll[j]) / nc[1], (cz + b->gll[k]) / nc[2]};
+              geom.point(xi, &X[3 * l]);
+            }
+    }
+
+    // position and Jacobian d x_d / d xi_e of the cell geometry at quadrature point (q0,q1,q2)
+    void
+    cell_geometry(const vector<double> &X, const int q0, const int q1, const int q2, double x[3], double J[3][3]) const
+    {
+      for (int d = 0; d < 3; ++d)
+        x[d] = J[d][0] = J[d][1] = J[d][2] = 0;
+      for (int k = 0, l = 0; k < n; ++k)
+        for (int j = 0; j < n; ++j)
+          for (int i = 0; i < n; ++i, ++l)
+            {
+              const double v[3]  = {b->S[q0 * n + i], b->S[q1 * n + j], b->S[q2 * n + k]};
+              const double dv[3] = {b->G[q0 * n + i], b->G[q1 * n + j], b->G[q2 * n + k]};
+              for (int d = 0; d < 3; ++d)
+                {
+                  x[d] += X[3 * l + d] * v[0] * v[1] * v[2];
+                  J[d][0] += X[3 * l + d] * dv[0] * v[1] * v[2];
+                  J[d][1] += X[3 * l + d] * v[0] * dv[1] * v[2];
+                  J[d][2] += X[3 * l + d] * v[0] * v[1] * dv[2];
+                }
+            }
+    }
+
+    // symmetric tensor scale * J^-1 J^-T in the storage order 00, 11, 22, 01, 02, 12 (laplace_operator.h:382-386)
+    static void
+    merged_tensor(const double J[3][3], const double scale_without_det, T *c)
+    {
+      double       inv[3][3];
+      const double det = invert3(J, inv);
+      const double f   = scale_without_det * std::fabs(det);
+      const int    pe[6] = {0, 1, 2, 0, 0, 1}, pf[6] = {0, 1, 2, 1, 2, 2};
+      for (int s = 0; s < 6; ++s)
+        {
+          double m = 0;
+          for (int d = 0; d < 3; ++d)
+            m += inv[pe[s]][d] * inv[pf[s]][d];
+          c[s] = (T)(f * m);
+        }
+    }
+
     // laplace_operator.h:359-432
     void
     evaluate_coefficient(Fn coefficient, const bool is_constant)
@@ -194,6 +327,42 @@ namespace orc
       const double detJ   = h[0] * h[1] * h[2];
       const int    nq     = n * n * n;
       variable            = !is_constant;
+      if (geom.kind == 2 && is_constant)
+        {
+          // affine cells: one tensor per geometry class (:374-387), quadrature weight applied in the cell kernel
+          double J[3][3];
+          for (int d = 0; d < 3; ++d)
+            for (int e = 0; e < 3; ++e)
+              J[d][e] = geom.par[3 * d + e] * h[e];
+          const double x0[3] = {0, 0, 0};
+          merged_tensor(J, coefficient(x0), coef_affine);
+          return;
+        }
+      if (geom.kind != 0)
+        {
+          // general cells: one tensor per quadrature point, JxW includes the weight (:388-430)
+          variable = true;
+          coef_q.resize(ncells * nq * 6);
+#pragma omp parallel for collapse(2)
+          for (int cz = 0; cz < nc[2]; ++cz)
+            for (int cy = 0; cy < nc[1]; ++cy)
+              for (int cx = 0; cx < nc[0]; ++cx)
+                {
+                  const size_t   cell = ((size_t)cz * nc[1] + cy) * nc[0] + cx;
+                  vector<double> X;
+                  cell_nodes(cx, cy, cz, X);
+                  for (int q2 = 0; q2 < n; ++q2)
+                    for (int q1 = 0; q1 < n; ++q1)
+                      for (int q0 = 0; q0 < n; ++q0)
+                        {
+                          double x[3], J[3][3];
+                          cell_geometry(X, q0, q1, q2, x, J);
+                          merged_tensor(J, coefficient(x) * (b->wq[q0] * b->wq[q1] * b->wq[q2]),
+                                        &coef_q[(cell * nq + (q2 * n + q1) * n + q0) * 6]);
+                        }
+                }
+          return;
+        }
       if (is_constant)
         {
           const double x0[3] = {0, 0, 0};
@@ -487,11 +656,20 @@ namespace orc
             for (int cy = 0; cy < nc[1]; ++cy)
               for (int cx = 0; cx < nc[0]; ++cx)
                 {
-                  vector<double> v(nq), t(nq);
+                  vector<double> v(nq), t(nq), X;
+                  if (geom.kind != 0)
+                    cell_nodes(cx, cy, cz, X);
                   for (int q2 = 0, q = 0; q2 < n; ++q2)
                     for (int q1 = 0; q1 < n; ++q1)
                       for (int q0 = 0; q0 < n; ++q0, ++q)
                         {
+                          if (geom.kind != 0)
+                            {
+                              double x[3], J[3][3], inv[3][3];
+                              cell_geometry(X, q0, q1, q2, x, J);
+                              v[q] = rhs_function(x) * b->wq[q0] * b->wq[q1] * b->wq[q2] * std::fabs(invert3(J, inv));
+                              continue;
+                            }
                           const double x[3] = {lo[0] + (cx + b->xq[q0]) * h[0],
                                                lo[1] + (cy + b->xq[q1]) * h[1],
                                                lo[2] + (cz + b->xq[q2]) * h[2]};
@@ -1000,7 +1178,8 @@ namespace orc
                     const unsigned int pre,
                     const unsigned int post,
                     const unsigned int cycles,
-                    const int     problem)
+                    const int     problem,
+                    const Geometry &geometry = Geometry())
       : p(degree)
       , nlevels(n_refine + 1)
       , degree_pre(pre)
@@ -1047,8 +1226,10 @@ namespace orc
           for (int d = 0; d < 3; ++d)
             nc[d] = nsub[d] << l;
           matrix[l].init(basis, nc, lo, hi);
+          matrix[l].geom = geometry;
           matrix[l].evaluate_coefficient(f_coef, const_coef);
           matrix_dp[l].init(basis, nc, lo, hi);
+          matrix_dp[l].geom = geometry;
           matrix_dp[l].evaluate_coefficient(f_coef, const_coef);
           const size_t N = matrix[l].ndofs;
           defect[l].assign(N, 0);
@@ -1074,9 +1255,14 @@ namespace orc
               for (int i = 0; i < op.nd[0]; ++i)
                 if (op.on_boundary(i, j, k))
                   {
-                    const double x[3] = {support_point(op, 0, i),
-                                         support_point(op, 1, j),
-                                         support_point(op, 2, k)};
+                    double x[3] = {support_point(op, 0, i), support_point(op, 1, j), support_point(op, 2, k)};
+                    if (op.geom.kind != 0)
+                      {
+                        // mapped support point = the geometry map at the node's mesh coordinates
+                        const double xi[3] = {unit_coordinate(op, 0, i), unit_coordinate(op, 1, j),
+                                              unit_coordinate(op, 2, k)};
+                        op.geom.point(xi, x);
+                      }
                     const double value = f_solution(x);
                     if (value != 0.0)
                       inhomogeneous_bc[l].emplace_back(((size_t)k * op.nd[1] + j) * op.nd[0] + i,
@@ -1116,6 +1302,13 @@ namespace orc
       return op.lo[d] + (cell + basis.gll[i - cell * p]) * op.h[d];
     }
 
+    double
+    unit_coordinate(const LevelOp<double> &op, const int d, const int i) const
+    {
+      const int cell = std::min(i / p, op.nc[d] - 1);
+      return (cell + basis.gll[i - cell * p]) / op.nc[d];
+    }
+
     // multigrid_solver.h:298-343
     double
     compute_l2_error(const int level)
@@ -1131,7 +1324,9 @@ namespace orc
         for (int cy = 0; cy < op.nc[1]; ++cy)
           for (int cx = 0; cx < op.nc[0]; ++cx)
             {
-              vector<double> u(n * n * n), w(n * n * n);
+              vector<double> u(n * n * n), w(n * n * n), X;
+              if (op.geom.kind != 0)
+                op.cell_nodes(cx, cy, cz, X);
               for (int k = 0, l = 0; k < n; ++k)
                 for (int j = 0; j < n; ++j)
                   for (int i = 0; i < n; ++i, ++l)
@@ -1159,10 +1354,16 @@ namespace orc
                 for (int q1 = 0; q1 < n; ++q1)
                   for (int q0 = 0; q0 < n; ++q0, ++q)
                     {
-                      const double x[3] = {op.lo[0] + (cx + basis.xq[q0]) * op.h[0],
-                                           op.lo[1] + (cy + basis.xq[q1]) * op.h[1],
-                                           op.lo[2] + (cz + basis.xq[q2]) * op.h[2]};
-                      const double JxW  = basis.wq[q0] * basis.wq[q1] * basis.wq[q2] * detJ;
+                      double x[3] = {op.lo[0] + (cx + basis.xq[q0]) * op.h[0],
+                                     op.lo[1] + (cy + basis.xq[q1]) * op.h[1],
+                                     op.lo[2] + (cz + basis.xq[q2]) * op.h[2]};
+                      double JxW  = basis.wq[q0] * basis.wq[q1] * basis.wq[q2] * detJ;
+                      if (op.geom.kind != 0)
+                        {
+                          double J[3][3], inv[3][3];
+                          op.cell_geometry(X, q0, q1, q2, x, J);
+                          JxW = basis.wq[q0] * basis.wq[q1] * basis.wq[q2] * std::fabs(invert3(J, inv));
+                        }
                       const double diff = u[q] - f_solution(x);
                       err += diff * diff * JxW;
                       vol += JxW;
@@ -1332,6 +1533,34 @@ extern "C"
     if (degree < 1 || degree > 8)
       return nullptr;
     return new MultigridSolver(degree, nsub, n_refine, lower, upper, pre, post, cycles, problem);
+  }
+
+  // the same on a mapped mesh: geometry 0 box, 1 shell sector (params r0, r1, half-angle), 2 affine (params A row-major)
+  void *
+  orc_mg_create_mapped(int           degree,
+                       const int    *nsub,
+                       int           n_refine,
+                       const double *lower,
+                       const double *upper,
+                       unsigned int  pre,
+                       unsigned int  post,
+                       unsigned int  cycles,
+                       int           problem,
+                       int           geometry,
+                       const double *params)
+  {
+    if (degree < 1 || degree > 8 || geometry < 0 || geometry > 2)
+      return nullptr;
+    Geometry g;
+    g.kind = geometry;
+    for (int d = 0; d < 3; ++d)
+      {
+        g.lo[d] = lower[d];
+        g.hi[d] = upper[d];
+      }
+    for (int i = 0; i < 12; ++i)
+      g.par[i] = params[i];
+    return new MultigridSolver(degree, nsub, n_refine, lower, upper, pre, post, cycles, problem, g);
   }
 
   void

@@ -43,6 +43,8 @@ def lib():
         ip = C.POINTER(C.c_int)
         L.orc_mg_create.restype = C.c_void_p
         L.orc_mg_create.argtypes = [C.c_int, ip, C.c_int, dp, dp, C.c_uint, C.c_uint, C.c_uint, C.c_int]
+        L.orc_mg_create_mapped.restype = C.c_void_p
+        L.orc_mg_create_mapped.argtypes = [C.c_int, ip, C.c_int, dp, dp, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, dp]
         L.orc_mg_destroy.argtypes = [C.c_void_p]
         L.orc_mg_n_levels.argtypes = [C.c_void_p]
         L.orc_mg_n_dofs.restype = C.c_longlong
@@ -172,14 +174,21 @@ class MultigridSolver:
     """multigrid_solver.h:96-782 restated on the CPU; vectors in lexicographic numbering."""
 
     def __init__(self, degree, n_subdivisions, n_refine, lower=(-0.9,) * 3, upper=(1.0,) * 3,
-                 degree_pre=2, degree_post=2, n_cycles=2, problem=0):
+                 degree_pre=2, degree_post=2, n_cycles=2, problem=0, geometry=0, geometry_params=None):
+        """geometry 0: box [lower, upper]; 1: one coarse cell of hyper_shell(0, r0, r1, 6) and its refinements,
+        geometry_params = (r0, r1, opening half-angle), default (0.5, 1.0, pi/4); 2: affine, geometry_params = A (9)"""
         if isinstance(n_subdivisions, int):
             n_subdivisions = (n_subdivisions,) * 3
         self.degree = degree
         nsub = (C.c_int * 3)(*n_subdivisions)
         lo = (C.c_double * 3)(*lower)
         hi = (C.c_double * 3)(*upper)
-        self.h = lib().orc_mg_create(degree, nsub, n_refine, lo, hi, degree_pre, degree_post, n_cycles, problem)
+        gp = [0.5, 1.0, np.pi / 4] + [0.0] * 9
+        if geometry_params is not None:
+            gp[:len(geometry_params)] = list(geometry_params)
+        par = (C.c_double * 12)(*gp)
+        self.h = lib().orc_mg_create_mapped(degree, nsub, n_refine, lo, hi, degree_pre, degree_post, n_cycles, problem,
+                                            geometry, par)
         if not self.h:
             raise ValueError("unsupported degree")
         self.n_levels = lib().orc_mg_n_levels(self.h)

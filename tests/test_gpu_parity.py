@@ -137,6 +137,57 @@ def test_variable_coefficient_solve(mgb, orc, torch, mesh):
     assert abs(e - e_o) <= 5e-3 * e_o, (e, e_o)
 
 
+SHEAR = [1.0, 0.12, 0.24, 0.06, 1.1, 0.18, -0.1, 0.05, 0.9]   # a full 3 x 3 matrix: all six tensor entries non-zero
+MAPPED = [  # (p, nsub, nref, problem, geometry, params)
+    (4, (1, 1, 1), 2, 0, 2, SHEAR), (3, (2, 1, 1), 2, 1, 2, SHEAR), (2, (1, 1, 1), 3, 0, 1, None),
+    (4, (1, 1, 1), 2, 1, 1, None), (3, (1, 2, 1), 2, 1, 1, (0.5, 1.0, 0.6)), (5, (1, 1, 1), 1, 1, 1, None),
+]
+
+
+@pytest.mark.parametrize("case", MAPPED)
+def test_mapped_geometry(mgb, orc, torch, case):
+    """Curved and sheared cells (config 3 of BASELINE.json): the merged coefficient c JxW J^-1 J^-T with all six
+    entries from the Jacobian of the polynomial cell geometry (laplace_operator.h:388-430), on one coarse cell of
+    hyper_shell(0, 0.5, 1, 6) with its refinements (poisson_shell/program.cc:418-431) and on an affine sheared box;
+    operator, diagonal, right-hand side with the boundary lift, FMG and CG solves against the oracle on the same mesh"""
+    p, nsub, nref, problem, geometry, params = case
+    P = Pair(mgb, orc, torch, p, nsub, nref, problem=problem, geometry=geometry, geometry_params=params,
+             lower=(0.1, 0.2, 0.3), upper=(0.9, 1.1, 1.0))
+    L = P.g.n_levels - 1
+    n = P.g.n_dofs()
+    x = np.random.default_rng(7).random(n)
+    for double in (True, False):
+        op = P.g.matrix_dp() if double else P.g.matrix()
+        dst = op.initialize_dof_vector()
+        op.vmult(dst, P.to_dev(x, -1, double))
+        ref = P.o.vmult(x, -1, double)
+        assert rel(P.to_lex(dst, -1), ref) <= TOL[double] * (1 if double else 3), (double, rel(P.to_lex(dst, -1), ref))
+    d = P.g.matrix_dp().get_matrix_diagonal_inverse()
+    assert rel(P.to_lex(d, -1), P.o.inverse_diagonal_dp()) <= 1e-12
+    scale = np.abs(P.o.get_vector(orc.VEC_RHS, L)).max()
+    for level in range(P.g.n_levels):
+        rhs = P.g.get_vector("rhs", level)[P.lex(level)]
+        ref = P.o.get_vector(orc.VEC_RHS, level)
+        # (the one interior DoF of a one-cell level can sit where the data cancel to rounding: absolute floor)
+        assert np.abs(rhs - ref).max() <= 1e-11 * max(np.abs(ref).max(), scale), ("rhs", level)
+    its, rate = P.g.solve_cg()
+    its_o, rate_o, hist_o = P.o.solve_cg()
+    assert its == its_o, (its, its_o)
+    hist = P.g.cg_history()
+    head = hist_o > 1e-5 * hist_o[0]
+    # with the 1e6 coefficient contrast the float V-cycle's rounding shows in the last residuals (7 orders down):
+    # 5 % on the first five orders of magnitude, a factor of 3 on the tail
+    assert np.allclose(hist[head], hist_o[head], rtol=0.05), (hist, hist_o)
+    assert np.all(hist[~head] < 3 * hist_o[~head]) and np.all(hist_o[~head] < 3 * hist[~head]), (hist, hist_o)
+    e, e_o = P.g.compute_l2_error(), P.o.compute_l2_error()
+    assert abs(e - e_o) <= 1e-3 * e_o, (e, e_o)
+    sol = P.g.get_solution()[P.lex(L)]
+    assert rel(sol, P.o.get_vector(orc.VEC_SOLUTION)) <= 1e-6
+    red, trace = P.g.solve(True)
+    red_o, trace_o = P.o.solve(True)
+    assert np.allclose(trace[1:], trace_o[1:], rtol=3e-2), (trace, trace_o)
+
+
 @pytest.mark.parametrize("mesh", [(4, (1, 1, 1), 2), (3, (2, 1, 3), 1), (1, (1, 1, 1), 2), (8, (1, 1, 1), 1)])
 def test_diagonal_and_cg_update(mgb, orc, torch, mesh):
     p, nsub, nref = mesh
