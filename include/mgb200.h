@@ -352,6 +352,19 @@ int mgb_adaptive_vmult(mgb_adaptive h, int precision, void *dst, const void *src
 int mgb_adaptive_inverse_diagonal(mgb_adaptive h, int precision, void *inv_diag);
 int mgb_adaptive_vmult_host(mgb_adaptive h, int precision, void *dst_host, const void *src_host);
 int mgb_adaptive_sync(mgb_adaptive h);
+/* Local-smoothing multigrid on the forest and the CG solver of poisson_l (program.cc:283-420): level operators with the
+ * refinement-edge DoFs constrained, edge matrices (MGInterfaceOperator: vmult_interface_down / _up), matrix-free
+ * transfer between partially refined levels, Chebyshev smoothers (range 15, degree n_smoother; level 0: tolerance 1e-3),
+ * PreconditionMG::vmult, and SolverCG in double on the operator with hanging-node constraints.
+ * level_info: 0 DoFs, 1 cells, 2 refinement-edge DoFs, 3 cells at the edge, 4 DoFs copied from/to the active vector,
+ * 5 constrained DoFs, 6 Chebyshev degree, 7 / 8 smallest / largest eigenvalue estimate, 9 theta, 10 delta, 11 CG steps. */
+int mgb_adaptive_mg_setup(mgb_adaptive h, int n_smoother);
+int mgb_adaptive_mg_n_levels(mgb_adaptive h);
+int mgb_adaptive_mg_level_info(mgb_adaptive h, int level, double info[12]);
+int mgb_adaptive_mg_vmult(mgb_adaptive h, double *dst_dev, const double *src_dev);
+/* x = 0; CG to |r| <= rel_tol |r0| (or 1e-13 absolute); history (may be NULL): residual norms, *n_history in: capacity */
+int mgb_adaptive_solve_cg(mgb_adaptive h, double *x_dev, const double *rhs_dev, double rel_tol, unsigned int *iterations,
+                          double *reduction_rate, double *history, int *n_history);
 int64_t mgb_adaptive_launch_count(mgb_adaptive h);
 
 /* The subset of LinearAlgebra::distributed::Vector<Number> the drivers use (poisson_cube/program.cc:262-380,

@@ -144,6 +144,11 @@ SYMBOLS = {
     "mgb_vec_sadd": (_i, [_vp, _i, _i, _vp, _d, _d, _vp]),
     "mgb_vec_set": (_i, [_vp, _i, _i, _vp, _d]),
     "mgb_vec_update_ghost_values": (_i, [_vp, _i, _i, _vp]),
+    "mgb_adaptive_mg_setup": (_i, [_vp, _i]),
+    "mgb_adaptive_mg_n_levels": (_i, [_vp]),
+    "mgb_adaptive_mg_level_info": (_i, [_vp, _i, _dp]),
+    "mgb_adaptive_mg_vmult": (_i, [_vp, _vp, _vp]),
+    "mgb_adaptive_solve_cg": (_i, [_vp, _vp, _vp, _d, C.POINTER(C.c_uint), _dp, _dp, _ip]),
     "mgb_vec_compress_add": (_i, [_vp, _i, _i, _vp]),
     "mgb_vec_zero_out_ghost_values": (_i, [_vp, _i, _i, _vp]),
     "mgb_device_alloc": (_i, [_vp, C.c_size_t, C.POINTER(_vp)]),
@@ -1036,6 +1041,38 @@ class LaplaceOperatorAdaptive:
 
     def sync(self):
         _check(lib().mgb_adaptive_sync(self.h))
+
+    # ---- local-smoothing multigrid and CG (poisson_l/program.cc:283-420)
+    MG_INFO = ("n_dofs", "n_cells", "n_edge_dofs", "n_edge_cells", "n_copy", "n_constrained", "degree", "min_eig", "max_eig",
+               "theta", "delta", "cg_iterations")
+
+    def setup_multigrid(self, n_smoother=3):
+        """level operators, edge matrices, transfer and Chebyshev smoothers on the current mesh (redo after refine)"""
+        _check(lib().mgb_adaptive_mg_setup(self.h, int(n_smoother)))
+        self.n_levels = lib().mgb_adaptive_mg_n_levels(self.h)
+
+    def mg_level_info(self, level):
+        v = np.zeros(12)
+        _check(lib().mgb_adaptive_mg_level_info(self.h, level, v.ctypes.data_as(_dp)))
+        return dict(zip(self.MG_INFO, v))
+
+    def mg_vmult(self, dst, src):
+        """PreconditionMG::vmult: one local-smoothing V-cycle (float) on a double vector of the active mesh"""
+        import torch
+        torch.cuda.synchronize()
+        _check(lib().mgb_adaptive_mg_vmult(self.h, _ptr(dst), _ptr(src)))
+        self.sync()
+
+    def solve_cg(self, x, rhs, rel_tol=1e-9):
+        """SolverCG (double) preconditioned by the V-cycle, zero start vector; returns (iterations, rate, history)"""
+        import torch
+        torch.cuda.synchronize()
+        its, rate = C.c_uint(), C.c_double()
+        hist = np.zeros(1024)
+        nh = C.c_int(hist.size)
+        _check(lib().mgb_adaptive_solve_cg(self.h, _ptr(x), _ptr(rhs), float(rel_tol), C.byref(its), C.byref(rate),
+                                           hist.ctypes.data_as(_dp), C.byref(nh)))
+        return its.value, rate.value, hist[:nh.value]
 
     def vmult(self, dst, src, precision=F64):
         import torch

@@ -447,3 +447,4 @@ namespace mgb
 } // namespace mgb
 
 #include "adaptive_kernels.cuh"
+#include "adaptive_solver.cuh"

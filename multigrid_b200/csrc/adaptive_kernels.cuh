@@ -10,7 +10,9 @@ namespace mgb
   {
     int            n_cells;
     const int32_t *cell_index; // [cell][n^3]
+    const int32_t *cell_index_out = nullptr; // scatter through another table (edge matrices of the local smoothing); null: the same
     const uint8_t *cell_level;
+    int            uniform_level = -1;       // >= 0: all cells are of this level (level operators), cell_level unused
     const int32_t *row_start, *row_dof;
     const T       *row_w;
     const T       *M1, *K1;    // reference-cell 1-D mass and stiffness matrices, (p+1)^2
@@ -149,12 +151,21 @@ namespace mgb
           U[(k * n + j) * n + i] = ad_read(A, e[k]);
         }
     __syncthreads();
-    const int lev = active ? A.cell_level[cell] : 0;
+    const int lev = A.uniform_level >= 0 ? A.uniform_level : (active ? A.cell_level[cell] : 0);
     T         out[n];
     ad_cell_apply<p, T>(U, T1, T2, Q, Ms, Ks, A.coef[lev][0], A.coef[lev][1], A.coef[lev][2], i, j, active, out);
     if (active)
-      for (int k = 0; k < n; ++k)
-        ad_add(A, e[k], out[k]);
+      {
+        if (A.cell_index_out != nullptr)
+          {
+            const int32_t *odx = A.cell_index_out + (size_t)cell * n3;
+            for (int k = 0; k < n; ++k)
+              ad_add(A, odx[(k * n + j) * n + i], out[k]);
+          }
+        else
+          for (int k = 0; k < n; ++k)
+            ad_add(A, e[k], out[k]);
+      }
   }
 
   // diag[g] += v^T K_cell v with v = column g of the cell's constraint matrix, for every DoF g the cell refers to
@@ -299,9 +310,21 @@ namespace mgb
     void        *d_buf[2]   = {nullptr, nullptr};
     int          n_dirichlet = 0;
     int64_t      launches    = 0;
+    // local-smoothing multigrid built on this mesh (adaptive_solver.cuh); dropped whenever the mesh changes
+    void *mg                  = nullptr;
+    void (*mg_deleter)(void *) = nullptr;
+
+    void
+    drop_multigrid()
+    {
+      if (mg && mg_deleter)
+        mg_deleter(mg);
+      mg = nullptr;
+    }
 
     ~AdaptiveOperator()
     {
+      drop_multigrid();
       release_device();
       delete num;
     }
@@ -309,6 +332,7 @@ namespace mgb
     void
     invalidate()
     {
+      drop_multigrid();
       release_device();
       delete num;
       num = nullptr;

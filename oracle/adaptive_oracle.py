@@ -144,3 +144,293 @@ class AdaptiveOracle:
         R = self.C[self.cell_nodes[c]].toarray()
         R[:, self.dirichlet] = 0
         return R
+
+
+# ======================================================================================================================
+# Local-smoothing multigrid on the adaptive mesh (config 5, poisson_l/program.cc:283-420)
+# ======================================================================================================================
+def _chebyshev_setup(A, inv_diag, constrained, smoothing_range, degree, eig_cg_n_iterations):
+    """deal.II PreconditionChebyshev set-up on an assembled matrix: CG/Lanczos estimate of the
+    largest eigenvalue of D^-1 A from the start vector "index mod 11, mean removed, constrained entries zero" (the
+    indices are those of the level numbering, sorted by z, y, x of the support point), then theta / delta."""
+    n = A.shape[0]
+    pattern = (np.arange(n) % 11).astype(np.float64)
+    g = -(pattern - pattern.sum() / n)
+    g[constrained] = 0
+    diag, off = [], []
+    res = np.sqrt(g @ g)
+    its = 0
+    min_eig = max_eig = 1.0
+    if res > 1e-10 and eig_cg_n_iterations > 0:
+        h = inv_diag * g
+        d = -h
+        gh = g @ h
+        alpha_old = beta_old = 0.0
+        it = 1
+        while True:
+            h = A @ d
+            alpha = gh / (d @ h)
+            g = g + alpha * h
+            res = np.sqrt(g @ g)
+            if it == 1:
+                diag.append(1.0 / alpha)
+            else:
+                diag.append(1.0 / alpha + beta_old / alpha_old)
+                off.append(np.sqrt(beta_old) / alpha_old)
+            its = it
+            if it >= eig_cg_n_iterations or res <= 1e-10:
+                break
+            h = inv_diag * g
+            gh_new = g @ h
+            beta = gh_new / gh
+            gh = gh_new
+            d = beta * d - h
+            alpha_old, beta_old = alpha, beta
+            it += 1
+        T = np.diag(diag) + np.diag(off, 1) + np.diag(off, -1)
+        ev = np.linalg.eigvalsh(T)
+        min_eig, max_eig = ev[0], ev[-1]
+    max_est = 1.2 * max_eig
+    alpha = max_est / smoothing_range if smoothing_range > 1.0 else min(0.9 * max_est, min_eig)
+    if degree is None:
+        actual_range = max_est / alpha
+        sigma = (1.0 - np.sqrt(1.0 / actual_range)) / (1.0 + np.sqrt(1.0 / actual_range))
+        eps = smoothing_range
+        degree = 1 + int(np.log(1.0 / eps + np.sqrt(1.0 / eps / eps - 1.0)) / np.log(1.0 / sigma))
+    return dict(theta=0.5 * (max_est + alpha), delta=0.5 * (max_est - alpha), degree=degree, min_eig=min_eig,
+                max_eig=max_eig, cg_iterations=its)
+
+
+def _chebyshev_apply(A, inv_diag, info, b, x=None):
+    """vmult (x = None: zero initial guess, degree - 1 matrix products) or step (degree products)"""
+    theta, delta, degree = info["theta"], info["delta"], info["degree"]
+    if x is None:
+        x = inv_diag * b / theta
+        x_old = np.zeros_like(x)
+    else:
+        x_old = x
+        x = x + inv_diag * (b - A @ x) / theta
+    if degree < 2:
+        return x
+    rhok, sigma = delta / theta, theta / delta
+    for _ in range(degree - 1):
+        rhokp = 1.0 / (2.0 * sigma - rhok)
+        f1, f2 = rhokp * rhok, 2.0 * rhokp / delta
+        rhok = rhokp
+        x, x_old = x + f1 * (x - x_old) + f2 * inv_diag * (b - A @ x), x
+    return x
+
+
+class LocalSmoothingOracle:
+    """PreconditionMG with deal.II's local-smoothing Multigrid on the 2:1-balanced forest, assembled with scipy.
+
+    Level l holds all cells of size root_size / 2^l that are active or refined (parallel::distributed::Triangulation
+    with construct_multigrid_hierarchy).  Level operators (poisson_l/program.cc:283-305): no hanging nodes inside a
+    level; the DoFs on the domain boundary AND on the refinement edge (faces towards coarser active cells) are
+    constrained to zero with identity rows (mg_matrices[level].initialize(mf, mg_constrained_dofs, level)).  Edge
+    matrices (:374-383, MGInterfaceOperator; semantics at gpu/poisson_l.cu:390-436): interface_down(x) = rows of the
+    refinement-edge DoFs of K_level applied to x with the constrained entries zeroed; interface_up(x) = K_level applied
+    to the refinement-edge part of x, constrained rows zeroed.  Transfer: MGTransferMatrixFree with
+    initialize_constraints (:312-313): interpolation of the parent's polynomial, boundary DoFs zero, restriction its
+    transpose.  copy_to_mg / copy_from_mg: the DoFs of the active cells of a level except those on its refinement
+    edge.  Smoothers (:346-363): Chebyshev(point Jacobi), range 15, degree n_smoother, 15 CG steps for the eigenvalue
+    estimate; level 0: range 1e-3 as tolerance, degree automatic, m() CG steps.  V-cycle: deal.II
+    Multigrid::level_v_step with edge_out = edge_in = the interface matrices.  Outer solver (:385-392): SolverCG,
+    ReductionControl(m(), 1e-13, 1e-9), zero start vector.  **Parity unpinned** against deal.II (not available)."""
+
+    def __init__(self, degree, cell_lower, cell_size, root_size, origin, n_smoother=3):
+        self.active = AdaptiveOracle(degree, cell_lower, cell_size)
+        self.p, self.n = degree, degree + 1
+        self.origin = np.asarray(origin, dtype=np.float64)
+        self.root = np.asarray(root_size, dtype=np.float64)
+        lo, sz = self.active.lo, self.active.sz
+        lev = np.round(np.log2(self.root[0] / sz[:, 0])).astype(int)
+        self.n_levels = int(lev.max()) + 1
+        self.scale = sz.min()
+        b = orc.basis(degree)
+        self.gll = b["gll"]
+        # ---- level cell sets: integer positions of active cells and of their ancestors
+        pos = np.round((lo - self.origin) / sz).astype(np.int64)
+        cells = [set() for _ in range(self.n_levels)]
+        active_at = [set() for _ in range(self.n_levels)]
+        for c in range(lo.shape[0]):
+            l, q = int(lev[c]), tuple(int(v) for v in pos[c])
+            active_at[l].add(q)
+            while True:
+                cells[l].add(q)
+                if l == 0:
+                    break
+                l, q = l - 1, tuple(v // 2 for v in q)
+        self.levels = []
+        for l in range(self.n_levels):
+            self.levels.append(self._build_level(l, sorted(cells[l], key=lambda q: (q[2], q[1], q[0])), active_at[l]))
+        for l in range(1, self.n_levels):
+            self._build_transfer(l)
+        self._build_copy_indices()
+        for l, L in enumerate(self.levels):
+            n = L["A"].shape[0]
+            L["inv_diag"] = 1.0 / L["A"].diagonal()
+            if l > 0:
+                L["cheb"] = _chebyshev_setup(L["A"], L["inv_diag"], L["constrained"], 15.0, n_smoother, 15)
+            else:
+                L["cheb"] = _chebyshev_setup(L["A"], L["inv_diag"], L["constrained"], 1e-3, None, n)
+
+    # ------------------------------------------------------------------------------------------------------------------
+    def _key(self, pts):
+        return np.round((pts - self.origin) / (self.scale * 1e-6)).astype(np.int64)
+
+    def _build_level(self, l, cell_pos, active_pos):
+        n, g = self.n, self.gll
+        h = self.root / 2 ** l
+        P = np.array(cell_pos, dtype=np.int64).reshape(-1, 3)
+        lo = self.origin + P * h
+        k, j, i = np.meshgrid(np.arange(n), np.arange(n), np.arange(n), indexing="ij")
+        ref = np.stack([g[i], g[j], g[k]], axis=-1).reshape(-1, 3)
+        X = lo[:, None, :] + h * ref[None, :, :]
+        keys = self._key(X).reshape(-1, 3)
+        # level numbering: sorted by (z, y, x) of the support point
+        uniq, inverse = np.unique(keys[:, ::-1], axis=0, return_inverse=True)
+        nd = uniq.shape[0]
+        cell_dofs = inverse.reshape(P.shape[0], n ** 3)
+        points = np.zeros((nd, 3))
+        points[cell_dofs.ravel()] = X.reshape(-1, 3)
+        # boundary / refinement edge: look into the eight octants around a support point
+        in_level = set(cell_pos)
+        alo, asz = self.active.lo, self.active.sz
+        eps = 1e-4 * self.scale
+        boundary = np.zeros(nd, dtype=bool)
+        edge = np.zeros(nd, dtype=bool)
+        for sx in (-eps, eps):
+            for sy in (-eps, eps):
+                for sz_ in (-eps, eps):
+                    Q = points + np.array([sx, sy, sz_])
+                    inside = np.zeros(nd, dtype=bool)
+                    for c in range(alo.shape[0]):
+                        inside |= np.all((Q > alo[c]) & (Q < alo[c] + asz[c]), axis=1)
+                    boundary |= ~inside
+                    qpos = np.floor((Q - self.origin) / h).astype(np.int64)
+                    covered = np.array([tuple(v) in in_level for v in qpos])
+                    edge |= inside & ~covered
+        edge &= ~boundary
+        constrained = boundary | edge
+        # assembly without constraints
+        M1, K1 = self.active.M1, self.active.K1
+        vol = h[0] * h[1] * h[2]
+        Kc = vol * (np.kron(M1, np.kron(M1, K1)) / h[0] ** 2 + np.kron(M1, np.kron(K1, M1)) / h[1] ** 2 +
+                    np.kron(K1, np.kron(M1, M1)) / h[2] ** 2)
+        rows = np.repeat(cell_dofs, n ** 3, axis=1).ravel()
+        cols = np.tile(cell_dofs, (1, n ** 3)).ravel()
+        K = sp.csr_matrix((np.tile(Kc.ravel(), P.shape[0]), (rows, cols)), shape=(nd, nd))
+        keep = sp.diags((~constrained).astype(float))
+        A = (keep @ K @ keep + sp.diags(constrained.astype(float))).tocsr()
+        return dict(pos=cell_pos, pos_index={q: c for c, q in enumerate(cell_pos)}, active=active_pos, h=h, lo=lo,
+                    cell_dofs=cell_dofs, points=points, boundary=boundary, edge=edge, constrained=constrained, K=K, A=A,
+                    n=nd)
+
+    def _build_transfer(self, l):
+        """P (n_l x n_{l-1}): value of the parent's polynomial at every support point of its children"""
+        F, C = self.levels[l], self.levels[l - 1]
+        n, g = self.n, self.gll
+        rows, cols, vals = [], [], []
+        done = np.zeros(F["n"], dtype=bool)
+        for c, q in enumerate(F["pos"]):
+            parent = C["pos_index"][tuple(v // 2 for v in q)]
+            plo, ph = C["lo"][parent], C["h"]
+            for loc, f in enumerate(F["cell_dofs"][c]):
+                if done[f]:
+                    continue
+                done[f] = True
+                xi = (F["points"][f] - plo) / ph
+                w = [lagrange(g, xi[d])[0] for d in range(3)]
+                W = np.einsum("c,b,a->cba", w[2], w[1], w[0]).ravel()
+                nz = np.abs(W) > 1e-13
+                rows += [f] * int(nz.sum())
+                cols += list(C["cell_dofs"][parent][nz])
+                vals += list(W[nz])
+        P = sp.csr_matrix((vals, (rows, cols)), shape=(F["n"], C["n"]))
+        P = sp.diags((~F["boundary"]).astype(float)) @ P @ sp.diags((~C["boundary"]).astype(float))
+        F["P"] = P.tocsr()
+
+    def _build_copy_indices(self):
+        """(active DoF, level DoF) pairs per level: support points of the active cells of the level that carry an
+        unconstrained active DoF and do not lie on the level's refinement edge"""
+        act = self.active
+        lut = {tuple(k): d for d, k in enumerate(act._key(act.points))}
+        for L in self.levels:
+            pairs = {}
+            for q in L["active"]:
+                c = L["pos_index"][q]
+                for f in L["cell_dofs"][c]:
+                    if L["edge"][f] or L["boundary"][f]:
+                        continue
+                    d = lut.get(tuple(act._key(L["points"][f][None, :])[0]))
+                    if d is not None and not act.dirichlet[d]:
+                        pairs[int(f)] = d
+            L["copy_level"] = np.array(sorted(pairs), dtype=np.int64)
+            L["copy_active"] = np.array([pairs[f] for f in sorted(pairs)], dtype=np.int64)
+
+    # ------------------------------------------------------------------------------------------------------------------
+    def interface_down(self, l, x):
+        L = self.levels[l]
+        y = L["K"] @ np.where(L["constrained"], 0.0, x)
+        return np.where(L["edge"], y, 0.0)
+
+    def interface_up(self, l, x):
+        L = self.levels[l]
+        y = L["K"] @ np.where(L["edge"], x, 0.0)
+        return np.where(L["constrained"], 0.0, y)
+
+    def level_v_step(self, l, defect, solution):
+        L = self.levels[l]
+        if l == 0:
+            solution[0] = _chebyshev_apply(L["A"], L["inv_diag"], L["cheb"], defect[0])
+            return
+        solution[l] = _chebyshev_apply(L["A"], L["inv_diag"], L["cheb"], defect[l])
+        t = L["A"] @ solution[l] + self.interface_down(l, solution[l])
+        t = defect[l] - t
+        defect[l - 1] = defect[l - 1] + L["P"].T @ t
+        self.level_v_step(l - 1, defect, solution)
+        solution[l] = solution[l] + L["P"] @ solution[l - 1]
+        defect[l] = defect[l] - self.interface_up(l, solution[l])
+        solution[l] = _chebyshev_apply(L["A"], L["inv_diag"], L["cheb"], defect[l], solution[l])
+
+    def vmult(self, src):
+        """PreconditionMG::vmult: copy_to_mg, one V-cycle, copy_from_mg"""
+        defect = [np.zeros(L["n"]) for L in self.levels]
+        solution = [np.zeros(L["n"]) for L in self.levels]
+        for l, L in enumerate(self.levels):
+            defect[l][L["copy_level"]] = src[L["copy_active"]]
+        self.level_v_step(self.n_levels - 1, defect, solution)
+        dst = np.zeros_like(src)
+        for l, L in enumerate(self.levels):
+            dst[L["copy_active"]] = solution[l][L["copy_level"]]
+        return dst
+
+    def solve_cg(self, rhs, rel_tol=1e-9, abs_tol=1e-13):
+        """deal.II SolverCG on the active operator, preconditioned by vmult; returns (x, iterations, residual history)"""
+        K = self.active.K
+        x = np.zeros_like(rhs)
+        g = -rhs.copy()
+        res0 = res = np.sqrt(g @ g)
+        hist = [res]
+        it = 0
+        if res > abs_tol:
+            h = self.vmult(g)
+            d = -h
+            gh = g @ h
+            while True:
+                it += 1
+                h = K @ d
+                alpha = gh / (d @ h)
+                x += alpha * d
+                g += alpha * h
+                res = np.sqrt(g @ g)
+                hist.append(res)
+                if res <= abs_tol or res <= rel_tol * res0 or it >= rhs.size:
+                    break
+                h = self.vmult(g)
+                gh_new = g @ h
+                beta = gh_new / gh
+                gh = gh_new
+                d = beta * d - h
+        return x, it, np.array(hist)

@@ -73,3 +73,46 @@ def test_refine_after_use_rebuilds(mgb, torch):
     op.vmult(y, x)
     # constants: A 1 vanishes away from the Dirichlet boundary's neighbourhood is not true in general; check energy >= 0
     assert float(x @ y) > 0
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_local_smoothing_solver(mgb, torch, name):
+    """config 5 as a solve: local-smoothing V-cycle (level operators with constrained refinement edges, edge matrices,
+    transfer between partially refined levels, Chebyshev smoothers; all float) inside CG (double) on the operator with
+    hanging-node constraints, against the assembled oracle composition (poisson_l/program.cc:283-420)"""
+    from oracle import adaptive_oracle
+    op = make(mgb, name)
+    lo, sz = op.cell_boxes()
+    root = (np.array(op.upper) - np.array(op.lower)) / np.array(op.n_roots)
+    o = adaptive_oracle.LocalSmoothingOracle(op.degree, lo, sz, root, op.lower, n_smoother=3)
+    perm = o.active.permutation_to(op.dof_points())
+    op.setup_multigrid(3)
+    assert op.n_levels == o.n_levels
+    for l in range(o.n_levels):
+        g, L = op.mg_level_info(l), o.levels[l]
+        assert (g["n_dofs"], g["n_edge_dofs"], g["n_copy"]) == (L["n"], int(L["edge"].sum()), L["copy_level"].size), (l, g)
+        assert g["n_constrained"] == int(L["constrained"].sum())
+        assert g["degree"] == L["cheb"]["degree"], (l, g, L["cheb"])
+        assert abs(g["max_eig"] - L["cheb"]["max_eig"]) <= 1e-3 * L["cheb"]["max_eig"], (l, g, L["cheb"])
+    free = ~op.dirichlet_mask()
+    rng = np.random.default_rng(5)
+    b = np.where(free, rng.standard_normal(op.m()), 0.0)
+    bo = np.zeros_like(b)
+    bo[perm] = b
+    # one application of the preconditioner
+    src = torch.tensor(b, device="cuda")
+    dst = torch.zeros_like(src)
+    op.mg_vmult(dst, src)
+    ref = o.vmult(bo)[perm]
+    assert rel(dst.cpu().numpy(), ref) <= 5e-3, rel(dst.cpu().numpy(), ref)
+    # the solve
+    x = torch.zeros_like(src)
+    its, rate, hist = op.solve_cg(x, src)
+    xo, its_o, hist_o = o.solve_cg(bo)
+    assert its == its_o, (its, its_o)
+    assert np.allclose(hist, hist_o, rtol=0.05), (hist, hist_o)
+    assert rel(x.cpu().numpy(), xo[perm]) <= 1e-6
+    # and it solves the system of the device operator
+    r = torch.zeros_like(src)
+    op.vmult(r, x)
+    assert float((r - src).norm()) <= 2e-9 * float(src.norm())

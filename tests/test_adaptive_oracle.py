@@ -97,3 +97,30 @@ def test_refinement_api_errors(mgb):
         for _ in range(13):
             lo, sz = deep.cell_boxes()
             deep.refine(np.linalg.norm(lo, axis=1) < 1e-9 + np.linalg.norm(lo, axis=1).min())
+
+
+@pytest.mark.parametrize("name", ["hyper_l_p2", "extruded_l_p1", "box_point_p2"])
+def test_local_smoothing_oracle_properties(mgb, ado, name):
+    """the local-smoothing multigrid restatement (poisson_l/program.cc:283-420): every unconstrained active DoF is copied
+    from / to exactly one level, the preconditioner is symmetric positive, the edge matrices are transposes of each other
+    on the unconstrained / refinement-edge blocks, CG converges at a multigrid rate to the solution of the active system"""
+    op = make(mgb, name)
+    lo, sz = op.cell_boxes()
+    root = (np.array(op.upper) - np.array(op.lower)) / np.array(op.n_roots)
+    o = ado.LocalSmoothingOracle(op.degree, lo, sz, root, op.lower, n_smoother=3)
+    act = o.active
+    free = ~act.dirichlet
+    copied = np.concatenate([L["copy_active"] for L in o.levels])
+    assert np.array_equal(np.sort(copied), np.where(free)[0])
+    assert sum(int(L["edge"].sum()) for L in o.levels) > 0          # the case has refinement edges
+    rng = np.random.default_rng(2)
+    u, v = (np.where(free, rng.standard_normal(free.size), 0.0) for _ in range(2))
+    Mu, Mv = o.vmult(u), o.vmult(v)
+    assert abs(v @ Mu - u @ Mv) <= 1e-10 * abs(v @ Mu) and u @ Mu > 0
+    for l in range(1, o.n_levels):
+        L = o.levels[l]
+        a, b = rng.standard_normal(L["n"]), rng.standard_normal(L["n"])
+        assert abs(b @ o.interface_down(l, a) - a @ o.interface_up(l, b)) <= 1e-10 * (np.abs(L["K"]).sum() ** 0.5 + 1)
+    x, its, hist = o.solve_cg(u)
+    assert its <= 14 and (hist[-1] / hist[0]) ** (1.0 / its) < 0.25
+    assert np.linalg.norm(act.K @ x - u) <= 1e-8 * np.linalg.norm(u)
