@@ -129,6 +129,25 @@ int mgb_solver_vcycle(mgb_solver s, double *dst_dev, const double *src_dev);
  * factor update_old> over all ranks (factor == 0: residual untouched, sums[1] = sums[0]); Dirichlet rows are identity rows. */
 int mgb_solver_vmult_with_residual_update(mgb_solver s, double *residual_dev, double *update_dev, double factor,
                                           double sums[2]);
+/* Problem data supplied by the caller instead of the built-in MGB_PROBLEM_* functions -- what the reference passes as
+ * Function<dim> objects (MultigridSolver(dof_handler, boundary_values, right_hand_side, coefficient, ...),
+ * multigrid_solver.h:100-106; LaplaceOperator::evaluate_coefficient(const Function &) and compute_residual(dst, src,
+ * rhs_function), laplace_operator.h:103-109).  The caller evaluates its functions at the points the library reports:
+ *   quadrature points   [cell][q][3], cells of this rank's box in lexicographic order (x fastest), q = (q2 n + q1) n + q0
+ *                       (FEEvaluation::quadrature_point); n_quadrature_points = cells (p+1)^3
+ *   support points      [dof][3] in the library's numbering (VectorTools::interpolate_boundary_values positions)
+ * set_coefficient_values: c at the quadrature points of one level (call it for every level, then reinit_smoothers, which
+ * recomputes the diagonals and the Chebyshev eigenvalue estimates); set_rhs_values: f at the quadrature points and the
+ * Dirichlet values at the support points (one value per DoF, non-boundary entries ignored; NULL = homogeneous) of one
+ * level -> rhs = int f phi - K u_bc (solve_cg needs the finest level, the FMG solve() all levels);
+ * set_exact_solution_values: u at the quadrature points, used by mgb_solver_l2_error instead of the built-in solution. */
+int64_t mgb_solver_n_quadrature_points(mgb_solver s, int level);
+int mgb_solver_quadrature_points(mgb_solver s, int level, double *xyz_host);
+int mgb_solver_support_points(mgb_solver s, int level, double *xyz_host);
+int mgb_solver_set_coefficient_values(mgb_solver s, int level, const double *c_host);
+int mgb_solver_reinit_smoothers(mgb_solver s);
+int mgb_solver_set_rhs_values(mgb_solver s, int level, const double *f_host, const double *u_boundary_host);
+int mgb_solver_set_exact_solution_values(mgb_solver s, int level, const double *u_host);
 /* MultigridSolver::do_matvec / do_matvec_smoother         multigrid_solver.h:624-637 */
 int mgb_solver_do_matvec(mgb_solver s);
 int mgb_solver_do_matvec_smoother(mgb_solver s);

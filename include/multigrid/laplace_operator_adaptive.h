@@ -54,12 +54,40 @@ namespace multigrid
       return (std::size_t)n;
     }
     std::size_t n() const { return m(); }
+    // 1 for the DoFs on the Dirichlet boundary (identity rows of the operator)
+    std::vector<unsigned char>
+    dirichlet_mask() const
+    {
+      std::vector<unsigned char> mask(m());
+      check(mgb_adaptive_dirichlet(h_, mask.data()));
+      return mask;
+    }
     void        initialize_dof_vector(VectorType &v) const { v.reinit(m()); }
     // laplace_operator.h:575-601 with the constraints applied in the kernel
     void vmult(VectorType &dst, const VectorType &src) const { check(mgb_adaptive_vmult(h_, prec, dst.begin(), src.begin())); }
     // compute_diagonal + get_matrix_diagonal_inverse   laplace_operator.h:747-800
     void compute_diagonal(VectorType &inverse_diagonal) const { check(mgb_adaptive_inverse_diagonal(h_, prec, inverse_diagonal.begin())); }
     void synchronize() const { check(mgb_adaptive_sync(h_)); }
+
+    // ---- the solver of poisson_l/program.cc:337-420 on this mesh (double vectors only): level operators with constrained
+    // refinement edges, MGInterfaceOperator edge matrices, MGTransferMatrixFree, Chebyshev smoothers of degree n_smoother
+    void setup_multigrid(const unsigned int n_smoother) { check(mgb_adaptive_mg_setup(h_, (int)n_smoother)); }
+    unsigned int n_levels() const { return (unsigned int)mgb_adaptive_mg_n_levels(h_); }
+    // PreconditionMG::vmult: one local-smoothing V-cycle in float
+    void
+    precondition(DGVector<double> &dst, const DGVector<double> &src) const
+    {
+      check(mgb_adaptive_mg_vmult(h_, dst.begin(), src.begin()));
+    }
+    // SolverCG with ReductionControl(m(), 1e-13, rel_tol) from a zero start vector; (iterations, reduction per iteration)
+    std::pair<unsigned int, double>
+    solve_cg(DGVector<double> &x, const DGVector<double> &rhs, const double rel_tol = 1e-9) const
+    {
+      unsigned int its  = 0;
+      double       rate = 0;
+      check(mgb_adaptive_solve_cg(h_, x.begin(), rhs.begin(), rel_tol, &its, &rate, nullptr, nullptr));
+      return std::make_pair(its, rate);
+    }
 
   private:
     static constexpr int prec = precision_of<number>::value;

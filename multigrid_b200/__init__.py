@@ -114,6 +114,13 @@ SYMBOLS = {
     "mgb_solver_l2_error": (_i, [_vp, _i, _dp]),
     "mgb_solver_vcycle": (_i, [_vp, _vp, _vp]),
     "mgb_solver_vmult_with_residual_update": (_i, [_vp, _vp, _vp, _d, C.POINTER(C.c_double)]),
+    "mgb_solver_n_quadrature_points": (C.c_int64, [_vp, _i]),
+    "mgb_solver_quadrature_points": (_i, [_vp, _i, _dp]),
+    "mgb_solver_support_points": (_i, [_vp, _i, _dp]),
+    "mgb_solver_set_coefficient_values": (_i, [_vp, _i, _dp]),
+    "mgb_solver_reinit_smoothers": (_i, [_vp]),
+    "mgb_solver_set_rhs_values": (_i, [_vp, _i, _dp, _dp]),
+    "mgb_solver_set_exact_solution_values": (_i, [_vp, _i, _dp]),
     "mgb_solver_do_matvec": (_i, [_vp]),
     "mgb_solver_do_matvec_smoother": (_i, [_vp]),
     "mgb_solver_timings": (_i, [_vp, _dp, _i]),
@@ -512,6 +519,48 @@ class MultigridSolver:
         self._torch_sync()
         _check(lib().mgb_solver_vcycle(self.h, _ptr(dst), _ptr(src)))
         self.sync()
+
+    # ---- problem data supplied by the caller (the reference's Function<dim> arguments, multigrid_solver.h:100-106)
+    def quadrature_points(self, level=-1):
+        """(n_cells (p+1)^3, 3): cells lexicographic (x fastest) on this rank's box, points x fastest inside a cell"""
+        l = self._l(level)
+        out = np.zeros((lib().mgb_solver_n_quadrature_points(self.h, l), 3))
+        _check(lib().mgb_solver_quadrature_points(self.h, l, out.ctypes.data_as(_dp)))
+        return out
+
+    def support_points(self, level=-1):
+        """(n_dofs, 3) in the library's numbering"""
+        out = np.zeros((self.n_dofs(level), 3))
+        _check(lib().mgb_solver_support_points(self.h, self._l(level), out.ctypes.data_as(_dp)))
+        return out
+
+    def set_problem(self, coefficient=None, right_hand_side=None, boundary_values=None, exact_solution=None):
+        """Functions f(x, y, z) -> values on arrays, evaluated here at the library's quadrature / support points of every
+        level and handed over as samples (LaplaceOperator::evaluate_coefficient(const Function &), compute_residual(...,
+        rhs_function), interpolate_boundary_values)."""
+        for l in range(self.n_levels):
+            xq = None
+            if coefficient is not None or right_hand_side is not None or exact_solution is not None:
+                xq = self.quadrature_points(l)
+            if coefficient is not None:
+                c = np.ascontiguousarray(coefficient(xq[:, 0], xq[:, 1], xq[:, 2]), dtype=np.float64)
+                _check(lib().mgb_solver_set_coefficient_values(self.h, l, c.ctypes.data_as(_dp)))
+        if coefficient is not None:
+            _check(lib().mgb_solver_reinit_smoothers(self.h))
+        for l in range(self.n_levels):
+            if right_hand_side is not None:
+                xq = self.quadrature_points(l)
+                f = np.ascontiguousarray(right_hand_side(xq[:, 0], xq[:, 1], xq[:, 2]), dtype=np.float64)
+                g = None
+                if boundary_values is not None:
+                    xs = self.support_points(l)
+                    g = np.ascontiguousarray(boundary_values(xs[:, 0], xs[:, 1], xs[:, 2]), dtype=np.float64)
+                _check(lib().mgb_solver_set_rhs_values(self.h, l, f.ctypes.data_as(_dp),
+                                                       g.ctypes.data_as(_dp) if g is not None else None))
+            if exact_solution is not None:
+                xq = self.quadrature_points(l)
+                u = np.ascontiguousarray(exact_solution(xq[:, 0], xq[:, 1], xq[:, 2]), dtype=np.float64)
+                _check(lib().mgb_solver_set_exact_solution_values(self.h, l, u.ctypes.data_as(_dp)))
 
     def vmult_with_residual_update(self, residual, update, factor):
         """multigrid_solver.h:516-619: residual += factor update; update = V-cycle(residual); returns

@@ -618,13 +618,15 @@ namespace mgb
           {
             double x[3], J[3][3];
             mapped_point<p>(X, q0, q1, q2, x, J);
-            v[q] = eval_fn(A.fn_id, x[0], x[1], x[2]) * ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * fabs(det3(J));
+            const double f = A.values ? A.values[(size_t)cell * n3 + q] : eval_fn(A.fn_id, x[0], x[1], x[2]);
+            v[q]           = f * ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * fabs(det3(J));
             continue;
           }
         const double x = A.L.lo[0] + (cx + ctab.xq[q0]) * A.L.h[0];
         const double y = A.L.lo[1] + (cy + ctab.xq[q1]) * A.L.h[1];
         const double z = A.L.lo[2] + (cz + ctab.xq[q2]) * A.L.h[2];
-        v[q]           = eval_fn(A.fn_id, x, y, z) * ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * detJ;
+        const double f = A.values ? A.values[(size_t)cell * n3 + q] : eval_fn(A.fn_id, x, y, z);
+        v[q]           = f * ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * detJ;
       }
     __syncthreads();
     for (int l = threadIdx.x; l < n3; l += blockDim.x)
@@ -651,6 +653,47 @@ namespace mgb
   {
     constexpr int n3 = (p + 1) * (p + 1) * (p + 1);
     k_rhs_values<p><<<A.L.n_cells, n3 < 256 ? ((n3 + 31) / 32) * 32 : 256, 0, stream>>>(A);
+  }
+
+  // ------------------------------------------------------------------ quadrature points
+  template <int p>
+  __global__ void
+  k_quadrature_points(const PointsArgs A)
+  {
+    constexpr int     n = p + 1, n3 = n * n * n;
+    __shared__ double X[3 * n3];
+    const uint32_t    cell = blockIdx.x;
+    int               cx, cy, cz;
+    cell_coords(A.L, cell, cx, cy, cz);
+    const bool mapped = A.geom.kind != 0;
+    if (mapped)
+      {
+        cell_support_points<p>(A.geom, A.L, cx, cy, cz, X);
+        __syncthreads();
+      }
+    for (int q = threadIdx.x; q < n3; q += blockDim.x)
+      {
+        const int q0 = q % n, q1 = (q / n) % n, q2 = q / (n * n);
+        double    x[3] = {A.L.lo[0] + (cx + ctab.xq[q0]) * A.L.h[0], A.L.lo[1] + (cy + ctab.xq[q1]) * A.L.h[1],
+                          A.L.lo[2] + (cz + ctab.xq[q2]) * A.L.h[2]};
+        if (mapped)
+          {
+            double J[3][3];
+            mapped_point<p>(X, q0, q1, q2, x, J);
+          }
+        double *o = A.xyz + ((size_t)cell * n3 + q) * 3;
+        o[0]      = x[0];
+        o[1]      = x[1];
+        o[2]      = x[2];
+      }
+  }
+
+  template <int p>
+  void
+  launch_quadrature_points(const PointsArgs &A, cudaStream_t stream)
+  {
+    constexpr int n3 = (p + 1) * (p + 1) * (p + 1);
+    k_quadrature_points<p><<<A.L.n_cells, n3 < 128 ? ((n3 + 31) / 32) * 32 : 128, 0, stream>>>(A);
   }
 
   // ------------------------------------------------------------------ L2 error
@@ -704,7 +747,7 @@ namespace mgb
             z   = xm[2];
             JxW = ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * fabs(det3(J));
           }
-        const double diff = val - eval_fn(A.fn_id, x, y, z);
+        const double diff = val - (A.values ? A.values[(size_t)cell * n3 + q] : eval_fn(A.fn_id, x, y, z));
         err += diff * diff * JxW;
         vol += JxW;
       }

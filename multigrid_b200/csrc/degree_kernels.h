@@ -70,6 +70,7 @@ namespace mgb
     Geometry  geom;
     double   *dst; // += int f phi
     int       fn_id;
+    const double *values = nullptr; // caller-supplied f at the quadrature points [cell][n^3] instead of fn_id
   };
 
   struct ErrorArgs
@@ -79,6 +80,15 @@ namespace mgb
     const double *u;
     int           fn_id;
     double       *accum; // [0] += error^2, [1] += volume
+    const double *values = nullptr; // caller-supplied exact solution at the quadrature points [cell][n^3] instead of fn_id
+  };
+
+  // quadrature points of all cells, [cell][n^3][3] (FEEvaluation::quadrature_point, laplace_operator.h:400-407)
+  struct PointsArgs
+  {
+    LevelDesc L;
+    Geometry  geom;
+    double   *xyz;
   };
 
   // merged coefficient c(x_q) JxW J^-1 J^-T per quadrature point on a mapped mesh (laplace_operator.h:388-430)
@@ -107,6 +117,7 @@ namespace mgb
     void (*coefficient_f)(const CoefArgs<float> &, cudaStream_t);
     void (*coefficient_d)(const CoefArgs<double> &, cudaStream_t);
     void (*rhs_values)(const RhsArgs &, cudaStream_t);
+    void (*quadrature_points)(const PointsArgs &, cudaStream_t);
     void (*l2_error)(const ErrorArgs &, cudaStream_t);
   };
 

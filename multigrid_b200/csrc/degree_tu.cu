@@ -27,6 +27,7 @@ namespace mgb
                                     &launch_coefficient<MGB_P, float>,
                                     &launch_coefficient<MGB_P, double>,
                                     &launch_rhs_values<MGB_P>,
+                                    &launch_quadrature_points<MGB_P>,
                                     &launch_l2_error<MGB_P>};
     return k;
   }

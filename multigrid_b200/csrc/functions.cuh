@@ -13,7 +13,8 @@ namespace mgb
     FN_CUBE_RHS,
     FN_SHELL_SOLUTION,
     FN_SHELL_RHS,
-    FN_SHELL_COEFFICIENT
+    FN_SHELL_COEFFICIENT,
+    FN_ONE_PER_POINT // the value 1 stored per quadrature point (to be scaled by caller-supplied samples)
   };
 
   __host__ __device__ inline double
@@ -23,6 +24,7 @@ namespace mgb
     switch (id)
       {
         case FN_ONE:
+        case FN_ONE_PER_POINT:
           return 1.;
         case FN_CUBE_SOLUTION: // poisson_cube/program.cc:98-104, wave_number = 3
           return sin(pi * x * 3.) * sin(pi * y * 3.) * sin(pi * z * 3.);

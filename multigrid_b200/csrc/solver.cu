@@ -1152,6 +1152,25 @@ namespace mgb
       });
     }
 
+    // evaluate_coefficient(const Function &) with the function sampled by the caller (laplace_operator.h:108-109,
+    // :388-430): c[cell][q] at the quadrature points; the geometry part JxW J^-1 J^-T comes from the mesh
+    void
+    set_coefficient_values(const Basis &basis, const Geometry &geom, const double *c_dev)
+    {
+      const LevelDesc &L  = level->d;
+      const int        n3 = L.n * L.n * L.n;
+      evaluate_coefficient(basis, FN_ONE_PER_POINT, geom); // per-point tensors of the geometry alone
+      cartesian   = false;
+      T *cq       = coef_q.p;
+      foreach (*ctx, (size_t)L.n_cells * n3, [=] __device__(size_t idx) {
+        const size_t cell = idx / n3, q = idx - cell * n3;
+        const T      c    = (T)c_dev[idx];
+        T           *e    = cq + cell * 6 * n3 + q;
+        for (int k = 0; k < 6; ++k)
+          e[k * n3] *= c;
+      });
+    }
+
     bool use_cartesian() const
     {
       // the streaming kernel is compiled for the default tile width of the degree
@@ -1913,10 +1932,154 @@ namespace mgb
       });
     }
 
+    // ---- problem data supplied by the caller instead of the built-in functions (what evaluate_coefficient(const
+    //      Function &) and compute_residual(dst, src, rhs_function) of laplace_operator.h:103-109 take): samples at the
+    //      quadrature points, cells in lexicographic order (x fastest) of this rank's box, points x fastest inside a cell
+    DVec<double> caller_values;          // staging for one level
+    std::vector<std::unique_ptr<DVec<double>>> exact_q; // caller's exact solution at the quadrature points, per level
+    bool         smoothers_stale = false;
+
+    size_t
+    n_quadrature_points(const int level) const
+    {
+      const LevelDesc &L = levels[level]->d;
+      return (size_t)L.n_cells * L.n * L.n * L.n;
+    }
+
+    void
+    quadrature_points(const int level, double *xyz_host)
+    {
+      const size_t nq = n_quadrature_points(level);
+      DVec<double> buf;
+      buf.alloc(3 * nq, ctx.stream);
+      PointsArgs A;
+      A.L    = levels[level]->d;
+      A.geom = geom;
+      A.xyz  = buf.p;
+      degree_kernels(opt.degree).quadrature_points(A, ctx.stream);
+      ctx.check_launch();
+      MGB_CUDA_CHECK(cudaMemcpyAsync(xyz_host, buf.p, 3 * nq * sizeof(double), cudaMemcpyDeviceToHost, ctx.stream));
+      ctx.sync();
+    }
+
+    void
+    support_points(const int level, double *xyz_host)
+    {
+      const LevelDesc L = levels[level]->d;
+      DVec<double>    buf;
+      buf.alloc(3 * (size_t)L.n_dofs, ctx.stream);
+      Nodes1D nd;
+      for (int i = 0; i <= opt.degree; ++i)
+        nd.nodes[i] = basis.nodes[i];
+      double        *out = buf.p;
+      const Geometry gm  = geom;
+      patch_points(ctx, L, [=] __device__(uint32_t dof, bool, int gi, int gj, int gk) {
+        double x[3] = {support_point(L, nd, 0, gi), support_point(L, nd, 1, gj), support_point(L, nd, 2, gk)};
+        if (gm.kind != MGB_GEOMETRY_BOX)
+          geometry_point(gm, unit_coordinate(L, nd, 0, gi), unit_coordinate(L, nd, 1, gj), unit_coordinate(L, nd, 2, gk), x);
+        out[3 * (size_t)dof]     = x[0];
+        out[3 * (size_t)dof + 1] = x[1];
+        out[3 * (size_t)dof + 2] = x[2];
+      });
+      MGB_CUDA_CHECK(cudaMemcpyAsync(xyz_host, buf.p, 3 * (size_t)L.n_dofs * sizeof(double), cudaMemcpyDeviceToHost, ctx.stream));
+      ctx.sync();
+    }
+
+    void
+    stage_values(const double *host, const size_t count)
+    {
+      if (caller_values.n < count)
+        caller_values.alloc(count, ctx.stream);
+      MGB_CUDA_CHECK(cudaMemcpyAsync(caller_values.p, host, count * sizeof(double), cudaMemcpyHostToDevice, ctx.stream));
+    }
+
+    void
+    set_coefficient_values(const int level, const double *c_host)
+    {
+      stage_values(c_host, n_quadrature_points(level));
+      matrix[level]->set_coefficient_values(basis, geom, caller_values.p);
+      matrix_dp[level]->set_coefficient_values(basis, geom, caller_values.p);
+      ctx.sync();
+      smoothers_stale = true;
+      cycle_graphs_invalidate();
+    }
+
+    // diagonals and Chebyshev eigenvalue estimates after the coefficient changed (multigrid_solver.h:268-289)
+    void
+    reinit_smoothers()
+    {
+      for (int l = 0; l < n_levels; ++l)
+        {
+          matrix[l]->compute_diagonal();
+          Chebyshev<float> &s = *smooth[l];
+          if (l == 0)
+            {
+              s.degree              = Chebyshev<float>::invalid_degree;
+              s.eig_cg_n_iterations = (unsigned int)matrix[0]->m_global();
+            }
+          s.initialize(ctx, *matrix[l], basis);
+        }
+      cycle_graphs_invalidate();
+      choose_graph_level();
+      smoothers_stale = false;
+      ctx.sync();
+    }
+
+    // rhs = int f phi - K u_bc with f sampled at the quadrature points and the boundary values at the support points
+    // (u_bc_host: one value per DoF of the level, only the Dirichlet entries are used; null = homogeneous)
+    void
+    set_rhs_values(const int level, const double *f_host, const double *u_bc_host)
+    {
+      const LevelDesc L = levels[level]->d;
+      const size_t    N = L.n_dofs;
+      double         *bc = bc_values[level]->p;
+      MGB_CUDA_CHECK(cudaMemsetAsync(bc, 0, N * sizeof(double), ctx.stream));
+      if (u_bc_host)
+        {
+          stage_values(u_bc_host, N);
+          const double   *v     = caller_values.p;
+          const uint32_t *clist = levels[level]->constrained.p;
+          foreach (ctx, levels[level]->constrained.n, [=] __device__(size_t i) { bc[clist[i]] = v[clist[i]]; });
+        }
+      double *neg = residual[level]->p;
+      foreach (ctx, N, [=] __device__(size_t i) { neg[i] = -bc[i]; });
+      MGB_CUDA_CHECK(cudaMemsetAsync(rhs[level]->p, 0, N * sizeof(double), ctx.stream));
+      matrix_dp[level]->apply(APPLY_ADD, rhs[level]->p, neg, nullptr, nullptr, 0, 0, 0, /*read_plain=*/true);
+      ctx.sync(); // the staging buffer is reused below
+      stage_values(f_host, n_quadrature_points(level));
+      RhsArgs R;
+      R.L      = L;
+      R.geom   = geom;
+      R.dst    = rhs[level]->p;
+      R.fn_id  = FN_ZERO;
+      R.values = caller_values.p;
+      degree_kernels(opt.degree).rhs_values(R, ctx.stream);
+      ctx.check_launch();
+      levels[level]->update_ghosts(rhs[level]->p);
+      MGB_CUDA_CHECK(cudaMemsetAsync(residual[level]->p, 0, N * sizeof(double), ctx.stream));
+      ctx.sync();
+    }
+
+    // the exact solution for compute_l2_error, sampled at the quadrature points of `level`
+    void
+    set_exact_solution_values(const int level, const double *u_host)
+    {
+      if ((int)exact_q.size() < n_levels)
+        exact_q.resize(n_levels);
+      if (!exact_q[level])
+        exact_q[level].reset(new DVec<double>());
+      const size_t nq = n_quadrature_points(level);
+      exact_q[level]->alloc(nq, ctx.stream);
+      MGB_CUDA_CHECK(cudaMemcpyAsync(exact_q[level]->p, u_host, nq * sizeof(double), cudaMemcpyHostToDevice, ctx.stream));
+      ctx.sync();
+    }
+
     // multigrid_solver.h:298-343
     double
     compute_l2_error(const int level)
     {
+      if (smoothers_stale)
+        throw std::runtime_error("the coefficient changed: call mgb_solver_reinit_smoothers before solving");
       set_boundary_values(level, false);
       levels[level]->update_ghosts(solution[level]->p);
       MGB_CUDA_CHECK(cudaMemsetAsync(ctx.scal_dev, 0, 2 * sizeof(double), ctx.stream));
@@ -1926,6 +2089,8 @@ namespace mgb
       E.u     = solution[level]->p;
       E.fn_id = fn_solution;
       E.accum = ctx.scal_dev;
+      if ((int)exact_q.size() > level && exact_q[level])
+        E.values = exact_q[level]->p;
       degree_kernels(opt.degree).l2_error(E, ctx.stream);
       ctx.check_launch();
       if (levels[level]->slab.distributed)
@@ -1960,6 +2125,16 @@ namespace mgb
           st.push_back(smooth[l]->solution_old.p);
         }
       return st;
+    }
+
+    void
+    cycle_graphs_invalidate()
+    {
+      ctx.sync();
+      for (CycleGraph &g : cycle_graphs)
+        if (g.exec)
+          cudaGraphExecDestroy(g.exec);
+      cycle_graphs.clear();
     }
 
     void
@@ -2249,6 +2424,8 @@ namespace mgb
     std::pair<unsigned int, double>
     solve_cg()
     {
+      if (smoothers_stale)
+        throw std::runtime_error("the coefficient changed: call mgb_solver_reinit_smoothers before solving");
       // deal.II SolverCG (x0 = 0): g = -b; h = M^-1 g; d = -h; loop { h = A d; alpha = g.h_old / d.h;
       // x += alpha d; g += alpha h; check |g|; h = M^-1 g; beta = g.h / g.h_old; d = beta d - h }.
       // Vector work is fused as in the reference's merged loops (laplace_operator.h:640-719,
@@ -2772,6 +2949,74 @@ extern "C"
     const std::array<double, 2> r = S(s).vmult_with_residual_update(residual_dev, update_dev, factor);
     sums[0]                       = r[0];
     sums[1]                       = r[1];
+    MGB_CATCH
+  }
+
+  int64_t
+  mgb_solver_n_quadrature_points(mgb_solver s, int level)
+  {
+    try
+      {
+        MultigridSolver &m = S(s);
+        return (int64_t)m.n_quadrature_points(check_level(m, level));
+      }
+    catch (const std::exception &e)
+      {
+        g_last_error = e.what();
+        return -1;
+      }
+  }
+
+  int
+  mgb_solver_quadrature_points(mgb_solver s, int level, double *xyz_host)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    m.quadrature_points(check_level(m, level), xyz_host);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_support_points(mgb_solver s, int level, double *xyz_host)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    m.support_points(check_level(m, level), xyz_host);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_set_coefficient_values(mgb_solver s, int level, const double *c_host)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    m.set_coefficient_values(check_level(m, level), c_host);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_reinit_smoothers(mgb_solver s)
+  {
+    MGB_TRY
+    S(s).reinit_smoothers();
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_set_rhs_values(mgb_solver s, int level, const double *f_host, const double *u_boundary_host)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    m.set_rhs_values(check_level(m, level), f_host, u_boundary_host);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_set_exact_solution_values(mgb_solver s, int level, const double *u_host)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    m.set_exact_solution_values(check_level(m, level), u_host);
     MGB_CATCH
   }
 

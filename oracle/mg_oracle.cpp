@@ -397,6 +397,21 @@ namespace orc
             }
     }
 
+    // evaluate_coefficient(const Function &) with the function given by its samples c[cell][q] at the quadrature points
+    void
+    set_coefficient_values(const double *c)
+    {
+      evaluate_coefficient(coef_one, /*is_constant=*/false); // per-point tensors of the geometry alone
+      const size_t nq = (size_t)n * n * n;
+      variable        = true;
+      if (coef_q.empty()) // (affine geometry with the constant-tensor shortcut cannot happen: is_constant is false)
+        return;
+      for (size_t cell = 0; cell < ncells; ++cell)
+        for (size_t q = 0; q < nq; ++q)
+          for (int e = 0; e < 6; ++e)
+            coef_q[(cell * nq + q) * 6 + e] *= (T)c[cell * nq + q];
+    }
+
     // evaluate + quadrature-point operation + integrate on one cell
     // (laplace_operator.h:544-551 with :438-523 in between)
     template <int nn>
@@ -638,7 +653,7 @@ namespace orc
 
     // laplace_operator.h:806-845: dst = int f phi - K u_bc (rows of Dirichlet DoFs dropped)
     void
-    compute_residual(T *dst, const T *src, Fn rhs_function) const
+    compute_residual(T *dst, const T *src, Fn rhs_function, const double *rhs_values = nullptr) const
     {
       for (size_t i = 0; i < ndofs; ++i)
         dst[i] = 0;
@@ -667,13 +682,17 @@ namespace orc
                             {
                               double x[3], J[3][3], inv[3][3];
                               cell_geometry(X, q0, q1, q2, x, J);
-                              v[q] = rhs_function(x) * b->wq[q0] * b->wq[q1] * b->wq[q2] * std::fabs(invert3(J, inv));
+                              const size_t cell = ((size_t)cz * nc[1] + cy) * nc[0] + cx;
+                              const double f    = rhs_values ? rhs_values[cell * nq + q] : rhs_function(x);
+                              v[q] = f * b->wq[q0] * b->wq[q1] * b->wq[q2] * std::fabs(invert3(J, inv));
                               continue;
                             }
                           const double x[3] = {lo[0] + (cx + b->xq[q0]) * h[0],
                                                lo[1] + (cy + b->xq[q1]) * h[1],
                                                lo[2] + (cz + b->xq[q2]) * h[2]};
-                          v[q] = rhs_function(x) * b->wq[q0] * b->wq[q1] * b->wq[q2] * detJ;
+                          const size_t cell = ((size_t)cz * nc[1] + cy) * nc[0] + cx;
+                          const double f    = rhs_values ? rhs_values[cell * nq + q] : rhs_function(x);
+                          v[q] = f * b->wq[q0] * b->wq[q1] * b->wq[q2] * detJ;
                         }
                   // S^T in x, y, z (plain loops; set-up only)
                   for (int dir = 0; dir < 3; ++dir)
@@ -1168,6 +1187,7 @@ namespace orc
     vector<vector<double>>    solution, rhs, residual;
     vector<vector<float>>     defect, t, solution_update;
     vector<vector<std::pair<size_t, double>>> inhomogeneous_bc;
+    vector<vector<double>>    exact_values; // caller-supplied exact solution at the quadrature points, per level
     double                    timings_setup[3] = {0, 0, 0};
 
     MultigridSolver(const int     degree,
@@ -1302,6 +1322,107 @@ namespace orc
       return op.lo[d] + (cell + basis.gll[i - cell * p]) * op.h[d];
     }
 
+    // ---- problem data supplied by samples (the Function<dim> arguments of multigrid_solver.h:100-106)
+    void
+    quadrature_points(const int level, double *out) const
+    {
+      const LevelOp<double> &op = matrix_dp[level];
+      const int              n  = op.n;
+      for (int cz = 0; cz < op.nc[2]; ++cz)
+        for (int cy = 0; cy < op.nc[1]; ++cy)
+          for (int cx = 0; cx < op.nc[0]; ++cx)
+            {
+              const size_t   cell = ((size_t)cz * op.nc[1] + cy) * op.nc[0] + cx;
+              vector<double> X;
+              if (op.geom.kind != 0)
+                op.cell_nodes(cx, cy, cz, X);
+              for (int q2 = 0, q = 0; q2 < n; ++q2)
+                for (int q1 = 0; q1 < n; ++q1)
+                  for (int q0 = 0; q0 < n; ++q0, ++q)
+                    {
+                      double x[3] = {op.lo[0] + (cx + basis.xq[q0]) * op.h[0], op.lo[1] + (cy + basis.xq[q1]) * op.h[1],
+                                     op.lo[2] + (cz + basis.xq[q2]) * op.h[2]};
+                      if (op.geom.kind != 0)
+                        {
+                          double J[3][3];
+                          op.cell_geometry(X, q0, q1, q2, x, J);
+                        }
+                      for (int d = 0; d < 3; ++d)
+                        out[(cell * n * n * n + q) * 3 + d] = x[d];
+                    }
+            }
+    }
+
+    void
+    support_points(const int level, double *out) const
+    {
+      const LevelOp<double> &op = matrix_dp[level];
+      for (int k = 0; k < op.nd[2]; ++k)
+        for (int j = 0; j < op.nd[1]; ++j)
+          for (int i = 0; i < op.nd[0]; ++i)
+            {
+              double x[3] = {support_point(op, 0, i), support_point(op, 1, j), support_point(op, 2, k)};
+              if (op.geom.kind != 0)
+                {
+                  const double xi[3] = {unit_coordinate(op, 0, i), unit_coordinate(op, 1, j), unit_coordinate(op, 2, k)};
+                  op.geom.point(xi, x);
+                }
+              for (int d = 0; d < 3; ++d)
+                out[(((size_t)k * op.nd[1] + j) * op.nd[0] + i) * 3 + d] = x[d];
+            }
+    }
+
+    void
+    set_coefficient_values(const int level, const double *c)
+    {
+      matrix[level].set_coefficient_values(c);
+      matrix_dp[level].set_coefficient_values(c);
+    }
+
+    void
+    reinit_smoothers()
+    {
+      for (int l = 0; l < nlevels; ++l)
+        {
+          if (l == 0)
+            {
+              smooth[0].degree              = Chebyshev<float>::invalid_degree;
+              smooth[0].eig_cg_n_iterations = matrix[0].m();
+            }
+          matrix[l].compute_diagonal();
+          smooth[l].initialize(matrix[l]);
+        }
+    }
+
+    void
+    set_rhs_values(const int level, const double *f, const double *u_bc)
+    {
+      const LevelOp<double> &op = matrix_dp[level];
+      inhomogeneous_bc[level].clear();
+      std::fill(solution[level].begin(), solution[level].end(), 0.);
+      if (u_bc)
+        for (int k = 0; k < op.nd[2]; ++k)
+          for (int j = 0; j < op.nd[1]; ++j)
+            for (int i = 0; i < op.nd[0]; ++i)
+              if (op.on_boundary(i, j, k))
+                {
+                  const size_t idx = ((size_t)k * op.nd[1] + j) * op.nd[0] + i;
+                  if (u_bc[idx] != 0.0)
+                    inhomogeneous_bc[level].emplace_back(idx, u_bc[idx]);
+                }
+      for (auto &i : inhomogeneous_bc[level])
+        solution[level][i.first] = i.second;
+      op.compute_residual(rhs[level].data(), solution[level].data(), f_rhs, f);
+    }
+
+    void
+    set_exact_values(const int level, const double *u)
+    {
+      exact_values.resize(nlevels);
+      const size_t nq = matrix_dp[level].ncells * (size_t)matrix_dp[level].n * matrix_dp[level].n * matrix_dp[level].n;
+      exact_values[level].assign(u, u + nq);
+    }
+
     double
     unit_coordinate(const LevelOp<double> &op, const int d, const int i) const
     {
@@ -1364,7 +1485,9 @@ namespace orc
                           op.cell_geometry(X, q0, q1, q2, x, J);
                           JxW = basis.wq[q0] * basis.wq[q1] * basis.wq[q2] * std::fabs(invert3(J, inv));
                         }
-                      const double diff = u[q] - f_solution(x);
+                      const size_t cell = ((size_t)cz * op.nc[1] + cy) * op.nc[0] + cx;
+                      const bool   have = (int)exact_values.size() > level && !exact_values[level].empty();
+                      const double diff = u[q] - (have ? exact_values[level][cell * n * n * n + q] : f_solution(x));
                       err += diff * diff * JxW;
                       vol += JxW;
                     }
@@ -1533,6 +1656,37 @@ extern "C"
     if (degree < 1 || degree > 8)
       return nullptr;
     return new MultigridSolver(degree, nsub, n_refine, lower, upper, pre, post, cycles, problem);
+  }
+
+  void
+  orc_mg_quadrature_points(void *h, int level, double *out)
+  {
+    static_cast<MultigridSolver *>(h)->quadrature_points(level, out);
+  }
+  void
+  orc_mg_support_points(void *h, int level, double *out)
+  {
+    static_cast<MultigridSolver *>(h)->support_points(level, out);
+  }
+  void
+  orc_mg_set_coefficient_values(void *h, int level, const double *c)
+  {
+    static_cast<MultigridSolver *>(h)->set_coefficient_values(level, c);
+  }
+  void
+  orc_mg_reinit_smoothers(void *h)
+  {
+    static_cast<MultigridSolver *>(h)->reinit_smoothers();
+  }
+  void
+  orc_mg_set_rhs_values(void *h, int level, const double *f, const double *u_bc)
+  {
+    static_cast<MultigridSolver *>(h)->set_rhs_values(level, f, u_bc);
+  }
+  void
+  orc_mg_set_exact_values(void *h, int level, const double *u)
+  {
+    static_cast<MultigridSolver *>(h)->set_exact_values(level, u);
   }
 
   // the same on a mapped mesh: geometry 0 box, 1 shell sector (params r0, r1, half-angle), 2 affine (params A row-major)

@@ -45,6 +45,12 @@ def lib():
         L.orc_mg_create.argtypes = [C.c_int, ip, C.c_int, dp, dp, C.c_uint, C.c_uint, C.c_uint, C.c_int]
         L.orc_mg_create_mapped.restype = C.c_void_p
         L.orc_mg_create_mapped.argtypes = [C.c_int, ip, C.c_int, dp, dp, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, dp]
+        L.orc_mg_quadrature_points.argtypes = [C.c_void_p, C.c_int, dp]
+        L.orc_mg_support_points.argtypes = [C.c_void_p, C.c_int, dp]
+        L.orc_mg_set_coefficient_values.argtypes = [C.c_void_p, C.c_int, dp]
+        L.orc_mg_reinit_smoothers.argtypes = [C.c_void_p]
+        L.orc_mg_set_rhs_values.argtypes = [C.c_void_p, C.c_int, dp, dp]
+        L.orc_mg_set_exact_values.argtypes = [C.c_void_p, C.c_int, dp]
         L.orc_mg_destroy.argtypes = [C.c_void_p]
         L.orc_mg_n_levels.argtypes = [C.c_void_p]
         L.orc_mg_n_dofs.restype = C.c_longlong
@@ -208,6 +214,35 @@ class MultigridSolver:
 
     def _l(self, level):
         return level if level >= 0 else self.n_levels + level
+
+    # ---- problem data given by samples (the Function<dim> arguments of multigrid_solver.h:100-106)
+    def n_cells(self, level=-1):
+        nd = self.dof_grid(level)
+        return int(np.prod([(v - 1) // self.degree for v in nd]))
+
+    def quadrature_points(self, level=-1):
+        out = np.zeros((self.n_cells(level) * (self.degree + 1) ** 3, 3))
+        lib().orc_mg_quadrature_points(self.h, self._l(level), _dp(out))
+        return out
+
+    def support_points(self, level=-1):
+        out = np.zeros((self.n_dofs(level), 3))
+        lib().orc_mg_support_points(self.h, self._l(level), _dp(out))
+        return out
+
+    def set_problem(self, coefficient=None, right_hand_side=None, boundary_values=None, exact_solution=None):
+        ev = lambda f, x: np.ascontiguousarray(f(x[:, 0], x[:, 1], x[:, 2]), dtype=np.float64)
+        if coefficient is not None:
+            for l in range(self.n_levels):
+                lib().orc_mg_set_coefficient_values(self.h, l, _dp(ev(coefficient, self.quadrature_points(l))))
+            lib().orc_mg_reinit_smoothers(self.h)
+        for l in range(self.n_levels):
+            if right_hand_side is not None:
+                f = ev(right_hand_side, self.quadrature_points(l))
+                g = ev(boundary_values, self.support_points(l)) if boundary_values is not None else None
+                lib().orc_mg_set_rhs_values(self.h, l, _dp(f), _dp(g) if g is not None else None)
+            if exact_solution is not None:
+                lib().orc_mg_set_exact_values(self.h, l, _dp(ev(exact_solution, self.quadrature_points(l))))
 
     def solve(self, do_analyze=False):
         trace = np.zeros((self.n_levels, 4))

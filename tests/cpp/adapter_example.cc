@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 
+#include <cmath>
 #include "multigrid/laplace_operator_adaptive.h"
 #include "multigrid/laplace_operator_dg.h"
 #include "multigrid/multigrid_solver_dg.h"
@@ -130,6 +131,26 @@ main(int argc, char **argv)
         for (double v : r)
           e += v;
         std::printf("adaptive_cells %zu adaptive_m %zu adaptive_xAx %.12e\n", ad.n_active_cells(), ad.m(), e);
+        // the solve of poisson_l/program.cc:337-420 on this mesh: A x = A 1 by CG with the local-smoothing V-cycle
+        // (right-hand side zero on the Dirichlet rows, as an assembled one is: the solution is 1 inside, 0 on the boundary)
+        ad.setup_multigrid(3);
+        const std::vector<unsigned char> bnd = ad.dirichlet_mask();
+        std::vector<double>              rhs = r;
+        for (std::size_t i = 0; i < rhs.size(); ++i)
+          if (bnd[i])
+            rhs[i] = 0;
+        multigrid::DGVector<double> sol, b;
+        ad.initialize_dof_vector(sol);
+        ad.initialize_dof_vector(b);
+        b.import_from_host(rhs);
+        const std::pair<unsigned int, double> cg = ad.solve_cg(sol, b);
+        ad.synchronize();
+        const std::vector<double> xs = sol.export_to_host();
+        double                    err = 0;
+        for (std::size_t i = 0; i < xs.size(); ++i)
+          err = std::max(err, std::fabs(xs[i] - (bnd[i] ? 0.0 : 1.0)));
+        std::printf("adaptive_levels %u adaptive_cg_its %u adaptive_cg_rate %.6e adaptive_solution_error %.3e\n", ad.n_levels(),
+                    cg.first, cg.second, err);
       }
 
       // DG multigrid solver as poisson_dg/program.cc:227-263: [-1,1]^3, 2 refinements, tolerance 1e-3

@@ -83,6 +83,9 @@ def test_example_driver_matches_oracle(mgb, orc):
     assert int(out["adaptive_cells"]) == a.n_cells() and int(out["adaptive_m"]) == oa.n_dofs()
     e_ref = float(np.ones(oa.n_dofs()) @ oa.vmult(np.ones(oa.n_dofs())))
     assert abs(float(out["adaptive_xAx"]) - e_ref) <= 1e-10 * abs(e_ref)
+    # the local-smoothing solve through the adapter: A x = A 1 (identity rows on the boundary), so x = 1
+    assert int(out["adaptive_levels"]) == 3 and 0 < int(out["adaptive_cg_its"]) <= 14
+    assert float(out["adaptive_cg_rate"]) < 0.25 and float(out["adaptive_solution_error"]) <= 1e-7
     ds = orc.MultigridSolverDG(4, (1, 1, 1), 2, basis=orc.DG_BASIS_HERMITE)   # the adapter's default, as the reference
     _, rate_dg, _ = ds.solve_cg(1e-3)
     assert int(out["dg_cg_its"]) == ds.last_step

@@ -304,6 +304,50 @@ def test_solver_against_oracle(mgb, orc, torch, mesh, kernel):
     assert rel(sol, P.o.get_vector(orc.VEC_SOLUTION)) <= 1e-6
 
 
+@pytest.mark.parametrize("case", [(3, 1, 2, 0, None), (4, (1, 2, 1), 2, 1, (0.5, 1.0, 0.6)), (2, 1, 3, 2, SHEAR)])
+def test_caller_supplied_problem(mgb, orc, torch, case):
+    """a problem that exists only in this test, handed over as samples at the library's quadrature / support points
+    (the Function<dim> arguments of MultigridSolver, multigrid_solver.h:100-106; evaluate_coefficient(const Function &) and
+    compute_residual(dst, src, rhs_function), laplace_operator.h:103-109): u = e^x sin 2y cos z, c = 1 + x^2 + sin(3y)/2"""
+    p, nsub, nref, geometry, params = case
+    u = lambda x, y, z: np.exp(x) * np.sin(2 * y) * np.cos(z)
+    c = lambda x, y, z: 1 + x * x + 0.5 * np.sin(3 * y)
+
+    def f(x, y, z):
+        ux, uy = u(x, y, z), 2 * np.exp(x) * np.cos(2 * y) * np.cos(z)
+        return -(c(x, y, z) * (ux - 5 * u(x, y, z)) + 2 * x * ux + 1.5 * np.cos(3 * y) * uy)
+
+    P = Pair(mgb, orc, torch, p, nsub, nref, lower=(0., 0., 0.), upper=(1., 1.2, 0.8), geometry=geometry,
+             geometry_params=params)
+    L = P.g.n_levels - 1
+    # the points the caller evaluates its functions at
+    assert rel(P.g.quadrature_points(L), P.o.quadrature_points(L)) <= 1e-14
+    assert rel(P.g.support_points(L)[P.lex(L)], P.o.support_points(L)) <= 1e-14
+    P.g.set_problem(c, f, u, u)
+    P.o.set_problem(c, f, u, u)
+    x = np.random.default_rng(3).random(P.g.n_dofs())
+    dst = P.g.matrix_dp().initialize_dof_vector()
+    P.g.matrix_dp().vmult(dst, P.to_dev(x, L))
+    assert rel(P.to_lex(dst, L), P.o.vmult(x, L, True)) <= 1e-12
+    scale = np.abs(P.o.get_vector(orc.VEC_RHS, L)).max()
+    for level in range(P.g.n_levels):
+        rhs = P.g.get_vector("rhs", level)[P.lex(level)]
+        ref = P.o.get_vector(orc.VEC_RHS, level)
+        assert np.abs(rhs - ref).max() <= 1e-11 * max(np.abs(ref).max(), scale), ("rhs", level)
+        gi, oi = P.g.smoother_info(level), P.o.chebyshev_info(level)
+        assert abs(gi["max_eig"] - oi["max_eig"]) < 5e-4 * oi["max_eig"] and gi["degree"] == oi["degree"], (level, gi, oi)
+    its, rate = P.g.solve_cg()
+    its_o, rate_o, hist_o = P.o.solve_cg()
+    assert its == its_o, (its, its_o)
+    assert np.allclose(P.g.cg_history(), hist_o, rtol=0.05)
+    e, e_o = P.g.compute_l2_error(), P.o.compute_l2_error()
+    assert abs(e - e_o) <= 1e-3 * e_o and e < 1e-2, (e, e_o)
+    assert rel(P.g.get_solution()[P.lex(L)], P.o.get_vector(orc.VEC_SOLUTION)) <= 1e-6
+    red, trace = P.g.solve(True)
+    red_o, trace_o = P.o.solve(True)
+    assert np.allclose(trace[1:], trace_o[1:], rtol=3e-2), (trace, trace_o)
+
+
 @pytest.mark.parametrize("mesh", [(4, 1, 2), (2, (1, 2, 1), 2)])
 def test_vmult_with_residual_update(mgb, orc, torch, mesh):
     """MultigridSolver::vmult_with_residual_update (multigrid_solver.h:516-619) against its definition composed from the

@@ -44,6 +44,24 @@ def run(degree=3, n_global=4, rounds=3, reps=20):
             best = min(best, (time.perf_counter() - t0) / reps * 1e3)
         bytes_per_dof = 2 * nb + 4.0 * n3 * op.n_cells() / n
         out[name] = dict(ms=best, dofs_per_s=n / best * 1e3, bytes_per_dof=bytes_per_dof, gbs=n * bytes_per_dof / best / 1e6)
+    # the solve of poisson_l (program.cc:337-420): local-smoothing V-cycle (float) inside CG (double), right-hand side 1
+    t0 = time.perf_counter()
+    op.setup_multigrid(3)
+    op.sync()
+    mg_setup = time.perf_counter() - t0
+    free = torch.tensor(~op.dirichlet_mask(), device="cuda")
+    b = torch.where(free, torch.ones(n, dtype=torch.float64, device="cuda"), torch.zeros(n, dtype=torch.float64, device="cuda"))
+    x = torch.zeros_like(b)
+    op.solve_cg(x, b)
+    best = 1e30
+    for _ in range(3):
+        t0 = time.perf_counter()
+        its, rate, hist = op.solve_cg(x, b)
+        best = min(best, time.perf_counter() - t0)
+    out["solve_cg"] = dict(ms=best * 1e3, iterations=its, reduction_per_iteration=rate, dofs_per_s=n / best,
+                           n_levels=op.n_levels, multigrid_setup_s=mg_setup,
+                           level_dofs=[int(op.mg_level_info(l)["n_dofs"]) for l in range(op.n_levels)],
+                           level_edge_dofs=[int(op.mg_level_info(l)["n_edge_dofs"]) for l in range(op.n_levels)])
     op.close()
     return out
 
