@@ -512,6 +512,15 @@ def varcoef_lines(r):
     for k in ("fp64", "fp32"):
         out[k]["frac_hbm"] = out[k]["gbs"] / r["hbm_gbs"]
     out["workload"] = "FE_Q(4) variable-coefficient matvec, 64^3 cells, per-q-point merged coefficient streamed once"
+    # the same operator and the solves on the curved mesh: one coarse cell of hyper_shell(0, 0.5, 1, 6) refined 6 times
+    # (262144 cells, 17 M DoF), six-entry coefficient from the Jacobian of the MappingQ(4) cell geometry
+    import time_shell
+    sh = time_shell.run(6, DEGREE, reps=10)
+    for k in ("fp64", "fp32"):
+        sh[k]["frac_hbm"] = sh[k]["gbs"] / r["hbm_gbs"]
+    sh["workload"] = ("poisson_shell functions on one hyper_shell(0, 0.5, 1, 6) coarse cell, 6 refinements: curved cells, "
+                      "coefficient contrast 1e6; operator, solve_cg to 1e-9, FMG solve")
+    out["shell_sector"] = sh
     return out
 
 

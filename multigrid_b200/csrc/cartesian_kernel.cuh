@@ -558,10 +558,6 @@ namespace mgb
     return on;
   }
 
-  // cartesian_kernel_v5.cuh: second generation of the float kernel; false = not served, use the kernels of this file
-  template <int p, int MODE>
-  bool launch_apply_tile_v5(const ApplyArgs<float> &A, cudaStream_t stream);
-
   // MGB200_SHORT_SEGMENTS=0 keeps segments of >= 4 cell layers on every level (A/B measurements)
   inline bool
   use_short_segments()
@@ -578,9 +574,6 @@ namespace mgb
   launch_apply_tile(const ApplyArgs<T> &A, cudaStream_t stream)
   {
     using C           = TileCfg<p>;
-    if constexpr (std::is_same<T, float>::value)
-      if (launch_apply_tile_v5<p, MODE>(A, stream))
-        return;
     // the zero-guess Chebyshev instance stages the planes of b and P^-1: one more double-buffered plane array
     const size_t smem  = (size_t)C::SMEM * sizeof(T),
                  smem2 = (size_t)(C::SMEM2 + (MODE == APPLY_CHEBYSHEV_ZERO ? 2 * C::U_SIZE : 0)) * sizeof(float);
@@ -667,4 +660,3 @@ namespace mgb
 } // namespace mgb
 
 #include "cartesian_kernel_f32x2.cuh"
-#include "cartesian_kernel_v5.cuh"

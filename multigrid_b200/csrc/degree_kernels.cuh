@@ -75,6 +75,13 @@ namespace mgb
   }
 
   // ------------------------------------------------------------------ general cell kernel
+  // FEEvaluation-style cell loop (laplace_operator.h:529-558): gather, evaluate the reference gradient at the Gauss
+  // points by sum factorisation (S in x, y, z, collocation derivative D per direction), quadrature-point operation with the
+  // merged coefficient (:438-523), integrate (the transposes), scatter-add.  (p+1)^2 threads per cell; thread (a, b) owns
+  // the z-pencil (i, j) = (b, a) at both ends: the gathered values go into the first sweep from registers and the last
+  // sweep leaves the result in registers for the scatter, so one DoF index is computed per thread (the p+1 points of a
+  // pencil are one plane pitch apart) and the per-point coefficients are read in their storage order (x fastest across the
+  // threads: coalesced).  Three shared-memory arrays per cell: values / residual U, and the x- and y-components G0, G1.
   template <int p, typename T, bool VAR>
   __global__ void
   __launch_bounds__(cells_per_block(p) * (p + 1) * (p + 1))
@@ -94,97 +101,132 @@ namespace mgb
     const int      b      = t - a * n;
     const uint32_t cell   = blockIdx.x * CPB + cl;
     const bool     active = cell < A.L.n_cells;
-    T             *u      = smem + cl * 4 * NN;
-    T             *g0     = u + NN;
-    T             *g1     = g0 + NN;
-    T             *g2     = g1 + NN;
-    (void)g0;
+    T             *U      = smem + cl * NN; // [array][cell]: the cells of a block side by side (fewer bank conflicts
+    T             *G0     = U + CPB * NN;   // where a warp straddles two cells)
+    T             *G1     = G0 + CPB * NN;
 #define IDX(i, j, k) (((k)*n + (j)) * npad + (i))
-
-    // gather (vector_access_reduced.h:11-251): constrained entities read as zero
-    if (active)
-      for (int l = t; l < n * n * n; l += tpc)
-        {
-          const int i = l % n, j = (l / n) % n, k = l / (n * n);
-          bool      c;
-          const uint32_t d = cell_dof(A.L, cell, i, j, k, c);
-          u[IDX(i, j, k)]  = (c && !A.read_plain) ? T(0) : A.src[d];
-        }
-    __syncthreads();
 
     const T *Sm = Tab<T>::S();
     const T *Dm = Tab<T>::D();
     T        r[n], s[n];
 
-    // evaluate: basis change to the Gauss points in x, y, z
+    // gather (vector_access_reduced.h:11-251): the z-pencil at (i, j) = (b, a); constrained entries read as zero
+    const LevelDesc &L = A.L;
+    int              cx = 0, cy = 0, cz = 0;
+    if (active)
+      cell_coords(L, cell, cx, cy, cz);
+    const int      gi = cx * p + b, gj = cy * p + a;
+    const uint32_t pitch = plane_pitch(L);
+    const uint32_t base  = active ? dof_index(L, gi, gj, cz * p) : 0u;
+    const bool     xycon = is_constrained_xy(L, gi, gj);
+    const bool     zlo = cz == 0 && (L.dirichlet & 16u), zhi = cz == L.ncell[2] - 1 && (L.dirichlet & 32u);
 #pragma unroll
-    for (int i = 0; i < n; ++i)
-      r[i] = u[IDX(i, b, a)];
+    for (int m = 0; m < n; ++m)
+      {
+        const bool c = xycon || (m == 0 && zlo) || (m == n - 1 && zhi);
+        r[m]         = (active && !(c && !A.read_plain)) ? A.src[base + (uint32_t)m * pitch] : T(0);
+      }
+    // the merged coefficients of this thread's quadrature points (b, a, k): requested now, used after the evaluation
+    // sweeps (the stream that dominates the HBM traffic: its latency is covered by the sweeps instead of stalling the
+    // quadrature-point loop)
+    // float: into registers; double (registers are short: 60 more would halve the occupancy): asynchronous copies of the
+    // block's contiguous coefficient range into shared memory
+    constexpr bool PF_REG = VAR && sizeof(T) == 4, PF_SMEM = VAR && sizeof(T) == 8;
+    T              cf[PF_REG ? 6 : 1][PF_REG ? n : 1];
+    T             *cs = smem + ((3 * CPB * NN + 1) & ~1); // behind the three arrays (16-byte aligned): [cell][6][n^3]
+    if (PF_REG)
+      {
+        const T *cq = A.coef_q + (size_t)(active ? cell : 0) * 6 * (n * n * n) + a * n + b;
+#pragma unroll
+        for (int e = 0; e < 6; ++e)
+#pragma unroll
+          for (int k = 0; k < n; ++k)
+            cf[PF_REG ? e : 0][PF_REG ? k : 0] = active ? cq[e * n * n * n + k * n * n] : T(0);
+      }
+    if (PF_SMEM)
+      {
+        // 16-byte chunks; a cell's block of 6 n^3 doubles is a multiple of 16 bytes and 16-byte aligned
+        const uint32_t first = blockIdx.x * CPB;
+        const uint32_t ncell = A.L.n_cells - first < (uint32_t)CPB ? A.L.n_cells - first : (uint32_t)CPB;
+        const uint32_t nchunk = ncell * (6 * n * n * n / 2);
+        const T       *g      = A.coef_q + (size_t)first * 6 * (n * n * n);
+        const uint32_t sb     = (uint32_t)__cvta_generic_to_shared(cs);
+        for (uint32_t q = threadIdx.x; q < nchunk; q += blockDim.x)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sb + q * 16u), "l"(g + 2 * q));
+        asm volatile("cp.async.commit_group;\n" ::);
+      }
+    // evaluate: S in z from the registers, then y, then x together with the x-derivative
     mat_vec<n, T, false, false>(Sm, r, s);
-#pragma unroll
-    for (int i = 0; i < n; ++i)
-      u[IDX(i, b, a)] = s[i];
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < n; ++j)
-      r[j] = u[IDX(b, j, a)];
-    mat_vec<n, T, false, false>(Sm, r, s);
-#pragma unroll
-    for (int j = 0; j < n; ++j)
-      u[IDX(b, j, a)] = s[j];
-    __syncthreads();
-    // z: values at quadrature points, and collocation derivative in z
 #pragma unroll
     for (int k = 0; k < n; ++k)
-      r[k] = u[IDX(b, a, k)];
+      U[IDX(b, a, k)] = s[k];
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      r[j] = U[IDX(b, j, a)];
+    mat_vec<n, T, false, false>(Sm, r, s);
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      U[IDX(b, j, a)] = s[j];
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < n; ++i)
+      r[i] = U[IDX(i, b, a)];
     mat_vec<n, T, false, false>(Sm, r, s);
     mat_vec<n, T, false, false>(Dm, s, r);
 #pragma unroll
-    for (int k = 0; k < n; ++k)
+    for (int i = 0; i < n; ++i)
       {
-        u[IDX(b, a, k)]  = s[k];
-        g2[IDX(b, a, k)] = r[k];
+        U[IDX(i, b, a)]  = s[i];
+        G0[IDX(i, b, a)] = r[i];
       }
     __syncthreads();
-    // y derivative
+    // y-derivative
 #pragma unroll
     for (int j = 0; j < n; ++j)
-      r[j] = u[IDX(b, j, a)];
+      r[j] = U[IDX(b, j, a)];
     mat_vec<n, T, false, false>(Dm, r, s);
 #pragma unroll
     for (int j = 0; j < n; ++j)
-      g1[IDX(b, j, a)] = s[j];
+      G1[IDX(b, j, a)] = s[j];
+    if (PF_SMEM)
+      asm volatile("cp.async.wait_group 0;\n" ::: "memory"); // own copies landed; the barrier below publishes all of them
     __syncthreads();
-    // x derivative, quadrature-point operation (laplace_operator.h:438-523), D_x^T
+    // z-derivative and the quadrature-point operation (laplace_operator.h:438-523) on the points (b, a, k); D_z^T of the
+    // z-component stays with this thread and opens the residual in U
 #pragma unroll
-    for (int i = 0; i < n; ++i)
-      r[i] = u[IDX(i, b, a)];
+    for (int k = 0; k < n; ++k)
+      r[k] = U[IDX(b, a, k)];
     mat_vec<n, T, false, false>(Dm, r, s);
     {
       const T *wq  = Tab<T>::w();
       const T  wab = wq[a] * wq[b];
-      const T *cq  = VAR ? A.coef_q + (size_t)cell * 6 * (n * n * n) + (a * n + b) * n : nullptr;
 #pragma unroll
-      for (int i = 0; i < n; ++i)
+      for (int k = 0; k < n; ++k)
         {
           T c0, c1, c2, c3, c4, c5;
-          if (VAR)
+          if (PF_REG)
             {
-              if (active)
-                {
-                  c0 = cq[0 * n * n * n + i];
-                  c1 = cq[1 * n * n * n + i];
-                  c2 = cq[2 * n * n * n + i];
-                  c3 = cq[3 * n * n * n + i];
-                  c4 = cq[4 * n * n * n + i];
-                  c5 = cq[5 * n * n * n + i];
-                }
-              else
-                c0 = c1 = c2 = c3 = c4 = c5 = T(0);
+              c0 = cf[0][PF_REG ? k : 0];
+              c1 = cf[PF_REG ? 1 : 0][PF_REG ? k : 0];
+              c2 = cf[PF_REG ? 2 : 0][PF_REG ? k : 0];
+              c3 = cf[PF_REG ? 3 : 0][PF_REG ? k : 0];
+              c4 = cf[PF_REG ? 4 : 0][PF_REG ? k : 0];
+              c5 = cf[PF_REG ? 5 : 0][PF_REG ? k : 0];
+            }
+          else if (PF_SMEM)
+            {
+              const T *c = cs + cl * 6 * (n * n * n) + k * n * n + t;
+              c0         = active ? c[0 * n * n * n] : T(0);
+              c1         = active ? c[1 * n * n * n] : T(0);
+              c2         = active ? c[2 * n * n * n] : T(0);
+              c3         = active ? c[3 * n * n * n] : T(0);
+              c4         = active ? c[4 * n * n * n] : T(0);
+              c5         = active ? c[5 * n * n * n] : T(0);
             }
           else
             {
-              const T weight = wq[i] * wab;
+              const T weight = wq[k] * wab;
               c0             = A.coef[0] * weight;
               c1             = A.coef[1] * weight;
               c2             = A.coef[2] * weight;
@@ -192,71 +234,65 @@ namespace mgb
               c4             = A.coef[4] * weight;
               c5             = A.coef[5] * weight;
             }
-          const T t0 = s[i], t1 = g1[IDX(i, b, a)], t2 = g2[IDX(i, b, a)];
-          r[i]              = c0 * t0 + c3 * t1 + c4 * t2;
-          g1[IDX(i, b, a)]  = c3 * t0 + c1 * t1 + c5 * t2;
-          g2[IDX(i, b, a)]  = c4 * t0 + c5 * t1 + c2 * t2;
+          const T t0 = G0[IDX(b, a, k)], t1 = G1[IDX(b, a, k)], t2 = s[k];
+          G0[IDX(b, a, k)] = c0 * t0 + c3 * t1 + c4 * t2;
+          G1[IDX(b, a, k)] = c3 * t0 + c1 * t1 + c5 * t2;
+          r[k]             = c4 * t0 + c5 * t1 + c2 * t2;
         }
     }
     mat_vec<n, T, true, false>(Dm, r, s);
 #pragma unroll
-    for (int i = 0; i < n; ++i)
-      u[IDX(i, b, a)] = s[i];
-    __syncthreads();
-    // integrate: += D_y^T
-#pragma unroll
-    for (int j = 0; j < n; ++j)
-      {
-        r[j] = g1[IDX(b, j, a)];
-        s[j] = u[IDX(b, j, a)];
-      }
-    mat_vec<n, T, true, true>(Dm, r, s);
-#pragma unroll
-    for (int j = 0; j < n; ++j)
-      u[IDX(b, j, a)] = s[j];
-    __syncthreads();
-    // += D_z^T, then S_z^T
-#pragma unroll
     for (int k = 0; k < n; ++k)
+      U[IDX(b, a, k)] = s[k];
+    __syncthreads();
+    // integrate.  x-pencils: S_x^T (U + D_x^T G0) -> U, and S_x^T G1 in place (it commutes with the D_y^T to come)
+#pragma unroll
+    for (int i = 0; i < n; ++i)
       {
-        r[k] = g2[IDX(b, a, k)];
-        s[k] = u[IDX(b, a, k)];
+        r[i] = G0[IDX(i, b, a)];
+        s[i] = U[IDX(i, b, a)];
       }
     mat_vec<n, T, true, true>(Dm, r, s);
     mat_vec<n, T, true, false>(Sm, s, r);
 #pragma unroll
+    for (int i = 0; i < n; ++i)
+      {
+        U[IDX(i, b, a)] = r[i];
+        s[i]            = G1[IDX(i, b, a)];
+      }
+    mat_vec<n, T, true, false>(Sm, s, r);
+#pragma unroll
+    for (int i = 0; i < n; ++i)
+      G1[IDX(i, b, a)] = r[i];
+    __syncthreads();
+    // y-pencils: S_y^T (U + D_y^T G1) -> U
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      {
+        r[j] = G1[IDX(b, j, a)];
+        s[j] = U[IDX(b, j, a)];
+      }
+    mat_vec<n, T, true, true>(Dm, r, s);
+    mat_vec<n, T, true, false>(Sm, s, r);
+#pragma unroll
+    for (int j = 0; j < n; ++j)
+      U[IDX(b, j, a)] = r[j];
+    __syncthreads();
+    // z-pencils: S_z^T into registers, scatter-add (vector_access_reduced.h:255-505): constrained entries skipped
+#pragma unroll
     for (int k = 0; k < n; ++k)
-      u[IDX(b, a, k)] = r[k];
-    __syncthreads();
-    // S_y^T
-#pragma unroll
-    for (int j = 0; j < n; ++j)
-      r[j] = u[IDX(b, j, a)];
+      r[k] = U[IDX(b, a, k)];
     mat_vec<n, T, true, false>(Sm, r, s);
-#pragma unroll
-    for (int j = 0; j < n; ++j)
-      u[IDX(b, j, a)] = s[j];
-    __syncthreads();
-    // S_x^T
-#pragma unroll
-    for (int i = 0; i < n; ++i)
-      r[i] = u[IDX(i, b, a)];
-    mat_vec<n, T, true, false>(Sm, r, s);
-#pragma unroll
-    for (int i = 0; i < n; ++i)
-      u[IDX(i, b, a)] = s[i];
-    __syncthreads();
-
-    // scatter-add (vector_access_reduced.h:255-505): constrained entities skipped
     if (active)
-      for (int l = t; l < n * n * n; l += tpc)
-        {
-          const int i = l % n, j = (l / n) % n, k = l / (n * n);
-          bool      c;
-          const uint32_t d = cell_dof(A.L, cell, i, j, k, c);
-          if (!c)
-            atomicAdd(&acc[d], u[IDX(i, j, k)]);
-        }
+      {
+#pragma unroll
+        for (int m = 0; m < n; ++m)
+          {
+            const bool c = xycon || (m == 0 && zlo) || (m == n - 1 && zhi);
+            if (!c)
+              atomicAdd(&acc[base + (uint32_t)m * pitch], s[m]);
+          }
+      }
 #undef IDX
   }
 
@@ -267,8 +303,15 @@ namespace mgb
     constexpr int n    = p + 1;
     constexpr int NN   = n * n * (n | 1);
     constexpr int CPB  = cells_per_block(p);
-    const size_t  smem = (size_t)CPB * 4 * NN * sizeof(T);
+    // three work arrays per cell; the double instance with per-point coefficients also stages them (6 n^3 per cell)
+    const size_t  smem = (size_t)(((3 * CPB * NN + 1) & ~1) + (A.coef_q && sizeof(T) == 8 ? CPB * 6 * n * n * n : 0)) * sizeof(T);
     const unsigned grid = (A.L.n_cells + CPB - 1) / CPB;
+    static bool    attr = false;
+    if (!attr && A.coef_q)
+      {
+        cudaFuncSetAttribute(k_apply_general<p, T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr = true;
+      }
     if (A.coef_q)
       k_apply_general<p, T, true><<<grid, CPB * n * n, smem, stream>>>(A, A.dst);
     else
