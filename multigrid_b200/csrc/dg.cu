@@ -178,6 +178,15 @@ namespace mgb
         t.f1[i] = (T)b.f1[i];
         t.w[i]  = (T)b.wq[i];
       }
+    // traces of the collocation basis (Lagrange polynomials in the Gauss points): what FE_DGQArbitraryNodes(QGauss) has
+    const DGBasis g = b.kind == DG_BASIS_GAUSS ? b : make_dg_basis(b.p, DG_BASIS_GAUSS);
+    for (int i = 0; i < n; ++i)
+      {
+        t.qf0[i] = (T)g.f0[i];
+        t.qf1[i] = (T)g.f1[i];
+        t.qe0[i] = (T)g.e0[i];
+        t.qe1[i] = (T)g.e1[i];
+      }
     const std::vector<double> V = jacobi_transformed_eigenvectors(b);
     for (int i = 0; i < n * n; ++i)
       t.V[i] = (T)V[i];

