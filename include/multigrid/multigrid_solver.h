@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <array>
 #include <utility>
+#include <vector>
 
 #include "laplace_operator.h"
 
@@ -20,6 +21,10 @@ namespace multigrid
     int    n_refinements     = 0;         // Triangulation::refine_global
     double lower[3] = {-0.9, -0.9, -0.9}, upper[3] = {1., 1., 1.};
     int    problem = MGB_PROBLEM_CUBE_SINE;
+    // geometry of the structured mesh: MGB_GEOMETRY_BOX, _SHELL_SECTOR (params r0, r1, opening half-angle: one coarse
+    // cell of GridGenerator::hyper_shell(.., 6), poisson_shell/program.cc:426) or _AFFINE (params: 3 x 3 matrix)
+    int    geometry = MGB_GEOMETRY_BOX;
+    double geometry_params[12] = {0.5, 1.0, 0.78539816339744830962, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     // one process per GPU (MPI_COMM_WORLD of the reference): rank, size and the id of mgb_comm_unique_id()
     int           comm_rank = 0, comm_size = 1;
     unsigned char comm_id[128] = {};
@@ -54,6 +59,9 @@ namespace multigrid
       o.degree_post   = (int)degree_post;
       o.n_cycles      = (int)n_cycles;
       o.problem       = mesh.problem;
+      o.geometry      = mesh.geometry;
+      for (int i = 0; i < 12; ++i)
+        o.geometry_params[i] = mesh.geometry_params[i];
       o.device        = mesh.device;
       o.comm_rank     = mesh.comm_rank;
       o.comm_size     = mesh.comm_size;
@@ -71,6 +79,57 @@ namespace multigrid
 
     mgb_solver   handle() const { return s_; }
     unsigned int n_levels() const { return (unsigned int)mgb_solver_n_levels(s_); }
+
+    // ---- the Function<dim> arguments of the reference's constructor (boundary_values, right_hand_side, coefficient,
+    // multigrid_solver.h:100-106) as callables double(double x, double y, double z): evaluated here at the library's
+    // quadrature points (coefficient, right-hand side, exact solution for compute_l2_error) and support points (boundary
+    // values) of every level and handed over as samples.  Any of them may be null (keep what the problem id set).
+    template <typename Coefficient, typename RightHandSide, typename BoundaryValues>
+    void
+    set_problem(const Coefficient *coefficient, const RightHandSide *right_hand_side, const BoundaryValues *boundary_values,
+                const bool boundary_values_are_exact_solution = true)
+    {
+      const int           nl = (int)n_levels();
+      std::vector<double> pts, val, bc;
+      for (int l = 0; l < nl && coefficient; ++l)
+        {
+          sample(l, true, *coefficient, pts, val);
+          check(mgb_solver_set_coefficient_values(s_, l, val.data()));
+        }
+      if (coefficient)
+        check(mgb_solver_reinit_smoothers(s_));
+      for (int l = 0; l < nl; ++l)
+        {
+          if (right_hand_side)
+            {
+              sample(l, true, *right_hand_side, pts, val);
+              if (boundary_values)
+                sample(l, false, *boundary_values, pts, bc);
+              check(mgb_solver_set_rhs_values(s_, l, val.data(), boundary_values ? bc.data() : nullptr));
+            }
+          if (boundary_values && boundary_values_are_exact_solution)
+            {
+              sample(l, true, *boundary_values, pts, val);
+              check(mgb_solver_set_exact_solution_values(s_, l, val.data()));
+            }
+        }
+    }
+    // FEEvaluation::quadrature_point of all cells of a level, [cell][q][3] (cells lexicographic, x fastest)
+    std::vector<double>
+    quadrature_points(const int level) const
+    {
+      std::vector<double> xyz(3 * (std::size_t)mgb_solver_n_quadrature_points(s_, level));
+      check(mgb_solver_quadrature_points(s_, level, xyz.data()));
+      return xyz;
+    }
+    // support points of the DoFs of a level in the library's numbering, [dof][3]
+    std::vector<double>
+    support_points(const int level) const
+    {
+      std::vector<double> xyz(3 * (std::size_t)mgb_solver_n_dofs(s_, level));
+      check(mgb_solver_support_points(s_, level, xyz.data()));
+      return xyz;
+    }
 
     // level operators: matrix[level] (float) and matrix_dp[level] (double), multigrid_solver.h:740-745
     LaplaceOperator<dim, fe_degree, Number>
@@ -149,6 +208,16 @@ namespace multigrid
     void synchronize() const { check(mgb_solver_sync(s_)); }
 
   private:
+    template <typename F>
+    void
+    sample(const int level, const bool at_quadrature_points, const F &f, std::vector<double> &pts, std::vector<double> &val) const
+    {
+      pts = at_quadrature_points ? quadrature_points(level) : support_points(level);
+      val.resize(pts.size() / 3);
+      for (std::size_t i = 0; i < val.size(); ++i)
+        val[i] = f(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]);
+    }
+
     mgb_solver s_ = nullptr;
   };
 } // namespace multigrid

@@ -11,6 +11,25 @@
 #include "multigrid/multigrid_solver_dg.h"
 #include "multigrid/multigrid_solver.h"
 
+// A third problem, defined only here (the Function<dim> objects a driver of the reference would write):
+// -div(c grad u) = f with u = exp(x) sin(2y) cos(z), c = 1 + x^2 + sin(3y) / 2, on the curved shell sector.
+static double
+third_solution(const double x, const double y, const double z)
+{
+  return std::exp(x) * std::sin(2 * y) * std::cos(z);
+}
+static double
+third_coefficient(const double x, const double y, const double)
+{
+  return 1 + x * x + 0.5 * std::sin(3 * y);
+}
+static double
+third_rhs(const double x, const double y, const double z)
+{
+  const double u = third_solution(x, y, z), ux = u, uy = 2 * std::exp(x) * std::cos(2 * y) * std::cos(z);
+  return -(third_coefficient(x, y, z) * (ux - 5 * u) + 2 * x * ux + 1.5 * std::cos(3 * y) * uy);
+}
+
 int
 main(int argc, char **argv)
 {
@@ -37,6 +56,20 @@ main(int argc, char **argv)
       const double pq = p * q;
       A.vmult_residual(q, p, r); // r = q - A p = 0
       std::printf("operator m %zu pAp %.12e residual_norm %.3e\n", A.m(), pq, (double)r.l2_norm());
+
+      // the third problem on one coarse cell of hyper_shell(0, 0.5, 1, 6) with 2 refinements (curved cells, six-entry
+      // coefficient), handed over as samples at the library's quadrature / support points
+      {
+        multigrid::MeshDescription shell;
+        shell.n_refinements = 2;
+        shell.geometry      = MGB_GEOMETRY_SHELL_SECTOR;
+        multigrid::MultigridSolver<3, degree, float, double> third(shell, 3, 3, 2);
+        double (*c)(double, double, double) = third_coefficient, (*f)(double, double, double) = third_rhs,
+                                   (*g)(double, double, double) = third_solution;
+        third.set_problem(&c, &f, &g);
+        const std::pair<unsigned int, double> cg3 = third.solve_cg();
+        std::printf("third_cg_its %u third_cg_rate %.6e third_l2 %.6e\n", cg3.first, cg3.second, third.compute_l2_error());
+      }
 
       // DG operator on the mesh of matvec_dg/program.cc, 2 refinements
       mgb_dg_options o;

@@ -60,6 +60,21 @@ def test_example_driver_matches_oracle(mgb, orc):
     ones = np.ones(o.n_dofs())
     assert abs(float(out["pAp"]) - ones @ o.vmult(ones)) <= 1e-10 * abs(ones @ o.vmult(ones))
     assert float(out["residual_norm"]) <= 1e-10
+    # the third problem of the example (defined only in tests/cpp/adapter_example.cc) against the oracle with the same
+    # functions handed over as samples
+    u3 = lambda x, y, z: np.exp(x) * np.sin(2 * y) * np.cos(z)
+    c3 = lambda x, y, z: 1 + x * x + 0.5 * np.sin(3 * y)
+
+    def f3(x, y, z):
+        ux, uy = u3(x, y, z), 2 * np.exp(x) * np.cos(2 * y) * np.cos(z)
+        return -(c3(x, y, z) * (ux - 5 * u3(x, y, z)) + 2 * x * ux + 1.5 * np.cos(3 * y) * uy)
+
+    o3 = orc.MultigridSolver(4, 1, 2, degree_pre=3, degree_post=3, geometry=1)
+    o3.set_problem(c3, f3, u3, u3)
+    its3, rate3, _ = o3.solve_cg()
+    assert int(out["third_cg_its"]) == its3
+    assert abs(float(out["third_cg_rate"]) - rate3) <= 0.05 * rate3
+    assert abs(float(out["third_l2"]) - o3.compute_l2_error()) <= 1e-3 * o3.compute_l2_error()
     d = orc.DGOperator(4, (4, 4, 4))
     x = np.ones(d.n_dofs())
     assert abs(float(out["xAx"]) - x @ d.vmult(x)) <= 1e-10 * abs(x @ d.vmult(x))
