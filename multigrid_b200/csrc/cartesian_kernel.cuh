@@ -149,6 +149,9 @@ namespace mgb
   // it loads anyway.  Same float operations as the stored variant, (f0 * P^-1) * b, so the results are bit-identical.
   constexpr int APPLY_CHEBYSHEV_ZERO    = 6;
   constexpr int APPLY_CHEBYSHEV_DERIVED = 7;
+  // q = A p with the four sums of vmult_with_cg_update taken while the result is stored (laplace_operator.h:698-701):
+  // q.p, r.r, q.r, q.q (r passed as `rhs`); Dirichlet rows of q stay zero as in the reference's merged loop
+  constexpr int APPLY_SET_DOT4 = 8;
 
   // Operands of the fused vector operation (the post-range operation of laplace_operator.h:607-741) on
   // COUNT planes of one point column: loaded early (load_operands, before the y-stage) so that their
@@ -180,7 +183,8 @@ namespace mgb
           o.os[r] = dst[d];
         else
           {
-            if (MODE != APPLY_CHEBYSHEV_ZERO && (CHEB || MODE == APPLY_SET_DOT || (BND && ((con >> r) & 1u))))
+            if (MODE != APPLY_CHEBYSHEV_ZERO &&
+                (CHEB || MODE == APPLY_SET_DOT || MODE == APPLY_SET_DOT4 || (BND && ((con >> r) & 1u))))
               o.xs[r] = src[d];
             if (MODE != APPLY_SET && MODE != APPLY_SET_DOT)
               o.rs[r] = rhs[d];
@@ -195,7 +199,7 @@ namespace mgb
   template <int p, typename T, int MODE, int COUNT, bool BND>
   __device__ __forceinline__ double
   store_planes(const ApplyArgs<T> &A, const Operands<T, COUNT> &o, const T (&y)[p + 1], const uint32_t d0,
-               const uint32_t stride, const unsigned int con)
+               const uint32_t stride, const unsigned int con, double *sums4 = nullptr)
   {
     double dot = 0;
     T *__restrict__ dst = A.dst;
@@ -225,6 +229,15 @@ namespace mgb
           {
             dst[d] = v;
             dot += (double)xs * (double)v;
+          }
+        else if (MODE == APPLY_SET_DOT4)
+          {
+            const double q = c ? 0. : (double)y[r], rr = (double)o.rs[r];
+            dst[d]         = (T)q;
+            sums4[0] += q * (double)xs;
+            sums4[1] += rr * rr;
+            sums4[2] += q * rr;
+            sums4[3] += q * q;
           }
         else if (MODE == APPLY_RESIDUAL)
           dst[d] = o.rs[r] - v;
@@ -357,6 +370,7 @@ namespace mgb
     T Pz[n], Qz[n]; // P, Q of this thread's column on the planes of the current cell layer
     T carry = 0;
     double dot_acc = 0; // APPLY_SET_DOT
+    double sums4[MODE == APPLY_SET_DOT4 ? 4 : 1] = {0}; // APPLY_SET_DOT4
 
     const uint32_t u_base = (uint32_t)__cvta_generic_to_shared(u_s + tid);
 
@@ -504,9 +518,9 @@ namespace mgb
             if (c >= c0)
               {
                 if (bnd)
-                  dot_acc += store_planes<p, T, MODE, p, true>(A, ops, y, d_layer, own_stride, con);
+                  dot_acc += store_planes<p, T, MODE, p, true>(A, ops, y, d_layer, own_stride, con, sums4);
                 else
-                  dot_acc += store_planes<p, T, MODE, p, false>(A, ops, y, d_layer, own_stride, 0u);
+                  dot_acc += store_planes<p, T, MODE, p, false>(A, ops, y, d_layer, own_stride, 0u, sums4);
                 d_layer += p * own_stride;
               }
           }
@@ -520,7 +534,30 @@ namespace mgb
         const unsigned int con = (xy_constrained || (L.dirichlet & 32u)) ? 1u : 0u;
         Operands<T, 1>     ops;
         load_operands<p, T, MODE, 1, true>(A, ops, d_layer, own_stride, con);
-        dot_acc += store_planes<p, T, MODE, 1, true>(A, ops, y, d_layer, own_stride, con);
+        dot_acc += store_planes<p, T, MODE, 1, true>(A, ops, y, d_layer, own_stride, con, sums4);
+      }
+    if (MODE == APPLY_SET_DOT4)
+      {
+        // block sums: warp shuffles, then one atomic per block and sum
+        __syncthreads();
+        double *red = reinterpret_cast<double *>(smem_raw); // [4][warps]
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          {
+            double v = sums4[MODE == APPLY_SET_DOT4 ? k : 0];
+            for (int o = 16; o > 0; o >>= 1)
+              v += __shfl_down_sync(0xffffffffu, v, o);
+            if ((tid & 31) == 0)
+              red[k * (NT / 32) + (tid >> 5)] = v;
+          }
+        __syncthreads();
+        if (tid < 4)
+          {
+            double t = 0;
+            for (int w = 0; w < NT / 32; ++w)
+              t += red[tid * (NT / 32) + w];
+            atomicAdd(A.dot_out + tid, t);
+          }
       }
     if (MODE == APPLY_SET_DOT)
       {
@@ -582,7 +619,7 @@ namespace mgb
       {
         if constexpr (MODE != APPLY_CHEBYSHEV_ZERO && MODE != APPLY_CHEBYSHEV_DERIVED)
           cudaFuncSetAttribute(k_apply_tile<p, T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if constexpr (std::is_same<T, float>::value)
+        if constexpr (std::is_same<T, float>::value && MODE != APPLY_SET_DOT4)
           cudaFuncSetAttribute(k_apply_tile_f32x2<p, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
         first = false;
       }
@@ -612,7 +649,7 @@ namespace mgb
         lps  = 1;
         nseg = 2;
       }
-    if constexpr (std::is_same<T, float>::value)
+    if constexpr (std::is_same<T, float>::value && MODE != APPLY_SET_DOT4)
       if (use_f32x2() || MODE == APPLY_CHEBYSHEV_ZERO || MODE == APPLY_CHEBYSHEV_DERIVED)
         {
           k_apply_tile_f32x2<p, MODE><<<ntiles * nseg, C::NT, smem2, stream>>>(A, lps, l0, l1);
@@ -630,6 +667,11 @@ namespace mgb
       {
         case APPLY_ADD: launch_apply_tile<p, T, APPLY_ADD>(A, stream); break;
         case APPLY_SET:
+          if (A.dot_out != nullptr && A.rhs != nullptr) // q = A p with the four sums of vmult_with_cg_update
+            {
+              launch_apply_tile<p, T, APPLY_SET_DOT4>(A, stream);
+              break;
+            }
           if constexpr (sizeof(T) == 8)
             if (A.dot_out != nullptr)
               {

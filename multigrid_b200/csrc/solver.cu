@@ -1354,7 +1354,11 @@ namespace mgb
     void vmult_add(T *dst, const T *src) { apply(APPLY_ADD, dst, src); }
     void vmult_residual(const T *rhs, const T *lhs, T *residual) { apply(APPLY_RESIDUAL, residual, lhs, rhs); }
 
-    // laplace_operator.h:640-719 (q = A p after the vector update, 4 dot products)
+    // laplace_operator.h:640-719 (q = A p after the vector update, 4 dot products).  Two passes over the vectors on
+    // Cartesian levels: the pre-range update x += alpha p, p = beta p + q as one vector kernel (it must be complete
+    // on the halo of every tile before any block reads p, which is why it cannot ride in the apply's load stage
+    // without a second copy of q), then the tile kernel stores q = A p and takes the four sums from the values it
+    // holds (mode SET_DOT4): 40 + 24 bytes per DoF in double instead of the 96 of update / memset / apply-add / sums.
     void
     vmult_with_cg_update(const T alpha, const T beta, const T *r, T *q, T *pp, T *x, double sums[4])
     {
@@ -1366,6 +1370,19 @@ namespace mgb
           x[i] += alpha * pp[i];
           pp[i] = beta * pp[i] + q[i];
         });
+      if (use_cartesian())
+        {
+          MGB_CUDA_CHECK(cudaMemsetAsync(ctx->scal_dev, 0, 4 * sizeof(double), ctx->stream));
+          apply(APPLY_SET, q, pp, r, nullptr, 0, 0, 0, false, ctx->scal_dev);
+          if (level->owned().all_ranks)
+            ctx->all_reduce_sum(ctx->scal_dev, 4);
+          MGB_CUDA_CHECK(cudaMemcpyAsync(ctx->scal_host, ctx->scal_dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+          ctx->sync();
+          ctx->check_p2p_error();
+          for (int k = 0; k < 4; ++k)
+            sums[k] = ctx->scal_host[k];
+          return;
+        }
       // the reference leaves constrained rows of q at zero here (no identity fix-up)
       MGB_CUDA_CHECK(cudaMemsetAsync(q, 0, N * sizeof(T), ctx->stream));
       apply(APPLY_ADD, q, pp);
