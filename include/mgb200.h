@@ -338,6 +338,48 @@ int mgb_dg_solver_solve_cg_host(mgb_dg_solver h, double tolerance, double *solut
                                 double *reduction_rate, unsigned int *n_iterations);
 int64_t mgb_dg_solver_launch_count(mgb_dg_solver h);      /* kernels of the DG part + the FE_Q hierarchy */
 
+/* ---- Pure DG h-multigrid: multigrid::MultigridSolverDGPlain<3,p,float,double,type>
+ *                                                                  common/multigrid_solver_dg_plain.h:54-590
+ * The SIP-DG operator on every level of the refinement hierarchy (level l = the coarse mesh refined l times), no
+ * FE_Q space: Chebyshev over JacobiTransformed on each level (:192-213: range 20, degree degree_pre on inner levels,
+ * max(1, degree_pre - 1) on the finest, 15 CG steps for the eigenvalues; level 0: Chebyshev run as solver with
+ * tolerance 1e-5, its degree chosen by deal.II's rule, m() CG steps), the embedding of the DG space of a cell into
+ * its eight children as transfer (MGTransferMatrixFree; restriction its transpose), V-cycle :456-497 in float under
+ * CG in double (:304-316).  Driver: poisson_dg_plain/program.cc:232-330.  Options and problem data as mgb_dg_solver
+ * (options.basis = the reference's template argument `type`; preconditioner is 1 in the reference).  One GPU.   */
+typedef struct mgb_dg_plain_solver_t *mgb_dg_plain_solver;
+
+int mgb_dg_plain_solver_create(const mgb_dg_solver_options *opt, mgb_dg_plain_solver *out);   /* constructor :58-215 */
+int mgb_dg_plain_solver_destroy(mgb_dg_plain_solver h);
+int64_t mgb_dg_plain_solver_n_dofs(mgb_dg_plain_solver h);
+int mgb_dg_plain_solver_n_levels(mgb_dg_plain_solver h);
+/* matrix[level] (:550), owned by the solver, for the operator-level entry points                              */
+int mgb_dg_plain_solver_level_operator(mgb_dg_plain_solver h, int level, mgb_dg *dg_operator);
+/* solve_cg(tolerance) :304-316, as mgb_dg_solver_solve_cg                                                      */
+int mgb_dg_plain_solver_solve_cg(mgb_dg_plain_solver h, double tolerance, double *iterations_estimate,
+                                 double *reduction_rate, unsigned int *n_iterations);
+int mgb_dg_plain_solver_residual_history(mgb_dg_plain_solver h, double *history, int capacity, int *count);
+int mgb_dg_plain_solver_vmult(mgb_dg_plain_solver h, double *dst, const double *src);          /* vmult :321-337 */
+int mgb_dg_plain_solver_l2_error(mgb_dg_plain_solver h, double *error);             /* compute_l2_error :221-259 */
+/* device pointers: 0 solution, 1 rhs, 2 residual (double, finest level; `level` ignored); 3 defect[level],
+ * 4 solution_update[level], 5 t[level] (float; the smoother swaps vectors, ask again after a cycle)   :535-545 */
+int mgb_dg_plain_solver_vector(mgb_dg_plain_solver h, int which, int level, void **dev_ptr);
+/* the same vector copied to a host buffer of its length and type                                              */
+int mgb_dg_plain_solver_get_vector(mgb_dg_plain_solver h, int which, int level, void *host);
+int mgb_dg_plain_solver_get_solution(mgb_dg_plain_solver h, double *solution_host);
+/* info = {min_eig, max_eig, theta, delta, degree, cg_iterations} of smooth[level]                     :192-213 */
+int mgb_dg_plain_solver_smoother_info(mgb_dg_plain_solver h, int level, double info[6]);
+/* the level transfer on float device vectors (transfer.prolongate / restrict_and_add, :476-486): `level` is the
+ * finer of the two levels; add != 0 adds to dst instead of overwriting it                                     */
+int mgb_dg_plain_solver_prolongate(mgb_dg_plain_solver h, int to_level, float *dst, const float *src, int add);
+int mgb_dg_plain_solver_restrict(mgb_dg_plain_solver h, int from_level, float *dst, const float *src, int add);
+int mgb_dg_plain_solver_do_matvec(mgb_dg_plain_solver h);                           /* :432-436 (double)  */
+int mgb_dg_plain_solver_do_matvec_smoother(mgb_dg_plain_solver h);                  /* :441-445 (float)   */
+int mgb_dg_plain_solver_sync(mgb_dg_plain_solver h);
+int mgb_dg_plain_solver_solve_cg_host(mgb_dg_plain_solver h, double tolerance, double *solution_host,
+                                      double *iterations_estimate, double *reduction_rate, unsigned int *n_iterations);
+int64_t mgb_dg_plain_solver_launch_count(mgb_dg_plain_solver h);
+
 /* ---- Adaptive meshes with hanging nodes (poisson_l/program.cc:232-260,465-541)
  * FE_Q(p) Laplacian on a forest of n_roots[0] x n_roots[1] x n_roots[2] root cells filling [lower, upper]
  * (root_mask[z][y][x] != 0 keeps a root cell; NULL keeps all: GridGenerator::hyper_L is a 2x2x2 grid with one

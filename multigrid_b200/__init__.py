@@ -204,6 +204,26 @@ SYMBOLS = {
     "mgb_dg_solver_sync": (_i, [_vp]),
     "mgb_dg_solver_solve_cg_host": (_i, [_vp, _d, _vp, _dp, _dp, C.POINTER(_u)]),
     "mgb_dg_solver_launch_count": (C.c_int64, [_vp]),
+    "mgb_dg_plain_solver_create": (_i, [C.POINTER(DGSolverOptions), C.POINTER(_vp)]),
+    "mgb_dg_plain_solver_destroy": (_i, [_vp]),
+    "mgb_dg_plain_solver_n_dofs": (C.c_int64, [_vp]),
+    "mgb_dg_plain_solver_n_levels": (_i, [_vp]),
+    "mgb_dg_plain_solver_level_operator": (_i, [_vp, _i, C.POINTER(_vp)]),
+    "mgb_dg_plain_solver_solve_cg": (_i, [_vp, _d, _dp, _dp, C.POINTER(_u)]),
+    "mgb_dg_plain_solver_residual_history": (_i, [_vp, _dp, _i, _ip]),
+    "mgb_dg_plain_solver_vmult": (_i, [_vp, _vp, _vp]),
+    "mgb_dg_plain_solver_l2_error": (_i, [_vp, _dp]),
+    "mgb_dg_plain_solver_vector": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
+    "mgb_dg_plain_solver_get_vector": (_i, [_vp, _i, _i, _vp]),
+    "mgb_dg_plain_solver_get_solution": (_i, [_vp, _vp]),
+    "mgb_dg_plain_solver_smoother_info": (_i, [_vp, _i, _dp]),
+    "mgb_dg_plain_solver_prolongate": (_i, [_vp, _i, _vp, _vp, _i]),
+    "mgb_dg_plain_solver_restrict": (_i, [_vp, _i, _vp, _vp, _i]),
+    "mgb_dg_plain_solver_do_matvec": (_i, [_vp]),
+    "mgb_dg_plain_solver_do_matvec_smoother": (_i, [_vp]),
+    "mgb_dg_plain_solver_sync": (_i, [_vp]),
+    "mgb_dg_plain_solver_solve_cg_host": (_i, [_vp, _d, _vp, _dp, _dp, C.POINTER(_u)]),
+    "mgb_dg_plain_solver_launch_count": (C.c_int64, [_vp]),
     # adaptive meshes with hanging nodes
     "mgb_adaptive_create": (_i, [_i, _ip, C.POINTER(C.c_ubyte), _dp, _dp, _i, _i, C.POINTER(_vp)]),
     "mgb_adaptive_destroy": (_i, [_vp]),
@@ -1000,6 +1020,134 @@ class MultigridSolverDG:
 
     def launch_count(self):
         return lib().mgb_dg_solver_launch_count(self.h)
+
+
+class MultigridSolverDGPlain:
+    """multigrid::MultigridSolverDGPlain<3,p,float,double,type> (common/multigrid_solver_dg_plain.h:54-590): CG in
+    double on the SIP-DG operator preconditioned by one float V-cycle whose levels are the DG spaces of the refinement
+    hierarchy (Chebyshev/JacobiTransformed smoothers, cell-wise embedding as transfer).  Problem data and mesh of
+    poisson_dg_plain/program.cc:70-135,356-409.  One GPU."""
+
+    def __init__(self, degree=4, n_subdivisions=(1, 1, 1), n_refinements=3, lower=(-1.,) * 3, upper=(1.,) * 3,
+                 degree_pre=3, degree_post=3, device=0, basis=DG_BASIS_HERMITE):
+        """basis: DG_BASIS_* = the reference's template argument `type` (poisson_dg_plain/program.cc:420-446 runs all three)"""
+        import torch
+        o = DGSolverOptions()
+        lib().mgb_dg_solver_default_options(C.byref(o))
+        o.degree = degree
+        if isinstance(n_subdivisions, int):
+            n_subdivisions = (n_subdivisions,) * 3
+        o.n_subdivisions[:] = list(n_subdivisions)
+        o.n_refinements = n_refinements
+        o.lower[:] = list(lower)
+        o.upper[:] = list(upper)
+        o.degree_pre, o.degree_post, o.preconditioner, o.device = degree_pre, degree_post, 1, device
+        o.basis = basis
+        self.h = C.c_void_p()
+        self.device = torch.device("cuda", device)
+        self.degree = degree
+        _check(lib().mgb_dg_plain_solver_create(C.byref(o), C.byref(self.h)))
+
+    def close(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.mgb_dg_plain_solver_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def n_dofs(self):
+        return lib().mgb_dg_plain_solver_n_dofs(self.h)
+
+    def n_levels(self):
+        return lib().mgb_dg_plain_solver_n_levels(self.h)
+
+    def level_n_dofs(self, level):
+        op = C.c_void_p()
+        _check(lib().mgb_dg_plain_solver_level_operator(self.h, level, C.byref(op)))
+        return lib().mgb_dg_n_dofs(op)
+
+    def sync(self):
+        _check(lib().mgb_dg_plain_solver_sync(self.h))
+
+    def solve_cg(self, tolerance=1e-3):
+        """-> (log(tol)/log(rate), rate) as the reference; `last_step` holds the iteration count"""
+        est, rate, its = C.c_double(), C.c_double(), C.c_uint()
+        _check(lib().mgb_dg_plain_solver_solve_cg(self.h, tolerance, C.byref(est), C.byref(rate), C.byref(its)))
+        self.last_step = its.value
+        return est.value, rate.value
+
+    def solve_cg_host(self, tolerance, solution_host=None):
+        est, rate, its = C.c_double(), C.c_double(), C.c_uint()
+        ptr = None if solution_host is None else C.c_void_p(
+            solution_host.data_ptr() if hasattr(solution_host, "data_ptr") else solution_host.ctypes.data)
+        _check(lib().mgb_dg_plain_solver_solve_cg_host(self.h, tolerance, ptr, C.byref(est), C.byref(rate), C.byref(its)))
+        self.last_step = its.value
+        return est.value, rate.value
+
+    def residual_history(self):
+        hist = np.zeros(128)
+        cnt = C.c_int()
+        _check(lib().mgb_dg_plain_solver_residual_history(self.h, hist.ctypes.data_as(_dp), 128, C.byref(cnt)))
+        return hist[:cnt.value]
+
+    def vmult(self, dst, src):
+        """one V-cycle as preconditioner: double device tensors"""
+        import torch
+        assert dst.dtype == torch.float64 and src.dtype == torch.float64 and dst.numel() == src.numel() == self.n_dofs()
+        torch.cuda.synchronize(self.device)
+        _check(lib().mgb_dg_plain_solver_vmult(self.h, C.c_void_p(dst.data_ptr()), C.c_void_p(src.data_ptr())))
+        self.sync()
+
+    def _transfer(self, fn, level, dst, src, n_dst, n_src, add):
+        import torch
+        assert dst.dtype == torch.float32 and src.dtype == torch.float32
+        assert dst.numel() == n_dst and src.numel() == n_src and dst.is_cuda and src.is_cuda
+        torch.cuda.synchronize(self.device)
+        _check(fn(self.h, level, C.c_void_p(dst.data_ptr()), C.c_void_p(src.data_ptr()), int(add)))
+        self.sync()
+
+    def prolongate(self, to_level, dst, src, add=False):
+        """dst (level to_level) = or += P src (level to_level - 1), float device tensors"""
+        self._transfer(lib().mgb_dg_plain_solver_prolongate, to_level, dst, src, self.level_n_dofs(to_level),
+                       self.level_n_dofs(to_level - 1), add)
+
+    def restrict(self, from_level, dst, src, add=False):
+        """dst (level from_level - 1) = or += P^T src (level from_level), float device tensors"""
+        self._transfer(lib().mgb_dg_plain_solver_restrict, from_level, dst, src, self.level_n_dofs(from_level - 1),
+                       self.level_n_dofs(from_level), add)
+
+    def compute_l2_error(self):
+        e = C.c_double()
+        _check(lib().mgb_dg_plain_solver_l2_error(self.h, C.byref(e)))
+        return e.value
+
+    def get_solution(self):
+        out = np.zeros(self.n_dofs())
+        _check(lib().mgb_dg_plain_solver_get_solution(self.h, C.c_void_p(out.ctypes.data)))
+        return out
+
+    def get_vector(self, which, level=None):
+        """host copy of 0 solution, 1 rhs, 2 residual (double, finest level), 3 defect[level], 4 solution_update[level],
+        5 t[level] (float)"""
+        level = self.n_levels() - 1 if level is None else level
+        out = np.zeros(self.n_dofs() if which < 3 else self.level_n_dofs(level), dtype=np.float64 if which < 3 else np.float32)
+        _check(lib().mgb_dg_plain_solver_get_vector(self.h, which, level, C.c_void_p(out.ctypes.data)))
+        return out
+
+    def smoother_info(self, level):
+        info = np.zeros(6)
+        _check(lib().mgb_dg_plain_solver_smoother_info(self.h, level, info.ctypes.data_as(_dp)))
+        return dict(min_eig=info[0], max_eig=info[1], theta=info[2], delta=info[3], degree=int(info[4]),
+                    cg_iterations=int(info[5]))
+
+    def do_matvec(self):
+        _check(lib().mgb_dg_plain_solver_do_matvec(self.h))
+
+    def do_matvec_smoother(self):
+        _check(lib().mgb_dg_plain_solver_do_matvec_smoother(self.h))
+
+    def launch_count(self):
+        return lib().mgb_dg_plain_solver_launch_count(self.h)
 
 
 class LaplaceOperatorAdaptive:

@@ -224,6 +224,10 @@ namespace mgb
     std::vector<double> e0, e1;   // phi_i'(0), phi_i'(1)
     std::vector<double> B;        // B[j n + i] = phi_i(Gauss-Lobatto point j): nodal values from coefficients
     std::vector<double> Binv;     // coefficients from the values in the Gauss-Lobatto points
+    // h-embedding of the 1-D basis into the two children of a cell (the DG level transfer of MGTransferMatrixFree):
+    // E[o][jf n + ic] = coefficient jf of the child o = 0 / 1 of the parent's basis function ic, i.e. the child's
+    // representation of phi_ic((o + xi) / 2)
+    std::vector<double> E[2];
   };
 
   namespace detail
@@ -441,6 +445,19 @@ namespace mgb
     for (int i = 0; i < n; ++i)
       for (int j = 0; j < n; ++j)
         b.Binv[i * n + j] = clean(A[i * 2 * n + n + j]);
+    // embedding: values of the parent's functions in the Gauss-Lobatto points of the child, then to coefficients
+    for (int o = 0; o < 2; ++o)
+      {
+        b.E[o].assign(n * n, 0.);
+        for (int jf = 0; jf < n; ++jf)
+          for (int ic = 0; ic < n; ++ic)
+            {
+              ld s = 0;
+              for (int k = 0; k < n; ++k)
+                s += A[jf * 2 * n + n + k] * phi[ic].value((o + xl[k]) / 2);
+              b.E[o][jf * n + ic] = clean(s);
+            }
+      }
     return b;
   }
 } // namespace mgb

@@ -7,6 +7,8 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
+#include <memory>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -1056,6 +1058,7 @@ namespace mgb
 } // namespace mgb
 
 #include "dg_solver.cuh"
+#include "dg_plain_solver.cuh"
 
 // ====================================================================== C ABI
 using namespace mgb;
@@ -1103,6 +1106,28 @@ DGS(mgb_dg_solver h)
   if (!h || !h->impl)
     throw std::runtime_error("null DG solver handle");
   return *h->impl;
+}
+
+struct mgb_dg_plain_solver_t
+{
+  DGPlainSolver        *impl;
+  std::vector<mgb_dg_t> ops; // views of the level operators
+};
+
+static DGPlainSolver &
+DGP(mgb_dg_plain_solver h)
+{
+  if (!h || !h->impl)
+    throw std::runtime_error("null DG plain solver handle");
+  return *h->impl;
+}
+
+static int
+check_level(const DGPlainSolver &m, const int level)
+{
+  if (level < 0 || level >= m.n_levels)
+    throw std::runtime_error("level out of range");
+  return level;
 }
 
 static void
@@ -1578,5 +1603,233 @@ extern "C"
     if (!h || !h->impl)
       return -1;
     return h->impl->op->launches + mgb_solver_launch_count(h->impl->fe);
+  }
+
+  // ------------------------------------------------------------------ pure DG h-multigrid solver
+  int
+  mgb_dg_plain_solver_create(const mgb_dg_solver_options *opt, mgb_dg_plain_solver *out)
+  {
+    DG_TRY
+    if (!opt || !out)
+      throw std::runtime_error("null argument");
+    *out    = nullptr;
+    auto *h = new mgb_dg_plain_solver_t;
+    h->impl = nullptr;
+    try
+      {
+        h->impl = new DGPlainSolver(*opt);
+        for (auto &o : h->impl->ops)
+          h->ops.push_back(mgb_dg_t{o.get()});
+      }
+    catch (...)
+      {
+        delete h;
+        throw;
+      }
+    *out = h;
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_destroy(mgb_dg_plain_solver h)
+  {
+    DG_TRY
+    if (h)
+      {
+        delete h->impl;
+        delete h;
+      }
+    DG_CATCH
+  }
+
+  int64_t
+  mgb_dg_plain_solver_n_dofs(mgb_dg_plain_solver h)
+  {
+    return h && h->impl ? (int64_t)h->impl->N : -1;
+  }
+
+  int
+  mgb_dg_plain_solver_n_levels(mgb_dg_plain_solver h)
+  {
+    return h && h->impl ? h->impl->n_levels : -1;
+  }
+
+  int
+  mgb_dg_plain_solver_level_operator(mgb_dg_plain_solver h, int level, mgb_dg *dg)
+  {
+    DG_TRY
+    *dg = &h->ops[check_level(DGP(h), level)];
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_solve_cg(mgb_dg_plain_solver h, double tolerance, double *its_estimate, double *rate, unsigned int *its)
+  {
+    DG_TRY
+    if (!(tolerance > 0 && tolerance < 1))
+      throw std::runtime_error("tolerance must be in (0, 1)");
+    DGP(h).solve_cg(tolerance, its_estimate, rate, its);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_residual_history(mgb_dg_plain_solver h, double *history, int capacity, int *count)
+  {
+    DG_TRY
+    DGPlainSolver &m = DGP(h);
+    const int      k = (int)m.residual_history.size();
+    for (int i = 0; i < std::min(k, capacity); ++i)
+      history[i] = m.residual_history[i];
+    if (count)
+      *count = k;
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_vmult(mgb_dg_plain_solver h, double *dst, const double *src)
+  {
+    DG_TRY
+    DGP(h).vmult(dst, src);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_l2_error(mgb_dg_plain_solver h, double *error)
+  {
+    DG_TRY
+    *error = DGP(h).compute_l2_error();
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_vector(mgb_dg_plain_solver h, int which, int level, void **dev_ptr)
+  {
+    DG_TRY
+    DGPlainSolver &m = DGP(h);
+    switch (which)
+      {
+        case 0: *dev_ptr = m.solution; break;
+        case 1: *dev_ptr = m.rhs; break;
+        case 2: *dev_ptr = m.g; break;
+        case 3: *dev_ptr = m.defect[check_level(m, level)]; break;
+        case 4: *dev_ptr = m.solution_update[check_level(m, level)]; break;
+        case 5: *dev_ptr = m.t[check_level(m, level)]; break;
+        default: throw std::runtime_error("unknown vector id");
+      }
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_get_vector(mgb_dg_plain_solver h, int which, int level, void *host)
+  {
+    DG_TRY
+    DGPlainSolver &m   = DGP(h);
+    void          *dev = nullptr;
+    if (mgb_dg_plain_solver_vector(h, which, level, &dev) != 0)
+      throw std::runtime_error(mgb_last_error());
+    const size_t bytes = which < 3 ? m.N * sizeof(double) : m.ops[level]->n_dofs * sizeof(float);
+    MGB_DG_CHECK(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, m.stream));
+    MGB_DG_CHECK(cudaStreamSynchronize(m.stream));
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_get_solution(mgb_dg_plain_solver h, double *host)
+  {
+    DG_TRY
+    DGPlainSolver &m = DGP(h);
+    MGB_DG_CHECK(cudaMemcpyAsync(host, m.solution, m.N * sizeof(double), cudaMemcpyDeviceToHost, m.stream));
+    MGB_DG_CHECK(cudaStreamSynchronize(m.stream));
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_smoother_info(mgb_dg_plain_solver h, int level, double info[6])
+  {
+    DG_TRY
+    DGPlainSolver     &m = DGP(h);
+    const DGChebyshev &c = m.smooth[check_level(m, level)];
+    info[0]              = c.min_eig;
+    info[1]              = c.max_eig;
+    info[2]              = c.theta;
+    info[3]              = c.delta;
+    info[4]              = c.degree;
+    info[5]              = c.cg_iterations;
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_prolongate(mgb_dg_plain_solver h, int to_level, float *dst, const float *src, int add)
+  {
+    DG_TRY
+    DGPlainSolver &m = DGP(h);
+    if (check_level(m, to_level) < 1)
+      throw std::runtime_error("no level below level 0");
+    if (add)
+      m.transfer<false, true>(to_level, dst, src);
+    else
+      m.transfer<false, false>(to_level, dst, src);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_restrict(mgb_dg_plain_solver h, int from_level, float *dst, const float *src, int add)
+  {
+    DG_TRY
+    DGPlainSolver &m = DGP(h);
+    if (check_level(m, from_level) < 1)
+      throw std::runtime_error("no level below level 0");
+    if (add)
+      m.transfer<true, true>(from_level, dst, src);
+    else
+      m.transfer<true, false>(from_level, dst, src);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_do_matvec(mgb_dg_plain_solver h)
+  {
+    DG_TRY
+    DGPlainSolver &m = DGP(h);
+    m.ops.back()->apply<double>(DG_SET, m.g, m.solution);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_do_matvec_smoother(mgb_dg_plain_solver h)
+  {
+    DG_TRY
+    DGPlainSolver &m = DGP(h);
+    m.ops.back()->apply<float>(DG_SET, m.solution_update.back(), m.defect.back());
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_sync(mgb_dg_plain_solver h)
+  {
+    DG_TRY
+    MGB_DG_CHECK(cudaStreamSynchronize(DGP(h).stream));
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_solve_cg_host(mgb_dg_plain_solver h, double tolerance, double *solution_host, double *its_estimate,
+                                    double *rate, unsigned int *its)
+  {
+    DG_TRY
+    if (!(tolerance > 0 && tolerance < 1))
+      throw std::runtime_error("tolerance must be in (0, 1)");
+    DGPlainSolver &m = DGP(h);
+    m.solve_cg(tolerance, its_estimate, rate, its);
+    if (solution_host)
+      MGB_DG_CHECK(cudaMemcpyAsync(solution_host, m.solution, m.N * sizeof(double), cudaMemcpyDeviceToHost, m.stream));
+    MGB_DG_CHECK(cudaStreamSynchronize(m.stream));
+    DG_CATCH
+  }
+
+  int64_t
+  mgb_dg_plain_solver_launch_count(mgb_dg_plain_solver h)
+  {
+    return h && h->impl ? h->impl->launch_count() : -1;
   }
 }

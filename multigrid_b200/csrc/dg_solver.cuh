@@ -109,6 +109,7 @@ namespace mgb
   // Jacobi) is the one selected on the operator.  vmult / step are the fused vmult_with_chebyshev_update calls.
   struct DGChebyshev
   {
+    static constexpr unsigned int invalid_degree = 0xffffffffu;
     DGOperator  *A = nullptr;
     double       smoothing_range = 20.;
     unsigned int degree = 3, eig_cg_n_iterations = 15, cg_iterations = 0;
@@ -185,6 +186,14 @@ namespace mgb
         min_eig = max_eig = 1.;
       const double max_est = 1.2 * max_eig;
       const double alpha   = smoothing_range > 1. ? max_est / smoothing_range : std::min(0.9 * max_est, min_eig);
+      if (degree == invalid_degree)
+        {
+          // coarse solver: smoothing_range is the tolerance (deal.II PreconditionChebyshev, multigrid_solver_dg_plain.h:204-208)
+          const double actual_range = max_est / alpha;
+          const double sigma        = (1. - std::sqrt(1. / actual_range)) / (1. + std::sqrt(1. / actual_range));
+          const double eps          = smoothing_range;
+          degree = 1 + static_cast<unsigned int>(std::log(1. / eps + std::sqrt(1. / eps / eps - 1.)) / std::log(1. / sigma));
+        }
       theta                = (max_est + alpha) * 0.5;
       delta                = (max_est - alpha) * 0.5;
       MGB_DG_CHECK(cudaStreamSynchronize(op.stream));
@@ -225,6 +234,63 @@ namespace mgb
       loop(x, b, false);
     }
   };
+
+  // deal.II SolverCG with ReductionControl(100, 1e-16, tolerance) from a zero start vector, in double on the DG operator
+  // `op`, preconditioned by `cycle()` which maps the float vector `defect` to the float vector it returns
+  // (multigrid_solver_dg.h:410-424, multigrid_solver_dg_plain.h:304-316).  Returns the iteration count and the final
+  // residual norm; `history` receives the residual norms.
+  inline unsigned int
+  dg_solve_cg(DGOperator &op, const size_t N, double *x, const double *b, double *gp, double *dp, double *hp, float *def,
+              const std::function<const float *()> &cycle, const double tolerance, std::vector<double> &history, double &res0_out, double &res_out)
+  {
+    double r[2];
+    history.clear();
+    MGB_DG_CHECK(cudaMemsetAsync(x, 0, N * sizeof(double), op.stream));
+    op.foreach (N, [=] __device__(size_t i) { gp[i] = -b[i]; }); // g = A x - b with x = 0
+    op.sums<2>(r, [=] __device__(size_t i, double *acc) { acc[0] += gp[i] * gp[i]; });
+    const double res0 = std::sqrt(r[0]);
+    double       res  = res0;
+    history.push_back(res0);
+    unsigned int it = 0;
+    double       gh = 0;
+    const auto   converged = [&](const double v) { return v <= 1e-16 || v <= tolerance * res0; };
+    if (!converged(res0))
+      for (it = 1;; ++it)
+        {
+          // h = M^-1 g, gh = g.h fused into the conversion back to double
+          op.foreach (N, [=] __device__(size_t i) { def[i] = (float)gp[i]; });
+          const float *upd = cycle();
+          op.sums<2>(r, [=] __device__(size_t i, double *acc) {
+            const double hi = (double)upd[i];
+            hp[i]           = hi;
+            acc[0] += gp[i] * hi;
+          });
+          const double beta = it > 1 ? r[0] / gh : 0.;
+          gh                = r[0];
+          if (it > 1)
+            op.foreach (N, [=] __device__(size_t i) { dp[i] = beta * dp[i] - hp[i]; });
+          else
+            op.foreach (N, [=] __device__(size_t i) { dp[i] = -hp[i]; });
+          op.apply<double>(DG_SET, hp, dp);
+          op.sums<2>(r, [=] __device__(size_t i, double *acc) { acc[0] += dp[i] * hp[i]; });
+          const double alpha = gh / r[0];
+          op.sums<2>(r, [=] __device__(size_t i, double *acc) {
+            x[i] += alpha * dp[i];
+            const double gi = gp[i] + alpha * hp[i];
+            gp[i]           = gi;
+            acc[0] += gi * gi;
+          });
+          res = std::sqrt(r[0]);
+          history.push_back(res);
+          if (converged(res))
+            break;
+          if (it >= 100)
+            throw std::runtime_error("SolverCG: no convergence within 100 iterations");
+        }
+    res0_out = res0;
+    res_out  = res;
+    return it;
+  }
 
   struct DGMultigridSolver
   {
@@ -437,54 +503,14 @@ namespace mgb
     void
     solve_cg(const double tolerance, double *iterations_estimate, double *reduction_rate, unsigned int *n_iterations)
     {
-      double *x = solution, *gp = g, *dp = d, *hp = h;
-      const double *b = rhs;
-      double        r[2];
-      residual_history.clear();
-      MGB_DG_CHECK(cudaMemsetAsync(x, 0, N * sizeof(double), op->stream));
-      op->foreach (N, [=] __device__(size_t i) { gp[i] = -b[i]; }); // g = A x - b with x = 0
-      op->sums<2>(r, [=] __device__(size_t i, double *acc) { acc[0] += gp[i] * gp[i]; });
-      const double res0 = std::sqrt(r[0]);
-      double       res  = res0;
-      residual_history.push_back(res0);
-      unsigned int it = 0;
-      double       gh = 0;
-      const auto   converged = [&](const double v) { return v <= 1e-16 || v <= tolerance * res0; };
-      if (!converged(res0))
-        for (it = 1;; ++it)
-          {
-            // h = M^-1 g, gh = g.h fused into the conversion back to double
-            float *def = defect_dg;
-            op->foreach (N, [=] __device__(size_t i) { def[i] = (float)gp[i]; });
-            dg_v_cycle();
-            const float *upd = solution_update_dg;
-            op->sums<2>(r, [=] __device__(size_t i, double *acc) {
-              const double hi = (double)upd[i];
-              hp[i]           = hi;
-              acc[0] += gp[i] * hi;
-            });
-            const double beta = it > 1 ? r[0] / gh : 0.;
-            gh                = r[0];
-            if (it > 1)
-              op->foreach (N, [=] __device__(size_t i) { dp[i] = beta * dp[i] - hp[i]; });
-            else
-              op->foreach (N, [=] __device__(size_t i) { dp[i] = -hp[i]; });
-            op->apply<double>(DG_SET, hp, dp);
-            op->sums<2>(r, [=] __device__(size_t i, double *acc) { acc[0] += dp[i] * hp[i]; });
-            const double alpha = gh / r[0];
-            op->sums<2>(r, [=] __device__(size_t i, double *acc) {
-              x[i] += alpha * dp[i];
-              const double gi = gp[i] + alpha * hp[i];
-              gp[i]           = gi;
-              acc[0] += gi * gi;
-            });
-            res = std::sqrt(r[0]);
-            residual_history.push_back(res);
-            if (converged(res))
-              break;
-            if (it >= 100)
-              throw std::runtime_error("SolverCG: no convergence within 100 iterations");
-          }
+      double             res0 = 0, res = 0;
+      const unsigned int it   = dg_solve_cg(
+        *op, N, solution, rhs, g, d, h, defect_dg,
+        [&]() -> const float * {
+          dg_v_cycle();
+          return solution_update_dg;
+        },
+        tolerance, residual_history, res0, res);
       const double rate = it > 0 ? std::pow(res / res0, 1. / it) : 0.;
       if (reduction_rate)
         *reduction_rate = rate;

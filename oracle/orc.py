@@ -167,8 +167,12 @@ def dg_basis(p, kind=DG_BASIS_GAUSS_LOBATTO):
     t["G"] = np.array([[der(i, x) for i in range(n)] for x in b["xq"]])
     t["B"] = np.array([[val(i, x) for i in range(n)] for x in b["gll"]])
     t["f0"], t["f1"] = np.array([val(i, 0.) for i in range(n)]), np.array([val(i, 1.) for i in range(n)])
+    # embedding of the cell's space into its two 1-D children (the prolongation matrices of the element, used by
+    # MGTransferMatrixFree): E_o[j, i] = coefficient j on child o of phi_i restricted to it
+    for o in (0, 1):
+        t["E%d" % o] = np.linalg.solve(t["B"], np.array([[val(i, 0.5 * (o + x)) for i in range(n)] for x in b["gll"]]))
     t["e0"], t["e1"] = np.array([der(i, 0.) for i in range(n)]), np.array([der(i, 1.) for i in range(n)])
-    for k in ("S", "G", "B", "f0", "f1", "e0", "e1"):
+    for k in ("S", "G", "B", "f0", "f1", "e0", "e1", "E0", "E1"):
         t[k] = np.ascontiguousarray(np.where(np.abs(t[k]) < 1e-15, 0., t[k]))
     return t
 
@@ -478,6 +482,8 @@ class ChebyshevDG:
     then the three-term recurrence (vmult: zero start, step: given start)."""
 
     def __init__(self, op, prec, smoothing_range=20., degree=3, eig_cg_n_iterations=15):
+        """degree None: the smoother as coarse solver, smoothing_range is then the tolerance and the degree follows
+        from it (multigrid_solver_dg_plain.h:204-208)"""
         self.op, self.prec, self.degree = op, prec, degree
         N = op.n_dofs()
         g = (np.arange(N) % 11).astype(np.float64)
@@ -509,7 +515,12 @@ class ChebyshevDG:
         ev = np.linalg.eigvalsh(T)
         self.min_eig, self.max_eig = ev[0], ev[-1]
         max_est = 1.2 * self.max_eig
-        a = max_est / smoothing_range
+        a = max_est / smoothing_range if smoothing_range > 1. else min(0.9 * max_est, self.min_eig)
+        if degree is None:
+            rng = max_est / a
+            sigma = (1. - np.sqrt(1. / rng)) / (1. + np.sqrt(1. / rng))
+            eps = smoothing_range
+            self.degree = 1 + int(np.log(1. / eps + np.sqrt(1. / eps / eps - 1.)) / np.log(1. / sigma))
         self.theta, self.delta = 0.5 * (max_est + a), 0.5 * (max_est - a)
 
     def _loop(self, x, x_old, b):
@@ -629,3 +640,90 @@ class MultigridSolverDG:
         X, Y, Z = self.Xq
         ex = np.sin(3 * np.pi * X) * np.sin(3 * np.pi * Y) * np.sin(3 * np.pi * Z)
         return np.sqrt(np.sum((uq - ex) ** 2 * self.W) / np.sum(self.W))
+
+
+class MultigridSolverDGPlain:
+    """multigrid::MultigridSolverDGPlain (common/multigrid_solver_dg_plain.h:54-590) composed from the oracle's parts:
+    the face-based DG operator (dg_oracle.cpp) on every level, JacobiTransformed / ChebyshevDG with the settings of
+    :192-213, the cell-wise embedding as level transfer, the V-cycle of :456-497 and SolverCG (:304-316).  Double
+    precision throughout (the reference runs the cycle in float); small meshes only."""
+
+    def __init__(self, degree, n_subdivisions, n_refine, lower=(-1.,) * 3, upper=(1.,) * 3, degree_pre=3, degree_post=3,
+                 basis=DG_BASIS_GAUSS_LOBATTO):
+        if isinstance(n_subdivisions, int):
+            n_subdivisions = (n_subdivisions,) * 3
+        assert degree_pre == degree_post
+        self.degree, self.n_levels = degree, n_refine + 1
+        self.ops, self.jt, self.smooth = [], [], []
+        for l in range(self.n_levels):
+            nc = [k << l for k in n_subdivisions]
+            op = DGOperator(degree, nc, lower=lower, upper=upper, trafo=np.eye(3), basis=basis)
+            jt = JacobiTransformed(op)
+            if l == 0:
+                sm = ChebyshevDG(op, jt.vmult, 1e-5, None, op.n_dofs())
+            else:
+                sm = ChebyshevDG(op, jt.vmult, 20., degree_pre if l < n_refine else max(1, degree_pre - 1), 15)
+            self.ops.append(op)
+            self.jt.append(jt)
+            self.smooth.append(sm)
+        self.op = self.ops[-1]
+        b = self.op.tables
+        self.E = (b["E0"], b["E1"])
+        n = degree + 1
+        nc = self.op.ncell
+        cz, cy, cx, k, j, i = np.meshgrid(np.arange(nc[2]), np.arange(nc[1]), np.arange(nc[0]), np.arange(n),
+                                          np.arange(n), np.arange(n), indexing="ij")
+        S, xq, wq = b["S"], b["xq"], b["wq"]
+        h = [(upper[d] - lower[d]) / nc[d] for d in range(3)]
+        self.nc = nc
+        X = lower[0] + h[0] * (cx + xq[i])
+        Y = lower[1] + h[1] * (cy + xq[j])
+        Z = lower[2] + h[2] * (cz + xq[k])
+        self.Xq = (X, Y, Z)
+        f = 3 * (3 * np.pi) ** 2 * np.sin(3 * np.pi * X) * np.sin(3 * np.pi * Y) * np.sin(3 * np.pi * Z)
+        self.W = wq[k] * wq[j] * wq[i] * h[0] * h[1] * h[2]
+        self.S = S
+        self.rhs = np.einsum("rc,qb,pa,zyxrqp->zyxcba", S, S, S, f * self.W).ravel()   # :162-185
+        self.solution = np.zeros_like(self.rhs)
+
+    def n_dofs(self):
+        return self.op.n_dofs()
+
+    def prolongate(self, to_level, src):
+        """coarse cell -> its eight children, (E_oz x E_oy x E_ox) per child"""
+        n = self.degree + 1
+        ncx, ncy, ncz = self.ops[to_level - 1].ncell
+        u = np.asarray(src, dtype=np.float64).reshape(ncz, ncy, ncx, n, n, n)
+        out = np.zeros((2 * ncz, 2 * ncy, 2 * ncx, n, n, n))
+        for oz in (0, 1):
+            for oy in (0, 1):
+                for ox in (0, 1):
+                    out[oz::2, oy::2, ox::2] = np.einsum("kc,jb,ia,zyxcba->zyxkji", self.E[oz], self.E[oy], self.E[ox], u)
+        return out.ravel()
+
+    def restrict(self, from_level, src):
+        """the transpose of prolongate()"""
+        n = self.degree + 1
+        ncx, ncy, ncz = self.ops[from_level - 1].ncell
+        r = np.asarray(src, dtype=np.float64).reshape(2 * ncz, 2 * ncy, 2 * ncx, n, n, n)
+        out = np.zeros((ncz, ncy, ncx, n, n, n))
+        for oz in (0, 1):
+            for oy in (0, 1):
+                for ox in (0, 1):
+                    out += np.einsum("kc,jb,ia,zyxkji->zyxcba", self.E[oz], self.E[oy], self.E[ox], r[oz::2, oy::2, ox::2])
+        return out.ravel()
+
+    def v_cycle(self, level, defect):
+        """:456-497 with my_n_cycles = 1"""
+        if level == 0:
+            return self.smooth[0].vmult(defect)
+        x = self.smooth[level].vmult(defect)
+        t = defect - self.ops[level].vmult(x)
+        x = x + self.prolongate(level, self.v_cycle(level - 1, self.restrict(level, t)))
+        return self.smooth[level].step(x, defect)
+
+    def vmult(self, src):
+        return self.v_cycle(self.n_levels - 1, src)
+
+    solve_cg = MultigridSolverDG.solve_cg
+    compute_l2_error = MultigridSolverDG.compute_l2_error
