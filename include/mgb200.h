@@ -323,6 +323,12 @@ int mgb_dg_solver_solve_cg(mgb_dg_solver h, double tolerance, double *iterations
 int mgb_dg_solver_residual_history(mgb_dg_solver h, double *history, int capacity, int *count);
 /* vmult(dst, src) :429-441: one cycle as preconditioner, double device vectors of mgb_dg_solver_n_dofs()     */
 int mgb_dg_solver_vmult(mgb_dg_solver h, double *dst, const double *src);
+/* vmult_with_residual_update(residual, update, factor) :445-527, the preconditioner call of a CG solver with merged
+ * vector operations: one cycle on residual + factor * update; afterwards residual += factor * update, update = the
+ * cycle's result, results = {update_new . residual_new, update_new . (factor * update_old)} (factor 0: both the
+ * first).  Double device vectors                                                                             */
+int mgb_dg_solver_vmult_with_residual_update(mgb_dg_solver h, double *residual, double *update, double factor,
+                                             double results[2]);
 int mgb_dg_solver_l2_error(mgb_dg_solver h, double *error);                        /* compute_l2_error :328-366 */
 /* device pointers of the solver's vectors: 0 solution, 1 rhs, 2 residual (double); 3 defect_dg,
  * 4 solution_update_dg (float; the smoother swaps vectors, ask again after a cycle)              :663-693 */
@@ -360,6 +366,9 @@ int mgb_dg_plain_solver_solve_cg(mgb_dg_plain_solver h, double tolerance, double
                                  double *reduction_rate, unsigned int *n_iterations);
 int mgb_dg_plain_solver_residual_history(mgb_dg_plain_solver h, double *history, int capacity, int *count);
 int mgb_dg_plain_solver_vmult(mgb_dg_plain_solver h, double *dst, const double *src);          /* vmult :321-337 */
+/* vmult_with_residual_update :340-427, as mgb_dg_solver_vmult_with_residual_update                             */
+int mgb_dg_plain_solver_vmult_with_residual_update(mgb_dg_plain_solver h, double *residual, double *update, double factor,
+                                                   double results[2]);
 int mgb_dg_plain_solver_l2_error(mgb_dg_plain_solver h, double *error);             /* compute_l2_error :221-259 */
 /* device pointers: 0 solution, 1 rhs, 2 residual (double, finest level; `level` ignored); 3 defect[level],
  * 4 solution_update[level], 5 t[level] (float; the smoother swaps vectors, ask again after a cycle)   :535-545 */

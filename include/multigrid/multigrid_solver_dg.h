@@ -5,6 +5,7 @@
 #ifndef MULTIGRID_MULTIGRID_SOLVER_DG_H
 #define MULTIGRID_MULTIGRID_SOLVER_DG_H
 
+#include <array>
 #include <utility>
 
 #include "laplace_operator_dg.h"
@@ -69,6 +70,14 @@ namespace multigrid
     unsigned int last_step() const { return last_step_; } // solver_control.last_step()
     // :429-441
     void vmult(DGVector<Number2> &dst, const DGVector<Number2> &src) const { check(mgb_dg_solver_vmult(s_, dst.begin(), src.begin())); }
+    // :445-527: the preconditioner call of a CG solver with merged vector operations
+    std::array<Number2, 2>
+    vmult_with_residual_update(DGVector<Number2> &residual, DGVector<Number2> &update, const Number2 factor) const
+    {
+      std::array<Number2, 2> results;
+      check(mgb_dg_solver_vmult_with_residual_update(s_, residual.begin(), update.begin(), factor, results.data()));
+      return results;
+    }
     // :328-366
     double
     compute_l2_error() const

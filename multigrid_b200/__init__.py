@@ -195,6 +195,7 @@ SYMBOLS = {
     "mgb_dg_solver_solve_cg": (_i, [_vp, _d, _dp, _dp, C.POINTER(_u)]),
     "mgb_dg_solver_residual_history": (_i, [_vp, _dp, _i, _ip]),
     "mgb_dg_solver_vmult": (_i, [_vp, _vp, _vp]),
+    "mgb_dg_solver_vmult_with_residual_update": (_i, [_vp, _vp, _vp, _d, _dp]),
     "mgb_dg_solver_l2_error": (_i, [_vp, _dp]),
     "mgb_dg_solver_vector": (_i, [_vp, _i, C.POINTER(_vp)]),
     "mgb_dg_solver_get_solution": (_i, [_vp, _vp]),
@@ -212,6 +213,7 @@ SYMBOLS = {
     "mgb_dg_plain_solver_solve_cg": (_i, [_vp, _d, _dp, _dp, C.POINTER(_u)]),
     "mgb_dg_plain_solver_residual_history": (_i, [_vp, _dp, _i, _ip]),
     "mgb_dg_plain_solver_vmult": (_i, [_vp, _vp, _vp]),
+    "mgb_dg_plain_solver_vmult_with_residual_update": (_i, [_vp, _vp, _vp, _d, _dp]),
     "mgb_dg_plain_solver_l2_error": (_i, [_vp, _dp]),
     "mgb_dg_plain_solver_vector": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
     "mgb_dg_plain_solver_get_vector": (_i, [_vp, _i, _i, _vp]),
@@ -967,6 +969,18 @@ class MultigridSolverDG:
         _check(lib().mgb_dg_solver_vmult(self.h, C.c_void_p(dst.data_ptr()), C.c_void_p(src.data_ptr())))
         self.sync()
 
+    def vmult_with_residual_update(self, residual, update, factor):
+        """the preconditioner call of CG with merged vector operations (double device tensors, both updated in place)
+        -> (update_new . residual_new, update_new . (factor * update_old))"""
+        import torch
+        assert residual.dtype == torch.float64 and update.dtype == torch.float64
+        assert residual.numel() == update.numel() == self.n_dofs()
+        torch.cuda.synchronize(self.device)
+        out = np.zeros(2)
+        _check(lib().mgb_dg_solver_vmult_with_residual_update(self.h, C.c_void_p(residual.data_ptr()), C.c_void_p(update.data_ptr()),
+                                                   float(factor), out.ctypes.data_as(_dp)))
+        return out[0], out[1]
+
     def compute_l2_error(self):
         e = C.c_double()
         _check(lib().mgb_dg_solver_l2_error(self.h, C.byref(e)))
@@ -1115,6 +1129,18 @@ class MultigridSolverDGPlain:
         """dst (level from_level - 1) = or += P^T src (level from_level), float device tensors"""
         self._transfer(lib().mgb_dg_plain_solver_restrict, from_level, dst, src, self.level_n_dofs(from_level - 1),
                        self.level_n_dofs(from_level), add)
+
+    def vmult_with_residual_update(self, residual, update, factor):
+        """the preconditioner call of CG with merged vector operations (double device tensors, both updated in place)
+        -> (update_new . residual_new, update_new . (factor * update_old))"""
+        import torch
+        assert residual.dtype == torch.float64 and update.dtype == torch.float64
+        assert residual.numel() == update.numel() == self.n_dofs()
+        torch.cuda.synchronize(self.device)
+        out = np.zeros(2)
+        _check(lib().mgb_dg_plain_solver_vmult_with_residual_update(self.h, C.c_void_p(residual.data_ptr()), C.c_void_p(update.data_ptr()),
+                                                   float(factor), out.ctypes.data_as(_dp)))
+        return out[0], out[1]
 
     def compute_l2_error(self):
         e = C.c_double()

@@ -1508,6 +1508,14 @@ extern "C"
   }
 
   int
+  mgb_dg_solver_vmult_with_residual_update(mgb_dg_solver h, double *residual, double *update, double factor, double results[2])
+  {
+    DG_TRY
+    DGS(h).vmult_with_residual_update(residual, update, factor, results);
+    DG_CATCH
+  }
+
+  int
   mgb_dg_solver_l2_error(mgb_dg_solver h, double *error)
   {
     DG_TRY
@@ -1690,6 +1698,15 @@ extern "C"
   {
     DG_TRY
     DGP(h).vmult(dst, src);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_plain_solver_vmult_with_residual_update(mgb_dg_plain_solver h, double *residual, double *update, double factor,
+                                                 double results[2])
+  {
+    DG_TRY
+    DGP(h).vmult_with_residual_update(residual, update, factor, results);
     DG_CATCH
   }
 

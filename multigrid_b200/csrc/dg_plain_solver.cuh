@@ -313,6 +313,19 @@ namespace mgb
       op.foreach (N, [=] __device__(size_t i) { dst[i] = (double)upd[i]; });
     }
 
+    // :340-427
+    void
+    vmult_with_residual_update(double *residual, double *update, const double factor, double results[2])
+    {
+      dg_vmult_with_residual_update(
+        *ops.back(), N, residual, update, factor, defect.back(),
+        [&]() -> const float * {
+          v_cycle(n_levels - 1);
+          return solution_update.back();
+        },
+        results);
+    }
+
     void
     solve_cg(const double tolerance, double *iterations_estimate, double *reduction_rate, unsigned int *n_iterations)
     {

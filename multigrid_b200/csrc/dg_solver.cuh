@@ -292,6 +292,41 @@ namespace mgb
     return it;
   }
 
+  // vmult_with_residual_update of the two DG solvers (multigrid_solver_dg.h:445-527, multigrid_solver_dg_plain.h:340-427),
+  // the preconditioner call of a CG solver with merged vector operations: defect = residual + factor * update in float,
+  // one cycle, then residual += factor * update, update = M^-1 defect and the two sums
+  // {update_new . residual_new, update_new . (factor * update_old)} in the same sweep
+  inline void
+  dg_vmult_with_residual_update(DGOperator &op, const size_t N, double *residual, double *update, const double factor,
+                                float *def, const std::function<const float *()> &cycle, double results[2])
+  {
+    if (factor != 0.)
+      op.foreach (N, [=] __device__(size_t i) { def[i] = (float)(residual[i] + factor * update[i]); });
+    else
+      op.foreach (N, [=] __device__(size_t i) { def[i] = (float)residual[i]; });
+    const float *mg = cycle();
+    double       r[2];
+    if (factor != 0.)
+      op.sums<2>(r, [=] __device__(size_t i, double *acc) {
+        const double m = (double)mg[i], u = update[i] * factor, res = residual[i] + u;
+        acc[0] += m * res;
+        acc[1] += m * u;
+        residual[i] = res;
+        update[i]   = m;
+      });
+    else
+      {
+        op.sums<2>(r, [=] __device__(size_t i, double *acc) {
+          const double m = (double)mg[i];
+          acc[0] += m * residual[i];
+          update[i] = m;
+        });
+        r[1] = r[0];
+      }
+    results[0] = r[0];
+    results[1] = r[1];
+  }
+
   struct DGMultigridSolver
   {
     mgb_dg_solver_options opt;
@@ -497,6 +532,19 @@ namespace mgb
       dg_v_cycle();
       const float *upd = solution_update_dg;
       op->foreach (N, [=] __device__(size_t i) { dst[i] = (double)upd[i]; });
+    }
+
+    // multigrid_solver_dg.h:445-527
+    void
+    vmult_with_residual_update(double *residual, double *update, const double factor, double results[2])
+    {
+      dg_vmult_with_residual_update(
+        *op, N, residual, update, factor, defect_dg,
+        [&]() -> const float * {
+          dg_v_cycle();
+          return solution_update_dg;
+        },
+        results);
     }
 
     // multigrid_solver_dg.h:410-424: deal.II SolverCG with ReductionControl(100, 1e-16, tolerance), zero start

@@ -9,6 +9,7 @@
 #include "multigrid/laplace_operator_adaptive.h"
 #include "multigrid/laplace_operator_dg.h"
 #include "multigrid/multigrid_solver_dg.h"
+#include "multigrid/multigrid_solver_dg_plain.h"
 #include "multigrid/multigrid_solver.h"
 
 // A third problem, defined only here (the Function<dim> objects a driver of the reference would write):
@@ -195,6 +196,29 @@ main(int argc, char **argv)
       const std::pair<double, double>                         dg_cg = dg_solver.solve_cg(1e-3);
       std::printf("dg_cg_its %u dg_cg_rate %.6e dg_l2 %.6e\n", dg_solver.last_step(), dg_cg.second,
                   dg_solver.compute_l2_error());
+
+      // pure DG h-multigrid as poisson_dg_plain/program.cc:232-263 on the same mesh, FE_DGQArbitraryNodes (type 2); one
+      // preconditioned CG step by hand through vmult_with_residual_update (residual r = b - A 0 = b is not available
+      // to a driver, so the step runs on r = 1: update = M^-1 r, results[0] = r . M^-1 r > 0)
+      multigrid::MultigridSolverDGPlain<3, degree, float, double, 2> plain(dmesh, 3, 3, 1);
+      const std::pair<double, double>                                 plain_cg = plain.solve_cg(1e-3);
+      std::printf("plain_levels %u plain_cg_its %u plain_cg_rate %.6e plain_l2 %.6e\n", plain.n_levels(), plain.last_step(),
+                  plain_cg.second, plain.compute_l2_error());
+      {
+        multigrid::DGVector<double> res, upd;
+        dg.initialize_dof_vector(res);
+        dg.initialize_dof_vector(upd);
+        std::vector<double> ones(plain.m(), 1.0), zeros(plain.m(), 0.0);
+        res.import_from_host(ones);
+        upd.import_from_host(zeros);
+        const std::array<double, 2> ip = plain.vmult_with_residual_update(res, upd, 0.);
+        plain.synchronize();
+        const std::vector<double> m = upd.export_to_host();
+        double                    s = 0;
+        for (double v : m)
+          s += v;
+        std::printf("plain_rMr %.10e plain_rMr_check %.10e\n", ip[0], s);
+      }
     }
   catch (const std::exception &e)
     {

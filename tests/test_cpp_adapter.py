@@ -106,3 +106,12 @@ def test_example_driver_matches_oracle(mgb, orc):
     assert int(out["dg_cg_its"]) == ds.last_step
     assert abs(float(out["dg_cg_rate"]) - rate_dg) <= 3e-2 * rate_dg
     assert abs(float(out["dg_l2"]) - ds.compute_l2_error()) <= 1e-3 * ds.compute_l2_error()
+    dp = orc.MultigridSolverDGPlain(4, (1, 1, 1), 2, basis=orc.DG_BASIS_GAUSS)
+    _, rate_p, _ = dp.solve_cg(1e-3)
+    assert int(out["plain_levels"]) == 3 and int(out["plain_cg_its"]) == dp.last_step
+    assert abs(float(out["plain_cg_rate"]) - rate_p) <= 3e-2 * rate_p
+    assert abs(float(out["plain_l2"]) - dp.compute_l2_error()) <= 1e-3 * dp.compute_l2_error()
+    ones = np.ones(dp.n_dofs())
+    rMr = ones @ dp.vmult(ones)
+    assert abs(float(out["plain_rMr"]) - rMr) <= 1e-4 * rMr
+    assert abs(float(out["plain_rMr"]) - float(out["plain_rMr_check"])) <= 1e-9 * rMr

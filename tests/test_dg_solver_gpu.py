@@ -100,3 +100,22 @@ def test_l2_error_at_scale(mgb, torch):
         errs.append(g.compute_l2_error())
         assert g.last_step <= 12
     assert 24 < errs[0] / errs[1] < 40
+
+
+@pytest.mark.parametrize("factor", [0., -0.37])
+def test_vmult_with_residual_update(mgb, torch, factor):
+    """multigrid_solver_dg.h:445-527: the merged call equals its parts -- cycle on residual + factor * update, the two vector updates, the two sums"""
+    g = mgb.MultigridSolverDG(2, (1, 1, 1), 2)
+    rng = np.random.default_rng(11)
+    res0, upd0 = rng.standard_normal(g.n_dofs()), rng.standard_normal(g.n_dofs())
+    res, upd = torch.tensor(res0, device="cuda"), torch.tensor(upd0, device="cuda")
+    a, b = g.vmult_with_residual_update(res, upd, factor)
+    new_res = res0 + factor * upd0
+    mg = torch.zeros_like(res)
+    g.vmult(mg, torch.tensor(new_res, device="cuda"))
+    mg = mg.cpu().numpy()
+    assert np.abs(res.cpu().numpy() - new_res).max() <= 1e-14 * np.abs(new_res).max()
+    assert np.abs(upd.cpu().numpy() - mg).max() <= 1e-6 * np.abs(mg).max()
+    assert abs(a - mg @ new_res) <= 1e-6 * abs(mg @ new_res)
+    expect_b = mg @ (factor * upd0) if factor != 0. else mg @ new_res
+    assert abs(b - expect_b) <= 1e-6 * abs(mg @ new_res)
