@@ -148,6 +148,27 @@ int mgb_solver_set_coefficient_values(mgb_solver s, int level, const double *c_h
 int mgb_solver_reinit_smoothers(mgb_solver s);
 int mgb_solver_set_rhs_values(mgb_solver s, int level, const double *f_host, const double *u_boundary_host);
 int mgb_solver_set_exact_solution_values(mgb_solver s, int level, const double *u_host);
+
+/* ---- Minimal surface problem: minimal_surface/program.cc, here in 3-D on the solver's mesh, one GPU.
+ * Newton's method with line search for -div(grad u / sqrt(1 + |grad u|^2)) = 0 with Dirichlet data.  One step
+ * (LaplaceProblem::solve(first_time), :412-572): the solution is carried to every level by the FE_Q restriction
+ * matrices (:417-456); MinimalSurfaceOperator::evaluate_coefficient (:117-163) fills the merged coefficient
+ * JxW J^-1 T J^-T on every level from the gradient of that vector -- T = I the first time, else the Newton tensor
+ * (I - g g^T / (1 + |g|^2)) / sqrt(1 + |g|^2), all six entries per quadrature point; diagonals and Chebyshev
+ * smoothers are rebuilt (:458-486; create the solver with degree_pre = degree_post = 2 for the reference's setting);
+ * the update solves A du = r by CG with the V-cycle, ReductionControl(m(), 1e-13, 1e-4), r the nonlinear residual of
+ * MinimalSurfaceOperator::compute_residual (:169-198); the step length is halved until the residual norm falls
+ * (:543-557).  The iterate is the solver's finest-level solution vector (mgb_solver_get_solution / mgb_solver_vector). */
+/* interpolate_boundary_values :396-408: Dirichlet values from u_host (one value per DoF of the finest level, library
+ * numbering; only boundary entries are used) or, if NULL, from the analytic solution of options.problem; the iterate
+ * is set to these values on the boundary and to zero inside                                                        */
+int mgb_solver_minimal_surface_set_boundary_values(mgb_solver s, const double *u_host);
+/* info = {initial residual norm, final residual norm, CG iterations, line search halvings, step length}            */
+int mgb_solver_minimal_surface_step(mgb_solver s, int first_time, double info[5]);
+/* compute_residual(dst, u, first_time) :169-198 on double device vectors of the finest level; *norm = |dst|_2      */
+int mgb_solver_minimal_surface_residual(mgb_solver s, double *dst, const double *u, int first_time, double *norm);
+/* coefficient_solutions[level] of the last step (float device vector of the level), :417-456                       */
+int mgb_solver_minimal_surface_level_solution(mgb_solver s, int level, float **dev_ptr);
 /* MultigridSolver::do_matvec / do_matvec_smoother         multigrid_solver.h:624-637 */
 int mgb_solver_do_matvec(mgb_solver s);
 int mgb_solver_do_matvec_smoother(mgb_solver s);

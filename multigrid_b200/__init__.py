@@ -121,6 +121,10 @@ SYMBOLS = {
     "mgb_solver_reinit_smoothers": (_i, [_vp]),
     "mgb_solver_set_rhs_values": (_i, [_vp, _i, _dp, _dp]),
     "mgb_solver_set_exact_solution_values": (_i, [_vp, _i, _dp]),
+    "mgb_solver_minimal_surface_set_boundary_values": (_i, [_vp, _dp]),
+    "mgb_solver_minimal_surface_step": (_i, [_vp, _i, _dp]),
+    "mgb_solver_minimal_surface_residual": (_i, [_vp, _vp, _vp, _i, _dp]),
+    "mgb_solver_minimal_surface_level_solution": (_i, [_vp, _i, C.POINTER(_vp)]),
     "mgb_solver_do_matvec": (_i, [_vp]),
     "mgb_solver_do_matvec_smoother": (_i, [_vp]),
     "mgb_solver_timings": (_i, [_vp, _dp, _i]),
@@ -583,6 +587,50 @@ class MultigridSolver:
                 xq = self.quadrature_points(l)
                 u = np.ascontiguousarray(exact_solution(xq[:, 0], xq[:, 1], xq[:, 2]), dtype=np.float64)
                 _check(lib().mgb_solver_set_exact_solution_values(self.h, l, u.ctypes.data_as(_dp)))
+
+    # ---- minimal_surface/program.cc: Newton's method with line search on -div(grad u / sqrt(1 + |grad u|^2)) = 0
+    def minimal_surface_set_boundary_values(self, boundary_values=None):
+        """interpolate_boundary_values (:396-408): a callable g(x, y, z) evaluated at the support points of the finest
+        level, or None for the analytic solution of `problem`; the iterate becomes g on the boundary, zero inside"""
+        g = None
+        if boundary_values is not None:
+            xs = self.support_points()
+            g = np.ascontiguousarray(boundary_values(xs[:, 0], xs[:, 1], xs[:, 2]), dtype=np.float64)
+        _check(lib().mgb_solver_minimal_surface_set_boundary_values(self.h, g.ctypes.data_as(_dp) if g is not None else None))
+
+    def minimal_surface_step(self, first_time):
+        """LaplaceProblem::solve(first_time) (:412-572): coefficients from the iterate on every level, smoothers, CG with
+        the V-cycle on the linearised operator, line search"""
+        info = np.zeros(5)
+        _check(lib().mgb_solver_minimal_surface_step(self.h, int(first_time), info.ctypes.data_as(_dp)))
+        return dict(initial_residual=info[0], final_residual=info[1], linear_iterations=int(info[2]),
+                    line_search_steps=int(info[3]), step_length=info[4])
+
+    def minimal_surface_solve(self, max_steps=100, tolerance=1e-12):
+        """the inner loop of LaplaceProblem::run (:652-659) -> the list of the steps' records"""
+        steps = []
+        for it in range(max_steps):
+            steps.append(self.minimal_surface_step(it == 0))
+            if steps[-1]["final_residual"] < tolerance:
+                break
+        return steps
+
+    def minimal_surface_residual(self, dst, u, first_time=False):
+        """MinimalSurfaceOperator::compute_residual (:169-198) on double device tensors; returns |dst|_2"""
+        import torch
+        assert dst.dtype == torch.float64 and u.dtype == torch.float64 and dst.numel() == u.numel() == self.n_dofs()
+        self._torch_sync()
+        norm = C.c_double()
+        _check(lib().mgb_solver_minimal_surface_residual(self.h, _ptr(dst), _ptr(u), int(first_time), C.byref(norm)))
+        return norm.value
+
+    def minimal_surface_level_solution(self, level):
+        """host copy of coefficient_solutions[level] (:417-456) of the last step, library numbering"""
+        p = C.c_void_p()
+        _check(lib().mgb_solver_minimal_surface_level_solution(self.h, self._l(level), C.byref(p)))
+        out = np.zeros(self.n_dofs(level), dtype=np.float32)
+        _check(lib().mgb_copy_to_host(self.h, C.c_void_p(out.ctypes.data), p, out.nbytes))
+        return out
 
     def vmult_with_residual_update(self, residual, update, factor):
         """multigrid_solver.h:516-619: residual += factor update; update = V-cycle(residual); returns

@@ -19,6 +19,8 @@ namespace mgb
     std::vector<double> M1;      // sum_q S[q][i] w_q S[q][j]      (reference-cell 1-D mass)
     std::vector<double> K1;      // sum_q G[q][i] w_q G[q][j]      (reference-cell 1-D stiffness)
     std::vector<double> P1;      // P1[f*n+i] = phi_i(child support point f), f = 0..2p
+    std::vector<double> R1;      // R1[i*(2p+1)+f]: value at coarse support point i of the fine function on the two children
+                                 // (FE_Q restriction matrices = interpolation; the child containing the point contributes)
   };
 
   namespace detail
@@ -199,6 +201,13 @@ namespace mgb
         const ld xf = f <= p ? 0.5L * xl[f] : 0.5L + 0.5L * xl[f - p];
         for (int i = 0; i < n; ++i)
           b.P1[f * n + i] = (double)lag(xl, i, xf);
+      }
+    b.R1.assign(n * (2 * p + 1), 0.);
+    for (int i = 0; i < n; ++i)
+      {
+        const int child = xl[i] <= 0.5L ? 0 : 1;
+        for (int m = 0; m < n; ++m)
+          b.R1[i * (2 * p + 1) + child * p + m] = (double)lag(xl, m, 2 * xl[i] - child);
       }
     return b;
   }

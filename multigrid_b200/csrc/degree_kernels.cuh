@@ -27,6 +27,7 @@ namespace mgb
     float  Sf[n * n], Df[n * n], M1f[n * n], K1f[n * n], wf[n];
     double P1[(2 * n - 1) * n];
     float  P1f[(2 * n - 1) * n];
+    double R1[n * (2 * n - 1)];
   };
 
   __constant__ ConstTables<MGB_P + 1> ctab;
@@ -635,6 +636,158 @@ namespace mgb
     k_mapped_coefficient<p, T><<<A.L.n_cells, n3 < 128 ? ((n3 + 31) / 32) * 32 : 128, 0, stream>>>(A);
   }
 
+  // MinimalSurfaceOperator::evaluate_coefficient(first_time, solution) (minimal_surface/program.cc:117-163): the merged
+  // coefficient JxW J^-1 T J^-T from the gradient g of `u` at the quadrature points (all entries of u are read, Dirichlet
+  // values included): mode 0 T = I; mode 1 T = (I - g g^T / (1 + |g|^2)) / sqrt(1 + |g|^2), the Newton linearisation of
+  // the minimal surface operator; mode 2 T = I / sqrt(1 + |g|^2), the flux of the nonlinear residual (:188-192)
+  template <int p, typename T>
+  __global__ void
+  k_solution_coefficient(const SolutionCoefArgs<T> A)
+  {
+    constexpr int     n = p + 1, n3 = n * n * n;
+    __shared__ double X[3 * n3];
+    __shared__ double U[n3];
+    const uint32_t    cell = blockIdx.x;
+    int               cx, cy, cz;
+    cell_coords(A.L, cell, cx, cy, cz);
+    cell_support_points<p>(A.geom, A.L, cx, cy, cz, X);
+    for (int l = threadIdx.x; l < n3; l += blockDim.x)
+      {
+        bool           con;
+        const uint32_t d = cell_dof(A.L, cell, l % n, (l / n) % n, l / (n * n), con);
+        U[l]             = (double)A.u[d];
+      }
+    __syncthreads();
+    for (int q = threadIdx.x; q < n3; q += blockDim.x)
+      {
+        const int q0 = q % n, q1 = (q / n) % n, q2 = q / (n * n);
+        double    J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, gr[3] = {0, 0, 0};
+        for (int k = 0; k < n; ++k)
+          for (int j = 0; j < n; ++j)
+            {
+              const double s2 = ctab.S[q2 * n + k], g2 = ctab.G[q2 * n + k];
+              const double s1 = ctab.S[q1 * n + j], g1 = ctab.G[q1 * n + j];
+              for (int i = 0; i < n; ++i)
+                {
+                  const double s0 = ctab.S[q0 * n + i], g0 = ctab.G[q0 * n + i];
+                  const int    l  = (k * n + j) * n + i;
+                  const double d0 = g0 * s1 * s2, d1 = s0 * g1 * s2, d2 = s0 * s1 * g2;
+                  for (int d = 0; d < 3; ++d)
+                    {
+                      const double Xd = X[d * n3 + l];
+                      J[d][0] += Xd * d0;
+                      J[d][1] += Xd * d1;
+                      J[d][2] += Xd * d2;
+                    }
+                  gr[0] += U[l] * d0;
+                  gr[1] += U[l] * d1;
+                  gr[2] += U[l] * d2;
+                }
+            }
+        const double det = det3(J);
+        double       I[3][3]; // I[e][d] = d xi_e / d x_d
+        I[0][0] = (J[1][1] * J[2][2] - J[1][2] * J[2][1]) / det;
+        I[0][1] = (J[0][2] * J[2][1] - J[0][1] * J[2][2]) / det;
+        I[0][2] = (J[0][1] * J[1][2] - J[0][2] * J[1][1]) / det;
+        I[1][0] = (J[1][2] * J[2][0] - J[1][0] * J[2][2]) / det;
+        I[1][1] = (J[0][0] * J[2][2] - J[0][2] * J[2][0]) / det;
+        I[1][2] = (J[0][2] * J[1][0] - J[0][0] * J[1][2]) / det;
+        I[2][0] = (J[1][0] * J[2][1] - J[1][1] * J[2][0]) / det;
+        I[2][1] = (J[0][1] * J[2][0] - J[0][0] * J[2][1]) / det;
+        I[2][2] = (J[0][0] * J[1][1] - J[0][1] * J[1][0]) / det;
+        double g[3];
+        for (int d = 0; d < 3; ++d)
+          g[d] = I[0][d] * gr[0] + I[1][d] * gr[1] + I[2][d] * gr[2];
+        const double g2n = g[0] * g[0] + g[1] * g[1] + g[2] * g[2];
+        const double isq = A.mode == 0 ? 1. : 1. / sqrt(1. + g2n);
+        const double f   = ctab.w[q0] * ctab.w[q1] * ctab.w[q2] * fabs(det);
+        // a_e = J^-1 g (row e of I times g): J^-1 (g g^T) J^-T = a a^T
+        double a[3] = {0, 0, 0};
+        if (A.mode == 1)
+          for (int e = 0; e < 3; ++e)
+            a[e] = I[e][0] * g[0] + I[e][1] * g[1] + I[e][2] * g[2];
+        auto m = [&](const int e, const int h) {
+          return f * isq * (I[e][0] * I[h][0] + I[e][1] * I[h][1] + I[e][2] * I[h][2] - a[e] * a[h] / (1. + g2n));
+        };
+        T *c      = A.coef_q + (size_t)cell * 6 * n3 + q;
+        c[0 * n3] = (T)m(0, 0);
+        c[1 * n3] = (T)m(1, 1);
+        c[2 * n3] = (T)m(2, 2);
+        c[3 * n3] = (T)m(0, 1);
+        c[4 * n3] = (T)m(0, 2);
+        c[5 * n3] = (T)m(1, 2);
+      }
+  }
+
+  template <int p, typename T>
+  void
+  launch_solution_coefficient(const SolutionCoefArgs<T> &A, cudaStream_t stream)
+  {
+    constexpr int n3 = (p + 1) * (p + 1) * (p + 1);
+    k_solution_coefficient<p, T><<<A.L.n_cells, n3 < 128 ? ((n3 + 31) / 32) * 32 : 128, 0, stream>>>(A);
+  }
+
+  // The FE_Q restriction matrices applied to a level vector (minimal_surface/program.cc:417-456): the coarse vector
+  // interpolates the fine function in the coarse support points.  One block per coarse cell: the (2p+1)^3 fine values of
+  // its eight children, R1 along z, y, x, all (p+1)^3 coarse entries written (entries shared with a neighbour get the
+  // same value from both: R1 selects the face value in the normal direction).
+  template <int p>
+  __global__ void
+  k_interpolate_to_coarse(const TransferArgs<float> A)
+  {
+    constexpr int    n = p + 1, nf = 2 * p + 1;
+    __shared__ float buf0[nf * nf * nf], buf1[n * nf * nf];
+    const int        tid = threadIdx.x, nt = blockDim.x;
+    const uint32_t   ccell = blockIdx.x;
+    int              cx, cy, cz;
+    cell_coords(A.coarse, ccell, cx, cy, cz);
+    for (int l = tid; l < nf * nf * nf; l += nt)
+      {
+        const int      I = l % nf, J = (l / nf) % nf, K = l / (nf * nf);
+        const int      fx = 2 * cx + (I > p), fy = 2 * cy + (J > p), fz = 2 * cz + (K > p);
+        const uint32_t fcell = cell_number(A.fine, fx, fy, fz);
+        bool           c;
+        const uint32_t d = cell_dof(A.fine, fcell, I - (I > p) * p, J - (J > p) * p, K - (K > p) * p, c);
+        buf0[l]          = A.src[d];
+      }
+    __syncthreads();
+    for (int l = tid; l < n * nf * nf; l += nt) // z
+      {
+        const int IJ = l % (nf * nf), k = l / (nf * nf);
+        double    s  = 0;
+        for (int K = 0; K < nf; ++K)
+          s += ctab.R1[k * nf + K] * (double)buf0[K * nf * nf + IJ];
+        buf1[l] = (float)s;
+      }
+    __syncthreads();
+    for (int l = tid; l < n * n * nf; l += nt) // y: buf0[(k n + j) nf + I]
+      {
+        const int I = l % nf, j = (l / nf) % n, k = l / (nf * n);
+        double    s = 0;
+        for (int Jf = 0; Jf < nf; ++Jf)
+          s += ctab.R1[j * nf + Jf] * (double)buf1[(k * nf + Jf) * nf + I];
+        buf0[l] = (float)s;
+      }
+    __syncthreads();
+    for (int l = tid; l < n * n * n; l += nt) // x
+      {
+        const int i = l % n, kj = l / n;
+        double    s = 0;
+        for (int If = 0; If < nf; ++If)
+          s += ctab.R1[i * nf + If] * (double)buf0[kj * nf + If];
+        bool           c;
+        const uint32_t d = cell_dof(A.coarse, ccell, i, kj % n, kj / n, c);
+        A.dst[d]         = (float)s;
+      }
+  }
+
+  template <int p>
+  void
+  launch_interpolate_to_coarse(const TransferArgs<float> &A, cudaStream_t stream)
+  {
+    k_interpolate_to_coarse<p><<<A.coarse.n_cells, 128, 0, stream>>>(A);
+  }
+
   // ------------------------------------------------------------------ right-hand side values
   template <int p>
   __global__ void
@@ -859,6 +1012,7 @@ namespace mgb
       {
         h->P1[i]  = b.P1[i];
         h->P1f[i] = (float)b.P1[i];
+        h->R1[i]  = b.R1[i];
       }
     cudaMemcpyToSymbol(ctab, h, sizeof(*h));
     delete h;

@@ -101,6 +101,18 @@ namespace mgb
     int       fn_id;
   };
 
+  // merged coefficient from the gradient of a level vector (MinimalSurfaceOperator::evaluate_coefficient,
+  // minimal_surface/program.cc:117-163); mode 0 identity tensor, 1 Newton linearisation, 2 residual flux
+  template <typename T>
+  struct SolutionCoefArgs
+  {
+    LevelDesc L;
+    Geometry  geom;
+    T        *coef_q;
+    const T  *u;
+    int       mode;
+  };
+
   struct DegreeKernels
   {
     void (*init)(const Basis &);
@@ -119,6 +131,9 @@ namespace mgb
     void (*rhs_values)(const RhsArgs &, cudaStream_t);
     void (*quadrature_points)(const PointsArgs &, cudaStream_t);
     void (*l2_error)(const ErrorArgs &, cudaStream_t);
+    void (*solution_coefficient_f)(const SolutionCoefArgs<float> &, cudaStream_t);
+    void (*solution_coefficient_d)(const SolutionCoefArgs<double> &, cudaStream_t);
+    void (*interpolate_to_coarse)(const TransferArgs<float> &, cudaStream_t);
   };
 
   const DegreeKernels &degree_kernels(int p);

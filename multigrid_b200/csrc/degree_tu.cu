@@ -28,7 +28,10 @@ namespace mgb
                                     &launch_coefficient<MGB_P, double>,
                                     &launch_rhs_values<MGB_P>,
                                     &launch_quadrature_points<MGB_P>,
-                                    &launch_l2_error<MGB_P>};
+                                    &launch_l2_error<MGB_P>,
+                                    &launch_solution_coefficient<MGB_P, float>,
+                                    &launch_solution_coefficient<MGB_P, double>,
+                                    &launch_interpolate_to_coarse<MGB_P>};
     return k;
   }
 } // namespace mgb

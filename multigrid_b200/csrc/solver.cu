@@ -1171,6 +1171,29 @@ namespace mgb
       });
     }
 
+    // MinimalSurfaceOperator::evaluate_coefficient(first_time, solution) (minimal_surface/program.cc:117-163): the merged
+    // coefficient from the gradient of the level vector u (mode 0 identity, 1 Newton linearisation, 2 residual flux)
+    void
+    evaluate_solution_coefficient(const Geometry &geom, const int mode, const T *u)
+    {
+      const LevelDesc &L  = level->d;
+      const size_t     nc = (size_t)L.n_cells * 6 * L.n * L.n * L.n;
+      cartesian           = false;
+      if (coef_q.n != nc)
+        coef_q.alloc(nc, ctx->stream);
+      SolutionCoefArgs<T> A;
+      A.L      = L;
+      A.geom   = geom;
+      A.coef_q = coef_q.p;
+      A.u      = u;
+      A.mode   = mode;
+      if (sizeof(T) == 8)
+        dk->solution_coefficient_d(reinterpret_cast<const SolutionCoefArgs<double> &>(A), ctx->stream);
+      else
+        dk->solution_coefficient_f(reinterpret_cast<const SolutionCoefArgs<float> &>(A), ctx->stream);
+      ctx->check_launch();
+    }
+
     bool use_cartesian() const
     {
       // the streaming kernel is compiled for the default tile width of the degree
@@ -2437,9 +2460,143 @@ namespace mgb
       return {{sums[0], sums[1]}};
     }
 
+    // ---- minimal_surface/program.cc: Newton's method with line search for -div(grad u / sqrt(1 + |grad u|^2)) = 0
+    //      with Dirichlet data; the linear systems by CG with the V-cycle on the linearised operator
+    //      (LaplaceProblem::solve, :412-572).  Here in 3-D on the solver's mesh; one GPU.
+    std::vector<std::unique_ptr<DVec<float>>> coefficient_solutions;
+    std::unique_ptr<LaplaceOperator<double>>  ms_residual_op;
+    DVec<double>                              ms_search, ms_tentative, ms_rhs, ms_current;
+
+    void
+    ms_require_one_gpu() const
+    {
+      if (ctx.n_ranks > 1)
+        throw std::runtime_error("the minimal surface solver runs on one GPU");
+    }
+
+    // interpolate_boundary_values (:396-408): the Dirichlet data in the boundary entries of `solution`, zero inside.
+    // u_host: one value per DoF of the finest level in library numbering (only the Dirichlet entries are used), or
+    // null for the solver's analytic solution
+    void
+    ms_set_boundary_values(const double *u_host)
+    {
+      ms_require_one_gpu();
+      const int    L = n_levels - 1;
+      const size_t N = levels[L]->d.n_dofs;
+      if (u_host)
+        {
+          stage_values(u_host, N);
+          double         *bc    = bc_values[L]->p;
+          const double   *v     = caller_values.p;
+          const uint32_t *clist = levels[L]->constrained.p;
+          foreach (ctx, levels[L]->constrained.n, [=] __device__(size_t i) { bc[clist[i]] = v[clist[i]]; });
+        }
+      MGB_CUDA_CHECK(cudaMemsetAsync(solution[L]->p, 0, N * sizeof(double), ctx.stream));
+      set_boundary_values(L, false);
+      if (!ms_residual_op)
+        {
+          ms_residual_op.reset(new LaplaceOperator<double>());
+          ms_residual_op->initialize(ctx, *levels[L], basis, FN_ONE, geom);
+          ms_residual_op->kernel = MGB_KERNEL_GENERAL;
+          coefficient_solutions.clear();
+          for (int l = 0; l < n_levels; ++l)
+            {
+              coefficient_solutions.emplace_back(new DVec<float>());
+              coefficient_solutions[l]->alloc(levels[l]->d.n_dofs, ctx.stream);
+            }
+          for (DVec<double> *v : {&ms_search, &ms_tentative, &ms_rhs, &ms_current})
+            v->alloc(N, ctx.stream);
+        }
+      ctx.sync();
+    }
+
+    // MinimalSurfaceOperator::compute_residual (:169-198): dst_i = -(grad phi_i, grad u / sqrt(1 + |grad u|^2)) on the
+    // rows without Dirichlet condition (first_time: the Laplace residual); returns the l2 norm
+    double
+    ms_residual(double *dst, const double *u, const bool first_time)
+    {
+      const int    L = n_levels - 1;
+      const size_t N = levels[L]->d.n_dofs;
+      if (!ms_residual_op)
+        throw std::runtime_error("call mgb_solver_minimal_surface_set_boundary_values first");
+      ms_residual_op->evaluate_solution_coefficient(geom, first_time ? 0 : 2, u);
+      double *neg = residual[L]->p;
+      foreach (ctx, N, [=] __device__(size_t i) { neg[i] = -u[i]; });
+      MGB_CUDA_CHECK(cudaMemsetAsync(dst, 0, N * sizeof(double), ctx.stream));
+      ms_residual_op->apply(APPLY_ADD, dst, neg, nullptr, nullptr, 0, 0, 0, /*read_plain=*/true);
+      return std::sqrt(dot(ctx, dst, dst, levels[L]->owned()));
+    }
+
+    // LaplaceProblem::solve(first_time): info = {initial residual, final residual, linear iterations, line search
+    // steps, step length}
+    void
+    ms_newton_step(const bool first_time, double info[5])
+    {
+      ms_require_one_gpu();
+      if (!ms_residual_op)
+        throw std::runtime_error("call mgb_solver_minimal_surface_set_boundary_values first");
+      const int    L   = n_levels - 1;
+      const size_t N   = levels[L]->d.n_dofs;
+      double      *sol = solution[L]->p;
+      // the solution on every level: conversion to float, then the FE_Q restriction matrices level by level (:417-456)
+      convert(ctx, coefficient_solutions[L]->p, sol, N);
+      for (int l = L; l > 0; --l)
+        {
+          TransferArgs<float> A;
+          A.fine        = levels[l]->d;
+          A.coarse      = levels[l - 1]->d;
+          A.src         = coefficient_solutions[l]->p;
+          A.dst         = coefficient_solutions[l - 1]->p;
+          A.mode        = 0;
+          A.constrained = 0;
+          A.cz_begin = A.cz_end = A.f_shift = A.close_top = 0;
+          degree_kernels(opt.degree).interpolate_to_coarse(A, ctx.stream);
+          ctx.check_launch();
+        }
+      const int mode = first_time ? 0 : 1;
+      matrix_dp[L]->evaluate_solution_coefficient(geom, mode, sol);
+      for (int l = 0; l < n_levels; ++l)
+        matrix[l]->evaluate_solution_coefficient(geom, mode, coefficient_solutions[l]->p);
+      reinit_smoothers(); // diagonals, eigenvalue estimates (:458-486)
+      const double initial_residual_norm = ms_residual(ms_rhs.p, sol, first_time);
+      // SolverCG with ReductionControl(m(), 1e-13, 1e-4) from a zero start (:505-535); the solver works in solution / rhs
+      MGB_CUDA_CHECK(cudaMemcpyAsync(ms_current.p, sol, N * sizeof(double), cudaMemcpyDeviceToDevice, ctx.stream));
+      MGB_CUDA_CHECK(cudaMemcpyAsync(rhs[L]->p, ms_rhs.p, N * sizeof(double), cudaMemcpyDeviceToDevice, ctx.stream));
+      const auto cg = solve_cg((unsigned int)matrix_dp[L]->m_global(), 1e-13, 1e-4);
+      MGB_CUDA_CHECK(cudaMemcpyAsync(ms_search.p, sol, N * sizeof(double), cudaMemcpyDeviceToDevice, ctx.stream));
+      MGB_CUDA_CHECK(cudaMemcpyAsync(sol, ms_current.p, N * sizeof(double), cudaMemcpyDeviceToDevice, ctx.stream));
+      {
+        double         *sd    = ms_search.p;
+        const uint32_t *clist = levels[L]->constrained.p;
+        foreach (ctx, levels[L]->constrained.n, [=] __device__(size_t i) { sd[clist[i]] = 0.; }); // constraints.distribute
+      }
+      // line search (:543-557)
+      double       final_residual_norm = initial_residual_norm, alpha = 1.;
+      unsigned int n_steps             = 0;
+      while (n_steps < 100)
+        {
+          double       *tent = ms_tentative.p;
+          const double *sd   = ms_search.p;
+          const double  a    = alpha;
+          foreach (ctx, N, [=] __device__(size_t i) { tent[i] = sol[i] + a * sd[i]; });
+          final_residual_norm = ms_residual(ms_rhs.p, tent, false);
+          if (final_residual_norm < initial_residual_norm)
+            break;
+          alpha /= 2.;
+          ++n_steps;
+        }
+      MGB_CUDA_CHECK(cudaMemcpyAsync(sol, ms_tentative.p, N * sizeof(double), cudaMemcpyDeviceToDevice, ctx.stream));
+      ctx.sync();
+      info[0] = initial_residual_norm;
+      info[1] = final_residual_norm;
+      info[2] = cg.first;
+      info[3] = n_steps;
+      info[4] = alpha;
+    }
+
     // multigrid_solver.h:483-493 + deal.II SolverCG with ReductionControl(1000, 1e-16, 1e-9)
     std::pair<unsigned int, double>
-    solve_cg()
+    solve_cg(const unsigned int max_it = 1000, const double abs_tol = 1e-16, const double rel_tol = 1e-9)
     {
       if (smoothers_stale)
         throw std::runtime_error("the coefficient changed: call mgb_solver_reinit_smoothers before solving");
@@ -2474,7 +2631,7 @@ namespace mgb
       const double res0 = res;
       cg_history.push_back(res);
       unsigned int it = 0;
-      if (res > 1e-16)
+      if (res > abs_tol)
         {
           double gh = 0;
           // x += alpha d is postponed into the next direction update (which reads d anyway) or the final pass:
@@ -2522,7 +2679,7 @@ namespace mgb
               }
               res = std::sqrt(r2);
               cg_history.push_back(res);
-              if (res <= 1e-16 || res <= 1e-9 * res0 || it >= 1000)
+              if (res <= abs_tol || res <= rel_tol * res0 || it >= max_it)
                 break;
             }
           {
@@ -3034,6 +3191,47 @@ extern "C"
     MGB_TRY
     MultigridSolver &m = S(s);
     m.set_exact_solution_values(check_level(m, level), u_host);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_minimal_surface_set_boundary_values(mgb_solver s, const double *u_host)
+  {
+    MGB_TRY
+    S(s).ms_set_boundary_values(u_host);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_minimal_surface_step(mgb_solver s, int first_time, double info[5])
+  {
+    MGB_TRY
+    S(s).ms_newton_step(first_time != 0, info);
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_minimal_surface_residual(mgb_solver s, double *dst, const double *u, int first_time, double *norm)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    m.ms_require_one_gpu();
+    const double r = m.ms_residual(dst, u, first_time != 0);
+    m.ctx.sync();
+    if (norm)
+      *norm = r;
+    MGB_CATCH
+  }
+
+  int
+  mgb_solver_minimal_surface_level_solution(mgb_solver s, int level, float **dev_ptr)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    check_level(m, level);
+    if ((int)m.coefficient_solutions.size() != m.n_levels)
+      throw std::runtime_error("call mgb_solver_minimal_surface_set_boundary_values first");
+    *dev_ptr = m.coefficient_solutions[level]->p;
     MGB_CATCH
   }
 

@@ -412,6 +412,102 @@ namespace orc
             coef_q[(cell * nq + q) * 6 + e] *= (T)c[cell * nq + q];
     }
 
+    // out[q2][q1][q0] = sum_kji M2[q2][k] M1[q1][j] M0[q0][i] in[k][j][i]; plain loops (set-up code)
+    static void
+    tensor3(const int n, const double *M0, const double *M1, const double *M2, const double *in, double *out)
+    {
+      vector<double> a(n * n * n), c(n * n * n);
+      for (int k = 0; k < n; ++k)
+        for (int j = 0; j < n; ++j)
+          for (int q0 = 0; q0 < n; ++q0)
+            {
+              double s = 0;
+              for (int i = 0; i < n; ++i)
+                s += M0[q0 * n + i] * in[(k * n + j) * n + i];
+              a[(k * n + j) * n + q0] = s;
+            }
+      for (int k = 0; k < n; ++k)
+        for (int q1 = 0; q1 < n; ++q1)
+          for (int q0 = 0; q0 < n; ++q0)
+            {
+              double s = 0;
+              for (int j = 0; j < n; ++j)
+                s += M1[q1 * n + j] * a[(k * n + j) * n + q0];
+              c[(k * n + q1) * n + q0] = s;
+            }
+      for (int q2 = 0; q2 < n; ++q2)
+        for (int q1 = 0; q1 < n; ++q1)
+          for (int q0 = 0; q0 < n; ++q0)
+            {
+              double s = 0;
+              for (int k = 0; k < n; ++k)
+                s += M2[q2 * n + k] * c[(k * n + q1) * n + q0];
+              out[(q2 * n + q1) * n + q0] = s;
+            }
+    }
+
+    // MinimalSurfaceOperator::evaluate_coefficient(first_time, solution) (minimal_surface/program.cc:117-163): the merged
+    // coefficient JxW J^-1 T J^-T with the tensor T of the gradient g of `u` (all entries of u are read, boundary values
+    // included: the FEEvaluation without Dirichlet constraints of :123):
+    // mode 0 (first_time): T = I;  mode 1: T = (I - g g^T / (1 + |g|^2)) / sqrt(1 + |g|^2), the Newton linearisation;
+    // mode 2: T = I / sqrt(1 + |g|^2), the flux of the nonlinear residual (:188-192) written as an operator on u
+    void
+    evaluate_solution_coefficient(const int mode, const T *u)
+    {
+      const int nq = n * n * n;
+      variable     = true;
+      coef_q.resize(ncells * nq * 6);
+#pragma omp parallel for collapse(2)
+      for (int cz = 0; cz < nc[2]; ++cz)
+        for (int cy = 0; cy < nc[1]; ++cy)
+          for (int cx = 0; cx < nc[0]; ++cx)
+            {
+              const size_t   cell = ((size_t)cz * nc[1] + cy) * nc[0] + cx;
+              vector<double> X, ul(nq), gr[3] = {vector<double>(nq), vector<double>(nq), vector<double>(nq)};
+              if (geom.kind != 0)
+                cell_nodes(cx, cy, cz, X);
+              for (int k = 0, l = 0; k < n; ++k)
+                for (int j = 0; j < n; ++j)
+                  for (int i = 0; i < n; ++i, ++l)
+                    ul[l] = u[((size_t)(cz * p + k) * nd[1] + cy * p + j) * nd[0] + cx * p + i];
+              const double *Sb = b->S.data(), *Gb = b->G.data();
+              tensor3(n, Gb, Sb, Sb, ul.data(), gr[0].data());
+              tensor3(n, Sb, Gb, Sb, ul.data(), gr[1].data());
+              tensor3(n, Sb, Sb, Gb, ul.data(), gr[2].data());
+              for (int q2 = 0, q = 0; q2 < n; ++q2)
+                for (int q1 = 0; q1 < n; ++q1)
+                  for (int q0 = 0; q0 < n; ++q0, ++q)
+                    {
+                      double x[3], J[3][3] = {{h[0], 0, 0}, {0, h[1], 0}, {0, 0, h[2]}}, inv[3][3];
+                      if (geom.kind != 0)
+                        cell_geometry(X, q0, q1, q2, x, J);
+                      const double det = invert3(J, inv); // inv[e][d] = d xi_e / d x_d
+                      double       g[3], Tn[3][3];
+                      for (int d = 0; d < 3; ++d)
+                        g[d] = inv[0][d] * gr[0][q] + inv[1][d] * gr[1][q] + inv[2][d] * gr[2][q];
+                      const double g2 = g[0] * g[0] + g[1] * g[1] + g[2] * g[2];
+                      for (int d = 0; d < 3; ++d)
+                        for (int e = 0; e < 3; ++e)
+                          {
+                            const double id = d == e ? 1. : 0.;
+                            Tn[d][e]        = mode == 0 ? id :
+                                                          (mode == 1 ? (id - g[d] * g[e] / (1. + g2)) / std::sqrt(1. + g2) :
+                                                                       id / std::sqrt(1. + g2));
+                          }
+                      const double f     = b->wq[q0] * b->wq[q1] * b->wq[q2] * std::fabs(det);
+                      const int    pe[6] = {0, 1, 2, 0, 0, 1}, pf[6] = {0, 1, 2, 1, 2, 2};
+                      for (int s = 0; s < 6; ++s)
+                        {
+                          double m = 0;
+                          for (int d = 0; d < 3; ++d)
+                            for (int e = 0; e < 3; ++e)
+                              m += inv[pe[s]][d] * Tn[d][e] * inv[pf[s]][e];
+                          coef_q[(cell * nq + q) * 6 + s] = (T)(f * m);
+                        }
+                    }
+            }
+    }
+
     // evaluate + quadrature-point operation + integrate on one cell
     // (laplace_operator.h:544-551 with :438-523 in between)
     template <int nn>
@@ -1586,7 +1682,8 @@ namespace orc
     // multigrid_solver.h:483-493 with deal.II SolverCG + ReductionControl(1000,1e-16,1e-9)
     // 
     std::pair<unsigned int, double>
-    solve_cg(vector<double> *history = nullptr)
+    solve_cg(vector<double> *history = nullptr, const unsigned int max_it = 1000, const double abs_tol = 1e-16,
+             const double rel_tol = 1e-9)
     {
       const int              L = nlevels - 1;
       const LevelOp<double> &A = matrix_dp[L];
@@ -1601,7 +1698,7 @@ namespace orc
       if (history)
         history->push_back(res);
       unsigned int it = 0;
-      if (res > 1e-16 && res0 > 0)
+      if (res > abs_tol && res0 > 0)
         {
           vmult(h, g);
           for (size_t i = 0; i < N; ++i)
@@ -1621,7 +1718,7 @@ namespace orc
               res = std::sqrt(dot(g, g));
               if (history)
                 history->push_back(res);
-              if (res <= 1e-16 || res <= 1e-9 * res0 || it >= 1000)
+              if (res <= abs_tol || res <= rel_tol * res0 || it >= max_it)
                 break;
               vmult(h, g);
               const double gh_new = dot(g, h);
@@ -1633,6 +1730,149 @@ namespace orc
             }
         }
       return std::make_pair(it, it > 0 ? std::pow(res / res0, 1. / it) : 0.);
+    }
+
+    // ------------------------------------------------------------------ minimal_surface/program.cc
+    // Newton's method with line search for -div(grad u / sqrt(1 + |grad u|^2)) = 0 with Dirichlet data, the linear
+    // systems solved by CG with the V-cycle on the linearised operator (LaplaceProblem::solve, :412-572).
+    vector<vector<float>> coefficient_solutions;
+    LevelOp<double>       residual_op;
+    vector<double>        search_direction, tentative_solution, system_rhs;
+
+    // interpolate_boundary_values (:396-408): the Dirichlet data in the boundary entries of `solution`, zero inside
+    void
+    ms_set_boundary_values(const double *u_bc)
+    {
+      const int              L  = nlevels - 1;
+      const LevelOp<double> &op = matrix_dp[L];
+      std::fill(solution[L].begin(), solution[L].end(), 0.);
+      inhomogeneous_bc[L].clear();
+      for (int k = 0; k < op.nd[2]; ++k)
+        for (int j = 0; j < op.nd[1]; ++j)
+          for (int i = 0; i < op.nd[0]; ++i)
+            if (op.on_boundary(i, j, k))
+              {
+                const size_t idx = ((size_t)k * op.nd[1] + j) * op.nd[0] + i;
+                if (u_bc)
+                  solution[L][idx] = u_bc[idx];
+                else
+                  {
+                    double x[3] = {support_point(op, 0, i), support_point(op, 1, j), support_point(op, 2, k)};
+                    if (op.geom.kind != 0)
+                      {
+                        const double xi[3] = {unit_coordinate(op, 0, i), unit_coordinate(op, 1, j), unit_coordinate(op, 2, k)};
+                        op.geom.point(xi, x);
+                      }
+                    solution[L][idx] = f_solution(x);
+                  }
+                inhomogeneous_bc[L].emplace_back(idx, solution[L][idx]);
+              }
+      residual_op      = matrix_dp[L];
+      coefficient_solutions.resize(nlevels);
+      smooth[0].smoothing_range = 1e-3; // :470-474
+    }
+
+    // the FE_Q restriction matrices of :433-447 (interpolation of the fine function in the support points of the coarse
+    // cell, each child contributing the points inside it) as one 1-D matrix R[i][m] over the 2p+1 fine points of a
+    // coarse cell, applied in the three directions
+    void
+    ms_restrict_solution(const int level, vector<float> &coarse, const vector<float> &fine) const
+    {
+      const LevelOp<float> &oc = matrix[level - 1], &of = matrix[level];
+      const int             n = oc.n, nf = 2 * p + 1;
+      vector<long double>   nodes(basis.gll.begin(), basis.gll.end());
+      vector<double>        R(n * nf, 0.);
+      for (int i = 0; i < n; ++i)
+        {
+          const int child = basis.gll[i] <= 0.5 ? 0 : 1;
+          for (int m = 0; m < n; ++m)
+            R[i * nf + child * p + m] = (double)lagrange(nodes, m, 2 * (long double)basis.gll[i] - child);
+        }
+      coarse.assign(oc.ndofs, 0.f);
+#pragma omp parallel for collapse(2)
+      for (int k = 0; k < oc.nd[2]; ++k)
+        for (int j = 0; j < oc.nd[1]; ++j)
+          for (int i = 0; i < oc.nd[0]; ++i)
+            {
+              const int c[3] = {std::min(i / p, oc.nc[0] - 1), std::min(j / p, oc.nc[1] - 1), std::min(k / p, oc.nc[2] - 1)};
+              const int l[3] = {i - c[0] * p, j - c[1] * p, k - c[2] * p};
+              double    sum  = 0;
+              for (int mz = 0; mz < nf; ++mz)
+                for (int my = 0; my < nf; ++my)
+                  for (int mx = 0; mx < nf; ++mx)
+                    {
+                      const double w = R[l[0] * nf + mx] * R[l[1] * nf + my] * R[l[2] * nf + mz];
+                      if (w != 0.)
+                        sum += w * (double)fine[((size_t)(2 * c[2] * p + mz) * of.nd[1] + 2 * c[1] * p + my) * of.nd[0] +
+                                                2 * c[0] * p + mx];
+                    }
+              coarse[((size_t)k * oc.nd[1] + j) * oc.nd[0] + i] = (float)sum;
+            }
+    }
+
+    // MinimalSurfaceOperator::compute_residual (:169-198): dst_i = -(grad phi_i, grad u / sqrt(1 + |grad u|^2)) on the
+    // rows without Dirichlet condition (first_time: the Laplace residual)
+    void
+    ms_residual(vector<double> &dst, const vector<double> &u, const bool first_time)
+    {
+      residual_op.evaluate_solution_coefficient(first_time ? 0 : 2, u.data());
+      dst.assign(u.size(), 0.);
+      residual_op.apply_add(dst.data(), u.data(), /*read_plain=*/true);
+      for (double &v : dst)
+        v = -v;
+    }
+
+    // LaplaceProblem::solve(first_time) (:412-572); info = {initial residual, final residual, linear iterations,
+    // line search steps, step length}
+    void
+    ms_newton_step(const bool first_time, double *info)
+    {
+      const int L = nlevels - 1;
+      coefficient_solutions[L].resize(solution[L].size());
+      convert(coefficient_solutions[L], solution[L]);
+      for (int l = L; l > 0; --l)
+        ms_restrict_solution(l, coefficient_solutions[l - 1], coefficient_solutions[l]);
+      matrix_dp[L].evaluate_solution_coefficient(first_time ? 0 : 1, solution[L].data());
+      for (int l = 0; l < nlevels; ++l)
+        {
+          matrix[l].evaluate_solution_coefficient(first_time ? 0 : 1, coefficient_solutions[l].data());
+          if (l == 0)
+            {
+              smooth[0].degree              = Chebyshev<float>::invalid_degree;
+              smooth[0].eig_cg_n_iterations = matrix[0].m();
+            }
+          matrix[l].compute_diagonal();
+          smooth[l].initialize(matrix[l]);
+        }
+      ms_residual(system_rhs, solution[L], first_time);
+      const double initial_residual_norm = std::sqrt(dot(system_rhs, system_rhs));
+      // ReductionControl(m(), 1e-13, 1e-4), zero start; the Newton update lives in solution[L] during the solve
+      vector<double> current = solution[L];
+      rhs[L]                 = system_rhs;
+      const auto cg          = solve_cg(nullptr, (unsigned int)matrix_dp[L].m(), 1e-13, 1e-4);
+      search_direction       = solution[L];
+      solution[L]            = current;
+      matrix_dp[L].for_boundary([&](const size_t i) { search_direction[i] = 0; }); // constraints.distribute
+      double       final_residual_norm = initial_residual_norm, alpha = 1.;
+      unsigned int n_steps             = 0;
+      while (n_steps < 100)
+        {
+          tentative_solution = solution[L];
+          for (size_t i = 0; i < tentative_solution.size(); ++i)
+            tentative_solution[i] += alpha * search_direction[i];
+          ms_residual(system_rhs, tentative_solution, false);
+          final_residual_norm = std::sqrt(dot(system_rhs, system_rhs));
+          if (final_residual_norm < initial_residual_norm)
+            break;
+          alpha /= 2.;
+          ++n_steps;
+        }
+      solution[L] = tentative_solution;
+      info[0]     = initial_residual_norm;
+      info[1]     = final_residual_norm;
+      info[2]     = cg.first;
+      info[3]     = n_steps;
+      info[4]     = alpha;
     }
   };
 } // namespace orc
@@ -1721,6 +1961,37 @@ extern "C"
   orc_mg_destroy(void *h)
   {
     delete static_cast<MultigridSolver *>(h);
+  }
+
+  void
+  orc_mg_ms_set_boundary_values(void *h, const double *u_bc)
+  {
+    static_cast<MultigridSolver *>(h)->ms_set_boundary_values(u_bc);
+  }
+
+  void
+  orc_mg_ms_newton_step(void *h, int first_time, double *info)
+  {
+    static_cast<MultigridSolver *>(h)->ms_newton_step(first_time != 0, info);
+  }
+
+  void
+  orc_mg_ms_residual(void *h, const double *u, int first_time, double *dst)
+  {
+    MultigridSolver *m = static_cast<MultigridSolver *>(h);
+    const size_t     N = m->matrix_dp[m->nlevels - 1].ndofs;
+    vector<double>   in(u, u + N), out;
+    m->ms_residual(out, in, first_time != 0);
+    std::copy(out.begin(), out.end(), dst);
+  }
+
+  // coefficient_solutions[level] of the last Newton step, converted to double
+  void
+  orc_mg_ms_level_solution(void *h, int level, double *out)
+  {
+    MultigridSolver *m = static_cast<MultigridSolver *>(h);
+    for (size_t i = 0; i < m->coefficient_solutions[level].size(); ++i)
+      out[i] = m->coefficient_solutions[level][i];
   }
 
   int

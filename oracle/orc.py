@@ -52,6 +52,10 @@ def lib():
         L.orc_mg_set_rhs_values.argtypes = [C.c_void_p, C.c_int, dp, dp]
         L.orc_mg_set_exact_values.argtypes = [C.c_void_p, C.c_int, dp]
         L.orc_mg_destroy.argtypes = [C.c_void_p]
+        L.orc_mg_ms_set_boundary_values.argtypes = [C.c_void_p, dp]
+        L.orc_mg_ms_newton_step.argtypes = [C.c_void_p, C.c_int, dp]
+        L.orc_mg_ms_residual.argtypes = [C.c_void_p, dp, C.c_int, dp]
+        L.orc_mg_ms_level_solution.argtypes = [C.c_void_p, C.c_int, dp]
         L.orc_mg_n_levels.argtypes = [C.c_void_p]
         L.orc_mg_n_dofs.restype = C.c_longlong
         L.orc_mg_n_dofs.argtypes = [C.c_void_p, C.c_int]
@@ -247,6 +251,42 @@ class MultigridSolver:
                 lib().orc_mg_set_rhs_values(self.h, l, _dp(f), _dp(g) if g is not None else None)
             if exact_solution is not None:
                 lib().orc_mg_set_exact_values(self.h, l, _dp(ev(exact_solution, self.quadrature_points(l))))
+
+    # ---- minimal_surface/program.cc: Newton's method with line search on -div(grad u / sqrt(1 + |grad u|^2)) = 0
+    def minimal_surface_set_boundary_values(self, boundary_values=None):
+        """interpolate_boundary_values (:396-408); a callable g(x, y, z) or None = the solver's analytic solution"""
+        g = None
+        if boundary_values is not None:
+            x = self.support_points()
+            g = np.ascontiguousarray(boundary_values(x[:, 0], x[:, 1], x[:, 2]), dtype=np.float64)
+        lib().orc_mg_ms_set_boundary_values(self.h, _dp(g) if g is not None else None)
+
+    def minimal_surface_step(self, first_time):
+        """LaplaceProblem::solve(first_time) (:412-572) -> dict(initial_residual, final_residual, linear_iterations,
+        line_search_steps, step_length)"""
+        info = np.zeros(5)
+        lib().orc_mg_ms_newton_step(self.h, int(first_time), _dp(info))
+        return dict(initial_residual=info[0], final_residual=info[1], linear_iterations=int(info[2]),
+                    line_search_steps=int(info[3]), step_length=info[4])
+
+    def minimal_surface_solve(self, max_steps=100, tolerance=1e-12):
+        """the inner loop of run() (:652-659) -> list of the steps' dicts"""
+        steps = []
+        for it in range(max_steps):
+            steps.append(self.minimal_surface_step(it == 0))
+            if steps[-1]["final_residual"] < tolerance:
+                break
+        return steps
+
+    def minimal_surface_residual(self, u, first_time=False):
+        out = np.zeros(self.n_dofs())
+        lib().orc_mg_ms_residual(self.h, _dp(np.ascontiguousarray(u, dtype=np.float64)), int(first_time), _dp(out))
+        return out
+
+    def minimal_surface_level_solution(self, level):
+        out = np.zeros(self.n_dofs(level))
+        lib().orc_mg_ms_level_solution(self.h, self._l(level), _dp(out))
+        return out
 
     def solve(self, do_analyze=False):
         trace = np.zeros((self.n_levels, 4))
