@@ -644,13 +644,17 @@ namespace mgb
   __global__ void
   k_solution_coefficient(const SolutionCoefArgs<T> A)
   {
-    constexpr int     n = p + 1, n3 = n * n * n;
-    __shared__ double X[3 * n3];
-    __shared__ double U[n3];
-    const uint32_t    cell = blockIdx.x;
-    int               cx, cy, cz;
+    // one thread per quadrature point; reference derivatives of the three coordinate fields of the cell geometry and of
+    // u by sum factorisation (x: S, G; y: three combinations; z in registers), field after field through shared memory
+    constexpr int n = p + 1, n2 = n * n, n3 = n * n * n;
+    extern __shared__ double sc_smem[];
+    double        *X = sc_smem, *U = X + 3 * n3, *a_s = U + n3 /* x-stage: (S u, G u) */, *b_s = a_s + 2 * n3 /* y-stage */;
+    const uint32_t cell = blockIdx.x;
+    int            cx, cy, cz;
     cell_coords(A.L, cell, cx, cy, cz);
-    cell_support_points<p>(A.geom, A.L, cx, cy, cz, X);
+    const bool box = A.geom.kind == 0;
+    if (!box)
+      cell_support_points<p>(A.geom, A.L, cx, cy, cz, X);
     for (int l = threadIdx.x; l < n3; l += blockDim.x)
       {
         bool           con;
@@ -658,32 +662,65 @@ namespace mgb
         U[l]             = (double)A.u[d];
       }
     __syncthreads();
-    for (int q = threadIdx.x; q < n3; q += blockDim.x)
+    const int  q = threadIdx.x, q0 = q % n, q1 = (q / n) % n, q2 = q / n2;
+    const bool act = q < n3;
+    double     der[4][3]; // [field][reference direction]
+    for (int f = box ? 3 : 0; f < 4; ++f)
       {
-        const int q0 = q % n, q1 = (q / n) % n, q2 = q / (n * n);
-        double    J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, gr[3] = {0, 0, 0};
-        for (int k = 0; k < n; ++k)
-          for (int j = 0; j < n; ++j)
-            {
-              const double s2 = ctab.S[q2 * n + k], g2 = ctab.G[q2 * n + k];
-              const double s1 = ctab.S[q1 * n + j], g1 = ctab.G[q1 * n + j];
-              for (int i = 0; i < n; ++i)
-                {
-                  const double s0 = ctab.S[q0 * n + i], g0 = ctab.G[q0 * n + i];
-                  const int    l  = (k * n + j) * n + i;
-                  const double d0 = g0 * s1 * s2, d1 = s0 * g1 * s2, d2 = s0 * s1 * g2;
-                  for (int d = 0; d < 3; ++d)
-                    {
-                      const double Xd = X[d * n3 + l];
-                      J[d][0] += Xd * d0;
-                      J[d][1] += Xd * d1;
-                      J[d][2] += Xd * d2;
-                    }
-                  gr[0] += U[l] * d0;
-                  gr[1] += U[l] * d1;
-                  gr[2] += U[l] * d2;
-                }
-            }
+        const double *in = X + f * n3;
+        if (act)
+          { // x: thread (q0, j = q1, k = q2)
+            double s = 0, g = 0;
+            for (int i = 0; i < n; ++i)
+              {
+                const double v = in[(q2 * n + q1) * n + i];
+                s += ctab.S[q0 * n + i] * v;
+                g += ctab.G[q0 * n + i] * v;
+              }
+            a_s[q]      = s;
+            a_s[n3 + q] = g;
+          }
+        __syncthreads();
+        if (act)
+          { // y: thread (q0, q1, k = q2): G S, S G, S S
+            double gs = 0, sg = 0, ss = 0;
+            for (int j = 0; j < n; ++j)
+              {
+                const double vs = a_s[(q2 * n + j) * n + q0], vg = a_s[n3 + (q2 * n + j) * n + q0];
+                gs += ctab.S[q1 * n + j] * vg;
+                sg += ctab.G[q1 * n + j] * vs;
+                ss += ctab.S[q1 * n + j] * vs;
+              }
+            b_s[q]          = gs;
+            b_s[n3 + q]     = sg;
+            b_s[2 * n3 + q] = ss;
+          }
+        __syncthreads();
+        if (act)
+          { // z
+            double d0 = 0, d1 = 0, d2 = 0;
+            for (int k = 0; k < n; ++k)
+              {
+                const int l = (k * n + q1) * n + q0;
+                d0 += ctab.S[q2 * n + k] * b_s[l];
+                d1 += ctab.S[q2 * n + k] * b_s[n3 + l];
+                d2 += ctab.G[q2 * n + k] * b_s[2 * n3 + l];
+              }
+            der[f][0] = d0;
+            der[f][1] = d1;
+            der[f][2] = d2;
+          }
+        // (the next field's x-stage writes a_s, which nobody reads any more; its y-stage writes b_s after the barrier
+        // that follows the x-stage, by when every thread has left this z-stage)
+      }
+    if (act)
+      {
+        double J[3][3] = {{A.L.h[0], 0, 0}, {0, A.L.h[1], 0}, {0, 0, A.L.h[2]}};
+        if (!box)
+          for (int d = 0; d < 3; ++d)
+            for (int e = 0; e < 3; ++e)
+              J[d][e] = der[d][e];
+        const double gr[3] = {der[3][0], der[3][1], der[3][2]};
         const double det = det3(J);
         double       I[3][3]; // I[e][d] = d xi_e / d x_d
         I[0][0] = (J[1][1] * J[2][2] - J[1][2] * J[2][1]) / det;
@@ -724,7 +761,14 @@ namespace mgb
   launch_solution_coefficient(const SolutionCoefArgs<T> &A, cudaStream_t stream)
   {
     constexpr int n3 = (p + 1) * (p + 1) * (p + 1);
-    k_solution_coefficient<p, T><<<A.L.n_cells, n3 < 128 ? ((n3 + 31) / 32) * 32 : 128, 0, stream>>>(A);
+    constexpr size_t smem = (size_t)9 * n3 * sizeof(double);
+    static bool      attribute_set = false;
+    if (!attribute_set && smem > 48 * 1024)
+      {
+        cudaFuncSetAttribute(k_solution_coefficient<p, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attribute_set = true;
+      }
+    k_solution_coefficient<p, T><<<A.L.n_cells, ((n3 + 31) / 32) * 32, smem, stream>>>(A);
   }
 
   // The FE_Q restriction matrices applied to a level vector (minimal_surface/program.cc:417-456): the coarse vector

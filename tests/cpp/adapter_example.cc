@@ -8,6 +8,7 @@
 #include <cmath>
 #include "multigrid/laplace_operator_adaptive.h"
 #include "multigrid/laplace_operator_dg.h"
+#include "multigrid/minimal_surface.h"
 #include "multigrid/multigrid_solver_dg.h"
 #include "multigrid/multigrid_solver_dg_plain.h"
 #include "multigrid/multigrid_solver.h"
@@ -196,6 +197,29 @@ main(int argc, char **argv)
       const std::pair<double, double>                         dg_cg = dg_solver.solve_cg(1e-3);
       std::printf("dg_cg_its %u dg_cg_rate %.6e dg_l2 %.6e\n", dg_solver.last_step(), dg_cg.second,
                   dg_solver.compute_l2_error());
+
+      // the minimal surface problem of minimal_surface/program.cc on [-1,1]^3 with 2 refinements: Scherk's surface
+      // log(cos x / cos y) solves the equation, so the Newton iteration started from its boundary values must find it
+      {
+        multigrid::MeshDescription ms_mesh;
+        ms_mesh.n_refinements = 2;
+        for (int d = 0; d < 3; ++d)
+          ms_mesh.lower[d] = -1.;
+        multigrid::MinimalSurfaceProblem<3, 3> minimal(ms_mesh);
+        const auto scherk = [](const double x, const double y, const double) { return std::log(std::cos(x) / std::cos(y)); };
+        minimal.interpolate_boundary_values(scherk);
+        const auto                steps = minimal.run(20, 1e-11);
+        const std::vector<double> u     = minimal.get_solution();
+        const std::vector<double> xyz   = minimal.solver().support_points((int)minimal.solver().n_levels() - 1);
+        double                    err   = 0;
+        unsigned int              its   = 0;
+        for (std::size_t i = 0; i < u.size(); ++i)
+          err = std::max(err, std::fabs(u[i] - scherk(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2])));
+        for (const auto &st : steps)
+          its += st.linear_iterations;
+        std::printf("minimal_steps %zu minimal_linear_its %u minimal_residual %.3e minimal_error %.6e\n", steps.size(), its,
+                    steps.back().final_residual_norm, err);
+      }
 
       // pure DG h-multigrid as poisson_dg_plain/program.cc:232-263 on the same mesh, FE_DGQArbitraryNodes (type 2); one
       // preconditioned CG step by hand through vmult_with_residual_update (residual r = b - A 0 = b is not available

@@ -115,3 +115,12 @@ def test_example_driver_matches_oracle(mgb, orc):
     rMr = ones @ dp.vmult(ones)
     assert abs(float(out["plain_rMr"]) - rMr) <= 1e-4 * rMr
     assert abs(float(out["plain_rMr"]) - float(out["plain_rMr_check"])) <= 1e-9 * rMr
+    scherk = lambda x, y, z: np.log(np.cos(x) / np.cos(y)) + 0 * z
+    om = orc.MultigridSolver(3, 1, 2, lower=(-1,) * 3, upper=(1,) * 3, degree_pre=2, degree_post=2, n_cycles=1)
+    om.minimal_surface_set_boundary_values(scherk)
+    steps = om.minimal_surface_solve(20, 1e-11)
+    xs = om.support_points()
+    err = np.abs(om.get_vector(orc.VEC_SOLUTION) - scherk(xs[:, 0], xs[:, 1], xs[:, 2])).max()
+    assert int(out["minimal_steps"]) == len(steps) and float(out["minimal_residual"]) < 1e-11
+    assert abs(int(out["minimal_linear_its"]) - sum(st["linear_iterations"] for st in steps)) <= 1
+    assert abs(float(out["minimal_error"]) - err) <= 1e-3 * err
