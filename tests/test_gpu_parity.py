@@ -175,13 +175,18 @@ def test_mapped_geometry(mgb, orc, torch, case):
     hist = P.g.cg_history()
     # with the 1e6 coefficient contrast CG needs about 20 steps at a rate of 0.35 and the float V-cycle's rounding (and
     # the summation order of the scatter-add) shows in the last residuals, 7 orders down: the step at which 1e-9 is
-    # crossed may differ by one; 5 % on the first five orders of magnitude, a factor of 3 on the tail
+    # crossed may differ by one; 5 % on the first three orders of magnitude, decade crossings on the tail (single entries
+    # further down were seen 20 % apart between two runs of the same binary: the atomicAdd order of the general kernel)
     assert abs(its - its_o) <= (1 if problem == 1 else 0), (its, its_o)
     m = min(len(hist), len(hist_o))
     hist, hist_o = hist[:m], hist_o[:m]
-    head = hist_o > 1e-5 * hist_o[0]
+    head = hist_o > 1e-3 * hist_o[0]
     assert np.allclose(hist[head], hist_o[head], rtol=0.05), (hist, hist_o)
-    assert np.all(hist[~head] < 3 * hist_o[~head]) and np.all(hist_o[~head] < 3 * hist[~head]), (hist, hist_o)
+    # below that the two histories wander around each other (plateaus of one or two steps at different places): every
+    # decade of residual reduction is crossed at the same step, give or take one
+    for k in range(1, 9):
+        a, b = np.nonzero(hist <= 10. ** -k * hist[0])[0], np.nonzero(hist_o <= 10. ** -k * hist_o[0])[0]
+        assert a.size and b.size and abs(int(a[0]) - int(b[0])) <= 1, (k, hist, hist_o)
     e, e_o = P.g.compute_l2_error(), P.o.compute_l2_error()
     assert abs(e - e_o) <= 1e-3 * e_o, (e, e_o)
     sol = P.g.get_solution()[P.lex(L)]
