@@ -472,6 +472,19 @@ int mgb_vec_update_ghost_values(mgb_solver s, int level, int precision, void *v)
 int mgb_vec_compress_add(mgb_solver s, int level, int precision, void *v);
 int mgb_vec_zero_out_ghost_values(mgb_solver s, int level, int precision, void *v);
 
+/* ---- Allocation-free dot product.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * *result_dev = sum_i x[i] y[i] over n entries of two device vectors of the given precision, accumulated in double;
+ * result_dev is a device pointer, the work is queued on `cuda_stream` (a cudaStream_t, NULL = the default stream) and the
+ * call does not synchronise.  It needs no solver handle and allocates nothing: the partial sums live in a static
+ * __device__ array of 512.25 KiB inside the library (held by every GPU that loads it until exit), which bounds the
+ * length: n <= MGB_NOALLOC_DOT_MAX_N, larger calls fail with a message.  All calls on a GPU share that array: calls on
+ * one stream are ordered, calls that overlap on the GPU (other streams, other threads) race.  The first call on a device
+ * looks up the array's device address (cudaGetSymbolAddress, with that device current); n = 0 does only that -- call it
+ * once before starting a capture.  Fixed summation order: bitwise reproducible.  (csrc/noalloc.cu)                     */
+#define MGB_NOALLOC_DOT_MAX_N 268435456LL
+int mgb_noalloc_dot(int precision, int64_t n, const void *x_dev, const void *y_dev, double *result_dev, void *cuda_stream);
+
 /* plain host<->device helpers so that a C/C++ caller needs no CUDA runtime of its own; `s` may be NULL (vectors
  * of the DG operator): current device, synchronous */
 int mgb_device_alloc(mgb_solver s, size_t bytes, void **dev_ptr);

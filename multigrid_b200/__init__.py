@@ -152,6 +152,7 @@ SYMBOLS = {
     "mgb_transfer_restrict_and_add": (_i, [_vp, _i, _vp, _vp]),
     "mgb_transfer_prolongate_no_boundary": (_i, [_vp, _i, _vp, _vp]),
     "mgb_vec_dot": (_i, [_vp, _i, _i, _vp, _vp, _dp]),
+    "mgb_noalloc_dot": (_i, [_i, C.c_int64, _vp, _vp, _vp, _vp]),
     "mgb_vec_sadd": (_i, [_vp, _i, _i, _vp, _d, _d, _vp]),
     "mgb_vec_set": (_i, [_vp, _i, _i, _vp, _d]),
     "mgb_vec_update_ghost_values": (_i, [_vp, _i, _i, _vp]),
@@ -331,6 +332,29 @@ def comm_unique_id():
     buf = (C.c_ubyte * 128)()
     _check(lib().mgb_comm_unique_id(buf))
     return bytes(buf)
+
+
+NOALLOC_DOT_MAX_N = 268435456
+
+
+def noalloc_dot(x, y, out, stream=None):
+    """mgb_noalloc_dot: out[0] = x . y (accumulated in double) for two CUDA tensors of dtype float32 or float64; `out` is
+    a float64 CUDA tensor with one entry.  Allocates nothing (the scratch is a static device array in the library), needs
+    no solver, is queued on `stream` (a torch.cuda.Stream; default: torch's current stream) and does not synchronise.
+    At most NOALLOC_DOT_MAX_N entries; calls that overlap on one GPU race on the shared scratch array."""
+    import torch
+    if x.dtype != y.dtype or x.dtype not in (torch.float32, torch.float64):
+        raise MgbError("noalloc_dot: float32 or float64 tensors of the same dtype")
+    if x.numel() != y.numel() or not (x.is_cuda and y.is_cuda and out.is_cuda) or not (x.is_contiguous() and y.is_contiguous()):
+        raise MgbError("noalloc_dot: contiguous CUDA tensors of the same length")
+    if out.dtype != torch.float64 or out.numel() < 1:
+        raise MgbError("noalloc_dot: out must be a float64 CUDA tensor")
+    if stream is None:
+        stream = torch.cuda.current_stream(x.device)
+    with torch.cuda.device(x.device):
+        _check(lib().mgb_noalloc_dot(F64 if x.dtype == torch.float64 else F32, x.numel(), C.c_void_p(x.data_ptr()),
+                                     C.c_void_p(y.data_ptr()), C.c_void_p(out.data_ptr()), C.c_void_p(stream.cuda_stream)))
+    return out
 
 
 def comm_from_torch_distributed():
