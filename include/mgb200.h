@@ -302,6 +302,15 @@ int mgb_dg_vmult_residual_and_restrict_to_cg(mgb_dg h, mgb_solver s, int level, 
                                              const void *lhs, void *restricted_residual);
 /* end-to-end: host vectors in, apply, host vector out */
 int mgb_dg_vmult_host(mgb_dg h, int precision, void *dst_host, const void *src_host);
+/* The CG solver of solver_dg/program.cc:180-262 on this operator: SolverCG with IterationNumberControl(n_iterations,
+ * 1e-20) from x = 0 and a diagonal preconditioner (device vector; mgb_dg_lumped_mass_inverse gives the program's, the
+ * inverse of (1, phi_i), :134-148).  interleaved = 0: "cell-based loops" (operator apply, then vector updates and dot
+ * products as separate passes, :216-227); interleaved != 0: "interleaved loops" (LaplaceOperatorInterleave, :39-70 --
+ * the vector updates ride in one kernel before the apply and the five sums in the apply's store stage; one GPU).
+ * stats = {iterations done, last residual norm}                                                                    */
+int mgb_dg_lumped_mass_inverse(mgb_dg h, int precision, void *out);
+int mgb_dg_solve_cg(mgb_dg h, int precision, unsigned int n_iterations, int interleaved, void *x, const void *b,
+                    const void *diagonal_preconditioner, double stats[2]);
 int mgb_dg_timer_start(mgb_dg h);
 int mgb_dg_timer_stop(mgb_dg h, double *ms);
 int64_t mgb_dg_launch_count(mgb_dg h);

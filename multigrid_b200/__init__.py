@@ -188,6 +188,8 @@ SYMBOLS = {
     "mgb_dg_set_preconditioner": (_i, [_vp, _i]),
     "mgb_dg_preconditioner_vmult": (_i, [_vp, _i, _vp, _vp]),
     "mgb_dg_vmult_host": (_i, [_vp, _i, _vp, _vp]),
+    "mgb_dg_lumped_mass_inverse": (_i, [_vp, _i, _vp]),
+    "mgb_dg_solve_cg": (_i, [_vp, _i, _u, _i, _vp, _vp, _vp, _dp]),
     "mgb_dg_timer_start": (_i, [_vp]),
     "mgb_dg_timer_stop": (_i, [_vp, _dp]),
     "mgb_dg_launch_count": (C.c_int64, [_vp]),
@@ -902,6 +904,25 @@ class LaplaceOperatorDG:
         _check(lib().mgb_dg_inverse_diagonal(self.h, self.precision, _ptr(d)))
         self.sync()
         return d
+
+    def lumped_mass_inverse(self):
+        """the diagonal preconditioner of solver_dg/program.cc:134-148: 1 / (1, phi_i)"""
+        d = self.initialize_dof_vector()
+        self._torch_sync()
+        _check(lib().mgb_dg_lumped_mass_inverse(self.h, self.precision, _ptr(d)))
+        self.sync()
+        return d
+
+    def solve_cg(self, x, b, diagonal_preconditioner, n_iterations, interleaved=True):
+        """SolverCG with IterationNumberControl(n_iterations, 1e-20) and a diagonal preconditioner from x = 0
+        (solver_dg/program.cc:180-262); interleaved: the vector updates merged with the operator (LaplaceOperatorInterleave,
+        :39-70) instead of separate passes.  -> (iterations, last residual norm)"""
+        self._chk(x, b, diagonal_preconditioner)
+        stats = (C.c_double * 2)()
+        self._torch_sync()
+        _check(lib().mgb_dg_solve_cg(self.h, self.precision, int(n_iterations), int(interleaved), _ptr(x), _ptr(b),
+                                     _ptr(diagonal_preconditioner), stats))
+        return int(stats[0]), stats[1]
 
     def vmult_with_chebyshev_update(self, rhs, iteration_index, factor1, factor2, solution, solution_old):
         """as the reference (laplace_operator_dg.h:907-955): the new iterate lands in `solution_old`; the caller

@@ -283,6 +283,35 @@ namespace mgb
   }
 
   // four sums of vmult_with_cg_update: q.p, r.r, q.r, q.q (warp shuffles, one atomic per block and sum)
+  // out[0..4] += column sums of partial[n_blocks][5] (the per-block sums of k_dg_apply in mode DG_SET_SUMS); out zeroed
+  // by the caller, one atomicAdd per block and column
+  __global__ void
+  k_dg_sum_partials(const size_t n_blocks, const double *__restrict__ partial, double *out)
+  {
+    double       acc[5] = {0, 0, 0, 0, 0};
+    const size_t total = n_blocks * 5, stride = (size_t)gridDim.x * blockDim.x * 5;
+    for (size_t e = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 5; e < total; e += stride)
+      for (int s = 0; s < 5; ++s)
+        acc[s] += partial[e + s];
+    __shared__ double red[5][32];
+    for (int s = 0; s < 5; ++s)
+      {
+        double v = acc[s];
+        for (int o = 16; o > 0; o >>= 1)
+          v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0)
+          red[s][threadIdx.x >> 5] = v;
+      }
+    __syncthreads();
+    if (threadIdx.x < 5)
+      {
+        double v = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w)
+          v += red[threadIdx.x][w];
+        atomicAdd(&out[threadIdx.x], v);
+      }
+  }
+
   template <typename T>
   __global__ void
   k_dg_cg_sums(const size_t off, const size_t n, const T *__restrict__ q, const T *__restrict__ p, const T *__restrict__ r,
@@ -554,8 +583,8 @@ namespace mgb
       MGB_DG_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
       MGB_DG_CHECK(cudaEventCreate(&ev[0]));
       MGB_DG_CHECK(cudaEventCreate(&ev[1]));
-      MGB_DG_CHECK(cudaMalloc(&scal_dev, 4 * sizeof(double)));
-      MGB_DG_CHECK(cudaMallocHost(&scal_host, 4 * sizeof(double)));
+      MGB_DG_CHECK(cudaMalloc(&scal_dev, 8 * sizeof(double)));
+      MGB_DG_CHECK(cudaMallocHost(&scal_host, 8 * sizeof(double)));
       if (borrowed)
         comm = borrowed;
       else if (n_ranks > 1)
@@ -575,6 +604,12 @@ namespace mgb
           if (ev[i])
             cudaEventDestroy(ev[i]);
         }
+      for (int k = 0; k < 2; ++k)
+        for (int i = 0; i < 3; ++i)
+          if (cg_ws[k][i])
+            cudaFree(cg_ws[k][i]);
+      if (cg_partial)
+        cudaFree(cg_partial);
       if (scal_dev)
         cudaFree(scal_dev);
       if (scal_host)
@@ -893,9 +928,11 @@ namespace mgb
 
     template <typename T>
     void
-    apply(const int mode, T *dst, const T *src, const T *rhs = nullptr, const double f1 = 0, const double f2 = 0)
+    apply(const int mode, T *dst, const T *src, const T *rhs = nullptr, const double f1 = 0, const double f2 = 0,
+          const T *diagonal_preconditioner = nullptr, double *partial = nullptr)
     {
       DGArgs<T> A;
+      A.partial = partial;
       for (int d = 0; d < 3; ++d)
         {
           A.nc[d]    = nc[d];
@@ -913,8 +950,15 @@ namespace mgb
       A.src      = src;
       A.dst      = dst;
       A.rhs      = rhs;
-      A.inv_diag = (mode >= DG_CHEBYSHEV && preconditioner == 0) ? get_inverse_diagonal<T>() : nullptr;
-      A.jt_dinv  = (mode >= DG_CHEBYSHEV && preconditioner == 1) ? get_jt_dinv<T>() : nullptr;
+      const bool chebyshev = mode == DG_CHEBYSHEV || mode == DG_CHEBYSHEV_FIRST;
+      A.inv_diag = (chebyshev && preconditioner == 0) ? get_inverse_diagonal<T>() : nullptr;
+      A.jt_dinv  = (chebyshev && preconditioner == 1) ? get_jt_dinv<T>() : nullptr;
+      if (mode == DG_SET_SUMS)
+        {
+          if (n_ranks > 1)
+            throw std::runtime_error("the interleaved CG runs on one GPU");
+          A.inv_diag = diagonal_preconditioner;
+        }
       A.f1       = (T)f1;
       A.f2       = (T)f2;
       A.mode     = mode;
@@ -999,6 +1043,146 @@ namespace mgb
       MGB_DG_CHECK(cudaStreamSynchronize(stream));
       for (int s = 0; s < 4; ++s)
         sums[s] = scal_host[s];
+    }
+
+    // solver_dg/program.cc:180-262: SolverCG with IterationNumberControl(n_iterations, 1e-20) from x = 0 on this operator
+    // with a diagonal preconditioner (there: the inverse of the lumped mass matrix).
+    // interleaved = false, "cell-based loops" (:216-227): operator apply, then the vector updates and dot products as
+    // separate passes.  interleaved = true, "interleaved loops" (LaplaceOperatorInterleave, :39-70, :237-248): deal.II's
+    // SolverCG hands the vector updates to the operator's loop; here one vector kernel before the apply
+    // (x += alpha p, r -= alpha v, p = D r + beta p) and the sums p.v, v.Dr, v.Dv, r.v, v.v in the apply's store stage,
+    // from which alpha, beta = (r.Dr - 2 alpha v.Dr + alpha^2 v.Dv) / r.Dr and |r|^2 follow without another pass.
+    // stats = {iterations done, last residual norm}
+    void   *cg_ws[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+    double *cg_partial  = nullptr;
+    template <typename T>
+    void
+    solve_cg_diagonal(const unsigned int n_iterations, const bool interleaved, T *x, const T *b, const T *D, double stats[2])
+    {
+      const size_t N = n_dofs;
+      const int    k = sizeof(T) == 8;
+      for (int i = 0; i < 3; ++i)
+        if (!cg_ws[k][i])
+          MGB_DG_CHECK(cudaMalloc(&cg_ws[k][i], N * sizeof(T)));
+      T *r = (T *)cg_ws[k][0], *pp = (T *)cg_ws[k][1], *v = (T *)cg_ws[k][2];
+      MGB_DG_CHECK(cudaMemsetAsync(x, 0, N * sizeof(T), stream));
+      double sum[4];
+      sums<2>(sum, [=] __device__(size_t i, double *acc) {
+        const T ri = b[i], zi = D[i] * ri;
+        r[i]       = ri;
+        pp[i]      = zi;
+        acc[0] += (double)ri * zi;
+        acc[1] += (double)ri * ri;
+      });
+      double       rz = sum[0], rr = sum[1];
+      unsigned int it = 0;
+      if (!interleaved)
+        {
+          while (it < n_iterations && std::sqrt(rr) > 1e-20)
+            {
+              ++it;
+              apply<T>(DG_SET, v, pp);
+              sums<1>(sum, [=] __device__(size_t i, double *acc) { acc[0] += (double)pp[i] * v[i]; });
+              const T alpha = (T)(rz / sum[0]);
+              sums<2>(sum, [=] __device__(size_t i, double *acc) {
+                x[i] += alpha * pp[i];
+                const T ri = r[i] - alpha * v[i];
+                r[i]       = ri;
+                acc[0] += (double)ri * (D[i] * ri);
+                acc[1] += (double)ri * ri;
+              });
+              const T beta = (T)(sum[0] / rz);
+              rz           = sum[0];
+              rr           = sum[1];
+              foreach (N, [=] __device__(size_t i) { pp[i] = D[i] * r[i] + beta * pp[i]; });
+            }
+        }
+      else
+        {
+          if (n_ranks > 1)
+            throw std::runtime_error("the interleaved CG runs on one GPU");
+          const int    tpc = ((n * n + 31) / 32) * 32, cpb = tpc >= 128 ? 1 : 128 / tpc; // DGCfg<p>
+          const size_t n_blocks = ((size_t)nc[0] * nc[1] * lz + cpb - 1) / cpb;
+          if (!cg_partial)
+            MGB_DG_CHECK(cudaMalloc(&cg_partial, n_blocks * 5 * sizeof(double)));
+          double alpha = 0, beta = 0;
+          while (it < n_iterations && std::sqrt(std::fabs(rr)) > 1e-20)
+            {
+              if (it > 0)
+                {
+                  const T a = (T)alpha, be = (T)beta;
+                  foreach (N, [=] __device__(size_t i) {
+                    const T pi = pp[i];
+                    x[i] += a * pi;
+                    const T ri = r[i] - a * v[i];
+                    r[i]       = ri;
+                    pp[i]      = D[i] * ri + be * pi;
+                  });
+                }
+              ++it;
+              apply<T>(DG_SET_SUMS, v, pp, r, 0., 0., D, cg_partial);
+              MGB_DG_CHECK(cudaMemsetAsync(scal_dev, 0, 8 * sizeof(double), stream));
+              k_dg_sum_partials<<<(unsigned)std::min<size_t>((n_blocks + 255) / 256, 296), 256, 0, stream>>>(n_blocks, cg_partial,
+                                                                                                          scal_dev);
+              ++launches;
+              MGB_DG_CHECK(cudaMemcpyAsync(scal_host, scal_dev, 5 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+              MGB_DG_CHECK(cudaStreamSynchronize(stream));
+              const double pv = scal_host[0], vDr = scal_host[1], vDv = scal_host[2], rv = scal_host[3], vv = scal_host[4];
+              alpha               = rz / pv;
+              const double rz_new = rz - 2. * alpha * vDr + alpha * alpha * vDv;
+              rr                  = rr - 2. * alpha * rv + alpha * alpha * vv;
+              beta                = rz_new / rz;
+              rz                  = rz_new;
+            }
+          if (it > 0)
+            {
+              const T a = (T)alpha;
+              foreach (N, [=] __device__(size_t i) {
+                x[i] += a * pp[i];
+                r[i] -= a * v[i];
+              });
+            }
+        }
+      MGB_DG_CHECK(cudaStreamSynchronize(stream));
+      stats[0] = it;
+      stats[1] = std::sqrt(std::fabs(rr));
+    }
+
+    // |det J| of the (affine) cells
+    double
+    cell_volume() const
+    {
+      double J[3][3];
+      for (int k = 0; k < 3; ++k)
+        for (int d = 0; d < 3; ++d)
+          J[k][d] = opt.trafo[k * 3 + d] * (opt.upper[d] - opt.lower[d]) / nc[d];
+      return std::fabs(J[0][0] * (J[1][1] * J[2][2] - J[1][2] * J[2][1]) - J[0][1] * (J[1][0] * J[2][2] - J[1][2] * J[2][0]) +
+                       J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]));
+    }
+
+    // the diagonal of solver_dg/program.cc:134-148: 1 / (1, phi_i), the inverse of the lumped mass matrix
+    template <typename T>
+    void
+    lumped_mass_inverse(T *out)
+    {
+      std::vector<double> col(n, 0.);
+      for (int i = 0; i < n; ++i)
+        for (int q = 0; q < n; ++q)
+          col[i] += basis.wq[q] * basis.S[q * n + i];
+      const int      n3 = n * n * n;
+      std::vector<T> cellv(n3);
+      const double   detJ = cell_volume();
+      for (int i2 = 0; i2 < n; ++i2)
+        for (int i1 = 0; i1 < n; ++i1)
+          for (int i0 = 0; i0 < n; ++i0)
+            cellv[(i2 * n + i1) * n + i0] = (T)(1. / (detJ * col[i0] * col[i1] * col[i2]));
+      T *dev = nullptr;
+      MGB_DG_CHECK(cudaMalloc(&dev, n3 * sizeof(T)));
+      MGB_DG_CHECK(cudaMemcpyAsync(dev, cellv.data(), n3 * sizeof(T), cudaMemcpyHostToDevice, stream));
+      const T *cv = dev;
+      foreach (n_dofs, [=] __device__(size_t i) { out[i] = cv[i % n3]; });
+      MGB_DG_CHECK(cudaStreamSynchronize(stream));
+      cudaFree(dev);
     }
 
     // laplace_operator_dg.h:907-955 with the point-Jacobi preconditioner
@@ -1394,6 +1578,35 @@ extern "C"
     float t = 0;
     MGB_DG_CHECK(cudaEventElapsedTime(&t, o.ev[0], o.ev[1]));
     *ms = t;
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_lumped_mass_inverse(mgb_dg h, int precision, void *out)
+  {
+    DG_TRY
+    check_precision(precision);
+    if (precision == MGB_F64)
+      DGH(h).lumped_mass_inverse<double>((double *)out);
+    else
+      DGH(h).lumped_mass_inverse<float>((float *)out);
+    DG_CATCH
+  }
+
+  int
+  mgb_dg_solve_cg(mgb_dg h, int precision, unsigned int n_iterations, int interleaved, void *x, const void *b,
+                  const void *diagonal_preconditioner, double stats[2])
+  {
+    DG_TRY
+    check_precision(precision);
+    if (!x || !b || !diagonal_preconditioner || !stats)
+      throw std::runtime_error("null argument");
+    if (precision == MGB_F64)
+      DGH(h).solve_cg_diagonal<double>(n_iterations, interleaved != 0, (double *)x, (const double *)b,
+                                       (const double *)diagonal_preconditioner, stats);
+    else
+      DGH(h).solve_cg_diagonal<float>(n_iterations, interleaved != 0, (float *)x, (const float *)b,
+                                      (const float *)diagonal_preconditioner, stats);
     DG_CATCH
   }
 

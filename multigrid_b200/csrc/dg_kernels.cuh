@@ -30,7 +30,10 @@ namespace mgb
     DG_SET = 0,             // dst = A src                                   (action 0)
     DG_RESIDUAL = 1,        // dst = rhs - A src                             (action 4)
     DG_CHEBYSHEV = 2,       // dst = (1+f1) src - f1 dst + f2 P^-1 (rhs - A src)   (action 3, iteration_index > 1)
-    DG_CHEBYSHEV_FIRST = 3  // dst = (1+f1) src + f2 P^-1 (rhs - A src)            (action 3, iteration_index == 1)
+    DG_CHEBYSHEV_FIRST = 3, // dst = (1+f1) src + f2 P^-1 (rhs - A src)            (action 3, iteration_index == 1)
+    DG_SET_SUMS = 4         // dst = v = A src and, per block, the five sums of the interleaved CG with the diagonal
+                            // preconditioner D = inv_diag and the residual r = rhs (solver_dg/program.cc:39-70: the
+                            // operation_after_loop of deal.II's SolverCG): src.v, v.D r, v.D v, r.v, v.v -> partial[block][5]
   };
 
   template <typename T, int n>
@@ -60,6 +63,7 @@ namespace mgb
     const T *jt_dinv;  // JacobiTransformed: 1 / diag(V^T A_KK V) per cell type [64][n^3]; nullptr: point Jacobi
     T        f1, f2;
     int      mode;
+    double  *partial;  // DG_SET_SUMS: [blocks][5]
     T        gt[6];    // detJ J^-1 J^-T: 00 11 22 01 02 12
     T        gs[3][3]; // gs[d][e] = grad xi_d . grad xi_e / |grad xi_d|
     T        sigma[3]; // (p+1)^2 |grad xi_d|
@@ -620,6 +624,43 @@ namespace mgb
                 r -= A.f1 * A.dst[off + i];
               A.dst[off + i] = r;
             }
+        return;
+      }
+    if (A.mode == DG_SET_SUMS)
+      {
+        double acc[5] = {0, 0, 0, 0, 0};
+        if (valid)
+          {
+            const size_t off = (size_t)c * n3;
+            for (int i = t; i < n3; i += TPC)
+              {
+                const double v = y_s[i], r = A.rhs[off + i], dv = (double)A.inv_diag[off + i] * v;
+                acc[0] += (double)u_s[i] * v;
+                acc[1] += dv * r;
+                acc[2] += dv * v;
+                acc[3] += r * v;
+                acc[4] += v * v;
+                A.dst[off + i] = y_s[i];
+              }
+          }
+        __shared__ double red[5][C::NT / 32];
+#pragma unroll
+        for (int s = 0; s < 5; ++s)
+          {
+            double v = acc[s];
+            for (int o = 16; o > 0; o >>= 1)
+              v += __shfl_down_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0)
+              red[s][threadIdx.x >> 5] = v;
+          }
+        __syncthreads();
+        if (threadIdx.x < 5)
+          {
+            double v = 0;
+            for (int w = 0; w < C::NT / 32; ++w)
+              v += red[threadIdx.x][w];
+            A.partial[(size_t)blockIdx.x * 5 + threadIdx.x] = v;
+          }
         return;
       }
     if (valid)

@@ -198,3 +198,57 @@ def test_dg_fe_q_transfer(mgb, orc, torch, mesh, precision):
     # transpose property: <P c, d> = <c, P^T d> on unconstrained entries
     c2 = rng.random(s.n_dofs(L)) * mask
     assert abs(((c2)[lex]) @ res - c2 @ ref_lex) <= 1e-10 * abs(c2 @ ref_lex)
+
+
+CG_MESHES = [  # p, n_subdivisions, n_refinements, sheared, basis
+    (3, (2, 1, 1), 1, True, 2),      # solver_dg/program.cc: degree 3, FE_DGQArbitraryNodes(QGauss), sheared mesh
+    (4, (1, 1, 1), 1, True, 0), (2, (2, 2, 1), 1, False, 1), (5, (1, 2, 1), 0, True, 2), (7, (1, 1, 1), 1, True, 2),
+]
+
+
+@pytest.mark.parametrize("precision", [1, 0])
+@pytest.mark.parametrize("mesh", CG_MESHES)
+def test_cg_solver_plain_and_interleaved(mgb, orc, torch, mesh, precision):
+    """solver_dg/program.cc:180-262: n iterations of CG with the inverse lumped mass matrix as preconditioner; the
+    cell-based and the interleaved loop against a numpy CG on the oracle's operator (the program's own verification is
+    the difference of the variants, :229-230)"""
+    p, nsub, nref, sheared, basis = mesh
+    trafo = orc.dg_trafo() if sheared else np.eye(3)
+    g = mgb.LaplaceOperatorDG(p, nsub, nref, trafo=trafo, precision=precision, basis=basis)
+    nc = [s << nref for s in nsub]
+    o = orc.DGOperator(p, nc, trafo=trafo, basis=basis)
+    t = o.tables
+    col = t["wq"] @ t["S"]                                        # (1, phi_i) in 1-D
+    h = [(o.upper[d] - o.lower[d]) / nc[d] for d in range(3)]
+    detJ = abs(np.linalg.det(np.asarray(trafo).reshape(3, 3) @ np.diag(h)))
+    D = 1. / (detJ * np.einsum("k,j,i->kji", col, col, col).ravel())
+    D = np.tile(D, o.n_dofs() // D.size)
+    dD = g.lumped_mass_inverse()
+    assert rel(dD.double().cpu().numpy(), D) <= (1e-14 if precision else 1e-6)
+    rng = np.random.default_rng(7)
+    b = rng.random(o.n_dofs())
+    n_it = 12
+    # reference CG
+    x, r = np.zeros_like(b), b.copy()
+    z = D * r
+    pp, rz = z.copy(), r @ z
+    for _ in range(n_it):
+        v = o.vmult(pp)
+        alpha = rz / (pp @ v)
+        x += alpha * pp
+        r -= alpha * v
+        z = D * r
+        rz_new = r @ z
+        pp = z + (rz_new / rz) * pp
+        rz = rz_new
+    db = torch.tensor(b, dtype=g.dtype, device="cuda")
+    tol = 1e-9 if precision else 2e-3
+    out = {}
+    for interleaved in (False, True):
+        dx = g.initialize_dof_vector()
+        its, res = g.solve_cg(dx, db, dD, n_it, interleaved)
+        assert its == n_it
+        out[interleaved] = dx.double().cpu().numpy()
+        assert rel(out[interleaved], x) <= tol, (interleaved, rel(out[interleaved], x))
+        assert abs(res - np.linalg.norm(r)) <= (1e-7 if precision else 2e-2) * np.linalg.norm(r)
+    assert rel(out[True], out[False]) <= tol
