@@ -467,6 +467,41 @@ int mgb_adaptive_solve_cg(mgb_adaptive h, double *x_dev, const double *rhs_dev, 
                           double *reduction_rate, double *history, int *n_history);
 int64_t mgb_adaptive_launch_count(mgb_adaptive h);
 
+/* ---- The adaptive loop around the solver (LaplaceProblem::run, poisson_l/program.cc:497-602)
+ * Vectors here carry the Dirichlet data in their boundary entries (the reference's `solution`).
+ * refine_and_coarsen: Triangulation::execute_coarsening_and_refinement (:533-541) -- flagged cells are refined (2:1
+ *   balance kept), then every family of eight active siblings all flagged for coarsening is replaced by its parent unless
+ *   the parent would touch a cell more than one level finer; coarsen_flags may be NULL.
+ * refine_and_coarsen_fixed_number: GridRefinement::refine_and_coarsen_fixed_number (:532-533; serial semantics: the
+ *   int(top_fraction N) largest indicators refined, the int(bottom_fraction N) smallest coarsened, ties at the
+ *   thresholds flagged), followed by refine_and_coarsen.  indicators: host array, one float per active cell.
+ * face_neighbours: type[cell][6] (-1 boundary, 0 same level, 1 coarser, 2 four finer) and ids[cell][6][4], faces -x +x
+ *   -y +y -z +z.   plain_table: the cell -> DoF table that keeps Dirichlet DoFs, [cell][(p+1)^3] (rows as mgb_adaptive_tables)
+ * interpolate_boundary_values (:321-333): u = g on the Dirichlet DoFs, zero elsewhere; g: 0 = zero, 1 =
+ *   Functions::LSingularityFunction in (x, y) (program.cc:85-135)
+ * compute_residual (laplace_operator.h:806-845, program.cc:546-549): dst = (f, phi) - K src on rows without Dirichlet
+ *   condition (zero on the others), f constant
+ * estimate_kelly: KellyErrorEstimator<3>::estimate (:524-531) with QGauss<2>(p+1), no Neumann data, strategy
+ *   cell_diameter_over_24: eta_K = sqrt(diameter_K / 24 * sum_F int_F [du/dn]^2); indicators to a host array
+ * integrate_difference: VectorTools::integrate_difference (:556-575) against g; norm 0 = L2, 1 = H1 seminorm, with
+ *   n_q_points Gauss points per direction; cell_squares_host (may be NULL): the cells' squared contributions
+ * solve_cycle: :545-575 for the current mesh -- boundary values, right-hand side, CG with the local-smoothing V-cycle
+ *   (mgb_adaptive_mg_setup(n_smoother) inside), solution = boundary values + update; stats = {CG iterations, rate, L2
+ *   error with QGauss(p+2), H1-seminorm error with QGauss(p+1)}; *solution_dev: device vector owned by the handle, valid
+ *   until the mesh changes                                                                                            */
+int mgb_adaptive_refine_and_coarsen(mgb_adaptive h, const unsigned char *refine_flags, const unsigned char *coarsen_flags);
+int mgb_adaptive_refine_and_coarsen_fixed_number(mgb_adaptive h, const float *indicators, double top_fraction,
+                                                 double bottom_fraction);
+int mgb_adaptive_face_neighbours(mgb_adaptive h, signed char *type, int32_t *ids);
+int mgb_adaptive_plain_table(mgb_adaptive h, int32_t *cell_index_plain);
+int mgb_adaptive_interpolate_boundary_values(mgb_adaptive h, int function_id, double *u_dev);
+int mgb_adaptive_compute_residual(mgb_adaptive h, double *dst_dev, const double *src_dev, double f);
+int mgb_adaptive_estimate_kelly(mgb_adaptive h, const double *u_dev, float *indicators_host);
+int mgb_adaptive_integrate_difference(mgb_adaptive h, const double *u_dev, int function_id, int norm, int n_q_points,
+                                      double *result, double *cell_squares_host);
+int mgb_adaptive_solve_cycle(mgb_adaptive h, int function_id, double f, int n_smoother, double stats[4],
+                             double **solution_dev);
+
 /* The subset of LinearAlgebra::distributed::Vector<Number> the drivers use (poisson_cube/program.cc:262-380,
  * multigrid_solver.h:54-67): device vectors of one level in the precision given; sums run over the owned
  * entries of all ranks.  dot: a . b (l2_norm = sqrt(dot(v,v)));  sadd: y = sy y + ax x;  set: y = value;

@@ -249,6 +249,15 @@ SYMBOLS = {
     "mgb_adaptive_vmult_host": (_i, [_vp, _i, _vp, _vp]),
     "mgb_adaptive_sync": (_i, [_vp]),
     "mgb_adaptive_launch_count": (C.c_int64, [_vp]),
+    "mgb_adaptive_refine_and_coarsen": (_i, [_vp, C.POINTER(C.c_ubyte), C.POINTER(C.c_ubyte)]),
+    "mgb_adaptive_refine_and_coarsen_fixed_number": (_i, [_vp, C.POINTER(C.c_float), _d, _d]),
+    "mgb_adaptive_face_neighbours": (_i, [_vp, C.POINTER(C.c_byte), C.POINTER(C.c_int32)]),
+    "mgb_adaptive_plain_table": (_i, [_vp, C.POINTER(C.c_int32)]),
+    "mgb_adaptive_interpolate_boundary_values": (_i, [_vp, _i, _vp]),
+    "mgb_adaptive_compute_residual": (_i, [_vp, _vp, _vp, _d]),
+    "mgb_adaptive_estimate_kelly": (_i, [_vp, _vp, C.POINTER(C.c_float)]),
+    "mgb_adaptive_integrate_difference": (_i, [_vp, _vp, _i, _i, _i, _dp, _dp]),
+    "mgb_adaptive_solve_cycle": (_i, [_vp, _i, _d, _i, _dp, C.POINTER(_vp)]),
     # host-only helpers
     "mgb_host_basis": (_i, [_i] + [_dp] * 9),
     "mgb_host_numbering": (_i, [_i, _ip, _i, C.POINTER(C.c_int64), _ip, C.POINTER(C.c_int64),
@@ -1401,6 +1410,104 @@ class LaplaceOperatorAdaptive:
         torch.cuda.synchronize()
         _check(lib().mgb_adaptive_inverse_diagonal(self.h, precision, _ptr(out)))
         self.sync()
+
+    # ---- the adaptive loop around the solver (poisson_l/program.cc:497-602)
+    FUNCTION_ZERO, FUNCTION_L_SINGULARITY = 0, 1
+    NORM_L2, NORM_H1_SEMINORM = 0, 1
+
+    def refine_and_coarsen(self, refine_flags, coarsen_flags=None):
+        """execute_coarsening_and_refinement with explicit flags (one per active cell)"""
+        r = np.ascontiguousarray(refine_flags, dtype=np.uint8)
+        c = None if coarsen_flags is None else np.ascontiguousarray(coarsen_flags, dtype=np.uint8)
+        assert r.size == self.n_cells() and (c is None or c.size == r.size)
+        ub = C.POINTER(C.c_ubyte)
+        _check(lib().mgb_adaptive_refine_and_coarsen(self.h, r.ctypes.data_as(ub), None if c is None else c.ctypes.data_as(ub)))
+
+    def refine_and_coarsen_fixed_number(self, indicators, top_fraction, bottom_fraction):
+        """GridRefinement::refine_and_coarsen_fixed_number + execute_coarsening_and_refinement (:532-541)"""
+        e = np.ascontiguousarray(indicators, dtype=np.float32)
+        assert e.size == self.n_cells()
+        _check(lib().mgb_adaptive_refine_and_coarsen_fixed_number(self.h, e.ctypes.data_as(C.POINTER(C.c_float)),
+                                                                  float(top_fraction), float(bottom_fraction)))
+
+    def face_neighbours(self):
+        t = np.zeros((self.n_cells(), 6), dtype=np.int8)
+        ids = np.zeros((self.n_cells(), 6, 4), dtype=np.int32)
+        _check(lib().mgb_adaptive_face_neighbours(self.h, t.ctypes.data_as(C.POINTER(C.c_byte)),
+                                                  ids.ctypes.data_as(C.POINTER(C.c_int32))))
+        return t, ids
+
+    def plain_table(self):
+        """cell -> DoF table that keeps the Dirichlet DoFs (rows refer to the CSR list of tables())"""
+        ci = np.zeros((self.n_cells(), (self.degree + 1) ** 3), dtype=np.int32)
+        _check(lib().mgb_adaptive_plain_table(self.h, ci.ctypes.data_as(C.POINTER(C.c_int32))))
+        return ci
+
+    def interpolate_boundary_values(self, u, function=1):
+        import torch
+        torch.cuda.synchronize()
+        _check(lib().mgb_adaptive_interpolate_boundary_values(self.h, int(function), _ptr(u)))
+
+    def compute_residual(self, dst, src, f=0.):
+        """dst = (f, phi) - K src on the rows without Dirichlet condition; src carries the boundary values"""
+        import torch
+        torch.cuda.synchronize()
+        _check(lib().mgb_adaptive_compute_residual(self.h, _ptr(dst), _ptr(src), float(f)))
+        self.sync()
+
+    def estimate_kelly(self, u):
+        """KellyErrorEstimator::estimate (:524-531) -> float32 indicator per active cell"""
+        import torch
+        torch.cuda.synchronize()
+        out = np.zeros(self.n_cells(), dtype=np.float32)
+        _check(lib().mgb_adaptive_estimate_kelly(self.h, _ptr(u), out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
+
+    def integrate_difference(self, u, function=1, norm=0, n_q_points=None, per_cell=False):
+        """VectorTools::integrate_difference (:556-575) -> norm (and the cells' squared contributions)"""
+        import torch
+        torch.cuda.synchronize()
+        nq = self.degree + (2 if norm == 0 else 1) if n_q_points is None else n_q_points
+        res = C.c_double()
+        sq = np.zeros(self.n_cells()) if per_cell else None
+        _check(lib().mgb_adaptive_integrate_difference(self.h, _ptr(u), int(function), int(norm), int(nq), C.byref(res),
+                                                       sq.ctypes.data_as(_dp) if per_cell else None))
+        return (res.value, sq) if per_cell else res.value
+
+    def solve_cycle(self, function=1, f=0., n_smoother=3):
+        """one cycle of LaplaceProblem::run on the current mesh (:545-575) -> dict(iterations, rate, l2_error, h1_error),
+        the solution as a device tensor view owned by the operator (valid until the mesh changes)"""
+        import torch
+        stats = np.zeros(4)
+        ptr = C.c_void_p()
+        _check(lib().mgb_adaptive_solve_cycle(self.h, int(function), float(f), int(n_smoother), stats.ctypes.data_as(_dp),
+                                              C.byref(ptr)))
+        self.sync()
+        out = dict(iterations=int(stats[0]), rate=stats[1], l2_error=stats[2], h1_error=stats[3], n_cells=self.n_cells(),
+                   n_dofs=self.m())
+        self._solution_ptr = ptr.value
+        return out
+
+    def solution(self):
+        """host copy of the solution of the last solve_cycle"""
+        out = np.zeros(self.m())
+        _check(lib().mgb_copy_to_host(None, C.c_void_p(out.ctypes.data), C.c_void_p(self._solution_ptr), out.nbytes))
+        return out
+
+    def run_adaptive_loop(self, n_cycles, function=1, f=0., n_smoother=3, top_fraction=0.3, bottom_fraction=0.03,
+                          max_size=None):
+        """LaplaceProblem::run (:497-602) from the current mesh: solve, estimate, refine / coarsen, n_cycles times"""
+        table = []
+        for cycle in range(n_cycles):
+            if cycle > 0:
+                import torch
+                u = torch.tensor(self.solution(), device="cuda")
+                eta = self.estimate_kelly(u)
+                self.refine_and_coarsen_fixed_number(eta, top_fraction, bottom_fraction)
+            table.append(self.solve_cycle(function, f, n_smoother))
+            if max_size is not None and table[-1]["n_dofs"] > max_size:
+                break
+        return table
 
     def vmult_host(self, dst_host, src_host, precision=F64):
         _check(lib().mgb_adaptive_vmult_host(self.h, precision, C.c_void_p(dst_host.ctypes.data),

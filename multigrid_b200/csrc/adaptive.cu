@@ -178,6 +178,122 @@ namespace mgb
       cells.swap(next);
       rebuild_index();
     }
+
+    // Triangulation::execute_coarsening_and_refinement (poisson_l/program.cc:533-541): refine the cells flagged for
+    // refinement (keeping the 2:1 balance, which may refine further cells), then replace every family of eight active
+    // siblings that are all flagged for coarsening by their parent, provided the parent would not touch a cell more than
+    // one level finer than itself (judged on the mesh after the refinement, so the outcome does not depend on the order
+    // in which families are visited).  A coarsening flag on a cell that is refined, or whose family is incomplete, lapses.
+    void
+    refine_and_coarsen(const uint8_t *refine_flags, const uint8_t *coarsen_flags)
+    {
+      std::unordered_map<uint64_t, int> flagged; // keys of the cells flagged for coarsening
+      for (size_t i = 0; i < cells.size(); ++i)
+        if (coarsen_flags && coarsen_flags[i] && !refine_flags[i] && cells[i].level > 0)
+          flagged[pack_key(cells[i].level, cells[i].c[0], cells[i].c[1], cells[i].c[2])] = 1;
+      refine(refine_flags);
+      std::unordered_map<uint64_t, int> family; // parent key -> flagged children that are still active
+      for (const ACell &k : cells)
+        if (k.level > 0 && flagged.count(pack_key(k.level, k.c[0], k.c[1], k.c[2])))
+          ++family[pack_key(k.level - 1, k.c[0] >> 1, k.c[1] >> 1, k.c[2] >> 1)];
+      std::vector<ACell> parents;
+      for (const ACell &k : cells)
+        {
+          if (k.level == 0 || (k.c[0] & 1) || (k.c[1] & 1) || (k.c[2] & 1)) // visit a family through its first child
+            continue;
+          const int par[3] = {k.c[0] >> 1, k.c[1] >> 1, k.c[2] >> 1};
+          auto      it     = family.find(pack_key(k.level - 1, par[0], par[1], par[2]));
+          if (it == family.end() || it->second != 8)
+            continue;
+          // the shell of child-level positions around the family: each one inside the domain must be covered by an
+          // active cell of the children's level or coarser
+          bool ok = true;
+          for (int dz = -1; dz <= 2 && ok; ++dz)
+            for (int dy = -1; dy <= 2 && ok; ++dy)
+              for (int dx = -1; dx <= 2 && ok; ++dx)
+                {
+                  if (dx >= 0 && dx <= 1 && dy >= 0 && dy <= 1 && dz >= 0 && dz <= 1)
+                    continue;
+                  const int q[3] = {k.c[0] + dx, k.c[1] + dy, k.c[2] + dz};
+                  if (!inside(k.level, q))
+                    continue;
+                  bool covered = false;
+                  int  r[3]    = {q[0], q[1], q[2]};
+                  for (int l = k.level; l >= 0 && !covered; --l)
+                    {
+                      covered = find(l, r) >= 0;
+                      for (int d = 0; d < 3; ++d)
+                        r[d] >>= 1;
+                    }
+                  ok = covered;
+                }
+          if (ok)
+            parents.push_back(ACell{k.level - 1, {par[0], par[1], par[2]}});
+        }
+      if (parents.empty())
+        return;
+      std::unordered_map<uint64_t, int> gone;
+      for (const ACell &P : parents)
+        gone[pack_key(P.level, P.c[0], P.c[1], P.c[2])] = 1;
+      std::vector<ACell> next;
+      next.reserve(cells.size());
+      for (const ACell &k : cells)
+        if (k.level == 0 || !gone.count(pack_key(k.level - 1, k.c[0] >> 1, k.c[1] >> 1, k.c[2] >> 1)))
+          next.push_back(k);
+      next.insert(next.end(), parents.begin(), parents.end());
+      cells.swap(next);
+      rebuild_index();
+    }
+
+    // face neighbours of every active cell: faces 0..5 = -x, +x, -y, +y, -z, +z.  type -1: boundary; 0: one neighbour of the
+    // same level; 1: one neighbour twice as large; 2: four neighbours half as large (in the order of their position in
+    // the two tangential directions, first tangential direction fastest).  ids[cell][face][4].
+    void
+    face_neighbours(std::vector<int8_t> &type, std::vector<int32_t> &ids) const
+    {
+      type.assign(cells.size() * 6, -1);
+      ids.assign(cells.size() * 24, -1);
+      for (size_t c = 0; c < cells.size(); ++c)
+        {
+          const ACell &K = cells[c];
+          for (int f = 0; f < 6; ++f)
+            {
+              const int d = f / 2, side = f % 2;
+              int       q[3] = {K.c[0], K.c[1], K.c[2]};
+              q[d] += side ? 1 : -1;
+              if (!inside(K.level, q))
+                continue;
+              int j = find(K.level, q);
+              if (j >= 0)
+                {
+                  type[c * 6 + f]    = 0;
+                  ids[c * 24 + f * 4] = j;
+                  continue;
+                }
+              const int par[3] = {q[0] >> 1, q[1] >> 1, q[2] >> 1};
+              j                = K.level > 0 ? find(K.level - 1, par) : -1;
+              if (j >= 0)
+                {
+                  type[c * 6 + f]    = 1;
+                  ids[c * 24 + f * 4] = j;
+                  continue;
+                }
+              const int t1 = d == 0 ? 1 : 0, t2 = d == 2 ? 1 : 2;
+              type[c * 6 + f] = 2;
+              for (int s = 0; s < 4; ++s)
+                {
+                  int r[3];
+                  r[d]  = 2 * q[d] + (side ? 0 : 1);
+                  r[t1] = 2 * q[t1] + (s & 1);
+                  r[t2] = 2 * q[t2] + (s >> 1);
+                  const int ch = find(K.level + 1, r);
+                  if (ch < 0)
+                    throw std::runtime_error("the mesh is not 2:1 balanced across a face");
+                  ids[c * 24 + f * 4 + s] = ch;
+                }
+            }
+        }
+    }
   };
 
   // ------------------------------------------------------------------ numbering and constraints
@@ -195,7 +311,9 @@ namespace mgb
     std::unordered_map<uint64_t, int> dof_of_key;  // canonical (level, node index) -> DoF
     std::vector<uint8_t> dirichlet;                // per DoF
     std::vector<double>  points;                   // per DoF: x, y, z
-    std::vector<int32_t> cell_index;               // [cell][n^3]
+    std::vector<int32_t> cell_index;               // [cell][n^3], Dirichlet DoFs read as zero (the operator's table)
+    std::vector<int32_t> cell_index_plain;         // [cell][n^3], Dirichlet DoFs kept: values of a vector that carries the
+                                                   // boundary data (compute_residual, error estimator, error norms)
     std::vector<int32_t> row_start;                // constraint rows
     std::vector<int32_t> row_dof;
     std::vector<double>  row_w;
@@ -318,7 +436,7 @@ namespace mgb
       return id;
     }
 
-    // value at node (level, nd) as a combination of DoFs; Dirichlet DoFs are dropped (homogeneous data)
+    // value at node (level, nd) as a combination of DoFs (Dirichlet DoFs included; build() drops them for the operator)
     void
     resolve(const int level, const int nd[3], const double weight, std::vector<Term> &out)
     {
@@ -328,8 +446,7 @@ namespace mgb
         {
           int       q[3] = {nd[0], nd[1], nd[2]};
           const int id   = regular_dof(level, q);
-          if (!dirichlet[id])
-            out.push_back(Term{id, weight});
+          out.push_back(Term{id, weight});
           return;
         }
       // weights of the coarse cell's nodes: 1-D Lagrange polynomials at the node's position inside the coarse cell
@@ -367,8 +484,31 @@ namespace mgb
       gll           = b.nodes;
       gll_ld.assign(b.nodes.begin(), b.nodes.end());
       cell_index.assign(mesh.cells.size() * (size_t)n3, -1);
+      cell_index_plain.assign(mesh.cells.size() * (size_t)n3, -1);
       row_start.assign(1, 0);
-      std::vector<Term> terms;
+      std::vector<Term> terms, merged, kept;
+      // table entry of a combination of DoFs: -1 (nothing), a DoF (weight one) or a row of the CSR list
+      const auto encode = [&](const std::vector<Term> &t) -> int32_t {
+        if (t.empty())
+          return -1;
+        if (t.size() == 1 && std::fabs(t[0].w - 1.) < 1e-13)
+          return t[0].dof;
+        std::vector<std::pair<int, int64_t>> sig;
+        for (const Term &e : t)
+          sig.emplace_back(e.dof, (int64_t)std::llround(e.w * 1e13));
+        auto it = row_cache.find(sig);
+        if (it != row_cache.end())
+          return -2 - it->second;
+        const int row = (int)row_start.size() - 1;
+        for (const Term &e : t)
+          {
+            row_dof.push_back(e.dof);
+            row_w.push_back(e.w);
+          }
+        row_start.push_back((int32_t)row_dof.size());
+        row_cache[sig] = row;
+        return -2 - row;
+      };
       for (size_t c = 0; c < mesh.cells.size(); ++c)
         {
           const ACell &K = mesh.cells[c];
@@ -378,59 +518,38 @@ namespace mgb
                 {
                   const int nd[3] = {K.c[0] * p + i, K.c[1] * p + j, K.c[2] * p + k};
                   terms.clear();
-                  int  cp[3];
-                  const bool hanging = coarser_cell_at(K.level, nd, cp) >= 0;
-                  int32_t    entry   = -1;
+                  int          cp[3];
+                  const bool   hanging = coarser_cell_at(K.level, nd, cp) >= 0;
+                  const size_t slot    = c * (size_t)n3 + (size_t)(k * n + j) * n + i;
                   if (!hanging)
                     {
                       int       q[3] = {nd[0], nd[1], nd[2]};
                       const int id   = regular_dof(K.level, q);
-                      entry          = dirichlet[id] ? -1 : id;
+                      cell_index[slot]       = dirichlet[id] ? -1 : id;
+                      cell_index_plain[slot] = id;
+                      continue;
                     }
-                  else
-                    {
-                      ++n_hanging;
-                      resolve(K.level, nd, 1., terms);
-                      // merge equal DoFs
-                      std::sort(terms.begin(), terms.end(), [](const Term &a, const Term &b) { return a.dof < b.dof; });
-                      std::vector<Term> merged;
-                      for (const Term &t : terms)
-                        if (!merged.empty() && merged.back().dof == t.dof)
-                          merged.back().w += t.w;
-                        else
-                          merged.push_back(t);
-                      terms.clear();
-                      for (const Term &t : merged)
-                        if (std::fabs(t.w) > 1e-14)
-                          terms.push_back(t);
-                      if (terms.empty())
-                        entry = -1;
-                      else if (terms.size() == 1 && std::fabs(terms[0].w - 1.) < 1e-13)
-                        entry = terms[0].dof;
-                      else
-                        {
-                          std::vector<std::pair<int, int64_t>> sig;
-                          for (const Term &t : terms)
-                            sig.emplace_back(t.dof, (int64_t)std::llround(t.w * 1e13));
-                          auto it = row_cache.find(sig);
-                          int  row;
-                          if (it != row_cache.end())
-                            row = it->second;
-                          else
-                            {
-                              row = (int)row_start.size() - 1;
-                              for (const Term &t : terms)
-                                {
-                                  row_dof.push_back(t.dof);
-                                  row_w.push_back(t.w);
-                                }
-                              row_start.push_back((int32_t)row_dof.size());
-                              row_cache[sig] = row;
-                            }
-                          entry = -2 - row;
-                        }
-                    }
-                  cell_index[c * (size_t)n3 + (size_t)(k * n + j) * n + i] = entry;
+                  ++n_hanging;
+                  resolve(K.level, nd, 1., terms);
+                  // merge equal DoFs
+                  std::sort(terms.begin(), terms.end(), [](const Term &a, const Term &b) { return a.dof < b.dof; });
+                  merged.clear();
+                  for (const Term &t : terms)
+                    if (!merged.empty() && merged.back().dof == t.dof)
+                      merged.back().w += t.w;
+                    else
+                      merged.push_back(t);
+                  terms.clear();
+                  kept.clear();
+                  for (const Term &t : merged)
+                    if (std::fabs(t.w) > 1e-14)
+                      {
+                        terms.push_back(t);
+                        if (!dirichlet[t.dof])
+                          kept.push_back(t);
+                      }
+                  cell_index[slot]       = encode(kept);
+                  cell_index_plain[slot] = kept.size() == terms.size() ? cell_index[slot] : encode(terms);
                 }
         }
       row_cache.clear();
@@ -448,3 +567,4 @@ namespace mgb
 
 #include "adaptive_kernels.cuh"
 #include "adaptive_solver.cuh"
+#include "adaptive_estimate.cuh"

@@ -321,6 +321,16 @@ namespace mgb
         mg_deleter(mg);
       mg = nullptr;
     }
+    // device tables of the error estimator and the error norms (adaptive_estimate.cuh); dropped with the device data
+    void *est                   = nullptr;
+    void (*est_deleter)(void *) = nullptr;
+    void
+    drop_estimate()
+    {
+      if (est && est_deleter)
+        est_deleter(est);
+      est = nullptr;
+    }
 
     ~AdaptiveOperator()
     {
@@ -352,6 +362,7 @@ namespace mgb
     void
     release_device()
     {
+      drop_estimate();
       if (!on_device)
         return;
       for (void *ptr : {(void *)d_cell_index, (void *)d_row_start, (void *)d_row_dof, (void *)d_dir_list, (void *)d_cell_dof_start,

@@ -434,3 +434,225 @@ class LocalSmoothingOracle:
                 gh = gh_new
                 d = beta * d - h
         return x, it, np.array(hist)
+
+
+# ======================================================================================================================
+# The adaptive loop around the solver (poisson_l/program.cc:497-602): boundary data, right-hand side, Kelly error
+# estimator, fixed-number refinement and coarsening, error norms.  Geometric like the classes above; small meshes only.
+# ======================================================================================================================
+def lagrange_derivative(nodes, x):
+    """derivatives of all Lagrange polynomials on `nodes` at the points x: shape (len(x), len(nodes))"""
+    x = np.atleast_1d(x)
+    out = np.zeros((x.size, nodes.size))
+    for i in range(nodes.size):
+        for m in range(nodes.size):
+            if m == i:
+                continue
+            t = np.ones(x.size) / (nodes[i] - nodes[m])
+            for l in range(nodes.size):
+                if l != i and l != m:
+                    t *= (x - nodes[l]) / (nodes[i] - nodes[l])
+            out[:, i] += t
+    return out
+
+
+def l_singularity(x, y, z=None):
+    """deal.II Functions::LSingularityFunction (the exact solution of poisson_l/program.cc:85-135)"""
+    phi = np.arctan2(y, -x) + np.pi
+    r2 = x * x + y * y
+    return np.where((x >= 0) & (y >= 0), 0., r2 ** (1. / 3.) * np.sin(2. / 3. * phi))
+
+
+def l_singularity_gradient(x, y, z=None):
+    phi = np.arctan2(y, -x) + np.pi
+    r43 = (x * x + y * y) ** (2. / 3.)
+    gx = 2. / 3. * (np.sin(2. / 3. * phi) * x + np.cos(2. / 3. * phi) * y) / r43
+    gy = 2. / 3. * (np.sin(2. / 3. * phi) * y - np.cos(2. / 3. * phi) * x) / r43
+    out = (x >= 0) & (y >= 0)
+    return np.where(out, 0., gx), np.where(out, 0., gy), np.zeros_like(gx)
+
+
+def gauss_01(nq):
+    x, w = np.polynomial.legendre.leggauss(nq)
+    return 0.5 * (x + 1), 0.5 * w
+
+
+class AdaptiveLoopOracle(AdaptiveOracle):
+    def cell_values(self, u):
+        """nodal values of every cell, hanging nodes interpolated, Dirichlet values kept: (cells, n^3)"""
+        return np.stack([self.C[self.cell_nodes[c]] @ u for c in range(self.lo.shape[0])])
+
+    def boundary_values(self, fn):
+        """interpolate_boundary_values (:321-333): fn on the Dirichlet DoFs, zero elsewhere"""
+        u = np.zeros(self.n_dofs())
+        P = self.points[self.dirichlet]
+        u[self.dirichlet] = fn(P[:, 0], P[:, 1], P[:, 2])
+        return u
+
+    def compute_residual(self, u, f=0.):
+        """(f, phi) - K u on the rows without Dirichlet condition (laplace_operator.h:806-845)"""
+        xq, wq = gauss_01(self.n)
+        m1 = wq @ lagrange(self.gll, xq)
+        m3 = np.einsum("c,b,a->cba", m1, m1, m1).ravel()
+        load = np.zeros(self.n_dofs())
+        for c in range(self.lo.shape[0]):
+            load += self.C[self.cell_nodes[c]].T @ (np.prod(self.sz[c]) * m3)
+        r = f * load - self.K_free @ u
+        r[self.dirichlet] = 0
+        return r
+
+    def evaluate(self, vals_c, c, X):
+        """value and gradient of the polynomial of cell c (nodal values vals_c) at physical points X (m, 3)"""
+        n = self.n
+        xi = (X - self.lo[c]) / self.sz[c]
+        L = [lagrange(self.gll, xi[:, d]) for d in range(3)]
+        D = [lagrange_derivative(self.gll, xi[:, d]) / self.sz[c, d] for d in range(3)]
+        V = vals_c.reshape(n, n, n)
+        val = np.einsum("mk,mj,mi,kji->m", L[2], L[1], L[0], V)
+        g = [np.einsum("mk,mj,mi,kji->m", L[2], L[1], D[0], V), np.einsum("mk,mj,mi,kji->m", L[2], D[1], L[0], V),
+             np.einsum("mk,mj,mi,kji->m", D[2], L[1], L[0], V)]
+        return val, g
+
+    def _cell_at(self, point):
+        hit = np.where(np.all((point > self.lo) & (point < self.lo + self.sz), axis=1))[0]
+        return int(hit[0]) if hit.size else -1
+
+    def kelly(self, u):
+        """KellyErrorEstimator::estimate with QGauss(p+1) on the faces, strategy cell_diameter_over_24, no Neumann data
+        (:524-531): eta_K = sqrt(diameter_K / 24 * sum over the faces of int_F [du/dn]^2); a face between cells of
+        different size is integrated over the small cells' faces and counted on both sides"""
+        vals = self.cell_values(u)
+        xq, wq = gauss_01(self.n)
+        nc = self.lo.shape[0]
+        eps = 1e-3 * self.sz.min()
+
+        def face_integral(small, d, side, other):
+            t1, t2 = [k for k in range(3) if k != d]
+            A, B = np.meshgrid(xq, xq, indexing="ij")
+            X = np.zeros((A.size, 3))
+            X[:, d] = self.lo[small, d] + (self.sz[small, d] if side else 0.)
+            X[:, t1] = self.lo[small, t1] + self.sz[small, t1] * A.ravel()
+            X[:, t2] = self.lo[small, t2] + self.sz[small, t2] * B.ravel()
+            W = np.outer(wq, wq).ravel() * self.sz[small, t1] * self.sz[small, t2]
+            _, g1 = self.evaluate(vals[small], small, X)
+            _, g2 = self.evaluate(vals[other], other, X)
+            return float(W @ (g1[d] - g2[d]) ** 2)
+
+        eta = np.zeros(nc)
+        for c in range(nc):
+            total = 0.
+            for d in range(3):
+                t1, t2 = [k for k in range(3) if k != d]
+                for side in (0, 1):
+                    nbs = []
+                    for a in (0.25, 0.75):
+                        for b in (0.25, 0.75):
+                            P = self.lo[c].copy()
+                            P[d] += self.sz[c, d] + eps if side else -eps
+                            P[t1] += a * self.sz[c, t1]
+                            P[t2] += b * self.sz[c, t2]
+                            nbs.append(self._cell_at(P))
+                    if nbs[0] < 0:
+                        continue                                   # boundary face
+                    if len(set(nbs)) == 1:                         # same size or larger
+                        total += face_integral(c, d, side, nbs[0])
+                    else:                                          # four smaller neighbours: their faces
+                        for nb in nbs:
+                            total += face_integral(nb, d, 1 - side, c)
+            eta[c] = np.sqrt(np.linalg.norm(self.sz[c]) / 24. * total)
+        return eta
+
+    def integrate_difference(self, u, fn, grad, norm, nq):
+        """VectorTools::integrate_difference (:556-575): L2 (norm 0) or H1 seminorm (norm 1) -> (norm, cell squares)"""
+        vals = self.cell_values(u)
+        xq, wq = gauss_01(nq)
+        K, J, I = np.meshgrid(xq, xq, xq, indexing="ij")
+        W = np.einsum("c,b,a->cba", wq, wq, wq).ravel()
+        sq = np.zeros(self.lo.shape[0])
+        for c in range(self.lo.shape[0]):
+            X = self.lo[c] + self.sz[c] * np.stack([I.ravel(), J.ravel(), K.ravel()], axis=1)
+            v, g = self.evaluate(vals[c], c, X)
+            if norm == 0:
+                d2 = (v - fn(X[:, 0], X[:, 1], X[:, 2])) ** 2
+            else:
+                e = grad(X[:, 0], X[:, 1], X[:, 2])
+                d2 = sum((g[k] - e[k]) ** 2 for k in range(3))
+            sq[c] = np.prod(self.sz[c]) * (W @ d2)
+        return np.sqrt(sq.sum()), sq
+
+
+def fixed_number_flags(indicators, top_fraction, bottom_fraction):
+    """GridRefinement::refine_and_coarsen_fixed_number (serial): thresholds at the int(fraction N)-th largest / smallest
+    indicator, ties flagged, refinement wins"""
+    e = np.asarray(indicators, dtype=np.float32)
+    n_ref, n_coa = int(top_fraction * e.size), int(bottom_fraction * e.size)
+    ref = np.zeros(e.size, dtype=bool)
+    coa = np.zeros(e.size, dtype=bool)
+    if n_ref > 0:
+        ref = e >= np.sort(e)[::-1][n_ref - 1]
+    if n_coa > 0:
+        coa = (e <= np.sort(e)[n_coa - 1]) & ~ref
+    return ref, coa
+
+
+def refine_and_coarsen(cells, refine, coarsen, n_roots, root_mask):
+    """execute_coarsening_and_refinement on a forest given as a list of (level, x, y, z): refine the flagged cells keeping
+    the 2:1 balance over faces, edges and corners; then replace complete families of coarsen-flagged siblings by their
+    parent unless it would touch a cell more than one level finer.  Returns the new set of cells."""
+    def inside(l, q):
+        for d in range(3):
+            if q[d] < 0 or q[d] >= (n_roots[d] << l):
+                return False
+        r = [q[d] >> l for d in range(3)]
+        return root_mask is None or bool(root_mask[r[2]][r[1]][r[0]])
+
+    active = set(cells)
+    wish = {c for c, r, k in zip(cells, refine, coarsen) if k and not r and c[0] > 0}
+    todo = [c for c, r in zip(cells, refine) if r]
+    marked = set(todo)
+    while todo:
+        l, x, y, z = todo.pop()
+        if l == 0:
+            continue
+        for dz in (-1, 0, 1):
+            for dy in (-1, 0, 1):
+                for dx in (-1, 0, 1):
+                    q = (x + dx, y + dy, z + dz)
+                    if (dx, dy, dz) == (0, 0, 0) or not inside(l, q):
+                        continue
+                    par = (l - 1, q[0] >> 1, q[1] >> 1, q[2] >> 1)
+                    if par in active and par not in marked:
+                        marked.add(par)
+                        todo.append(par)
+    new = set()
+    for c in active:
+        if c in marked:
+            l, x, y, z = c
+            new |= {(l + 1, 2 * x + a, 2 * y + b, 2 * z + e) for a in (0, 1) for b in (0, 1) for e in (0, 1)}
+        else:
+            new.add(c)
+    parents = []
+    for c in sorted(new):
+        l, x, y, z = c
+        if l == 0 or (x | y | z) & 1:
+            continue
+        family = [(l, x + a, y + b, z + e) for a in (0, 1) for b in (0, 1) for e in (0, 1)]
+        if not all(k in new and k in wish for k in family):
+            continue
+        ok = True
+        for dz in range(-1, 3):
+            for dy in range(-1, 3):
+                for dx in range(-1, 3):
+                    if 0 <= dx <= 1 and 0 <= dy <= 1 and 0 <= dz <= 1:
+                        continue
+                    q = (x + dx, y + dy, z + dz)
+                    if not inside(l, q):
+                        continue
+                    covered = any((l - s, q[0] >> s, q[1] >> s, q[2] >> s) in new for s in range(l + 1))
+                    ok &= covered
+        if ok:
+            parents.append((family, (l - 1, x >> 1, y >> 1, z >> 1)))
+    for family, par in parents:
+        new -= set(family)
+        new.add(par)
+    return new
