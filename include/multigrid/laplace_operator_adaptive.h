@@ -69,6 +69,92 @@ namespace multigrid
     void compute_diagonal(VectorType &inverse_diagonal) const { check(mgb_adaptive_inverse_diagonal(h_, prec, inverse_diagonal.begin())); }
     void synchronize() const { check(mgb_adaptive_sync(h_)); }
 
+    // ---- the loop around the solver, LaplaceProblem::run of poisson_l/program.cc:497-602; the functions of the program
+    //      are selected by id: 0 = zero, 1 = Functions::LSingularityFunction (the exact solution on the extruded L)
+    // interpolate_boundary_values (:321-333): u = g on the Dirichlet DoFs, zero elsewhere
+    void
+    interpolate_boundary_values(DGVector<double> &u, const int function_id) const
+    {
+      check(mgb_adaptive_interpolate_boundary_values(h_, function_id, u.begin()));
+    }
+    // compute_residual(dst, src, ConstantFunction(f)) (laplace_operator.h:806-845): src carries the boundary values
+    void
+    compute_residual(DGVector<double> &dst, const DGVector<double> &src, const double f) const
+    {
+      check(mgb_adaptive_compute_residual(h_, dst.begin(), src.begin(), f));
+    }
+    // KellyErrorEstimator<dim>::estimate(dof_handler, QGauss<dim-1>(p+1), {}, solution, estimated_error_per_cell) :524-531
+    std::vector<float>
+    estimate_kelly(const DGVector<double> &solution) const
+    {
+      std::vector<float> eta(n_active_cells());
+      check(mgb_adaptive_estimate_kelly(h_, solution.begin(), eta.data()));
+      return eta;
+    }
+    // GridRefinement::refine_and_coarsen_fixed_number + execute_coarsening_and_refinement :532-541
+    void
+    refine_and_coarsen_fixed_number(const std::vector<float> &indicators, const double top_fraction, const double bottom_fraction)
+    {
+      if (indicators.size() != n_active_cells())
+        throw std::runtime_error("one indicator per active cell");
+      check(mgb_adaptive_refine_and_coarsen_fixed_number(h_, indicators.data(), top_fraction, bottom_fraction));
+    }
+    void
+    execute_coarsening_and_refinement(const std::vector<unsigned char> &refine_flags, const std::vector<unsigned char> &coarsen_flags)
+    {
+      check(mgb_adaptive_refine_and_coarsen(h_, refine_flags.data(), coarsen_flags.empty() ? nullptr : coarsen_flags.data()));
+    }
+    // VectorTools::integrate_difference (:556-575): norm 0 = L2_norm, 1 = H1_seminorm, n_q_points per direction
+    double
+    integrate_difference(const DGVector<double> &solution, const int function_id, const int norm, const int n_q_points) const
+    {
+      double r = 0;
+      check(mgb_adaptive_integrate_difference(h_, solution.begin(), function_id, norm, n_q_points, &r, nullptr));
+      return r;
+    }
+    // one cycle on the current mesh (:545-575): {CG iterations, rate, L2 error (QGauss(p+2)), H1-seminorm error (QGauss(p+1))};
+    // the solution stays on the device (solution_device(), valid until the mesh changes)
+    struct CycleResult
+    {
+      unsigned int iterations;
+      double       rate, l2_error, h1_error;
+      std::size_t  n_cells, n_dofs;
+    };
+    CycleResult
+    solve_cycle(const int function_id, const double f, const unsigned int n_smoother)
+    {
+      double stats[4];
+      check(mgb_adaptive_solve_cycle(h_, function_id, f, (int)n_smoother, stats, &solution_));
+      CycleResult r;
+      r.iterations = (unsigned int)stats[0];
+      r.rate       = stats[1];
+      r.l2_error   = stats[2];
+      r.h1_error   = stats[3];
+      r.n_cells    = n_active_cells();
+      r.n_dofs     = m();
+      return r;
+    }
+    const double *solution_device() const { return solution_; }
+    // LaplaceProblem::run (:497-602) from the current mesh: the convergence table of the program
+    std::vector<CycleResult>
+    run(const unsigned int n_cycles, const std::size_t max_size, const unsigned int n_smoother, const bool use_hyper_l)
+    {
+      std::vector<CycleResult> table;
+      for (unsigned int cycle = 0; cycle < n_cycles; ++cycle)
+        {
+          if (cycle > 0)
+            {
+              std::vector<float> eta(n_active_cells());
+              check(mgb_adaptive_estimate_kelly(h_, solution_, eta.data()));
+              refine_and_coarsen_fixed_number(eta, use_hyper_l ? 0.15 : 0.3, 0.03);
+            }
+          table.push_back(solve_cycle(use_hyper_l ? 0 : 1, use_hyper_l ? 1. : 0., n_smoother));
+          if (table.back().n_dofs > max_size)
+            break;
+        }
+      return table;
+    }
+
     // ---- the solver of poisson_l/program.cc:337-420 on this mesh (double vectors only): level operators with constrained
     // refinement edges, MGInterfaceOperator edge matrices, MGTransferMatrixFree, Chebyshev smoothers of degree n_smoother
     void setup_multigrid(const unsigned int n_smoother) { check(mgb_adaptive_mg_setup(h_, (int)n_smoother)); }
@@ -92,6 +178,7 @@ namespace multigrid
   private:
     static constexpr int prec = precision_of<number>::value;
     mgb_adaptive         h_   = nullptr;
+    double              *solution_ = nullptr; // owned by the library handle
   };
 } // namespace multigrid
 #endif

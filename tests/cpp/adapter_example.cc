@@ -188,6 +188,20 @@ main(int argc, char **argv)
                     cg.first, cg.second, err);
       }
 
+      // the adaptive loop of poisson_l/program.cc:497-602 in its default case: the L-shaped domain extruded in z, exact
+      // solution r^(2/3) sin(2 phi / 3) as Dirichlet data, Kelly estimator, 30 % refined / 3 % coarsened per cycle
+      {
+        const int           roots[3] = {2, 2, 1};
+        const unsigned char mask[4]  = {1, 1, 1, 0};
+        const double        lo[3] = {-1, -1, 0}, hi[3] = {1, 1, 1};
+        multigrid::AdaptiveLaplaceOperator<3, 2, double> lp;
+        lp.reinit(roots, mask, lo, hi, 1);
+        const auto table = lp.run(4, 1000000, 3, false);
+        for (std::size_t c = 0; c < table.size(); ++c)
+          std::printf("loop%zu_cells %zu loop%zu_dofs %zu loop%zu_its %u loop%zu_l2 %.6e loop%zu_h1 %.6e\n", c, table[c].n_cells, c,
+                      table[c].n_dofs, c, table[c].iterations, c, table[c].l2_error, c, table[c].h1_error);
+      }
+
       // DG multigrid solver as poisson_dg/program.cc:227-263: [-1,1]^3, 2 refinements, tolerance 1e-3
       multigrid::MeshDescription dmesh;
       dmesh.n_refinements = 2;

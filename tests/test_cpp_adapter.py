@@ -124,3 +124,13 @@ def test_example_driver_matches_oracle(mgb, orc):
     assert int(out["minimal_steps"]) == len(steps) and float(out["minimal_residual"]) < 1e-11
     assert abs(int(out["minimal_linear_its"]) - sum(st["linear_iterations"] for st in steps)) <= 1
     assert abs(float(out["minimal_error"]) - err) <= 1e-3 * err
+    # the adaptive loop through the adapter against the Python mirror's loop on the same forest
+    from adaptive_cases import L_EXTRUDED
+    lp = mgb.LaplaceOperatorAdaptive(2, (2, 2, 1), L_EXTRUDED, (-1., -1., 0.), (1., 1., 1.), 1)
+    table = lp.run_adaptive_loop(4, function=lp.FUNCTION_L_SINGULARITY, f=0., n_smoother=3)
+    for c, t in enumerate(table):
+        assert int(out["loop%d_cells" % c]) == t["n_cells"] and int(out["loop%d_dofs" % c]) == t["n_dofs"]
+        assert int(out["loop%d_its" % c]) == t["iterations"]
+        assert abs(float(out["loop%d_h1" % c]) - t["h1_error"]) <= 1e-5 * t["h1_error"]
+        assert abs(float(out["loop%d_l2" % c]) - t["l2_error"]) <= 1e-4 * t["l2_error"]
+    assert float(out["loop3_h1"]) < 0.45 * float(out["loop0_h1"])
