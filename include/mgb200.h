@@ -200,6 +200,12 @@ int mgb_op_Tvmult(mgb_solver s, int level, int precision, void *dst, const void 
 int mgb_op_vmult_host(mgb_solver s, int level, int precision, void *dst_host, const void *src_host);
 int mgb_op_vmult_residual(mgb_solver s, int level, int precision, const void *rhs, const void *lhs,
                           void *residual);                                                       /* :607-634 */
+/* compute_residual(dst, src, rhs_function) :103-106 (806-845), double operator: dst = (f, phi) - K src on the rows without
+ * Dirichlet condition; src is read with its Dirichlet entries (the boundary values); f sampled at the quadrature
+ * points of mgb_solver_quadrature_points (host array) or NULL for the right-hand side function of options.problem   */
+int mgb_op_compute_residual(mgb_solver s, int level, double *dst, const double *src, const double *f_values_host);
+/* MatrixFreeOperators::Base::el(row, row): the diagonal entry (1 on Dirichlet rows)                               */
+int mgb_op_el(mgb_solver s, int level, int precision, int64_t row, double *value);
 /* std::array<number,4> vmult_with_cg_update(alpha,beta,r,q,p,x)                                    :640-719 */
 int mgb_op_vmult_with_cg_update(mgb_solver s, int level, int precision, double alpha, double beta,
                                 const void *r, void *q, void *p, void *x, double sums[4]);
@@ -461,6 +467,10 @@ int mgb_adaptive_sync(mgb_adaptive h);
 int mgb_adaptive_mg_setup(mgb_adaptive h, int n_smoother);
 int mgb_adaptive_mg_n_levels(mgb_adaptive h);
 int mgb_adaptive_mg_level_info(mgb_adaptive h, int level, double info[12]);
+/* the level operator and the edge matrices of one level on float device vectors of that level (length: info[0] of
+ * mgb_adaptive_mg_level_info): which 0 = matrix[level].vmult (refinement-edge and boundary rows identity), 1 =
+ * vmult_interface_down, 2 = vmult_interface_up (MGInterfaceOperator, poisson_l/program.cc:374-383)                */
+int mgb_adaptive_mg_level_vmult(mgb_adaptive h, int level, int which, float *dst_dev, const float *src_dev);
 int mgb_adaptive_mg_vmult(mgb_adaptive h, double *dst_dev, const double *src_dev);
 /* x = 0; CG to |r| <= rel_tol |r0| (or 1e-13 absolute); history (may be NULL): residual norms, *n_history in: capacity */
 int mgb_adaptive_solve_cg(mgb_adaptive h, double *x_dev, const double *rhs_dev, double rel_tol, unsigned int *iterations,
@@ -508,6 +518,8 @@ int mgb_adaptive_solve_cycle(mgb_adaptive h, int function_id, double f, int n_sm
  * update_ghost_values: refresh the ghost planes of a z-slab (no-op on one GPU).                       */
 int mgb_vec_dot(mgb_solver s, int level, int precision, const void *a, const void *b, double *result);
 int mgb_vec_sadd(mgb_solver s, int level, int precision, void *y, double sy, double ax, const void *x);
+/* dst = src converted to dst_precision (src has the other precision): Vector::operator=(const Vector<OtherNumber> &)  */
+int mgb_vec_convert(mgb_solver s, int level, int dst_precision, void *dst, const void *src);
 int mgb_vec_set(mgb_solver s, int level, int precision, void *y, double value);
 int mgb_vec_update_ghost_values(mgb_solver s, int level, int precision, void *v);
 /* compress(VectorOperation::add) and zero_out_ghost_values of LinearAlgebra::distributed::Vector (the calls around

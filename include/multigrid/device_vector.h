@@ -91,6 +91,16 @@ namespace multigrid
       check(mgb_vec_set(s_, level_, precision_of<Number>::value, data_, (double)value));
       return *this;
     }
+    // Vector::operator=(const Vector<OtherNumber> &): precision-converting copy (same solver and level)
+    template <typename Other>
+    typename std::enable_if<!std::is_same<Other, Number>::value, DeviceVector &>::type
+    operator=(const DeviceVector<Other> &x)
+    {
+      if (data_ == nullptr)
+        reinit(x.solver(), x.level());
+      check(mgb_vec_convert(s_, level_, precision_of<Number>::value, data_, x.begin()));
+      return *this;
+    }
     Number
     operator*(const DeviceVector &other) const
     {

@@ -84,8 +84,64 @@ namespace multigrid
       check(mgb_op_inverse_diagonal(s_, level_, prec, inverse_diagonal.begin()));
     }
 
+    // get_matrix_diagonal_inverse(): the vector of compute_diagonal(), computed on first use
+    const VectorType &
+    get_matrix_diagonal_inverse() const
+    {
+      if (inverse_diagonal_.begin() == nullptr)
+        compute_diagonal(inverse_diagonal_);
+      return inverse_diagonal_;
+    }
+    // MatrixFreeOperators::Base::el(row, col): only diagonal entries exist
+    number
+    el(const std::size_t row, const std::size_t col) const
+    {
+      if (row != col)
+        throw std::runtime_error("matrix-free operator: only diagonal entries are available");
+      double v = 0;
+      check(mgb_op_el(s_, level_, prec, (int64_t)row, &v));
+      return (number)v;
+    }
+    // vmult_interface_down / vmult_interface_up (MatrixFreeOperators::Base): the coupling over refinement edges; the
+    // levels of a globally refined mesh have none, and deal.II returns dst = 0 there
+    void vmult_interface_down(VectorType &dst, const VectorType &) const { dst = number(0); }
+    void vmult_interface_up(VectorType &dst, const VectorType &) const { dst = number(0); }
+    // laplace_operator.h:103-106 (806-845) for the double operator: dst = (f, phi) - K src on the rows without Dirichlet
+    // condition, src carrying the boundary values; rhs_function(x, y, z) is sampled at the library's quadrature points
+    template <typename RightHandSide>
+    void
+    compute_residual(VectorType &dst, const VectorType &src, const RightHandSide &rhs_function) const
+    {
+      static_assert(std::is_same<number, double>::value, "compute_residual runs on the double operator (matrix_dp)");
+      const int64_t nq = mgb_solver_n_quadrature_points(s_, level_);
+      if (nq < 0)
+        throw std::runtime_error(std::string("mgb200: ") + mgb_last_error());
+      std::vector<double> xyz(3 * (std::size_t)nq), f((std::size_t)nq);
+      check(mgb_solver_quadrature_points(s_, level_, xyz.data()));
+      for (std::size_t q = 0; q < f.size(); ++q)
+        f[q] = rhs_function(xyz[3 * q], xyz[3 * q + 1], xyz[3 * q + 2]);
+      check(mgb_op_compute_residual(s_, level_, dst.begin(), src.begin(), f.data()));
+    }
+    // laplace_operator.h:108-109 (359-432): the coefficient sampled at the quadrature points; sets it on the float and
+    // the double operator of the level (call MultigridSolver::reinit_smoothers() after the last level is set)
+    template <typename Coefficient>
+    void
+    evaluate_coefficient(const Coefficient &coefficient)
+    {
+      const int64_t nq = mgb_solver_n_quadrature_points(s_, level_);
+      if (nq < 0)
+        throw std::runtime_error(std::string("mgb200: ") + mgb_last_error());
+      std::vector<double> xyz(3 * (std::size_t)nq), c((std::size_t)nq);
+      check(mgb_solver_quadrature_points(s_, level_, xyz.data()));
+      for (std::size_t q = 0; q < c.size(); ++q)
+        c[q] = coefficient(xyz[3 * q], xyz[3 * q + 1], xyz[3 * q + 2]);
+      check(mgb_solver_set_coefficient_values(s_, level_, c.data()));
+      inverse_diagonal_.clear();
+    }
+
   private:
     static constexpr int prec = precision_of<number>::value;
+    mutable VectorType   inverse_diagonal_;
     mgb_solver           s_     = nullptr;
     int                  level_ = 0;
   };

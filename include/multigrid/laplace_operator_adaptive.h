@@ -165,6 +165,27 @@ namespace multigrid
     {
       check(mgb_adaptive_mg_vmult(h_, dst.begin(), src.begin()));
     }
+    // the level operator and the edge matrices of level `level` of the local-smoothing hierarchy on float level vectors
+    // (mg_matrices[level].vmult, vmult_interface_down, vmult_interface_up; poisson_l/program.cc:283-291,374-383)
+    std::size_t
+    level_size(const unsigned int level) const
+    {
+      double info[12];
+      check(mgb_adaptive_mg_level_info(h_, (int)level, info));
+      return (std::size_t)info[0];
+    }
+    void level_vmult(const unsigned int level, DGVector<float> &dst, const DGVector<float> &src) const
+    {
+      check(mgb_adaptive_mg_level_vmult(h_, (int)level, 0, dst.begin(), src.begin()));
+    }
+    void vmult_interface_down(const unsigned int level, DGVector<float> &dst, const DGVector<float> &src) const
+    {
+      check(mgb_adaptive_mg_level_vmult(h_, (int)level, 1, dst.begin(), src.begin()));
+    }
+    void vmult_interface_up(const unsigned int level, DGVector<float> &dst, const DGVector<float> &src) const
+    {
+      check(mgb_adaptive_mg_level_vmult(h_, (int)level, 2, dst.begin(), src.begin()));
+    }
     // SolverCG with ReductionControl(m(), 1e-13, rel_tol) from a zero start vector; (iterations, reduction per iteration)
     std::pair<unsigned int, double>
     solve_cg(DGVector<double> &x, const DGVector<double> &rhs, const double rel_tol = 1e-9) const

@@ -152,6 +152,10 @@ SYMBOLS = {
     "mgb_transfer_restrict_and_add": (_i, [_vp, _i, _vp, _vp]),
     "mgb_transfer_prolongate_no_boundary": (_i, [_vp, _i, _vp, _vp]),
     "mgb_vec_dot": (_i, [_vp, _i, _i, _vp, _vp, _dp]),
+    "mgb_vec_convert": (_i, [_vp, _i, _i, _vp, _vp]),
+    "mgb_op_compute_residual": (_i, [_vp, _i, _vp, _vp, _dp]),
+    "mgb_op_el": (_i, [_vp, _i, _i, C.c_int64, _dp]),
+    "mgb_adaptive_mg_level_vmult": (_i, [_vp, _i, _i, _vp, _vp]),
     "mgb_noalloc_dot": (_i, [_i, C.c_int64, _vp, _vp, _vp, _vp]),
     "mgb_vec_sadd": (_i, [_vp, _i, _i, _vp, _d, _d, _vp]),
     "mgb_vec_set": (_i, [_vp, _i, _i, _vp, _d]),
@@ -437,6 +441,26 @@ class LaplaceOperator:
         _check(lib().mgb_op_vmult_residual(self.solver.h, self.level, self.precision, _ptr(rhs), _ptr(lhs),
                                            _ptr(residual)))
         self.solver.sync()
+
+    def compute_residual(self, dst, src, rhs_function=None):
+        """laplace_operator.h:103-106: dst = (f, phi) - K src on the rows without Dirichlet condition (double operator);
+        rhs_function(x, y, z) on arrays, None = the right-hand side of the solver's problem"""
+        self._chk(dst, src)
+        f = None
+        if rhs_function is not None:
+            xq = self.solver.quadrature_points(self.level)
+            f = np.ascontiguousarray(rhs_function(xq[:, 0], xq[:, 1], xq[:, 2]), dtype=np.float64)
+        self.solver._torch_sync()
+        _check(lib().mgb_op_compute_residual(self.solver.h, self.level, _ptr(dst), _ptr(src),
+                                             f.ctypes.data_as(_dp) if f is not None else None))
+
+    def el(self, row, col=None):
+        """MatrixFreeOperators::Base::el(row, row)"""
+        if col is not None and col != row:
+            raise MgbError("matrix-free operator: only diagonal entries are available")
+        v = C.c_double()
+        _check(lib().mgb_op_el(self.solver.h, self.level, self.precision, int(row), C.byref(v)))
+        return v.value
 
     def vmult_with_cg_update(self, alpha, beta, r, q, p, x):
         self._chk(r, q, p, x)
@@ -1380,6 +1404,15 @@ class LaplaceOperatorAdaptive:
         v = np.zeros(12)
         _check(lib().mgb_adaptive_mg_level_info(self.h, level, v.ctypes.data_as(_dp)))
         return dict(zip(self.MG_INFO, v))
+
+    def mg_level_vmult(self, level, which, dst, src):
+        """which 0: matrix[level].vmult, 1: vmult_interface_down, 2: vmult_interface_up, on float level vectors"""
+        import torch
+        assert dst.dtype == torch.float32 and src.dtype == torch.float32
+        n = int(self.mg_level_info(level)["n_dofs"])
+        assert dst.numel() == src.numel() == n
+        torch.cuda.synchronize()
+        _check(lib().mgb_adaptive_mg_level_vmult(self.h, int(level), int(which), _ptr(dst), _ptr(src)))
 
     def mg_vmult(self, dst, src):
         """PreconditionMG::vmult: one local-smoothing V-cycle (float) on a double vector of the active mesh"""

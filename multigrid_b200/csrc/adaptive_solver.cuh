@@ -835,6 +835,33 @@ extern "C"
     AD_CATCH
   }
 
+  // level operator and edge matrices of the local smoothing on float device vectors of the level (mg_level_info: n_dofs):
+  // which = 0: matrix[level].vmult; 1: vmult_interface_down; 2: vmult_interface_up (MatrixFreeOperators::Base, used
+  // through MGInterfaceOperator, poisson_l/program.cc:374-383); dst is overwritten
+  int
+  mgb_adaptive_mg_level_vmult(mgb_adaptive h, int level, int which, float *dst_dev, const float *src_dev)
+  {
+    AD_TRY
+    AdaptiveSolver &s = ADS(h);
+    if (level < 0 || level >= (int)s.levels.size())
+      throw std::runtime_error("level out of range");
+    if (which < 0 || which > 2 || !dst_dev || !src_dev)
+      throw std::runtime_error("which: 0 vmult, 1 vmult_interface_down, 2 vmult_interface_up");
+    AdLevel &lv = s.levels[level];
+    if (which == 0)
+      s.apply_level(lv, dst_dev, src_dev);
+    else
+      {
+        MGB_AD_CHECK(cudaMemsetAsync(dst_dev, 0, (size_t)lv.n_dofs * sizeof(float), s.stream));
+        if (which == 1)
+          s.apply_edge(lv, dst_dev, src_dev, lv.edge_in, lv.edge_out);
+        else
+          s.apply_edge(lv, dst_dev, src_dev, lv.edge_out, lv.edge_in);
+      }
+    MGB_AD_CHECK(cudaStreamSynchronize(s.stream));
+    AD_CATCH
+  }
+
   int
   mgb_adaptive_mg_vmult(mgb_adaptive h, double *dst_dev, const double *src_dev)
   {

@@ -2100,6 +2100,38 @@ namespace mgb
       ctx.sync();
     }
 
+    // LaplaceOperator::compute_residual(dst, src, rhs_function) (laplace_operator.h:103-106, 806-845) on the double operator
+    // of `level`: dst = (f, phi) - K src on the rows without Dirichlet condition, src read with its Dirichlet entries; f by
+    // samples at the quadrature points (host) or, if null, the right-hand side function of the solver's problem
+    void
+    compute_residual(const int level, double *dst, const double *src, const double *f_host)
+    {
+      const LevelDesc L = levels[level]->d;
+      const size_t    N = L.n_dofs;
+      if (caller_scratch.n < N)
+        caller_scratch.alloc(N, ctx.stream);
+      double *neg = caller_scratch.p;
+      foreach (ctx, N, [=] __device__(size_t i) { neg[i] = -src[i]; });
+      MGB_CUDA_CHECK(cudaMemsetAsync(dst, 0, N * sizeof(double), ctx.stream));
+      matrix_dp[level]->apply(APPLY_ADD, dst, neg, nullptr, nullptr, 0, 0, 0, /*read_plain=*/true);
+      RhsArgs R;
+      R.L     = L;
+      R.geom  = geom;
+      R.dst   = dst;
+      R.fn_id = fn_rhs;
+      if (f_host)
+        {
+          stage_values(f_host, n_quadrature_points(level));
+          R.fn_id  = FN_ZERO;
+          R.values = caller_values.p;
+        }
+      degree_kernels(opt.degree).rhs_values(R, ctx.stream);
+      ctx.check_launch();
+      levels[level]->update_ghosts(dst);
+      ctx.sync();
+    }
+    DVec<double> caller_scratch;
+
     // the exact solution for compute_l2_error, sampled at the quadrature points of `level`
     void
     set_exact_solution_values(const int level, const double *u_host)
@@ -3627,6 +3659,65 @@ extern "C"
       vec_ops<double>(m, level, 0, const_cast<void *>(a), b, 0, 0, result);
     else
       vec_ops<float>(m, level, 0, const_cast<void *>(a), b, 0, 0, result);
+    MGB_CATCH
+  }
+
+  int
+  mgb_vec_convert(mgb_solver s, int level, int dst_precision, void *dst, const void *src)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    const size_t N     = m.levels[level]->d.n_dofs;
+    if (dst_precision == MGB_F64)
+      convert(m.ctx, static_cast<double *>(dst), static_cast<const float *>(src), N);
+    else if (dst_precision == MGB_F32)
+      convert(m.ctx, static_cast<float *>(dst), static_cast<const double *>(src), N);
+    else
+      throw std::runtime_error("precision must be MGB_F32 or MGB_F64");
+    MGB_CATCH
+  }
+
+  int
+  mgb_op_compute_residual(mgb_solver s, int level, double *dst, const double *src, const double *f_values_host)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    if (!dst || !src)
+      throw std::runtime_error("null argument");
+    m.compute_residual(check_level(m, level), dst, src, f_values_host);
+    MGB_CATCH
+  }
+
+  int
+  mgb_op_el(mgb_solver s, int level, int precision, int64_t row, double *value)
+  {
+    MGB_TRY
+    MultigridSolver &m = S(s);
+    level              = check_level(m, level);
+    if (row < 0 || (size_t)row >= m.levels[level]->d.n_dofs || !value)
+      throw std::runtime_error("row out of range");
+    // MatrixFreeOperators::Base::el(row, row) = 1 / inverse_diagonal(row)
+    if (precision == MGB_F64)
+      {
+        if (!m.matrix_dp[level]->inverse_diagonal.p)
+          m.matrix_dp[level]->compute_diagonal();
+        double v;
+        MGB_CUDA_CHECK(cudaMemcpyAsync(&v, m.matrix_dp[level]->inverse_diagonal.p + row, sizeof(double), cudaMemcpyDeviceToHost, m.ctx.stream));
+        m.ctx.sync();
+        *value = 1. / v;
+      }
+    else if (precision == MGB_F32)
+      {
+        if (!m.matrix[level]->inverse_diagonal.p)
+          m.matrix[level]->compute_diagonal();
+        float v;
+        MGB_CUDA_CHECK(cudaMemcpyAsync(&v, m.matrix[level]->inverse_diagonal.p + row, sizeof(float), cudaMemcpyDeviceToHost, m.ctx.stream));
+        m.ctx.sync();
+        *value = 1. / (double)v;
+      }
+    else
+      throw std::runtime_error("precision must be MGB_F32 or MGB_F64");
     MGB_CATCH
   }
 

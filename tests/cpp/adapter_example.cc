@@ -59,6 +59,27 @@ main(int argc, char **argv)
       A.vmult_residual(q, p, r); // r = q - A p = 0
       std::printf("operator m %zu pAp %.12e residual_norm %.3e\n", A.m(), pq, (double)r.l2_norm());
 
+      // the rest of the operator concept: diagonal entry, precision-converting assignment, interface matrices (zero on a
+      // globally refined mesh), compute_residual with a right-hand side function of the caller
+      {
+        const double                 d0 = A.el(A.m() / 2, A.m() / 2);
+        multigrid::DeviceVector<float> pf;
+        pf = p; // double -> float
+        multigrid::DeviceVector<double> back;
+        back = pf;
+        back.add(-1.0, p);
+        A.vmult_interface_down(q, p);
+        const double                 idn = q.l2_norm();
+        multigrid::DeviceVector<double> zero, res;
+        A.initialize_dof_vector(zero);
+        A.initialize_dof_vector(res);
+        zero = 0.0;
+        A.compute_residual(res, zero, [](const double x, const double y, const double z) { return 1. + x * y - z; });
+        const double                 load = res * p; // sum of (f, phi_i) over the interior rows (p = 1)
+        std::printf("el_mid %.12e convert_roundtrip %.3e interface_down_norm %.3e load_sum %.12e diag_inv_norm %.12e\n", d0,
+                    (double)back.l2_norm(), idn, load, (double)A.get_matrix_diagonal_inverse().l2_norm());
+      }
+
       // the third problem on one coarse cell of hyper_shell(0, 0.5, 1, 6) with 2 refinements (curved cells, six-entry
       // coefficient), handed over as samples at the library's quadrature / support points
       {

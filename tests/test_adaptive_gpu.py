@@ -116,3 +116,33 @@ def test_local_smoothing_solver(mgb, torch, name):
     r = torch.zeros_like(src)
     op.vmult(r, x)
     assert float((r - src).norm()) <= 2e-9 * float(src.norm())
+
+
+def test_level_operator_and_interface_matrices(mgb, torch):
+    """mg_matrices[level].vmult, vmult_interface_down and vmult_interface_up of the local-smoothing hierarchy through the
+    C ABI against the oracle's level matrices (poisson_l/program.cc:283-291,374-383)"""
+    from oracle import adaptive_oracle
+    op = make(mgb, "hyper_l_p2")
+    lo, sz = op.cell_boxes()
+    root = (np.array(op.upper) - np.array(op.lower)) / np.array(op.n_roots)
+    o = adaptive_oracle.LocalSmoothingOracle(op.degree, lo, sz, root, op.lower, n_smoother=3)
+    op.setup_multigrid(3)
+    rng = np.random.default_rng(4)
+    checked = 0
+    for l in range(o.n_levels):
+        n = o.levels[l]["n"]
+        x = rng.standard_normal(n).astype(np.float32)
+        dx = torch.tensor(x, device="cuda")
+        out = torch.zeros_like(dx)
+        op.mg_level_vmult(l, 0, out, dx)
+        ref = o.levels[l]["A"] @ x.astype(np.float64)
+        assert rel(out.cpu().numpy(), ref) <= 2e-6, l
+        for which, fn in ((1, o.interface_down), (2, o.interface_up)):
+            op.mg_level_vmult(l, which, out, dx)
+            ref = fn(l, x.astype(np.float64))
+            if np.abs(ref).max() == 0:
+                assert float(out.abs().max()) == 0.0
+            else:
+                assert rel(out.cpu().numpy(), ref) <= 2e-6, (l, which)
+                checked += 1
+    assert checked >= 2

@@ -60,6 +60,14 @@ def test_example_driver_matches_oracle(mgb, orc):
     ones = np.ones(o.n_dofs())
     assert abs(float(out["pAp"]) - ones @ o.vmult(ones)) <= 1e-10 * abs(ones @ o.vmult(ones))
     assert float(out["residual_norm"]) <= 1e-10
+    # operator concept extras: el, converting assignment, interface matrices, compute_residual with a caller's function
+    inv = o.inverse_diagonal_dp()
+    assert abs(float(out["diag_inv_norm"]) - np.linalg.norm(inv)) <= 1e-10 * np.linalg.norm(inv)
+    assert float(out["convert_roundtrip"]) == 0.0 and float(out["interface_down_norm"]) == 0.0
+    assert float(out["el_mid"]) > 0
+    o.set_problem(right_hand_side=lambda x, y, z: 1. + x * y - z)
+    load = o.get_vector(orc.VEC_RHS).sum()
+    assert abs(float(out["load_sum"]) - load) <= 1e-10 * abs(load)
     # the third problem of the example (defined only in tests/cpp/adapter_example.cc) against the oracle with the same
     # functions handed over as samples
     u3 = lambda x, y, z: np.exp(x) * np.sin(2 * y) * np.cos(z)

@@ -433,3 +433,44 @@ def test_properties_at_scale(mgb, torch):
     s.solve(False)
     e = s.compute_l2_error()
     assert abs(e - row[3]) <= 1e-2 * row[3], e
+
+
+def test_operator_concept_extras(mgb, orc, torch):
+    """compute_residual(dst, src, rhs_function) (laplace_operator.h:103-106) with a function and boundary data of the caller,
+    el(row, row), and the precision-converting vector assignment, against the oracle"""
+    P = Pair(mgb, orc, torch, 3, (1, 2, 1), 2, lower=(0., 0., 0.), upper=(1., 1.5, 0.8))
+    L = P.g.n_levels - 1
+    f = lambda x, y, z: np.cos(2 * x) * y + z * z
+    u = lambda x, y, z: np.sin(x + 2 * y) * np.exp(0.5 * z)
+    P.o.set_problem(right_hand_side=f, boundary_values=u)
+    ref = P.o.get_vector(orc.VEC_RHS)
+    xs = P.g.support_points(L)
+    src_lib = u(xs[:, 0], xs[:, 1], xs[:, 2])
+    nd = P.g.dof_grid(L)
+    lex = P.lex(L)
+    interior = np.ones(nd[::-1], dtype=bool)
+    interior[1:-1, 1:-1, 1:-1] = False
+    src = np.zeros(P.g.n_dofs())
+    src[lex] = np.where(interior.ravel(), src_lib[lex], 0.)          # boundary values only, zero inside
+    op = P.g.matrix_dp()
+    dst = op.initialize_dof_vector()
+    op.compute_residual(dst, torch.tensor(src, device="cuda"), f)
+    assert rel(P.to_lex(dst, L), ref) <= 1e-12
+    # the built-in right-hand side of the problem with homogeneous data = the solver's own rhs
+    P2 = Pair(mgb, orc, torch, 2, (1, 1, 1), 2)
+    op2 = P2.g.matrix_dp()
+    dst2 = op2.initialize_dof_vector()
+    op2.compute_residual(dst2, torch.zeros_like(dst2))
+    assert rel(P2.to_lex(dst2, -1), P2.o.get_vector(orc.VEC_RHS)) <= 1e-12
+    inv = P2.o.inverse_diagonal_dp()
+    lex2 = P2.lex(-1)
+    for i in (0, 7, inv.size // 2, inv.size - 1):
+        assert abs(op2.el(int(lex2[i])) - 1. / inv[i]) <= 1e-12 / inv[i]
+    with pytest.raises(mgb.MgbError):
+        op2.el(1, 2)
+    v = torch.rand(P2.g.n_dofs(), dtype=torch.float64, device="cuda")
+    w = torch.zeros(P2.g.n_dofs(), dtype=torch.float32, device="cuda")
+    import ctypes as C
+    assert mgb.lib().mgb_vec_convert(P2.g.h, P2.g.n_levels - 1, mgb.F32, C.c_void_p(w.data_ptr()), C.c_void_p(v.data_ptr())) == 0
+    P2.g.sync()
+    assert torch.equal(w, v.float())
