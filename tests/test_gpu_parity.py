@@ -456,11 +456,11 @@ def test_operator_concept_extras(mgb, orc, torch):
     dst = op.initialize_dof_vector()
     op.compute_residual(dst, torch.tensor(src, device="cuda"), f)
     assert rel(P.to_lex(dst, L), ref) <= 1e-12
-    # the built-in right-hand side of the problem with homogeneous data = the solver's own rhs
+    # the built-in right-hand side function with the problem's boundary values in src = the solver's own rhs
     P2 = Pair(mgb, orc, torch, 2, (1, 1, 1), 2)
     op2 = P2.g.matrix_dp()
     dst2 = op2.initialize_dof_vector()
-    op2.compute_residual(dst2, torch.zeros_like(dst2))
+    op2.compute_residual(dst2, P2.to_dev(P2.o.get_vector(orc.VEC_SOLUTION), -1))     # before a solve: boundary values, zero inside
     assert rel(P2.to_lex(dst2, -1), P2.o.get_vector(orc.VEC_RHS)) <= 1e-12
     inv = P2.o.inverse_diagonal_dp()
     lex2 = P2.lex(-1)
